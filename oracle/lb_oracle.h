@@ -1,0 +1,114 @@
+/*
+ * lb_oracle.h -- TEST INFRASTRUCTURE ONLY. Not part of the product.
+ *
+ * Plain-C CPU restatement of the Ludwig (zazu29/ludwig v0.20.1) lattice
+ * Boltzmann time-step hot path, used as the parity checker for the CUDA
+ * path in ludwig_b200/. Only tests/, __graft_entry__.smoke() and bench.py's
+ * cpu_baseline / --impl reference legs may load the library built from it.
+ *
+ * Parity status: PINNED. tests/test_oracle_vs_ref.py compares every function
+ * here with the unmodified reference compiled in place (oracle/_ref, built by
+ * oracle/Makefile) and tests/golden/ holds vectors dumped from that build
+ * (generator: tests/golden/make_golden.py).
+ *
+ * All arrays use the reference's HOST layout (serial build, src/memory.h:124-130):
+ *   f[(index*ndist + n)*nvel + p]        LB_ADDR, src/lb_data.h:136
+ *   u/force[index*3 + a], rho[index], phi[index], grad[index*3 + a], delsq[index]
+ * with index = (ic*nall[Y] + jc)*nall[Z] + kc over the halo-inclusive local
+ * box, ic = 0..nall[X]-1 (src/coords.c:617-631 with nhalo = 1).
+ */
+
+#ifndef LB_ORACLE_H
+#define LB_ORACLE_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ORC_NVELMAX 27
+
+enum { ORC_RELAX_M10 = 0, ORC_RELAX_BGK = 1, ORC_RELAX_TRT = 2 };
+
+typedef struct orc_model_s {
+  int ndim;
+  int nvel;
+  int nhydro;                              /* 1 + ndim + ndim(ndim+1)/2 */
+  int cv[ORC_NVELMAX][3];
+  double wv[ORC_NVELMAX];
+  double na[ORC_NVELMAX];                  /* mode normalisers */
+  double ma[ORC_NVELMAX][ORC_NVELMAX];     /* modes from f   */
+  double mi[ORC_NVELMAX][ORC_NVELMAX];     /* f from modes   */
+  /* Forward matrix as the reference's collision actually applies it. It is
+   * ma except for D3Q19, whose hand-unrolled d3q19_f2mode_chunk has a zero
+   * where ma[13][4] = -1 (src/collision.c:2300, "fchunk[4]*c0"). Invisible
+   * with the default M10 scheme (ghost modes are fully relaxed) but part of
+   * the reference's BGK/TRT results, so parity needs it. */
+  double maf[ORC_NVELMAX][ORC_NVELMAX];
+} orc_model_t;
+
+typedef struct orc_param_s {
+  double rho0;
+  double eta_shear;
+  double eta_bulk;
+  double force_global[3];
+  int    nrelax;
+  /* binary fluid (symmetric free energy) */
+  double mobility;
+  double a, b, kappa;
+} orc_param_t;
+
+typedef struct orc_box_s {
+  int nlocal[3];
+  int nall[3];       /* nlocal + 2 */
+  long nsite;
+} orc_box_t;
+
+int  orc_model_init(int nvel, orc_model_t * model);
+int  orc_box_init(const int nlocal[3], orc_box_t * box);
+long orc_index(const orc_box_t * box, int ic, int jc, int kc); /* 1-based */
+
+int orc_rtau(const orc_model_t * model, const orc_param_t * prm,
+	     double rtau[ORC_NVELMAX]);
+
+int orc_equilib_set(const orc_model_t * model, int ndist, double * f,
+		    long index, double rho, const double u[3]);
+
+int orc_collide_mrt(const orc_model_t * model, const orc_box_t * box,
+		    const orc_param_t * prm, int ndist, double * f,
+		    const double * force, double * rho, double * u);
+
+int orc_collide_binary(const orc_model_t * model, const orc_box_t * box,
+		       const orc_param_t * prm, double * f,
+		       const double * force, double * u,
+		       const double * phi, const double * grad,
+		       const double * delsq);
+
+int orc_halo_periodic(const orc_box_t * box, int nfel, double * data);
+int orc_propagate(const orc_model_t * model, const orc_box_t * box,
+		  int ndist, const double * f, double * fprime);
+
+int orc_phi_from_g(const orc_model_t * model, const orc_box_t * box,
+		   const double * f, double * phi);
+int orc_grad_7pt(const orc_box_t * box, const double * phi,
+		 double * grad, double * delsq);
+
+int orc_fill(const orc_box_t * box, int nf, const double * v, double * data);
+
+/* stats[0..7] = sum rho, sum rho^2 (about mean is left to caller), min, max,
+ * momentum x, y, z, sum phi. Interior sites only. */
+int orc_stats(const orc_model_t * model, const orc_box_t * box, int ndist,
+	      const double * f, double stats[8]);
+
+/* One or more full time steps in the order of src/ludwig.c:530-862. All
+ * work arrays are caller-provided; f and fprime are swapped internally and
+ * the result is always left in f. Returns 0. */
+int orc_step(const orc_model_t * model, const orc_box_t * box,
+	     const orc_param_t * prm, int ndist, int nsteps,
+	     double * f, double * fprime, double * rho, double * u,
+	     double * force, double * phi, double * grad, double * delsq);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif

@@ -1,0 +1,331 @@
+/*
+ * lb_oracle_fields.c -- TEST INFRASTRUCTURE ONLY. See lb_oracle.h.
+ *
+ * Binary (two-distribution) collision, halo, propagation, order parameter,
+ * gradient, fills, diagnostics and the time loop of the CPU restatement.
+ */
+
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "lb_oracle.h"
+
+void orc_relax_modes(const orc_model_t * model, const double * rtau,
+		     const double force[3], const double sextra[3][3],
+		     double * m, double * rho_out, double u[3]);
+void orc_f_to_modes(const orc_model_t * model, const double * fs, double * m);
+void orc_modes_to_f(const orc_model_t * model, const double * m, double * fs);
+
+/* ------------------------------------------------------------------------
+ * orc_collide_binary: src/collision.c:720-1027 (lb_collision_mrt2_site),
+ * with the symmetric free energy stress and chemical potential of
+ * src/symmetric.c:371-420 and :307-320. ndist = 2, three dimensions only
+ * (src/collision.c:618). Same extent as the single-fluid collision.
+ * u is written; rho is NOT (src/collision.c:824-829).
+ * ---------------------------------------------------------------------- */
+
+int orc_collide_binary(const orc_model_t * model, const orc_box_t * box,
+		       const orc_param_t * prm, double * f,
+		       const double * force, double * u,
+		       const double * phi, const double * grad,
+		       const double * delsq) {
+
+  const int nvel = model->nvel;
+  const int ndist = 2;
+  const double cs2 = 1.0/3.0;
+  const long first = orc_index(box, 1, 0, 0);
+  const long last  = orc_index(box, box->nlocal[0] + 1, 0, 0);
+  const double rtau2 = 2.0/(1.0 + 2.0*prm->mobility);
+  double rtau[ORC_NVELMAX];
+
+  if (model->ndim != 3) return -1;
+  if (orc_rtau(model, prm, rtau) != 0) return -1;
+
+  #pragma omp parallel for schedule(static)
+  for (long index = first; index < last; index++) {
+
+    double m[ORC_NVELMAX];
+    double fl[3], ul[3], rl;
+    double sth[3][3];
+    double * fs = f + (index*ndist + 0)*nvel;
+    double * gs = f + (index*ndist + 1)*nvel;
+    const double ph = phi[index];
+    const double dsq = delsq[index];
+    const double * gr = grad + 3*index;
+
+    for (int a = 0; a < 3; a++) {
+      fl[a] = prm->force_global[a] + force[3*index + a];
+    }
+
+    {
+      double p0 = 0.5*prm->a*ph*ph + 0.75*prm->b*ph*ph*ph*ph
+	- prm->kappa*ph*dsq
+	- 0.5*prm->kappa*(gr[0]*gr[0] + gr[1]*gr[1] + gr[2]*gr[2]);
+      for (int a = 0; a < 3; a++) {
+	for (int b = 0; b < 3; b++) {
+	  double dab = (a == b);
+	  sth[a][b] = p0*dab + prm->kappa*gr[a]*gr[b];
+	}
+      }
+    }
+
+    orc_f_to_modes(model, fs, m);
+    orc_relax_modes(model, rtau, fl, (const double (*)[3]) sth, m, &rl, ul);
+    orc_modes_to_f(model, m, fs);
+    for (int a = 0; a < 3; a++) u[3*index + a] = ul[a];
+
+    /* Order parameter distribution */
+    {
+      double mu = prm->a*ph + prm->b*ph*ph*ph - prm->kappa*dsq;
+      double jphi[3] = {0.0, 0.0, 0.0};
+      double sphi[3][3];
+
+      for (int p = 1; p < nvel; p++) {
+	for (int a = 0; a < 3; a++) jphi[a] += model->cv[p][a]*gs[p];
+      }
+
+      for (int a = 0; a < 3; a++) {
+	for (int b = 0; b < 3; b++) {
+	  double dab = (a == b);
+	  sphi[a][b] = ph*ul[a]*ul[b] + mu*dab;
+	}
+	jphi[a] = jphi[a] - rtau2*(jphi[a] - ph*ul[a]);
+      }
+
+      for (int p = 0; p < nvel; p++) {
+	double jdotc = 0.0;
+	double sphidotq = 0.0;
+	for (int a = 0; a < 3; a++) {
+	  jdotc += jphi[a]*model->cv[p][a];
+	  for (int b = 0; b < 3; b++) {
+	    double dab = (a == b);
+	    sphidotq += sphi[a][b]*(model->cv[p][a]*model->cv[p][b] - cs2*dab);
+	  }
+	}
+	gs[p] = model->wv[p]*(jdotc*3.0 + sphidotq*4.5) + ph*(p == 0);
+      }
+    }
+  }
+
+  return 0;
+}
+
+/* ------------------------------------------------------------------------
+ * orc_halo_periodic: one-rank periodic halo of width 1 for a field with
+ * nfel doubles per site. Restates the net effect of halo_swap_packed for
+ * cartsz = 1 in every direction (src/halo_swap.c:709-1063): x faces over the
+ * full y,z extent, then y over full x,z, then z over full x,y, so edges and
+ * corners come for free. Pure copies: bit-exact.
+ * ---------------------------------------------------------------------- */
+
+int orc_halo_periodic(const orc_box_t * box, int nfel, double * data) {
+
+  const int nx = box->nlocal[0], ny = box->nlocal[1], nz = box->nlocal[2];
+  const size_t sz = (size_t) nfel*sizeof(double);
+
+  for (int j = 0; j < box->nall[1]; j++) {
+    for (int k = 0; k < box->nall[2]; k++) {
+      memcpy(data + nfel*orc_index(box, 0, j, k),
+	     data + nfel*orc_index(box, nx, j, k), sz);
+      memcpy(data + nfel*orc_index(box, nx + 1, j, k),
+	     data + nfel*orc_index(box, 1, j, k), sz);
+    }
+  }
+  for (int i = 0; i < box->nall[0]; i++) {
+    for (int k = 0; k < box->nall[2]; k++) {
+      memcpy(data + nfel*orc_index(box, i, 0, k),
+	     data + nfel*orc_index(box, i, ny, k), sz);
+      memcpy(data + nfel*orc_index(box, i, ny + 1, k),
+	     data + nfel*orc_index(box, i, 1, k), sz);
+    }
+  }
+  for (int i = 0; i < box->nall[0]; i++) {
+    for (int j = 0; j < box->nall[1]; j++) {
+      memcpy(data + nfel*orc_index(box, i, j, 0),
+	     data + nfel*orc_index(box, i, j, nz), sz);
+      memcpy(data + nfel*orc_index(box, i, j, nz + 1),
+	     data + nfel*orc_index(box, i, j, 1), sz);
+    }
+  }
+
+  return 0;
+}
+
+/* ------------------------------------------------------------------------
+ * orc_propagate: src/propagation.c:162-212. Pull: interior sites take
+ * f(r - c_p); y,z halo sites of planes 1..nlocal[X] copy themselves; the
+ * two x halo planes of fprime are not written. Bit-exact.
+ * ---------------------------------------------------------------------- */
+
+int orc_propagate(const orc_model_t * model, const orc_box_t * box,
+		  int ndist, const double * f, double * fprime) {
+
+  const int nvel = model->nvel;
+  const long sx = (long) box->nall[1]*box->nall[2];
+  const long sy = box->nall[2];
+
+  #pragma omp parallel for schedule(static)
+  for (int ic = 1; ic <= box->nlocal[0]; ic++) {
+    for (int jc = 0; jc < box->nall[1]; jc++) {
+      for (int kc = 0; kc < box->nall[2]; kc++) {
+	long index = orc_index(box, ic, jc, kc);
+	int inside = (jc >= 1 && jc <= box->nlocal[1] &&
+		      kc >= 1 && kc <= box->nlocal[2]);
+	for (int n = 0; n < ndist; n++) {
+	  for (int p = 0; p < nvel; p++) {
+	    long from = index;
+	    if (inside) {
+	      from -= model->cv[p][0]*sx + model->cv[p][1]*sy + model->cv[p][2];
+	    }
+	    fprime[(index*ndist + n)*nvel + p] = f[(from*ndist + n)*nvel + p];
+	  }
+	}
+      }
+    }
+  }
+
+  return 0;
+}
+
+/* src/phi_lb_coupler.c:72-102: phi = sum_p g_p, p in index order, interior */
+
+int orc_phi_from_g(const orc_model_t * model, const orc_box_t * box,
+		   const double * f, double * phi) {
+
+  const int nvel = model->nvel;
+
+  #pragma omp parallel for schedule(static)
+  for (int ic = 1; ic <= box->nlocal[0]; ic++) {
+    for (int jc = 1; jc <= box->nlocal[1]; jc++) {
+      for (int kc = 1; kc <= box->nlocal[2]; kc++) {
+	long index = orc_index(box, ic, jc, kc);
+	double phi0 = 0.0;
+	for (int p = 0; p < nvel; p++) phi0 += f[(index*2 + 1)*nvel + p];
+	phi[index] = phi0;
+      }
+    }
+  }
+  return 0;
+}
+
+/* src/gradient_3d_7pt_fluid.c:232-313 with nextra = 0: central differences
+ * and the 7-point Laplacian summed in the order +x -x +y -y +z -z -6 phi. */
+
+int orc_grad_7pt(const orc_box_t * box, const double * phi,
+		 double * grad, double * delsq) {
+
+  const long sx = (long) box->nall[1]*box->nall[2];
+  const long sy = box->nall[2];
+
+  #pragma omp parallel for schedule(static)
+  for (int ic = 1; ic <= box->nlocal[0]; ic++) {
+    for (int jc = 1; jc <= box->nlocal[1]; jc++) {
+      for (int kc = 1; kc <= box->nlocal[2]; kc++) {
+	long i = orc_index(box, ic, jc, kc);
+	grad[3*i + 0] = 0.5*(phi[i + sx] - phi[i - sx]);
+	grad[3*i + 1] = 0.5*(phi[i + sy] - phi[i - sy]);
+	grad[3*i + 2] = 0.5*(phi[i + 1] - phi[i - 1]);
+	delsq[i] = phi[i + sx] + phi[i - sx] + phi[i + sy] + phi[i - sy]
+	  + phi[i + 1] + phi[i - 1] - 6.0*phi[i];
+      }
+    }
+  }
+  return 0;
+}
+
+/* src/hydro.c:279-398: hydro_u_zero / hydro_f_zero fill ALL sites */
+
+int orc_fill(const orc_box_t * box, int nf, const double * v, double * data) {
+  #pragma omp parallel for schedule(static)
+  for (long i = 0; i < box->nsite; i++) {
+    for (int a = 0; a < nf; a++) data[nf*i + a] = v[a];
+  }
+  return 0;
+}
+
+/* src/stats_distribution.c:55-118 and :201-265 (plain sums here) */
+
+int orc_stats(const orc_model_t * model, const orc_box_t * box, int ndist,
+	      const double * f, double stats[8]) {
+
+  const int nvel = model->nvel;
+  double sr = 0.0, sr2 = 0.0, rmin = 1.0e300, rmax = -1.0e300;
+  double g[3] = {0.0, 0.0, 0.0}, sphi = 0.0;
+
+  for (int ic = 1; ic <= box->nlocal[0]; ic++) {
+    for (int jc = 1; jc <= box->nlocal[1]; jc++) {
+      for (int kc = 1; kc <= box->nlocal[2]; kc++) {
+	long index = orc_index(box, ic, jc, kc);
+	double rho = 0.0;
+	for (int p = 0; p < nvel; p++) {
+	  double fp = f[(index*ndist + 0)*nvel + p];
+	  rho += fp;
+	  for (int a = 0; a < 3; a++) g[a] += model->cv[p][a]*fp;
+	}
+	sr += rho; sr2 += rho*rho;
+	if (rho < rmin) rmin = rho;
+	if (rho > rmax) rmax = rho;
+	if (ndist == 2) {
+	  for (int p = 0; p < nvel; p++) sphi += f[(index*ndist + 1)*nvel + p];
+	}
+      }
+    }
+  }
+  stats[0] = sr; stats[1] = sr2; stats[2] = rmin; stats[3] = rmax;
+  stats[4] = g[0]; stats[5] = g[1]; stats[6] = g[2]; stats[7] = sphi;
+  return 0;
+}
+
+/* ------------------------------------------------------------------------
+ * orc_step: the time loop of src/ludwig.c:530-862 restricted to the hot
+ * path (periodic, no colloids/walls/LE planes):
+ *   hydro_f_zero; [phi_lb_to_field; field_halo; grad]; hydro_u_zero;
+ *   lb_collide; lb_halo; lb_propagation (+ pointer swap).
+ * ---------------------------------------------------------------------- */
+
+int orc_step(const orc_model_t * model, const orc_box_t * box,
+	     const orc_param_t * prm, int ndist, int nsteps,
+	     double * f, double * fprime, double * rho, double * u,
+	     double * force, double * phi, double * grad, double * delsq) {
+
+  const double zero[3] = {0.0, 0.0, 0.0};
+  const size_t nbytes = (size_t) box->nsite*ndist*model->nvel*sizeof(double);
+  double * a = f;
+  double * b = fprime;
+
+  for (int n = 0; n < nsteps; n++) {
+    double * t;
+    orc_fill(box, 3, zero, force);
+    if (ndist == 2) {
+      orc_phi_from_g(model, box, a, phi);
+      orc_halo_periodic(box, 1, phi);
+      orc_grad_7pt(box, phi, grad, delsq);
+    }
+    orc_fill(box, 3, zero, u);
+    if (ndist == 1) {
+      if (orc_collide_mrt(model, box, prm, 1, a, force, rho, u)) return -1;
+    }
+    else {
+      if (orc_collide_binary(model, box, prm, a, force, u, phi, grad, delsq)) {
+	return -1;
+      }
+    }
+    orc_halo_periodic(box, ndist*model->nvel, a);
+    orc_propagate(model, box, ndist, a, b);
+    t = a; a = b; b = t;
+  }
+
+  if (a != f) {
+    /* Odd number of steps: result is in the caller's fprime. Swap contents
+     * so that f holds the current state and fprime the previous one. */
+    double * tmp = (double *) malloc(nbytes);
+    if (tmp == NULL) return -2;
+    memcpy(tmp, f, nbytes);
+    memcpy(f, fprime, nbytes);
+    memcpy(fprime, tmp, nbytes);
+    free(tmp);
+  }
+
+  return 0;
+}

@@ -1,0 +1,196 @@
+"""ctypes wrapper of oracle/liblb_oracle.so -- TEST INFRASTRUCTURE ONLY.
+
+The CPU restatement of the Ludwig LB hot path (oracle/lb_oracle.c). Only
+tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / reference arm
+may import this module; the product (ludwig_b200/) never does.
+
+Arrays use the reference's host layout (see oracle/lb_oracle.h).
+"""
+
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = os.path.join(_HERE, "liblb_oracle.so")
+
+NVELMAX = 27
+RELAX_M10, RELAX_BGK, RELAX_TRT = 0, 1, 2
+
+c_double_p = ctypes.POINTER(ctypes.c_double)
+
+
+class Model(ctypes.Structure):
+    _fields_ = [
+        ("ndim", ctypes.c_int),
+        ("nvel", ctypes.c_int),
+        ("nhydro", ctypes.c_int),
+        ("cv", (ctypes.c_int * 3) * NVELMAX),
+        ("wv", ctypes.c_double * NVELMAX),
+        ("na", ctypes.c_double * NVELMAX),
+        ("ma", (ctypes.c_double * NVELMAX) * NVELMAX),
+        ("mi", (ctypes.c_double * NVELMAX) * NVELMAX),
+        ("maf", (ctypes.c_double * NVELMAX) * NVELMAX),
+    ]
+
+
+class Param(ctypes.Structure):
+    _fields_ = [
+        ("rho0", ctypes.c_double),
+        ("eta_shear", ctypes.c_double),
+        ("eta_bulk", ctypes.c_double),
+        ("force_global", ctypes.c_double * 3),
+        ("nrelax", ctypes.c_int),
+        ("mobility", ctypes.c_double),
+        ("a", ctypes.c_double),
+        ("b", ctypes.c_double),
+        ("kappa", ctypes.c_double),
+    ]
+
+
+class Box(ctypes.Structure):
+    _fields_ = [
+        ("nlocal", ctypes.c_int * 3),
+        ("nall", ctypes.c_int * 3),
+        ("nsite", ctypes.c_long),
+    ]
+
+
+def build():
+    """Compile the restatement (gcc only)."""
+    subprocess.check_call(["make", "-s", "-C", _HERE, "oracle"])
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_LIB):
+            build()
+        _lib = ctypes.CDLL(_LIB)
+        _lib.orc_index.restype = ctypes.c_long
+    return _lib
+
+
+def _p(a):
+    if a is None:
+        return None
+    assert a.dtype == np.float64 and a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(c_double_p)
+
+
+def make_param(rho0=1.0, eta_shear=0.1, eta_bulk=0.1, force=(0.0, 0.0, 0.0),
+               nrelax=RELAX_M10, mobility=0.0, a=0.0, b=0.0, kappa=0.0):
+    prm = Param()
+    prm.rho0, prm.eta_shear, prm.eta_bulk = rho0, eta_shear, eta_bulk
+    prm.force_global[:] = force
+    prm.nrelax = nrelax
+    prm.mobility, prm.a, prm.b, prm.kappa = mobility, a, b, kappa
+    return prm
+
+
+class Oracle:
+    """One periodic local box + one velocity set."""
+
+    def __init__(self, nvel, nlocal, ndist=1):
+        self.L = lib()
+        self.model = Model()
+        if self.L.orc_model_init(nvel, ctypes.byref(self.model)) != 0:
+            raise ValueError("bad nvel %d" % nvel)
+        self.box = Box()
+        self.L.orc_box_init((ctypes.c_int * 3)(*nlocal), ctypes.byref(self.box))
+        self.nvel = nvel
+        self.ndim = self.model.ndim
+        self.ndist = ndist
+        self.nlocal = tuple(nlocal)
+        self.nall = tuple(self.box.nall)
+        self.nsite = int(self.box.nsite)
+
+    # model tables as numpy
+    def cv(self):
+        return np.array([[self.model.cv[p][a] for a in range(3)]
+                         for p in range(self.nvel)], dtype=np.int64)
+
+    def wv(self):
+        return np.array(self.model.wv[:self.nvel])
+
+    def ma(self):
+        return np.array([[self.model.ma[m][p] for p in range(self.nvel)]
+                         for m in range(self.nvel)])
+
+    def maf(self):
+        return np.array([[self.model.maf[m][p] for p in range(self.nvel)]
+                         for m in range(self.nvel)])
+
+    def mi(self):
+        return np.array([[self.model.mi[p][m] for m in range(self.nvel)]
+                         for p in range(self.nvel)])
+
+    def index(self, ic, jc, kc):
+        return (ic * self.nall[1] + jc) * self.nall[2] + kc
+
+    def interior_mask(self):
+        m = np.zeros(self.nall, dtype=bool)
+        m[1:-1, 1:-1, 1:-1] = True
+        return m.reshape(-1)
+
+    def alloc_f(self):
+        return np.zeros((self.nsite, self.ndist, self.nvel))
+
+    def rtau(self, prm):
+        out = (ctypes.c_double * NVELMAX)()
+        rc = self.L.orc_rtau(ctypes.byref(self.model), ctypes.byref(prm), out)
+        if rc != 0:
+            raise ValueError("relaxation scheme not available")
+        return np.array(out[:self.nvel])
+
+    def equilib_set(self, f, index, rho, u):
+        self.L.orc_equilib_set(ctypes.byref(self.model), self.ndist, _p(f),
+                               ctypes.c_long(index), ctypes.c_double(rho),
+                               (ctypes.c_double * 3)(*u))
+
+    def collide_mrt(self, prm, f, force, rho, u):
+        rc = self.L.orc_collide_mrt(ctypes.byref(self.model),
+                                    ctypes.byref(self.box), ctypes.byref(prm),
+                                    self.ndist, _p(f), _p(force), _p(rho), _p(u))
+        assert rc == 0
+
+    def collide_binary(self, prm, f, force, u, phi, grad, delsq):
+        rc = self.L.orc_collide_binary(ctypes.byref(self.model),
+                                       ctypes.byref(self.box),
+                                       ctypes.byref(prm), _p(f), _p(force),
+                                       _p(u), _p(phi), _p(grad), _p(delsq))
+        assert rc == 0
+
+    def halo(self, data, nfel):
+        self.L.orc_halo_periodic(ctypes.byref(self.box), nfel, _p(data))
+
+    def propagate(self, f, fprime):
+        self.L.orc_propagate(ctypes.byref(self.model), ctypes.byref(self.box),
+                             self.ndist, _p(f), _p(fprime))
+
+    def phi_from_g(self, f, phi):
+        self.L.orc_phi_from_g(ctypes.byref(self.model), ctypes.byref(self.box),
+                              _p(f), _p(phi))
+
+    def grad_7pt(self, phi, grad, delsq):
+        self.L.orc_grad_7pt(ctypes.byref(self.box), _p(phi), _p(grad),
+                            _p(delsq))
+
+    def stats(self, f):
+        out = (ctypes.c_double * 8)()
+        self.L.orc_stats(ctypes.byref(self.model), ctypes.byref(self.box),
+                         self.ndist, _p(f), out)
+        return np.array(out[:])
+
+    def step(self, prm, nsteps, f, fprime, rho, u, force, phi=None, grad=None,
+             delsq=None):
+        rc = self.L.orc_step(ctypes.byref(self.model), ctypes.byref(self.box),
+                             ctypes.byref(prm), self.ndist, nsteps, _p(f),
+                             _p(fprime), _p(rho), _p(u), _p(force), _p(phi),
+                             _p(grad), _p(delsq))
+        assert rc == 0

@@ -1,0 +1,173 @@
+"""ctypes wrapper of oracle/_ref/libref_<model>.so -- TEST INFRASTRUCTURE ONLY.
+
+The UNMODIFIED reference (Ludwig v0.20.1) compiled in place from
+/root/reference by oracle/Makefile plus oracle/ref_driver.c. Present only
+where it was built (this container; the GPU box gets the prebuilt file with
+the snapshot). `available(nvel)` says whether it can be used.
+
+The reference keeps global state (physics singleton), so only one Ref object
+per model may be alive at a time; use it as a context manager.
+"""
+
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_NAMES = {19: "d3q19", 27: "d3q27", 9: "d2q9"}
+_libs = {}
+
+HALO_TARGET, HALO_OPENMP_FULL, HALO_OPENMP_REDUCED = 0, 1, 2
+c_double_p = ctypes.POINTER(ctypes.c_double)
+
+
+def _path(nvel):
+    return os.path.join(_HERE, "_ref", "libref_%s.so" % _NAMES[nvel])
+
+
+def build():
+    """Build the reference libraries if the reference sources are here."""
+    if os.path.isdir("/root/reference/src"):
+        ncpu = str(os.cpu_count() or 4)
+        subprocess.check_call(["make", "-s", "-j", ncpu, "-C", _HERE, "ref"],
+                              stdout=subprocess.DEVNULL)
+
+
+def available(nvel=19):
+    return nvel in _NAMES and os.path.exists(_path(nvel))
+
+
+def _lib(nvel):
+    if nvel not in _libs:
+        L = ctypes.CDLL(_path(nvel))
+        for name in ("refdrv_f", "refdrv_rho", "refdrv_u", "refdrv_force",
+                     "refdrv_phi", "refdrv_grad", "refdrv_delsq"):
+            getattr(L, name).restype = c_double_p
+        L.refdrv_status.restype = ctypes.POINTER(ctypes.c_char)
+        L.refdrv_step.restype = ctypes.c_double
+        _libs[nvel] = L
+    return _libs[nvel]
+
+
+class Ref:
+    """Reference objects on a periodic one-rank box ntotal, halo width 1."""
+
+    def __init__(self, nvel, ntotal, ndist=1, halo=HALO_TARGET):
+        self.L = _lib(nvel)
+        assert self.L.refdrv_nvel() == nvel
+        self.nvel, self.ndist = nvel, ndist
+        self.L.refdrv_init((ctypes.c_int * 3)(*ntotal), ndist, halo)
+        nall = (ctypes.c_int * 3)()
+        self.L.refdrv_nall(nall)
+        self.nall = tuple(nall)
+        self.nsite = self.L.refdrv_nsite()
+        self.nlocal = tuple(ntotal)
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def close(self):
+        if self.L is not None:
+            self.L.refdrv_finish()
+            self.L = None
+
+    def _arr(self, ptr, shape):
+        return np.ctypeslib.as_array(ptr, shape=shape)
+
+    # Views of the reference's own host arrays. NOTE: f's address changes at
+    # every lb_propagation (pointer swap, src/propagation.c:223), so call f()
+    # again after a propagation.
+    def f(self):
+        return self._arr(self.L.refdrv_f(), (self.nsite, self.ndist, self.nvel))
+
+    def rho(self):
+        return self._arr(self.L.refdrv_rho(), (self.nsite,))
+
+    def u(self):
+        return self._arr(self.L.refdrv_u(), (self.nsite, 3))
+
+    def force(self):
+        return self._arr(self.L.refdrv_force(), (self.nsite, 3))
+
+    def phi(self):
+        return self._arr(self.L.refdrv_phi(), (self.nsite,))
+
+    def grad(self):
+        return self._arr(self.L.refdrv_grad(), (self.nsite, 3))
+
+    def delsq(self):
+        return self._arr(self.L.refdrv_delsq(), (self.nsite,))
+
+    def index(self, ic, jc, kc):
+        return self.L.refdrv_index(ic, jc, kc)
+
+    def addr_f(self, index, n, p):
+        return self.L.refdrv_addr_f(index, n, p)
+
+    def model(self):
+        q = self.nvel
+        wv = np.zeros(q)
+        ma = np.zeros((q, q))
+        mi = np.zeros((q, q))
+        cv = np.zeros((q, 3), dtype=np.int32)
+        self.L.refdrv_model(wv.ctypes.data_as(c_double_p),
+                            ma.ctypes.data_as(c_double_p),
+                            mi.ctypes.data_as(c_double_p),
+                            cv.ctypes.data_as(ctypes.POINTER(ctypes.c_int)))
+        return wv, ma, mi, cv
+
+    def physics(self, rho0=1.0, eta_shear=0.1, eta_bulk=0.1,
+                force=(0.0, 0.0, 0.0), mobility=0.0):
+        self.L.refdrv_physics(ctypes.c_double(rho0), ctypes.c_double(eta_shear),
+                              ctypes.c_double(eta_bulk),
+                              (ctypes.c_double * 3)(*force),
+                              ctypes.c_double(mobility))
+
+    def relaxation(self, nrelax):
+        self.L.refdrv_relaxation(nrelax)
+
+    def fe_symm(self, a, b, kappa):
+        self.L.refdrv_fe_symm(ctypes.c_double(a), ctypes.c_double(b),
+                              ctypes.c_double(kappa))
+
+    def rtau(self):
+        out = np.zeros(self.nvel)
+        self.L.refdrv_rtau(out.ctypes.data_as(c_double_p))
+        return out
+
+    def equilib_set(self, index, rho, u):
+        self.L.refdrv_equilib_set(index, ctypes.c_double(rho),
+                                  (ctypes.c_double * 3)(*u))
+
+    def collide(self):
+        self.L.refdrv_collide()
+
+    def halo(self, scheme=-1):
+        self.L.refdrv_halo(scheme)
+
+    def propagate(self):
+        self.L.refdrv_propagate()
+
+    def phi_from_lb(self):
+        self.L.refdrv_phi_from_lb()
+
+    def phi_halo(self):
+        self.L.refdrv_phi_halo()
+
+    def grad_compute(self):
+        self.L.refdrv_grad_compute()
+
+    def hydro_f_zero(self, f=(0.0, 0.0, 0.0)):
+        self.L.refdrv_hydro_f_zero((ctypes.c_double * 3)(*f))
+
+    def hydro_u_zero(self, u=(0.0, 0.0, 0.0)):
+        self.L.refdrv_hydro_u_zero((ctypes.c_double * 3)(*u))
+
+    def step(self, nsteps):
+        """Runs nsteps of the src/ludwig.c:530-862 loop; returns seconds."""
+        return self.L.refdrv_step(nsteps)

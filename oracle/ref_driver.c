@@ -1,0 +1,260 @@
+/*****************************************************************************
+ *
+ *  ref_driver.c -- TEST INFRASTRUCTURE ONLY.
+ *
+ *  A thin ctypes-facing driver linked against the UNMODIFIED reference
+ *  (Ludwig v0.20.1 objects compiled in place from /root/reference by
+ *  oracle/Makefile). It builds the reference's own pe/cs/lb/hydro/map/
+ *  noise(/phi/phi_grad/fe_symm) objects on a periodic single-rank box and
+ *  calls the reference's own hot-path entry points one stage at a time so
+ *  that tests can compare raw fp64 arrays:
+ *
+ *    lb_collide           src/collision.c:144
+ *    lb_halo_swap         src/model.c:570
+ *    lb_propagation       src/propagation.c:43
+ *    phi_lb_to_field      src/phi_lb_coupler.c:39
+ *    field_halo           src/field.c:434
+ *    grad_3d_7pt_fluid_d2 src/gradient_3d_7pt_fluid.c:75
+ *    hydro_f_zero/u_zero  src/hydro.c:306,279
+ *
+ *  The step sequence of refdrv_step() follows src/ludwig.c:530-862 for the
+ *  "free_energy none" and "symmetric_lb" cases (periodic, no colloids).
+ *
+ *  Nothing under ludwig_b200/ links or loads this file.
+ *
+ *****************************************************************************/
+
+#include <assert.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "pe.h"
+#include "coords.h"
+#include "physics.h"
+#include "lb_data.h"
+#include "collision.h"
+#include "propagation.h"
+#include "hydro.h"
+#include "map.h"
+#include "noise.h"
+#include "field.h"
+#include "field_grad.h"
+#include "symmetric.h"
+#include "leesedwards.h"
+#include "phi_lb_coupler.h"
+#include "gradient_3d_7pt_fluid.h"
+#include "timer.h"
+
+typedef struct refdrv_s {
+  pe_t * pe;
+  cs_t * cs;
+  lees_edw_t * le;
+  physics_t * phys;
+  lb_t * lb;
+  hydro_t * hydro;
+  map_t * map;
+  noise_t * noise;
+  field_t * phi;
+  field_grad_t * phi_grad;
+  fe_symm_t * fe;
+  int ndist;
+  int mpi_up;
+} refdrv_t;
+
+static refdrv_t rd = {0};
+
+int refdrv_nvel(void) { return NVEL; }
+int refdrv_ndim(void) { return NDIM; }
+
+/* Create everything for a periodic box ntotal[3], halo width 1. */
+
+int refdrv_init(const int ntotal[3], int ndist, int halo_scheme) {
+
+  int nhalo = 1;
+
+  if (rd.mpi_up == 0) {
+    MPI_Init(NULL, NULL);
+    rd.mpi_up = 1;
+  }
+
+  pe_create(MPI_COMM_WORLD, PE_QUIET, &rd.pe);
+  cs_create(rd.pe, &rd.cs);
+  cs_nhalo_set(rd.cs, nhalo);
+  cs_ntotal_set(rd.cs, ntotal);
+  cs_init(rd.cs);
+  lees_edw_create(rd.pe, rd.cs, NULL, &rd.le);
+
+  physics_create(rd.pe, &rd.phys);
+
+  {
+    lb_data_options_t opts = lb_data_options_default();
+    opts.ndim  = NDIM;
+    opts.nvel  = NVEL;
+    opts.ndist = ndist;
+    opts.halo  = (lb_halo_enum_t) halo_scheme;
+    lb_data_create(rd.pe, rd.cs, &opts, &rd.lb);
+  }
+  rd.ndist = ndist;
+
+  {
+    hydro_options_t hopts = hydro_options_default();
+    hydro_create(rd.pe, rd.cs, rd.le, &hopts, &rd.hydro);
+  }
+
+  map_create(rd.pe, rd.cs, 0, &rd.map);
+  noise_create(rd.pe, rd.cs, &rd.noise);
+  noise_init(rd.noise, 0);
+
+  if (ndist == 2) {
+    field_options_t fopts = field_options_ndata_nhalo(1, nhalo);
+    field_create(rd.pe, rd.cs, rd.le, "phi", &fopts, &rd.phi);
+    field_grad_create(rd.pe, rd.phi, 2, &rd.phi_grad);
+    field_grad_set(rd.phi_grad, grad_3d_7pt_fluid_d2, NULL);
+    fe_symm_create(rd.pe, rd.cs, rd.phi, rd.phi_grad, &rd.fe);
+  }
+
+  return 0;
+}
+
+int refdrv_finish(void) {
+
+  if (rd.fe) fe_symm_free(rd.fe);
+  if (rd.phi_grad) field_grad_free(rd.phi_grad);
+  if (rd.phi) field_free(rd.phi);
+  if (rd.noise) noise_free(rd.noise);
+  if (rd.map) map_free(rd.map);
+  if (rd.hydro) hydro_free(rd.hydro);
+  if (rd.lb) lb_free(rd.lb);
+  if (rd.phys) physics_free(rd.phys);
+  if (rd.le) lees_edw_free(rd.le);
+  if (rd.cs) cs_free(rd.cs);
+  if (rd.pe) pe_free(rd.pe);
+  {
+    int up = rd.mpi_up;
+    memset(&rd, 0, sizeof(rd));
+    rd.mpi_up = up;
+  }
+  return 0;
+}
+
+/* Parameters */
+
+int refdrv_physics(double rho0, double eta_shear, double eta_bulk,
+		   const double fbody[3], double mobility) {
+  double f[3] = {fbody[0], fbody[1], fbody[2]};
+  physics_rho0_set(rd.phys, rho0);
+  physics_eta_shear_set(rd.phys, eta_shear);
+  physics_eta_bulk_set(rd.phys, eta_bulk);
+  physics_fbody_set(rd.phys, f);
+  physics_mobility_set(rd.phys, mobility);
+  return 0;
+}
+
+int refdrv_relaxation(int nrelax) {
+  return lb_collision_relaxation_set(rd.lb, (lb_relaxation_enum_t) nrelax);
+}
+
+int refdrv_fe_symm(double a, double b, double kappa) {
+  fe_symm_param_t p = {0};
+  p.a = a; p.b = b; p.kappa = kappa;
+  assert(rd.fe);
+  return fe_symm_param_set(rd.fe, p);
+}
+
+/* Raw host arrays of the reference objects. The host layout of a serial
+ * (non -DADDR_SOA) build is array-of-structures: src/memory.h:124-130,
+ *   f[(index*ndist + n)*nvel + p], u[index*3 + ia], grad[(index*nf+n)*3+ia].
+ * refdrv_addr_f() exposes LB_ADDR itself so tests can confirm that. */
+
+int refdrv_nsite(void) { return rd.lb->nsite; }
+int refdrv_nall(int nall[3]) { return cs_nall(rd.cs, nall); }
+int refdrv_index(int ic, int jc, int kc) { return cs_index(rd.cs, ic, jc, kc); }
+int refdrv_addr_f(int index, int n, int p) {
+  return LB_ADDR(rd.lb->nsite, rd.lb->ndist, rd.lb->nvel, index, n, p);
+}
+
+double * refdrv_f(void)     { return rd.lb->f; }
+double * refdrv_rho(void)   { return rd.hydro->rho->data; }
+double * refdrv_u(void)     { return rd.hydro->u->data; }
+double * refdrv_force(void) { return rd.hydro->force->data; }
+double * refdrv_phi(void)   { return rd.phi ? rd.phi->data : NULL; }
+double * refdrv_grad(void)  { return rd.phi_grad ? rd.phi_grad->grad : NULL; }
+double * refdrv_delsq(void) { return rd.phi_grad ? rd.phi_grad->delsq : NULL; }
+char   * refdrv_status(void) { return rd.map->status; }
+
+/* Model constants as the reference holds them after lb_data_create
+ * (src/model.c:358-390) */
+
+int refdrv_model(double * wv, double * ma, double * mi, int * cv) {
+  int p, m, ia;
+  for (p = 0; p < NVEL; p++) {
+    wv[p] = rd.lb->param->wv[p];
+    for (ia = 0; ia < 3; ia++) cv[3*p + ia] = rd.lb->param->cv[p][ia];
+    for (m = 0; m < NVEL; m++) {
+      ma[p*NVEL + m] = rd.lb->param->ma[p][m];
+      mi[p*NVEL + m] = rd.lb->param->mi[p][m];
+    }
+  }
+  return 0;
+}
+
+int refdrv_rtau(double * rtau) {
+  int p;
+  lb_collision_relaxation_times_set(rd.lb);
+  for (p = 0; p < NVEL; p++) rtau[p] = rd.lb->param->rtau[p];
+  return 0;
+}
+
+int refdrv_equilib_set(int index, double rho, const double u[3]) {
+  double uu[3] = {u[0], u[1], u[2]};
+  return lb_1st_moment_equilib_set(rd.lb, index, rho, uu);
+}
+
+/* Individual stages: each is the reference's public entry point */
+
+int refdrv_collide(void) {
+  return lb_collide(rd.lb, rd.hydro, rd.map, rd.noise, (fe_t *) rd.fe, NULL);
+}
+
+int refdrv_halo(int scheme) {
+  if (scheme < 0) return lb_halo(rd.lb);
+  return lb_halo_swap(rd.lb, (lb_halo_enum_t) scheme);
+}
+
+int refdrv_propagate(void)   { return lb_propagation(rd.lb); }
+int refdrv_phi_from_lb(void) { return phi_lb_to_field(rd.phi, rd.lb); }
+int refdrv_phi_halo(void)    { return field_halo(rd.phi); }
+int refdrv_grad_compute(void) { return field_grad_compute(rd.phi_grad); }
+
+int refdrv_hydro_f_zero(const double f[3]) { return hydro_f_zero(rd.hydro, f); }
+int refdrv_hydro_u_zero(const double u[3]) { return hydro_u_zero(rd.hydro, u); }
+
+/* The time loop, in the order of src/ludwig.c:530-862 for a periodic,
+ * colloid-free, wall-free system; returns wall-clock seconds. */
+
+double refdrv_step(int nsteps) {
+
+  int n;
+  double t0, t1;
+  const double zero[3] = {0.0, 0.0, 0.0};
+
+  t0 = MPI_Wtime();
+
+  for (n = 0; n < nsteps; n++) {
+    hydro_f_zero(rd.hydro, zero);
+    if (rd.ndist == 2) {
+      phi_lb_to_field(rd.phi, rd.lb);
+      field_halo(rd.phi);
+      field_grad_compute(rd.phi_grad);
+    }
+    hydro_u_zero(rd.hydro, zero);
+    lb_collide(rd.lb, rd.hydro, rd.map, rd.noise, (fe_t *) rd.fe, NULL);
+    lb_halo(rd.lb);
+    lb_propagation(rd.lb);
+  }
+
+  t1 = MPI_Wtime();
+
+  return (t1 - t0);
+}
