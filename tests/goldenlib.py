@@ -1,0 +1,33 @@
+"""Loads tests/golden/ref_*.npz (reference-produced, see tests/golden/make_golden.py)
+and regenerates the matching seeded inputs."""
+
+import os
+
+import numpy as np
+
+import lbinit
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+NAMES = {19: "d3q19", 27: "d3q27", 9: "d2q9"}
+PHYS = dict(eta_shear=0.05, eta_bulk=0.12)
+FG = (1e-4, -2e-4, 3e-4)
+BIN = dict(a=-0.00625, b=0.00625, kappa=0.004, mobility=3.75, eta=0.00625)
+
+
+def load(nvel):
+    return np.load(os.path.join(HERE, "golden", "ref_%s.npz" % NAMES[nvel]))
+
+
+def inputs(nvel, cv, wv, ndist=1):
+    g = load(nvel)
+    nlocal = tuple(int(x) for x in g["nlocal"])
+    ndim = 2 if nvel == 9 else 3
+    f0 = lbinit.make_state(cv, wv, nlocal, ndist=ndist, ndim=ndim)
+    force = lbinit.make_force(nlocal, ndim=ndim)
+    fg = FG if ndim == 3 else (FG[0], FG[1], 0.0)
+    return g, nlocal, f0, force, fg
+
+
+def relerr(a, b):
+    scale = max(np.max(np.abs(b)), 1e-300)
+    return np.max(np.abs(a - b)) / scale

@@ -1,0 +1,83 @@
+"""The CPU restatement against the committed reference-produced golden vectors
+(tests/golden/ref_*.npz). Runs anywhere gcc is (no /root/reference needed)."""
+
+import numpy as np
+import pytest
+
+from oracle import pyoracle
+import goldenlib
+from goldenlib import relerr
+
+
+@pytest.mark.parametrize("nvel", [19, 27, 9])
+def test_collide_halo_propagate(nvel):
+    o0 = pyoracle.Oracle(nvel, (2, 2, 1 if nvel == 9 else 2))
+    g, nlocal, f0, force, fg = goldenlib.inputs(nvel, o0.cv(), o0.wv())
+    orc = pyoracle.Oracle(nvel, nlocal)
+    m = orc.interior_mask()
+    for nrelax, name in ((0, "m10"), (1, "bgk"), (2, "trt")):
+        if "collide_%s_f" % name not in g:
+            continue
+        prm = pyoracle.make_param(force=fg, nrelax=nrelax, **goldenlib.PHYS)
+        f = f0.copy()
+        rho, u = np.zeros(orc.nsite), np.zeros((orc.nsite, 3))
+        orc.collide_mrt(prm, f, force, rho, u)
+        assert relerr(f[m], g["collide_%s_f" % name]) < 1e-13
+        assert relerr(rho[m], g["collide_%s_rho" % name]) < 1e-14
+        assert np.max(np.abs(u[m] - g["collide_%s_u" % name])) < 1e-15
+        if name == "m10":
+            orc.halo(f, nvel)
+            # halo is pure data movement: equal wherever the collided values are
+            fh = g["halo_f"]
+            assert relerr(f, fh) < 1e-13
+            f = fh.copy()
+            fp = np.zeros_like(f)
+            orc.propagate(f, fp)
+            assert np.array_equal(fp[m], g["prop_f"])      # bit-exact
+
+
+@pytest.mark.parametrize("nvel", [19, 27, 9])
+def test_ten_steps(nvel):
+    o0 = pyoracle.Oracle(nvel, (2, 2, 1 if nvel == 9 else 2))
+    g, nlocal, f0, force, fg = goldenlib.inputs(nvel, o0.cv(), o0.wv())
+    orc = pyoracle.Oracle(nvel, nlocal)
+    m = orc.interior_mask()
+    prm = pyoracle.make_param(eta_shear=0.1, eta_bulk=0.1)
+    f, fp = f0.copy(), np.zeros_like(f0)
+    n = orc.nsite
+    rho, u, frc = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
+    orc.step(prm, 10, f, fp, rho, u, frc)
+    assert relerr(f[m], g["step10_f"]) < 1e-12
+    assert relerr(rho[m], g["step10_rho"]) < 1e-12
+    assert np.max(np.abs(u[m] - g["step10_u"])) < 1e-14
+
+
+def test_binary():
+    nvel = 19
+    o0 = pyoracle.Oracle(nvel, (2, 2, 2))
+    g, nlocal, f0, force, fg = goldenlib.inputs(nvel, o0.cv(), o0.wv(), ndist=2)
+    B = goldenlib.BIN
+    orc = pyoracle.Oracle(nvel, nlocal, ndist=2)
+    m = orc.interior_mask()
+    n = orc.nsite
+    prm = pyoracle.make_param(eta_shear=B["eta"], eta_bulk=B["eta"],
+                              mobility=B["mobility"], a=B["a"], b=B["b"],
+                              kappa=B["kappa"])
+    phi, grad, delsq = np.zeros(n), np.zeros((n, 3)), np.zeros(n)
+    orc.phi_from_g(f0, phi)
+    orc.halo(phi, 1)
+    assert np.array_equal(phi, g["bin_phi"])
+    orc.grad_7pt(phi, grad, delsq)
+    assert np.array_equal(grad[m], g["bin_grad"])
+    assert np.array_equal(delsq[m], g["bin_delsq"])
+    f, u = f0.copy(), np.zeros((n, 3))
+    orc.collide_binary(prm, f, force, u, phi, grad, delsq)
+    assert relerr(f[m], g["bin_collide_f"]) < 1e-13
+    assert np.max(np.abs(u[m] - g["bin_collide_u"])) < 1e-15
+    f, fp = f0.copy(), np.zeros_like(f0)
+    rho, frc = np.zeros(n), np.zeros((n, 3))
+    orc.step(prm, 10, f, fp, rho, u, frc, phi, grad, delsq)
+    assert relerr(f[m], g["bin_step10_f"]) < 1e-12
+    # ref phi is the field at the START of step 10; recompute from step-9 state not
+    # available here, so compare the order parameter of the final state instead
+    assert abs(f[m][:, 1].sum() - g["bin_step10_f"][:, 1].sum()) < 1e-10

@@ -1,0 +1,176 @@
+"""Pins the CPU restatement (oracle/lb_oracle*.c) against the UNMODIFIED reference
+compiled in place (oracle/_ref/libref_*.so, built by oracle/Makefile from
+/root/reference). Skipped where that build is absent; the committed golden vectors
+(tests/golden, test_oracle_golden.py) carry the same pin to such machines.
+
+Tolerances: data movement bit-exact; arithmetic 1e-13 relative to max|f| (the
+restatement sums the same terms, the reference's unrolled D3Q19 code in a different
+association).
+"""
+
+import numpy as np
+import pytest
+
+from oracle import pyoracle, pyref
+import lbinit
+
+CASES = [(19, (12, 10, 8)), (27, (8, 6, 10)), (9, (16, 12, 1))]
+
+
+def need_ref(nvel):
+    if not pyref.available(nvel):
+        pytest.skip("reference build oracle/_ref not present")
+
+
+def relerr(a, b):
+    scale = max(np.max(np.abs(b)), 1e-300)
+    return np.max(np.abs(a - b)) / scale
+
+
+@pytest.mark.parametrize("nvel,nlocal", CASES)
+def test_model_constants(nvel, nlocal):
+    need_ref(nvel)
+    orc = pyoracle.Oracle(nvel, nlocal)
+    with pyref.Ref(nvel, nlocal) as ref:
+        wv, ma, mi, cv = ref.model()
+        assert np.array_equal(cv, orc.cv())
+        assert np.array_equal(wv, orc.wv())
+        assert np.max(np.abs(ma - orc.ma())) < 1e-15
+        assert np.max(np.abs(mi - orc.mi())) < 1e-15
+        assert ref.nall == orc.nall and ref.nsite == orc.nsite
+        assert ref.index(1, 2, 1) == orc.index(1, 2, 1)
+        # host layout is LB_ADDR AOS (src/memory.h:124-130)
+        assert ref.addr_f(5, 0, 3) == 5 * nvel + 3
+
+
+@pytest.mark.parametrize("nvel,nlocal", CASES)
+@pytest.mark.parametrize("nrelax", [pyoracle.RELAX_M10, pyoracle.RELAX_BGK,
+                                    pyoracle.RELAX_TRT])
+def test_collide_mrt(nvel, nlocal, nrelax):
+    need_ref(nvel)
+    if nrelax == pyoracle.RELAX_TRT and nvel != 19:
+        pytest.skip("reference TRT is D3Q15/D3Q19 only")
+    orc = pyoracle.Oracle(nvel, nlocal)
+    ndim = orc.ndim
+    f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal, ndim=ndim)
+    force = lbinit.make_force(nlocal, ndim=ndim)
+    fg = (1e-4, -2e-4, 3e-4 if ndim == 3 else 0.0)
+    prm = pyoracle.make_param(eta_shear=0.05, eta_bulk=0.12, force=fg,
+                              nrelax=nrelax)
+    with pyref.Ref(nvel, nlocal) as ref:
+        ref.physics(eta_shear=0.05, eta_bulk=0.12, force=fg)
+        ref.relaxation(nrelax)
+        assert np.allclose(ref.rtau()[orc.model.nhydro:nvel],
+                           orc.rtau(prm)[orc.model.nhydro:nvel], rtol=0, atol=1e-15)
+        ref.f()[...] = f0
+        ref.force()[...] = force
+        ref.collide()
+        f = f0.copy()
+        rho = np.zeros(orc.nsite)
+        u = np.zeros((orc.nsite, 3))
+        orc.collide_mrt(prm, f, force, rho, u)
+        m = orc.interior_mask()
+        assert relerr(f[m], ref.f()[m]) < 1e-13
+        assert relerr(rho[m], ref.rho()[m]) < 1e-14
+        assert np.max(np.abs(u[m] - ref.u()[m])) < 1e-15
+
+
+@pytest.mark.parametrize("nvel,nlocal", CASES)
+@pytest.mark.parametrize("ndist", [1, 2])
+def test_halo_and_propagation_bit_exact(nvel, nlocal, ndist):
+    need_ref(nvel)
+    if ndist == 2 and nvel == 9:
+        pytest.skip("two distributions are 3-d only in the hot path")
+    orc = pyoracle.Oracle(nvel, nlocal, ndist=ndist)
+    rng = np.random.default_rng(5)
+    f0 = rng.standard_normal((orc.nsite, ndist, nvel))
+    with pyref.Ref(nvel, nlocal, ndist=ndist) as ref:
+        ref.f()[...] = f0
+        ref.halo()
+        f = f0.copy()
+        orc.halo(f, ndist * nvel)
+        assert np.array_equal(f, ref.f())
+        ref.propagate()
+        fp = np.zeros_like(f)
+        orc.propagate(f, fp)
+        m = orc.interior_mask()
+        assert np.array_equal(fp[m], ref.f()[m])
+
+
+def test_halo_openmp_schemes_match_target():
+    nvel, nlocal = 19, (8, 6, 4)
+    need_ref(nvel)
+    orc = pyoracle.Oracle(nvel, nlocal)
+    rng = np.random.default_rng(6)
+    f0 = rng.standard_normal((orc.nsite, 1, nvel))
+    f = f0.copy()
+    orc.halo(f, nvel)
+    with pyref.Ref(nvel, nlocal, halo=pyref.HALO_OPENMP_FULL) as ref:
+        ref.f()[...] = f0
+        ref.halo()
+        assert np.array_equal(f, ref.f())
+
+
+def test_binary_stages():
+    nvel, nlocal = 19, (10, 8, 6)
+    need_ref(nvel)
+    orc = pyoracle.Oracle(nvel, nlocal, ndist=2)
+    f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal, ndist=2)
+    force = lbinit.make_force(nlocal)
+    A, B, K, M, eta = -0.00625, 0.00625, 0.004, 3.75, 0.00625
+    prm = pyoracle.make_param(eta_shear=eta, eta_bulk=eta, mobility=M, a=A, b=B,
+                              kappa=K)
+    with pyref.Ref(nvel, nlocal, ndist=2) as ref:
+        ref.physics(eta_shear=eta, eta_bulk=eta, mobility=M)
+        ref.fe_symm(A, B, K)
+        ref.f()[...] = f0
+        ref.force()[...] = force
+        ref.phi_from_lb()
+        phi = np.zeros(orc.nsite)
+        orc.phi_from_g(f0, phi)
+        m = orc.interior_mask()
+        assert np.array_equal(phi[m], ref.phi()[m])
+        ref.phi_halo()
+        orc.halo(phi, 1)
+        assert np.array_equal(phi, ref.phi())
+        ref.grad_compute()
+        grad = np.zeros((orc.nsite, 3))
+        delsq = np.zeros(orc.nsite)
+        orc.grad_7pt(phi, grad, delsq)
+        assert np.array_equal(grad[m], ref.grad()[m])
+        assert np.array_equal(delsq[m], ref.delsq()[m])
+        ref.collide()
+        f = f0.copy()
+        u = np.zeros((orc.nsite, 3))
+        orc.collide_binary(prm, f, force, u, phi, grad, delsq)
+        assert relerr(f[m][:, 0], ref.f()[m][:, 0]) < 1e-13
+        assert relerr(f[m][:, 1], ref.f()[m][:, 1]) < 1e-13
+        assert np.max(np.abs(u[m] - ref.u()[m])) < 1e-15
+
+
+@pytest.mark.parametrize("nvel,nlocal,ndist", [(19, (8, 8, 8), 1), (27, (6, 6, 6), 1),
+                                               (9, (12, 12, 1), 1), (19, (8, 8, 8), 2)])
+def test_time_loop(nvel, nlocal, ndist):
+    need_ref(nvel)
+    nsteps = 5
+    orc = pyoracle.Oracle(nvel, nlocal, ndist=ndist)
+    f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal, ndist=ndist, ndim=orc.ndim)
+    kw = dict(eta_shear=0.1, eta_bulk=0.1)
+    if ndist == 2:
+        kw = dict(eta_shear=0.00625, eta_bulk=0.00625, mobility=3.75)
+    prm = pyoracle.make_param(a=-0.00625, b=0.00625, kappa=0.004, **kw)
+    with pyref.Ref(nvel, nlocal, ndist=ndist) as ref:
+        ref.physics(**kw)
+        if ndist == 2:
+            ref.fe_symm(-0.00625, 0.00625, 0.004)
+        ref.f()[...] = f0
+        ref.step(nsteps)
+        f = f0.copy()
+        fp = np.zeros_like(f)
+        n = orc.nsite
+        rho, u, force = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
+        phi, grad, delsq = np.zeros(n), np.zeros((n, 3)), np.zeros(n)
+        orc.step(prm, nsteps, f, fp, rho, u, force, phi, grad, delsq)
+        m = orc.interior_mask()
+        assert relerr(f[m], ref.f()[m]) < 1e-12
+        assert abs(f[m][:, 0].sum() - f0[m][:, 0].sum()) < 1e-9
