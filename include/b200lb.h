@@ -1,0 +1,161 @@
+/*
+ * b200lb.h -- C ABI of libb200lb.so: the B200 (sm_100a) implementation of
+ * Ludwig's lattice-Boltzmann time-step hot path.
+ *
+ * This is the drop-in boundary. Every entry point is plain C (pointers, ints,
+ * doubles; no CUDA or torch types) and replaces one reference function or
+ * one tdpLaunchKernel dispatch (reference: zazu29/ludwig v0.20.1, paths relative
+ * to its root). INTEGRATION.md shows the few lines a Ludwig maintainer adds to
+ * src/collision.c, src/propagation.c, src/model.c ... to forward to these.
+ *
+ * Conventions
+ *   - all functions return 0 on success, non-zero on failure; the message of
+ *     the last failure on the calling thread is b200lb_last_error().
+ *   - there is NO CPU fallback: without a CUDA device b200lb_create() fails.
+ *   - host arrays use the reference's host layouts (src/memory.h:124-130,187):
+ *       B200LB_HOST_AOS  f[(index*ndist + n)*nvel + p]   (default host build)
+ *       B200LB_HOST_SOA  f[(n*nvel + p)*nsite + index]   (-DADDR_SOA builds)
+ *     rank-1 fields (u, force, grad) likewise [index*3 + a] or [a*nsite + index];
+ *     index = cs_index(ic,jc,kc) over the halo-inclusive local box with
+ *     nhalo = 1 (src/coords.c:617-631). The device layout is private.
+ *   - work is enqueued on the handle's own CUDA streams; functions that hand
+ *     data to the host synchronise first, so callers see the reference's
+ *     synchronous semantics.
+ */
+
+#ifndef B200LB_H
+#define B200LB_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200LB_NVELMAX 27
+
+enum { B200LB_HOST_AOS = 0, B200LB_HOST_SOA = 1 };
+
+/* lb_relaxation_enum_t, src/lb_data_options.h:18-23 */
+enum { B200LB_RELAX_M10 = 0, B200LB_RELAX_BGK = 1, B200LB_RELAX_TRT = 2 };
+
+/* lb_halo_enum_t, src/lb_data_options.h:26-28. TARGET = all velocities on six
+ * faces, x then y then z (src/halo_swap.c:709-1063). REDUCED = only the
+ * velocities that propagate into the receiving domain (src/model.c:1192-1219). */
+enum { B200LB_HALO_FULL = 0, B200LB_HALO_REDUCED = 2 };
+
+/* Fields that can be moved across the boundary (hydro_t src/hydro.h:33-49,
+ * field_t phi src/field.h:55-79, field_grad_t src/field_grad.h:24-43). */
+enum {
+  B200LB_FIELD_RHO = 0,      /* 1 double / site */
+  B200LB_FIELD_U = 1,        /* 3 */
+  B200LB_FIELD_FORCE = 2,    /* 3 */
+  B200LB_FIELD_PHI = 3,      /* 1 */
+  B200LB_FIELD_GRAD = 4,     /* 3 */
+  B200LB_FIELD_DELSQ = 5     /* 1 */
+};
+
+typedef struct b200lb_s b200lb_t;        /* opaque handle: one local lattice */
+
+/* What lb_data_create + cs_t know (src/model.c:56, src/coords.h:30-63). */
+typedef struct b200lb_desc_s {
+  int ndim;              /* 2 or 3 */
+  int nvel;              /* 9, 19 or 27 */
+  int ndist;             /* 1, or 2 for the binary fluid (f and g) */
+  int nlocal[3];         /* local interior extent; nlocal[2] = 1 when ndim = 2 */
+  int nhalo;             /* must be 1 */
+  int cartsz[3];         /* ranks per direction (cs_cartsz) */
+  int cartcoords[3];     /* this rank's Cartesian coordinates */
+  int periodic[3];       /* cs_periodic */
+  int nbr_lo[3];         /* rank of the lower neighbour per direction */
+  int nbr_hi[3];         /* rank of the upper neighbour per direction */
+  int rank;              /* this rank in the communicator */
+  int nranks;
+  int device;            /* CUDA device ordinal, or -1 for the current one */
+  int zalign;            /* 0 = default; interior rows start on zalign doubles */
+} b200lb_desc_t;
+
+/* lb_collide_param_t (src/lb_data.h:53-69), collide_param_t
+ * (src/collision.c:79-89) and fe_symm_param_t (src/symmetric.h:40-46):
+ * what lb_collide gathers from physics_ref() and commits every step. */
+typedef struct b200lb_param_s {
+  double rho0;
+  double eta_shear;
+  double eta_bulk;
+  double force_global[3];    /* fbody + fpulse sin(...) (src/collision.c:1945-1970) */
+  int    nrelax;             /* B200LB_RELAX_* */
+  double mobility;           /* binary: rtau2 = 2/(1 + 2 mobility) */
+  double a, b, kappa;        /* symmetric free energy */
+} b200lb_param_t;
+
+const char * b200lb_last_error(void);
+int  b200lb_device_count(void);
+const char * b200lb_version(void);
+
+int  b200lb_create(const b200lb_desc_t * desc, b200lb_t ** h);  /* lb_data_create + hydro_create (+ field/field_grad when ndist = 2) */
+int  b200lb_destroy(b200lb_t * h);                              /* lb_free, src/model.c:180 */
+long b200lb_nsite(const b200lb_t * h);                          /* host nsite = prod(nlocal + 2) */
+
+/* run-time options; recognised names:
+ *   "fused"       0/1  collide-and-stream in one pass (lazy propagation)
+ *   "halo"        B200LB_HALO_FULL / B200LB_HALO_REDUCED
+ *   "hydro_write" 0/1  store rho,u from the collision every step (reference
+ *                      behaviour, src/collision.c:570-579); 0 = on demand
+ *   "vec"         1/2  lattice sites per thread
+ *   "block"       threads per block along the contiguous direction */
+int  b200lb_set_option(b200lb_t * h, const char * name, long value);
+long b200lb_get_option(const b200lb_t * h, const char * name);
+
+/* lb_memcpy (src/model.c:228), hydro_memcpy (src/hydro.c:154), field_memcpy,
+ * field_grad_memcpy: layout boundary between host arrays and the device. */
+int  b200lb_f_upload(b200lb_t * h, const double * f_host, int host_layout);
+int  b200lb_f_download(b200lb_t * h, double * f_host, int host_layout);
+int  b200lb_field_upload(b200lb_t * h, int field, const double * host, int host_layout);
+int  b200lb_field_download(b200lb_t * h, int field, double * host, int host_layout);
+
+/* lb_collide_param_commit + lb_collision_parameters_commit
+ * (src/model.c:342, src/collision.c:1928-1980) */
+int  b200lb_set_param(b200lb_t * h, const b200lb_param_t * prm);
+
+/* The hot path. Names follow the reference call surface (src/ludwig.c:530-862). */
+int  b200lb_hydro_f_zero(b200lb_t * h, const double f[3]);   /* hydro_f_zero  src/hydro.c:306 */
+int  b200lb_hydro_u_zero(b200lb_t * h, const double u[3]);   /* hydro_u_zero  src/hydro.c:279 */
+int  b200lb_collide(b200lb_t * h);                           /* lb_collide    src/collision.c:144 */
+int  b200lb_halo(b200lb_t * h);                              /* lb_halo       src/model.c:553 */
+int  b200lb_halo_swap(b200lb_t * h, int scheme);             /* lb_halo_swap  src/model.c:570 */
+int  b200lb_propagate(b200lb_t * h);                         /* lb_propagation src/propagation.c:43 */
+int  b200lb_phi_from_g(b200lb_t * h);                        /* phi_lb_to_field src/phi_lb_coupler.c:39 */
+int  b200lb_phi_halo(b200lb_t * h);                          /* field_halo(phi) src/field.c:434 */
+int  b200lb_grad7(b200lb_t * h);                             /* grad_3d_7pt_fluid_d2 src/gradient_3d_7pt_fluid.c:75 */
+
+/* nsteps iterations of the src/ludwig.c:530-862 loop restricted to the hot
+ * path: f_zero; [phi_from_g; phi_halo; grad7]; u_zero; collide; halo; propagate */
+int  b200lb_step(b200lb_t * h, int nsteps);
+
+/* Conserved-quantity diagnostics over interior sites of this rank
+ * (stats_distribution_print / stats_distribution_momentum,
+ * src/stats_distribution.c:55-118,201-265):
+ * out = { sum rho, sum rho^2, min rho, max rho, gx, gy, gz, sum phi } */
+int  b200lb_stats(b200lb_t * h, double out[8]);
+
+int  b200lb_sync(b200lb_t * h);          /* tdpDeviceSynchronize for this handle */
+
+/* Multi-GPU: one rank per GPU; halo planes go device-to-device with NCCL
+ * send/recv (replaces the MPI_Isend/Irecv of host buffers, src/halo_swap.c:762-1035).
+ * Rank 0 makes the id, the caller's launcher (MPI_Bcast, torch.distributed ...)
+ * distributes its 128 bytes, every rank calls comm_init. */
+int  b200lb_nccl_unique_id(char id[128]);
+int  b200lb_comm_init(b200lb_t * h, const char id[128]);
+
+/* Timing on the handle's compute stream (CUDA events), for bench.py */
+int  b200lb_timer_start(b200lb_t * h);
+int  b200lb_timer_stop(b200lb_t * h, float * ms);     /* synchronises */
+long b200lb_launch_count(const b200lb_t * h);         /* kernels launched so far */
+
+/* Pinned host memory for lb->f and friends (optional; speeds up lb_memcpy) */
+int  b200lb_host_alloc(void ** ptr, long nbytes);
+int  b200lb_host_free(void * ptr);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif

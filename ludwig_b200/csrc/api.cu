@@ -1,0 +1,819 @@
+// api.cu -- the C ABI of include/b200lb.h: handle, layout, state machine,
+// halo exchange (local periodic copies and NCCL send/recv), transfers.
+//
+// There is deliberately no CPU path in this file: every operation is a CUDA
+// kernel launch or a CUDA/NCCL call, and b200lb_create fails without a device.
+
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+#include "../../include/b200lb.h"
+#include "common_kernels.cuh"
+#include "model_ops.cuh"
+
+// ---------------------------------------------------------------------------
+// errors
+// ---------------------------------------------------------------------------
+
+static thread_local char g_err[512] = "";
+
+static int fail(const char * fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return -1;
+}
+
+#define CU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) \
+  return fail("%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); } while (0)
+
+extern "C" const char * b200lb_last_error(void) { return g_err; }
+extern "C" const char * b200lb_version(void) { return "b200lb 0.1 (sm_100a)"; }
+
+extern "C" int b200lb_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+// ---------------------------------------------------------------------------
+// NCCL, resolved at run time so the library loads on a box without it and
+// shares whichever libnccl the process already has (e.g. the one torch loaded).
+// ---------------------------------------------------------------------------
+
+struct NcclApi {
+  void * lib;
+  decltype(&ncclGetUniqueId) GetUniqueId;
+  decltype(&ncclCommInitRank) CommInitRank;
+  decltype(&ncclCommDestroy) CommDestroy;
+  decltype(&ncclSend) Send;
+  decltype(&ncclRecv) Recv;
+  decltype(&ncclGroupStart) GroupStart;
+  decltype(&ncclGroupEnd) GroupEnd;
+  decltype(&ncclGetErrorString) GetErrorString;
+};
+
+static NcclApi g_nccl = {};
+
+static int nccl_load(void) {
+  if (g_nccl.lib) return 0;
+  void * lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+  if (!lib) lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+  if (!lib) return fail("NCCL not found: %s", dlerror());
+#define SYM(name) g_nccl.name = (decltype(g_nccl.name)) dlsym(lib, "nccl" #name); \
+  if (!g_nccl.name) return fail("NCCL symbol nccl" #name " missing")
+  SYM(GetUniqueId); SYM(CommInitRank); SYM(CommDestroy); SYM(Send); SYM(Recv);
+  SYM(GroupStart); SYM(GroupEnd); SYM(GetErrorString);
+#undef SYM
+  g_nccl.lib = lib;
+  return 0;
+}
+
+#define NC(call) do { ncclResult_t r_ = (call); if (r_ != ncclSuccess) \
+  return fail("%s:%d %s: %s", __FILE__, __LINE__, #call, g_nccl.GetErrorString(r_)); } while (0)
+
+// ---------------------------------------------------------------------------
+// handle
+// ---------------------------------------------------------------------------
+
+#define STAGE_BYTES ((size_t) 64 << 20)
+
+struct HaloBuf {
+  double * to_lo, * to_hi, * from_lo, * from_hi;
+  i64 nface;
+};
+
+struct b200lb_s {
+  b200lb_desc_t desc;
+  const ModelOps * ops;
+  Layout L;
+  int hostdim[3];            // physical nall
+  long nsite_host;
+  int nplane;                // ndist*nvel
+
+  double * lat[2];           // two lattices; lat[cur] is "f", the other "fprime"
+  int cur;
+  double * rho, * u, * force, * phi, * grad, * delsq;
+
+  // state machine (see b200lb_propagate)
+  bool prop_pending;         // lat[cur] holds post-collision values still to be streamed
+  bool force_uniform;        // force field == fconst everywhere (hydro_f_zero)
+  double fconst[3];
+  bool u_fill_pending;       // hydro_u_zero recorded but not yet applied
+  double uconst[3];
+  bool hydro_stale;          // collision ran without storing rho,u
+
+  b200lb_param_t prm;
+  double rtau_shear, rtau_bulk, rtau2;
+  double gkeep[B200LB_MAXGHOST];
+  bool ghost;
+
+  // options
+  int opt_fused, opt_halo, opt_hydro_write, opt_vec, opt_block;
+
+  cudaStream_t s_main, s_x[2];
+  cudaEvent_t ev0, ev1, ev_x[2];
+  double * stage[2];
+  double * partial; i64 npartial;
+  double * stats_dev; double * stats_host;
+  long launches;
+
+  ncclComm_t comm;
+  HaloBuf hb[3];             // per device axis (multi-rank directions only)
+  int hb_nel;
+};
+
+static int site_kparams(b200lb_s * h, KParams & P) {
+  memset(&P, 0, sizeof(P));
+  P.L = h->L;
+  for (int d = 0; d < 3; d++) { P.lo[d] = 0; P.hi[d] = h->L.n[d]; }
+  P.rtau_shear = h->rtau_shear; P.rtau_bulk = h->rtau_bulk;
+  P.rtau2 = h->rtau2; P.A = h->prm.a; P.B = h->prm.b; P.kappa = h->prm.kappa;
+  for (int k = 0; k < B200LB_MAXGHOST; k++) P.gkeep[k] = h->gkeep[k];
+  return 0;
+}
+
+static size_t plane_bytes(const b200lb_s * h) { return (size_t) h->L.nsd*sizeof(double); }
+
+// ---------------------------------------------------------------------------
+// create / destroy
+// ---------------------------------------------------------------------------
+
+static int derive_params(b200lb_s * h) {
+  const b200lb_param_t & p = h->prm;
+  const double cs2 = 1.0/3.0;
+  const ModelOps * m = h->ops;
+  const int ng = m->nvel - m->nhydro;
+  // lb_collision_relaxation_times_set, src/collision.c:1181-1264
+  h->rtau_shear = 1.0/(0.5 + p.eta_shear/(p.rho0*cs2));
+  h->rtau_bulk  = 1.0/(0.5 + p.eta_bulk/(p.rho0*cs2));
+  h->rtau2 = 2.0/(1.0 + 2.0*p.mobility);              // src/collision.c:1973
+  double rt[B200LB_MAXGHOST];
+  for (int k = 0; k < B200LB_MAXGHOST; k++) rt[k] = 1.0;
+  if (p.nrelax == B200LB_RELAX_M10) {
+    /* ghosts fully relaxed */
+  }
+  else if (p.nrelax == B200LB_RELAX_BGK) {
+    for (int k = 0; k < ng; k++) rt[k] = h->rtau_shear;
+    h->rtau_bulk = h->rtau_shear;
+  }
+  else if (p.nrelax == B200LB_RELAX_TRT) {
+    if (m->nvel != 19) return fail("TRT relaxation is available for D3Q19 only (as in the reference)");
+    const double tau = p.eta_shear/(p.rho0*cs2);
+    double r = 0.5 + 2.0*tau/(tau + 3.0/8.0);
+    if (r > 2.0) r = 2.0;
+    // modes 10,14,18 (even) relax with the shear rate, the odd ones with r
+    for (int k = 0; k < ng; k++) rt[k] = (k == 0 || k == 4 || k == 8) ? h->rtau_shear : r;
+  }
+  else {
+    return fail("unknown relaxation scheme %d", p.nrelax);
+  }
+  h->ghost = false;
+  for (int k = 0; k < B200LB_MAXGHOST; k++) {
+    h->gkeep[k] = (k < ng) ? 1.0 - rt[k] : 0.0;
+    if (h->gkeep[k] != 0.0) h->ghost = true;
+  }
+  return 0;
+}
+
+extern "C" int b200lb_create(const b200lb_desc_t * desc, b200lb_t ** out) {
+
+  if (!desc || !out) return fail("null argument");
+  *out = nullptr;
+  int ndev = b200lb_device_count();
+  if (ndev <= 0) return fail("no CUDA device: libb200lb has no CPU path");
+  if (desc->nhalo != 1) return fail("nhalo must be 1 (got %d)", desc->nhalo);
+  if (desc->ndist != 1 && desc->ndist != 2) return fail("ndist must be 1 or 2");
+
+  const ModelOps * ops = nullptr;
+  if (desc->nvel == 19) ops = model_ops_d3q19();
+  if (desc->nvel == 27) ops = model_ops_d3q27();
+  if (desc->nvel == 9)  ops = model_ops_d2q9();
+  if (!ops) return fail("unsupported nvel %d (9, 19, 27)", desc->nvel);
+  if (ops->ndim != desc->ndim) return fail("ndim %d does not match nvel %d", desc->ndim, desc->nvel);
+  if (desc->ndist == 2 && ops->ndim != 3) return fail("two distributions need a 3-d model");
+  if (ops->ndim == 2 && desc->nlocal[2] != 1) return fail("2-d model needs nlocal[2] = 1");
+  for (int a = 0; a < 3; a++) if (desc->nlocal[a] < 1) return fail("bad nlocal");
+
+  if (desc->device >= 0) CU(cudaSetDevice(desc->device));
+
+  b200lb_s * h = (b200lb_s *) calloc(1, sizeof(b200lb_s));
+  if (!h) return fail("out of host memory");
+  h->desc = *desc;
+  h->ops = ops;
+  h->nplane = desc->ndist*desc->nvel;
+
+  Layout & L = h->L;
+  int zalign = desc->zalign > 0 ? desc->zalign : 16;
+  if (zalign < 2 || (zalign & 1)) { free(h); return fail("zalign must be even"); }
+  h->nsite_host = 1;
+  for (int a = 0; a < 3; a++) {
+    h->hostdim[a] = desc->nlocal[a] + 2;
+    h->nsite_host *= h->hostdim[a];
+  }
+  for (int d = 0; d < 3; d++) {
+    const int a = ops->dax[d];
+    L.n[d] = desc->nlocal[a];
+    L.h[d] = (ops->ndim == 2 && a == 2) ? 0 : 1;
+    L.na[d] = L.n[d] + 2*L.h[d];
+  }
+  L.z0 = zalign - L.h[2];
+  {
+    i64 row = L.z0 + L.na[2];
+    row = (row + zalign - 1)/zalign*zalign;
+    L.s1 = row;
+    L.s0 = L.s1*L.na[1];
+    L.nsd = L.s0*L.na[0] + zalign;       // slack: masked lanes may read one row position past the end
+  }
+
+  CU(cudaStreamCreateWithFlags(&h->s_main, cudaStreamNonBlocking));
+  for (int i = 0; i < 2; i++) {
+    CU(cudaStreamCreateWithFlags(&h->s_x[i], cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&h->ev_x[i], cudaEventDisableTiming));
+  }
+  CU(cudaEventCreate(&h->ev0));
+  CU(cudaEventCreate(&h->ev1));
+
+  const size_t pb = plane_bytes(h);
+  for (int i = 0; i < 2; i++) {
+    CU(cudaMalloc(&h->lat[i], pb*h->nplane));
+    CU(cudaMemsetAsync(h->lat[i], 0, pb*h->nplane, h->s_main));
+  }
+  CU(cudaMalloc(&h->rho, pb));
+  CU(cudaMalloc(&h->u, 3*pb));
+  CU(cudaMalloc(&h->force, 3*pb));
+  CU(cudaMemsetAsync(h->rho, 0, pb, h->s_main));
+  CU(cudaMemsetAsync(h->u, 0, 3*pb, h->s_main));
+  CU(cudaMemsetAsync(h->force, 0, 3*pb, h->s_main));
+  if (desc->ndist == 2) {
+    CU(cudaMalloc(&h->phi, pb));
+    CU(cudaMalloc(&h->grad, 3*pb));
+    CU(cudaMalloc(&h->delsq, pb));
+    CU(cudaMemsetAsync(h->phi, 0, pb, h->s_main));
+    CU(cudaMemsetAsync(h->grad, 0, 3*pb, h->s_main));
+    CU(cudaMemsetAsync(h->delsq, 0, pb, h->s_main));
+  }
+  // diagnostics scratch: one partial per block of a (128 x 2) tiling
+  h->npartial = (i64)((L.n[2] + 127)/128)*((L.n[1] + 1)/2)*L.n[0];
+  CU(cudaMalloc(&h->partial, 8*sizeof(double)*h->npartial));
+  CU(cudaMalloc(&h->stats_dev, 8*sizeof(double)));
+  CU(cudaMallocHost(&h->stats_host, 8*sizeof(double)));
+
+  CU(ops->ghost_upload());
+
+  h->force_uniform = true;
+  h->opt_fused = 1;
+  h->opt_halo = B200LB_HALO_FULL;
+  h->opt_hydro_write = 1;
+  h->opt_vec = 2;
+  h->opt_block = 128;
+
+  b200lb_param_t p0;
+  memset(&p0, 0, sizeof(p0));
+  p0.rho0 = 1.0; p0.eta_shear = 1.0/6.0; p0.eta_bulk = 1.0/6.0;
+  h->prm = p0;
+  if (derive_params(h)) { free(h); return -1; }
+
+  CU(cudaStreamSynchronize(h->s_main));
+  *out = h;
+  return 0;
+}
+
+extern "C" int b200lb_destroy(b200lb_t * h) {
+  if (!h) return 0;
+  cudaDeviceSynchronize();
+  if (h->comm) g_nccl.CommDestroy(h->comm);
+  for (int d = 0; d < 3; d++) {
+    cudaFree(h->hb[d].to_lo); cudaFree(h->hb[d].to_hi);
+    cudaFree(h->hb[d].from_lo); cudaFree(h->hb[d].from_hi);
+  }
+  for (int i = 0; i < 2; i++) {
+    cudaFree(h->lat[i]);
+    cudaFree(h->stage[i]);
+    cudaStreamDestroy(h->s_x[i]);
+    cudaEventDestroy(h->ev_x[i]);
+  }
+  cudaFree(h->rho); cudaFree(h->u); cudaFree(h->force);
+  cudaFree(h->phi); cudaFree(h->grad); cudaFree(h->delsq);
+  cudaFree(h->partial); cudaFree(h->stats_dev); cudaFreeHost(h->stats_host);
+  cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
+  cudaStreamDestroy(h->s_main);
+  free(h);
+  return 0;
+}
+
+extern "C" long b200lb_nsite(const b200lb_t * h) { return h ? h->nsite_host : 0; }
+
+static int materialise(b200lb_s * h);
+
+extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
+  if (!h || !name) return fail("null argument");
+  if (!strcmp(name, "fused")) {
+    if (!v && h->prop_pending) { if (materialise(h)) return -1; }
+    h->opt_fused = (v != 0);
+    return 0;
+  }
+  if (!strcmp(name, "halo")) {
+    if (v != B200LB_HALO_FULL && v != B200LB_HALO_REDUCED) return fail("bad halo scheme %ld", v);
+    h->opt_halo = (int) v; return 0;
+  }
+  if (!strcmp(name, "hydro_write")) { h->opt_hydro_write = (v != 0); return 0; }
+  if (!strcmp(name, "vec")) {
+    if (v != 1 && v != 2) return fail("vec must be 1 or 2");
+    h->opt_vec = (int) v; return 0;
+  }
+  if (!strcmp(name, "block")) {
+    if (v != 32 && v != 64 && v != 128 && v != 256) return fail("block must be 32, 64, 128 or 256");
+    h->opt_block = (int) v; return 0;
+  }
+  return fail("unknown option '%s'", name);
+}
+
+extern "C" long b200lb_get_option(const b200lb_t * h, const char * name) {
+  if (!h || !name) return -1;
+  if (!strcmp(name, "fused")) return h->opt_fused;
+  if (!strcmp(name, "halo")) return h->opt_halo;
+  if (!strcmp(name, "hydro_write")) return h->opt_hydro_write;
+  if (!strcmp(name, "vec")) return h->opt_vec;
+  if (!strcmp(name, "block")) return h->opt_block;
+  if (!strcmp(name, "prop_pending")) return h->prop_pending;
+  if (!strcmp(name, "nsd")) return (long) h->L.nsd;
+  if (!strcmp(name, "row_pitch")) return (long) h->L.s1;
+  return -1;
+}
+
+extern "C" int b200lb_set_param(b200lb_t * h, const b200lb_param_t * prm) {
+  if (!h || !prm) return fail("null argument");
+  b200lb_param_t keep = h->prm;
+  h->prm = *prm;
+  if (derive_params(h)) { h->prm = keep; derive_params(h); return -1; }
+  return 0;
+}
+
+// ---------------------------------------------------------------------------
+// sweeps
+// ---------------------------------------------------------------------------
+
+static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
+		     double * dst) {
+  SweepArgs a;
+  site_kparams(h, a.P);
+  a.P.src = src; a.P.dst = dst;
+  a.pull = pull; a.collide = collide;
+  a.binary = (h->desc.ndist == 2);
+  a.ghost = h->ghost;
+  a.vec = h->opt_vec;
+  a.bx = h->opt_block;
+  a.stream = h->s_main;
+  if (collide) {
+    for (int i = 0; i < 3; i++) a.P.fg[i] = h->prm.force_global[i] + (h->force_uniform ? h->fconst[i] : 0.0);
+    a.P.force = h->force_uniform ? nullptr : h->force;
+    if (h->opt_hydro_write) { a.P.rho = h->rho; a.P.u = h->u; }
+    a.P.phi = h->phi; a.P.grad = h->grad; a.P.delsq = h->delsq;
+  }
+  CU(h->ops->sweep(a));
+  h->launches++;
+  if (collide) {
+    if (h->opt_hydro_write) { h->u_fill_pending = false; h->hydro_stale = false; }
+    else h->hydro_stale = true;
+  }
+  return 0;
+}
+
+// apply a deferred propagation so that lat[cur] is the streamed lattice
+static int materialise(b200lb_s * h) {
+  if (!h->prop_pending) return 0;
+  if (run_sweep(h, true, false, h->lat[h->cur], h->lat[1 - h->cur])) return -1;
+  h->cur = 1 - h->cur;
+  h->prop_pending = false;
+  return 0;
+}
+
+extern "C" int b200lb_collide(b200lb_t * h) {
+  if (!h) return fail("null handle");
+  if (h->prop_pending) {
+    // stream-then-collide in one pass over the lattice
+    if (run_sweep(h, true, true, h->lat[h->cur], h->lat[1 - h->cur])) return -1;
+    h->cur = 1 - h->cur;
+    h->prop_pending = false;
+    return 0;
+  }
+  return run_sweep(h, false, true, h->lat[h->cur], h->lat[h->cur]);
+}
+
+extern "C" int b200lb_propagate(b200lb_t * h) {
+  if (!h) return fail("null handle");
+  if (h->prop_pending) { if (materialise(h)) return -1; }
+  if (h->opt_fused) {
+    // Lazy: the streaming is folded into the next collision (or done on demand
+    // by the first call that observes the lattice).
+    h->prop_pending = true;
+    return 0;
+  }
+  if (run_sweep(h, true, false, h->lat[h->cur], h->lat[1 - h->cur])) return -1;
+  h->cur = 1 - h->cur;
+  return 0;
+}
+
+// ---------------------------------------------------------------------------
+// halo exchange
+// ---------------------------------------------------------------------------
+
+// element lists for device axis d: which planes are needed in the low / high halo
+static void halo_lists(const b200lb_s * h, int d, int scheme, int nplane_per_dist,
+		       bool lattice, HaloParams & H) {
+  H.nlo = H.nhi = 0;
+  const int nplane = lattice ? h->nplane : nplane_per_dist;
+  for (int e = 0; e < nplane; e++) {
+    int c = 0;
+    if (lattice && scheme == B200LB_HALO_REDUCED) {
+      const int p = e % h->desc.nvel;
+      c = h->ops->cv[p][h->ops->dax[d]];
+      // the low halo is read by sites pulling with c = +1, the high one with c = -1
+      if (c == 1)  H.el_lo[H.nlo++] = (unsigned char) e;
+      if (c == -1) H.el_hi[H.nhi++] = (unsigned char) e;
+    }
+    else {
+      H.el_lo[H.nlo++] = (unsigned char) e;
+      H.el_hi[H.nhi++] = (unsigned char) e;
+    }
+  }
+}
+
+static int halo_launch(b200lb_s * h, int mode, const HaloParams & H) {
+  const Layout & L = H.L;
+  const int d = H.axis;
+  const int fa = (d == 2) ? 1 : 2;
+  const int sl = (d == 0) ? 1 : 0;
+  dim3 block(fa == 2 ? 128 : 32, fa == 2 ? 2 : 8, 1);
+  dim3 grid((L.na[fa] + block.x - 1)/block.x, (L.na[sl] + block.y - 1)/block.y, H.nlo + H.nhi);
+  if (grid.z == 0) return 0;
+  if (mode == HALO_LOCAL)  halo_kernel<HALO_LOCAL><<<grid, block, 0, h->s_main>>>(H);
+  if (mode == HALO_PACK)   halo_kernel<HALO_PACK><<<grid, block, 0, h->s_main>>>(H);
+  if (mode == HALO_UNPACK) halo_kernel<HALO_UNPACK><<<grid, block, 0, h->s_main>>>(H);
+  CU(cudaGetLastError());
+  h->launches++;
+  return 0;
+}
+
+static int halo_buffers(b200lb_s * h, int d, int nel) {
+  HaloBuf & b = h->hb[d];
+  const int fa = (d == 2) ? 1 : 2;
+  const int sl = (d == 0) ? 1 : 0;
+  const i64 nface = (i64) h->L.na[fa]*h->L.na[sl];
+  if (b.to_lo && b.nface == nface && h->hb_nel >= nel) return 0;
+  const int want = nel > h->nplane ? nel : h->nplane;
+  cudaFree(b.to_lo); cudaFree(b.to_hi); cudaFree(b.from_lo); cudaFree(b.from_hi);
+  const size_t nb = (size_t) nface*want*sizeof(double);
+  CU(cudaMalloc(&b.to_lo, nb)); CU(cudaMalloc(&b.to_hi, nb));
+  CU(cudaMalloc(&b.from_lo, nb)); CU(cudaMalloc(&b.from_hi, nb));
+  b.nface = nface;
+  h->hb_nel = want;
+  return 0;
+}
+
+// Exchange the halo planes of `data` (nplane planes of nsd doubles).
+static int halo_exchange(b200lb_s * h, double * data, bool lattice, int nplane, int scheme) {
+  for (int d = 0; d < 3; d++) {
+    if (h->L.h[d] == 0) continue;
+    const int a = h->ops->dax[d];
+    HaloParams H;
+    memset(&H, 0, sizeof(H));
+    H.L = h->L; H.data = data; H.axis = d;
+    halo_lists(h, d, scheme, nplane, lattice, H);
+    if (h->desc.cartsz[a] == 1) {
+      if (!h->desc.periodic[a]) continue;        // physical boundary: nothing to receive
+      if (halo_launch(h, HALO_LOCAL, H)) return -1;
+      continue;
+    }
+    if (!h->comm) return fail("direction %d is decomposed over %d ranks but b200lb_comm_init was not called", a, h->desc.cartsz[a]);
+    if (halo_buffers(h, d, nplane)) return -1;
+    HaloBuf & b = h->hb[d];
+    H.to_lo = b.to_lo; H.to_hi = b.to_hi; H.from_lo = b.from_lo; H.from_hi = b.from_hi;
+    if (halo_launch(h, HALO_PACK, H)) return -1;
+    const int lo = h->desc.nbr_lo[a], hi = h->desc.nbr_hi[a];
+    // Order matters when lo == hi (two ranks, periodic): the peer's first
+    // message is its low face, which is my HIGH halo.
+    NC(g_nccl.GroupStart());
+    if (lo >= 0) NC(g_nccl.Send(b.to_lo, (size_t) H.nhi*b.nface, ncclDouble, lo, h->comm, h->s_main));
+    if (hi >= 0) NC(g_nccl.Send(b.to_hi, (size_t) H.nlo*b.nface, ncclDouble, hi, h->comm, h->s_main));
+    if (hi >= 0) NC(g_nccl.Recv(b.from_hi, (size_t) H.nhi*b.nface, ncclDouble, hi, h->comm, h->s_main));
+    if (lo >= 0) NC(g_nccl.Recv(b.from_lo, (size_t) H.nlo*b.nface, ncclDouble, lo, h->comm, h->s_main));
+    NC(g_nccl.GroupEnd());
+    // a missing neighbour (non-periodic edge) leaves that halo untouched
+    if (lo < 0) H.nlo = 0;
+    if (hi < 0) H.nhi = 0;
+    if (halo_launch(h, HALO_UNPACK, H)) return -1;
+  }
+  return 0;
+}
+
+extern "C" int b200lb_halo_swap(b200lb_t * h, int scheme) {
+  if (!h) return fail("null handle");
+  if (scheme == 1) scheme = B200LB_HALO_FULL;      // LB_HALO_OPENMP_FULL moves the same data
+  if (scheme != B200LB_HALO_FULL && scheme != B200LB_HALO_REDUCED) return fail("bad halo scheme %d", scheme);
+  if (h->prop_pending) { if (materialise(h)) return -1; }
+  return halo_exchange(h, h->lat[h->cur], true, h->nplane, scheme);
+}
+
+extern "C" int b200lb_halo(b200lb_t * h) {
+  if (!h) return fail("null handle");
+  return b200lb_halo_swap(h, h->opt_halo);
+}
+
+extern "C" int b200lb_phi_halo(b200lb_t * h) {
+  if (!h) return fail("null handle");
+  if (!h->phi) return fail("no order parameter (ndist = 1)");
+  return halo_exchange(h, h->phi, false, 1, B200LB_HALO_FULL);
+}
+
+// ---------------------------------------------------------------------------
+// order parameter, gradient, hydro fills
+// ---------------------------------------------------------------------------
+
+extern "C" int b200lb_phi_from_g(b200lb_t * h) {
+  if (!h) return fail("null handle");
+  if (!h->phi) return fail("no order parameter (ndist = 1)");
+  const double * g = h->lat[h->cur] + (i64) h->desc.nvel*h->L.nsd;
+  CU(h->ops->phi_from_g(h->L, g, h->phi, h->prop_pending, h->s_main));
+  h->launches++;
+  return 0;
+}
+
+extern "C" int b200lb_grad7(b200lb_t * h) {
+  if (!h) return fail("null handle");
+  if (!h->phi) return fail("no order parameter (ndist = 1)");
+  const Layout & L = h->L;
+  dim3 block(GRAD_TZ, GRAD_TY, 1);
+  dim3 grid((L.n[2] + GRAD_TZ - 1)/GRAD_TZ, (L.n[1] + GRAD_TY - 1)/GRAD_TY,
+	    (L.n[0] + GRAD_NX - 1)/GRAD_NX);
+  grad7_kernel<<<grid, block, 0, h->s_main>>>(L, h->phi, h->grad, h->delsq);
+  CU(cudaGetLastError());
+  h->launches++;
+  return 0;
+}
+
+static int fill3(b200lb_s * h, double * data, int nf, const double v[3]) {
+  const i64 n = h->L.nsd;
+  fill_kernel<<<(unsigned) ((n + 255)/256), 256, 0, h->s_main>>>(data, n, n, nf, v[0], nf > 1 ? v[1] : 0.0, nf > 2 ? v[2] : 0.0);
+  CU(cudaGetLastError());
+  h->launches++;
+  return 0;
+}
+
+extern "C" int b200lb_hydro_f_zero(b200lb_t * h, const double f[3]) {
+  if (!h) return fail("null handle");
+  // The whole field takes one value: remember it instead of sweeping 24 B/site
+  // (src/hydro.c:306 fills all nsite every step). Materialised on demand.
+  for (int i = 0; i < 3; i++) h->fconst[i] = f ? f[i] : 0.0;
+  h->force_uniform = true;
+  return 0;
+}
+
+extern "C" int b200lb_hydro_u_zero(b200lb_t * h, const double u[3]) {
+  if (!h) return fail("null handle");
+  for (int i = 0; i < 3; i++) h->uconst[i] = u ? u[i] : 0.0;
+  h->u_fill_pending = true;     // the next collision overwrites the interior anyway
+  return 0;
+}
+
+// ---------------------------------------------------------------------------
+// the time loop of src/ludwig.c:530-862 restricted to the hot path
+// ---------------------------------------------------------------------------
+
+extern "C" int b200lb_step(b200lb_t * h, int nsteps) {
+  if (!h) return fail("null handle");
+  const double zero[3] = {0.0, 0.0, 0.0};
+  for (int n = 0; n < nsteps; n++) {
+    if (b200lb_hydro_f_zero(h, zero)) return -1;
+    if (h->desc.ndist == 2) {
+      if (b200lb_phi_from_g(h)) return -1;
+      if (b200lb_phi_halo(h)) return -1;
+      if (b200lb_grad7(h)) return -1;
+    }
+    if (b200lb_hydro_u_zero(h, zero)) return -1;
+    if (b200lb_collide(h)) return -1;
+    if (h->prop_pending) return fail("internal: propagation pending after collide");
+    if (halo_exchange(h, h->lat[h->cur], true, h->nplane, h->opt_halo)) return -1;
+    if (b200lb_propagate(h)) return -1;
+  }
+  return 0;
+}
+
+// ---------------------------------------------------------------------------
+// diagnostics
+// ---------------------------------------------------------------------------
+
+extern "C" int b200lb_stats(b200lb_t * h, double out[8]) {
+  if (!h || !out) return fail("null argument");
+  if (materialise(h)) return -1;
+  const Layout & L = h->L;
+  dim3 block(128, 2, 1);
+  dim3 grid((L.n[2] + 127)/128, (L.n[1] + 1)/2, L.n[0]);
+  CU(h->ops->stats(L, h->lat[h->cur], h->desc.ndist, h->partial, grid, block, h->s_main));
+  stats_final_kernel<<<1, 256, 0, h->s_main>>>(h->partial, h->npartial, h->stats_dev);
+  CU(cudaGetLastError());
+  h->launches += 2;
+  CU(cudaMemcpyAsync(h->stats_host, h->stats_dev, 8*sizeof(double), cudaMemcpyDeviceToHost, h->s_main));
+  CU(cudaStreamSynchronize(h->s_main));
+  for (int k = 0; k < 8; k++) out[k] = h->stats_host[k];
+  return 0;
+}
+
+extern "C" int b200lb_sync(b200lb_t * h) {
+  if (!h) return fail("null handle");
+  CU(cudaStreamSynchronize(h->s_main));
+  CU(cudaStreamSynchronize(h->s_x[0]));
+  CU(cudaStreamSynchronize(h->s_x[1]));
+  return 0;
+}
+
+// ---------------------------------------------------------------------------
+// transfers: staged, double-buffered on two streams so the copy of one piece
+// overlaps the layout conversion of the previous one
+// ---------------------------------------------------------------------------
+
+static int ensure_stage(b200lb_s * h) {
+  for (int i = 0; i < 2; i++) {
+    if (!h->stage[i]) CU(cudaMalloc(&h->stage[i], STAGE_BYTES));
+  }
+  return 0;
+}
+
+// nel planes starting at device plane e0 of `dev`; host array `host` holds them
+// in `layout` for all nsite_host sites
+static int transfer(b200lb_s * h, double * dev, int nel, double * host, int layout, bool to_device) {
+  if (ensure_stage(h)) return -1;
+  CU(cudaStreamSynchronize(h->s_main));
+  XferParams X;
+  memset(&X, 0, sizeof(X));
+  X.L = h->L;
+  for (int a = 0; a < 3; a++) { X.hostdim[a] = h->hostdim[a]; X.dax[a] = h->ops->dax[a]; }
+  X.dev = dev;
+  const i64 ns = h->nsite_host;
+  int turn = 0;
+  if (layout == B200LB_HOST_AOS) {
+    const i64 chunk = (i64) (STAGE_BYTES/sizeof(double))/nel;
+    X.aos = 1; X.nel = nel; X.e0 = 0;
+    for (i64 s0 = 0; s0 < ns; s0 += chunk, turn ^= 1) {
+      const i64 s1 = (s0 + chunk < ns) ? s0 + chunk : ns;
+      cudaStream_t st = h->s_x[turn];
+      X.stage = h->stage[turn]; X.hs0 = s0; X.hs1 = s1;
+      const size_t nb = (size_t) (s1 - s0)*nel*sizeof(double);
+      const unsigned nblk = (unsigned) ((s1 - s0 + 255)/256);
+      if (to_device) {
+	CU(cudaMemcpyAsync(X.stage, host + s0*nel, nb, cudaMemcpyHostToDevice, st));
+	xfer_kernel<1><<<nblk, 256, 0, st>>>(X);
+      }
+      else {
+	xfer_kernel<0><<<nblk, 256, 0, st>>>(X);
+	CU(cudaMemcpyAsync(host + s0*nel, X.stage, nb, cudaMemcpyDeviceToHost, st));
+      }
+      CU(cudaGetLastError());
+      h->launches++;
+    }
+  }
+  else if (layout == B200LB_HOST_SOA) {
+    const i64 chunk = (i64) (STAGE_BYTES/sizeof(double));
+    X.aos = 0; X.nel = 1;
+    for (int e = 0; e < nel; e++) {
+      for (i64 s0 = 0; s0 < ns; s0 += chunk, turn ^= 1) {
+	const i64 s1 = (s0 + chunk < ns) ? s0 + chunk : ns;
+	cudaStream_t st = h->s_x[turn];
+	X.stage = h->stage[turn]; X.hs0 = s0; X.hs1 = s1; X.e0 = e;
+	const size_t nb = (size_t) (s1 - s0)*sizeof(double);
+	const unsigned nblk = (unsigned) ((s1 - s0 + 255)/256);
+	if (to_device) {
+	  CU(cudaMemcpyAsync(X.stage, host + e*ns + s0, nb, cudaMemcpyHostToDevice, st));
+	  xfer_kernel<1><<<nblk, 256, 0, st>>>(X);
+	}
+	else {
+	  xfer_kernel<0><<<nblk, 256, 0, st>>>(X);
+	  CU(cudaMemcpyAsync(host + e*ns + s0, X.stage, nb, cudaMemcpyDeviceToHost, st));
+	}
+	CU(cudaGetLastError());
+	h->launches++;
+      }
+    }
+  }
+  else {
+    return fail("unknown host layout %d", layout);
+  }
+  CU(cudaStreamSynchronize(h->s_x[0]));
+  CU(cudaStreamSynchronize(h->s_x[1]));
+  return 0;
+}
+
+extern "C" int b200lb_f_upload(b200lb_t * h, const double * f, int layout) {
+  if (!h || !f) return fail("null argument");
+  h->prop_pending = false;          // the host copy replaces whatever was in flight
+  return transfer(h, h->lat[h->cur], h->nplane, const_cast<double *>(f), layout, true);
+}
+
+extern "C" int b200lb_f_download(b200lb_t * h, double * f, int layout) {
+  if (!h || !f) return fail("null argument");
+  if (materialise(h)) return -1;
+  return transfer(h, h->lat[h->cur], h->nplane, f, layout, false);
+}
+
+static int field_info(b200lb_s * h, int field, double ** dev, int * nf) {
+  switch (field) {
+  case B200LB_FIELD_RHO:   *dev = h->rho;   *nf = 1; break;
+  case B200LB_FIELD_U:     *dev = h->u;     *nf = 3; break;
+  case B200LB_FIELD_FORCE: *dev = h->force; *nf = 3; break;
+  case B200LB_FIELD_PHI:   *dev = h->phi;   *nf = 1; break;
+  case B200LB_FIELD_GRAD:  *dev = h->grad;  *nf = 3; break;
+  case B200LB_FIELD_DELSQ: *dev = h->delsq; *nf = 1; break;
+  default: return fail("unknown field %d", field);
+  }
+  if (!*dev) return fail("field %d not allocated (ndist = 1)", field);
+  return 0;
+}
+
+extern "C" int b200lb_field_upload(b200lb_t * h, int field, const double * host, int layout) {
+  if (!h || !host) return fail("null argument");
+  double * dev; int nf;
+  if (field_info(h, field, &dev, &nf)) return -1;
+  if (field == B200LB_FIELD_FORCE) h->force_uniform = false;
+  if (field == B200LB_FIELD_U) h->u_fill_pending = false;
+  return transfer(h, dev, nf, const_cast<double *>(host), layout, true);
+}
+
+extern "C" int b200lb_field_download(b200lb_t * h, int field, double * host, int layout) {
+  if (!h || !host) return fail("null argument");
+  double * dev; int nf;
+  if (field_info(h, field, &dev, &nf)) return -1;
+  if (field == B200LB_FIELD_FORCE && h->force_uniform) {
+    if (fill3(h, h->force, 3, h->fconst)) return -1;
+  }
+  if (field == B200LB_FIELD_U && h->u_fill_pending) {
+    if (fill3(h, h->u, 3, h->uconst)) return -1;
+    h->u_fill_pending = false;
+  }
+  if ((field == B200LB_FIELD_U || field == B200LB_FIELD_RHO) && h->hydro_stale) {
+    return fail("rho/u were not stored by the last collision (option hydro_write = 0)");
+  }
+  return transfer(h, dev, nf, host, layout, false);
+}
+
+// ---------------------------------------------------------------------------
+// NCCL communicator
+// ---------------------------------------------------------------------------
+
+extern "C" int b200lb_nccl_unique_id(char id[128]) {
+  if (nccl_load()) return -1;
+  ncclUniqueId uid;
+  NC(g_nccl.GetUniqueId(&uid));
+  static_assert(sizeof(uid) == 128, "ncclUniqueId is 128 bytes");
+  memcpy(id, &uid, 128);
+  return 0;
+}
+
+extern "C" int b200lb_comm_init(b200lb_t * h, const char id[128]) {
+  if (!h || !id) return fail("null argument");
+  if (nccl_load()) return -1;
+  ncclUniqueId uid;
+  memcpy(&uid, id, 128);
+  NC(g_nccl.CommInitRank(&h->comm, h->desc.nranks, uid, h->desc.rank));
+  return 0;
+}
+
+// ---------------------------------------------------------------------------
+// timing, pinned memory
+// ---------------------------------------------------------------------------
+
+extern "C" int b200lb_timer_start(b200lb_t * h) {
+  if (!h) return fail("null handle");
+  CU(cudaStreamSynchronize(h->s_main));
+  CU(cudaEventRecord(h->ev0, h->s_main));
+  return 0;
+}
+
+extern "C" int b200lb_timer_stop(b200lb_t * h, float * ms) {
+  if (!h || !ms) return fail("null argument");
+  CU(cudaEventRecord(h->ev1, h->s_main));
+  CU(cudaEventSynchronize(h->ev1));
+  CU(cudaEventElapsedTime(ms, h->ev0, h->ev1));
+  return 0;
+}
+
+extern "C" long b200lb_launch_count(const b200lb_t * h) { return h ? h->launches : 0; }
+
+extern "C" int b200lb_host_alloc(void ** ptr, long nbytes) {
+  if (!ptr) return fail("null argument");
+  CU(cudaMallocHost(ptr, (size_t) nbytes));
+  return 0;
+}
+
+extern "C" int b200lb_host_free(void * ptr) {
+  if (ptr) CU(cudaFreeHost(ptr));
+  return 0;
+}

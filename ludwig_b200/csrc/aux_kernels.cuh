@@ -1,0 +1,117 @@
+// aux_kernels.cuh -- model-dependent helpers: order parameter and diagnostics.
+
+#pragma once
+
+#include "layout.cuh"
+#include "models.cuh"
+
+// ---------------------------------------------------------------------------
+// phi = sum_p g_p, p in index order (src/phi_lb_coupler.c:72-102), interior.
+// PULL: the lattice holds post-collision values whose propagation is still
+// pending, so the sum runs over g_p(r - c_p): identical to propagating first.
+// ---------------------------------------------------------------------------
+
+template <class M, bool PULL>
+__global__ void __launch_bounds__(256)
+phi_from_g_kernel(const Layout L, const double * __restrict__ g, double * __restrict__ phi) {
+
+  const int i2 = blockIdx.x*blockDim.x + threadIdx.x;
+  const int i1 = blockIdx.y*blockDim.y + threadIdx.y;
+  const int i0 = blockIdx.z;
+  if (i2 >= L.n[2] || i1 >= L.n[1]) return;
+  const i64 site = (i64)(i0 + L.h[0])*L.s0 + (i64)(i1 + L.h[1])*L.s1 + L.z0 + L.h[2] + i2;
+
+  double v[M::NVEL];
+  #pragma unroll
+  for (int p = 0; p < M::NVEL; p++) {
+    i64 s = site;
+    if (PULL) s -= dcv<M>(p, 0)*L.s0 + dcv<M>(p, 1)*L.s1 + dcv<M>(p, 2);
+    v[p] = __ldg(g + (i64) p*L.nsd + s);
+  }
+  double sum = 0.0;
+  #pragma unroll
+  for (int p = 0; p < M::NVEL; p++) sum += v[p];
+  phi[site] = sum;
+}
+
+// ---------------------------------------------------------------------------
+// Conserved-quantity diagnostics over the interior (restates the sums of
+// stats_distribution_print / distribution_gm_kernel,
+// src/stats_distribution.c:55-118, :281-362): warp-shuffle reduction, one
+// partial per block, then one block folds the partials in a fixed order
+// (deterministic; no atomics).
+// out: sum rho, sum rho^2, min rho, max rho, g[3], sum phi
+// ---------------------------------------------------------------------------
+
+__device__ __forceinline__ double warp_sum(double v) {
+  #pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ double warp_min(double v) {
+  #pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ double warp_max(double v) {
+  #pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+__device__ __forceinline__ void block_reduce8(double (&q)[8], double * out) {
+  __shared__ double sm[8][8];
+  const int tid = threadIdx.y*blockDim.x + threadIdx.x;
+  const int lane = tid & 31, warp = tid >> 5;
+  const int nwarp = (blockDim.x*blockDim.y + 31) >> 5;
+  #pragma unroll
+  for (int k = 0; k < 8; k++) {
+    double r = (k == 2) ? warp_min(q[k]) : ((k == 3) ? warp_max(q[k]) : warp_sum(q[k]));
+    if (lane == 0) sm[k][warp] = r;
+  }
+  __syncthreads();
+  if (tid < 8) {
+    const int k = tid;
+    double r = sm[k][0];
+    for (int w = 1; w < nwarp; w++) {
+      r = (k == 2) ? fmin(r, sm[k][w]) : ((k == 3) ? fmax(r, sm[k][w]) : r + sm[k][w]);
+    }
+    out[k] = r;
+  }
+}
+
+template <class M, int NDIST>
+__global__ void __launch_bounds__(256)
+stats_kernel(const Layout L, const double * __restrict__ f, double * __restrict__ partial) {
+
+  const int i2 = blockIdx.x*blockDim.x + threadIdx.x;
+  const int i1 = blockIdx.y*blockDim.y + threadIdx.y;
+  const int i0 = blockIdx.z;
+  double q[8] = {0.0, 0.0, 1.0e300, -1.0e300, 0.0, 0.0, 0.0, 0.0};
+
+  if (i2 < L.n[2] && i1 < L.n[1]) {
+    const i64 site = (i64)(i0 + L.h[0])*L.s0 + (i64)(i1 + L.h[1])*L.s1 + L.z0 + L.h[2] + i2;
+    double rho = 0.0, g[3] = {0.0, 0.0, 0.0};
+    #pragma unroll
+    for (int p = 0; p < M::NVEL; p++) {
+      const double fp = __ldg(f + (i64) p*L.nsd + site);
+      rho += fp;
+      #pragma unroll
+      for (int a = 0; a < M::NDIM; a++) {
+	if (M::cv(p, a) ==  1) g[a] += fp;
+	if (M::cv(p, a) == -1) g[a] -= fp;
+      }
+    }
+    q[0] = rho; q[1] = rho*rho; q[2] = rho; q[3] = rho;
+    q[4] = g[0]; q[5] = g[1]; q[6] = g[2];
+    if (NDIST == 2) {
+      double ph = 0.0;
+      #pragma unroll
+      for (int p = 0; p < M::NVEL; p++) ph += __ldg(f + (i64)(M::NVEL + p)*L.nsd + site);
+      q[7] = ph;
+    }
+  }
+  const i64 b = ((i64) blockIdx.z*gridDim.y + blockIdx.y)*gridDim.x + blockIdx.x;
+  block_reduce8(q, partial + 8*b);
+}
+

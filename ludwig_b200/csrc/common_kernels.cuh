@@ -1,0 +1,227 @@
+// common_kernels.cuh -- model-independent kernels: halo planes, 7-point
+// gradient, fills, the last stage of the diagnostics and the host<->device
+// layout conversion. Included by api.cu only.
+
+#pragma once
+
+#include "layout.cuh"
+#include "aux_kernels.cuh"
+
+// ---------------------------------------------------------------------------
+// Halo planes of one device axis. Restates the data movement of
+// halo_swap_pack_rank1 / halo_swap_unpack_rank1 (src/halo_swap.c:1074-1274)
+// and, for a direction with one rank, the self-exchange of
+// halo_swap_packed (src/halo_swap.c:846-860): the face spans the FULL
+// halo-inclusive extent of the other two axes, so doing the axes in order
+// carries edges and corners without diagonal messages.
+//
+// "lo list" = planes whose values travel into a LOW halo (they are read at
+// coordinate n of the sender), "hi list" likewise into a HIGH halo (read at
+// coordinate 1). With the full scheme both lists hold every plane; with the
+// reduced scheme only the populations that stream inwards (src/model.c:1192-1219).
+// Send/recv buffers are plane-major: buf[k*nface + facesite].
+// ---------------------------------------------------------------------------
+
+#define B200LB_MAXEL 54
+
+enum { HALO_LOCAL = 0, HALO_PACK = 1, HALO_UNPACK = 2 };
+
+struct HaloParams {
+  Layout L;
+  double * data;
+  int axis;
+  int nlo, nhi;
+  unsigned char el_lo[B200LB_MAXEL];
+  unsigned char el_hi[B200LB_MAXEL];
+  double * to_hi;      // PACK: values for the upper neighbour's low halo
+  double * to_lo;      // PACK: values for the lower neighbour's high halo
+  const double * from_lo;  // UNPACK: into my low halo
+  const double * from_hi;  // UNPACK: into my high halo
+};
+
+template <int MODE>
+__global__ void __launch_bounds__(256)
+halo_kernel(const HaloParams H) {
+
+  const Layout & L = H.L;
+  const int d = H.axis;
+  // the two other axes, fa the faster one
+  const int fa = (d == 2) ? 1 : 2;
+  const int sl = (d == 0) ? 1 : 0;
+  const int ia = blockIdx.x*blockDim.x + threadIdx.x;
+  const int ib = blockIdx.y*blockDim.y + threadIdx.y;
+  if (ia >= L.na[fa] || ib >= L.na[sl]) return;
+  const int k = blockIdx.z;            // entry of the lo list, then of the hi list
+
+  const i64 st[3] = {L.s0, L.s1, 1};
+  const i64 base = L.z0 + (i64) ia*st[fa] + (i64) ib*st[sl];
+  const i64 nface = (i64) L.na[fa]*L.na[sl];
+  const i64 fs = (i64) ib*L.na[fa] + ia;
+  const int n = L.n[d];
+
+  if (k < H.nlo) {
+    double * plane = H.data + (i64) H.el_lo[k]*L.nsd + base;
+    if (MODE == HALO_LOCAL)  plane[0] = plane[(i64) n*st[d]];
+    if (MODE == HALO_PACK)   H.to_hi[k*nface + fs] = plane[(i64) n*st[d]];
+    if (MODE == HALO_UNPACK) plane[0] = H.from_lo[k*nface + fs];
+  }
+  else {
+    const int kk = k - H.nlo;
+    double * plane = H.data + (i64) H.el_hi[kk]*L.nsd + base;
+    if (MODE == HALO_LOCAL)  plane[(i64) (n + 1)*st[d]] = plane[st[d]];
+    if (MODE == HALO_PACK)   H.to_lo[kk*nface + fs] = plane[st[d]];
+    if (MODE == HALO_UNPACK) plane[(i64) (n + 1)*st[d]] = H.from_hi[kk*nface + fs];
+  }
+}
+
+// ---------------------------------------------------------------------------
+// 7-point gradient and Laplacian (src/gradient_3d_7pt_fluid.c:232-313, nextra
+// = 0): grad = (phi(+) - phi(-))/2, delsq summed in the order
+// +x -x +y -y +z -z -6 phi so that results are bit-identical.
+//
+// One block sweeps a (TY x TZ) tile of rows along x, keeping three z-y planes of
+// phi in shared memory as a rolling window: every phi value is fetched from
+// global memory once per tile (plus the tile's one-site apron).
+// ---------------------------------------------------------------------------
+
+#define GRAD_TZ 64
+#define GRAD_TY 4
+#define GRAD_NX 16     // x-planes marched by one block
+
+__global__ void __launch_bounds__(GRAD_TZ*GRAD_TY)
+grad7_kernel(const Layout L, const double * __restrict__ phi,
+	     double * __restrict__ grad, double * __restrict__ delsq) {
+
+  __shared__ double sm[3][GRAD_TY + 2][GRAD_TZ + 2];
+
+  const int tz = threadIdx.x, ty = threadIdx.y;
+  const int i2 = blockIdx.x*GRAD_TZ + tz;          // interior coords
+  const int i1 = blockIdx.y*GRAD_TY + ty;
+  const int x0 = blockIdx.z*GRAD_NX;
+  const int x1 = min(x0 + GRAD_NX, L.n[0]);
+
+  // halo-inclusive coordinates of this thread's column, clamped for loads
+  const int c2 = min(i2, L.n[2] - 1) + L.h[2];
+  const int c1 = min(i1, L.n[1] - 1) + L.h[1];
+  const bool active = (i2 < L.n[2]) && (i1 < L.n[1]);
+  const i64 col = (i64) c1*L.s1 + L.z0 + c2;
+
+  // loads one z-y plane (with apron) at halo-inclusive x coordinate xa into sm[slot]
+  auto load_plane = [&](int slot, int xa) {
+    const double * pl = phi + (i64) xa*L.s0;
+    sm[slot][ty + 1][tz + 1] = __ldg(pl + col);
+    if (tz == 0)             sm[slot][ty + 1][0]           = __ldg(pl + col - 1);
+    if (tz == GRAD_TZ - 1 || i2 == L.n[2] - 1)
+      sm[slot][ty + 1][tz + 2] = __ldg(pl + col + 1);
+    if (ty == 0)             sm[slot][0][tz + 1]           = __ldg(pl + col - L.s1);
+    if (ty == GRAD_TY - 1 || i1 == L.n[1] - 1)
+      sm[slot][ty + 2][tz + 1] = __ldg(pl + col + L.s1);
+  };
+
+  // planes x0-1 (halo-inclusive x0) and x0
+  load_plane(0, x0);
+  load_plane(1, x0 + 1);
+
+  for (int x = x0; x < x1; x++) {
+    const int sm1 = (x - x0) % 3, s0_ = (x - x0 + 1) % 3, sp1 = (x - x0 + 2) % 3;
+    load_plane(sp1, x + 2);
+    __syncthreads();
+    if (active) {
+      const double c  = sm[s0_][ty + 1][tz + 1];
+      const double xp = sm[sp1][ty + 1][tz + 1], xm = sm[sm1][ty + 1][tz + 1];
+      const double yp = sm[s0_][ty + 2][tz + 1], ym = sm[s0_][ty][tz + 1];
+      const double zp = sm[s0_][ty + 1][tz + 2], zm = sm[s0_][ty + 1][tz];
+      const i64 site = (i64)(x + L.h[0])*L.s0 + (i64)(i1 + L.h[1])*L.s1 + L.z0 + L.h[2] + i2;
+      grad[site]           = 0.5*(xp - xm);
+      grad[L.nsd + site]   = 0.5*(yp - ym);
+      grad[2*L.nsd + site] = 0.5*(zp - zm);
+      delsq[site] = xp + xm + yp + ym + zp + zm - 6.0*c;
+    }
+    __syncthreads();
+  }
+}
+
+// ---------------------------------------------------------------------------
+// fills (hydro_field_set, src/hydro.c:381-398) and uniform-plane helpers
+// ---------------------------------------------------------------------------
+
+__global__ void fill_kernel(double * __restrict__ data, i64 n, i64 plane, int nf,
+			    double v0, double v1, double v2) {
+  const i64 i = (i64) blockIdx.x*blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  data[i] = v0;
+  if (nf > 1) data[plane + i] = v1;
+  if (nf > 2) data[2*plane + i] = v2;
+}
+
+__global__ void __launch_bounds__(256)
+stats_final_kernel(const double * __restrict__ partial, i64 nblock, double * __restrict__ out) {
+  double q[8] = {0.0, 0.0, 1.0e300, -1.0e300, 0.0, 0.0, 0.0, 0.0};
+  for (i64 b = threadIdx.x; b < nblock; b += blockDim.x) {
+    #pragma unroll
+    for (int k = 0; k < 8; k++) {
+      const double v = partial[8*b + k];
+      q[k] = (k == 2) ? fmin(q[k], v) : ((k == 3) ? fmax(q[k], v) : q[k] + v);
+    }
+  }
+  block_reduce8(q, out);
+}
+
+// ---------------------------------------------------------------------------
+// Layout conversion between a staged piece of a HOST array and the device
+// planes (the job lb_memcpy / hydro_memcpy / field_memcpy do in the reference,
+// src/model.c:228-270). The host site index is cs_index over the physical
+// halo-inclusive box (src/coords.c:617-631); hostdim = physical nall.
+//
+//   AOS piece: stage[(hs - hs0)*nel + e],  hs in [hs0, hs1)
+//   SOA piece: one plane e0:  stage[hs - hs0]
+// TO_DEVICE = 1 host -> device, 0 device -> host.
+// For a 2-d model every host z-plane maps onto the single device plane: upload
+// takes kc = 1, download replicates (a periodic z halo of extent 1).
+// ---------------------------------------------------------------------------
+
+struct XferParams {
+  Layout L;
+  int hostdim[3];     // physical nall (x,y,z)
+  int dax[3];         // device axis -> physical axis
+  double * dev;       // device base (plane 0)
+  double * stage;
+  i64 hs0, hs1;
+  int nel;            // planes per site in an AOS piece
+  int e0;             // first device plane (SOA piece: the plane)
+  int aos;
+};
+
+template <int TO_DEVICE>
+__global__ void __launch_bounds__(256)
+xfer_kernel(const XferParams X) {
+  const i64 hs = X.hs0 + (i64) blockIdx.x*blockDim.x + threadIdx.x;
+  if (hs >= X.hs1) return;
+  const Layout & L = X.L;
+  int pc[3];
+  pc[2] = (int) (hs % X.hostdim[2]);
+  const i64 r = hs / X.hostdim[2];
+  pc[1] = (int) (r % X.hostdim[1]);
+  pc[0] = (int) (r / X.hostdim[1]);
+  int dc[3];
+  bool primary = true;     // false for replicated planes of the unit axis
+  #pragma unroll
+  for (int d = 0; d < 3; d++) {
+    int c = pc[X.dax[d]];
+    if (L.h[d] == 0) { if (c != 1) primary = false; c = 0; }
+    dc[d] = c;
+  }
+  const i64 site = (i64) dc[0]*L.s0 + (i64) dc[1]*L.s1 + L.z0 + dc[2];
+  if (TO_DEVICE && !primary) return;
+  if (X.aos) {
+    double * st = X.stage + (hs - X.hs0)*X.nel;
+    for (int e = 0; e < X.nel; e++) {
+      if (TO_DEVICE) X.dev[(i64)(X.e0 + e)*L.nsd + site] = st[e];
+      else st[e] = X.dev[(i64)(X.e0 + e)*L.nsd + site];
+    }
+  }
+  else {
+    if (TO_DEVICE) X.dev[(i64) X.e0*L.nsd + site] = X.stage[hs - X.hs0];
+    else X.stage[hs - X.hs0] = X.dev[(i64) X.e0*L.nsd + site];
+  }
+}

@@ -1,0 +1,52 @@
+// layout.cuh -- the private device layout and the kernel parameter blocks.
+//
+// Device layout ("site-contiguous SoA"): one plane of doubles per population,
+//   f[(n*nvel + p)*nsd + site],  site = i0*s0 + i1*s1 + z0 + i2
+// with (i0,i1,i2) halo-inclusive 0-based device coordinates, i2 contiguous.
+// Rows are padded so that the first interior site of every row sits on a
+// multiple of `zalign` doubles (z0 = zalign - h2): 128-bit accesses of site
+// pairs are then always aligned and rows start on 128-byte lines.
+// For 3-d models device axes = physical (x,y,z); for D2Q9 they are (z,x,y) with
+// the unit z extent first (see models.cuh), so the contiguous axis is always long.
+//
+// The reference's layouts are src/memory.h:124-130 (AOS) and :187 (SOA) with int
+// indices; here every index is 64-bit.
+
+#pragma once
+
+typedef long long i64;
+
+struct Layout {
+  int n[3];     // interior extent per device axis
+  int h[3];     // halo width per device axis (1, or 0 for the unit axis of a 2-d lattice)
+  int na[3];    // n + 2h
+  int z0;       // padding in front of each row
+  i64 s0, s1;   // strides of device axes 0 and 1 (axis 2 has stride 1)
+  i64 nsd;      // doubles per population plane
+};
+
+#define B200LB_MAXGHOST 17
+
+// Per-launch parameters (passed by value: they live in the constant bank).
+struct KParams {
+  Layout L;
+  const double * src;     // lattice read
+  double * dst;           // lattice written (== src for the in-place collision)
+  double * rho;           // [nsd]
+  double * u;             // [3][nsd]
+  const double * force;   // [3][nsd] or nullptr when the force field is uniformly fzero
+  const double * phi;     // [nsd]
+  const double * grad;    // [3][nsd]
+  const double * delsq;   // [nsd]
+  int lo[3], hi[3];       // sub-box of the interior, 0-based interior coordinates, [lo,hi)
+  double rtau_shear, rtau_bulk;
+  double fg[3];           // uniform part of the force: force_global + constant field value
+  double rtau2, A, B, kappa;
+  double gkeep[B200LB_MAXGHOST];   // 1 - rtau_k for each ghost mode
+};
+
+// Ghost-mode projectors (host-built, one __constant__ copy per model).
+struct GhostTab {
+  double fwd[B200LB_MAXGHOST][27];   // m_k = sum_p fwd[k][p] f_p
+  double bwd[27][B200LB_MAXGHOST];   // f_p += sum_k bwd[p][k] m_k
+};

@@ -1,0 +1,105 @@
+// model_impl.cuh -- body shared by the three model translation units.
+// Define B200LB_MODEL (D3Q19 ...) and B200LB_OPS_FN before
+// including. Binary-fluid kernels are built for 3-d models only
+// (src/collision.c:618 asserts NDIM == 3 for lb_collision_binary).
+
+#include "model_ops.cuh"
+#include "model_tables.h"
+
+static __constant__ GhostTab c_ghost;
+
+#include "site_kernels.cuh"
+#include "aux_kernels.cuh"
+
+typedef B200LB_MODEL MODEL;
+
+template <int VEC, bool PULL, bool COLLIDE, bool BINARY, bool GHOST>
+static cudaError_t launch_one(const SweepArgs & a) {
+  const KParams & P = a.P;
+  const int n2 = P.hi[2] - P.lo[2], n1 = P.hi[1] - P.lo[1], n0 = P.hi[0] - P.lo[0];
+  if (n0 <= 0 || n1 <= 0 || n2 <= 0) return cudaSuccess;
+  const int nt2 = (n2 + VEC - 1)/VEC;
+  int bx = a.bx;
+  while (bx > 32 && bx/2 >= nt2) bx /= 2;
+  int by = 256/bx;
+  if (BINARY || GHOST) by = (128/bx > 0) ? 128/bx : 1;
+  while (by > 1 && by/2 >= n1) by /= 2;
+  dim3 block(bx, by, 1);
+  dim3 grid((nt2 + bx - 1)/bx, (n1 + by - 1)/by, n0);
+  lb_sweep_kernel<MODEL, VEC, PULL, COLLIDE, BINARY, GHOST>
+    <<<grid, block, 0, a.stream>>>(P);
+  return cudaGetLastError();
+}
+
+template <bool PULL, bool COLLIDE>
+static cudaError_t launch_pc(const SweepArgs & a) {
+  constexpr bool HAVE_BINARY = (MODEL::NDIM == 3);
+  if constexpr (!COLLIDE) {
+    // pure streaming: collision flags are irrelevant
+    if (a.binary) {
+      if (!HAVE_BINARY) return cudaErrorInvalidValue;
+      if (a.vec == 2) return launch_one<2, PULL, false, HAVE_BINARY, false>(a);
+      return launch_one<1, PULL, false, HAVE_BINARY, false>(a);
+    }
+    if (a.vec == 2) return launch_one<2, PULL, false, false, false>(a);
+    return launch_one<1, PULL, false, false, false>(a);
+  }
+  else {
+  if (a.binary) {
+    if (!HAVE_BINARY) return cudaErrorInvalidValue;
+    if (a.ghost) return launch_one<1, PULL, COLLIDE, HAVE_BINARY, true>(a);
+    return launch_one<1, PULL, COLLIDE, HAVE_BINARY, false>(a);
+  }
+  if (a.ghost) return launch_one<1, PULL, COLLIDE, false, true>(a);
+  if (a.vec == 2) return launch_one<2, PULL, COLLIDE, false, false>(a);
+  return launch_one<1, PULL, COLLIDE, false, false>(a);
+  }
+}
+
+static cudaError_t sweep_impl(const SweepArgs & a) {
+  if (a.pull && a.collide) return launch_pc<true, true>(a);
+  if (a.pull) return launch_pc<true, false>(a);
+  if (a.collide) return launch_pc<false, true>(a);
+  return cudaErrorInvalidValue;
+}
+
+static cudaError_t phi_impl(const Layout & L, const double * g, double * phi,
+			    bool pull, cudaStream_t s) {
+  dim3 block(128, 2, 1);
+  dim3 grid((L.n[2] + 127)/128, (L.n[1] + 1)/2, L.n[0]);
+  if (pull) phi_from_g_kernel<MODEL, true><<<grid, block, 0, s>>>(L, g, phi);
+  else phi_from_g_kernel<MODEL, false><<<grid, block, 0, s>>>(L, g, phi);
+  return cudaGetLastError();
+}
+
+static cudaError_t stats_impl(const Layout & L, const double * f, int ndist,
+			      double * partial, dim3 grid, dim3 block, cudaStream_t s) {
+  if (ndist == 2) stats_kernel<MODEL, 2><<<grid, block, 0, s>>>(L, f, partial);
+  else stats_kernel<MODEL, 1><<<grid, block, 0, s>>>(L, f, partial);
+  return cudaGetLastError();
+}
+
+static cudaError_t ghost_upload_impl(void) {
+  static GhostTab T;
+  build_ghost_tab<MODEL>(T);
+  return cudaMemcpyToSymbol(c_ghost, &T, sizeof(GhostTab));
+}
+
+const ModelOps * B200LB_OPS_FN(void) {
+  static ModelOps ops;
+  static bool init = false;
+  if (!init) {
+    ops.nvel = MODEL::NVEL; ops.ndim = MODEL::NDIM; ops.nhydro = MODEL::NHYDRO;
+    for (int d = 0; d < 3; d++) ops.dax[d] = MODEL::dax(d);
+    for (int p = 0; p < MODEL::NVEL; p++) {
+      for (int a = 0; a < 3; a++) ops.cv[p][a] = MODEL::cv(p, a);
+      ops.wv[p] = MODEL::wv(p);
+    }
+    ops.sweep = sweep_impl;
+    ops.phi_from_g = phi_impl;
+    ops.stats = stats_impl;
+    ops.ghost_upload = ghost_upload_impl;
+    init = true;
+  }
+  return &ops;
+}

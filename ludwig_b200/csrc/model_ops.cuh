@@ -1,0 +1,33 @@
+// model_ops.cuh -- per-velocity-set launchers, instantiated once per model in
+// model_d3q19.cu / model_d3q27.cu / model_d2q9.cu so the three compile in parallel.
+
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include "layout.cuh"
+
+struct SweepArgs {
+  KParams P;
+  bool pull, collide, binary, ghost;
+  int vec;            // sites per thread (1 or 2)
+  int bx;             // threads per block along the contiguous axis
+  cudaStream_t stream;
+};
+
+struct ModelOps {
+  int nvel, ndim, nhydro;
+  int dax[3];                                   // device axis -> physical axis
+  int cv[27][3];
+  double wv[27];
+  cudaError_t (*sweep)(const SweepArgs &);
+  cudaError_t (*phi_from_g)(const Layout &, const double * g, double * phi,
+			    bool pull, cudaStream_t);
+  cudaError_t (*stats)(const Layout &, const double * f, int ndist,
+		       double * partial, dim3 grid, dim3 block, cudaStream_t);
+  cudaError_t (*ghost_upload)(void);
+};
+
+const ModelOps * model_ops_d3q19(void);
+const ModelOps * model_ops_d3q27(void);
+const ModelOps * model_ops_d2q9(void);

@@ -1,0 +1,351 @@
+// site_kernels.cuh -- the lattice sweep: pull streaming and/or collision.
+//
+// ONE kernel template covers the three sweeps of the reference:
+//   PULL=0 COLLIDE=1   lb_collision_mrt1 / lb_collision_mrt2, in place
+//                      (src/collision.c:224-599, :660-1027)
+//   PULL=1 COLLIDE=0   lb_propagation_kernel (src/propagation.c:162-212)
+//   PULL=1 COLLIDE=1   fused stream-then-collide used by the lazy-propagation
+//                      mode: f'(r) = C( f(r - c_p) ), one read + one write of
+//                      every population per step.
+// It is not a port: the reference's generic Q x Q mode products become a
+// pair-symmetric projection onto the 10 (6 in 2-d) hydrodynamic moments with
+// constant-folded coefficients, ghost modes are touched only when a scheme
+// relaxes them partially, and every access is a coalesced 64/128-bit access of
+// the site-contiguous SoA layout (layout.cuh).
+
+#pragma once
+
+#include "layout.cuh"
+#include "models.cuh"
+
+// Each model lives in its own translation unit (model_*.cu), which defines its
+// ghost-mode projector table before including this file.
+template <class M> __device__ __forceinline__ const GhostTab & ghost_tab() { return c_ghost; }
+
+template <bool NC> __device__ __forceinline__ double ld1(const double * p) {
+  if (NC) return __ldg(p);
+  return *p;
+}
+template <bool NC> __device__ __forceinline__ double2 ld2(const double * p) {
+  if (NC) return __ldg(reinterpret_cast<const double2 *>(p));
+  return *reinterpret_cast<const double2 *>(p);
+}
+
+// ---------------------------------------------------------------------------
+// Multiple-relaxation-time collision of one site (src/collision.c:339-558).
+//   f      in: pre-collision populations, out: post-collision
+//   F      total force on the site (global + field), physical components
+//   sth    thermodynamic stress added to the equilibrium stress (binary fluid,
+//          src/collision.c:833-848), symmetric storage, or nullptr
+// Writes rho and u = (rho u + F/2)/rho (src/collision.c:355-382).
+// ---------------------------------------------------------------------------
+
+template <class M, bool GHOST, bool STH>
+__device__ __forceinline__ void
+mrt_site(double (&f)[M::NVEL], const double (&F)[3], const double * sth,
+	 const KParams & P, double & rho_out, double (&u)[3]) {
+
+  constexpr int Q  = M::NVEL;
+  constexpr int ND = M::NDIM;
+  constexpr int NS = NSym<M>::value;
+  constexpr int H  = (Q - 1)/2;
+  constexpr int NG = Q - M::NHYDRO;
+  constexpr double rdim = 1.0/ND;
+
+  // ghost modes of the incoming state (only when some are kept)
+  double mg[GHOST ? NG : 1];
+  if (GHOST) {
+    const GhostTab & T = ghost_tab<M>();
+    #pragma unroll
+    for (int k = 0; k < NG; k++) {
+      double s = 0.0;
+      #pragma unroll
+      for (int p = 0; p < Q; p++) s = fma(T.fwd[k][p], f[p], s);
+      mg[k] = P.gkeep[k]*s;
+    }
+  }
+
+  // hydrodynamic moments from (p, Q-p) pairs
+  double rho = f[0];
+  double j[ND];
+  double S[NS];
+  #pragma unroll
+  for (int a = 0; a < ND; a++) j[a] = 0.0;
+  #pragma unroll
+  for (int k = 0; k < NS; k++) S[k] = 0.0;
+
+  #pragma unroll
+  for (int p = 1; p <= H; p++) {
+    const double s = f[p] + f[Q - p];
+    const double d = f[p] - f[Q - p];
+    rho += s;
+    #pragma unroll
+    for (int a = 0; a < ND; a++) {
+      if (M::cv(p, a) ==  1) j[a] += d;
+      if (M::cv(p, a) == -1) j[a] -= d;
+      #pragma unroll
+      for (int b = a; b < ND; b++) {
+	if (M::cv(p, a)*M::cv(p, b) ==  1) S[sidx<M>(a, b)] += s;
+	if (M::cv(p, a)*M::cv(p, b) == -1) S[sidx<M>(a, b)] -= s;
+      }
+    }
+  }
+  // S_ab = sum_p (c_a c_b - cs2 delta_ab) f_p
+  #pragma unroll
+  for (int a = 0; a < ND; a++) S[sidx<M>(a, a)] -= (1.0/3.0)*rho;
+
+  const double rrho = 1.0/rho;
+  #pragma unroll
+  for (int a = 0; a < 3; a++) u[a] = 0.0;
+  #pragma unroll
+  for (int a = 0; a < ND; a++) u[a] = rrho*(j[a] + 0.5*F[a]);
+
+  // relax the stress towards rho u u (+ sth): trace with rtau_bulk, traceless
+  // part with rtau_shear, then the force correction (src/collision.c:413-474)
+  double seq[NS];
+  double tr_s = 0.0, tr_seq = 0.0;
+  #pragma unroll
+  for (int a = 0; a < ND; a++) {
+    #pragma unroll
+    for (int b = a; b < ND; b++) {
+      double e = rho*u[a]*u[b];
+      if (STH) e += sth[sidx<M>(a, b)];
+      seq[sidx<M>(a, b)] = e;
+    }
+    tr_s   += S[sidx<M>(a, a)];
+    tr_seq += seq[sidx<M>(a, a)];
+  }
+  #pragma unroll
+  for (int a = 0; a < ND; a++) {
+    S[sidx<M>(a, a)]   -= rdim*tr_s;
+    seq[sidx<M>(a, a)] -= rdim*tr_seq;
+  }
+  tr_s = tr_s - P.rtau_bulk*(tr_s - tr_seq);
+  const double fcorr = 2.0 - P.rtau_shear;
+  #pragma unroll
+  for (int a = 0; a < ND; a++) {
+    #pragma unroll
+    for (int b = a; b < ND; b++) {
+      const int k = sidx<M>(a, b);
+      double s = S[k] - P.rtau_shear*(S[k] - seq[k]);
+      if (a == b) s += rdim*tr_s;
+      s += fcorr*(u[a]*F[b] + F[a]*u[b]);
+      S[k] = s;
+    }
+  }
+  #pragma unroll
+  for (int a = 0; a < ND; a++) j[a] += F[a];
+
+  // back-projection: f_p = w_p (rho + 3 c.j + 9/2 (c_a c_a - 1/3) S_aa + 9 c_a c_b S_ab)
+  double A0 = rho;
+  #pragma unroll
+  for (int a = 0; a < ND; a++) {
+    A0 -= 1.5*S[sidx<M>(a, a)];
+    j[a] *= 3.0;
+    #pragma unroll
+    for (int b = a; b < ND; b++) S[sidx<M>(a, b)] *= (a == b) ? 4.5 : 9.0;
+  }
+  f[0] = M::wv(0)*A0;
+  #pragma unroll
+  for (int p = 1; p <= H; p++) {
+    double ev = A0;
+    double od = 0.0;
+    #pragma unroll
+    for (int a = 0; a < ND; a++) {
+      if (M::cv(p, a) ==  1) od += j[a];
+      if (M::cv(p, a) == -1) od -= j[a];
+      #pragma unroll
+      for (int b = a; b < ND; b++) {
+	if (M::cv(p, a)*M::cv(p, b) ==  1) ev += S[sidx<M>(a, b)];
+	if (M::cv(p, a)*M::cv(p, b) == -1) ev -= S[sidx<M>(a, b)];
+      }
+    }
+    f[p]     = M::wv(p)*(ev + od);
+    f[Q - p] = M::wv(p)*(ev - od);
+  }
+
+  if (GHOST) {
+    const GhostTab & T = ghost_tab<M>();
+    #pragma unroll
+    for (int p = 0; p < Q; p++) {
+      double s = f[p];
+      #pragma unroll
+      for (int k = 0; k < NG; k++) s = fma(T.bwd[p][k], mg[k], s);
+      f[p] = s;
+    }
+  }
+
+  rho_out = rho;
+}
+
+// ---------------------------------------------------------------------------
+// Order-parameter distribution of the binary fluid (src/collision.c:956-1023):
+// g is rebuilt from phi, the relaxed flux j_phi and phi u u + mu delta.
+// ---------------------------------------------------------------------------
+
+template <class M>
+__device__ __forceinline__ void
+phi_site(double (&g)[M::NVEL], double phi, double mu, const double (&u)[3],
+	 double rtau2) {
+
+  constexpr int Q  = M::NVEL;
+  constexpr int ND = M::NDIM;
+  constexpr int NS = NSym<M>::value;
+  constexpr int H  = (Q - 1)/2;
+
+  double j[ND];
+  #pragma unroll
+  for (int a = 0; a < ND; a++) j[a] = 0.0;
+  #pragma unroll
+  for (int p = 1; p <= H; p++) {
+    const double d = g[p] - g[Q - p];
+    #pragma unroll
+    for (int a = 0; a < ND; a++) {
+      if (M::cv(p, a) ==  1) j[a] += d;
+      if (M::cv(p, a) == -1) j[a] -= d;
+    }
+  }
+  double S[NS];
+  double B0 = 0.0;
+  #pragma unroll
+  for (int a = 0; a < ND; a++) {
+    j[a] = 3.0*(j[a] - rtau2*(j[a] - phi*u[a]));
+    #pragma unroll
+    for (int b = a; b < ND; b++) {
+      double s = phi*u[a]*u[b];
+      if (a == b) { s += mu; B0 -= 1.5*s; s *= 4.5; } else { s *= 9.0; }
+      S[sidx<M>(a, b)] = s;
+    }
+  }
+  g[0] = M::wv(0)*B0 + phi;
+  #pragma unroll
+  for (int p = 1; p <= H; p++) {
+    double ev = B0;
+    double od = 0.0;
+    #pragma unroll
+    for (int a = 0; a < ND; a++) {
+      if (M::cv(p, a) ==  1) od += j[a];
+      if (M::cv(p, a) == -1) od -= j[a];
+      #pragma unroll
+      for (int b = a; b < ND; b++) {
+	if (M::cv(p, a)*M::cv(p, b) ==  1) ev += S[sidx<M>(a, b)];
+	if (M::cv(p, a)*M::cv(p, b) == -1) ev -= S[sidx<M>(a, b)];
+      }
+    }
+    g[p]     = M::wv(p)*(ev + od);
+    g[Q - p] = M::wv(p)*(ev - od);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// The sweep. Thread (x) covers VEC consecutive sites of the contiguous axis,
+// thread (y) a row; blockIdx.z is the slowest axis. With VEC = 2 populations
+// moving along the contiguous axis are read as two 64-bit loads (they straddle
+// the aligned pair), all others and every store are 128-bit.
+// ---------------------------------------------------------------------------
+
+template <class M, int VEC, bool PULL, bool COLLIDE, bool BINARY, bool GHOST>
+__global__ void __launch_bounds__(256)
+lb_sweep_kernel(const KParams P) {
+
+  constexpr int Q  = M::NVEL;
+  constexpr int ND = M::NDIM;
+  constexpr int NDIST = BINARY ? 2 : 1;
+  constexpr bool NC = PULL;          // source is read-only when it is not the destination
+
+  const Layout & L = P.L;
+
+  const int i2 = P.lo[2] + VEC*(blockIdx.x*blockDim.x + threadIdx.x);
+  const int i1 = P.lo[1] + blockIdx.y*blockDim.y + threadIdx.y;
+  const int i0 = P.lo[0] + blockIdx.z;
+  if (i2 >= P.hi[2] || i1 >= P.hi[1]) return;
+  const int nv = (VEC == 2 && i2 + 1 < P.hi[2]) ? 2 : 1;
+
+  const i64 site = (i64)(i0 + L.h[0])*L.s0 + (i64)(i1 + L.h[1])*L.s1
+                 + L.z0 + L.h[2] + i2;
+
+  double f[NDIST][VEC][Q];
+
+  #pragma unroll
+  for (int n = 0; n < NDIST; n++) {
+    #pragma unroll
+    for (int p = 0; p < Q; p++) {
+      const double * src = P.src + (i64)(n*Q + p)*L.nsd + site;
+      int c2 = 0;
+      if (PULL) {
+	src -= dcv<M>(p, 0)*L.s0 + dcv<M>(p, 1)*L.s1 + dcv<M>(p, 2);
+	c2 = dcv<M>(p, 2);
+      }
+      if (VEC == 2) {
+	if (c2 == 0) {
+	  const double2 v = ld2<NC>(src);
+	  f[n][0][p] = v.x; f[n][VEC - 1][p] = v.y;
+	}
+	else {
+	  f[n][0][p] = ld1<NC>(src);
+	  f[n][VEC - 1][p] = ld1<NC>(src + 1);
+	}
+      }
+      else {
+	f[n][0][p] = ld1<NC>(src);
+      }
+    }
+  }
+
+  if (COLLIDE) {
+    #pragma unroll
+    for (int v = 0; v < VEC; v++) {
+      const i64 s = site + v;
+      double F[3] = {P.fg[0], P.fg[1], P.fg[2]};
+      if (P.force != nullptr) {          // uniform branch: per-site force field present
+	#pragma unroll
+	for (int a = 0; a < ND; a++) F[a] += P.force[a*L.nsd + s];
+      }
+      double rho, u[3];
+      if (BINARY) {
+	const double phi = P.phi[s];
+	const double dsq = P.delsq[s];
+	double gr[3];
+	#pragma unroll
+	for (int a = 0; a < 3; a++) gr[a] = P.grad[a*L.nsd + s];
+	// fe_symm_str_v / fe_symm_mu (src/symmetric.c:371-420, :307-320)
+	const double p0 = 0.5*P.A*phi*phi + 0.75*P.B*phi*phi*phi*phi
+	  - P.kappa*phi*dsq
+	  - 0.5*P.kappa*(gr[0]*gr[0] + gr[1]*gr[1] + gr[2]*gr[2]);
+	double sth[NSym<M>::value];
+	#pragma unroll
+	for (int a = 0; a < ND; a++) {
+	  #pragma unroll
+	  for (int b = a; b < ND; b++) {
+	    sth[sidx<M>(a, b)] = ((a == b) ? p0 : 0.0) + P.kappa*gr[a]*gr[b];
+	  }
+	}
+	const double mu = P.A*phi + P.B*phi*phi*phi - P.kappa*dsq;
+	mrt_site<M, GHOST, true>(f[0][v], F, sth, P, rho, u);
+	phi_site<M>(f[NDIST - 1][v], phi, mu, u, P.rtau2);
+      }
+      else {
+	mrt_site<M, GHOST, false>(f[0][v], F, nullptr, P, rho, u);
+      }
+      if (P.u != nullptr && (v < nv)) {  // uniform branch: hydro stored this step
+	if (!BINARY) P.rho[s] = rho;     // the binary collision leaves rho alone
+	#pragma unroll
+	for (int a = 0; a < 3; a++) P.u[a*L.nsd + s] = u[a];
+      }
+    }
+  }
+
+  #pragma unroll
+  for (int n = 0; n < NDIST; n++) {
+    #pragma unroll
+    for (int p = 0; p < Q; p++) {
+      double * dst = P.dst + (i64)(n*Q + p)*L.nsd + site;
+      if (VEC == 2 && nv == 2) {
+	*reinterpret_cast<double2 *>(dst) = make_double2(f[n][0][p], f[n][VEC - 1][p]);
+      }
+      else {
+	*dst = f[n][0][p];
+      }
+    }
+  }
+}

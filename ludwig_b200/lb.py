@@ -1,0 +1,306 @@
+"""ctypes binding of libb200lb.so and a thin mirror of the reference call surface.
+
+Method names follow the reference (zazu29/ludwig v0.20.1) so tests read like its own:
+lb_collide (src/collision.c:144), lb_halo / lb_halo_swap (src/model.c:553,570),
+lb_propagation (src/propagation.c:43), lb_memcpy (src/model.c:228),
+hydro_f_zero / hydro_u_zero (src/hydro.c:306,279), phi_lb_to_field
+(src/phi_lb_coupler.c:39), field_halo (src/field.c:434), field_grad_compute ->
+grad_3d_7pt_fluid_d2 (src/gradient_3d_7pt_fluid.c:75).
+"""
+
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIBPATH = os.path.join(_HERE, "libb200lb.so")
+
+HOST_AOS, HOST_SOA = 0, 1
+RELAX_M10, RELAX_BGK, RELAX_TRT = 0, 1, 2
+HALO_FULL, HALO_REDUCED = 0, 2
+FIELD_RHO, FIELD_U, FIELD_FORCE, FIELD_PHI, FIELD_GRAD, FIELD_DELSQ = range(6)
+_FIELD_NF = {FIELD_RHO: 1, FIELD_U: 3, FIELD_FORCE: 3, FIELD_PHI: 1, FIELD_GRAD: 3,
+             FIELD_DELSQ: 1}
+
+# every symbol include/b200lb.h declares (checked by tests/test_abi.py)
+ABI_SYMBOLS = [
+    "b200lb_last_error", "b200lb_device_count", "b200lb_version", "b200lb_create",
+    "b200lb_destroy", "b200lb_nsite", "b200lb_set_option", "b200lb_get_option",
+    "b200lb_f_upload", "b200lb_f_download", "b200lb_field_upload",
+    "b200lb_field_download", "b200lb_set_param", "b200lb_hydro_f_zero",
+    "b200lb_hydro_u_zero", "b200lb_collide", "b200lb_halo", "b200lb_halo_swap",
+    "b200lb_propagate", "b200lb_phi_from_g", "b200lb_phi_halo", "b200lb_grad7",
+    "b200lb_step", "b200lb_stats", "b200lb_sync", "b200lb_nccl_unique_id",
+    "b200lb_comm_init", "b200lb_timer_start", "b200lb_timer_stop",
+    "b200lb_launch_count", "b200lb_host_alloc", "b200lb_host_free",
+]
+
+
+class B200LBError(RuntimeError):
+    pass
+
+
+class Desc(ctypes.Structure):
+    _fields_ = [
+        ("ndim", ctypes.c_int), ("nvel", ctypes.c_int), ("ndist", ctypes.c_int),
+        ("nlocal", ctypes.c_int * 3), ("nhalo", ctypes.c_int),
+        ("cartsz", ctypes.c_int * 3), ("cartcoords", ctypes.c_int * 3),
+        ("periodic", ctypes.c_int * 3), ("nbr_lo", ctypes.c_int * 3),
+        ("nbr_hi", ctypes.c_int * 3), ("rank", ctypes.c_int),
+        ("nranks", ctypes.c_int), ("device", ctypes.c_int), ("zalign", ctypes.c_int),
+    ]
+
+
+class Param(ctypes.Structure):
+    _fields_ = [
+        ("rho0", ctypes.c_double), ("eta_shear", ctypes.c_double),
+        ("eta_bulk", ctypes.c_double), ("force_global", ctypes.c_double * 3),
+        ("nrelax", ctypes.c_int), ("mobility", ctypes.c_double),
+        ("a", ctypes.c_double), ("b", ctypes.c_double), ("kappa", ctypes.c_double),
+    ]
+
+
+def library_path():
+    return _LIBPATH
+
+
+def build(verbose=False):
+    """Compile libb200lb.so for sm_100a (nvcc cross-compiles without a GPU)."""
+    ncpu = str(min(os.cpu_count() or 4, 8))
+    out = None if verbose else subprocess.DEVNULL
+    subprocess.check_call(["make", "-s", "-j", ncpu, "-C", os.path.join(_HERE, "csrc")],
+                          stdout=out)
+
+
+_lib = None
+
+
+def load():
+    """Load the C-ABI library. Fails loudly if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(_LIBPATH):
+        raise B200LBError("%s is missing: run `python -c 'import __graft_entry__ as g; "
+                          "g.build()'` (there is no CPU fallback)" % _LIBPATH)
+    L = ctypes.CDLL(_LIBPATH)
+    L.b200lb_last_error.restype = ctypes.c_char_p
+    L.b200lb_version.restype = ctypes.c_char_p
+    L.b200lb_nsite.restype = ctypes.c_long
+    L.b200lb_get_option.restype = ctypes.c_long
+    L.b200lb_launch_count.restype = ctypes.c_long
+    vp = ctypes.c_void_p
+    L.b200lb_create.argtypes = [ctypes.POINTER(Desc), ctypes.POINTER(vp)]
+    L.b200lb_set_option.argtypes = [vp, ctypes.c_char_p, ctypes.c_long]
+    L.b200lb_get_option.argtypes = [vp, ctypes.c_char_p]
+    L.b200lb_set_param.argtypes = [vp, ctypes.POINTER(Param)]
+    for name in ("b200lb_f_upload", "b200lb_f_download"):
+        getattr(L, name).argtypes = [vp, vp, ctypes.c_int]
+    for name in ("b200lb_field_upload", "b200lb_field_download"):
+        getattr(L, name).argtypes = [vp, ctypes.c_int, vp, ctypes.c_int]
+    for name in ("b200lb_destroy", "b200lb_collide", "b200lb_halo", "b200lb_propagate",
+                 "b200lb_phi_from_g", "b200lb_phi_halo", "b200lb_grad7", "b200lb_sync",
+                 "b200lb_timer_start", "b200lb_nsite", "b200lb_launch_count"):
+        getattr(L, name).argtypes = [vp]
+    L.b200lb_halo_swap.argtypes = [vp, ctypes.c_int]
+    L.b200lb_step.argtypes = [vp, ctypes.c_int]
+    L.b200lb_hydro_f_zero.argtypes = [vp, ctypes.POINTER(ctypes.c_double)]
+    L.b200lb_hydro_u_zero.argtypes = [vp, ctypes.POINTER(ctypes.c_double)]
+    L.b200lb_stats.argtypes = [vp, ctypes.POINTER(ctypes.c_double)]
+    L.b200lb_timer_stop.argtypes = [vp, ctypes.POINTER(ctypes.c_float)]
+    L.b200lb_nccl_unique_id.argtypes = [ctypes.c_char_p]
+    L.b200lb_comm_init.argtypes = [vp, ctypes.c_char_p]
+    L.b200lb_host_alloc.argtypes = [ctypes.POINTER(vp), ctypes.c_long]
+    L.b200lb_host_free.argtypes = [vp]
+    _lib = L
+    return L
+
+
+def _ptr(a):
+    assert a.dtype == np.float64 and a.flags["C_CONTIGUOUS"]
+    return ctypes.c_void_p(a.ctypes.data)
+
+
+def pinned_empty(shape):
+    """numpy array over cudaMallocHost memory (kept alive by the returned array)."""
+    L = load()
+    n = int(np.prod(shape))
+    p = ctypes.c_void_p()
+    if L.b200lb_host_alloc(ctypes.byref(p), n * 8) != 0:
+        raise B200LBError(L.b200lb_last_error().decode())
+    buf = (ctypes.c_double * n).from_address(p.value)
+    arr = np.frombuffer(buf, dtype=np.float64).reshape(shape)
+
+    class _Owner:
+        def __init__(self, ptr):
+            self.ptr = ptr
+
+        def __del__(self):
+            try:
+                L.b200lb_host_free(self.ptr)
+            except Exception:
+                pass
+    arr = arr.view()
+    _OWNERS[id(buf)] = (_Owner(p), buf)
+    return arr
+
+
+_OWNERS = {}
+
+
+class Lattice:
+    """One rank's lattice on one B200: the lb_t + hydro_t (+ phi, grad) of the
+    reference, device-resident in the library's private layout."""
+
+    def __init__(self, nvel, nlocal, ndist=1, decomp=None, device=-1, zalign=0):
+        self.L = load()
+        self.nvel, self.ndist = nvel, ndist
+        self.ndim = 2 if nvel == 9 else 3
+        self.nlocal = tuple(int(x) for x in nlocal)
+        d = Desc()
+        d.ndim, d.nvel, d.ndist, d.nhalo = self.ndim, nvel, ndist, 1
+        d.nlocal[:] = self.nlocal
+        if decomp is None:
+            d.cartsz[:] = (1, 1, 1)
+            d.cartcoords[:] = (0, 0, 0)
+            d.periodic[:] = (1, 1, 1)
+            d.nbr_lo[:] = (0, 0, 0)
+            d.nbr_hi[:] = (0, 0, 0)
+            d.rank, d.nranks = 0, 1
+        else:
+            d.cartsz[:] = decomp.cartsz
+            d.cartcoords[:] = decomp.coords
+            d.periodic[:] = decomp.periodic
+            d.nbr_lo[:] = decomp.nbr_lo
+            d.nbr_hi[:] = decomp.nbr_hi
+            d.rank, d.nranks = decomp.rank, decomp.nranks
+        d.device, d.zalign = device, zalign
+        self.h = ctypes.c_void_p()
+        self._ck(self.L.b200lb_create(ctypes.byref(d), ctypes.byref(self.h)))
+        self.nall = tuple(n + 2 for n in self.nlocal)
+        self.nsite = int(self.L.b200lb_nsite(self.h))
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise B200LBError(self.L.b200lb_last_error().decode())
+
+    def close(self):
+        if self.h:
+            self.L.b200lb_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- options / parameters -------------------------------------------------
+    def set_option(self, name, value):
+        self._ck(self.L.b200lb_set_option(self.h, name.encode(), int(value)))
+
+    def get_option(self, name):
+        return int(self.L.b200lb_get_option(self.h, name.encode()))
+
+    def set_param(self, rho0=1.0, eta_shear=0.1, eta_bulk=0.1, force=(0.0, 0.0, 0.0),
+                  nrelax=RELAX_M10, mobility=0.0, a=0.0, b=0.0, kappa=0.0):
+        p = Param()
+        p.rho0, p.eta_shear, p.eta_bulk = rho0, eta_shear, eta_bulk
+        p.force_global[:] = force
+        p.nrelax, p.mobility, p.a, p.b, p.kappa = nrelax, mobility, a, b, kappa
+        self._ck(self.L.b200lb_set_param(self.h, ctypes.byref(p)))
+
+    # -- lb_memcpy and friends --------------------------------------------------
+    def alloc_f(self):
+        return np.zeros((self.nsite, self.ndist, self.nvel))
+
+    def lb_memcpy_h2d(self, f, layout=HOST_AOS):
+        self._ck(self.L.b200lb_f_upload(self.h, _ptr(f), layout))
+
+    def lb_memcpy_d2h(self, f=None, layout=HOST_AOS):
+        if f is None:
+            f = (self.alloc_f() if layout == HOST_AOS
+                 else np.zeros((self.ndist, self.nvel, self.nsite)))
+        self._ck(self.L.b200lb_f_download(self.h, _ptr(f), layout))
+        return f
+
+    def field_h2d(self, field, a, layout=HOST_AOS):
+        self._ck(self.L.b200lb_field_upload(self.h, field, _ptr(a), layout))
+
+    def field_d2h(self, field, layout=HOST_AOS):
+        nf = _FIELD_NF[field]
+        shape = (self.nsite,) if nf == 1 else ((self.nsite, nf) if layout == HOST_AOS
+                                              else (nf, self.nsite))
+        a = np.zeros(shape)
+        self._ck(self.L.b200lb_field_download(self.h, field, _ptr(a), layout))
+        return a
+
+    # -- the reference call surface ---------------------------------------------
+    def hydro_f_zero(self, f=(0.0, 0.0, 0.0)):
+        self._ck(self.L.b200lb_hydro_f_zero(self.h, (ctypes.c_double * 3)(*f)))
+
+    def hydro_u_zero(self, u=(0.0, 0.0, 0.0)):
+        self._ck(self.L.b200lb_hydro_u_zero(self.h, (ctypes.c_double * 3)(*u)))
+
+    def lb_collide(self):
+        self._ck(self.L.b200lb_collide(self.h))
+
+    def lb_halo(self):
+        self._ck(self.L.b200lb_halo(self.h))
+
+    def lb_halo_swap(self, scheme):
+        self._ck(self.L.b200lb_halo_swap(self.h, scheme))
+
+    def lb_propagation(self):
+        self._ck(self.L.b200lb_propagate(self.h))
+
+    def phi_lb_to_field(self):
+        self._ck(self.L.b200lb_phi_from_g(self.h))
+
+    def field_halo(self):
+        self._ck(self.L.b200lb_phi_halo(self.h))
+
+    def field_grad_compute(self):
+        self._ck(self.L.b200lb_grad7(self.h))
+
+    def step(self, nsteps=1):
+        self._ck(self.L.b200lb_step(self.h, nsteps))
+
+    def stats(self):
+        out = (ctypes.c_double * 8)()
+        self._ck(self.L.b200lb_stats(self.h, out))
+        return np.array(out[:])
+
+    def sync(self):
+        self._ck(self.L.b200lb_sync(self.h))
+
+    # -- timing / comm ------------------------------------------------------------
+    def timer_start(self):
+        self._ck(self.L.b200lb_timer_start(self.h))
+
+    def timer_stop(self):
+        ms = ctypes.c_float()
+        self._ck(self.L.b200lb_timer_stop(self.h, ctypes.byref(ms)))
+        return float(ms.value)
+
+    def launch_count(self):
+        return int(self.L.b200lb_launch_count(self.h))
+
+    @staticmethod
+    def nccl_unique_id():
+        L = load()
+        buf = ctypes.create_string_buffer(128)
+        if L.b200lb_nccl_unique_id(buf) != 0:
+            raise B200LBError(L.b200lb_last_error().decode())
+        return buf.raw
+
+    def comm_init(self, uid):
+        self._ck(self.L.b200lb_comm_init(self.h, ctypes.create_string_buffer(uid, 128)))

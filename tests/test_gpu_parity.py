@@ -1,0 +1,354 @@
+"""GPU parity: the CUDA path, called through the C ABI (libb200lb.so via ctypes),
+against the CPU oracle and the reference-produced golden vectors on identical inputs.
+
+Bars (BASELINE.json north_star): propagation, halo, layout conversion, phi and the
+7-point gradient are BIT-EXACT; collision and hydro agree within 1e-12 relative
+(relative to max |f|, the absolute floor the reference's own regression diff uses);
+mass conserved to round-off.
+"""
+
+import numpy as np
+import pytest
+
+import lbinit
+import goldenlib
+from goldenlib import relerr
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-12
+CASES = [(19, (12, 10, 8)), (27, (8, 6, 10)), (9, (16, 12, 1)),
+         (19, (5, 7, 33)), (9, (7, 131, 1))]
+
+
+def mk(nvel, nlocal, ndist=1, **kw):
+    import ludwig_b200 as lb
+    from oracle import pyoracle
+    lat = lb.Lattice(nvel, nlocal, ndist=ndist, **kw)
+    orc = pyoracle.Oracle(nvel, nlocal, ndist=ndist)
+    return lat, orc
+
+
+@pytest.mark.parametrize("nvel,nlocal", CASES)
+@pytest.mark.parametrize("ndist", [1, 2])
+def test_lb_memcpy_roundtrip(nvel, nlocal, ndist):
+    import ludwig_b200 as lb
+    if ndist == 2 and nvel == 9:
+        pytest.skip("binary fluid is 3-d")
+    lat, orc = mk(nvel, nlocal, ndist)
+    rng = np.random.default_rng(1)
+    f0 = rng.standard_normal((orc.nsite, ndist, nvel))
+    if nvel == 9:
+        # z halo planes of a 2-d lattice are periodic images of the single plane
+        f3 = f0.reshape(orc.nall + (ndist, nvel))
+        f3[:, :, 0] = f3[:, :, 1]
+        f3[:, :, 2] = f3[:, :, 1]
+    lat.lb_memcpy_h2d(f0)
+    assert np.array_equal(lat.lb_memcpy_d2h(), f0)
+    soa = lat.lb_memcpy_d2h(layout=lb.HOST_SOA)
+    assert np.array_equal(soa, np.ascontiguousarray(f0.transpose(1, 2, 0)))
+    lat.lb_memcpy_h2d(soa, layout=lb.HOST_SOA)
+    assert np.array_equal(lat.lb_memcpy_d2h(), f0)
+    lat.close()
+
+
+@pytest.mark.parametrize("nvel,nlocal", CASES)
+@pytest.mark.parametrize("nrelax", [0, 1, 2])
+@pytest.mark.parametrize("vec", [1, 2])
+def test_collide_vs_oracle(nvel, nlocal, nrelax, vec):
+    from oracle import pyoracle
+    import ludwig_b200 as lb
+    if nrelax == 2 and nvel != 19:
+        pytest.skip("TRT is D3Q19 only in the reference")
+    lat, orc = mk(nvel, nlocal)
+    lat.set_option("vec", vec)
+    ndim = orc.ndim
+    f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal, ndim=ndim)
+    force = lbinit.make_force(nlocal, ndim=ndim)
+    fg = (1e-4, -2e-4, 3e-4 if ndim == 3 else 0.0)
+    prm = pyoracle.make_param(eta_shear=0.05, eta_bulk=0.12, force=fg, nrelax=nrelax)
+    f = f0.copy()
+    rho, u = np.zeros(orc.nsite), np.zeros((orc.nsite, 3))
+    orc.collide_mrt(prm, f, force, rho, u)
+    lat.set_param(eta_shear=0.05, eta_bulk=0.12, force=fg, nrelax=nrelax)
+    lat.lb_memcpy_h2d(f0)
+    lat.field_h2d(lb.FIELD_FORCE, force)
+    lat.hydro_u_zero()
+    lat.lb_collide()
+    m = orc.interior_mask()
+    fd = lat.lb_memcpy_d2h()
+    assert relerr(fd[m], f[m]) < TOL
+    assert relerr(lat.field_d2h(lb.FIELD_RHO)[m], rho[m]) < TOL
+    assert np.max(np.abs(lat.field_d2h(lb.FIELD_U)[m] - u[m])) < TOL
+    # halo sites are untouched by the device collision
+    assert np.array_equal(fd[~m], f0[~m])
+    lat.close()
+
+
+@pytest.mark.parametrize("nvel", [19, 27, 9])
+def test_collide_vs_reference_golden(nvel):
+    import ludwig_b200 as lb
+    from oracle import pyoracle
+    o0 = pyoracle.Oracle(nvel, (2, 2, 1 if nvel == 9 else 2))
+    g, nlocal, f0, force, fg = goldenlib.inputs(nvel, o0.cv(), o0.wv())
+    lat, orc = mk(nvel, nlocal)
+    m = orc.interior_mask()
+    for nrelax, name in ((0, "m10"), (1, "bgk"), (2, "trt")):
+        if "collide_%s_f" % name not in g:
+            continue
+        lat.set_param(force=fg, nrelax=nrelax, **goldenlib.PHYS)
+        lat.lb_memcpy_h2d(f0)
+        lat.field_h2d(lb.FIELD_FORCE, force)
+        lat.lb_collide()
+        assert relerr(lat.lb_memcpy_d2h()[m], g["collide_%s_f" % name]) < TOL
+        assert relerr(lat.field_d2h(lb.FIELD_RHO)[m], g["collide_%s_rho" % name]) < TOL
+        assert np.max(np.abs(lat.field_d2h(lb.FIELD_U)[m] - g["collide_%s_u" % name])) < TOL
+    # halo + propagation of the reference's own collided state: bit-exact
+    fh = g["halo_f"].copy()
+    lat.set_option("fused", 0)
+    lat.lb_memcpy_h2d(fh)
+    lat.lb_halo()
+    assert np.array_equal(lat.lb_memcpy_d2h(), fh)
+    lat.lb_propagation()
+    assert np.array_equal(lat.lb_memcpy_d2h()[m], g["prop_f"])
+    lat.close()
+
+
+@pytest.mark.parametrize("nvel,nlocal", CASES)
+@pytest.mark.parametrize("ndist", [1, 2])
+@pytest.mark.parametrize("vec", [1, 2])
+def test_halo_and_propagation_bit_exact(nvel, nlocal, ndist, vec):
+    if ndist == 2 and nvel == 9:
+        pytest.skip("binary fluid is 3-d")
+    lat, orc = mk(nvel, nlocal, ndist)
+    lat.set_option("fused", 0)
+    lat.set_option("vec", vec)
+    rng = np.random.default_rng(5)
+    f0 = rng.standard_normal((orc.nsite, ndist, nvel))
+    f = f0.copy()
+    orc.halo(f, ndist * nvel)
+    lat.lb_memcpy_h2d(f0)
+    lat.lb_halo()
+    fd = lat.lb_memcpy_d2h()
+    if nvel == 9:
+        # the device keeps ONE plane: its z halos are images of the interior plane
+        f3 = f.reshape(orc.nall + (ndist, nvel))
+        assert np.array_equal(f3[:, :, 0], f3[:, :, 1])
+    assert np.array_equal(fd, f)
+    fp = np.zeros_like(f)
+    orc.propagate(f, fp)
+    lat.lb_propagation()
+    m = orc.interior_mask()
+    assert np.array_equal(lat.lb_memcpy_d2h()[m], fp[m])
+    lat.close()
+
+
+@pytest.mark.parametrize("nvel,nlocal", CASES[:3])
+def test_halo_reduced(nvel, nlocal):
+    """Reduced scheme: every population that propagates INTO the domain from a halo
+    site must equal the periodic image (the check of tests/unit/test_model.c:117-207);
+    then one propagation must equal the full-scheme result bit for bit."""
+    import ludwig_b200 as lb
+    lat, orc = mk(nvel, nlocal)
+    lat.set_option("fused", 0)
+    rng = np.random.default_rng(7)
+    f0 = rng.standard_normal((orc.nsite, 1, nvel))
+    f = f0.copy()
+    orc.halo(f, nvel)
+    fp = np.zeros_like(f)
+    orc.propagate(f, fp)
+    lat.lb_memcpy_h2d(f0)
+    lat.lb_halo_swap(lb.HALO_REDUCED)
+    lat.lb_propagation()
+    m = orc.interior_mask()
+    assert np.array_equal(lat.lb_memcpy_d2h()[m], fp[m])
+    lat.close()
+
+
+def test_prop_source_destination():
+    """tests/unit/test_prop.c:165-262: f = global site id; after halo + propagation a
+    site must hold the id of r - c_p with periodic wrap. ndist 1 and 2."""
+    for ndist in (1, 2):
+        nvel, nlocal = 19, (8, 8, 8)
+        lat, orc = mk(nvel, nlocal, ndist)
+        ids = lbinit.global_ids(nlocal).astype(np.float64).reshape(-1)
+        f0 = np.repeat(ids[:, None, None], ndist * nvel, axis=1).reshape(orc.nsite, ndist, nvel)
+        f0 = np.ascontiguousarray(f0)
+        lat.lb_memcpy_h2d(f0)
+        lat.lb_halo()
+        lat.lb_propagation()
+        f = lat.lb_memcpy_d2h().reshape(orc.nall + (ndist, nvel))
+        cv = orc.cv()
+        n = nlocal
+        ii, jj, kk = np.meshgrid(np.arange(n[0]), np.arange(n[1]), np.arange(n[2]), indexing="ij")
+        for p in range(nvel):
+            src = (((ii - cv[p, 0]) % n[0]) * n[1] + ((jj - cv[p, 1]) % n[1])) * n[2] + ((kk - cv[p, 2]) % n[2])
+            for nd in range(ndist):
+                assert np.array_equal(f[1:-1, 1:-1, 1:-1, nd, p], src.astype(np.float64))
+        lat.close()
+
+
+@pytest.mark.parametrize("nvel,nlocal", CASES)
+@pytest.mark.parametrize("vec", [1, 2])
+def test_time_loop_fused_equals_unfused_and_oracle(nvel, nlocal, vec):
+    from oracle import pyoracle
+    nsteps = 6
+    lat, orc = mk(nvel, nlocal)
+    f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal, ndim=orc.ndim)
+    prm = pyoracle.make_param(eta_shear=0.1, eta_bulk=0.1)
+    f, fp = f0.copy(), np.zeros_like(f0)
+    n = orc.nsite
+    rho, u, frc = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
+    orc.step(prm, nsteps, f, fp, rho, u, frc)
+    m = orc.interior_mask()
+    res = {}
+    for fused in (0, 1):
+        lat.set_option("fused", fused)
+        lat.set_option("vec", vec)
+        lat.set_param(eta_shear=0.1, eta_bulk=0.1)
+        lat.lb_memcpy_h2d(f0)
+        lat.step(nsteps)
+        res[fused] = lat.lb_memcpy_d2h()
+        assert relerr(res[fused][m], f[m]) < TOL
+        import ludwig_b200 as lb
+        assert relerr(lat.field_d2h(lb.FIELD_RHO)[m], rho[m]) < TOL
+        assert np.max(np.abs(lat.field_d2h(lb.FIELD_U)[m] - u[m])) < TOL
+        st = lat.stats()
+        assert abs(st[0] - f0[m][:, 0].sum()) < 1e-9 * n     # mass to round-off
+    assert np.array_equal(res[0][m], res[1][m])              # fusion changes nothing
+    lat.close()
+
+
+@pytest.mark.parametrize("nvel", [19, 27, 9])
+def test_ten_steps_vs_reference_golden(nvel):
+    from oracle import pyoracle
+    import ludwig_b200 as lb
+    o0 = pyoracle.Oracle(nvel, (2, 2, 1 if nvel == 9 else 2))
+    g, nlocal, f0, force, fg = goldenlib.inputs(nvel, o0.cv(), o0.wv())
+    lat, orc = mk(nvel, nlocal)
+    m = orc.interior_mask()
+    lat.set_param(eta_shear=0.1, eta_bulk=0.1)
+    lat.lb_memcpy_h2d(f0)
+    lat.step(10)
+    assert relerr(lat.lb_memcpy_d2h()[m], g["step10_f"]) < TOL
+    assert relerr(lat.field_d2h(lb.FIELD_RHO)[m], g["step10_rho"]) < TOL
+    assert np.max(np.abs(lat.field_d2h(lb.FIELD_U)[m] - g["step10_u"])) < TOL
+    lat.close()
+
+
+def test_stats_vs_oracle():
+    for nvel, nlocal, ndist in ((19, (9, 8, 7), 1), (19, (6, 6, 6), 2), (9, (10, 9, 1), 1)):
+        lat, orc = mk(nvel, nlocal, ndist)
+        f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal, ndist=ndist, ndim=orc.ndim)
+        lat.lb_memcpy_h2d(f0)
+        st = lat.stats()
+        ref = orc.stats(f0)
+        assert np.allclose(st[[0, 1, 7]], ref[[0, 1, 7]], rtol=1e-13, atol=1e-12)
+        assert st[2] == ref[2] and st[3] == ref[3]
+        assert np.allclose(st[4:7], ref[4:7], rtol=0, atol=1e-12)
+        lat.close()
+
+
+def test_binary_stages_and_loop():
+    import ludwig_b200 as lb
+    from oracle import pyoracle
+    nvel, nlocal = 19, (10, 8, 6)
+    lat, orc = mk(nvel, nlocal, 2)
+    B = goldenlib.BIN
+    f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal, ndist=2)
+    force = lbinit.make_force(nlocal)
+    prm = pyoracle.make_param(eta_shear=B["eta"], eta_bulk=B["eta"], mobility=B["mobility"],
+                              a=B["a"], b=B["b"], kappa=B["kappa"])
+    kw = dict(eta_shear=B["eta"], eta_bulk=B["eta"], mobility=B["mobility"],
+              a=B["a"], b=B["b"], kappa=B["kappa"])
+    n = orc.nsite
+    m = orc.interior_mask()
+    phi, grad, delsq = np.zeros(n), np.zeros((n, 3)), np.zeros(n)
+    orc.phi_from_g(f0, phi)
+    orc.halo(phi, 1)
+    orc.grad_7pt(phi, grad, delsq)
+    lat.set_param(**kw)
+    lat.lb_memcpy_h2d(f0)
+    lat.field_h2d(lb.FIELD_FORCE, force)
+    lat.phi_lb_to_field()
+    lat.field_halo()
+    assert np.array_equal(lat.field_d2h(lb.FIELD_PHI), phi)            # bit-exact
+    lat.field_grad_compute()
+    assert np.array_equal(lat.field_d2h(lb.FIELD_GRAD)[m], grad[m])    # bit-exact
+    assert np.array_equal(lat.field_d2h(lb.FIELD_DELSQ)[m], delsq[m])
+    f, u = f0.copy(), np.zeros((n, 3))
+    orc.collide_binary(prm, f, force, u, phi, grad, delsq)
+    lat.lb_collide()
+    fd = lat.lb_memcpy_d2h()
+    assert relerr(fd[m][:, 0], f[m][:, 0]) < TOL
+    assert relerr(fd[m][:, 1], f[m][:, 1]) < TOL
+    assert np.max(np.abs(lat.field_d2h(lb.FIELD_U)[m] - u[m])) < TOL
+    # the time loop, fused and unfused
+    nsteps = 6
+    f, fp = f0.copy(), np.zeros_like(f0)
+    rho, frc = np.zeros(n), np.zeros((n, 3))
+    orc.step(prm, nsteps, f, fp, rho, u, frc, phi, grad, delsq)
+    res = {}
+    for fused in (0, 1):
+        lat.set_option("fused", fused)
+        lat.lb_memcpy_h2d(f0)
+        lat.step(nsteps)
+        res[fused] = lat.lb_memcpy_d2h()
+        assert relerr(res[fused][m], f[m]) < TOL
+    assert np.array_equal(res[0][m], res[1][m])
+    lat.close()
+
+
+def test_binary_vs_reference_golden():
+    import ludwig_b200 as lb
+    from oracle import pyoracle
+    nvel = 19
+    o0 = pyoracle.Oracle(nvel, (2, 2, 2))
+    g, nlocal, f0, force, fg = goldenlib.inputs(nvel, o0.cv(), o0.wv(), ndist=2)
+    B = goldenlib.BIN
+    lat, orc = mk(nvel, nlocal, 2)
+    m = orc.interior_mask()
+    lat.set_param(eta_shear=B["eta"], eta_bulk=B["eta"], mobility=B["mobility"],
+                  a=B["a"], b=B["b"], kappa=B["kappa"])
+    lat.lb_memcpy_h2d(f0)
+    lat.field_h2d(lb.FIELD_FORCE, force)
+    lat.phi_lb_to_field()
+    lat.field_halo()
+    assert np.array_equal(lat.field_d2h(lb.FIELD_PHI), g["bin_phi"])
+    lat.field_grad_compute()
+    assert np.array_equal(lat.field_d2h(lb.FIELD_GRAD)[m], g["bin_grad"])
+    assert np.array_equal(lat.field_d2h(lb.FIELD_DELSQ)[m], g["bin_delsq"])
+    lat.lb_collide()
+    assert relerr(lat.lb_memcpy_d2h()[m], g["bin_collide_f"]) < TOL
+    assert np.max(np.abs(lat.field_d2h(lb.FIELD_U)[m] - g["bin_collide_u"])) < TOL
+    lat.lb_memcpy_h2d(f0)
+    lat.hydro_f_zero()
+    lat.step(10)
+    assert relerr(lat.lb_memcpy_d2h()[m], g["bin_step10_f"]) < TOL
+    lat.close()
+
+
+def test_full_size_properties():
+    """BASELINE configs at full size (256^3 D3Q19): size-independent properties --
+    mass and momentum conserved to round-off over fused steps, and a uniform state at
+    rest is a fixed point."""
+    nvel, nlocal = 19, (256, 256, 256)
+    import ludwig_b200 as lb
+    from oracle import pyoracle
+    lat = lb.Lattice(nvel, nlocal)
+    o0 = pyoracle.Oracle(nvel, (2, 2, 2))
+    nsite = lat.nsite
+    ids = np.arange(nsite, dtype=np.uint64)
+    rho = 1.0 + 0.01 * lbinit.uniform(ids, 1)
+    u = 0.01 * np.stack([lbinit.uniform(ids, 2 + a) for a in range(3)], axis=1)
+    f0 = lbinit.equilibrium(o0.cv(), o0.wv(), rho, u).reshape(nsite, 1, nvel)
+    lat.set_param(eta_shear=0.1, eta_bulk=0.1)
+    lat.lb_memcpy_h2d(f0)
+    lat.lb_halo()
+    s0 = lat.stats()
+    lat.step(20)
+    s1 = lat.stats()
+    nint = 256.0 ** 3
+    assert abs(s1[0] - s0[0]) / nint < 1e-14
+    assert np.max(np.abs(s1[4:7] - s0[4:7])) / nint < 1e-14
+    lat.close()
