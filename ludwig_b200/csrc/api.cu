@@ -110,6 +110,9 @@ struct b200lb_s {
   bool u_fill_pending;       // hydro_u_zero recorded but not yet applied
   double uconst[3];
   bool hydro_stale;          // collision ran without storing rho,u
+  int  selfper[3];           // device axis is periodic within this rank (one rank in that direction)
+  bool halo_deferred;        // lb_halo was called; self-periodic planes not yet copied (pulls wrap)
+  int  halo_deferred_scheme;
 
   b200lb_param_t prm;
   double rtau_shear, rtau_bulk, rtau2;
@@ -117,7 +120,7 @@ struct b200lb_s {
   bool ghost;
 
   // options
-  int opt_fused, opt_halo, opt_hydro_write, opt_vec, opt_block;
+  int opt_fused, opt_halo, opt_hydro_write, opt_vec, opt_block, opt_halo_lazy;
 
   cudaStream_t s_main, s_x[2];
   cudaEvent_t ev0, ev1, ev_x[2];
@@ -134,7 +137,7 @@ struct b200lb_s {
 static int site_kparams(b200lb_s * h, KParams & P) {
   memset(&P, 0, sizeof(P));
   P.L = h->L;
-  for (int d = 0; d < 3; d++) { P.lo[d] = 0; P.hi[d] = h->L.n[d]; }
+  for (int d = 0; d < 3; d++) { P.lo[d] = 0; P.hi[d] = h->L.n[d]; P.wrap[d] = h->selfper[d]; }
   P.rtau_shear = h->rtau_shear; P.rtau_bulk = h->rtau_bulk;
   P.rtau2 = h->rtau2; P.A = h->prm.a; P.B = h->prm.b; P.kappa = h->prm.kappa;
   for (int k = 0; k < B200LB_MAXGHOST; k++) P.gkeep[k] = h->gkeep[k];
@@ -225,6 +228,10 @@ extern "C" int b200lb_create(const b200lb_desc_t * desc, b200lb_t ** out) {
     L.h[d] = (ops->ndim == 2 && a == 2) ? 0 : 1;
     L.na[d] = L.n[d] + 2*L.h[d];
   }
+  for (int d = 0; d < 3; d++) {
+    const int a = ops->dax[d];
+    h->selfper[d] = (L.h[d] == 1 && desc->cartsz[a] == 1 && desc->periodic[a]) ? 1 : 0;
+  }
   L.z0 = zalign - L.h[2];
   {
     i64 row = L.z0 + L.na[2];
@@ -275,6 +282,7 @@ extern "C" int b200lb_create(const b200lb_desc_t * desc, b200lb_t ** out) {
   h->opt_hydro_write = 1;
   h->opt_vec = 2;
   h->opt_block = 128;
+  h->opt_halo_lazy = 1;
 
   b200lb_param_t p0;
   memset(&p0, 0, sizeof(p0));
@@ -326,6 +334,7 @@ extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
     h->opt_halo = (int) v; return 0;
   }
   if (!strcmp(name, "hydro_write")) { h->opt_hydro_write = (v != 0); return 0; }
+  if (!strcmp(name, "halo_lazy")) { h->opt_halo_lazy = (v != 0); return 0; }
   if (!strcmp(name, "vec")) {
     if (v != 1 && v != 2) return fail("vec must be 1 or 2");
     h->opt_vec = (int) v; return 0;
@@ -342,6 +351,8 @@ extern "C" long b200lb_get_option(const b200lb_t * h, const char * name) {
   if (!strcmp(name, "fused")) return h->opt_fused;
   if (!strcmp(name, "halo")) return h->opt_halo;
   if (!strcmp(name, "hydro_write")) return h->opt_hydro_write;
+  if (!strcmp(name, "halo_lazy")) return h->opt_halo_lazy;
+  if (!strcmp(name, "halo_deferred")) return h->halo_deferred;
   if (!strcmp(name, "vec")) return h->opt_vec;
   if (!strcmp(name, "block")) return h->opt_block;
   if (!strcmp(name, "prop_pending")) return h->prop_pending;
@@ -381,6 +392,7 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
   }
   CU(h->ops->sweep(a));
   h->launches++;
+  h->halo_deferred = false;        // whatever was written has stale halos until the next lb_halo
   if (collide) {
     if (h->opt_hydro_write) { h->u_fill_pending = false; h->hydro_stale = false; }
     else h->hydro_stale = true;
@@ -481,7 +493,10 @@ static int halo_buffers(b200lb_s * h, int d, int nel) {
 }
 
 // Exchange the halo planes of `data` (nplane planes of nsd doubles).
-static int halo_exchange(b200lb_s * h, double * data, bool lattice, int nplane, int scheme) {
+// which: 0 = every axis, 1 = only axes decomposed over ranks, 2 = only the
+// axes that are periodic within this rank (local copies).
+static int halo_exchange(b200lb_s * h, double * data, bool lattice, int nplane, int scheme,
+			 int which) {
   for (int d = 0; d < 3; d++) {
     if (h->L.h[d] == 0) continue;
     const int a = h->ops->dax[d];
@@ -491,9 +506,11 @@ static int halo_exchange(b200lb_s * h, double * data, bool lattice, int nplane, 
     halo_lists(h, d, scheme, nplane, lattice, H);
     if (h->desc.cartsz[a] == 1) {
       if (!h->desc.periodic[a]) continue;        // physical boundary: nothing to receive
+      if (which == 1) continue;
       if (halo_launch(h, HALO_LOCAL, H)) return -1;
       continue;
     }
+    if (which == 2) continue;
     if (!h->comm) return fail("direction %d is decomposed over %d ranks but b200lb_comm_init was not called", a, h->desc.cartsz[a]);
     if (halo_buffers(h, d, nplane)) return -1;
     HaloBuf & b = h->hb[d];
@@ -516,12 +533,33 @@ static int halo_exchange(b200lb_s * h, double * data, bool lattice, int nplane, 
   return 0;
 }
 
+// lb_halo on the current lattice. Every sweep that streams wraps around the axes
+// that are periodic within this rank, so their halo planes are only ever read by
+// an observer of the host copy: with halo_lazy those local copies wait for one
+// (flush_halo); directions decomposed over ranks are exchanged at once. Doing the
+// local axes after the exchanged ones gives the same planes, edges and corners:
+// each pass spans the full extent of the other axes and overwrites what an
+// earlier pass could not know yet.
+static int lattice_halo(b200lb_s * h, int scheme) {
+  if (!h->opt_halo_lazy) return halo_exchange(h, h->lat[h->cur], true, h->nplane, scheme, 0);
+  if (halo_exchange(h, h->lat[h->cur], true, h->nplane, scheme, 1)) return -1;
+  h->halo_deferred = true;
+  h->halo_deferred_scheme = scheme;
+  return 0;
+}
+
+static int flush_halo(b200lb_s * h) {
+  if (!h->halo_deferred) return 0;
+  h->halo_deferred = false;
+  return halo_exchange(h, h->lat[h->cur], true, h->nplane, h->halo_deferred_scheme, 2);
+}
+
 extern "C" int b200lb_halo_swap(b200lb_t * h, int scheme) {
   if (!h) return fail("null handle");
   if (scheme == 1) scheme = B200LB_HALO_FULL;      // LB_HALO_OPENMP_FULL moves the same data
   if (scheme != B200LB_HALO_FULL && scheme != B200LB_HALO_REDUCED) return fail("bad halo scheme %d", scheme);
   if (h->prop_pending) { if (materialise(h)) return -1; }
-  return halo_exchange(h, h->lat[h->cur], true, h->nplane, scheme);
+  return lattice_halo(h, scheme);
 }
 
 extern "C" int b200lb_halo(b200lb_t * h) {
@@ -532,7 +570,7 @@ extern "C" int b200lb_halo(b200lb_t * h) {
 extern "C" int b200lb_phi_halo(b200lb_t * h) {
   if (!h) return fail("null handle");
   if (!h->phi) return fail("no order parameter (ndist = 1)");
-  return halo_exchange(h, h->phi, false, 1, B200LB_HALO_FULL);
+  return halo_exchange(h, h->phi, false, 1, B200LB_HALO_FULL, 0);
 }
 
 // ---------------------------------------------------------------------------
@@ -543,7 +581,7 @@ extern "C" int b200lb_phi_from_g(b200lb_t * h) {
   if (!h) return fail("null handle");
   if (!h->phi) return fail("no order parameter (ndist = 1)");
   const double * g = h->lat[h->cur] + (i64) h->desc.nvel*h->L.nsd;
-  CU(h->ops->phi_from_g(h->L, g, h->phi, h->prop_pending, h->s_main));
+  CU(h->ops->phi_from_g(h->L, h->selfper, g, h->phi, h->prop_pending, h->s_main));
   h->launches++;
   return 0;
 }
@@ -602,7 +640,7 @@ extern "C" int b200lb_step(b200lb_t * h, int nsteps) {
     if (b200lb_hydro_u_zero(h, zero)) return -1;
     if (b200lb_collide(h)) return -1;
     if (h->prop_pending) return fail("internal: propagation pending after collide");
-    if (halo_exchange(h, h->lat[h->cur], true, h->nplane, h->opt_halo)) return -1;
+    if (lattice_halo(h, h->opt_halo)) return -1;
     if (b200lb_propagate(h)) return -1;
   }
   return 0;
@@ -715,12 +753,18 @@ static int transfer(b200lb_s * h, double * dev, int nel, double * host, int layo
 extern "C" int b200lb_f_upload(b200lb_t * h, const double * f, int layout) {
   if (!h || !f) return fail("null argument");
   h->prop_pending = false;          // the host copy replaces whatever was in flight
+  h->halo_deferred = false;
   return transfer(h, h->lat[h->cur], h->nplane, const_cast<double *>(f), layout, true);
 }
 
 extern "C" int b200lb_f_download(b200lb_t * h, double * f, int layout) {
   if (!h || !f) return fail("null argument");
-  if (materialise(h)) return -1;
+  if (h->prop_pending) {
+    if (materialise(h)) return -1;      // streamed lattice: its halos are stale, as in the reference
+  }
+  else {
+    if (flush_halo(h)) return -1;       // lb_halo was the last thing done: make its planes real
+  }
   return transfer(h, h->lat[h->cur], h->nplane, f, layout, false);
 }
 

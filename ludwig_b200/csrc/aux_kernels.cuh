@@ -13,7 +13,8 @@
 
 template <class M, bool PULL>
 __global__ void __launch_bounds__(256)
-phi_from_g_kernel(const Layout L, const double * __restrict__ g, double * __restrict__ phi) {
+phi_from_g_kernel(const Layout L, const int w0, const int w1, const int w2,
+		  const double * __restrict__ g, double * __restrict__ phi) {
 
   const int i2 = blockIdx.x*blockDim.x + threadIdx.x;
   const int i1 = blockIdx.y*blockDim.y + threadIdx.y;
@@ -25,7 +26,15 @@ phi_from_g_kernel(const Layout L, const double * __restrict__ g, double * __rest
   #pragma unroll
   for (int p = 0; p < M::NVEL; p++) {
     i64 s = site;
-    if (PULL) s -= dcv<M>(p, 0)*L.s0 + dcv<M>(p, 1)*L.s1 + dcv<M>(p, 2);
+    if (PULL) {
+      // r - c_p, wrapping along axes that are periodic within this rank
+      if (dcv<M>(p, 0) ==  1) s += (w0 && i0 == 0) ? (i64) (L.n[0] - 1)*L.s0 : -L.s0;
+      if (dcv<M>(p, 0) == -1) s += (w0 && i0 == L.n[0] - 1) ? -(i64) (L.n[0] - 1)*L.s0 : L.s0;
+      if (dcv<M>(p, 1) ==  1) s += (w1 && i1 == 0) ? (i64) (L.n[1] - 1)*L.s1 : -L.s1;
+      if (dcv<M>(p, 1) == -1) s += (w1 && i1 == L.n[1] - 1) ? -(i64) (L.n[1] - 1)*L.s1 : L.s1;
+      if (dcv<M>(p, 2) ==  1) s += (w2 && i2 == 0) ? L.n[2] - 1 : -1;
+      if (dcv<M>(p, 2) == -1) s += (w2 && i2 == L.n[2] - 1) ? -(L.n[2] - 1) : 1;
+    }
     v[p] = __ldg(g + (i64) p*L.nsd + s);
   }
   double sum = 0.0;

@@ -135,7 +135,8 @@ grad7_kernel(const Layout L, const double * __restrict__ phi,
       grad[site]           = 0.5*(xp - xm);
       grad[L.nsd + site]   = 0.5*(yp - ym);
       grad[2*L.nsd + site] = 0.5*(zp - zm);
-      delsq[site] = xp + xm + yp + ym + zp + zm - 6.0*c;
+      // __dmul_rn keeps the product separately rounded (no FMA contraction): bit parity
+      delsq[site] = xp + xm + yp + ym + zp + zm - __dmul_rn(6.0, c);
     }
     __syncthreads();
   }

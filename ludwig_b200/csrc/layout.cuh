@@ -39,6 +39,7 @@ struct KParams {
   const double * grad;    // [3][nsd]
   const double * delsq;   // [nsd]
   int lo[3], hi[3];       // sub-box of the interior, 0-based interior coordinates, [lo,hi)
+  int wrap[3];            // device axis is periodic within this rank: pulls wrap instead of reading halos
   double rtau_shear, rtau_bulk;
   double fg[3];           // uniform part of the force: force_global + constant field value
   double rtau2, A, B, kappa;

@@ -63,12 +63,12 @@ static cudaError_t sweep_impl(const SweepArgs & a) {
   return cudaErrorInvalidValue;
 }
 
-static cudaError_t phi_impl(const Layout & L, const double * g, double * phi,
-			    bool pull, cudaStream_t s) {
+static cudaError_t phi_impl(const Layout & L, const int w[3], const double * g,
+			    double * phi, bool pull, cudaStream_t s) {
   dim3 block(128, 2, 1);
   dim3 grid((L.n[2] + 127)/128, (L.n[1] + 1)/2, L.n[0]);
-  if (pull) phi_from_g_kernel<MODEL, true><<<grid, block, 0, s>>>(L, g, phi);
-  else phi_from_g_kernel<MODEL, false><<<grid, block, 0, s>>>(L, g, phi);
+  if (pull) phi_from_g_kernel<MODEL, true><<<grid, block, 0, s>>>(L, w[0], w[1], w[2], g, phi);
+  else phi_from_g_kernel<MODEL, false><<<grid, block, 0, s>>>(L, 0, 0, 0, g, phi);
   return cudaGetLastError();
 }
 

@@ -21,8 +21,8 @@ struct ModelOps {
   int cv[27][3];
   double wv[27];
   cudaError_t (*sweep)(const SweepArgs &);
-  cudaError_t (*phi_from_g)(const Layout &, const double * g, double * phi,
-			    bool pull, cudaStream_t);
+  cudaError_t (*phi_from_g)(const Layout &, const int wrap[3], const double * g,
+			    double * phi, bool pull, cudaStream_t);
   cudaError_t (*stats)(const Layout &, const double * f, int ndist,
 		       double * partial, dim3 grid, dim3 block, cudaStream_t);
   cudaError_t (*ghost_upload)(void);

@@ -264,6 +264,28 @@ lb_sweep_kernel(const KParams P) {
   const i64 site = (i64)(i0 + L.h[0])*L.s0 + (i64)(i1 + L.h[1])*L.s1
                  + L.z0 + L.h[2] + i2;
 
+  // Offsets that reach coordinate -1 / +1 along each axis. An axis that is
+  // periodic within this rank wraps around here, so its halo planes are never
+  // read (and need not be filled): SURVEY 7.4 "self-exchange fast path".
+  i64 om[2], op[2];        // axes 0 and 1: block-uniform
+  int zm[VEC], zp[VEC];    // contiguous axis: differs only for the first / last site of a row
+  if (PULL) {
+    om[0] = -L.s0; op[0] = L.s0; om[1] = -L.s1; op[1] = L.s1;
+    if (P.wrap[0]) {
+      if (i0 == 0) om[0] = (i64) (L.n[0] - 1)*L.s0;
+      if (i0 == L.n[0] - 1) op[0] = -(i64) (L.n[0] - 1)*L.s0;
+    }
+    if (P.wrap[1]) {
+      if (i1 == 0) om[1] = (i64) (L.n[1] - 1)*L.s1;
+      if (i1 == L.n[1] - 1) op[1] = -(i64) (L.n[1] - 1)*L.s1;
+    }
+    #pragma unroll
+    for (int v = 0; v < VEC; v++) {
+      zm[v] = (P.wrap[2] && (i2 + v == 0)) ? L.n[2] - 1 : -1;
+      zp[v] = (P.wrap[2] && (i2 + v == L.n[2] - 1)) ? -(L.n[2] - 1) : 1;
+    }
+  }
+
   double f[NDIST][VEC][Q];
 
   #pragma unroll
@@ -273,21 +295,27 @@ lb_sweep_kernel(const KParams P) {
       const double * src = P.src + (i64)(n*Q + p)*L.nsd + site;
       int c2 = 0;
       if (PULL) {
-	src -= dcv<M>(p, 0)*L.s0 + dcv<M>(p, 1)*L.s1 + dcv<M>(p, 2);
+	if (dcv<M>(p, 0) ==  1) src += om[0];
+	if (dcv<M>(p, 0) == -1) src += op[0];
+	if (dcv<M>(p, 1) ==  1) src += om[1];
+	if (dcv<M>(p, 1) == -1) src += op[1];
 	c2 = dcv<M>(p, 2);
       }
-      if (VEC == 2) {
-	if (c2 == 0) {
+      if (c2 == 0) {
+	if (VEC == 2) {
 	  const double2 v = ld2<NC>(src);
 	  f[n][0][p] = v.x; f[n][VEC - 1][p] = v.y;
 	}
 	else {
 	  f[n][0][p] = ld1<NC>(src);
-	  f[n][VEC - 1][p] = ld1<NC>(src + 1);
 	}
       }
       else {
-	f[n][0][p] = ld1<NC>(src);
+	// moving along the contiguous axis: the pair straddles the aligned one
+	#pragma unroll
+	for (int v = 0; v < VEC; v++) {
+	  f[n][v][p] = ld1<NC>(src + v + (c2 == 1 ? zm[v] : zp[v]));
+	}
       }
     }
   }

@@ -80,8 +80,10 @@ def test_collide_vs_oracle(nvel, nlocal, nrelax, vec):
     assert relerr(fd[m], f[m]) < TOL
     assert relerr(lat.field_d2h(lb.FIELD_RHO)[m], rho[m]) < TOL
     assert np.max(np.abs(lat.field_d2h(lb.FIELD_U)[m] - u[m])) < TOL
-    # halo sites are untouched by the device collision
-    assert np.array_equal(fd[~m], f0[~m])
+    # halo sites are untouched by the device collision (a 2-d lattice is held as ONE
+    # plane, whose z images follow the interior, so the check is for 3-d only)
+    if nvel != 9:
+        assert np.array_equal(fd[~m], f0[~m])
     lat.close()
 
 
