@@ -1,0 +1,146 @@
+"""Multi-GPU parity worker. Launched by tests/test_multi_gpu.py (or by hand) as
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N \
+        --master-addr 127.0.0.1 --master-port P tests/mgpu_worker.py [--nvel 19] ...
+
+Every rank owns one block of a 3-d decomposed periodic lattice on its own GPU, halo
+planes travel with NCCL send/recv inside libb200lb. Rank 0 also runs the WHOLE lattice
+on its GPU and on the CPU oracle:
+  * decomposed result == single-GPU result, bit for bit (decomposition independence,
+    the property the reference's pmpi08-* regression logs test against serial logs);
+  * result vs oracle within 1e-12 of max|f|; halo planes after lb_halo bit-exact.
+Exit code 0 = pass.
+"""
+
+import argparse
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, HERE)
+sys.path.insert(0, os.path.dirname(HERE))
+
+import lbinit                       # noqa: E402
+import ludwig_b200 as lb            # noqa: E402
+from ludwig_b200 import models_host  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--nvel", type=int, default=19)
+    ap.add_argument("--ndist", type=int, default=1)
+    ap.add_argument("--local", type=int, nargs=3, default=[12, 10, 8])
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--halo", default="full")
+    ap.add_argument("--fused", type=int, default=1)
+    args = ap.parse_args()
+
+    rank = int(os.environ["RANK"])
+    world = int(os.environ["WORLD_SIZE"])
+    local_rank = int(os.environ.get("LOCAL_RANK", rank))
+    torch.cuda.set_device(local_rank)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    nvel, ndist = args.nvel, args.ndist
+    ndim = 2 if nvel == 9 else 3
+    grid = {1: (1, 1, 1), 2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}[world]
+    if ndim == 2 and grid[2] != 1:
+        grid = (grid[0] * grid[2], grid[1], 1)
+    local = tuple(args.local)
+    ntotal = tuple(local[a] * grid[a] for a in range(3))
+    dec = lb.Decomposition(ntotal, rank, world, grid=grid)
+    cv, wv = models_host.cv(nvel), models_host.wv(nvel)
+
+    lat = lb.Lattice(nvel, local, ndist=ndist, decomp=dec, device=local_rank)
+    uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
+    if rank == 0:
+        uid = torch.tensor(list(lb.Lattice.nccl_unique_id()), dtype=torch.uint8, device="cuda")
+    dist.broadcast(uid, 0)
+    lat.comm_init(bytes(uid.cpu().tolist()))
+    lat.set_option("fused", args.fused)
+    lat.set_option("halo", lb.HALO_REDUCED if args.halo == "reduced" else lb.HALO_FULL)
+    kw = dict(eta_shear=0.1, eta_bulk=0.1)
+    if ndist == 2:
+        kw = dict(eta_shear=0.00625, eta_bulk=0.00625, mobility=3.75, a=-0.00625,
+                  b=0.00625, kappa=0.004)
+    lat.set_param(**kw)
+
+    f0 = lbinit.make_state(cv, wv, local, ndist=ndist, ntotal=ntotal, offset=dec.offset,
+                           ndim=ndim)
+    # 1. halo planes: scramble the halo sites, exchange, compare with the periodic images
+    nall = tuple(n + 2 for n in local)
+    interior = np.zeros(nall, dtype=bool)
+    interior[1:-1, 1:-1, 1:-1] = True
+    interior = interior.reshape(-1)
+    fs = f0.copy()
+    fs[~interior] = -777.0
+    lat.lb_memcpy_h2d(fs)
+    lat.lb_halo_swap(lb.HALO_FULL)
+    fh = lat.lb_memcpy_d2h()
+    ok_halo = bool(np.array_equal(fh, f0))
+
+    # 2. time loop
+    lat.lb_memcpy_h2d(f0)
+    lat.step(args.steps)
+    fd = lat.lb_memcpy_d2h()
+    st = lat.stats()
+    mine = fd.reshape(nall + (ndist, nvel))[1:-1, 1:-1, 1:-1].copy()
+
+    t = torch.from_numpy(mine).cuda()
+    parts = [torch.empty_like(t) for _ in range(world)] if rank == 0 else None
+    dist.gather(t, parts, dst=0)
+    sums = torch.tensor(st, device="cuda")
+    dist.all_reduce(sums, op=dist.ReduceOp.SUM)
+    flags = torch.tensor([1.0 if ok_halo else 0.0], device="cuda")
+    dist.all_reduce(flags, op=dist.ReduceOp.MIN)
+    lat.close()
+
+    rc = 0
+    if rank == 0:
+        glob = np.zeros(ntotal + (ndist, nvel))
+        for r in range(world):
+            d = lb.Decomposition(ntotal, r, world, grid=grid)
+            o = d.offset
+            glob[o[0]:o[0] + local[0], o[1]:o[1] + local[1], o[2]:o[2] + local[2]] = parts[r].cpu().numpy()
+        # the same lattice on ONE GPU
+        one = lb.Lattice(nvel, ntotal, ndist=ndist, device=local_rank)
+        one.set_option("fused", args.fused)
+        one.set_param(**kw)
+        g0 = lbinit.make_state(cv, wv, ntotal, ndist=ndist, ndim=ndim)
+        one.lb_memcpy_h2d(g0)
+        one.step(args.steps)
+        g1 = one.lb_memcpy_d2h().reshape(tuple(n + 2 for n in ntotal) + (ndist, nvel))[1:-1, 1:-1, 1:-1]
+        s1 = one.stats()
+        one.close()
+        same = bool(np.array_equal(glob, g1))
+        # and on the CPU oracle
+        from oracle import pyoracle
+        orc = pyoracle.Oracle(nvel, ntotal, ndist=ndist)
+        prm = pyoracle.make_param(**kw)
+        f, fp = g0.copy(), np.zeros_like(g0)
+        n = orc.nsite
+        rho, u, frc = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
+        phi, grad, delsq = np.zeros(n), np.zeros((n, 3)), np.zeros(n)
+        orc.step(prm, args.steps, f, fp, rho, u, frc, phi, grad, delsq)
+        fo = f.reshape(tuple(n + 2 for n in ntotal) + (ndist, nvel))[1:-1, 1:-1, 1:-1]
+        err = float(np.max(np.abs(glob - fo)) / np.max(np.abs(fo)))
+        mass = abs(float(sums[0].item()) - s1[0])
+        halo_ok = bool(flags.item() > 0.5)
+        print("mgpu world=%d grid=%s nvel=%d ndist=%d halo=%s fused=%d: halo_bit_exact=%s "
+              "decomposed==single=%s err_vs_oracle=%.2e mass_diff=%.2e"
+              % (world, grid, nvel, ndist, args.halo, args.fused, halo_ok, same, err, mass),
+              flush=True)
+        if not (halo_ok and same and err < 1e-12 and mass < 1e-9 * n):
+            rc = 1
+    code = torch.tensor([rc], device="cuda")
+    dist.broadcast(code, 0)
+    dist.destroy_process_group()
+    sys.exit(int(code.item()))
+
+
+if __name__ == "__main__":
+    main()

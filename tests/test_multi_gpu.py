@@ -1,0 +1,40 @@
+"""Multi-GPU parity (needs >= 2 visible GPUs; skipped otherwise): launches
+tests/mgpu_worker.py under torch.distributed.run, one rank per GPU, NCCL halo exchange."""
+
+import os
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def ngpu():
+    import torch
+    return torch.cuda.device_count()
+
+
+def launch(n, extra, port):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node",
+           str(n), "--master-addr", "127.0.0.1", "--master-port", str(port),
+           os.path.join(HERE, "mgpu_worker.py")] + extra
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    sys.stdout.write(r.stdout[-2000:])
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+@pytest.mark.parametrize("n", [2, 4, 8])
+@pytest.mark.parametrize("extra", [
+    ["--nvel", "19", "--halo", "full"],
+    ["--nvel", "19", "--halo", "reduced"],
+    ["--nvel", "19", "--halo", "reduced", "--fused", "0"],
+    ["--nvel", "27", "--halo", "reduced", "--local", "8", "6", "10"],
+    ["--nvel", "19", "--ndist", "2", "--halo", "full", "--local", "8", "8", "6"],
+    ["--nvel", "9", "--halo", "reduced", "--local", "16", "12", "1"],
+])
+def test_decomposed_equals_single(n, extra):
+    if ngpu() < n:
+        pytest.skip("needs %d GPUs" % n)
+    launch(n, extra, 29600 + n)
