@@ -120,10 +120,15 @@ struct b200lb_s {
   bool ghost;
 
   // options
-  int opt_fused, opt_halo, opt_hydro_write, opt_vec, opt_block, opt_halo_lazy;
+  int opt_fused, opt_halo, opt_hydro_write, opt_vec, opt_block, opt_halo_lazy, opt_overlap, opt_direct;
 
   cudaStream_t s_main, s_x[2];
+  cudaStream_t s_comm;       // halo exchange of decomposed directions (overlaps the interior sweep)
   cudaEvent_t ev0, ev1, ev_x[2];
+  cudaEvent_t ev_bnd;        // boundary slabs of the current sweep written
+  cudaEvent_t ev_halo;       // exchange on s_comm finished
+  bool bnd_valid;            // ev_bnd belongs to the sweep that produced lat[cur]
+  bool halo_inflight;        // s_main must wait for ev_halo before touching the lattice
   double * stage[2];
   double * partial; i64 npartial;
   double * stats_dev; double * stats_host;
@@ -132,6 +137,16 @@ struct b200lb_s {
   ncclComm_t comm;
   HaloBuf hb[3];             // per device axis (multi-rank directions only)
   int hb_nel;
+
+  // direct reduced exchange (one message per neighbour direction)
+  int direct_state;          // 0 = not set up, 1 = ready, -1 = unavailable (fall back to x,y,z phases)
+  int npack, nunpack;
+  HaloMsg * msg_pack, * msg_unpack;        // device tables
+  int pack_peer[B200LB_MAXMSG], unpack_peer[B200LB_MAXMSG];
+  i64 pack_off[B200LB_MAXMSG], pack_cnt[B200LB_MAXMSG];
+  i64 unpack_off[B200LB_MAXMSG], unpack_cnt[B200LB_MAXMSG];
+  i64 pack_max, unpack_max;
+  double * dsend, * drecv;
 };
 
 static int site_kparams(b200lb_s * h, KParams & P) {
@@ -242,6 +257,15 @@ extern "C" int b200lb_create(const b200lb_desc_t * desc, b200lb_t ** out) {
   }
 
   CU(cudaStreamCreateWithFlags(&h->s_main, cudaStreamNonBlocking));
+  {
+    // highest priority: the small pack / NCCL / unpack kernels must get SMs while
+    // the interior sweep (tens of thousands of blocks) is running on s_main
+    int plo = 0, phi_ = 0;
+    CU(cudaDeviceGetStreamPriorityRange(&plo, &phi_));
+    CU(cudaStreamCreateWithPriority(&h->s_comm, cudaStreamNonBlocking, phi_));
+  }
+  CU(cudaEventCreateWithFlags(&h->ev_bnd, cudaEventDisableTiming));
+  CU(cudaEventCreateWithFlags(&h->ev_halo, cudaEventDisableTiming));
   for (int i = 0; i < 2; i++) {
     CU(cudaStreamCreateWithFlags(&h->s_x[i], cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&h->ev_x[i], cudaEventDisableTiming));
@@ -283,6 +307,8 @@ extern "C" int b200lb_create(const b200lb_desc_t * desc, b200lb_t ** out) {
   h->opt_vec = 2;
   h->opt_block = 128;
   h->opt_halo_lazy = 1;
+  h->opt_overlap = 1;
+  h->opt_direct = 1;
 
   b200lb_param_t p0;
   memset(&p0, 0, sizeof(p0));
@@ -299,6 +325,7 @@ extern "C" int b200lb_destroy(b200lb_t * h) {
   if (!h) return 0;
   cudaDeviceSynchronize();
   if (h->comm) g_nccl.CommDestroy(h->comm);
+  cudaFree(h->msg_pack); cudaFree(h->msg_unpack); cudaFree(h->dsend); cudaFree(h->drecv);
   for (int d = 0; d < 3; d++) {
     cudaFree(h->hb[d].to_lo); cudaFree(h->hb[d].to_hi);
     cudaFree(h->hb[d].from_lo); cudaFree(h->hb[d].from_hi);
@@ -314,6 +341,8 @@ extern "C" int b200lb_destroy(b200lb_t * h) {
   cudaFree(h->partial); cudaFree(h->stats_dev); cudaFreeHost(h->stats_host);
   cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
   cudaStreamDestroy(h->s_main);
+  cudaStreamDestroy(h->s_comm);
+  cudaEventDestroy(h->ev_bnd); cudaEventDestroy(h->ev_halo);
   free(h);
   return 0;
 }
@@ -335,6 +364,8 @@ extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
   }
   if (!strcmp(name, "hydro_write")) { h->opt_hydro_write = (v != 0); return 0; }
   if (!strcmp(name, "halo_lazy")) { h->opt_halo_lazy = (v != 0); return 0; }
+  if (!strcmp(name, "overlap")) { h->opt_overlap = (v != 0); return 0; }
+  if (!strcmp(name, "direct")) { h->opt_direct = (v != 0); return 0; }
   if (!strcmp(name, "vec")) {
     if (v != 1 && v != 2) return fail("vec must be 1 or 2");
     h->opt_vec = (int) v; return 0;
@@ -352,6 +383,9 @@ extern "C" long b200lb_get_option(const b200lb_t * h, const char * name) {
   if (!strcmp(name, "halo")) return h->opt_halo;
   if (!strcmp(name, "hydro_write")) return h->opt_hydro_write;
   if (!strcmp(name, "halo_lazy")) return h->opt_halo_lazy;
+  if (!strcmp(name, "overlap")) return h->opt_overlap;
+  if (!strcmp(name, "direct")) return h->opt_direct;
+  if (!strcmp(name, "direct_state")) return h->direct_state;
   if (!strcmp(name, "halo_deferred")) return h->halo_deferred;
   if (!strcmp(name, "vec")) return h->opt_vec;
   if (!strcmp(name, "block")) return h->opt_block;
@@ -373,8 +407,53 @@ extern "C" int b200lb_set_param(b200lb_t * h, const b200lb_param_t * prm) {
 // sweeps
 // ---------------------------------------------------------------------------
 
+// s_main waits for an exchange still running on s_comm
+static int join_comm(b200lb_s * h) {
+  if (h->halo_inflight) {
+    CU(cudaStreamWaitEvent(h->s_main, h->ev_halo, 0));
+    h->halo_inflight = false;
+  }
+  return 0;
+}
+
+// Sub-boxes for the comm/compute overlap: along every direction decomposed over
+// ranks the two outermost slabs (one site thick; sixteen -- one 128-byte line -- along
+// the contiguous axis so that slab and interior rows stay line-aligned and coalesced)
+// are swept first, then the interior.
+// The slabs are disjoint, so the in-place collision touches each site once.
+// Returns the number of boxes; the LAST one is the interior. 1 = no split.
+static int split_boxes(const b200lb_s * h, int lo[7][3], int hi[7][3]) {
+  const Layout & L = h->L;
+  int ilo[3] = {0, 0, 0}, ihi[3] = {L.n[0], L.n[1], L.n[2]};
+  int nb = 0;
+  bool any = false;
+  for (int d = 0; d < 3; d++) {
+    const int a = h->ops->dax[d];
+    if (L.h[d] == 0 || h->desc.cartsz[a] == 1) continue;
+    const int t = (d == 2) ? ((L.n[2] >= 64) ? 16 : 2) : 1;
+    if (L.n[d] < 3*t + 1 || (d == 2 && (L.n[2] & 1))) return 1;
+    any = true;
+  }
+  if (!any || !h->comm || !h->opt_overlap) return 1;
+  for (int d = 0; d < 3; d++) {
+    const int a = h->ops->dax[d];
+    if (L.h[d] == 0 || h->desc.cartsz[a] == 1) continue;
+    const int t = (d == 2) ? ((L.n[2] >= 64) ? 16 : 2) : 1;
+    for (int side = 0; side < 2; side++) {
+      for (int e = 0; e < 3; e++) { lo[nb][e] = ilo[e]; hi[nb][e] = ihi[e]; }
+      if (side == 0) { lo[nb][d] = 0; hi[nb][d] = t; }
+      else { lo[nb][d] = L.n[d] - t; hi[nb][d] = L.n[d]; }
+      nb++;
+    }
+    ilo[d] = t; ihi[d] = L.n[d] - t;
+  }
+  for (int e = 0; e < 3; e++) { lo[nb][e] = ilo[e]; hi[nb][e] = ihi[e]; }
+  return nb + 1;
+}
+
 static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
 		     double * dst) {
+  if (join_comm(h)) return -1;
   SweepArgs a;
   site_kparams(h, a.P);
   a.P.src = src; a.P.dst = dst;
@@ -390,8 +469,21 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
     if (h->opt_hydro_write) { a.P.rho = h->rho; a.P.u = h->u; }
     a.P.phi = h->phi; a.P.grad = h->grad; a.P.delsq = h->delsq;
   }
-  CU(h->ops->sweep(a));
-  h->launches++;
+  int lo[7][3], hi[7][3];
+  const int nbox = split_boxes(h, lo, hi);
+  h->bnd_valid = false;
+  for (int b = 0; b < nbox; b++) {
+    if (nbox > 1) {
+      for (int e = 0; e < 3; e++) { a.P.lo[e] = lo[b][e]; a.P.hi[e] = hi[b][e]; }
+      if (b == nbox - 1) {
+	// everything a neighbour needs is written: the exchange may start now
+	CU(cudaEventRecord(h->ev_bnd, h->s_main));
+	h->bnd_valid = true;
+      }
+    }
+    CU(h->ops->sweep(a));
+    h->launches++;
+  }
   h->halo_deferred = false;        // whatever was written has stale halos until the next lb_halo
   if (collide) {
     if (h->opt_hydro_write) { h->u_fill_pending = false; h->hydro_stale = false; }
@@ -460,7 +552,7 @@ static void halo_lists(const b200lb_s * h, int d, int scheme, int nplane_per_dis
   }
 }
 
-static int halo_launch(b200lb_s * h, int mode, const HaloParams & H) {
+static int halo_launch(b200lb_s * h, int mode, const HaloParams & H, cudaStream_t st) {
   const Layout & L = H.L;
   const int d = H.axis;
   const int fa = (d == 2) ? 1 : 2;
@@ -468,9 +560,9 @@ static int halo_launch(b200lb_s * h, int mode, const HaloParams & H) {
   dim3 block(fa == 2 ? 128 : 32, fa == 2 ? 2 : 8, 1);
   dim3 grid((L.na[fa] + block.x - 1)/block.x, (L.na[sl] + block.y - 1)/block.y, H.nlo + H.nhi);
   if (grid.z == 0) return 0;
-  if (mode == HALO_LOCAL)  halo_kernel<HALO_LOCAL><<<grid, block, 0, h->s_main>>>(H);
-  if (mode == HALO_PACK)   halo_kernel<HALO_PACK><<<grid, block, 0, h->s_main>>>(H);
-  if (mode == HALO_UNPACK) halo_kernel<HALO_UNPACK><<<grid, block, 0, h->s_main>>>(H);
+  if (mode == HALO_LOCAL)  halo_kernel<HALO_LOCAL><<<grid, block, 0, st>>>(H);
+  if (mode == HALO_PACK)   halo_kernel<HALO_PACK><<<grid, block, 0, st>>>(H);
+  if (mode == HALO_UNPACK) halo_kernel<HALO_UNPACK><<<grid, block, 0, st>>>(H);
   CU(cudaGetLastError());
   h->launches++;
   return 0;
@@ -496,7 +588,7 @@ static int halo_buffers(b200lb_s * h, int d, int nel) {
 // which: 0 = every axis, 1 = only axes decomposed over ranks, 2 = only the
 // axes that are periodic within this rank (local copies).
 static int halo_exchange(b200lb_s * h, double * data, bool lattice, int nplane, int scheme,
-			 int which) {
+			 int which, cudaStream_t st) {
   for (int d = 0; d < 3; d++) {
     if (h->L.h[d] == 0) continue;
     const int a = h->ops->dax[d];
@@ -507,7 +599,7 @@ static int halo_exchange(b200lb_s * h, double * data, bool lattice, int nplane, 
     if (h->desc.cartsz[a] == 1) {
       if (!h->desc.periodic[a]) continue;        // physical boundary: nothing to receive
       if (which == 1) continue;
-      if (halo_launch(h, HALO_LOCAL, H)) return -1;
+      if (halo_launch(h, HALO_LOCAL, H, st)) return -1;
       continue;
     }
     if (which == 2) continue;
@@ -515,22 +607,158 @@ static int halo_exchange(b200lb_s * h, double * data, bool lattice, int nplane, 
     if (halo_buffers(h, d, nplane)) return -1;
     HaloBuf & b = h->hb[d];
     H.to_lo = b.to_lo; H.to_hi = b.to_hi; H.from_lo = b.from_lo; H.from_hi = b.from_hi;
-    if (halo_launch(h, HALO_PACK, H)) return -1;
+    if (halo_launch(h, HALO_PACK, H, st)) return -1;
     const int lo = h->desc.nbr_lo[a], hi = h->desc.nbr_hi[a];
     // Order matters when lo == hi (two ranks, periodic): the peer's first
     // message is its low face, which is my HIGH halo.
     NC(g_nccl.GroupStart());
-    if (lo >= 0) NC(g_nccl.Send(b.to_lo, (size_t) H.nhi*b.nface, ncclDouble, lo, h->comm, h->s_main));
-    if (hi >= 0) NC(g_nccl.Send(b.to_hi, (size_t) H.nlo*b.nface, ncclDouble, hi, h->comm, h->s_main));
-    if (hi >= 0) NC(g_nccl.Recv(b.from_hi, (size_t) H.nhi*b.nface, ncclDouble, hi, h->comm, h->s_main));
-    if (lo >= 0) NC(g_nccl.Recv(b.from_lo, (size_t) H.nlo*b.nface, ncclDouble, lo, h->comm, h->s_main));
+    if (lo >= 0) NC(g_nccl.Send(b.to_lo, (size_t) H.nhi*b.nface, ncclDouble, lo, h->comm, st));
+    if (hi >= 0) NC(g_nccl.Send(b.to_hi, (size_t) H.nlo*b.nface, ncclDouble, hi, h->comm, st));
+    if (hi >= 0) NC(g_nccl.Recv(b.from_hi, (size_t) H.nhi*b.nface, ncclDouble, hi, h->comm, st));
+    if (lo >= 0) NC(g_nccl.Recv(b.from_lo, (size_t) H.nlo*b.nface, ncclDouble, lo, h->comm, st));
     NC(g_nccl.GroupEnd());
     // a missing neighbour (non-periodic edge) leaves that halo untouched
     if (lo < 0) H.nlo = 0;
     if (hi < 0) H.nhi = 0;
-    if (halo_launch(h, HALO_UNPACK, H)) return -1;
+    if (halo_launch(h, HALO_UNPACK, H, st)) return -1;
   }
   return 0;
+}
+
+
+// ---------------------------------------------------------------------------
+// direct reduced exchange (see halo_direct_kernel)
+// ---------------------------------------------------------------------------
+
+// rank of the process at Cartesian coordinates coords + dir (physical axes), in
+// the row-major order of MPI_Cart_create without reordering (z fastest), or -1
+static int cart_rank(const b200lb_s * h, const int dir[3]) {
+  int c[3];
+  for (int a = 0; a < 3; a++) {
+    c[a] = h->desc.cartcoords[a] + dir[a];
+    if (c[a] < 0 || c[a] >= h->desc.cartsz[a]) {
+      if (!h->desc.periodic[a]) return -1;
+      c[a] = (c[a] + h->desc.cartsz[a]) % h->desc.cartsz[a];
+    }
+  }
+  return (c[0]*h->desc.cartsz[1] + c[1])*h->desc.cartsz[2] + c[2];
+}
+
+static int direct_setup(b200lb_s * h) {
+  if (h->direct_state != 0) return 0;
+  h->direct_state = -1;
+  const Layout & L = h->L;
+  // the neighbour table of the descriptor must agree with row-major ranks
+  for (int a = 0; a < 3; a++) {
+    if (h->desc.cartsz[a] == 1) continue;
+    int dm[3] = {0, 0, 0}, dp[3] = {0, 0, 0};
+    dm[a] = -1; dp[a] = 1;
+    if (cart_rank(h, dm) != h->desc.nbr_lo[a] || cart_rank(h, dp) != h->desc.nbr_hi[a]) return 0;
+  }
+  static HaloMsg pk[B200LB_MAXMSG], up[B200LB_MAXMSG];
+  int np = 0, nu = 0;
+  i64 poff = 0, uoff = 0;
+  h->pack_max = h->unpack_max = 0;
+  for (int e0 = -1; e0 <= 1; e0++) {
+    for (int e1 = -1; e1 <= 1; e1++) {
+      for (int e2 = -1; e2 <= 1; e2++) {
+	const int dir[3] = {e0, e1, e2};              // device axes
+	if (!e0 && !e1 && !e2) continue;
+	bool ok = true;
+	int pdir[3] = {0, 0, 0}, mdir[3] = {0, 0, 0};  // physical axes
+	for (int d = 0; d < 3; d++) {
+	  const int a = h->ops->dax[d];
+	  if (dir[d] != 0 && (L.h[d] == 0 || h->desc.cartsz[a] == 1)) ok = false;
+	  pdir[a] = dir[d]; mdir[a] = -dir[d];
+	}
+	if (!ok) continue;
+	HaloMsg m;
+	memset(&m, 0, sizeof(m));
+	for (int n = 0; n < h->desc.ndist; n++) {
+	  for (int p = 0; p < h->desc.nvel; p++) {
+	    bool match = true;
+	    for (int d = 0; d < 3; d++) {
+	      if (dir[d] != 0 && h->ops->cv[p][h->ops->dax[d]] != dir[d]) match = false;
+	    }
+	    if (match) {
+	      if (m.npop >= B200LB_MSGPOP) return 0;
+	      m.plane[m.npop++] = n*h->desc.nvel + p;
+	    }
+	  }
+	}
+	if (m.npop == 0) continue;                     // e.g. corners of D3Q19
+	m.nsite = 1;
+	for (int d = 0; d < 3; d++) {
+	  if (dir[d] == 1)       { m.slo[d] = L.n[d];  m.rlo[d] = 0;          m.dim[d] = 1; }
+	  else if (dir[d] == -1) { m.slo[d] = 1;       m.rlo[d] = L.n[d] + 1; m.dim[d] = 1; }
+	  else                   { m.slo[d] = L.h[d];  m.rlo[d] = L.h[d];     m.dim[d] = L.n[d]; }
+	  m.nsite *= m.dim[d];
+	}
+	const i64 cnt = m.nsite*m.npop;
+	const int to = cart_rank(h, pdir), from = cart_rank(h, mdir);
+	if (to >= 0) {
+	  m.off = poff; pk[np] = m;
+	  h->pack_peer[np] = to; h->pack_off[np] = poff; h->pack_cnt[np] = cnt;
+	  poff += cnt; np++;
+	  if (cnt > h->pack_max) h->pack_max = cnt;
+	}
+	if (from >= 0) {
+	  m.off = uoff; up[nu] = m;
+	  h->unpack_peer[nu] = from; h->unpack_off[nu] = uoff; h->unpack_cnt[nu] = cnt;
+	  uoff += cnt; nu++;
+	  if (cnt > h->unpack_max) h->unpack_max = cnt;
+	}
+      }
+    }
+  }
+  if (np == 0 && nu == 0) return 0;
+  h->npack = np; h->nunpack = nu;
+  CU(cudaMalloc(&h->msg_pack, sizeof(HaloMsg)*B200LB_MAXMSG));
+  CU(cudaMalloc(&h->msg_unpack, sizeof(HaloMsg)*B200LB_MAXMSG));
+  CU(cudaMemcpy(h->msg_pack, pk, sizeof(HaloMsg)*B200LB_MAXMSG, cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(h->msg_unpack, up, sizeof(HaloMsg)*B200LB_MAXMSG, cudaMemcpyHostToDevice));
+  CU(cudaMalloc(&h->dsend, sizeof(double)*(poff + 1)));
+  CU(cudaMalloc(&h->drecv, sizeof(double)*(uoff + 1)));
+  h->direct_state = 1;
+  return 0;
+}
+
+static int direct_exchange(b200lb_s * h, double * data, cudaStream_t st) {
+  if (h->npack > 0) {
+    unsigned gx = (unsigned) ((h->pack_max + 255)/256);
+    if (gx > 1024) gx = 1024;
+    halo_direct_kernel<0><<<dim3(gx, h->npack, 1), 256, 0, st>>>(h->L, h->msg_pack, data, h->dsend);
+    CU(cudaGetLastError());
+    h->launches++;
+  }
+  // Sends and receives are listed in the same direction order on every rank, so
+  // several messages between the same pair of ranks (2 ranks in a periodic
+  // direction) match up in order.
+  NC(g_nccl.GroupStart());
+  for (int i = 0; i < h->npack; i++) {
+    NC(g_nccl.Send(h->dsend + h->pack_off[i], (size_t) h->pack_cnt[i], ncclDouble, h->pack_peer[i], h->comm, st));
+  }
+  for (int i = 0; i < h->nunpack; i++) {
+    NC(g_nccl.Recv(h->drecv + h->unpack_off[i], (size_t) h->unpack_cnt[i], ncclDouble, h->unpack_peer[i], h->comm, st));
+  }
+  NC(g_nccl.GroupEnd());
+  if (h->nunpack > 0) {
+    unsigned gx = (unsigned) ((h->unpack_max + 255)/256);
+    if (gx > 1024) gx = 1024;
+    halo_direct_kernel<1><<<dim3(gx, h->nunpack, 1), 256, 0, st>>>(h->L, h->msg_unpack, data, h->drecv);
+    CU(cudaGetLastError());
+    h->launches++;
+  }
+  return 0;
+}
+
+// the decomposed directions of the current lattice, by the cheapest valid route
+static int lattice_exchange(b200lb_s * h, int scheme, cudaStream_t st) {
+  if (scheme == B200LB_HALO_REDUCED && h->comm && h->opt_direct) {
+    if (direct_setup(h)) return -1;
+    if (h->direct_state == 1) return direct_exchange(h, h->lat[h->cur], st);
+  }
+  return halo_exchange(h, h->lat[h->cur], true, h->nplane, scheme, 1, st);
 }
 
 // lb_halo on the current lattice. Every sweep that streams wraps around the axes
@@ -541,17 +769,35 @@ static int halo_exchange(b200lb_s * h, double * data, bool lattice, int nplane, 
 // each pass spans the full extent of the other axes and overwrites what an
 // earlier pass could not know yet.
 static int lattice_halo(b200lb_s * h, int scheme) {
-  if (!h->opt_halo_lazy) return halo_exchange(h, h->lat[h->cur], true, h->nplane, scheme, 0);
-  if (halo_exchange(h, h->lat[h->cur], true, h->nplane, scheme, 1)) return -1;
+  if (!h->opt_halo_lazy) {
+    if (join_comm(h)) return -1;
+    return halo_exchange(h, h->lat[h->cur], true, h->nplane, scheme, 0, h->s_main);
+  }
+  if (h->comm && h->opt_overlap) {
+    // The exchange runs on its own stream behind the boundary slabs of the sweep
+    // that produced this lattice, next to that sweep's interior launch. s_main
+    // joins it again before the next operation on the lattice (join_comm).
+    if (join_comm(h)) return -1;
+    if (!h->bnd_valid) CU(cudaEventRecord(h->ev_bnd, h->s_main));
+    h->bnd_valid = false;
+    CU(cudaStreamWaitEvent(h->s_comm, h->ev_bnd, 0));
+    if (lattice_exchange(h, scheme, h->s_comm)) return -1;
+    CU(cudaEventRecord(h->ev_halo, h->s_comm));
+    h->halo_inflight = true;
+  }
+  else {
+    if (lattice_exchange(h, scheme, h->s_main)) return -1;
+  }
   h->halo_deferred = true;
   h->halo_deferred_scheme = scheme;
   return 0;
 }
 
 static int flush_halo(b200lb_s * h) {
+  if (join_comm(h)) return -1;
   if (!h->halo_deferred) return 0;
   h->halo_deferred = false;
-  return halo_exchange(h, h->lat[h->cur], true, h->nplane, h->halo_deferred_scheme, 2);
+  return halo_exchange(h, h->lat[h->cur], true, h->nplane, h->halo_deferred_scheme, 2, h->s_main);
 }
 
 extern "C" int b200lb_halo_swap(b200lb_t * h, int scheme) {
@@ -570,7 +816,8 @@ extern "C" int b200lb_halo(b200lb_t * h) {
 extern "C" int b200lb_phi_halo(b200lb_t * h) {
   if (!h) return fail("null handle");
   if (!h->phi) return fail("no order parameter (ndist = 1)");
-  return halo_exchange(h, h->phi, false, 1, B200LB_HALO_FULL, 0);
+  if (join_comm(h)) return -1;
+  return halo_exchange(h, h->phi, false, 1, B200LB_HALO_FULL, 0, h->s_main);
 }
 
 // ---------------------------------------------------------------------------
@@ -580,6 +827,7 @@ extern "C" int b200lb_phi_halo(b200lb_t * h) {
 extern "C" int b200lb_phi_from_g(b200lb_t * h) {
   if (!h) return fail("null handle");
   if (!h->phi) return fail("no order parameter (ndist = 1)");
+  if (join_comm(h)) return -1;
   const double * g = h->lat[h->cur] + (i64) h->desc.nvel*h->L.nsd;
   CU(h->ops->phi_from_g(h->L, h->selfper, g, h->phi, h->prop_pending, h->s_main));
   h->launches++;
@@ -653,6 +901,7 @@ extern "C" int b200lb_step(b200lb_t * h, int nsteps) {
 extern "C" int b200lb_stats(b200lb_t * h, double out[8]) {
   if (!h || !out) return fail("null argument");
   if (materialise(h)) return -1;
+  if (join_comm(h)) return -1;
   const Layout & L = h->L;
   dim3 block(128, 2, 1);
   dim3 grid((L.n[2] + 127)/128, (L.n[1] + 1)/2, L.n[0]);
@@ -668,6 +917,7 @@ extern "C" int b200lb_stats(b200lb_t * h, double out[8]) {
 
 extern "C" int b200lb_sync(b200lb_t * h) {
   if (!h) return fail("null handle");
+  if (join_comm(h)) return -1;
   CU(cudaStreamSynchronize(h->s_main));
   CU(cudaStreamSynchronize(h->s_x[0]));
   CU(cudaStreamSynchronize(h->s_x[1]));
@@ -690,6 +940,7 @@ static int ensure_stage(b200lb_s * h) {
 // in `layout` for all nsite_host sites
 static int transfer(b200lb_s * h, double * dev, int nel, double * host, int layout, bool to_device) {
   if (ensure_stage(h)) return -1;
+  if (join_comm(h)) return -1;
   CU(cudaStreamSynchronize(h->s_main));
   XferParams X;
   memset(&X, 0, sizeof(X));
@@ -836,6 +1087,7 @@ extern "C" int b200lb_comm_init(b200lb_t * h, const char id[128]) {
 
 extern "C" int b200lb_timer_start(b200lb_t * h) {
   if (!h) return fail("null handle");
+  if (join_comm(h)) return -1;
   CU(cudaStreamSynchronize(h->s_main));
   CU(cudaEventRecord(h->ev0, h->s_main));
   return 0;
@@ -843,6 +1095,7 @@ extern "C" int b200lb_timer_start(b200lb_t * h) {
 
 extern "C" int b200lb_timer_stop(b200lb_t * h, float * ms) {
   if (!h || !ms) return fail("null argument");
+  if (join_comm(h)) return -1;
   CU(cudaEventRecord(h->ev1, h->s_main));
   CU(cudaEventSynchronize(h->ev1));
   CU(cudaEventElapsedTime(ms, h->ev0, h->ev1));

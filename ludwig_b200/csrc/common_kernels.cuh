@@ -226,3 +226,48 @@ xfer_kernel(const XferParams X) {
     else X.stage[hs - X.hs0] = X.dev[(i64) X.e0*L.nsd + site];
   }
 }
+
+// ---------------------------------------------------------------------------
+// Direct reduced halo: one message per neighbour direction (faces, edges and,
+// for D3Q27, corners of the directions decomposed over ranks), each carrying only
+// the populations whose velocity points into the receiver -- the message set of
+// the reference's LB_HALO_OPENMP_REDUCED scheme (src/model.c:1161-1219), but
+// packed by ONE kernel launch, sent in ONE NCCL group and unpacked by one launch:
+// no x -> y -> z dependency chain. Directions that are periodic within the rank
+// need nothing (the sweeps wrap), so regions span only interior sites there.
+// ---------------------------------------------------------------------------
+
+#define B200LB_MAXMSG 26
+#define B200LB_MSGPOP 18
+
+struct HaloMsg {
+  int npop;
+  int plane[B200LB_MSGPOP];   // n*nvel + p
+  int slo[3];                 // first site of the send region (halo-inclusive device coords)
+  int rlo[3];                 // first site of the receive region
+  int dim[3];                 // region extent
+  i64 nsite;                  // dim[0]*dim[1]*dim[2]
+  i64 off;                    // offset of this message in the send / receive buffers
+};
+
+template <int UNPACK>
+__global__ void __launch_bounds__(256)
+halo_direct_kernel(const Layout L, const HaloMsg * __restrict__ msgs,
+		   double * __restrict__ data, double * __restrict__ buf) {
+  const HaloMsg & m = msgs[blockIdx.y];
+  const i64 total = m.nsite*m.npop;
+  for (i64 idx = (i64) blockIdx.x*blockDim.x + threadIdx.x; idx < total;
+       idx += (i64) gridDim.x*blockDim.x) {
+    const int k = (int) (idx / m.nsite);
+    const i64 s = idx - (i64) k*m.nsite;
+    const int a2 = (int) (s % m.dim[2]);
+    const i64 r = s / m.dim[2];
+    const int a1 = (int) (r % m.dim[1]);
+    const int a0 = (int) (r / m.dim[1]);
+    const int * o = UNPACK ? m.rlo : m.slo;
+    const i64 site = (i64) (o[0] + a0)*L.s0 + (i64) (o[1] + a1)*L.s1 + L.z0 + o[2] + a2;
+    double * p = data + (i64) m.plane[k]*L.nsd + site;
+    if (UNPACK) *p = buf[m.off + idx];
+    else buf[m.off + idx] = *p;
+  }
+}

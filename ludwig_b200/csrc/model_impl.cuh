@@ -20,7 +20,7 @@ static cudaError_t launch_one(const SweepArgs & a) {
   if (n0 <= 0 || n1 <= 0 || n2 <= 0) return cudaSuccess;
   const int nt2 = (n2 + VEC - 1)/VEC;
   int bx = a.bx;
-  while (bx > 32 && bx/2 >= nt2) bx /= 2;
+  while (bx > 1 && bx/2 >= nt2) bx /= 2;      // thin slabs: let the warp span rows instead
   int by = 256/bx;
   if (BINARY || GHOST) by = (128/bx > 0) ? 128/bx : 1;
   while (by > 1 && by/2 >= n1) by /= 2;

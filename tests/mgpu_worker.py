@@ -33,10 +33,12 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--nvel", type=int, default=19)
     ap.add_argument("--ndist", type=int, default=1)
-    ap.add_argument("--local", type=int, nargs=3, default=[12, 10, 8])
+    ap.add_argument("--lsize", type=int, nargs=3, default=[12, 10, 8])
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--halo", default="full")
     ap.add_argument("--fused", type=int, default=1)
+    ap.add_argument("--overlap", type=int, default=1)
+    ap.add_argument("--direct", type=int, default=1)
     args = ap.parse_args()
 
     rank = int(os.environ["RANK"])
@@ -50,7 +52,7 @@ def main():
     grid = {1: (1, 1, 1), 2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}[world]
     if ndim == 2 and grid[2] != 1:
         grid = (grid[0] * grid[2], grid[1], 1)
-    local = tuple(args.local)
+    local = tuple(args.lsize)
     ntotal = tuple(local[a] * grid[a] for a in range(3))
     dec = lb.Decomposition(ntotal, rank, world, grid=grid)
     cv, wv = models_host.cv(nvel), models_host.wv(nvel)
@@ -62,6 +64,8 @@ def main():
     dist.broadcast(uid, 0)
     lat.comm_init(bytes(uid.cpu().tolist()))
     lat.set_option("fused", args.fused)
+    lat.set_option("overlap", args.overlap)
+    lat.set_option("direct", args.direct)
     lat.set_option("halo", lb.HALO_REDUCED if args.halo == "reduced" else lb.HALO_FULL)
     kw = dict(eta_shear=0.1, eta_bulk=0.1)
     if ndist == 2:
@@ -130,9 +134,9 @@ def main():
         err = float(np.max(np.abs(glob - fo)) / np.max(np.abs(fo)))
         mass = abs(float(sums[0].item()) - s1[0])
         halo_ok = bool(flags.item() > 0.5)
-        print("mgpu world=%d grid=%s nvel=%d ndist=%d halo=%s fused=%d: halo_bit_exact=%s "
+        print("mgpu world=%d grid=%s nvel=%d ndist=%d halo=%s fused=%d overlap=%d direct=%d: halo_bit_exact=%s "
               "decomposed==single=%s err_vs_oracle=%.2e mass_diff=%.2e"
-              % (world, grid, nvel, ndist, args.halo, args.fused, halo_ok, same, err, mass),
+              % (world, grid, nvel, ndist, args.halo, args.fused, args.overlap, args.direct, halo_ok, same, err, mass),
               flush=True)
         if not (halo_ok and same and err < 1e-12 and mass < 1e-9 * n):
             rc = 1

@@ -30,9 +30,12 @@ def launch(n, extra, port):
     ["--nvel", "19", "--halo", "full"],
     ["--nvel", "19", "--halo", "reduced"],
     ["--nvel", "19", "--halo", "reduced", "--fused", "0"],
-    ["--nvel", "27", "--halo", "reduced", "--local", "8", "6", "10"],
-    ["--nvel", "19", "--ndist", "2", "--halo", "full", "--local", "8", "8", "6"],
-    ["--nvel", "9", "--halo", "reduced", "--local", "16", "12", "1"],
+    ["--nvel", "19", "--halo", "reduced", "--overlap", "0"],
+    ["--nvel", "19", "--halo", "reduced", "--direct", "0"],
+    ["--nvel", "19", "--halo", "full", "--overlap", "0", "--lsize", "8", "8", "8"],
+    ["--nvel", "27", "--halo", "reduced", "--lsize", "8", "6", "10"],
+    ["--nvel", "19", "--ndist", "2", "--halo", "full", "--lsize", "8", "8", "6"],
+    ["--nvel", "9", "--halo", "reduced", "--lsize", "16", "12", "1"],
 ])
 def test_decomposed_equals_single(n, extra):
     if ngpu() < n:
