@@ -120,6 +120,28 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(self.reasons), "samples": len(self.sm)}
 
 
+def workload_name(nvel, ndist, local, grid):
+    ndim = 2 if nvel == 9 else 3
+    return ("D%dQ%d %s MRT %dx%dx%d periodic per GPU, grid %s"
+            % (ndim, nvel, "binary symmetric_lb" if ndist == 2 else "single-fluid",
+               local[0], local[1], local[2], "x".join(str(g) for g in grid)))
+
+
+def ncu_traffic(nvel, ndist, local, hydro_write, vec):
+    """DRAM bytes per launch of the dominant kernel from the committed ncu capture, when
+    it was taken on this very configuration; else None."""
+    path = os.path.join(ROOT, "profiles", "r1_ncu_traffic.json")
+    try:
+        with open(path) as fh:
+            t = json.load(fh)
+        if (t["nvel"], t["ndist"], tuple(t["local"]), t["hydro_write"], t["vec"]) == \
+                (nvel, ndist, tuple(local), int(hydro_write), vec):
+            return t["dram_bytes_per_launch"]
+    except Exception:
+        pass
+    return None
+
+
 def grid_for(n):
     # The contiguous (z) direction is left undivided: its faces are strided in memory
     # and NVSwitch gives every pair of GPUs the same bandwidth, so a 4x2x1 grid beats
@@ -179,19 +201,33 @@ def cpu_reference(nvel, size, seconds, nsteps_fixed=None, warmup=1):
 
 
 def run_reference(args):
+    """Reference arm: the reference's own CPU implementation of the path (oracle/_ref =
+    the unmodified Ludwig sources, OpenMP over all host cores; the oracle port if that
+    build is absent) on this arm's workload. Each step is a bounded sample: the full
+    lattice when K + W steps of it fit in about two minutes, else a 128^3 block of it
+    (MLUPS is an intensive quantity). Rank 0 only."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    nvel = args.nvel
+    nvel, ndist = args.nvel, args.ndist
+    ndim = 2 if nvel == 9 else 3
     local = tuple(args.local or ((4096, 4096, 1) if nvel == 9 else (256, 256, 256)))
-    size = tuple(args.ref_size or ((1024, 1024, 1) if nvel == 9 else (128, 128, 128)))
+    grid = tuple(args.grid) if args.grid else grid_for(args.gpus)
+    small = (1024, 1024, 1) if nvel == 9 else (128, 128, 128)
+    if args.ref_size:
+        size = tuple(args.ref_size)
+    else:
+        probe, _, _ = cpu_reference(nvel, small, 0.0, nsteps_fixed=2, warmup=1)
+        t_full = float(np.prod(local)) / (probe["value"] * 1e6)
+        size = local if t_full * (args.steps + args.warmup) < 120.0 else small
     base, n, t = cpu_reference(nvel, size, 0.0, nsteps_fixed=args.steps, warmup=args.warmup)
     line = {
-        "impl": "reference", "metric": "D3Q19 fp64 MLUPS" if nvel == 19 else "D%dQ%d fp64 MLUPS" % (2 if nvel == 9 else 3, nvel),
+        "impl": "reference",
+        "metric": "D3Q19 fp64 MLUPS" if nvel == 19 else "D%dQ%d fp64 MLUPS" % (ndim, nvel),
         "value": base["value"], "unit": "MLUPS", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * t / n, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "D3Q%d single-fluid MRT %dx%dx%d periodic" % (nvel, *local),
+        "config": {"workload": workload_name(nvel, ndist, local, grid),
                    "sample": base["sample"]},
         "cpu_baseline": base,
         "e2e": {"value": base["value"], "unit": "MLUPS", "h2d_bytes_per_step": 0,
@@ -318,30 +354,43 @@ def main():
     if kernel_ms:
         ach = balg * sites_local / (kernel_ms * 1e-3) / 1e9
         roof = {"bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s",
-                "frac": ach / hbm, "traffic": None, "kernel": "lb_sweep_kernel<pull,collide>",
+                "frac": ach / hbm,
+                "traffic": ncu_traffic(nvel, ndist, local, args.hydro_write, args.vec),
+                "kernel": "lb_sweep_kernel<pull,collide>",
                 "kernel_ms": kernel_ms, "bytes_per_site": balg, "peak_source": hbm_src,
                 "step_frac": balg * sites_local * args.steps / (ms * 1e-3) / 1e9 / hbm}
 
     # ---- end to end through the host call surface with HOST buffers ---------------
+    # The user-visible job: the lattice lives in a (page-locked) host array in the
+    # reference's AOS layout; lb_memcpy H2D, then every step = the hot path + the
+    # conserved sums of that step read back to the host (gathered inside the collision
+    # sweep), then lb_memcpy D2H. Wall clock around the lot.
     e2e = None
     if not args.no_e2e:
-        # restore the state so the conserved sums are comparable
+        hbuf = lb.pinned_empty(f0.shape)
+        hbuf[...] = f0
+        lat.set_option("diag", 1)
         barrier()
         t0 = time.perf_counter()
-        lat.lb_memcpy_h2d(f0)                       # lb_memcpy(H2D), host AOS layout
-        lat.step(args.steps)
-        st = lat.stats()                            # conserved sums back to the host
-        fout = lat.lb_memcpy_d2h(f0)                # lb_memcpy(D2H) into the host array
+        lat.lb_memcpy_h2d(hbuf)
+        mass = 0.0
+        for _ in range(args.steps):
+            lat.step(1)
+            mass = lat.step_diag()[0]           # 64 B device -> host, every step
+        lat.lb_memcpy_d2h(hbuf)
         lat.sync()
         te = time.perf_counter() - t0
         te = max_over_ranks(te)
+        lat.set_option("diag", 0)
         e2e = {"value": sites_total * args.steps / te / 1e6, "unit": "MLUPS",
                "h2d_bytes_per_step": lattice_bytes / args.steps,
-               "d2h_bytes_per_step": (lattice_bytes + 64) / args.steps,
-               "what": "lb_memcpy H2D of the host lattice (AOS), %d steps, stats, "
-                       "lb_memcpy D2H; wall clock" % args.steps,
-               "mass": float(st[0])}
-        del fout
+               "d2h_bytes_per_step": lattice_bytes / args.steps + 64,
+               "seconds": te,
+               "what": "pinned host lattice (reference AOS layout): lb_memcpy H2D, %d x "
+                       "[step + per-step conserved sums D2H], lb_memcpy D2H; wall clock"
+                       % args.steps,
+               "mass": float(mass)}
+        lb.pinned_free(hbuf)
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -360,9 +409,7 @@ def main():
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
             "config": {
-                "workload": "D%dQ%d %s MRT %dx%dx%d periodic per GPU, grid %s"
-                            % (ndim, nvel, "binary symmetric_lb" if ndist == 2 else "single-fluid",
-                               local[0], local[1], local[2], par),
+                "workload": workload_name(nvel, ndist, local, grid),
                 "global_lattice": list(ntotal), "decomposition": par,
                 "fused": bool(args.fused), "vec": args.vec, "halo": args.halo,
                 "hydro_write": bool(args.hydro_write), "overlap": bool(args.overlap), "direct_halo": bool(args.direct),

@@ -100,7 +100,11 @@ long b200lb_nsite(const b200lb_t * h);                          /* host nsite = 
  *   "hydro_write" 0/1  store rho,u from the collision every step (reference
  *                      behaviour, src/collision.c:570-579); 0 = on demand
  *   "vec"         1/2  lattice sites per thread
- *   "block"       threads per block along the contiguous direction */
+ *   "block"       threads per block along the contiguous direction
+ *   "halo_lazy"   0/1  defer the local periodic halo copies until the host looks
+ *   "overlap"     0/1  exchange halos on a second stream next to the interior sweep
+ *   "direct"      0/1  reduced halo as one message per neighbour direction
+ *   "diag"        0/1  gather conserved sums inside the collision sweep */
 int  b200lb_set_option(b200lb_t * h, const char * name, long value);
 long b200lb_get_option(const b200lb_t * h, const char * name);
 
@@ -135,6 +139,12 @@ int  b200lb_step(b200lb_t * h, int nsteps);
  * src/stats_distribution.c:55-118,201-265):
  * out = { sum rho, sum rho^2, min rho, max rho, gx, gy, gz, sum phi } */
 int  b200lb_stats(b200lb_t * h, double out[8]);
+
+/* The same sums gathered inside the last lb_collide sweep (option "diag" = 1):
+ * warp-shuffle + per-block partials in the sweep itself, folded here. They describe
+ * the state that ENTERED that collision (= the lattice after the previous
+ * lb_propagation); momentum is sum_p c_p f_p. Costs no extra pass over the lattice. */
+int  b200lb_step_diag(b200lb_t * h, double out[8]);
 
 int  b200lb_sync(b200lb_t * h);          /* tdpDeviceSynchronize for this handle */
 

@@ -120,7 +120,7 @@ struct b200lb_s {
   bool ghost;
 
   // options
-  int opt_fused, opt_halo, opt_hydro_write, opt_vec, opt_block, opt_halo_lazy, opt_overlap, opt_direct;
+  int opt_fused, opt_halo, opt_hydro_write, opt_vec, opt_block, opt_halo_lazy, opt_overlap, opt_direct, opt_diag;
 
   cudaStream_t s_main, s_x[2];
   cudaStream_t s_comm;       // halo exchange of decomposed directions (overlaps the interior sweep)
@@ -131,6 +131,7 @@ struct b200lb_s {
   bool halo_inflight;        // s_main must wait for ev_halo before touching the lattice
   double * stage[2];
   double * partial; i64 npartial;
+  double * diag; i64 diag_cap, diag_count;   // in-sweep diagnostics: per-block partials of the last collision
   double * stats_dev; double * stats_host;
   long launches;
 
@@ -295,6 +296,8 @@ extern "C" int b200lb_create(const b200lb_desc_t * desc, b200lb_t ** out) {
   // diagnostics scratch: one partial per block of a (128 x 2) tiling
   h->npartial = (i64)((L.n[2] + 127)/128)*((L.n[1] + 1)/2)*L.n[0];
   CU(cudaMalloc(&h->partial, 8*sizeof(double)*h->npartial));
+  h->diag_cap = 4*h->npartial + 4096;
+  CU(cudaMalloc(&h->diag, 8*sizeof(double)*h->diag_cap));
   CU(cudaMalloc(&h->stats_dev, 8*sizeof(double)));
   CU(cudaMallocHost(&h->stats_host, 8*sizeof(double)));
 
@@ -338,7 +341,7 @@ extern "C" int b200lb_destroy(b200lb_t * h) {
   }
   cudaFree(h->rho); cudaFree(h->u); cudaFree(h->force);
   cudaFree(h->phi); cudaFree(h->grad); cudaFree(h->delsq);
-  cudaFree(h->partial); cudaFree(h->stats_dev); cudaFreeHost(h->stats_host);
+  cudaFree(h->partial); cudaFree(h->diag); cudaFree(h->stats_dev); cudaFreeHost(h->stats_host);
   cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
   cudaStreamDestroy(h->s_main);
   cudaStreamDestroy(h->s_comm);
@@ -366,6 +369,7 @@ extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
   if (!strcmp(name, "halo_lazy")) { h->opt_halo_lazy = (v != 0); return 0; }
   if (!strcmp(name, "overlap")) { h->opt_overlap = (v != 0); return 0; }
   if (!strcmp(name, "direct")) { h->opt_direct = (v != 0); return 0; }
+  if (!strcmp(name, "diag")) { h->opt_diag = (v != 0); return 0; }
   if (!strcmp(name, "vec")) {
     if (v != 1 && v != 2) return fail("vec must be 1 or 2");
     h->opt_vec = (int) v; return 0;
@@ -385,6 +389,7 @@ extern "C" long b200lb_get_option(const b200lb_t * h, const char * name) {
   if (!strcmp(name, "halo_lazy")) return h->opt_halo_lazy;
   if (!strcmp(name, "overlap")) return h->opt_overlap;
   if (!strcmp(name, "direct")) return h->opt_direct;
+  if (!strcmp(name, "diag")) return h->opt_diag;
   if (!strcmp(name, "direct_state")) return h->direct_state;
   if (!strcmp(name, "halo_deferred")) return h->halo_deferred;
   if (!strcmp(name, "vec")) return h->opt_vec;
@@ -472,6 +477,10 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
   int lo[7][3], hi[7][3];
   const int nbox = split_boxes(h, lo, hi);
   h->bnd_valid = false;
+  a.diag = collide && h->opt_diag;
+  a.P.diag = h->diag;
+  a.P.diag_base = 0;
+  if (collide) h->diag_count = 0;
   for (int b = 0; b < nbox; b++) {
     if (nbox > 1) {
       for (int e = 0; e < 3; e++) { a.P.lo[e] = lo[b][e]; a.P.hi[e] = hi[b][e]; }
@@ -483,6 +492,11 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
     }
     CU(h->ops->sweep(a));
     h->launches++;
+    if (a.diag) {
+      a.P.diag_base += a.nblocks;
+      if (a.P.diag_base > h->diag_cap) return fail("internal: diagnostics buffer too small");
+      h->diag_count = a.P.diag_base;
+    }
   }
   h->halo_deferred = false;        // whatever was written has stale halos until the next lb_halo
   if (collide) {
@@ -909,6 +923,22 @@ extern "C" int b200lb_stats(b200lb_t * h, double out[8]) {
   stats_final_kernel<<<1, 256, 0, h->s_main>>>(h->partial, h->npartial, h->stats_dev);
   CU(cudaGetLastError());
   h->launches += 2;
+  CU(cudaMemcpyAsync(h->stats_host, h->stats_dev, 8*sizeof(double), cudaMemcpyDeviceToHost, h->s_main));
+  CU(cudaStreamSynchronize(h->s_main));
+  for (int k = 0; k < 8; k++) out[k] = h->stats_host[k];
+  return 0;
+}
+
+// Conserved sums gathered INSIDE the last collision sweep (option "diag"): the
+// state that entered that collision, i.e. what stats_distribution_print /
+// stats_distribution_momentum would report before it. No extra pass over the lattice.
+extern "C" int b200lb_step_diag(b200lb_t * h, double out[8]) {
+  if (!h || !out) return fail("null argument");
+  if (!h->opt_diag || h->diag_count == 0) return fail("no in-sweep diagnostics: set option diag = 1 before lb_collide");
+  if (join_comm(h)) return -1;
+  stats_final_kernel<<<1, 256, 0, h->s_main>>>(h->diag, h->diag_count, h->stats_dev);
+  CU(cudaGetLastError());
+  h->launches++;
   CU(cudaMemcpyAsync(h->stats_host, h->stats_dev, 8*sizeof(double), cudaMemcpyDeviceToHost, h->s_main));
   CU(cudaStreamSynchronize(h->s_main));
   for (int k = 0; k < 8; k++) out[k] = h->stats_host[k];

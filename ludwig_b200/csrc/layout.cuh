@@ -38,6 +38,8 @@ struct KParams {
   const double * phi;     // [nsd]
   const double * grad;    // [3][nsd]
   const double * delsq;   // [nsd]
+  double * diag;          // per-block partial sums of the in-kernel diagnostics, or unused
+  i64 diag_base;          // first partial slot of this launch
   int lo[3], hi[3];       // sub-box of the interior, 0-based interior coordinates, [lo,hi)
   int wrap[3];            // device axis is periodic within this rank: pulls wrap instead of reading halos
   double rtau_shear, rtau_bulk;

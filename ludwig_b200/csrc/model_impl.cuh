@@ -14,9 +14,10 @@ static __constant__ GhostTab c_ghost;
 typedef B200LB_MODEL MODEL;
 
 template <int VEC, bool PULL, bool COLLIDE, bool BINARY, bool GHOST>
-static cudaError_t launch_one(const SweepArgs & a) {
+static cudaError_t launch_one(SweepArgs & a) {
   const KParams & P = a.P;
   const int n2 = P.hi[2] - P.lo[2], n1 = P.hi[1] - P.lo[1], n0 = P.hi[0] - P.lo[0];
+  a.nblocks = 0;
   if (n0 <= 0 || n1 <= 0 || n2 <= 0) return cudaSuccess;
   const int nt2 = (n2 + VEC - 1)/VEC;
   int bx = a.bx;
@@ -26,13 +27,20 @@ static cudaError_t launch_one(const SweepArgs & a) {
   while (by > 1 && by/2 >= n1) by /= 2;
   dim3 block(bx, by, 1);
   dim3 grid((nt2 + bx - 1)/bx, (n1 + by - 1)/by, n0);
-  lb_sweep_kernel<MODEL, VEC, PULL, COLLIDE, BINARY, GHOST>
-    <<<grid, block, 0, a.stream>>>(P);
+  a.nblocks = (long long) grid.x*grid.y*grid.z;
+  if (COLLIDE && a.diag) {
+    lb_sweep_kernel<MODEL, VEC, PULL, COLLIDE, BINARY, GHOST, COLLIDE>
+      <<<grid, block, 0, a.stream>>>(P);
+  }
+  else {
+    lb_sweep_kernel<MODEL, VEC, PULL, COLLIDE, BINARY, GHOST, false>
+      <<<grid, block, 0, a.stream>>>(P);
+  }
   return cudaGetLastError();
 }
 
 template <bool PULL, bool COLLIDE>
-static cudaError_t launch_pc(const SweepArgs & a) {
+static cudaError_t launch_pc(SweepArgs & a) {
   constexpr bool HAVE_BINARY = (MODEL::NDIM == 3);
   if constexpr (!COLLIDE) {
     // pure streaming: collision flags are irrelevant
@@ -56,7 +64,7 @@ static cudaError_t launch_pc(const SweepArgs & a) {
   }
 }
 
-static cudaError_t sweep_impl(const SweepArgs & a) {
+static cudaError_t sweep_impl(SweepArgs & a) {
   if (a.pull && a.collide) return launch_pc<true, true>(a);
   if (a.pull) return launch_pc<true, false>(a);
   if (a.collide) return launch_pc<false, true>(a);

@@ -10,6 +10,8 @@
 struct SweepArgs {
   KParams P;
   bool pull, collide, binary, ghost;
+  bool diag;          // accumulate conserved sums in the sweep (collide only)
+  long long nblocks;  // out: blocks launched (= diagnostic partials written)
   int vec;            // sites per thread (1 or 2)
   int bx;             // threads per block along the contiguous axis
   cudaStream_t stream;
@@ -20,7 +22,7 @@ struct ModelOps {
   int dax[3];                                   // device axis -> physical axis
   int cv[27][3];
   double wv[27];
-  cudaError_t (*sweep)(const SweepArgs &);
+  cudaError_t (*sweep)(SweepArgs &);
   cudaError_t (*phi_from_g)(const Layout &, const int wrap[3], const double * g,
 			    double * phi, bool pull, cudaStream_t);
   cudaError_t (*stats)(const Layout &, const double * f, int ndist,

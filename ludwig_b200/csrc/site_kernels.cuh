@@ -17,6 +17,7 @@
 
 #include "layout.cuh"
 #include "models.cuh"
+#include "aux_kernels.cuh"
 
 // Each model lives in its own translation unit (model_*.cu), which defines its
 // ghost-mode projector table before including this file.
@@ -244,7 +245,7 @@ phi_site(double (&g)[M::NVEL], double phi, double mu, const double (&u)[3],
 // the aligned pair), all others and every store are 128-bit.
 // ---------------------------------------------------------------------------
 
-template <class M, int VEC, bool PULL, bool COLLIDE, bool BINARY, bool GHOST>
+template <class M, int VEC, bool PULL, bool COLLIDE, bool BINARY, bool GHOST, bool DIAG>
 __global__ void __launch_bounds__(256)
 lb_sweep_kernel(const KParams P) {
 
@@ -255,11 +256,20 @@ lb_sweep_kernel(const KParams P) {
 
   const Layout & L = P.L;
 
-  const int i2 = P.lo[2] + VEC*(blockIdx.x*blockDim.x + threadIdx.x);
-  const int i1 = P.lo[1] + blockIdx.y*blockDim.y + threadIdx.y;
+  int i2 = P.lo[2] + VEC*(blockIdx.x*blockDim.x + threadIdx.x);
+  int i1 = P.lo[1] + blockIdx.y*blockDim.y + threadIdx.y;
   const int i0 = P.lo[0] + blockIdx.z;
-  if (i2 >= P.hi[2] || i1 >= P.hi[1]) return;
-  const int nv = (VEC == 2 && i2 + 1 < P.hi[2]) ? 2 : 1;
+  int nv;
+  if (i2 >= P.hi[2] || i1 >= P.hi[1]) {
+    // Outside the box. With in-kernel diagnostics every thread of the block must
+    // reach the reduction: such threads redo the box's first site and store nothing.
+    if (!DIAG) return;
+    i2 = P.lo[2]; i1 = P.lo[1]; nv = 0;
+  }
+  else {
+    nv = (VEC == 2 && i2 + 1 < P.hi[2]) ? 2 : 1;
+  }
+  double dq[8] = {0.0, 0.0, 1.0e300, -1.0e300, 0.0, 0.0, 0.0, 0.0};
 
   const i64 site = (i64)(i0 + L.h[0])*L.s0 + (i64)(i1 + L.h[1])*L.s1
                  + L.z0 + L.h[2] + i2;
@@ -355,6 +365,14 @@ lb_sweep_kernel(const KParams P) {
       else {
 	mrt_site<M, GHOST, false>(f[0][v], F, nullptr, P, rho, u);
       }
+      if (DIAG && (v < nv)) {
+	// conserved sums of the state that entered this collision: rho, rho^2, min,
+	// max, momentum sum_p c_p f_p = rho u - F/2, and phi (binary)
+	dq[0] += rho; dq[1] += rho*rho; dq[2] = fmin(dq[2], rho); dq[3] = fmax(dq[3], rho);
+	#pragma unroll
+	for (int a = 0; a < ND; a++) dq[4 + a] += rho*u[a] - 0.5*F[a];
+	if (BINARY) dq[7] += P.phi[s];
+      }
       if (P.u != nullptr && (v < nv)) {  // uniform branch: hydro stored this step
 	if (!BINARY) P.rho[s] = rho;     // the binary collision leaves rho alone
 	#pragma unroll
@@ -371,9 +389,14 @@ lb_sweep_kernel(const KParams P) {
       if (VEC == 2 && nv == 2) {
 	*reinterpret_cast<double2 *>(dst) = make_double2(f[n][0][p], f[n][VEC - 1][p]);
       }
-      else {
+      else if (nv >= 1) {
 	*dst = f[n][0][p];
       }
     }
+  }
+
+  if (DIAG) {
+    const i64 b = ((i64) blockIdx.z*gridDim.y + blockIdx.y)*gridDim.x + blockIdx.x;
+    block_reduce8(dq, P.diag + 8*(P.diag_base + b));
   }
 }

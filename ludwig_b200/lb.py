@@ -32,7 +32,7 @@ ABI_SYMBOLS = [
     "b200lb_field_download", "b200lb_set_param", "b200lb_hydro_f_zero",
     "b200lb_hydro_u_zero", "b200lb_collide", "b200lb_halo", "b200lb_halo_swap",
     "b200lb_propagate", "b200lb_phi_from_g", "b200lb_phi_halo", "b200lb_grad7",
-    "b200lb_step", "b200lb_stats", "b200lb_sync", "b200lb_nccl_unique_id",
+    "b200lb_step", "b200lb_stats", "b200lb_step_diag", "b200lb_sync", "b200lb_nccl_unique_id",
     "b200lb_comm_init", "b200lb_timer_start", "b200lb_timer_stop",
     "b200lb_launch_count", "b200lb_host_alloc", "b200lb_host_free",
 ]
@@ -109,6 +109,7 @@ def load():
     L.b200lb_hydro_f_zero.argtypes = [vp, ctypes.POINTER(ctypes.c_double)]
     L.b200lb_hydro_u_zero.argtypes = [vp, ctypes.POINTER(ctypes.c_double)]
     L.b200lb_stats.argtypes = [vp, ctypes.POINTER(ctypes.c_double)]
+    L.b200lb_step_diag.argtypes = [vp, ctypes.POINTER(ctypes.c_double)]
     L.b200lb_timer_stop.argtypes = [vp, ctypes.POINTER(ctypes.c_float)]
     L.b200lb_nccl_unique_id.argtypes = [ctypes.c_char_p]
     L.b200lb_comm_init.argtypes = [vp, ctypes.c_char_p]
@@ -124,7 +125,9 @@ def _ptr(a):
 
 
 def pinned_empty(shape):
-    """numpy array over cudaMallocHost memory (kept alive by the returned array)."""
+    """numpy array over page-locked host memory (b200lb_host_alloc = cudaMallocHost),
+    e.g. for lb->f: lb_memcpy then runs at full PCIe rate. The block lives until
+    pinned_free(array) or process exit."""
     L = load()
     n = int(np.prod(shape))
     p = ctypes.c_void_p()
@@ -132,22 +135,17 @@ def pinned_empty(shape):
         raise B200LBError(L.b200lb_last_error().decode())
     buf = (ctypes.c_double * n).from_address(p.value)
     arr = np.frombuffer(buf, dtype=np.float64).reshape(shape)
-
-    class _Owner:
-        def __init__(self, ptr):
-            self.ptr = ptr
-
-        def __del__(self):
-            try:
-                L.b200lb_host_free(self.ptr)
-            except Exception:
-                pass
-    arr = arr.view()
-    _OWNERS[id(buf)] = (_Owner(p), buf)
+    _PINNED[arr.ctypes.data] = p
     return arr
 
 
-_OWNERS = {}
+def pinned_free(arr):
+    p = _PINNED.pop(arr.ctypes.data, None)
+    if p is not None:
+        load().b200lb_host_free(p)
+
+
+_PINNED = {}
 
 
 class Lattice:
@@ -277,6 +275,11 @@ class Lattice:
     def stats(self):
         out = (ctypes.c_double * 8)()
         self._ck(self.L.b200lb_stats(self.h, out))
+        return np.array(out[:])
+
+    def step_diag(self):
+        out = (ctypes.c_double * 8)()
+        self._ck(self.L.b200lb_step_diag(self.h, out))
         return np.array(out[:])
 
     def sync(self):

@@ -354,3 +354,43 @@ def test_full_size_properties():
     assert abs(s1[0] - s0[0]) / nint < 1e-14
     assert np.max(np.abs(s1[4:7] - s0[4:7])) / nint < 1e-14
     lat.close()
+
+
+def test_in_sweep_diagnostics():
+    """Option diag: conserved sums gathered inside the collision sweep equal the
+    separate diagnostics pass (and the oracle) on the state that entered the collision."""
+    from oracle import pyoracle
+    for nvel, nlocal, ndist in ((19, (12, 10, 8), 1), (19, (5, 7, 33), 1), (27, (8, 6, 10), 1),
+                                (9, (16, 12, 1), 1), (19, (8, 8, 6), 2)):
+        lat, orc = mk(nvel, nlocal, ndist)
+        f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal, ndist=ndist, ndim=orc.ndim)
+        kw = dict(eta_shear=0.1, eta_bulk=0.1)
+        if ndist == 2:
+            kw = dict(eta_shear=0.00625, eta_bulk=0.00625, mobility=3.75, a=-0.00625,
+                      b=0.00625, kappa=0.004)
+        prm = pyoracle.make_param(**kw)
+        lat.set_param(**kw)
+        lat.set_option("diag", 1)
+        lat.lb_memcpy_h2d(f0)
+        lat.step(3)
+        d = lat.step_diag()                  # state after 2 steps (entered the 3rd collision)
+        f, fp = f0.copy(), np.zeros_like(f0)
+        n = orc.nsite
+        rho, u, frc = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
+        phi, grad, delsq = np.zeros(n), np.zeros((n, 3)), np.zeros(n)
+        orc.step(prm, 2, f, fp, rho, u, frc, phi, grad, delsq)
+        ref = orc.stats(f)
+        nint = float(np.prod(nlocal))
+        assert abs(d[0] - ref[0]) < 1e-13 * nint and abs(d[1] - ref[1]) < 1e-12 * nint
+        assert abs(d[2] - ref[2]) < 1e-13 and abs(d[3] - ref[3]) < 1e-13
+        assert np.max(np.abs(d[4:7] - ref[4:7])) < 1e-13 * nint
+        if ndist == 2:
+            assert abs(d[7] - ref[7]) < 1e-12 * nint
+        # and the result of the steps is unchanged by gathering them
+        lat2, _ = mk(nvel, nlocal, ndist)
+        lat2.set_param(**kw)
+        lat2.lb_memcpy_h2d(f0)
+        lat2.step(3)
+        assert np.array_equal(lat2.lb_memcpy_d2h(), lat.lb_memcpy_d2h())
+        lat.close()
+        lat2.close()
