@@ -1,0 +1,248 @@
+/*
+ * lb_b200.c -- see lb_b200.h. Plain C; every operation forwards to the C ABI of
+ * libb200lb.so. No arithmetic on lattice data happens on the host.
+ */
+
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "lb_b200.h"
+
+static char host_err[512] = "";
+
+static int host_fail(const char * what) {
+  snprintf(host_err, sizeof(host_err), "%s: %s", what, b200lb_last_error());
+  return -1;
+}
+
+const char * lb_b200_error(void) { return host_err; }
+
+#define TRY(call) do { if ((call) != 0) return host_fail(#call); } while (0)
+
+lb_data_options_t lb_data_options_default(void) {
+  /* src/lb_data_options.c: D3Q19, one distribution, M10, LB_HALO_TARGET */
+  lb_data_options_t opts = {3, 19, 1, LB_RELAXATION_M10, LB_HALO_TARGET};
+  return opts;
+}
+
+int lb_data_create(cs_t * cs, physics_t * phys, const lb_data_options_t * opts, lb_t ** plb) {
+
+  b200lb_desc_t d;
+  lb_t * lb = NULL;
+
+  if (cs == NULL || phys == NULL || opts == NULL || plb == NULL) {
+    snprintf(host_err, sizeof(host_err), "lb_data_create: null argument");
+    return -1;
+  }
+  lb = (lb_t *) calloc(1, sizeof(lb_t));
+  if (lb == NULL) return -1;
+
+  memset(&d, 0, sizeof(d));
+  d.ndim = opts->ndim; d.nvel = opts->nvel; d.ndist = opts->ndist;
+  d.nhalo = cs->nhalo;
+  for (int a = 0; a < 3; a++) {
+    d.nlocal[a] = cs->nlocal[a];
+    d.cartsz[a] = cs->mpi_cartsz[a];
+    d.cartcoords[a] = cs->mpi_cartcoords[a];
+    d.periodic[a] = cs->periodic[a];
+    d.nbr_lo[a] = cs->mpi_cart_neighbours[0][a];
+    d.nbr_hi[a] = cs->mpi_cart_neighbours[1][a];
+  }
+  d.rank = cs->mpi_cartrank; d.nranks = cs->nranks;
+  d.device = -1;
+
+  if (b200lb_create(&d, &lb->target) != 0) { free(lb); return host_fail("lb_data_create"); }
+
+  lb->ndim = opts->ndim; lb->nvel = opts->nvel; lb->ndist = opts->ndist;
+  lb->nsite = (int) b200lb_nsite(lb->target);
+  lb->cs = cs; lb->phys = phys;
+  lb->nrelax = opts->nrelax; lb->haloscheme = opts->halo;
+  lb->f = (double *) calloc((size_t) lb->nsite*lb->ndist*lb->nvel, sizeof(double));
+  if (lb->f == NULL) { b200lb_destroy(lb->target); free(lb); return -1; }
+  *plb = lb;
+  return 0;
+}
+
+int lb_free(lb_t * lb) {
+  if (lb == NULL) return 0;
+  b200lb_destroy(lb->target);
+  free(lb->f);
+  free(lb);
+  return 0;
+}
+
+int lb_memcpy(lb_t * lb, tdpMemcpyKind flag) {
+  if (flag == tdpMemcpyHostToDevice) TRY(b200lb_f_upload(lb->target, lb->f, B200LB_HOST_AOS));
+  else TRY(b200lb_f_download(lb->target, lb->f, B200LB_HOST_AOS));
+  return 0;
+}
+
+int lb_collision_relaxation_set(lb_t * lb, lb_relaxation_enum_t nrelax) {
+  lb->nrelax = nrelax;
+  return 0;
+}
+
+/* lb_collide: gathers the parameters the reference commits every step
+ * (src/collision.c:144-163, :1181-1264, :1928-1980) and runs the collision. */
+
+int lb_collide(lb_t * lb, hydro_t * hydro, map_t * map, noise_t * noise, fe_t * fe, visc_t * visc) {
+
+  b200lb_param_t p;
+
+  (void) map; (void) noise; (void) visc;
+  if (hydro == NULL) return 0;               /* src/collision.c:149 */
+
+  memset(&p, 0, sizeof(p));
+  p.rho0 = lb->phys->rho0;
+  p.eta_shear = lb->phys->eta_shear;
+  p.eta_bulk = lb->phys->eta_bulk;
+  for (int a = 0; a < 3; a++) p.force_global[a] = lb->phys->fbody[a];
+  p.nrelax = (int) lb->nrelax;
+  p.mobility = lb->phys->mobility;
+  if (lb->ndist == 2) {
+    fe_symm_t * fs = (fe_symm_t *) fe;     /* src/collision.c:160 */
+    if (fs == NULL) {
+      snprintf(host_err, sizeof(host_err), "lb_collide: ndist = 2 needs the symmetric free energy");
+      return -1;
+    }
+    p.a = fs->param.a; p.b = fs->param.b; p.kappa = fs->param.kappa;
+  }
+  TRY(b200lb_set_param(lb->target, &p));
+  TRY(b200lb_collide(lb->target));
+  return 0;
+}
+
+int lb_halo(lb_t * lb) { return lb_halo_swap(lb, lb->haloscheme); }
+
+int lb_halo_swap(lb_t * lb, lb_halo_enum_t flag) {
+  int scheme = (flag == LB_HALO_OPENMP_REDUCED) ? B200LB_HALO_REDUCED : B200LB_HALO_FULL;
+  TRY(b200lb_halo_swap(lb->target, scheme));
+  return 0;
+}
+
+int lb_propagation(lb_t * lb) {
+  TRY(b200lb_propagate(lb->target));
+  return 0;
+}
+
+/* hydro */
+
+static int field_init(field_t * f, lb_t * lb, int nf, int id) {
+  f->nf = nf; f->nsites = lb->nsite; f->lb = lb; f->id = id;
+  f->data = (double *) calloc((size_t) nf*lb->nsite, sizeof(double));
+  return (f->data == NULL) ? -1 : 0;
+}
+
+int hydro_create(lb_t * lb, hydro_t ** ph) {
+  hydro_t * h = (hydro_t *) calloc(1, sizeof(hydro_t));
+  if (h == NULL) return -1;
+  h->nsite = lb->nsite; h->lb = lb;
+  if (field_init(&h->rho, lb, 1, B200LB_FIELD_RHO) || field_init(&h->u, lb, 3, B200LB_FIELD_U)
+      || field_init(&h->force, lb, 3, B200LB_FIELD_FORCE)) return -1;
+  *ph = h;
+  return 0;
+}
+
+int hydro_free(hydro_t * h) {
+  if (h == NULL) return 0;
+  free(h->rho.data); free(h->u.data); free(h->force.data); free(h);
+  return 0;
+}
+
+static int field_xfer(field_t * f, tdpMemcpyKind flag) {
+  if (flag == tdpMemcpyHostToDevice) TRY(b200lb_field_upload(f->lb->target, f->id, f->data, B200LB_HOST_AOS));
+  else TRY(b200lb_field_download(f->lb->target, f->id, f->data, B200LB_HOST_AOS));
+  return 0;
+}
+
+int hydro_memcpy(hydro_t * h, tdpMemcpyKind flag) {
+  /* src/hydro.c:154-178 copies rho, u, force (eta is not on this path) */
+  if (flag == tdpMemcpyHostToDevice) {
+    if (field_xfer(&h->rho, flag) || field_xfer(&h->u, flag) || field_xfer(&h->force, flag)) return -1;
+    return 0;
+  }
+  if (field_xfer(&h->rho, flag) || field_xfer(&h->u, flag) || field_xfer(&h->force, flag)) return -1;
+  return 0;
+}
+
+int hydro_f_zero(hydro_t * h, const double fzero[3]) {
+  TRY(b200lb_hydro_f_zero(h->lb->target, fzero));
+  return 0;
+}
+
+int hydro_u_zero(hydro_t * h, const double uzero[3]) {
+  TRY(b200lb_hydro_u_zero(h->lb->target, uzero));
+  return 0;
+}
+
+/* order parameter, gradient, free energy */
+
+int field_create(lb_t * lb, const char * name, field_t ** pphi) {
+  field_t * phi = (field_t *) calloc(1, sizeof(field_t));
+  (void) name;
+  if (phi == NULL || field_init(phi, lb, 1, B200LB_FIELD_PHI)) return -1;
+  *pphi = phi;
+  return 0;
+}
+
+int field_free(field_t * phi) { if (phi) { free(phi->data); free(phi); } return 0; }
+int field_memcpy(field_t * phi, tdpMemcpyKind flag) { return field_xfer(phi, flag); }
+
+int field_halo(field_t * phi) {
+  TRY(b200lb_phi_halo(phi->lb->target));
+  return 0;
+}
+
+int phi_lb_to_field(field_t * phi, lb_t * lb) {
+  (void) phi;
+  TRY(b200lb_phi_from_g(lb->target));
+  return 0;
+}
+
+int field_grad_create(field_t * phi, field_grad_t ** pg) {
+  field_grad_t * g = (field_grad_t *) calloc(1, sizeof(field_grad_t));
+  if (g == NULL) return -1;
+  g->field = phi; g->lb = phi->lb;
+  g->grad = (double *) calloc((size_t) 3*phi->nsites, sizeof(double));
+  g->delsq = (double *) calloc((size_t) phi->nsites, sizeof(double));
+  if (g->grad == NULL || g->delsq == NULL) return -1;
+  *pg = g;
+  return 0;
+}
+
+int field_grad_free(field_grad_t * g) { if (g) { free(g->grad); free(g->delsq); free(g); } return 0; }
+
+int field_grad_compute(field_grad_t * g) {
+  /* obj->d2(obj) with d2 = grad_3d_7pt_fluid_d2 (src/field_grad.c:312) */
+  TRY(b200lb_grad7(g->lb->target));
+  return 0;
+}
+
+int field_grad_memcpy(field_grad_t * g, tdpMemcpyKind flag) {
+  if (flag == tdpMemcpyHostToDevice) {
+    TRY(b200lb_field_upload(g->lb->target, B200LB_FIELD_GRAD, g->grad, B200LB_HOST_AOS));
+    TRY(b200lb_field_upload(g->lb->target, B200LB_FIELD_DELSQ, g->delsq, B200LB_HOST_AOS));
+  }
+  else {
+    TRY(b200lb_field_download(g->lb->target, B200LB_FIELD_GRAD, g->grad, B200LB_HOST_AOS));
+    TRY(b200lb_field_download(g->lb->target, B200LB_FIELD_DELSQ, g->delsq, B200LB_HOST_AOS));
+  }
+  return 0;
+}
+
+int fe_symm_create(field_t * phi, field_grad_t * dphi, fe_symm_t ** pfe) {
+  fe_symm_t * fe = (fe_symm_t *) calloc(1, sizeof(fe_symm_t));
+  if (fe == NULL) return -1;
+  fe->phi = phi; fe->dphi = dphi;
+  *pfe = fe;
+  return 0;
+}
+
+int fe_symm_free(fe_symm_t * fe) { free(fe); return 0; }
+int fe_symm_param_set(fe_symm_t * fe, fe_symm_param_t values) { fe->param = values; return 0; }
+
+int stats_distribution_sums(lb_t * lb, double sums[8]) {
+  TRY(b200lb_stats(lb->target, sums));
+  return 0;
+}

@@ -1,0 +1,135 @@
+/*
+ * lb_b200.h -- host-side C mirror of the reference call surface for the LB hot path,
+ * implemented entirely on top of the C ABI (include/b200lb.h -> libb200lb.so).
+ *
+ * Host code stays in C, as in the reference (zazu29/ludwig v0.20.1). The names,
+ * argument meaning, return convention (0 = success) and the host array layouts are
+ * those of the reference, so code written against
+ *   lb_collide            src/collision.h:27       lb_propagation  src/propagation.h:21
+ *   lb_halo, lb_halo_swap src/lb_data.h:159-160    lb_memcpy       src/lb_data.h:156
+ *   hydro_f_zero/u_zero   src/hydro.h:64-65        hydro_memcpy    src/hydro.h:56
+ *   phi_lb_to_field       src/phi_lb_coupler.h:22  field_halo      src/field.h:97
+ *   field_grad_compute    src/field_grad.h:49      field_memcpy, field_grad_memcpy
+ * reads the same here. The objects are slim: they hold the host arrays (the
+ * interchange format, LB_ADDR / addr_rank1 AOS, src/memory.h:124-130) and share ONE
+ * device handle; everything outside the hot path (pe_t, io, colloids ...) is absent.
+ * Where the reference pulls state from the physics_ref() singleton, this mirror takes
+ * a physics_t argument at creation. Failures: the reference aborts through pe_fatal;
+ * here every function returns non-zero and lb_b200_error() gives the message.
+ */
+
+#ifndef LUDWIG_LB_B200_H
+#define LUDWIG_LB_B200_H
+
+#include "../../include/b200lb.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum tdpMemcpyKind_enum { tdpMemcpyHostToDevice = 1, tdpMemcpyDeviceToHost = 2 } tdpMemcpyKind;
+
+typedef enum lb_relaxation_enum { LB_RELAXATION_M10, LB_RELAXATION_BGK, LB_RELAXATION_TRT } lb_relaxation_enum_t;
+typedef enum lb_halo_enum { LB_HALO_TARGET, LB_HALO_OPENMP_FULL, LB_HALO_OPENMP_REDUCED } lb_halo_enum_t;
+
+/* the part of cs_t the path needs (src/coords.h:30-63) */
+typedef struct cs_s {
+  int ntotal[3];
+  int nlocal[3];
+  int nhalo;                 /* 1 */
+  int mpi_cartsz[3];
+  int mpi_cartcoords[3];
+  int periodic[3];
+  int mpi_cart_neighbours[2][3];   /* [CS_BACKWARD/CS_FORWARD][X,Y,Z] */
+  int mpi_cartrank;
+  int nranks;
+} cs_t;
+
+/* what lb_collide reads from physics_ref() (src/collision.c:1197-1205, :1945-1973) */
+typedef struct physics_s {
+  double rho0;
+  double eta_shear;
+  double eta_bulk;
+  double fbody[3];
+  double mobility;
+} physics_t;
+
+typedef struct lb_data_options_s {
+  int ndim;
+  int nvel;
+  int ndist;
+  lb_relaxation_enum_t nrelax;
+  lb_halo_enum_t halo;
+} lb_data_options_t;
+
+typedef struct fe_symm_param_s { double a, b, kappa, c, h; } fe_symm_param_t;
+
+typedef struct lb_data_s {
+  int ndim, nvel, ndist, nsite;
+  cs_t * cs;
+  double * f;                      /* host distributions, LB_ADDR(nsite,ndist,nvel,index,n,p) */
+  lb_relaxation_enum_t nrelax;
+  lb_halo_enum_t haloscheme;
+  physics_t * phys;                /* stands in for physics_ref() */
+  b200lb_t * target;               /* the device side (reference: lb->target) */
+} lb_t;
+
+typedef struct field_s { int nf; int nsites; double * data; lb_t * lb; int id; } field_t;
+
+typedef struct hydro_s {
+  int nsite;
+  field_t rho, u, force;           /* host copies, addr_rank1(nsite, nf, index, ia) */
+  lb_t * lb;
+} hydro_t;
+
+typedef struct field_grad_s { field_t * field; double * grad; double * delsq; lb_t * lb; } field_grad_t;
+
+typedef struct fe_symm_s { fe_symm_param_t param; field_t * phi; field_grad_t * dphi; } fe_symm_t;
+
+typedef void map_t;     /* configs are all-fluid: not consulted */
+typedef void noise_t;   /* isothermal fluctuations off */
+typedef void visc_t;    /* no viscosity model */
+typedef void fe_t;
+
+const char * lb_b200_error(void);
+
+lb_data_options_t lb_data_options_default(void);
+int lb_data_create(cs_t * cs, physics_t * phys, const lb_data_options_t * opts, lb_t ** lb);
+int lb_free(lb_t * lb);
+int lb_memcpy(lb_t * lb, tdpMemcpyKind flag);
+int lb_collision_relaxation_set(lb_t * lb, lb_relaxation_enum_t nrelax);
+
+int lb_collide(lb_t * lb, hydro_t * hydro, map_t * map, noise_t * noise, fe_t * fe, visc_t * visc);
+int lb_halo(lb_t * lb);
+int lb_halo_swap(lb_t * lb, lb_halo_enum_t flag);
+int lb_propagation(lb_t * lb);
+
+int hydro_create(lb_t * lb, hydro_t ** hydro);
+int hydro_free(hydro_t * hydro);
+int hydro_memcpy(hydro_t * hydro, tdpMemcpyKind flag);
+int hydro_f_zero(hydro_t * hydro, const double fzero[3]);
+int hydro_u_zero(hydro_t * hydro, const double uzero[3]);
+
+int field_create(lb_t * lb, const char * name, field_t ** phi);      /* the order parameter */
+int field_free(field_t * phi);
+int field_memcpy(field_t * phi, tdpMemcpyKind flag);
+int field_halo(field_t * phi);
+int phi_lb_to_field(field_t * phi, lb_t * lb);
+
+int field_grad_create(field_t * phi, field_grad_t ** grad);           /* d2 = grad_3d_7pt_fluid_d2 */
+int field_grad_free(field_grad_t * grad);
+int field_grad_compute(field_grad_t * grad);
+int field_grad_memcpy(field_grad_t * grad, tdpMemcpyKind flag);
+
+int fe_symm_create(field_t * phi, field_grad_t * dphi, fe_symm_t ** fe);
+int fe_symm_free(fe_symm_t * fe);
+int fe_symm_param_set(fe_symm_t * fe, fe_symm_param_t values);
+
+/* stats_distribution_print / stats_distribution_momentum sums (src/stats_distribution.c) */
+int stats_distribution_sums(lb_t * lb, double sums[8]);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif

@@ -1,0 +1,213 @@
+/*
+ * test_host_shim.c -- C test of the host-side mirror (ludwig_b200/host/lb_b200.h),
+ * written the way the reference's own unit tests are (tests/unit/test_prop.c:81-262,
+ * tests/unit/test_model.c): real objects on a periodic box, no mocks.
+ *
+ *   1. do_test_velocity            every site keeps its own p after halo + propagation
+ *   2. do_test_source_destination  f = global site id lands at r + c_p (periodic)
+ *   3. the src/ludwig.c:530-862 loop through lb_collide / lb_halo / lb_propagation
+ *      against the CPU oracle (oracle/lb_oracle.h), single fluid and binary, 1e-12
+ *
+ * Build and run: see tests/test_host_shim.py. Exit code 0 = pass.
+ */
+
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "../../ludwig_b200/host/lb_b200.h"
+#include "../../oracle/lb_oracle.h"
+
+static int nfail = 0;
+#define CHECK(cond, msg) do { if (!(cond)) { printf("FAIL %s:%d %s\n", __FILE__, __LINE__, msg); nfail++; } } while (0)
+#define OK(call) do { if ((call) != 0) { printf("ERROR %s:%d %s -> %s\n", __FILE__, __LINE__, #call, lb_b200_error()); exit(2); } } while (0)
+
+static void cs_serial(cs_t * cs, int nx, int ny, int nz) {
+  memset(cs, 0, sizeof(cs_t));
+  cs->ntotal[0] = cs->nlocal[0] = nx;
+  cs->ntotal[1] = cs->nlocal[1] = ny;
+  cs->ntotal[2] = cs->nlocal[2] = nz;
+  cs->nhalo = 1;
+  for (int a = 0; a < 3; a++) { cs->mpi_cartsz[a] = 1; cs->periodic[a] = 1; }
+  cs->nranks = 1;
+}
+
+static long cs_index(const cs_t * cs, int ic, int jc, int kc) {   /* src/coords.c:617-631, nhalo = 1 */
+  return ((long) ic*(cs->nlocal[1] + 2) + jc)*(cs->nlocal[2] + 2) + kc;
+}
+
+#define LB_ADDR(nsite, ndist, nvel, index, n, p) (((long) (index)*(ndist) + (n))*(nvel) + (p))
+
+static void test_prop(int ndist, lb_halo_enum_t halo) {
+  cs_t cs;
+  physics_t phys = {1.0, 0.1, 0.1, {0.0, 0.0, 0.0}, 0.0};
+  lb_data_options_t opts = lb_data_options_default();
+  lb_t * lb = NULL;
+  orc_model_t model;
+  const int nx = 8, ny = 6, nz = 10;
+
+  cs_serial(&cs, nx, ny, nz);
+  opts.ndist = ndist; opts.halo = halo;
+  OK(lb_data_create(&cs, &phys, &opts, &lb));
+  orc_model_init(lb->nvel, &model);
+
+  /* do_test_velocity */
+  for (int ic = 1; ic <= nx; ic++) for (int jc = 1; jc <= ny; jc++) for (int kc = 1; kc <= nz; kc++) {
+    long index = cs_index(&cs, ic, jc, kc);
+    for (int n = 0; n < ndist; n++) for (int p = 0; p < lb->nvel; p++)
+      lb->f[LB_ADDR(lb->nsite, ndist, lb->nvel, index, n, p)] = 1.0*(p + n*lb->nvel);
+  }
+  OK(lb_memcpy(lb, tdpMemcpyHostToDevice));
+  OK(lb_halo(lb));
+  OK(lb_propagation(lb));
+  OK(lb_memcpy(lb, tdpMemcpyDeviceToHost));
+  for (int ic = 1; ic <= nx; ic++) for (int jc = 1; jc <= ny; jc++) for (int kc = 1; kc <= nz; kc++) {
+    long index = cs_index(&cs, ic, jc, kc);
+    for (int n = 0; n < ndist; n++) for (int p = 0; p < lb->nvel; p++)
+      CHECK(lb->f[LB_ADDR(lb->nsite, ndist, lb->nvel, index, n, p)] == 1.0*(p + n*lb->nvel), "velocity mixing");
+  }
+
+  /* do_test_source_destination */
+  for (int ic = 1; ic <= nx; ic++) for (int jc = 1; jc <= ny; jc++) for (int kc = 1; kc <= nz; kc++) {
+    long index = cs_index(&cs, ic, jc, kc);
+    double id = (double) (((ic - 1)*ny + (jc - 1))*nz + (kc - 1));
+    for (int n = 0; n < ndist; n++) for (int p = 0; p < lb->nvel; p++)
+      lb->f[LB_ADDR(lb->nsite, ndist, lb->nvel, index, n, p)] = id;
+  }
+  OK(lb_memcpy(lb, tdpMemcpyHostToDevice));
+  OK(lb_halo(lb));
+  OK(lb_propagation(lb));
+  OK(lb_memcpy(lb, tdpMemcpyDeviceToHost));
+  for (int ic = 1; ic <= nx; ic++) for (int jc = 1; jc <= ny; jc++) for (int kc = 1; kc <= nz; kc++) {
+    long index = cs_index(&cs, ic, jc, kc);
+    for (int n = 0; n < ndist; n++) for (int p = 0; p < lb->nvel; p++) {
+      int is = (ic - 1 - model.cv[p][0] + nx) % nx;
+      int js = (jc - 1 - model.cv[p][1] + ny) % ny;
+      int ks = (kc - 1 - model.cv[p][2] + nz) % nz;
+      double id = (double) ((is*ny + js)*nz + ks);
+      CHECK(lb->f[LB_ADDR(lb->nsite, ndist, lb->nvel, index, n, p)] == id, "source-destination");
+    }
+  }
+  lb_free(lb);
+  printf("test_prop ndist %d halo %d done\n", ndist, (int) halo);
+}
+
+static double urand(unsigned long * s) {
+  *s = *s*6364136223846793005UL + 1442695040888963407UL;
+  return (double) ((*s >> 11) & 0xFFFFFFFFFFFFFUL)/4503599627370496.0 - 0.5;
+}
+
+static void test_loop(int ndist, int nsteps) {
+  cs_t cs;
+  physics_t phys = {1.0, 0.1, 0.1, {0.0, 0.0, 0.0}, 0.0};
+  lb_data_options_t opts = lb_data_options_default();
+  lb_t * lb = NULL; hydro_t * hydro = NULL;
+  field_t * phi = NULL; field_grad_t * dphi = NULL; fe_symm_t * fe = NULL;
+  orc_model_t model; orc_box_t box; orc_param_t prm;
+  const int nl[3] = {10, 8, 6};
+  const double zero[3] = {0.0, 0.0, 0.0};
+  unsigned long seed = 8361235;
+
+  cs_serial(&cs, nl[0], nl[1], nl[2]);
+  opts.ndist = ndist;
+  if (ndist == 2) { phys.eta_shear = phys.eta_bulk = 0.00625; phys.mobility = 3.75; }
+  OK(lb_data_create(&cs, &phys, &opts, &lb));
+  OK(hydro_create(lb, &hydro));
+  if (ndist == 2) {
+    fe_symm_param_t fp = {-0.00625, 0.00625, 0.004, 0.0, 0.0};
+    OK(field_create(lb, "phi", &phi));
+    OK(field_grad_create(phi, &dphi));
+    OK(fe_symm_create(phi, dphi, &fe));
+    OK(fe_symm_param_set(fe, fp));
+  }
+  orc_model_init(lb->nvel, &model);
+  orc_box_init(nl, &box);
+  memset(&prm, 0, sizeof(prm));
+  prm.rho0 = phys.rho0; prm.eta_shear = phys.eta_shear; prm.eta_bulk = phys.eta_bulk;
+  prm.mobility = phys.mobility; prm.a = -0.00625; prm.b = 0.00625; prm.kappa = 0.004;
+
+  size_t nf = (size_t) lb->nsite*ndist*lb->nvel;
+  double * f = (double *) calloc(nf, sizeof(double));
+  double * fprime = (double *) calloc(nf, sizeof(double));
+  double * rho = (double *) calloc(lb->nsite, sizeof(double));
+  double * u = (double *) calloc(3*(size_t) lb->nsite, sizeof(double));
+  double * force = (double *) calloc(3*(size_t) lb->nsite, sizeof(double));
+  double * ph = (double *) calloc(lb->nsite, sizeof(double));
+  double * gr = (double *) calloc(3*(size_t) lb->nsite, sizeof(double));
+  double * dsq = (double *) calloc(lb->nsite, sizeof(double));
+
+  for (int ic = 1; ic <= nl[0]; ic++) for (int jc = 1; jc <= nl[1]; jc++) for (int kc = 1; kc <= nl[2]; kc++) {
+    long index = cs_index(&cs, ic, jc, kc);
+    double r = 1.0 + 0.02*urand(&seed);
+    double uu[3] = {0.02*urand(&seed), 0.02*urand(&seed), 0.02*urand(&seed)};
+    orc_equilib_set(&model, ndist, f, index, r, uu);
+    if (ndist == 2) {
+      double p0 = urand(&seed);
+      for (int p = 0; p < lb->nvel; p++) f[LB_ADDR(lb->nsite, 2, lb->nvel, index, 1, p)] = (p == 0) ? p0 : 0.001*model.wv[p]*urand(&seed);
+    }
+  }
+  memcpy(lb->f, f, nf*sizeof(double));
+  OK(lb_memcpy(lb, tdpMemcpyHostToDevice));
+
+  /* the loop of src/ludwig.c:530-862 through the mirrored call surface */
+  for (int n = 0; n < nsteps; n++) {
+    OK(hydro_f_zero(hydro, zero));
+    if (ndist == 2) {
+      OK(phi_lb_to_field(phi, lb));
+      OK(field_halo(phi));
+      OK(field_grad_compute(dphi));
+    }
+    OK(hydro_u_zero(hydro, zero));
+    OK(lb_collide(lb, hydro, NULL, NULL, (fe_t *) fe, NULL));
+    OK(lb_halo(lb));
+    OK(lb_propagation(lb));
+  }
+  OK(lb_memcpy(lb, tdpMemcpyDeviceToHost));
+  OK(hydro_memcpy(hydro, tdpMemcpyDeviceToHost));
+
+  orc_step(&model, &box, &prm, ndist, nsteps, f, fprime, rho, u, force, ph, gr, dsq);
+
+  double emax = 0.0, fmax = 0.0, umax = 0.0, mass0 = 0.0, mass1 = 0.0;
+  for (int ic = 1; ic <= nl[0]; ic++) for (int jc = 1; jc <= nl[1]; jc++) for (int kc = 1; kc <= nl[2]; kc++) {
+    long index = cs_index(&cs, ic, jc, kc);
+    for (int n = 0; n < ndist; n++) for (int p = 0; p < lb->nvel; p++) {
+      long i = LB_ADDR(lb->nsite, ndist, lb->nvel, index, n, p);
+      if (fabs(lb->f[i] - f[i]) > emax) emax = fabs(lb->f[i] - f[i]);
+      if (fabs(f[i]) > fmax) fmax = fabs(f[i]);
+      if (n == 0) { mass0 += f[i]; mass1 += lb->f[i]; }
+    }
+    for (int a = 0; a < 3; a++) {
+      double d = fabs(hydro->u.data[3*index + a] - u[3*index + a]);
+      if (d > umax) umax = d;
+    }
+  }
+  printf("test_loop ndist %d: %d steps, max|df|/max|f| = %.3e, max|du| = %.3e, mass diff %.3e\n",
+	 ndist, nsteps, emax/fmax, umax, fabs(mass1 - mass0));
+  CHECK(emax/fmax < 1.0e-12, "time loop vs oracle");
+  CHECK(umax < 1.0e-12, "hydro u vs oracle");
+  CHECK(fabs(mass1 - mass0) < 1.0e-10, "mass");
+  {
+    double sums[8];
+    OK(stats_distribution_sums(lb, sums));
+    CHECK(fabs(sums[0] - mass1) < 1.0e-9, "device mass sum");
+  }
+
+  free(f); free(fprime); free(rho); free(u); free(force); free(ph); free(gr); free(dsq);
+  if (fe) fe_symm_free(fe);
+  if (dphi) field_grad_free(dphi);
+  if (phi) field_free(phi);
+  hydro_free(hydro);
+  lb_free(lb);
+}
+
+int main(void) {
+  test_prop(1, LB_HALO_TARGET);
+  test_prop(2, LB_HALO_TARGET);
+  test_prop(1, LB_HALO_OPENMP_REDUCED);
+  test_loop(1, 7);
+  test_loop(2, 7);
+  if (nfail) { printf("%d check(s) FAILED\n", nfail); return 1; }
+  printf("host shim: all passed\n");
+  return 0;
+}
