@@ -109,7 +109,9 @@ struct b200lb_s {
   double fconst[3];
   bool u_fill_pending;       // hydro_u_zero recorded but not yet applied
   double uconst[3];
-  bool hydro_stale;          // collision ran without storing rho,u
+  bool hydro_stale;          // collision ran without storing rho,u (recoverable from lat[cur], see ensure_hydro)
+  bool last_ffield;          // the last collision read the per-site force field
+  double last_fg[3];         // ... and this uniform part
   int  selfper[3];           // device axis is periodic within this rank (one rank in that direction)
   bool halo_deferred;        // lb_halo was called; self-periodic planes not yet copied (pulls wrap)
   int  halo_deferred_scheme;
@@ -120,7 +122,7 @@ struct b200lb_s {
   bool ghost;
 
   // options
-  int opt_fused, opt_halo, opt_hydro_write, opt_vec, opt_block, opt_halo_lazy, opt_overlap, opt_direct, opt_diag;
+  int opt_fused, opt_halo, opt_hydro_write, opt_vec, opt_block, opt_halo_lazy, opt_overlap, opt_direct, opt_diag, opt_loopback;
 
   cudaStream_t s_main, s_x[2];
   cudaStream_t s_comm;       // halo exchange of decomposed directions (overlaps the interior sweep)
@@ -149,6 +151,26 @@ struct b200lb_s {
   i64 pack_max, unpack_max;
   double * dsend, * drecv;
 };
+
+// A direction whose halo planes travel through send/receive buffers: decomposed over
+// ranks, or (option "loopback", for testing and profiling the multi-rank machinery on
+// one GPU) periodic within the rank with this rank as its own neighbour.
+static bool decomposed(const b200lb_s * h, int d) {
+  const int a = h->ops->dax[d];
+  if (h->L.h[d] == 0) return false;
+  if (h->desc.cartsz[a] > 1) return true;
+  return h->opt_loopback && h->desc.periodic[a];
+}
+
+static bool have_comm(const b200lb_s * h) { return h->comm != nullptr || h->opt_loopback; }
+
+static void update_selfper(b200lb_s * h) {
+  for (int d = 0; d < 3; d++) {
+    const int a = h->ops->dax[d];
+    h->selfper[d] = (h->L.h[d] == 1 && h->desc.cartsz[a] == 1 && h->desc.periodic[a]
+		     && !h->opt_loopback) ? 1 : 0;
+  }
+}
 
 static int site_kparams(b200lb_s * h, KParams & P) {
   memset(&P, 0, sizeof(P));
@@ -244,10 +266,7 @@ extern "C" int b200lb_create(const b200lb_desc_t * desc, b200lb_t ** out) {
     L.h[d] = (ops->ndim == 2 && a == 2) ? 0 : 1;
     L.na[d] = L.n[d] + 2*L.h[d];
   }
-  for (int d = 0; d < 3; d++) {
-    const int a = ops->dax[d];
-    h->selfper[d] = (L.h[d] == 1 && desc->cartsz[a] == 1 && desc->periodic[a]) ? 1 : 0;
-  }
+  update_selfper(h);
   L.z0 = zalign - L.h[2];
   {
     i64 row = L.z0 + L.na[2];
@@ -307,7 +326,7 @@ extern "C" int b200lb_create(const b200lb_desc_t * desc, b200lb_t ** out) {
   h->opt_fused = 1;
   h->opt_halo = B200LB_HALO_FULL;
   h->opt_hydro_write = 1;
-  h->opt_vec = 2;
+  h->opt_vec = (desc->nvel == 27) ? 1 : 2;   // D3Q27: 27 live populations per site, one site per thread is faster (measured)
   h->opt_block = 128;
   h->opt_halo_lazy = 1;
   h->opt_overlap = 1;
@@ -353,6 +372,8 @@ extern "C" int b200lb_destroy(b200lb_t * h) {
 extern "C" long b200lb_nsite(const b200lb_t * h) { return h ? h->nsite_host : 0; }
 
 static int materialise(b200lb_s * h);
+static int join_comm(b200lb_s * h);
+static int flush_halo(b200lb_s * h);
 
 extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
   if (!h || !name) return fail("null argument");
@@ -370,6 +391,20 @@ extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
   if (!strcmp(name, "overlap")) { h->opt_overlap = (v != 0); return 0; }
   if (!strcmp(name, "direct")) { h->opt_direct = (v != 0); return 0; }
   if (!strcmp(name, "diag")) { h->opt_diag = (v != 0); return 0; }
+  if (!strcmp(name, "loopback")) {
+    if (h->desc.nranks > 1 && v) return fail("loopback is for single-rank lattices");
+    if (join_comm(h)) return -1;
+    if (flush_halo(h)) return -1;
+    h->opt_loopback = (v != 0);
+    update_selfper(h);
+    // message tables depend on which directions are exchanged
+    CU(cudaStreamSynchronize(h->s_main));
+    CU(cudaStreamSynchronize(h->s_comm));
+    cudaFree(h->msg_pack); cudaFree(h->msg_unpack); cudaFree(h->dsend); cudaFree(h->drecv);
+    h->msg_pack = h->msg_unpack = nullptr; h->dsend = h->drecv = nullptr;
+    h->direct_state = 0;
+    return 0;
+  }
   if (!strcmp(name, "vec")) {
     if (v != 1 && v != 2) return fail("vec must be 1 or 2");
     h->opt_vec = (int) v; return 0;
@@ -390,6 +425,7 @@ extern "C" long b200lb_get_option(const b200lb_t * h, const char * name) {
   if (!strcmp(name, "overlap")) return h->opt_overlap;
   if (!strcmp(name, "direct")) return h->opt_direct;
   if (!strcmp(name, "diag")) return h->opt_diag;
+  if (!strcmp(name, "loopback")) return h->opt_loopback;
   if (!strcmp(name, "direct_state")) return h->direct_state;
   if (!strcmp(name, "halo_deferred")) return h->halo_deferred;
   if (!strcmp(name, "vec")) return h->opt_vec;
@@ -433,16 +469,14 @@ static int split_boxes(const b200lb_s * h, int lo[7][3], int hi[7][3]) {
   int nb = 0;
   bool any = false;
   for (int d = 0; d < 3; d++) {
-    const int a = h->ops->dax[d];
-    if (L.h[d] == 0 || h->desc.cartsz[a] == 1) continue;
+    if (!decomposed(h, d)) continue;
     const int t = (d == 2) ? ((L.n[2] >= 64) ? 16 : 2) : 1;
     if (L.n[d] < 3*t + 1 || (d == 2 && (L.n[2] & 1))) return 1;
     any = true;
   }
-  if (!any || !h->comm || !h->opt_overlap) return 1;
+  if (!any || !have_comm(h) || !h->opt_overlap) return 1;
   for (int d = 0; d < 3; d++) {
-    const int a = h->ops->dax[d];
-    if (L.h[d] == 0 || h->desc.cartsz[a] == 1) continue;
+    if (!decomposed(h, d)) continue;
     const int t = (d == 2) ? ((L.n[2] >= 64) ? 16 : 2) : 1;
     for (int side = 0; side < 2; side++) {
       for (int e = 0; e < 3; e++) { lo[nb][e] = ilo[e]; hi[nb][e] = ihi[e]; }
@@ -471,6 +505,8 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
   if (collide) {
     for (int i = 0; i < 3; i++) a.P.fg[i] = h->prm.force_global[i] + (h->force_uniform ? h->fconst[i] : 0.0);
     a.P.force = h->force_uniform ? nullptr : h->force;
+    h->last_ffield = !h->force_uniform;
+    for (int i = 0; i < 3; i++) h->last_fg[i] = a.P.fg[i];
     if (h->opt_hydro_write) { a.P.rho = h->rho; a.P.u = h->u; }
     a.P.phi = h->phi; a.P.grad = h->grad; a.P.delsq = h->delsq;
   }
@@ -506,9 +542,23 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
   return 0;
 }
 
+// rho,u that the last collision did not store: recompute them from its
+// post-collision populations, which must still be unstreamed in lat[cur]
+static int ensure_hydro(b200lb_s * h) {
+  if (!h->hydro_stale) return 0;
+  if (join_comm(h)) return -1;
+  CU(h->ops->hydro(h->L, h->lat[h->cur], h->desc.ndist, h->last_ffield ? h->force : nullptr,
+		   h->last_fg, h->rho, h->u, h->s_main));
+  h->launches++;
+  h->hydro_stale = false;
+  h->u_fill_pending = false;
+  return 0;
+}
+
 // apply a deferred propagation so that lat[cur] is the streamed lattice
 static int materialise(b200lb_s * h) {
   if (!h->prop_pending) return 0;
+  if (ensure_hydro(h)) return -1;       // last chance: streaming scatters f*
   if (run_sweep(h, true, false, h->lat[h->cur], h->lat[1 - h->cur])) return -1;
   h->cur = 1 - h->cur;
   h->prop_pending = false;
@@ -536,6 +586,7 @@ extern "C" int b200lb_propagate(b200lb_t * h) {
     h->prop_pending = true;
     return 0;
   }
+  if (ensure_hydro(h)) return -1;
   if (run_sweep(h, true, false, h->lat[h->cur], h->lat[1 - h->cur])) return -1;
   h->cur = 1 - h->cur;
   return 0;
@@ -610,14 +661,14 @@ static int halo_exchange(b200lb_s * h, double * data, bool lattice, int nplane, 
     memset(&H, 0, sizeof(H));
     H.L = h->L; H.data = data; H.axis = d;
     halo_lists(h, d, scheme, nplane, lattice, H);
-    if (h->desc.cartsz[a] == 1) {
+    if (!decomposed(h, d)) {
       if (!h->desc.periodic[a]) continue;        // physical boundary: nothing to receive
       if (which == 1) continue;
       if (halo_launch(h, HALO_LOCAL, H, st)) return -1;
       continue;
     }
     if (which == 2) continue;
-    if (!h->comm) return fail("direction %d is decomposed over %d ranks but b200lb_comm_init was not called", a, h->desc.cartsz[a]);
+    if (!have_comm(h)) return fail("direction %d is decomposed over %d ranks but b200lb_comm_init was not called", a, h->desc.cartsz[a]);
     if (halo_buffers(h, d, nplane)) return -1;
     HaloBuf & b = h->hb[d];
     H.to_lo = b.to_lo; H.to_hi = b.to_hi; H.from_lo = b.from_lo; H.from_hi = b.from_hi;
@@ -625,12 +676,19 @@ static int halo_exchange(b200lb_s * h, double * data, bool lattice, int nplane, 
     const int lo = h->desc.nbr_lo[a], hi = h->desc.nbr_hi[a];
     // Order matters when lo == hi (two ranks, periodic): the peer's first
     // message is its low face, which is my HIGH halo.
+    if (h->desc.cartsz[a] == 1) {
+      // loopback: this rank is its own neighbour on both sides
+      CU(cudaMemcpyAsync(b.from_lo, b.to_hi, sizeof(double)*H.nlo*b.nface, cudaMemcpyDeviceToDevice, st));
+      CU(cudaMemcpyAsync(b.from_hi, b.to_lo, sizeof(double)*H.nhi*b.nface, cudaMemcpyDeviceToDevice, st));
+    }
+    else {
     NC(g_nccl.GroupStart());
     if (lo >= 0) NC(g_nccl.Send(b.to_lo, (size_t) H.nhi*b.nface, ncclDouble, lo, h->comm, st));
     if (hi >= 0) NC(g_nccl.Send(b.to_hi, (size_t) H.nlo*b.nface, ncclDouble, hi, h->comm, st));
     if (hi >= 0) NC(g_nccl.Recv(b.from_hi, (size_t) H.nhi*b.nface, ncclDouble, hi, h->comm, st));
     if (lo >= 0) NC(g_nccl.Recv(b.from_lo, (size_t) H.nlo*b.nface, ncclDouble, lo, h->comm, st));
     NC(g_nccl.GroupEnd());
+    }
     // a missing neighbour (non-periodic edge) leaves that halo untouched
     if (lo < 0) H.nlo = 0;
     if (hi < 0) H.nhi = 0;
@@ -682,7 +740,7 @@ static int direct_setup(b200lb_s * h) {
 	int pdir[3] = {0, 0, 0}, mdir[3] = {0, 0, 0};  // physical axes
 	for (int d = 0; d < 3; d++) {
 	  const int a = h->ops->dax[d];
-	  if (dir[d] != 0 && (L.h[d] == 0 || h->desc.cartsz[a] == 1)) ok = false;
+	  if (dir[d] != 0 && !decomposed(h, d)) ok = false;
 	  pdir[a] = dir[d]; mdir[a] = -dir[d];
 	}
 	if (!ok) continue;
@@ -748,6 +806,15 @@ static int direct_exchange(b200lb_s * h, double * data, cudaStream_t st) {
   // Sends and receives are listed in the same direction order on every rank, so
   // several messages between the same pair of ranks (2 ranks in a periodic
   // direction) match up in order.
+  if (!h->comm) {
+    // loopback: every message goes to this rank itself; pack and unpack tables list
+    // the same directions in the same order, so one copy moves them all
+    i64 total = 0;
+    for (int i = 0; i < h->npack; i++) total += h->pack_cnt[i];
+    if (h->npack != h->nunpack) return fail("internal: loopback message tables differ");
+    CU(cudaMemcpyAsync(h->drecv, h->dsend, sizeof(double)*total, cudaMemcpyDeviceToDevice, st));
+  }
+  else {
   NC(g_nccl.GroupStart());
   for (int i = 0; i < h->npack; i++) {
     NC(g_nccl.Send(h->dsend + h->pack_off[i], (size_t) h->pack_cnt[i], ncclDouble, h->pack_peer[i], h->comm, st));
@@ -756,6 +823,7 @@ static int direct_exchange(b200lb_s * h, double * data, cudaStream_t st) {
     NC(g_nccl.Recv(h->drecv + h->unpack_off[i], (size_t) h->unpack_cnt[i], ncclDouble, h->unpack_peer[i], h->comm, st));
   }
   NC(g_nccl.GroupEnd());
+  }
   if (h->nunpack > 0) {
     unsigned gx = (unsigned) ((h->unpack_max + 255)/256);
     if (gx > 1024) gx = 1024;
@@ -768,7 +836,7 @@ static int direct_exchange(b200lb_s * h, double * data, cudaStream_t st) {
 
 // the decomposed directions of the current lattice, by the cheapest valid route
 static int lattice_exchange(b200lb_s * h, int scheme, cudaStream_t st) {
-  if (scheme == B200LB_HALO_REDUCED && h->comm && h->opt_direct) {
+  if (scheme == B200LB_HALO_REDUCED && have_comm(h) && h->opt_direct) {
     if (direct_setup(h)) return -1;
     if (h->direct_state == 1) return direct_exchange(h, h->lat[h->cur], st);
   }
@@ -787,7 +855,7 @@ static int lattice_halo(b200lb_s * h, int scheme) {
     if (join_comm(h)) return -1;
     return halo_exchange(h, h->lat[h->cur], true, h->nplane, scheme, 0, h->s_main);
   }
-  if (h->comm && h->opt_overlap) {
+  if (have_comm(h) && h->opt_overlap) {
     // The exchange runs on its own stream behind the boundary slabs of the sweep
     // that produced this lattice, next to that sweep's interior launch. s_main
     // joins it again before the next operation on the lattice (join_comm).
@@ -873,6 +941,7 @@ extern "C" int b200lb_hydro_f_zero(b200lb_t * h, const double f[3]) {
   if (!h) return fail("null handle");
   // The whole field takes one value: remember it instead of sweeping 24 B/site
   // (src/hydro.c:306 fills all nsite every step). Materialised on demand.
+  if (h->hydro_stale && h->last_ffield) { if (ensure_hydro(h)) return -1; }
   for (int i = 0; i < 3; i++) h->fconst[i] = f ? f[i] : 0.0;
   h->force_uniform = true;
   return 0;
@@ -1033,6 +1102,7 @@ static int transfer(b200lb_s * h, double * dev, int nel, double * host, int layo
 
 extern "C" int b200lb_f_upload(b200lb_t * h, const double * f, int layout) {
   if (!h || !f) return fail("null argument");
+  if (ensure_hydro(h)) return -1;   // hydro of the state being replaced stays available
   h->prop_pending = false;          // the host copy replaces whatever was in flight
   h->halo_deferred = false;
   return transfer(h, h->lat[h->cur], h->nplane, const_cast<double *>(f), layout, true);
@@ -1067,7 +1137,11 @@ extern "C" int b200lb_field_upload(b200lb_t * h, int field, const double * host,
   if (!h || !host) return fail("null argument");
   double * dev; int nf;
   if (field_info(h, field, &dev, &nf)) return -1;
-  if (field == B200LB_FIELD_FORCE) h->force_uniform = false;
+  if (field == B200LB_FIELD_FORCE) {
+    if (h->hydro_stale && h->last_ffield) { if (ensure_hydro(h)) return -1; }
+    h->force_uniform = false;
+  }
+  if ((field == B200LB_FIELD_U || field == B200LB_FIELD_RHO) && h->hydro_stale) h->hydro_stale = false;
   if (field == B200LB_FIELD_U) h->u_fill_pending = false;
   return transfer(h, dev, nf, const_cast<double *>(host), layout, true);
 }
@@ -1084,7 +1158,7 @@ extern "C" int b200lb_field_download(b200lb_t * h, int field, double * host, int
     h->u_fill_pending = false;
   }
   if ((field == B200LB_FIELD_U || field == B200LB_FIELD_RHO) && h->hydro_stale) {
-    return fail("rho/u were not stored by the last collision (option hydro_write = 0)");
+    if (ensure_hydro(h)) return -1;
   }
   return transfer(h, dev, nf, host, layout, false);
 }

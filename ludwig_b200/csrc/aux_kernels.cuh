@@ -124,3 +124,49 @@ stats_kernel(const Layout L, const double * __restrict__ f, double * __restrict_
   block_reduce8(q, partial + 8*b);
 }
 
+
+// ---------------------------------------------------------------------------
+// rho and u of the state that entered the last collision, recomputed from the
+// post-collision populations still sitting (unstreamed) at each site: mass is a
+// collision invariant and the collision adds the full force to the momentum, so
+//   rho = sum_p f*_p,   rho u = sum_p c_p f*_p - F/2      (src/collision.c:355-382, :523-525)
+// Used when the collision did not store them (option hydro_write = 0) and somebody
+// asks: identical to the stored values to round-off.
+// ---------------------------------------------------------------------------
+
+template <class M, bool BINARY>
+__global__ void __launch_bounds__(256)
+hydro_from_fstar_kernel(const Layout L, const double * __restrict__ f,
+			const double * __restrict__ force, const double fg0,
+			const double fg1, const double fg2,
+			double * __restrict__ rho, double * __restrict__ u) {
+
+  const int i2 = blockIdx.x*blockDim.x + threadIdx.x;
+  const int i1 = blockIdx.y*blockDim.y + threadIdx.y;
+  const int i0 = blockIdx.z;
+  if (i2 >= L.n[2] || i1 >= L.n[1]) return;
+  const i64 site = (i64)(i0 + L.h[0])*L.s0 + (i64)(i1 + L.h[1])*L.s1 + L.z0 + L.h[2] + i2;
+
+  double r = 0.0, g[3] = {0.0, 0.0, 0.0};
+  #pragma unroll
+  for (int p = 0; p < M::NVEL; p++) {
+    const double fp = __ldg(f + (i64) p*L.nsd + site);
+    r += fp;
+    #pragma unroll
+    for (int a = 0; a < M::NDIM; a++) {
+      if (M::cv(p, a) ==  1) g[a] += fp;
+      if (M::cv(p, a) == -1) g[a] -= fp;
+    }
+  }
+  double F[3] = {fg0, fg1, fg2};
+  if (force != nullptr) {
+    #pragma unroll
+    for (int a = 0; a < M::NDIM; a++) F[a] += force[a*L.nsd + site];
+  }
+  const double rr = 1.0/r;
+  if (!BINARY) rho[site] = r;          // the binary collision never stores rho
+  #pragma unroll
+  for (int a = 0; a < 3; a++) {
+    u[a*L.nsd + site] = (a < M::NDIM) ? rr*(g[a] - 0.5*F[a]) : 0.0;
+  }
+}

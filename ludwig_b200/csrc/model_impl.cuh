@@ -87,6 +87,16 @@ static cudaError_t stats_impl(const Layout & L, const double * f, int ndist,
   return cudaGetLastError();
 }
 
+static cudaError_t hydro_impl(const Layout & L, const double * f, int ndist,
+			      const double * force, const double fg[3], double * rho,
+			      double * u, cudaStream_t s) {
+  dim3 block(128, 2, 1);
+  dim3 grid((L.n[2] + 127)/128, (L.n[1] + 1)/2, L.n[0]);
+  if (ndist == 2) hydro_from_fstar_kernel<MODEL, true><<<grid, block, 0, s>>>(L, f, force, fg[0], fg[1], fg[2], rho, u);
+  else hydro_from_fstar_kernel<MODEL, false><<<grid, block, 0, s>>>(L, f, force, fg[0], fg[1], fg[2], rho, u);
+  return cudaGetLastError();
+}
+
 static cudaError_t ghost_upload_impl(void) {
   static GhostTab T;
   build_ghost_tab<MODEL>(T);
@@ -106,6 +116,7 @@ const ModelOps * B200LB_OPS_FN(void) {
     ops.sweep = sweep_impl;
     ops.phi_from_g = phi_impl;
     ops.stats = stats_impl;
+    ops.hydro = hydro_impl;
     ops.ghost_upload = ghost_upload_impl;
     init = true;
   }

@@ -27,6 +27,8 @@ struct ModelOps {
 			    double * phi, bool pull, cudaStream_t);
   cudaError_t (*stats)(const Layout &, const double * f, int ndist,
 		       double * partial, dim3 grid, dim3 block, cudaStream_t);
+  cudaError_t (*hydro)(const Layout &, const double * f, int ndist, const double * force,
+		       const double fg[3], double * rho, double * u, cudaStream_t);
   cudaError_t (*ghost_upload)(void);
 };
 

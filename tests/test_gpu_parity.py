@@ -394,3 +394,100 @@ def test_in_sweep_diagnostics():
         assert np.array_equal(lat2.lb_memcpy_d2h(), lat.lb_memcpy_d2h())
         lat.close()
         lat2.close()
+
+
+@pytest.mark.parametrize("nvel,nlocal,ndist", [(19, (12, 10, 8), 1), (27, (8, 6, 10), 1),
+                                               (9, (16, 12, 1), 1), (19, (8, 8, 6), 2)])
+@pytest.mark.parametrize("order", ["hydro_first", "lattice_first"])
+def test_hydro_on_demand(nvel, nlocal, ndist, order):
+    """hydro_write = 0: the collision stores no rho,u; asking for them later (before or
+    after the lattice has been looked at) gives the reference's values, with a force field."""
+    import ludwig_b200 as lb
+    from oracle import pyoracle
+    lat, orc = mk(nvel, nlocal, ndist)
+    ndim = orc.ndim
+    f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal, ndist=ndist, ndim=ndim)
+    force = lbinit.make_force(nlocal, ndim=ndim)
+    fg = (1e-4, -2e-4, 3e-4 if ndim == 3 else 0.0)
+    kw = dict(eta_shear=0.05, eta_bulk=0.12, force=fg)
+    if ndist == 2:
+        kw.update(mobility=3.75, a=-0.00625, b=0.00625, kappa=0.004)
+    prm = pyoracle.make_param(**kw)
+    n = orc.nsite
+    m = orc.interior_mask()
+    f = f0.copy()
+    rho, u = np.zeros(n), np.zeros((n, 3))
+    phi, grad, delsq = np.zeros(n), np.zeros((n, 3)), np.zeros(n)
+    if ndist == 2:
+        orc.phi_from_g(f, phi)
+        orc.halo(phi, 1)
+        orc.grad_7pt(phi, grad, delsq)
+        orc.collide_binary(prm, f, force, u, phi, grad, delsq)
+    else:
+        orc.collide_mrt(prm, f, force, rho, u)
+    orc.halo(f, ndist * nvel)
+    fp = np.zeros_like(f)
+    orc.propagate(f, fp)
+
+    lat.set_option("hydro_write", 0)
+    lat.set_param(**kw)
+    lat.lb_memcpy_h2d(f0)
+    lat.field_h2d(lb.FIELD_FORCE, force)
+    if ndist == 2:
+        lat.phi_lb_to_field()
+        lat.field_halo()
+        lat.field_grad_compute()
+    lat.hydro_u_zero()
+    lat.lb_collide()
+    lat.lb_halo()
+    lat.lb_propagation()                       # deferred
+    if order == "lattice_first":
+        assert np.array_equal(lat.lb_memcpy_d2h()[m], lat.lb_memcpy_d2h()[m])
+        assert relerr(lat.lb_memcpy_d2h()[m], fp[m]) < TOL
+    ud = lat.field_d2h(lb.FIELD_U)
+    assert np.max(np.abs(ud[m] - u[m])) < TOL
+    if ndist == 1:
+        assert relerr(lat.field_d2h(lb.FIELD_RHO)[m], rho[m]) < TOL
+    if order == "hydro_first":
+        assert relerr(lat.lb_memcpy_d2h()[m], fp[m]) < TOL
+    lat.close()
+
+
+@pytest.mark.parametrize("nvel,nlocal,ndist", [(19, (12, 10, 8), 1), (19, (8, 7, 70), 1),
+                                               (27, (8, 6, 10), 1), (9, (16, 12, 1), 1),
+                                               (19, (8, 8, 6), 2)])
+@pytest.mark.parametrize("halo,direct,overlap", [("reduced", 1, 1), ("reduced", 1, 0),
+                                                 ("reduced", 0, 1), ("full", 0, 1), ("full", 0, 0)])
+def test_loopback_exchange_equals_wrap(nvel, nlocal, ndist, halo, direct, overlap):
+    """Option loopback: the periodic directions go through the multi-rank machinery
+    (boundary slabs first, pack kernels, message buffers, unpack, second stream) with
+    this GPU as its own neighbour. The time loop must equal the wrap-around path bit
+    for bit, and lb_halo must still give the exact periodic images."""
+    import ludwig_b200 as lb
+    lat, orc = mk(nvel, nlocal, ndist)
+    f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal, ndist=ndist, ndim=orc.ndim)
+    kw = dict(eta_shear=0.1, eta_bulk=0.1)
+    if ndist == 2:
+        kw = dict(eta_shear=0.00625, eta_bulk=0.00625, mobility=3.75, a=-0.00625,
+                  b=0.00625, kappa=0.004)
+    lat.set_param(**kw)
+    lat.lb_memcpy_h2d(f0)
+    lat.step(5)
+    ref = lat.lb_memcpy_d2h()
+    lat.set_option("loopback", 1)
+    lat.set_option("halo", lb.HALO_REDUCED if halo == "reduced" else lb.HALO_FULL)
+    lat.set_option("direct", direct)
+    lat.set_option("overlap", overlap)
+    lat.lb_memcpy_h2d(f0)
+    lat.step(5)
+    m = orc.interior_mask()
+    assert np.array_equal(lat.lb_memcpy_d2h()[m], ref[m])
+    # halo planes through the buffers
+    rng = np.random.default_rng(11)
+    g0 = rng.standard_normal((orc.nsite, ndist, nvel))
+    g = g0.copy()
+    orc.halo(g, ndist * nvel)
+    lat.lb_memcpy_h2d(g0)
+    lat.lb_halo_swap(lb.HALO_FULL)
+    assert np.array_equal(lat.lb_memcpy_d2h(), g)
+    lat.close()
