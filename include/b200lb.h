@@ -104,7 +104,11 @@ long b200lb_nsite(const b200lb_t * h);                          /* host nsite = 
  *   "halo_lazy"   0/1  defer the local periodic halo copies until the host looks
  *   "overlap"     0/1  exchange halos on a second stream next to the interior sweep
  *   "direct"      0/1  reduced halo as one message per neighbour direction
- *   "diag"        0/1  gather conserved sums inside the collision sweep */
+ *   "diag"        0/1  gather conserved sums inside the collision sweep
+ *   "grad_lazy"   0/1  binary fluid: evaluate the 7-point stencil inside the collision
+ *                      and fill the grad/delsq arrays only when they are asked for
+ *   "loopback"    0/1  single rank: send periodic directions through the exchange
+ *                      buffers with this GPU as its own neighbour (tests, profiling) */
 int  b200lb_set_option(b200lb_t * h, const char * name, long value);
 long b200lb_get_option(const b200lb_t * h, const char * name);
 

@@ -114,6 +114,10 @@ struct b200lb_s {
   double last_fg[3];         // ... and this uniform part
   int  selfper[3];           // device axis is periodic within this rank (one rank in that direction)
   bool halo_deferred;        // lb_halo was called; self-periodic planes not yet copied (pulls wrap)
+  bool phi_halo_deferred;    // the same for field_halo(phi): every reader of phi wraps
+  int  grad_state;           // 0 = grad/delsq arrays hold the gradient of phi, 1 = gradient
+                             // requested but computed inside the collision (materialised
+                             // on demand), 2 = phi changed before that ever happened
   int  halo_deferred_scheme;
 
   b200lb_param_t prm;
@@ -122,7 +126,7 @@ struct b200lb_s {
   bool ghost;
 
   // options
-  int opt_fused, opt_halo, opt_hydro_write, opt_vec, opt_block, opt_halo_lazy, opt_overlap, opt_direct, opt_diag, opt_loopback;
+  int opt_fused, opt_halo, opt_hydro_write, opt_vec, opt_block, opt_halo_lazy, opt_overlap, opt_direct, opt_diag, opt_loopback, opt_grad_lazy;
 
   cudaStream_t s_main, s_x[2];
   cudaStream_t s_comm;       // halo exchange of decomposed directions (overlaps the interior sweep)
@@ -326,11 +330,14 @@ extern "C" int b200lb_create(const b200lb_desc_t * desc, b200lb_t ** out) {
   h->opt_fused = 1;
   h->opt_halo = B200LB_HALO_FULL;
   h->opt_hydro_write = 1;
-  h->opt_vec = (desc->nvel == 27) ? 1 : 2;   // D3Q27: 27 live populations per site, one site per thread is faster (measured)
+  // two sites per thread (128-bit accesses) for D3Q19; one for D3Q27 (27 live populations
+  // per site) and D2Q9 (few streams, occupancy matters more): measured, profiles/r1_bench_*
+  h->opt_vec = (desc->nvel == 19) ? 2 : 1;
   h->opt_block = 128;
   h->opt_halo_lazy = 1;
   h->opt_overlap = 1;
   h->opt_direct = 1;
+  h->opt_grad_lazy = 1;
 
   b200lb_param_t p0;
   memset(&p0, 0, sizeof(p0));
@@ -391,6 +398,7 @@ extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
   if (!strcmp(name, "overlap")) { h->opt_overlap = (v != 0); return 0; }
   if (!strcmp(name, "direct")) { h->opt_direct = (v != 0); return 0; }
   if (!strcmp(name, "diag")) { h->opt_diag = (v != 0); return 0; }
+  if (!strcmp(name, "grad_lazy")) { h->opt_grad_lazy = (v != 0); return 0; }
   if (!strcmp(name, "loopback")) {
     if (h->desc.nranks > 1 && v) return fail("loopback is for single-rank lattices");
     if (join_comm(h)) return -1;
@@ -425,6 +433,7 @@ extern "C" long b200lb_get_option(const b200lb_t * h, const char * name) {
   if (!strcmp(name, "overlap")) return h->opt_overlap;
   if (!strcmp(name, "direct")) return h->opt_direct;
   if (!strcmp(name, "diag")) return h->opt_diag;
+  if (!strcmp(name, "grad_lazy")) return h->opt_grad_lazy;
   if (!strcmp(name, "loopback")) return h->opt_loopback;
   if (!strcmp(name, "direct_state")) return h->direct_state;
   if (!strcmp(name, "halo_deferred")) return h->halo_deferred;
@@ -508,7 +517,11 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
     h->last_ffield = !h->force_uniform;
     for (int i = 0; i < 3; i++) h->last_fg[i] = a.P.fg[i];
     if (h->opt_hydro_write) { a.P.rho = h->rho; a.P.u = h->u; }
-    a.P.phi = h->phi; a.P.grad = h->grad; a.P.delsq = h->delsq;
+    a.P.phi = h->phi;
+    if (h->desc.ndist == 2 && h->grad_state == 2) {
+      return fail("lb_collide: the order parameter changed after the last field_grad_compute");
+    }
+    if (h->grad_state == 0) { a.P.grad = h->grad; a.P.delsq = h->delsq; }
   }
   int lo[7][3], hi[7][3];
   const int nbox = split_boxes(h, lo, hi);
@@ -895,11 +908,35 @@ extern "C" int b200lb_halo(b200lb_t * h) {
   return b200lb_halo_swap(h, h->opt_halo);
 }
 
+static int run_grad7(b200lb_s * h) {
+  const Layout & L = h->L;
+  dim3 block(GRAD_TZ, GRAD_TY, 1);
+  dim3 grid((L.n[2] + GRAD_TZ - 1)/GRAD_TZ, (L.n[1] + GRAD_TY - 1)/GRAD_TY,
+	    (L.n[0] + GRAD_NX - 1)/GRAD_NX);
+  grad7_kernel<<<grid, block, 0, h->s_main>>>(L, h->selfper[0], h->selfper[1], h->selfper[2],
+					      h->phi, h->grad, h->delsq);
+  CU(cudaGetLastError());
+  h->launches++;
+  h->grad_state = 0;
+  return 0;
+}
+
 extern "C" int b200lb_phi_halo(b200lb_t * h) {
   if (!h) return fail("null handle");
   if (!h->phi) return fail("no order parameter (ndist = 1)");
   if (join_comm(h)) return -1;
-  return halo_exchange(h, h->phi, false, 1, B200LB_HALO_FULL, 0, h->s_main);
+  if (!h->opt_halo_lazy) return halo_exchange(h, h->phi, false, 1, B200LB_HALO_FULL, 0, h->s_main);
+  // directions decomposed over ranks now; the local periodic copies only when the host
+  // looks at phi (the gradient stencil wraps around those directions)
+  if (halo_exchange(h, h->phi, false, 1, B200LB_HALO_FULL, 1, h->s_main)) return -1;
+  h->phi_halo_deferred = true;
+  return 0;
+}
+
+static int flush_phi_halo(b200lb_s * h) {
+  if (!h->phi_halo_deferred) return 0;
+  h->phi_halo_deferred = false;
+  return halo_exchange(h, h->phi, false, 1, B200LB_HALO_FULL, 2, h->s_main);
 }
 
 // ---------------------------------------------------------------------------
@@ -913,20 +950,21 @@ extern "C" int b200lb_phi_from_g(b200lb_t * h) {
   const double * g = h->lat[h->cur] + (i64) h->desc.nvel*h->L.nsd;
   CU(h->ops->phi_from_g(h->L, h->selfper, g, h->phi, h->prop_pending, h->s_main));
   h->launches++;
+  h->phi_halo_deferred = false;
+  if (h->grad_state == 1) h->grad_state = 2;      // the pending gradient belonged to the old phi
   return 0;
 }
 
 extern "C" int b200lb_grad7(b200lb_t * h) {
   if (!h) return fail("null handle");
   if (!h->phi) return fail("no order parameter (ndist = 1)");
-  const Layout & L = h->L;
-  dim3 block(GRAD_TZ, GRAD_TY, 1);
-  dim3 grid((L.n[2] + GRAD_TZ - 1)/GRAD_TZ, (L.n[1] + GRAD_TY - 1)/GRAD_TY,
-	    (L.n[0] + GRAD_NX - 1)/GRAD_NX);
-  grad7_kernel<<<grid, block, 0, h->s_main>>>(L, h->phi, h->grad, h->delsq);
-  CU(cudaGetLastError());
-  h->launches++;
-  return 0;
+  if (h->opt_grad_lazy) {
+    // The only consumer on the path is the binary collision, which evaluates the same
+    // 7-point stencil in registers; the arrays are filled when somebody asks for them.
+    h->grad_state = 1;
+    return 0;
+  }
+  return run_grad7(h);
 }
 
 static int fill3(b200lb_s * h, double * data, int nf, const double v[3]) {
@@ -1142,6 +1180,11 @@ extern "C" int b200lb_field_upload(b200lb_t * h, int field, const double * host,
     h->force_uniform = false;
   }
   if ((field == B200LB_FIELD_U || field == B200LB_FIELD_RHO) && h->hydro_stale) h->hydro_stale = false;
+  if (field == B200LB_FIELD_PHI) {
+    h->phi_halo_deferred = false;
+    if (h->grad_state == 1) h->grad_state = 2;
+  }
+  if (field == B200LB_FIELD_GRAD || field == B200LB_FIELD_DELSQ) h->grad_state = 0;
   if (field == B200LB_FIELD_U) h->u_fill_pending = false;
   return transfer(h, dev, nf, const_cast<double *>(host), layout, true);
 }
@@ -1159,6 +1202,11 @@ extern "C" int b200lb_field_download(b200lb_t * h, int field, double * host, int
   }
   if ((field == B200LB_FIELD_U || field == B200LB_FIELD_RHO) && h->hydro_stale) {
     if (ensure_hydro(h)) return -1;
+  }
+  if (field == B200LB_FIELD_PHI) { if (flush_phi_halo(h)) return -1; }
+  if (field == B200LB_FIELD_GRAD || field == B200LB_FIELD_DELSQ) {
+    if (h->grad_state == 2) return fail("the gradient of the previous order parameter was never materialised (option grad_lazy = 0 keeps the arrays current)");
+    if (h->grad_state == 1) { if (run_grad7(h)) return -1; }
   }
   return transfer(h, dev, nf, host, layout, false);
 }

@@ -89,7 +89,8 @@ halo_kernel(const HaloParams H) {
 #define GRAD_NX 16     // x-planes marched by one block
 
 __global__ void __launch_bounds__(GRAD_TZ*GRAD_TY)
-grad7_kernel(const Layout L, const double * __restrict__ phi,
+grad7_kernel(const Layout L, const int w0, const int w1, const int w2,
+	     const double * __restrict__ phi,
 	     double * __restrict__ grad, double * __restrict__ delsq) {
 
   __shared__ double sm[3][GRAD_TY + 2][GRAD_TZ + 2];
@@ -106,16 +107,25 @@ grad7_kernel(const Layout L, const double * __restrict__ phi,
   const bool active = (i2 < L.n[2]) && (i1 < L.n[1]);
   const i64 col = (i64) c1*L.s1 + L.z0 + c2;
 
+  // Offsets to the -1 / +1 neighbours along y and z. A direction that is periodic
+  // within this rank (w = 1) wraps around instead of reading the halo plane.
+  const i64 zmo = (w2 && c2 == 1)      ? (i64) (L.n[2] - 1) : -1;
+  const i64 zpo = (w2 && c2 == L.n[2]) ? -(i64) (L.n[2] - 1) : 1;
+  const i64 ymo = (w1 && c1 == 1)      ? (i64) (L.n[1] - 1)*L.s1 : -L.s1;
+  const i64 ypo = (w1 && c1 == L.n[1]) ? -(i64) (L.n[1] - 1)*L.s1 : L.s1;
+
   // loads one z-y plane (with apron) at halo-inclusive x coordinate xa into sm[slot]
   auto load_plane = [&](int slot, int xa) {
+    if (w0 && xa == 0) xa = L.n[0];
+    if (w0 && xa == L.n[0] + 1) xa = 1;
     const double * pl = phi + (i64) xa*L.s0;
     sm[slot][ty + 1][tz + 1] = __ldg(pl + col);
-    if (tz == 0)             sm[slot][ty + 1][0]           = __ldg(pl + col - 1);
+    if (tz == 0)             sm[slot][ty + 1][0]           = __ldg(pl + col + zmo);
     if (tz == GRAD_TZ - 1 || i2 == L.n[2] - 1)
-      sm[slot][ty + 1][tz + 2] = __ldg(pl + col + 1);
-    if (ty == 0)             sm[slot][0][tz + 1]           = __ldg(pl + col - L.s1);
+      sm[slot][ty + 1][tz + 2] = __ldg(pl + col + zpo);
+    if (ty == 0)             sm[slot][0][tz + 1]           = __ldg(pl + col + ymo);
     if (ty == GRAD_TY - 1 || i1 == L.n[1] - 1)
-      sm[slot][ty + 2][tz + 1] = __ldg(pl + col + L.s1);
+      sm[slot][ty + 2][tz + 1] = __ldg(pl + col + ypo);
   };
 
   // planes x0-1 (halo-inclusive x0) and x0

@@ -279,7 +279,7 @@ lb_sweep_kernel(const KParams P) {
   // read (and need not be filled): SURVEY 7.4 "self-exchange fast path".
   i64 om[2], op[2];        // axes 0 and 1: block-uniform
   int zm[VEC], zp[VEC];    // contiguous axis: differs only for the first / last site of a row
-  if (PULL) {
+  if (PULL || BINARY) {
     om[0] = -L.s0; op[0] = L.s0; om[1] = -L.s1; op[1] = L.s1;
     if (P.wrap[0]) {
       if (i0 == 0) om[0] = (i64) (L.n[0] - 1)*L.s0;
@@ -342,10 +342,24 @@ lb_sweep_kernel(const KParams P) {
       double rho, u[3];
       if (BINARY) {
 	const double phi = P.phi[s];
-	const double dsq = P.delsq[s];
+	double dsq;
 	double gr[3];
-	#pragma unroll
-	for (int a = 0; a < 3; a++) gr[a] = P.grad[a*L.nsd + s];
+	if (P.grad != nullptr) {
+	  dsq = P.delsq[s];
+	  #pragma unroll
+	  for (int a = 0; a < 3; a++) gr[a] = P.grad[a*L.nsd + s];
+	}
+	else {
+	  // gradient not materialised: the 7-point stencil of
+	  // src/gradient_3d_7pt_fluid.c:232-313 straight from phi (same operations in
+	  // the same order, so the values are those grad7_kernel would store)
+	  const double * ph = P.phi + s;
+	  const double xp = __ldg(ph + op[0]), xm = __ldg(ph + om[0]);
+	  const double yp = __ldg(ph + op[1]), ym = __ldg(ph + om[1]);
+	  const double zq = __ldg(ph + zp[v]), zn = __ldg(ph + zm[v]);
+	  gr[0] = 0.5*(xp - xm); gr[1] = 0.5*(yp - ym); gr[2] = 0.5*(zq - zn);
+	  dsq = xp + xm + yp + ym + zq + zn - __dmul_rn(6.0, phi);
+	}
 	// fe_symm_str_v / fe_symm_mu (src/symmetric.c:371-420, :307-320)
 	const double p0 = 0.5*P.A*phi*phi + 0.75*P.B*phi*phi*phi*phi
 	  - P.kappa*phi*dsq

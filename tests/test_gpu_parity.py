@@ -491,3 +491,33 @@ def test_loopback_exchange_equals_wrap(nvel, nlocal, ndist, halo, direct, overla
     lat.lb_halo_swap(lb.HALO_FULL)
     assert np.array_equal(lat.lb_memcpy_d2h(), g)
     lat.close()
+
+
+def test_binary_gradient_in_collision_equals_arrays():
+    """grad_lazy: the collision evaluates the 7-point stencil itself; the result must be
+    bit-identical to reading the arrays grad7 stores, and the arrays must still be
+    there (bit-exact) when asked for afterwards."""
+    import ludwig_b200 as lb
+    nvel, nlocal = 19, (9, 8, 10)
+    lat, orc = mk(nvel, nlocal, 2)
+    B = goldenlib.BIN
+    kw = dict(eta_shear=B["eta"], eta_bulk=B["eta"], mobility=B["mobility"],
+              a=B["a"], b=B["b"], kappa=B["kappa"])
+    f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal, ndist=2)
+    res = {}
+    for lazy in (0, 1):
+        lat.set_option("grad_lazy", lazy)
+        lat.set_param(**kw)
+        lat.lb_memcpy_h2d(f0)
+        lat.step(4)
+        res[lazy] = lat.lb_memcpy_d2h()
+    m = orc.interior_mask()
+    assert np.array_equal(res[0][m], res[1][m])
+    # arrays on demand after a lazy step: gradient of the phi of that step
+    n = orc.nsite
+    phi = lat.field_d2h(lb.FIELD_PHI)
+    grad, delsq = np.zeros((n, 3)), np.zeros(n)
+    orc.grad_7pt(phi, grad, delsq)
+    assert np.array_equal(lat.field_d2h(lb.FIELD_GRAD)[m], grad[m])
+    assert np.array_equal(lat.field_d2h(lb.FIELD_DELSQ)[m], delsq[m])
+    lat.close()
