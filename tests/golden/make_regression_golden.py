@@ -1,0 +1,49 @@
+"""Extracts the statistics block printed after the last time step from the reference's own
+regression golden logs (tests/regression/d3q19-short/serial-dist-*.log, Ludwig v0.20.1)
+into tests/golden/regression_logs.json, together with the input keys that define each
+case. Run in the build container (needs /root/reference)."""
+
+import json
+import os
+import re
+
+REF = "/root/reference/tests/regression/d3q19-short"
+HERE = os.path.dirname(os.path.abspath(__file__))
+CASES = ["serial-dist-3du", "serial-dist-1dp", "serial-dist-2kh", "serial-dist-2sw"]
+
+
+def floats(line):
+    return [float(x) for x in re.findall(r"[-+]?\d+\.\d+(?:[eE][-+]?\d+)?", line)]
+
+
+def main():
+    out = {}
+    for case in CASES:
+        inp = {}
+        for line in open(os.path.join(REF, case + ".inp")):
+            line = line.strip()
+            if not line or line.startswith("#"):
+                continue
+            parts = line.split()
+            inp[parts[0]] = parts[1] if len(parts) > 1 else ""
+        lines = open(os.path.join(REF, case + ".log")).read().splitlines()
+        start = max(i for i, l in enumerate(lines) if l.startswith("Scalars - total"))
+        blk = lines[start:start + 12]
+        rec = {"input": inp, "source": "tests/regression/d3q19-short/%s.log:%d-%d" % (case, start + 1, start + 10)}
+        for l in blk:
+            if l.startswith("[rho]"):
+                rec["rho"] = floats(l)                 # total mean variance min max
+            if l.startswith("[total   ]"):
+                rec["momentum"] = floats(l)
+            if l.startswith("[minimum ]"):
+                rec["umin"] = floats(l)
+            if l.startswith("[maximum ]"):
+                rec["umax"] = floats(l)
+        out[case] = rec
+    with open(os.path.join(HERE, "regression_logs.json"), "w") as fh:
+        json.dump(out, fh, indent=1)
+    print(json.dumps(out, indent=1)[:600])
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,126 @@
+"""Ludwig's own regression logs for the single-fluid path (tests/regression/d3q19-short/
+serial-dist-{3du,1dp,2kh,2sw}.{inp,log}): the statistics printed after the last step,
+reproduced the way tests/test-diff.sh + tests/awk-fp-diff.sh judge them -- every printed
+float, in the reference's printf format, within an ABSOLUTE 1e-12.
+
+The initial conditions restate src/distribution_rt.c:398-600 (analytic velocity
+profiles through lb_1st_moment_equilib_set); the golden numbers are extracted from the
+reference logs by tests/golden/make_regression_golden.py. The CPU oracle is checked
+everywhere, the CUDA path on a GPU (-m gpu).
+"""
+
+import json
+import math
+import os
+
+import numpy as np
+import pytest
+
+import lbinit
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+GOLD = json.load(open(os.path.join(HERE, "golden", "regression_logs.json")))
+FLT_MAX, FLT_MIN = 3.4028234663852886e+38, 1.1754943508222875e-38
+CASES = sorted(GOLD)
+
+
+def initial_state(inp, cv, wv):
+    """f [nsite,1,19] in the reference host layout, halo sites zero (as lb_init leaves them)."""
+    nt = tuple(int(x) for x in inp["size"].split("_"))
+    nall = tuple(n + 2 for n in nt)
+    lmin = 0.5
+    ic = np.arange(1, nt[0] + 1)[:, None, None] * np.ones(nt)
+    jc = np.arange(1, nt[1] + 1)[None, :, None] * np.ones(nt)
+    kc = np.arange(1, nt[2] + 1)[None, None, :] * np.ones(nt)
+    u = np.zeros(nt + (3,))
+    key = inp["distribution_initialisation"]
+    if key == "3d_uniform_u":
+        u[...] = [float(x) for x in inp["distribution_uniform_u"].split("_")]
+    elif key == "1d_poiseuille":
+        umax = [float(x) for x in inp["distribution_poiseuille_umax"].split("_")]
+        for a, c in enumerate((ic, jc, kc)):
+            x = 1.0 * c - lmin
+            u[..., a] = umax[a] * x * (nt[a] - x) * 4.0 / (nt[a] * nt[a])
+    elif key == "2d_kelvin_helmholtz":
+        u0 = float(inp["2d_kelvin_helmholtz_u0"])
+        delta = float(inp["2d_kelvin_helmholtz_delta"])
+        kappa = float(inp["2d_kelvin_helmholtz_kappa"])
+        x = (1.0 * ic - lmin) / nt[0]
+        y = (1.0 * jc - lmin) / nt[1]
+        u[..., 0] = np.where(y > 0.5, u0 * np.tanh(kappa * (0.75 - y)), u0 * np.tanh(kappa * (y - 0.25)))
+        u[..., 1] = u0 * delta * np.sin(2.0 * math.pi * (x + 0.25))
+    elif key == "2d_shear_wave":
+        y = (1.0 * jc - lmin) / nt[1]
+        u[..., 0] = 0.04 * np.sin(2.0 * math.pi * y)
+    else:
+        raise ValueError(key)
+    feq = lbinit.equilibrium(cv, wv, np.ones(int(np.prod(nt))), u.reshape(-1, 3))
+    f = np.zeros(nall + (1, len(wv)))
+    f[1:-1, 1:-1, 1:-1, 0, :] = feq.reshape(nt + (len(wv),))
+    return nt, np.ascontiguousarray(f.reshape(-1, 1, len(wv)))
+
+
+def printed(fmt, x):
+    return float(fmt % x)
+
+
+def check(rec, nt, sums, u_interior):
+    """sums = [sum rho, sum rho^2, min, max, gx, gy, gz]; u_interior [n,3]."""
+    vol = float(np.prod(nt))
+    mean = sums[0] / vol
+    var = abs(sums[1] / vol - mean * mean)
+    mine = [printed("%14.2f", sums[0]), printed("%14.11f", mean), printed("%14.7e", var),
+            printed("%14.11f", sums[2]), printed("%14.11f", sums[3])]
+    for a, b in zip(mine, rec["rho"]):
+        assert abs(a - b) <= 1e-12, ("rho", mine, rec["rho"])
+    mom = [printed("%14.7e", g) for g in sums[4:7]]
+    for a, b in zip(mom, rec["momentum"]):
+        assert abs(a - b) <= 1e-12, ("momentum", mom, rec["momentum"])
+    # stats_velocity_minmax starts from FLT_MAX / FLT_MIN (src/stats_velocity.c:75-76)
+    umin = [printed("%14.7e", min(FLT_MAX, u_interior[:, a].min())) for a in range(3)]
+    umax = [printed("%14.7e", max(FLT_MIN, u_interior[:, a].max())) for a in range(3)]
+    for a, b in zip(umin, rec["umin"]):
+        assert abs(a - b) <= 1e-12, ("umin", umin, rec["umin"])
+    for a, b in zip(umax, rec["umax"]):
+        assert abs(a - b) <= 1e-12, ("umax", umax, rec["umax"])
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_oracle_reproduces_reference_log(case):
+    from oracle import pyoracle
+    rec = GOLD[case]
+    o0 = pyoracle.Oracle(19, (2, 2, 2))
+    nt, f = initial_state(rec["input"], o0.cv(), o0.wv())
+    orc = pyoracle.Oracle(19, nt)
+    eta = float(rec["input"]["viscosity"])
+    prm = pyoracle.make_param(eta_shear=eta, eta_bulk=eta)
+    n = orc.nsite
+    fp = np.zeros_like(f)
+    rho, u, frc = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
+    orc.step(prm, int(rec["input"]["N_cycles"]), f, fp, rho, u, frc)
+    m = orc.interior_mask()
+    check(rec, nt, orc.stats(f), u[m])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", CASES)
+@pytest.mark.parametrize("hydro_write", [1, 0])
+def test_cuda_reproduces_reference_log(case, hydro_write):
+    import ludwig_b200 as lb
+    from ludwig_b200 import models_host
+    rec = GOLD[case]
+    nt, f = initial_state(rec["input"], models_host.cv(19), models_host.wv(19))
+    eta = float(rec["input"]["viscosity"])
+    lat = lb.Lattice(19, nt)
+    lat.set_option("hydro_write", hydro_write)
+    lat.set_option("halo", lb.HALO_REDUCED)          # lb_halo_openmp_reduced in the input
+    lat.set_param(eta_shear=eta, eta_bulk=eta)
+    lat.lb_memcpy_h2d(f)
+    lat.step(int(rec["input"]["N_cycles"]))
+    sums = lat.stats()                               # lb_memcpy D2H + stats_distribution_print
+    u = lat.field_d2h(lb.FIELD_U)                    # hydro_memcpy D2H + stats_velocity_minmax
+    nall = tuple(n + 2 for n in nt)
+    m = np.zeros(nall, dtype=bool)
+    m[1:-1, 1:-1, 1:-1] = True
+    check(rec, nt, sums, u[m.reshape(-1)])
+    lat.close()
