@@ -188,6 +188,18 @@ static int site_kparams(b200lb_s * h, KParams & P) {
 
 static size_t plane_bytes(const b200lb_s * h) { return (size_t) h->L.nsd*sizeof(double); }
 
+// lazily allocated field planes, zero-filled
+static int need_planes(b200lb_s * h, double ** p, int nplanes) {
+  if (*p) return 0;
+  CU(cudaMalloc(p, plane_bytes(h)*nplanes));
+  CU(cudaMemsetAsync(*p, 0, plane_bytes(h)*nplanes, h->s_main));
+  return 0;
+}
+static int need_hydro(b200lb_s * h) {
+  if (need_planes(h, &h->rho, 1)) return -1;
+  return need_planes(h, &h->u, 3);
+}
+
 // ---------------------------------------------------------------------------
 // create / destroy
 // ---------------------------------------------------------------------------
@@ -302,19 +314,12 @@ extern "C" int b200lb_create(const b200lb_desc_t * desc, b200lb_t ** out) {
     CU(cudaMalloc(&h->lat[i], pb*h->nplane));
     CU(cudaMemsetAsync(h->lat[i], 0, pb*h->nplane, h->s_main));
   }
-  CU(cudaMalloc(&h->rho, pb));
-  CU(cudaMalloc(&h->u, 3*pb));
-  CU(cudaMalloc(&h->force, 3*pb));
-  CU(cudaMemsetAsync(h->rho, 0, pb, h->s_main));
-  CU(cudaMemsetAsync(h->u, 0, 3*pb, h->s_main));
-  CU(cudaMemsetAsync(h->force, 0, 3*pb, h->s_main));
+  // rho, u, force, grad and delsq are allocated when first needed (need_planes): a
+  // run that keeps hydro on demand and never has a per-site force carries only the two
+  // lattices (1024^3 on two GPUs: 2 x 82 GB fit in 180 GB that way).
   if (desc->ndist == 2) {
     CU(cudaMalloc(&h->phi, pb));
-    CU(cudaMalloc(&h->grad, 3*pb));
-    CU(cudaMalloc(&h->delsq, pb));
     CU(cudaMemsetAsync(h->phi, 0, pb, h->s_main));
-    CU(cudaMemsetAsync(h->grad, 0, 3*pb, h->s_main));
-    CU(cudaMemsetAsync(h->delsq, 0, pb, h->s_main));
   }
   // diagnostics scratch: one partial per block of a (128 x 2) tiling
   h->npartial = (i64)((L.n[2] + 127)/128)*((L.n[1] + 1)/2)*L.n[0];
@@ -513,6 +518,11 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
   a.stream = h->s_main;
   if (collide) {
     for (int i = 0; i < 3; i++) a.P.fg[i] = h->prm.force_global[i] + (h->force_uniform ? h->fconst[i] : 0.0);
+    if (!h->force_uniform) { if (need_planes(h, &h->force, 3)) return -1; }
+    if (h->opt_hydro_write) { if (need_hydro(h)) return -1; }
+    if (h->desc.ndist == 2 && h->grad_state == 0) {
+      if (need_planes(h, &h->grad, 3) || need_planes(h, &h->delsq, 1)) return -1;
+    }
     a.P.force = h->force_uniform ? nullptr : h->force;
     h->last_ffield = !h->force_uniform;
     for (int i = 0; i < 3; i++) h->last_fg[i] = a.P.fg[i];
@@ -560,6 +570,7 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
 static int ensure_hydro(b200lb_s * h) {
   if (!h->hydro_stale) return 0;
   if (join_comm(h)) return -1;
+  if (need_hydro(h)) return -1;
   CU(h->ops->hydro(h->L, h->lat[h->cur], h->desc.ndist, h->last_ffield ? h->force : nullptr,
 		   h->last_fg, h->rho, h->u, h->s_main));
   h->launches++;
@@ -910,6 +921,7 @@ extern "C" int b200lb_halo(b200lb_t * h) {
 
 static int run_grad7(b200lb_s * h) {
   const Layout & L = h->L;
+  if (need_planes(h, &h->grad, 3) || need_planes(h, &h->delsq, 1)) return -1;
   dim3 block(GRAD_TZ, GRAD_TY, 1);
   dim3 grid((L.n[2] + GRAD_TZ - 1)/GRAD_TZ, (L.n[1] + GRAD_TY - 1)/GRAD_TY,
 	    (L.n[0] + GRAD_NX - 1)/GRAD_NX);
@@ -1158,16 +1170,18 @@ extern "C" int b200lb_f_download(b200lb_t * h, double * f, int layout) {
 }
 
 static int field_info(b200lb_s * h, int field, double ** dev, int * nf) {
+  if (field >= B200LB_FIELD_PHI && field <= B200LB_FIELD_DELSQ && h->desc.ndist != 2) {
+    return fail("field %d needs the binary fluid (ndist = 2)", field);
+  }
   switch (field) {
-  case B200LB_FIELD_RHO:   *dev = h->rho;   *nf = 1; break;
-  case B200LB_FIELD_U:     *dev = h->u;     *nf = 3; break;
-  case B200LB_FIELD_FORCE: *dev = h->force; *nf = 3; break;
-  case B200LB_FIELD_PHI:   *dev = h->phi;   *nf = 1; break;
-  case B200LB_FIELD_GRAD:  *dev = h->grad;  *nf = 3; break;
-  case B200LB_FIELD_DELSQ: *dev = h->delsq; *nf = 1; break;
+  case B200LB_FIELD_RHO:   if (need_hydro(h)) return -1; *dev = h->rho; *nf = 1; break;
+  case B200LB_FIELD_U:     if (need_hydro(h)) return -1; *dev = h->u; *nf = 3; break;
+  case B200LB_FIELD_FORCE: if (need_planes(h, &h->force, 3)) return -1; *dev = h->force; *nf = 3; break;
+  case B200LB_FIELD_PHI:   *dev = h->phi; *nf = 1; break;
+  case B200LB_FIELD_GRAD:  if (need_planes(h, &h->grad, 3)) return -1; *dev = h->grad; *nf = 3; break;
+  case B200LB_FIELD_DELSQ: if (need_planes(h, &h->delsq, 1)) return -1; *dev = h->delsq; *nf = 1; break;
   default: return fail("unknown field %d", field);
   }
-  if (!*dev) return fail("field %d not allocated (ndist = 1)", field);
   return 0;
 }
 

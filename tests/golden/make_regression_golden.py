@@ -1,5 +1,6 @@
 """Extracts the statistics block printed after the last time step from the reference's own
-regression golden logs (tests/regression/d3q19-short/serial-dist-*.log, Ludwig v0.20.1)
+regression golden logs (tests/regression/d3q19-short/serial-dist-*.log and d2q9/serial-2khz-bm1.log,
+Ludwig v0.20.1)
 into tests/golden/regression_logs.json, together with the input keys that define each
 case. Run in the build container (needs /root/reference)."""
 
@@ -7,9 +8,11 @@ import json
 import os
 import re
 
-REF = "/root/reference/tests/regression/d3q19-short"
+REF = "/root/reference/tests/regression"
 HERE = os.path.dirname(os.path.abspath(__file__))
-CASES = ["serial-dist-3du", "serial-dist-1dp", "serial-dist-2kh", "serial-dist-2sw"]
+CASES = ["d3q19-short/serial-dist-3du", "d3q19-short/serial-dist-1dp",
+         "d3q19-short/serial-dist-2kh", "d3q19-short/serial-dist-2sw", "d2q9/serial-2khz-bm1"]
+NVEL = {"d3q19-short": 19, "d2q9": 9}
 
 
 def floats(line):
@@ -29,7 +32,8 @@ def main():
         lines = open(os.path.join(REF, case + ".log")).read().splitlines()
         start = max(i for i, l in enumerate(lines) if l.startswith("Scalars - total"))
         blk = lines[start:start + 12]
-        rec = {"input": inp, "source": "tests/regression/d3q19-short/%s.log:%d-%d" % (case, start + 1, start + 10)}
+        rec = {"input": inp, "nvel": NVEL[case.split("/")[0]],
+               "source": "tests/regression/%s.log:%d-%d" % (case, start + 1, start + 10)}
         for l in blk:
             if l.startswith("[rho]"):
                 rec["rho"] = floats(l)                 # total mean variance min max
@@ -39,7 +43,7 @@ def main():
                 rec["umin"] = floats(l)
             if l.startswith("[maximum ]"):
                 rec["umax"] = floats(l)
-        out[case] = rec
+        out[case.split('/')[1]] = rec
     with open(os.path.join(HERE, "regression_logs.json"), "w") as fh:
         json.dump(out, fh, indent=1)
     print(json.dumps(out, indent=1)[:600])
