@@ -126,6 +126,8 @@ int  b200lb_set_param(b200lb_t * h, const b200lb_param_t * prm);
 /* The hot path. Names follow the reference call surface (src/ludwig.c:530-862). */
 int  b200lb_hydro_f_zero(b200lb_t * h, const double f[3]);   /* hydro_f_zero  src/hydro.c:306 */
 int  b200lb_hydro_u_zero(b200lb_t * h, const double u[3]);   /* hydro_u_zero  src/hydro.c:279 */
+int  b200lb_hydro_rho0(b200lb_t * h, double rho0);           /* hydro_rho0    src/hydro.c:335 */
+int  b200lb_hydro_correct_momentum(b200lb_t * h);            /* hydro_correct_momentum src/hydro.c:829 */
 int  b200lb_collide(b200lb_t * h);                           /* lb_collide    src/collision.c:144 */
 int  b200lb_halo(b200lb_t * h);                              /* lb_halo       src/model.c:553 */
 int  b200lb_halo_swap(b200lb_t * h, int scheme);             /* lb_halo_swap  src/model.c:570 */

@@ -56,6 +56,7 @@ struct NcclApi {
   decltype(&ncclCommDestroy) CommDestroy;
   decltype(&ncclSend) Send;
   decltype(&ncclRecv) Recv;
+  decltype(&ncclAllReduce) AllReduce;
   decltype(&ncclGroupStart) GroupStart;
   decltype(&ncclGroupEnd) GroupEnd;
   decltype(&ncclGetErrorString) GetErrorString;
@@ -70,7 +71,7 @@ static int nccl_load(void) {
   if (!lib) return fail("NCCL not found: %s", dlerror());
 #define SYM(name) g_nccl.name = (decltype(g_nccl.name)) dlsym(lib, "nccl" #name); \
   if (!g_nccl.name) return fail("NCCL symbol nccl" #name " missing")
-  SYM(GetUniqueId); SYM(CommInitRank); SYM(CommDestroy); SYM(Send); SYM(Recv);
+  SYM(GetUniqueId); SYM(CommInitRank); SYM(CommDestroy); SYM(Send); SYM(Recv); SYM(AllReduce);
   SYM(GroupStart); SYM(GroupEnd); SYM(GetErrorString);
 #undef SYM
   g_nccl.lib = lib;
@@ -1001,6 +1002,40 @@ extern "C" int b200lb_hydro_u_zero(b200lb_t * h, const double u[3]) {
   if (!h) return fail("null handle");
   for (int i = 0; i < 3; i++) h->uconst[i] = u ? u[i] : 0.0;
   h->u_fill_pending = true;     // the next collision overwrites the interior anyway
+  return 0;
+}
+
+extern "C" int b200lb_hydro_rho0(b200lb_t * h, double rho0) {
+  if (!h) return fail("null handle");
+  if (need_hydro(h)) return -1;
+  const double v[3] = {rho0, 0.0, 0.0};
+  h->hydro_stale = false;
+  return fill3(h, h->rho, 1, v);
+}
+
+extern "C" int b200lb_hydro_correct_momentum(b200lb_t * h) {
+  if (!h) return fail("null handle");
+  if (h->hydro_stale && h->last_ffield) { if (ensure_hydro(h)) return -1; }
+  if (need_planes(h, &h->force, 3)) return -1;
+  if (h->force_uniform) {                 // make the constant field real first
+    if (fill3(h, h->force, 3, h->fconst)) return -1;
+    h->force_uniform = false;
+  }
+  const Layout & L = h->L;
+  dim3 block(128, 2, 1);
+  dim3 grid((L.n[2] + 127)/128, (L.n[1] + 1)/2, L.n[0]);
+  force_sum_kernel<<<grid, block, 0, h->s_main>>>(L, h->force, h->partial);
+  stats_final_kernel<<<1, 256, 0, h->s_main>>>(h->partial, h->npartial, h->stats_dev);
+  CU(cudaGetLastError());
+  if (h->comm) {
+    // MPI_Allreduce(3 doubles, SUM) of src/hydro.c:873, on the device
+    NC(g_nccl.AllReduce(h->stats_dev + 4, h->stats_dev + 4, 3, ncclDouble, ncclSum, h->comm, h->s_main));
+  }
+  double vol = 1.0;
+  for (int a = 0; a < 3; a++) vol *= (double) h->desc.nlocal[a]*h->desc.cartsz[a];
+  force_correct_kernel<<<grid, block, 0, h->s_main>>>(L, h->force, h->stats_dev, 1.0/vol);
+  CU(cudaGetLastError());
+  h->launches += 3;
   return 0;
 }
 

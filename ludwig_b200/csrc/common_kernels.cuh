@@ -281,3 +281,37 @@ halo_direct_kernel(const Layout L, const HaloMsg * __restrict__ msgs,
     else buf[m.off + idx] = *p;
   }
 }
+
+// ---------------------------------------------------------------------------
+// hydro_correct_momentum (src/hydro.c:829-895, kernels :904-1099): remove the net
+// body force. Stage 1 sums the force over interior sites (warp shuffles, one partial
+// per block, no atomics), stats_final_kernel folds the partials, the caller
+// all-reduces over ranks, stage 2 adds -F_net/V to every interior site, reading the
+// sum from device memory (no host round trip).
+// ---------------------------------------------------------------------------
+
+__global__ void __launch_bounds__(256)
+force_sum_kernel(const Layout L, const double * __restrict__ force, double * __restrict__ partial) {
+  const int i2 = blockIdx.x*blockDim.x + threadIdx.x;
+  const int i1 = blockIdx.y*blockDim.y + threadIdx.y;
+  const int i0 = blockIdx.z;
+  double q[8] = {0.0, 0.0, 1.0e300, -1.0e300, 0.0, 0.0, 0.0, 0.0};
+  if (i2 < L.n[2] && i1 < L.n[1]) {
+    const i64 site = (i64)(i0 + L.h[0])*L.s0 + (i64)(i1 + L.h[1])*L.s1 + L.z0 + L.h[2] + i2;
+    q[4] = force[site]; q[5] = force[L.nsd + site]; q[6] = force[2*L.nsd + site];
+  }
+  const i64 b = ((i64) blockIdx.z*gridDim.y + blockIdx.y)*gridDim.x + blockIdx.x;
+  block_reduce8(q, partial + 8*b);
+}
+
+__global__ void __launch_bounds__(256)
+force_correct_kernel(const Layout L, double * __restrict__ force,
+		     const double * __restrict__ sums, const double rv) {
+  const int i2 = blockIdx.x*blockDim.x + threadIdx.x;
+  const int i1 = blockIdx.y*blockDim.y + threadIdx.y;
+  const int i0 = blockIdx.z;
+  if (i2 >= L.n[2] || i1 >= L.n[1]) return;
+  const i64 site = (i64)(i0 + L.h[0])*L.s0 + (i64)(i1 + L.h[1])*L.s1 + L.z0 + L.h[2] + i2;
+  #pragma unroll
+  for (int a = 0; a < 3; a++) force[a*L.nsd + site] += -sums[4 + a]*rv;
+}

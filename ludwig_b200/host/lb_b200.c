@@ -176,6 +176,16 @@ int hydro_u_zero(hydro_t * h, const double uzero[3]) {
   return 0;
 }
 
+int hydro_rho0(hydro_t * h, double rho0) {
+  TRY(b200lb_hydro_rho0(h->lb->target, rho0));
+  return 0;
+}
+
+int hydro_correct_momentum(hydro_t * h) {
+  TRY(b200lb_hydro_correct_momentum(h->lb->target));
+  return 0;
+}
+
 /* order parameter, gradient, free energy */
 
 int field_create(lb_t * lb, const char * name, field_t ** pphi) {

@@ -109,6 +109,8 @@ int hydro_free(hydro_t * hydro);
 int hydro_memcpy(hydro_t * hydro, tdpMemcpyKind flag);
 int hydro_f_zero(hydro_t * hydro, const double fzero[3]);
 int hydro_u_zero(hydro_t * hydro, const double uzero[3]);
+int hydro_rho0(hydro_t * hydro, double rho0);                      /* src/hydro.h:66 */
+int hydro_correct_momentum(hydro_t * hydro);                       /* src/hydro.h:63 */
 
 int field_create(lb_t * lb, const char * name, field_t ** phi);      /* the order parameter */
 int field_free(field_t * phi);

@@ -30,7 +30,7 @@ ABI_SYMBOLS = [
     "b200lb_destroy", "b200lb_nsite", "b200lb_set_option", "b200lb_get_option",
     "b200lb_f_upload", "b200lb_f_download", "b200lb_field_upload",
     "b200lb_field_download", "b200lb_set_param", "b200lb_hydro_f_zero",
-    "b200lb_hydro_u_zero", "b200lb_collide", "b200lb_halo", "b200lb_halo_swap",
+    "b200lb_hydro_u_zero", "b200lb_hydro_rho0", "b200lb_hydro_correct_momentum", "b200lb_collide", "b200lb_halo", "b200lb_halo_swap",
     "b200lb_propagate", "b200lb_phi_from_g", "b200lb_phi_halo", "b200lb_grad7",
     "b200lb_step", "b200lb_stats", "b200lb_step_diag", "b200lb_sync", "b200lb_nccl_unique_id",
     "b200lb_comm_init", "b200lb_timer_start", "b200lb_timer_stop",
@@ -102,9 +102,10 @@ def load():
         getattr(L, name).argtypes = [vp, ctypes.c_int, vp, ctypes.c_int]
     for name in ("b200lb_destroy", "b200lb_collide", "b200lb_halo", "b200lb_propagate",
                  "b200lb_phi_from_g", "b200lb_phi_halo", "b200lb_grad7", "b200lb_sync",
-                 "b200lb_timer_start", "b200lb_nsite", "b200lb_launch_count"):
+                 "b200lb_hydro_correct_momentum", "b200lb_timer_start", "b200lb_nsite", "b200lb_launch_count"):
         getattr(L, name).argtypes = [vp]
     L.b200lb_halo_swap.argtypes = [vp, ctypes.c_int]
+    L.b200lb_hydro_rho0.argtypes = [vp, ctypes.c_double]
     L.b200lb_step.argtypes = [vp, ctypes.c_int]
     L.b200lb_hydro_f_zero.argtypes = [vp, ctypes.POINTER(ctypes.c_double)]
     L.b200lb_hydro_u_zero.argtypes = [vp, ctypes.POINTER(ctypes.c_double)]
@@ -247,6 +248,12 @@ class Lattice:
 
     def hydro_u_zero(self, u=(0.0, 0.0, 0.0)):
         self._ck(self.L.b200lb_hydro_u_zero(self.h, (ctypes.c_double * 3)(*u)))
+
+    def hydro_rho0(self, rho0):
+        self._ck(self.L.b200lb_hydro_rho0(self.h, rho0))
+
+    def hydro_correct_momentum(self):
+        self._ck(self.L.b200lb_hydro_correct_momentum(self.h))
 
     def lb_collide(self):
         self._ck(self.L.b200lb_collide(self.h))

@@ -521,3 +521,57 @@ def test_binary_gradient_in_collision_equals_arrays():
     assert np.array_equal(lat.field_d2h(lb.FIELD_GRAD)[m], grad[m])
     assert np.array_equal(lat.field_d2h(lb.FIELD_DELSQ)[m], delsq[m])
     lat.close()
+
+
+def test_hydro_rho0_and_correct_momentum():
+    """hydro_rho0 (src/hydro.c:335) and hydro_correct_momentum (src/hydro.c:829-895):
+    the mean body force over the fluid volume is removed from every interior site."""
+    import ludwig_b200 as lb
+    nvel, nlocal = 19, (9, 8, 7)
+    lat, orc = mk(nvel, nlocal)
+    force = lbinit.make_force(nlocal) + np.array([1e-3, -2e-3, 5e-4])
+    m = orc.interior_mask()
+    lat.field_h2d(lb.FIELD_FORCE, force)
+    lat.hydro_correct_momentum()
+    got = lat.field_d2h(lb.FIELD_FORCE)
+    want = force.copy()
+    want[m] -= force[m].sum(axis=0) / float(np.prod(nlocal))
+    assert np.max(np.abs(got[m] - want[m])) < 1e-16 + 1e-13 * np.max(np.abs(force))
+    assert np.array_equal(got[~m], force[~m])
+    assert np.max(np.abs(got[m].sum(axis=0))) < 1e-15 * m.sum()
+    lat.hydro_rho0(1.25)
+    assert np.all(lat.field_d2h(lb.FIELD_RHO) == 1.25)
+    # a uniform field has no net force left after the correction
+    lat.hydro_f_zero((1e-3, 0.0, 0.0))
+    lat.hydro_correct_momentum()
+    assert np.max(np.abs(lat.field_d2h(lb.FIELD_FORCE)[m])) < 1e-18
+    lat.close()
+
+
+def test_config0_64cubed_1000_steps():
+    """BASELINE config[0]: D3Q19 single-fluid MRT, 64^3 periodic, 1000 steps, against the
+    CPU oracle: full lattice after 1, 10 and 1000 steps within 1e-12 of max|f|, mass to
+    round-off."""
+    from oracle import pyoracle
+    import ludwig_b200 as lb
+    nvel, nlocal = 19, (64, 64, 64)
+    lat, orc = mk(nvel, nlocal)
+    f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal)
+    prm = pyoracle.make_param(eta_shear=0.1, eta_bulk=0.1)
+    lat.set_param(eta_shear=0.1, eta_bulk=0.1)
+    lat.lb_memcpy_h2d(f0)
+    f, fp = f0.copy(), np.zeros_like(f0)
+    n = orc.nsite
+    rho, u, frc = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
+    m = orc.interior_mask()
+    mass0 = f0[m].sum()
+    done = 0
+    for upto in (1, 10, 1000):
+        orc.step(prm, upto - done, f, fp, rho, u, frc)
+        lat.step(upto - done)
+        done = upto
+        fd = lat.lb_memcpy_d2h()
+        assert relerr(fd[m], f[m]) < TOL, upto
+        assert abs(fd[m].sum() - mass0) < 1e-13 * m.sum() * 19
+    assert np.max(np.abs(lat.field_d2h(lb.FIELD_U)[m] - u[m])) < TOL
+    lat.close()
