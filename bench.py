@@ -50,6 +50,7 @@ def parse():
     ap.add_argument("--hydro-write", type=int, default=1)
     ap.add_argument("--overlap", type=int, default=1)
     ap.add_argument("--direct", type=int, default=1)
+    ap.add_argument("--p2p", type=int, default=1, help="peer-memory halo (CUDA IPC) instead of NCCL messages")
     ap.add_argument("--loopback", type=int, default=0, help="single GPU: run the halo exchange machinery with the GPU as its own neighbour")
     ap.add_argument("--grid", type=int, nargs=3, default=None, help="process grid (default 2x1x1, 2x2x1, 2x2x2)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
@@ -302,6 +303,13 @@ def main():
                                device="cuda")
         dist.broadcast(uid, 0)
         lat.comm_init(bytes(uid.cpu().tolist()))
+        if args.p2p:
+            mine = torch.tensor(list(lat.p2p_export()), dtype=torch.uint8, device="cuda")
+            allh = [torch.empty_like(mine) for _ in range(world)]
+            dist.all_gather(allh, mine)
+            lat.p2p_import(b"".join(bytes(t.cpu().tolist()) for t in allh), world)
+    elif args.loopback and args.p2p:
+        lat.p2p_import(None, 1)
 
     def barrier():
         lat.sync()
@@ -433,7 +441,7 @@ def main():
                 "workload": workload_name(nvel, ndist, local, grid),
                 "global_lattice": list(ntotal), "decomposition": par,
                 "fused": bool(args.fused), "vec": args.vec, "halo": args.halo,
-                "hydro_write": bool(args.hydro_write), "overlap": bool(args.overlap), "direct_halo": bool(args.direct), "loopback": bool(args.loopback),
+                "hydro_write": bool(args.hydro_write), "overlap": bool(args.overlap), "direct_halo": bool(args.direct), "p2p_halo": bool(args.p2p and (world > 1 or args.loopback)), "loopback": bool(args.loopback),
                 "l2": "lattice %.2f GB per GPU >> 126 MB L2 (no flush needed)" % (2 * lattice_bytes / 1e9),
             },
             "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "hydro_on_demand": lazy,

@@ -161,6 +161,15 @@ int  b200lb_sync(b200lb_t * h);          /* tdpDeviceSynchronize for this handle
 int  b200lb_nccl_unique_id(char id[128]);
 int  b200lb_comm_init(b200lb_t * h, const char id[128]);
 
+/* Peer-memory halo (one node, NVLink/NVSwitch): every rank exports CUDA IPC handles
+ * of its lattices (192 bytes), the launcher gathers them from all ranks in rank
+ * order, every rank imports. From then on the collision sweep stores the outgoing
+ * populations of boundary sites directly into the neighbours' halo sites and
+ * lb_halo (reduced scheme) has nothing left to send; option "p2p" = 0 goes back to
+ * NCCL messages. Ranks must issue the same sequence of calls (SPMD, as Ludwig does). */
+int  b200lb_p2p_export(b200lb_t * h, char out[192]);
+int  b200lb_p2p_import(b200lb_t * h, const char * all, int nranks);
+
 /* Timing on the handle's compute stream (CUDA events), for bench.py */
 int  b200lb_timer_start(b200lb_t * h);
 int  b200lb_timer_stop(b200lb_t * h, float * ms);     /* synchronises */

@@ -127,7 +127,7 @@ struct b200lb_s {
   bool ghost;
 
   // options
-  int opt_fused, opt_halo, opt_hydro_write, opt_vec, opt_block, opt_halo_lazy, opt_overlap, opt_direct, opt_diag, opt_loopback, opt_grad_lazy;
+  int opt_fused, opt_halo, opt_hydro_write, opt_vec, opt_block, opt_halo_lazy, opt_overlap, opt_direct, opt_diag, opt_loopback, opt_grad_lazy, opt_p2p;
 
   cudaStream_t s_main, s_x[2];
   cudaStream_t s_comm;       // halo exchange of decomposed directions (overlaps the interior sweep)
@@ -155,6 +155,15 @@ struct b200lb_s {
   i64 unpack_off[B200LB_MAXMSG], unpack_cnt[B200LB_MAXMSG];
   i64 pack_max, unpack_max;
   double * dsend, * drecv;
+
+  // peer-memory halo (CUDA IPC mappings of the neighbours' lattices)
+  int p2p_ready;
+  double * peer_lat[2][27];
+  P2PSync p2p;
+  void * ipc_open[64]; int n_ipc_open;
+  unsigned long long push_step;
+  bool push_wait_pending;     // a signal was sent: s_main must pass wait(push_step) before touching halos
+  bool pushed_valid;          // the halo data of lat[cur] was pushed by the sweep that wrote it
 };
 
 // A direction whose halo planes travel through send/receive buffers: decomposed over
@@ -344,6 +353,7 @@ extern "C" int b200lb_create(const b200lb_desc_t * desc, b200lb_t ** out) {
   h->opt_overlap = 1;
   h->opt_direct = 1;
   h->opt_grad_lazy = 1;
+  h->opt_p2p = 1;
 
   b200lb_param_t p0;
   memset(&p0, 0, sizeof(p0));
@@ -360,6 +370,8 @@ extern "C" int b200lb_destroy(b200lb_t * h) {
   if (!h) return 0;
   cudaDeviceSynchronize();
   if (h->comm) g_nccl.CommDestroy(h->comm);
+  for (int i = 0; i < h->n_ipc_open; i++) cudaIpcCloseMemHandle(h->ipc_open[i]);
+  cudaFree(h->p2p.flags);
   cudaFree(h->msg_pack); cudaFree(h->msg_unpack); cudaFree(h->dsend); cudaFree(h->drecv);
   for (int d = 0; d < 3; d++) {
     cudaFree(h->hb[d].to_lo); cudaFree(h->hb[d].to_hi);
@@ -405,12 +417,14 @@ extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
   if (!strcmp(name, "direct")) { h->opt_direct = (v != 0); return 0; }
   if (!strcmp(name, "diag")) { h->opt_diag = (v != 0); return 0; }
   if (!strcmp(name, "grad_lazy")) { h->opt_grad_lazy = (v != 0); return 0; }
+  if (!strcmp(name, "p2p")) { if (join_comm(h)) return -1; h->opt_p2p = (v != 0); h->pushed_valid = false; return 0; }
   if (!strcmp(name, "loopback")) {
     if (h->desc.nranks > 1 && v) return fail("loopback is for single-rank lattices");
     if (join_comm(h)) return -1;
     if (flush_halo(h)) return -1;
     h->opt_loopback = (v != 0);
     update_selfper(h);
+    h->p2p_ready = 0; h->pushed_valid = false; h->push_wait_pending = false;
     // message tables depend on which directions are exchanged
     CU(cudaStreamSynchronize(h->s_main));
     CU(cudaStreamSynchronize(h->s_comm));
@@ -440,6 +454,8 @@ extern "C" long b200lb_get_option(const b200lb_t * h, const char * name) {
   if (!strcmp(name, "direct")) return h->opt_direct;
   if (!strcmp(name, "diag")) return h->opt_diag;
   if (!strcmp(name, "grad_lazy")) return h->opt_grad_lazy;
+  if (!strcmp(name, "p2p")) return h->opt_p2p;
+  if (!strcmp(name, "p2p_ready")) return h->p2p_ready;
   if (!strcmp(name, "loopback")) return h->opt_loopback;
   if (!strcmp(name, "direct_state")) return h->direct_state;
   if (!strcmp(name, "halo_deferred")) return h->halo_deferred;
@@ -465,6 +481,14 @@ extern "C" int b200lb_set_param(b200lb_t * h, const b200lb_param_t * prm) {
 
 // s_main waits for an exchange still running on s_comm
 static int join_comm(b200lb_s * h) {
+  if (h->push_wait_pending) {
+    // neighbours must have finished the sweep that pushed into this rank's halos
+    // (and reading the buffer this rank pushes into next); 10 s watchdog
+    p2p_wait_kernel<<<1, 32, 0, h->s_main>>>(h->p2p, h->push_step, 10000000000ULL);
+    CU(cudaGetLastError());
+    h->launches++;
+    h->push_wait_pending = false;
+  }
   if (h->halo_inflight) {
     CU(cudaStreamWaitEvent(h->s_main, h->ev_halo, 0));
     h->halo_inflight = false;
@@ -535,8 +559,15 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
     if (h->grad_state == 0) { a.P.grad = h->grad; a.P.delsq = h->delsq; }
   }
   int lo[7][3], hi[7][3];
-  const int nbox = split_boxes(h, lo, hi);
+  const bool push = collide && h->p2p_ready && h->opt_p2p;
+  const int nbox = push ? 1 : split_boxes(h, lo, hi);
   h->bnd_valid = false;
+  h->pushed_valid = false;
+  if (push) {
+    const int which = (dst == h->lat[0]) ? 0 : 1;
+    a.P.push = 1;
+    for (int k = 0; k < 27; k++) a.P.peer[k] = h->peer_lat[which][k];
+  }
   a.diag = collide && h->opt_diag;
   a.P.diag = h->diag;
   a.P.diag_base = 0;
@@ -557,6 +588,14 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
       if (a.P.diag_base > h->diag_cap) return fail("internal: diagnostics buffer too small");
       h->diag_count = a.P.diag_base;
     }
+  }
+  if (push) {
+    h->push_step++;
+    p2p_signal_kernel<<<1, 32, 0, h->s_main>>>(h->p2p, h->push_step);
+    CU(cudaGetLastError());
+    h->launches++;
+    h->push_wait_pending = true;
+    h->pushed_valid = true;
   }
   h->halo_deferred = false;        // whatever was written has stale halos until the next lb_halo
   if (collide) {
@@ -861,6 +900,7 @@ static int direct_exchange(b200lb_s * h, double * data, cudaStream_t st) {
 
 // the decomposed directions of the current lattice, by the cheapest valid route
 static int lattice_exchange(b200lb_s * h, int scheme, cudaStream_t st) {
+  if (scheme == B200LB_HALO_REDUCED && h->pushed_valid) return 0;   // already in the neighbours' halos
   if (scheme == B200LB_HALO_REDUCED && have_comm(h) && h->opt_direct) {
     if (direct_setup(h)) return -1;
     if (h->direct_state == 1) return direct_exchange(h, h->lat[h->cur], st);
@@ -1105,6 +1145,11 @@ extern "C" int b200lb_sync(b200lb_t * h) {
   CU(cudaStreamSynchronize(h->s_main));
   CU(cudaStreamSynchronize(h->s_x[0]));
   CU(cudaStreamSynchronize(h->s_x[1]));
+  if (h->p2p.flags) {
+    unsigned long long err = 0;
+    CU(cudaMemcpy(&err, h->p2p.flags + 27, sizeof(err), cudaMemcpyDeviceToHost));
+    if (err) return fail("peer-memory halo: a neighbour did not reach step %llu within the watchdog time", err);
+  }
   return 0;
 }
 
@@ -1279,6 +1324,84 @@ extern "C" int b200lb_comm_init(b200lb_t * h, const char id[128]) {
   ncclUniqueId uid;
   memcpy(&uid, id, 128);
   NC(g_nccl.CommInitRank(&h->comm, h->desc.nranks, uid, h->desc.rank));
+  return 0;
+}
+
+// ---------------------------------------------------------------------------
+// peer-memory halo: CUDA IPC handles of the two lattices and the flag array
+// ---------------------------------------------------------------------------
+
+static int p2p_flags_alloc(b200lb_s * h) {
+  if (h->p2p.flags) return 0;
+  CU(cudaMalloc(&h->p2p.flags, 32*sizeof(unsigned long long)));
+  CU(cudaMemset(h->p2p.flags, 0, 32*sizeof(unsigned long long)));
+  return 0;
+}
+
+extern "C" int b200lb_p2p_export(b200lb_t * h, char out[192]) {
+  if (!h || !out) return fail("null argument");
+  if (p2p_flags_alloc(h)) return -1;
+  cudaIpcMemHandle_t hd[3];
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle is 64 bytes");
+  CU(cudaIpcGetMemHandle(&hd[0], h->lat[0]));
+  CU(cudaIpcGetMemHandle(&hd[1], h->lat[1]));
+  CU(cudaIpcGetMemHandle(&hd[2], h->p2p.flags));
+  memcpy(out, hd, 192);
+  return 0;
+}
+
+// all = nranks x 192 bytes (every rank's export, in rank order). With nranks = 1 and
+// option loopback the rank is its own neighbour and no IPC is involved.
+extern "C" int b200lb_p2p_import(b200lb_t * h, const char * all, int nranks) {
+  if (!h) return fail("null handle");
+  if (nranks != h->desc.nranks) return fail("p2p_import: nranks %d != %d", nranks, h->desc.nranks);
+  if (p2p_flags_alloc(h)) return -1;
+  const Layout & L = h->L;
+  for (int d = 0; d < 3; d++) {
+    if (decomposed(h, d) && L.n[d] < 2) return fail("peer-memory halo needs at least 2 sites per decomposed direction");
+  }
+  double * rlat[2][64]; unsigned long long * rflags[64];
+  bool opened[64];
+  if (nranks > 64) return fail("p2p_import: at most 64 ranks");
+  for (int r = 0; r < nranks; r++) opened[r] = false;
+  for (int k = 0; k < 27; k++) { h->peer_lat[0][k] = h->peer_lat[1][k] = nullptr; h->p2p.peer_flags[k] = nullptr; }
+  int npeer = 0;
+  for (int k = 0; k < 27; k++) {
+    const int dir[3] = {k/9 - 1, (k/3)%3 - 1, k%3 - 1};        // device axes
+    if (k == 13) continue;
+    bool ok = true;
+    int pdir[3] = {0, 0, 0};
+    for (int d = 0; d < 3; d++) {
+      if (dir[d] != 0 && !decomposed(h, d)) ok = false;
+      pdir[h->ops->dax[d]] = dir[d];
+    }
+    if (!ok) continue;
+    const int r = cart_rank(h, pdir);
+    if (r < 0) continue;
+    if (r == h->desc.rank) {
+      h->peer_lat[0][k] = h->lat[0]; h->peer_lat[1][k] = h->lat[1]; h->p2p.peer_flags[k] = h->p2p.flags;
+    }
+    else {
+      if (!all) return fail("p2p_import: handles missing");
+      if (!opened[r]) {
+        cudaIpcMemHandle_t hd[3];
+        memcpy(hd, all + (size_t) r*192, 192);
+        void * p0 = nullptr, * p1 = nullptr, * p2 = nullptr;
+        CU(cudaIpcOpenMemHandle(&p0, hd[0], cudaIpcMemLazyEnablePeerAccess));
+        CU(cudaIpcOpenMemHandle(&p1, hd[1], cudaIpcMemLazyEnablePeerAccess));
+        CU(cudaIpcOpenMemHandle(&p2, hd[2], cudaIpcMemLazyEnablePeerAccess));
+        rlat[0][r] = (double *) p0; rlat[1][r] = (double *) p1; rflags[r] = (unsigned long long *) p2;
+        h->ipc_open[h->n_ipc_open++] = p0; h->ipc_open[h->n_ipc_open++] = p1; h->ipc_open[h->n_ipc_open++] = p2;
+        opened[r] = true;
+      }
+      h->peer_lat[0][k] = rlat[0][r]; h->peer_lat[1][k] = rlat[1][r]; h->p2p.peer_flags[k] = rflags[r];
+    }
+    npeer++;
+  }
+  h->p2p_ready = (npeer > 0) ? 1 : 0;
+  h->push_step = 0;
+  h->push_wait_pending = false;
+  h->pushed_valid = false;
   return 0;
 }
 

@@ -315,3 +315,42 @@ force_correct_kernel(const Layout L, double * __restrict__ force,
   #pragma unroll
   for (int a = 0; a < 3; a++) force[a*L.nsd + site] += -sums[4 + a]*rv;
 }
+
+// ---------------------------------------------------------------------------
+// Peer-memory halo synchronisation. Every rank runs the same sequence
+//   wait(k) -> sweep k+1 (pushes into the neighbours' halo sites) -> signal(k+1)
+// where signal writes the step number into a slot of each neighbour's flag array
+// (peer memory) and wait spins on the local array until every neighbour has
+// reached that step. One rule covers both hazards: a neighbour's pushed values
+// are complete before they are read, and a neighbour has finished reading the
+// buffer this rank is about to push into. The spin has a watchdog (never hangs).
+// ---------------------------------------------------------------------------
+
+struct P2PSync {
+  unsigned long long * flags;            // local: [27] per direction + [27] = error
+  unsigned long long * peer_flags[27];   // neighbour's flag array per direction, or null
+};
+
+__global__ void p2p_signal_kernel(const P2PSync S, const unsigned long long step) {
+  const int t = threadIdx.x;
+  if (t < 27 && S.peer_flags[t] != nullptr) {
+    __threadfence_system();
+    // the neighbour in direction t sees this rank in direction -t = slot 26 - t
+    *((volatile unsigned long long *) (S.peer_flags[t] + (26 - t))) = step;
+  }
+}
+
+__global__ void p2p_wait_kernel(const P2PSync S, const unsigned long long step,
+				const unsigned long long timeout_ns) {
+  const int t = threadIdx.x;
+  if (t < 27 && S.peer_flags[t] != nullptr) {
+    unsigned long long t0, t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    while (*((volatile unsigned long long *) (S.flags + t)) < step) {
+      __nanosleep(200);
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+      if (t1 - t0 > timeout_ns) { S.flags[27] = step; break; }
+    }
+  }
+  __threadfence_system();
+}

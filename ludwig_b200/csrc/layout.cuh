@@ -38,6 +38,8 @@ struct KParams {
   const double * phi;     // [nsd]
   const double * grad;    // [3][nsd]
   const double * delsq;   // [nsd]
+  int push;               // write outgoing populations straight into the neighbours' halo sites
+  double * peer[27];      // neighbour's destination lattice per direction (dx+1)*9+(dy+1)*3+(dz+1), or null
   double * diag;          // per-block partial sums of the in-kernel diagnostics, or unused
   i64 diag_base;          // first partial slot of this launch
   int lo[3], hi[3];       // sub-box of the interior, 0-based interior coordinates, [lo,hi)

@@ -409,6 +409,50 @@ lb_sweep_kernel(const KParams P) {
     }
   }
 
+  // Peer-memory halo: a site on the face of the local box also stores the
+  // populations that leave through that face directly into the halo site of the
+  // neighbouring GPU's lattice (NVLink peer pointers, mapped with CUDA IPC), for
+  // faces, edges and corners alike. This replaces pack kernel + NCCL + unpack kernel:
+  // the transfer rides on the sweep itself. Same population set as the reduced
+  // scheme (src/model.c:1192-1219): p goes to direction s iff s picks components of
+  // c_p and the site lies on the boundary in each picked component.
+  if (COLLIDE && P.push) {
+    #pragma unroll
+    for (int v = 0; v < VEC; v++) {
+      if (v < nv) {
+	int e[3];
+	e[0] = (i0 == 0) ? -1 : ((i0 == L.n[0] - 1) ? 1 : 0);
+	e[1] = (i1 == 0) ? -1 : ((i1 == L.n[1] - 1) ? 1 : 0);
+	e[2] = (i2 + v == 0) ? -1 : ((i2 + v == L.n[2] - 1) ? 1 : 0);
+	if (e[0] | e[1] | e[2]) {
+	  #pragma unroll
+	  for (int n = 0; n < NDIST; n++) {
+	    #pragma unroll
+	    for (int p = 1; p < Q; p++) {
+	      #pragma unroll
+	      for (int m = 1; m < 8; m++) {
+		// sub-direction m of c_p (compile time); skip picks of a zero component
+		const int s0 = (m & 1) ? dcv<M>(p, 0) : 0;
+		const int s1 = (m & 2) ? dcv<M>(p, 1) : 0;
+		const int s2 = (m & 4) ? dcv<M>(p, 2) : 0;
+		const bool valid = (!(m & 1) || dcv<M>(p, 0) != 0) && (!(m & 2) || dcv<M>(p, 1) != 0)
+		  && (!(m & 4) || dcv<M>(p, 2) != 0);
+		if (valid) {
+		  const bool on = (s0 == 0 || e[0] == s0) && (s1 == 0 || e[1] == s1) && (s2 == 0 || e[2] == s2);
+		  double * peer = P.peer[(s0 + 1)*9 + (s1 + 1)*3 + (s2 + 1)];
+		  if (on && peer != nullptr) {
+		    const i64 rs = site + v - (i64) s0*L.n[0]*L.s0 - (i64) s1*L.n[1]*L.s1 - (i64) s2*L.n[2];
+		    peer[(i64)(n*Q + p)*L.nsd + rs] = f[n][v][p];
+		  }
+		}
+	      }
+	    }
+	  }
+	}
+      }
+    }
+  }
+
   if (DIAG) {
     const i64 b = ((i64) blockIdx.z*gridDim.y + blockIdx.y)*gridDim.x + blockIdx.x;
     block_reduce8(dq, P.diag + 8*(P.diag_base + b));

@@ -33,7 +33,7 @@ ABI_SYMBOLS = [
     "b200lb_hydro_u_zero", "b200lb_hydro_rho0", "b200lb_hydro_correct_momentum", "b200lb_collide", "b200lb_halo", "b200lb_halo_swap",
     "b200lb_propagate", "b200lb_phi_from_g", "b200lb_phi_halo", "b200lb_grad7",
     "b200lb_step", "b200lb_stats", "b200lb_step_diag", "b200lb_sync", "b200lb_nccl_unique_id",
-    "b200lb_comm_init", "b200lb_timer_start", "b200lb_timer_stop",
+    "b200lb_comm_init", "b200lb_p2p_export", "b200lb_p2p_import", "b200lb_timer_start", "b200lb_timer_stop",
     "b200lb_launch_count", "b200lb_host_alloc", "b200lb_host_free",
 ]
 
@@ -114,6 +114,8 @@ def load():
     L.b200lb_timer_stop.argtypes = [vp, ctypes.POINTER(ctypes.c_float)]
     L.b200lb_nccl_unique_id.argtypes = [ctypes.c_char_p]
     L.b200lb_comm_init.argtypes = [vp, ctypes.c_char_p]
+    L.b200lb_p2p_export.argtypes = [vp, ctypes.c_char_p]
+    L.b200lb_p2p_import.argtypes = [vp, ctypes.c_char_p, ctypes.c_int]
     L.b200lb_host_alloc.argtypes = [ctypes.POINTER(vp), ctypes.c_long]
     L.b200lb_host_free.argtypes = [vp]
     _lib = L
@@ -311,6 +313,17 @@ class Lattice:
         if L.b200lb_nccl_unique_id(buf) != 0:
             raise B200LBError(L.b200lb_last_error().decode())
         return buf.raw
+
+    def p2p_export(self):
+        buf = ctypes.create_string_buffer(192)
+        self._ck(self.L.b200lb_p2p_export(self.h, buf))
+        return buf.raw
+
+    def p2p_import(self, blobs, nranks):
+        """blobs: the concatenated p2p_export() of all ranks in rank order (or None for
+        a single rank in loopback mode)."""
+        arg = ctypes.create_string_buffer(blobs, len(blobs)) if blobs else None
+        self._ck(self.L.b200lb_p2p_import(self.h, arg, nranks))
 
     def comm_init(self, uid):
         self._ck(self.L.b200lb_comm_init(self.h, ctypes.create_string_buffer(uid, 128)))

@@ -39,6 +39,7 @@ def main():
     ap.add_argument("--fused", type=int, default=1)
     ap.add_argument("--overlap", type=int, default=1)
     ap.add_argument("--direct", type=int, default=1)
+    ap.add_argument("--p2p", type=int, default=1)
     args = ap.parse_args()
 
     rank = int(os.environ["RANK"])
@@ -63,6 +64,11 @@ def main():
         uid = torch.tensor(list(lb.Lattice.nccl_unique_id()), dtype=torch.uint8, device="cuda")
     dist.broadcast(uid, 0)
     lat.comm_init(bytes(uid.cpu().tolist()))
+    if args.p2p:
+        mine = torch.tensor(list(lat.p2p_export()), dtype=torch.uint8, device="cuda")
+        allh = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allh, mine)
+        lat.p2p_import(b"".join(bytes(t.cpu().tolist()) for t in allh), world)
     lat.set_option("fused", args.fused)
     lat.set_option("overlap", args.overlap)
     lat.set_option("direct", args.direct)
@@ -134,9 +140,9 @@ def main():
         err = float(np.max(np.abs(glob - fo)) / np.max(np.abs(fo)))
         mass = abs(float(sums[0].item()) - s1[0])
         halo_ok = bool(flags.item() > 0.5)
-        print("mgpu world=%d grid=%s nvel=%d ndist=%d halo=%s fused=%d overlap=%d direct=%d: halo_bit_exact=%s "
+        print("mgpu world=%d grid=%s nvel=%d ndist=%d halo=%s fused=%d overlap=%d direct=%d p2p=%d: halo_bit_exact=%s "
               "decomposed==single=%s err_vs_oracle=%.2e mass_diff=%.2e"
-              % (world, grid, nvel, ndist, args.halo, args.fused, args.overlap, args.direct, halo_ok, same, err, mass),
+              % (world, grid, nvel, ndist, args.halo, args.fused, args.overlap, args.direct, args.p2p, halo_ok, same, err, mass),
               flush=True)
         if not (halo_ok and same and err < 1e-12 and mass < 1e-9 * n):
             rc = 1

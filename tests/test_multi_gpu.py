@@ -30,7 +30,8 @@ def launch(n, extra, port):
     ["--nvel", "19", "--halo", "full"],
     ["--nvel", "19", "--halo", "reduced"],
     ["--nvel", "19", "--halo", "reduced", "--fused", "0"],
-    ["--nvel", "19", "--halo", "reduced", "--overlap", "0"],
+    ["--nvel", "19", "--halo", "reduced", "--overlap", "0", "--p2p", "0"],
+    ["--nvel", "19", "--halo", "reduced", "--p2p", "0"],
     ["--nvel", "19", "--halo", "reduced", "--direct", "0"],
     ["--nvel", "19", "--halo", "full", "--overlap", "0", "--lsize", "8", "8", "8"],
     ["--nvel", "27", "--halo", "reduced", "--lsize", "8", "6", "10"],
