@@ -1235,7 +1235,19 @@ extern "C" int b200lb_f_upload(b200lb_t * h, const double * f, int layout) {
   if (ensure_hydro(h)) return -1;   // hydro of the state being replaced stays available
   h->prop_pending = false;          // the host copy replaces whatever was in flight
   h->halo_deferred = false;
-  return transfer(h, h->lat[h->cur], h->nplane, const_cast<double *>(f), layout, true);
+  if (transfer(h, h->lat[h->cur], h->nplane, const_cast<double *>(f), layout, true)) return -1;
+  if (h->p2p_ready && h->opt_p2p) {
+    // The upload wrote this rank's halo sites too. Neighbours may push into them only
+    // after that, so the upload takes part in the signal/wait protocol like a sweep:
+    // nobody's next sweep starts before every neighbour has finished uploading.
+    h->push_step++;
+    p2p_signal_kernel<<<1, 32, 0, h->s_main>>>(h->p2p, h->push_step);
+    CU(cudaGetLastError());
+    h->launches++;
+    h->push_wait_pending = true;
+    h->pushed_valid = false;
+  }
+  return 0;
 }
 
 extern "C" int b200lb_f_download(b200lb_t * h, double * f, int layout) {

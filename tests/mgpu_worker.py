@@ -93,7 +93,10 @@ def main():
     fh = lat.lb_memcpy_d2h()
     ok_halo = bool(np.array_equal(fh, f0))
 
-    # 2. time loop
+    # 2. time loop. Ranks start it at different times on purpose: with the peer-memory
+    # halo an early rank must not push into a neighbour that is still uploading.
+    import time
+    time.sleep(0.3 * (rank % 3))
     lat.lb_memcpy_h2d(f0)
     lat.step(args.steps)
     fd = lat.lb_memcpy_d2h()
