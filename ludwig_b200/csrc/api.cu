@@ -251,6 +251,8 @@ static int derive_params(b200lb_s * h) {
   return 0;
 }
 
+static int create_impl(const b200lb_desc_t * desc, b200lb_s * h, const ModelOps * ops);
+
 extern "C" int b200lb_create(const b200lb_desc_t * desc, b200lb_t ** out) {
 
   if (!desc || !out) return fail("null argument");
@@ -274,13 +276,25 @@ extern "C" int b200lb_create(const b200lb_desc_t * desc, b200lb_t ** out) {
 
   b200lb_s * h = (b200lb_s *) calloc(1, sizeof(b200lb_s));
   if (!h) return fail("out of host memory");
+  if (create_impl(desc, h, ops) != 0) {
+    char keep[sizeof(g_err)];
+    memcpy(keep, g_err, sizeof(keep));
+    b200lb_destroy(h);                     // releases whatever was allocated so far
+    memcpy(g_err, keep, sizeof(keep));
+    return -1;
+  }
+  *out = h;
+  return 0;
+}
+
+static int create_impl(const b200lb_desc_t * desc, b200lb_s * h, const ModelOps * ops) {
   h->desc = *desc;
   h->ops = ops;
   h->nplane = desc->ndist*desc->nvel;
 
   Layout & L = h->L;
   int zalign = desc->zalign > 0 ? desc->zalign : 16;
-  if (zalign < 2 || (zalign & 1)) { free(h); return fail("zalign must be even"); }
+  if (zalign < 2 || (zalign & 1)) return fail("zalign must be even");
   h->nsite_host = 1;
   for (int a = 0; a < 3; a++) {
     h->hostdim[a] = desc->nlocal[a] + 2;
@@ -359,10 +373,9 @@ extern "C" int b200lb_create(const b200lb_desc_t * desc, b200lb_t ** out) {
   memset(&p0, 0, sizeof(p0));
   p0.rho0 = 1.0; p0.eta_shear = 1.0/6.0; p0.eta_bulk = 1.0/6.0;
   h->prm = p0;
-  if (derive_params(h)) { free(h); return -1; }
+  if (derive_params(h)) return -1;
 
   CU(cudaStreamSynchronize(h->s_main));
-  *out = h;
   return 0;
 }
 
@@ -791,7 +804,8 @@ static int direct_setup(b200lb_s * h) {
     dm[a] = -1; dp[a] = 1;
     if (cart_rank(h, dm) != h->desc.nbr_lo[a] || cart_rank(h, dp) != h->desc.nbr_hi[a]) return 0;
   }
-  static HaloMsg pk[B200LB_MAXMSG], up[B200LB_MAXMSG];
+  HaloMsg pk[B200LB_MAXMSG], up[B200LB_MAXMSG];
+  memset(pk, 0, sizeof(pk)); memset(up, 0, sizeof(up));
   int np = 0, nu = 0;
   i64 poff = 0, uoff = 0;
   h->pack_max = h->unpack_max = 0;

@@ -53,24 +53,26 @@ halo_kernel(const HaloParams H) {
   if (ia >= L.na[fa] || ib >= L.na[sl]) return;
   const int k = blockIdx.z;            // entry of the lo list, then of the hi list
 
-  const i64 st[3] = {L.s0, L.s1, 1};
-  const i64 base = L.z0 + (i64) ia*st[fa] + (i64) ib*st[sl];
+  const i64 st_d  = (d == 0) ? L.s0 : ((d == 1) ? L.s1 : 1);
+  const i64 st_fa = (fa == 1) ? L.s1 : 1;
+  const i64 st_sl = (sl == 0) ? L.s0 : L.s1;
+  const i64 base = L.z0 + (i64) ia*st_fa + (i64) ib*st_sl;
   const i64 nface = (i64) L.na[fa]*L.na[sl];
   const i64 fs = (i64) ib*L.na[fa] + ia;
   const int n = L.n[d];
 
   if (k < H.nlo) {
     double * plane = H.data + (i64) H.el_lo[k]*L.nsd + base;
-    if (MODE == HALO_LOCAL)  plane[0] = plane[(i64) n*st[d]];
-    if (MODE == HALO_PACK)   H.to_hi[k*nface + fs] = plane[(i64) n*st[d]];
+    if (MODE == HALO_LOCAL)  plane[0] = plane[(i64) n*st_d];
+    if (MODE == HALO_PACK)   H.to_hi[k*nface + fs] = plane[(i64) n*st_d];
     if (MODE == HALO_UNPACK) plane[0] = H.from_lo[k*nface + fs];
   }
   else {
     const int kk = k - H.nlo;
     double * plane = H.data + (i64) H.el_hi[kk]*L.nsd + base;
-    if (MODE == HALO_LOCAL)  plane[(i64) (n + 1)*st[d]] = plane[st[d]];
-    if (MODE == HALO_PACK)   H.to_lo[kk*nface + fs] = plane[st[d]];
-    if (MODE == HALO_UNPACK) plane[(i64) (n + 1)*st[d]] = H.from_hi[kk*nface + fs];
+    if (MODE == HALO_LOCAL)  plane[(i64) (n + 1)*st_d] = plane[st_d];
+    if (MODE == HALO_PACK)   H.to_lo[kk*nface + fs] = plane[st_d];
+    if (MODE == HALO_UNPACK) plane[(i64) (n + 1)*st_d] = H.from_hi[kk*nface + fs];
   }
 }
 
