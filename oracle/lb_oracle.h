@@ -91,6 +91,10 @@ int orc_phi_from_g(const orc_model_t * model, const orc_box_t * box,
 		   const double * f, double * phi);
 int orc_grad_7pt(const orc_box_t * box, const double * phi,
 		 double * grad, double * delsq);
+int orc_grad_27pt(const orc_box_t * box, const double * phi,
+		  double * grad, double * delsq);
+/* which stencil orc_step uses for the binary fluid: 7 (default) or 27 */
+int orc_gradient_select(int npt);
 
 int orc_fill(const orc_box_t * box, int nf, const double * v, double * data);
 

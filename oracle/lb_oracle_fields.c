@@ -234,6 +234,88 @@ int orc_grad_7pt(const orc_box_t * box, const double * phi,
   return 0;
 }
 
+/* src/gradient_3d_27pt_fluid.c:223-352 (GRAD_DEL2, nextra = 0). The 27-point
+ * box stencil: each first derivative is the sum of nine central differences
+ * scaled by (1/2)(1/9); the Laplacian is (1/9)(sum of 26 neighbours - 26 phi).
+ * Floating-point sums are not associative, so the loops below visit the
+ * terms in the order the reference writes them:
+ *   d/dx : (dy,dz) ascending, +phi(x+1) then -phi(x-1) for each pair
+ *   d/dy : dx ascending then dz ascending, +phi(y+1) then -phi(y-1)
+ *   d/dz : dx ascending then dy ascending, +phi(z+1) then -phi(z-1)
+ *   delsq: (dx,dy,dz) ascending without the centre, centre term last. */
+
+static int grad_select_npt = 7;
+
+int orc_gradient_select(int npt) {
+  if (npt != 7 && npt != 27) return -1;
+  grad_select_npt = npt;
+  return 0;
+}
+
+int orc_grad_27pt(const orc_box_t * box, const double * phi,
+		  double * grad, double * delsq) {
+
+  const long sx = (long) box->nall[1]*box->nall[2];
+  const long sy = box->nall[2];
+  const double r9 = (1.0/9.0);
+
+  #pragma omp parallel for schedule(static)
+  for (int ic = 1; ic <= box->nlocal[0]; ic++) {
+    for (int jc = 1; jc <= box->nlocal[1]; jc++) {
+      for (int kc = 1; kc <= box->nlocal[2]; kc++) {
+	const long i = orc_index(box, ic, jc, kc);
+	double gx = 0.0, gy = 0.0, gz = 0.0, d2 = 0.0;
+	int first;
+
+	first = 1;
+	for (int b = -1; b <= 1; b++) {
+	  for (int c = -1; c <= 1; c++) {
+	    const long o = b*sy + c;
+	    gx = first ? phi[i + sx + o] : gx + phi[i + sx + o];
+	    gx = gx - phi[i - sx + o];
+	    first = 0;
+	  }
+	}
+	first = 1;
+	for (int a = -1; a <= 1; a++) {
+	  for (int c = -1; c <= 1; c++) {
+	    const long o = a*sx + c;
+	    gy = first ? phi[i + sy + o] : gy + phi[i + sy + o];
+	    gy = gy - phi[i - sy + o];
+	    first = 0;
+	  }
+	}
+	first = 1;
+	for (int a = -1; a <= 1; a++) {
+	  for (int b = -1; b <= 1; b++) {
+	    const long o = a*sx + b*sy;
+	    gz = first ? phi[i + 1 + o] : gz + phi[i + 1 + o];
+	    gz = gz - phi[i - 1 + o];
+	    first = 0;
+	  }
+	}
+	first = 1;
+	for (int a = -1; a <= 1; a++) {
+	  for (int b = -1; b <= 1; b++) {
+	    for (int c = -1; c <= 1; c++) {
+	      if (a == 0 && b == 0 && c == 0) continue;
+	      d2 = first ? phi[i + a*sx + b*sy + c] : d2 + phi[i + a*sx + b*sy + c];
+	      first = 0;
+	    }
+	  }
+	}
+	d2 = d2 - 26.0*phi[i];
+
+	grad[3*i + 0] = 0.5*r9*gx;
+	grad[3*i + 1] = 0.5*r9*gy;
+	grad[3*i + 2] = 0.5*r9*gz;
+	delsq[i] = r9*d2;
+      }
+    }
+  }
+  return 0;
+}
+
 /* src/hydro.c:279-398: hydro_u_zero / hydro_f_zero fill ALL sites */
 
 int orc_fill(const orc_box_t * box, int nf, const double * v, double * data) {
@@ -300,7 +382,8 @@ int orc_step(const orc_model_t * model, const orc_box_t * box,
     if (ndist == 2) {
       orc_phi_from_g(model, box, a, phi);
       orc_halo_periodic(box, 1, phi);
-      orc_grad_7pt(box, phi, grad, delsq);
+      if (grad_select_npt == 27) orc_grad_27pt(box, phi, grad, delsq);
+      else orc_grad_7pt(box, phi, grad, delsq);
     }
     orc_fill(box, 3, zero, u);
     if (ndist == 1) {

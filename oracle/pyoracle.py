@@ -181,6 +181,13 @@ class Oracle:
         self.L.orc_grad_7pt(ctypes.byref(self.box), _p(phi), _p(grad),
                             _p(delsq))
 
+    def grad_27pt(self, phi, grad, delsq):
+        self.L.orc_grad_27pt(ctypes.byref(self.box), _p(phi), _p(grad),
+                             _p(delsq))
+
+    def gradient_select(self, npt):
+        assert self.L.orc_gradient_select(int(npt)) == 0
+
     def stats(self, f):
         out = (ctypes.c_double * 8)()
         self.L.orc_stats(ctypes.byref(self.model), ctypes.byref(self.box),

@@ -162,6 +162,9 @@ class Ref:
     def grad_compute(self):
         self.L.refdrv_grad_compute()
 
+    def grad_select(self, npt):
+        assert self.L.refdrv_grad_select(int(npt)) == 0
+
     def hydro_f_zero(self, f=(0.0, 0.0, 0.0)):
         self.L.refdrv_hydro_f_zero((ctypes.c_double * 3)(*f))
 

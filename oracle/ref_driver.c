@@ -15,6 +15,7 @@
  *    phi_lb_to_field      src/phi_lb_coupler.c:39
  *    field_halo           src/field.c:434
  *    grad_3d_7pt_fluid_d2 src/gradient_3d_7pt_fluid.c:75
+ *    grad_3d_27pt_fluid_d2 src/gradient_3d_27pt_fluid.c:75 (refdrv_grad_select(27))
  *    hydro_f_zero/u_zero  src/hydro.c:306,279
  *
  *  The step sequence of refdrv_step() follows src/ludwig.c:530-862 for the
@@ -44,6 +45,7 @@
 #include "leesedwards.h"
 #include "phi_lb_coupler.h"
 #include "gradient_3d_7pt_fluid.h"
+#include "gradient_3d_27pt_fluid.h"
 #include "timer.h"
 
 typedef struct refdrv_s {
@@ -226,6 +228,15 @@ int refdrv_propagate(void)   { return lb_propagation(rd.lb); }
 int refdrv_phi_from_lb(void) { return phi_lb_to_field(rd.phi, rd.lb); }
 int refdrv_phi_halo(void)    { return field_halo(rd.phi); }
 int refdrv_grad_compute(void) { return field_grad_compute(rd.phi_grad); }
+
+/* The reference's function-pointer plug point (src/field_grad.c field_grad_set):
+ * which d2 stencil field_grad_compute() runs, as gradient_rt.c would select. */
+int refdrv_grad_select(int npt) {
+  if (rd.phi_grad == NULL) return -1;
+  if (npt == 7)  return field_grad_set(rd.phi_grad, grad_3d_7pt_fluid_d2, NULL);
+  if (npt == 27) return field_grad_set(rd.phi_grad, grad_3d_27pt_fluid_d2, NULL);
+  return -1;
+}
 
 int refdrv_hydro_f_zero(const double f[3]) { return hydro_f_zero(rd.hydro, f); }
 int refdrv_hydro_u_zero(const double u[3]) { return hydro_u_zero(rd.hydro, u); }

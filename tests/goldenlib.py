@@ -31,3 +31,12 @@ def inputs(nvel, cv, wv, ndist=1):
 def relerr(a, b):
     scale = max(np.max(np.abs(b)), 1e-300)
     return np.max(np.abs(a - b)) / scale
+
+
+def inputs_grad27(nvel):
+    """ref_grad27.npz (tests/golden/make_golden_grad27.py) and its seeded input."""
+    from ludwig_b200 import models_host
+    g = np.load(os.path.join(HERE, "golden", "ref_grad27.npz"))
+    nlocal = tuple(int(x) for x in g["q%d_nlocal" % nvel])
+    f0 = lbinit.make_state(models_host.cv(nvel), models_host.wv(nvel), nlocal, ndist=2)
+    return g, nlocal, f0

@@ -81,3 +81,37 @@ def test_binary():
     # ref phi is the field at the START of step 10; recompute from step-9 state not
     # available here, so compare the order parameter of the final state instead
     assert abs(f[m][:, 1].sum() - g["bin_step10_f"][:, 1].sum()) < 1e-10
+
+
+@pytest.mark.parametrize("nvel", [19, 27])
+def test_gradient_27pt_golden(nvel):
+    """orc_grad_27pt against reference-produced vectors (tests/golden/ref_grad27.npz)."""
+    g, nlocal, f0 = goldenlib.inputs_grad27(nvel)
+    orc = pyoracle.Oracle(nvel, nlocal, ndist=2)
+    m = orc.interior_mask()
+    n = orc.nsite
+    tag = "q%d_" % nvel
+    phi = np.zeros(n)
+    orc.phi_from_g(f0, phi)
+    orc.halo(phi, 1)
+    assert np.array_equal(phi, g[tag + "phi"])
+    grad, delsq = np.zeros((n, 3)), np.zeros(n)
+    orc.grad_27pt(phi, grad, delsq)
+    assert np.array_equal(grad[m], g[tag + "grad"])
+    assert np.array_equal(delsq[m], g[tag + "delsq"])
+    B = goldenlib.BIN
+    prm = pyoracle.make_param(eta_shear=B["eta"], eta_bulk=B["eta"], mobility=B["mobility"],
+                              a=B["a"], b=B["b"], kappa=B["kappa"])
+    f = f0.copy()
+    u, force = np.zeros((n, 3)), np.zeros((n, 3))
+    orc.collide_binary(prm, f, force, u, phi, grad, delsq)
+    assert relerr(f[m], g[tag + "collide_f"]) < 1e-13
+    f = f0.copy()
+    fp, rho = np.zeros_like(f), np.zeros(n)
+    orc.gradient_select(27)
+    try:
+        orc.step(prm, 10, f, fp, rho, u, force, phi, grad, delsq)
+    finally:
+        orc.gradient_select(7)
+    assert relerr(f[m], g[tag + "step10_f"]) < 1e-12
+    assert np.max(np.abs(phi[m] - g[tag + "step10_phi"])) < 1e-13

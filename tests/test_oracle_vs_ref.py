@@ -174,3 +174,44 @@ def test_time_loop(nvel, nlocal, ndist):
         m = orc.interior_mask()
         assert relerr(f[m], ref.f()[m]) < 1e-12
         assert abs(f[m][:, 0].sum() - f0[m][:, 0].sum()) < 1e-9
+
+
+@pytest.mark.parametrize("nvel,nlocal", [(19, (10, 8, 6)), (27, (5, 7, 6))])
+def test_gradient_27pt(nvel, nlocal):
+    """grad_3d_27pt_fluid_d2 selected through field_grad_set: bit-exact, alone and
+    inside the time loop."""
+    need_ref(nvel)
+    orc = pyoracle.Oracle(nvel, nlocal, ndist=2)
+    f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal, ndist=2)
+    A, B, K, M, eta = -0.00625, 0.00625, 0.004, 3.75, 0.00625
+    prm = pyoracle.make_param(eta_shear=eta, eta_bulk=eta, mobility=M, a=A, b=B, kappa=K)
+    m = orc.interior_mask()
+    rng = np.random.default_rng(27)
+    with pyref.Ref(nvel, nlocal, ndist=2) as ref:
+        ref.physics(eta_shear=eta, eta_bulk=eta, mobility=M)
+        ref.fe_symm(A, B, K)
+        ref.grad_select(27)
+        phi = rng.standard_normal(orc.nsite)         # every site, halo too
+        ref.phi()[...] = phi
+        ref.grad_compute()
+        grad, delsq = np.zeros((orc.nsite, 3)), np.zeros(orc.nsite)
+        orc.grad_27pt(phi, grad, delsq)
+        assert np.array_equal(grad[m], ref.grad()[m])
+        assert np.array_equal(delsq[m], ref.delsq()[m])
+        # and it is not the 7-point result
+        g7, d7 = np.zeros_like(grad), np.zeros_like(delsq)
+        orc.grad_7pt(phi, g7, d7)
+        assert not np.allclose(g7[m], grad[m])
+        ref.f()[...] = f0
+        ref.step(5)
+        f = f0.copy()
+        fp = np.zeros_like(f)
+        n = orc.nsite
+        rho, u, force = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
+        phi2 = np.zeros(n)
+        orc.gradient_select(27)
+        try:
+            orc.step(prm, 5, f, fp, rho, u, force, phi2, grad, delsq)
+        finally:
+            orc.gradient_select(7)
+        assert relerr(f[m], ref.f()[m]) < 1e-12
