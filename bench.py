@@ -53,6 +53,10 @@ def parse():
     ap.add_argument("--p2p", type=int, default=1, help="peer-memory halo (CUDA IPC) instead of NCCL messages")
     ap.add_argument("--loopback", type=int, default=0, help="single GPU: run the halo exchange machinery with the GPU as its own neighbour")
     ap.add_argument("--grid", type=int, nargs=3, default=None, help="process grid (default 2x1x1, 2x2x1, 2x2x2)")
+    ap.add_argument("--gradient", type=int, default=7, choices=[7, 27],
+                    help="binary fluid: order-parameter gradient stencil")
+    ap.add_argument("--kt", type=float, default=0.0,
+                    help="> 0: isothermal fluctuations at this temperature (not the headline workload)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--ref-size", type=int, nargs=3, default=None)
@@ -292,9 +296,13 @@ def main():
         lat.set_option("loopback", 1)
     if ndist == 2:
         lat.set_param(eta_shear=0.00625, eta_bulk=0.00625, mobility=3.75, a=-0.00625,
-                      b=0.00625, kappa=0.004)
+                      b=0.00625, kappa=0.004, kt=args.kt)
+        lat.field_grad_set(args.gradient)
     else:
-        lat.set_param(eta_shear=0.1, eta_bulk=0.1)
+        lat.set_param(eta_shear=0.1, eta_bulk=0.1, kt=args.kt)
+    if args.kt > 0.0:
+        lat.noise_init(0)
+        lat.noise_present_set(1)
 
     if world > 1:
         uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
@@ -442,6 +450,8 @@ def main():
                 "global_lattice": list(ntotal), "decomposition": par,
                 "fused": bool(args.fused), "vec": args.vec, "halo": args.halo,
                 "hydro_write": bool(args.hydro_write), "overlap": bool(args.overlap), "direct_halo": bool(args.direct), "p2p_halo": bool(args.p2p and (world > 1 or args.loopback)), "loopback": bool(args.loopback),
+                "gradient_points": args.gradient if ndist == 2 else None,
+                "isothermal_fluctuations_kt": args.kt if args.kt > 0.0 else None,
                 "l2": "lattice %.2f GB per GPU >> 126 MB L2 (no flush needed)" % (2 * lattice_bytes / 1e9),
             },
             "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "hydro_on_demand": lazy,

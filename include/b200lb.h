@@ -84,6 +84,7 @@ typedef struct b200lb_param_s {
   int    nrelax;             /* B200LB_RELAX_* */
   double mobility;           /* binary: rtau2 = 2/(1 + 2 mobility) */
   double a, b, kappa;        /* symmetric free energy */
+  double kt;                 /* physics_kt: temperature of the isothermal fluctuations */
 } b200lb_param_t;
 
 const char * b200lb_last_error(void);
@@ -107,6 +108,8 @@ long b200lb_nsite(const b200lb_t * h);                          /* host nsite = 
  *   "diag"        0/1  gather conserved sums inside the collision sweep
  *   "grad_lazy"   0/1  binary fluid: evaluate the 7-point stencil inside the collision
  *                      and fill the grad/delsq arrays only when they are asked for
+ *   "gradient"    7/27 which stencil b200lb_step uses for the order parameter
+ *                      (fd_gradient_calculation 3d_7pt_fluid / 3d_27pt_fluid, src/gradient_rt.c:81-98)
  *   "loopback"    0/1  single rank: send periodic directions through the exchange
  *                      buffers with this GPU as its own neighbour (tests, profiling) */
 int  b200lb_set_option(b200lb_t * h, const char * name, long value);
@@ -135,9 +138,26 @@ int  b200lb_propagate(b200lb_t * h);                         /* lb_propagation s
 int  b200lb_phi_from_g(b200lb_t * h);                        /* phi_lb_to_field src/phi_lb_coupler.c:39 */
 int  b200lb_phi_halo(b200lb_t * h);                          /* field_halo(phi) src/field.c:434 */
 int  b200lb_grad7(b200lb_t * h);                             /* grad_3d_7pt_fluid_d2 src/gradient_3d_7pt_fluid.c:75 */
+int  b200lb_grad27(b200lb_t * h);                            /* grad_3d_27pt_fluid_d2 src/gradient_3d_27pt_fluid.c:75 */
+
+/* Isothermal fluctuations ("isothermal_fluctuations on", src/collision_rt.c:55):
+ * every site owns a KISS99 generator seeded from its global position, so results do
+ * not depend on the decomposition (noise_create + noise_init, src/noise.c:56,136;
+ * ludwig.c:243 calls it with master_seed 0). While present, lb_collide adds the random
+ * stress and ghost-mode terms of src/collision.c:476-515 / :1663-1745 at temperature
+ * param.kt and advances the generators of the interior sites it collides (the
+ * reference also advances the y,z halo images, which nothing reads).
+ * D2Q9 and D3Q19; D3Q27 has more ghost modes than one draw yields (src/noise.h:18).
+ * state: the reference's host array noise->state, state[index*4 + ia] (AOS) or
+ * state[ia*nsite + index] (SOA), index over the halo-inclusive box (noise_memcpy,
+ * noise I/O for restarts). */
+int  b200lb_noise_init(b200lb_t * h, int master_seed);                /* noise_init src/noise.c:136 */
+int  b200lb_noise_present_set(b200lb_t * h, int on);                  /* noise_present_set(NOISE_RHO) src/noise.c:557 */
+int  b200lb_noise_state_upload(b200lb_t * h, const unsigned int * state, int host_layout);   /* noise_memcpy H2D src/noise.c:253 */
+int  b200lb_noise_state_download(b200lb_t * h, unsigned int * state, int host_layout);       /* noise_memcpy D2H */
 
 /* nsteps iterations of the src/ludwig.c:530-862 loop restricted to the hot
- * path: f_zero; [phi_from_g; phi_halo; grad7]; u_zero; collide; halo; propagate */
+ * path: f_zero; [phi_from_g; phi_halo; grad7 | grad27]; u_zero; collide; halo; propagate */
 int  b200lb_step(b200lb_t * h, int nsteps);
 
 /* Conserved-quantity diagnostics over interior sites of this rank

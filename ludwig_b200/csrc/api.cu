@@ -103,6 +103,9 @@ struct b200lb_s {
   double * lat[2];           // two lattices; lat[cur] is "f", the other "fprime"
   int cur;
   double * rho, * u, * force, * phi, * grad, * delsq;
+  double * noise;            // [2][nsd] per-site generator state (noise_init), or null
+  bool noise_on;             // noise_present_set(NOISE_RHO)
+  double nv_diag, nv_off, nv_bulk, nv_ghost[B200LB_MAXNOISE];
 
   // state machine (see b200lb_propagate)
   bool prop_pending;         // lat[cur] holds post-collision values still to be streamed
@@ -127,7 +130,7 @@ struct b200lb_s {
   bool ghost;
 
   // options
-  int opt_fused, opt_halo, opt_hydro_write, opt_vec, opt_block, opt_halo_lazy, opt_overlap, opt_direct, opt_diag, opt_loopback, opt_grad_lazy, opt_p2p;
+  int opt_fused, opt_halo, opt_hydro_write, opt_vec, opt_block, opt_halo_lazy, opt_overlap, opt_direct, opt_diag, opt_loopback, opt_grad_lazy, opt_p2p, opt_gradient;
 
   cudaStream_t s_main, s_x[2];
   cudaStream_t s_comm;       // halo exchange of decomposed directions (overlaps the interior sweep)
@@ -193,6 +196,11 @@ static int site_kparams(b200lb_s * h, KParams & P) {
   P.rtau_shear = h->rtau_shear; P.rtau_bulk = h->rtau_bulk;
   P.rtau2 = h->rtau2; P.A = h->prm.a; P.B = h->prm.b; P.kappa = h->prm.kappa;
   for (int k = 0; k < B200LB_MAXGHOST; k++) P.gkeep[k] = h->gkeep[k];
+  P.noise = h->noise;
+  P.nv_diag = h->nv_diag; P.nv_off = h->nv_off; P.nv_bulk = h->nv_bulk;
+  for (int k = 0; k < B200LB_MAXNOISE; k++) P.nv_ghost[k] = h->nv_ghost[k];
+  P.nlv_big = sqrt(2.0 + sqrt(2.0));          // rtable of src/noise.c:70-77
+  P.nlv_small = sqrt(2.0 - sqrt(2.0));
   return 0;
 }
 
@@ -247,6 +255,24 @@ static int derive_params(b200lb_s * h) {
   for (int k = 0; k < B200LB_MAXGHOST; k++) {
     h->gkeep[k] = (k < ng) ? 1.0 - rt[k] : 0.0;
     if (h->gkeep[k] != 0.0) h->ghost = true;
+  }
+  // Variances of the fluctuating stress and ghost modes at temperature kt:
+  // lb_fluctuations_var_eta / _var_bulk / _var_ghost, src/collision.c:1756-1815
+  // (kT is normalised by cs^2). With the bulk and shear relaxation times of the scheme.
+  {
+    const double ktn = p.kt*3.0;
+    const double tau_s = 1.0/h->rtau_shear, tau_b = 1.0/h->rtau_bulk;
+    const double var_eta = sqrt(ktn)*sqrt(1.0/9.0)*sqrt((tau_s + tau_s - 1.0)/(tau_s*tau_s));
+    h->nv_diag = var_eta*sqrt(2.0);
+    h->nv_off  = var_eta;
+    h->nv_bulk = sqrt(ktn)*sqrt(2.0/9.0)*sqrt((tau_b + tau_b - 1.0)/(tau_b*tau_b));
+    for (int k = 0; k < B200LB_MAXNOISE; k++) {
+      h->nv_ghost[k] = 0.0;
+      if (k < ng) {
+	const double tau_g = 1.0/rt[k];
+	h->nv_ghost[k] = sqrt(ktn*m->ghost_norm[k])*sqrt((tau_g + tau_g - 1.0)/(tau_g*tau_g));
+      }
+    }
   }
   return 0;
 }
@@ -367,6 +393,7 @@ static int create_impl(const b200lb_desc_t * desc, b200lb_s * h, const ModelOps 
   h->opt_overlap = 1;
   h->opt_direct = 1;
   h->opt_grad_lazy = 1;
+  h->opt_gradient = 7;
   h->opt_p2p = 1;
 
   b200lb_param_t p0;
@@ -397,7 +424,7 @@ extern "C" int b200lb_destroy(b200lb_t * h) {
     cudaEventDestroy(h->ev_x[i]);
   }
   cudaFree(h->rho); cudaFree(h->u); cudaFree(h->force);
-  cudaFree(h->phi); cudaFree(h->grad); cudaFree(h->delsq);
+  cudaFree(h->phi); cudaFree(h->grad); cudaFree(h->delsq); cudaFree(h->noise);
   cudaFree(h->partial); cudaFree(h->diag); cudaFree(h->stats_dev); cudaFreeHost(h->stats_host);
   cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
   cudaStreamDestroy(h->s_main);
@@ -430,6 +457,12 @@ extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
   if (!strcmp(name, "direct")) { h->opt_direct = (v != 0); return 0; }
   if (!strcmp(name, "diag")) { h->opt_diag = (v != 0); return 0; }
   if (!strcmp(name, "grad_lazy")) { h->opt_grad_lazy = (v != 0); return 0; }
+  if (!strcmp(name, "gradient")) {
+    if (v != 7 && v != 27) return fail("gradient: 7 or 27 points");
+    if (v == 27 && h->desc.ndim != 3) return fail("the 27-point gradient is three-dimensional");
+    h->opt_gradient = (int) v;
+    return 0;
+  }
   if (!strcmp(name, "p2p")) { if (join_comm(h)) return -1; h->opt_p2p = (v != 0); h->pushed_valid = false; return 0; }
   if (!strcmp(name, "loopback")) {
     if (h->desc.nranks > 1 && v) return fail("loopback is for single-rank lattices");
@@ -467,6 +500,7 @@ extern "C" long b200lb_get_option(const b200lb_t * h, const char * name) {
   if (!strcmp(name, "direct")) return h->opt_direct;
   if (!strcmp(name, "diag")) return h->opt_diag;
   if (!strcmp(name, "grad_lazy")) return h->opt_grad_lazy;
+  if (!strcmp(name, "gradient")) return h->opt_gradient;
   if (!strcmp(name, "p2p")) return h->opt_p2p;
   if (!strcmp(name, "p2p_ready")) return h->p2p_ready;
   if (!strcmp(name, "loopback")) return h->opt_loopback;
@@ -551,6 +585,14 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
   a.pull = pull; a.collide = collide;
   a.binary = (h->desc.ndist == 2);
   a.ghost = h->ghost;
+  a.noise = collide && h->noise_on;
+  if (a.noise) {
+    if (h->ops->nvel - h->ops->nhydro > B200LB_MAXNOISE)
+      return fail("isothermal fluctuations: the site generator yields %d variates per draw, nvel %d has %d ghost modes (src/noise.h:18)",
+		  B200LB_MAXNOISE, h->ops->nvel, h->ops->nvel - h->ops->nhydro);
+    if (!h->noise) return fail("isothermal fluctuations are on but noise_init was never called");
+    if (h->prm.kt < 0.0) return fail("negative temperature");
+  }
   a.vec = h->opt_vec;
   a.bx = h->opt_block;
   a.stream = h->s_main;
@@ -988,6 +1030,21 @@ static int run_grad7(b200lb_s * h) {
   return 0;
 }
 
+static int run_grad27(b200lb_s * h) {
+  const Layout & L = h->L;
+  if (h->desc.ndim != 3) return fail("the 27-point gradient is three-dimensional (ndim = %d)", h->desc.ndim);
+  if (need_planes(h, &h->grad, 3) || need_planes(h, &h->delsq, 1)) return -1;
+  dim3 block(G27_TZ, G27_TY, 1);
+  dim3 grid((L.n[2] + G27_TZ - 1)/G27_TZ, (L.n[1] + G27_TY - 1)/G27_TY,
+	    (L.n[0] + G27_NX - 1)/G27_NX);
+  grad27_kernel<<<grid, block, 0, h->s_main>>>(L, h->selfper[0], h->selfper[1], h->selfper[2],
+					       h->phi, h->grad, h->delsq);
+  CU(cudaGetLastError());
+  h->launches++;
+  h->grad_state = 0;
+  return 0;
+}
+
 extern "C" int b200lb_phi_halo(b200lb_t * h) {
   if (!h) return fail("null handle");
   if (!h->phi) return fail("no order parameter (ndist = 1)");
@@ -1032,6 +1089,14 @@ extern "C" int b200lb_grad7(b200lb_t * h) {
     return 0;
   }
   return run_grad7(h);
+}
+
+extern "C" int b200lb_grad27(b200lb_t * h) {
+  if (!h) return fail("null handle");
+  if (!h->phi) return fail("no order parameter (ndist = 1)");
+  // 40 B/site, against ~650 B/site of the binary collision that consumes it: the arrays
+  // are always written (the collision reads them; no in-register variant).
+  return run_grad27(h);
 }
 
 static int fill3(b200lb_s * h, double * data, int nf, const double v[3]) {
@@ -1105,7 +1170,8 @@ extern "C" int b200lb_step(b200lb_t * h, int nsteps) {
     if (h->desc.ndist == 2) {
       if (b200lb_phi_from_g(h)) return -1;
       if (b200lb_phi_halo(h)) return -1;
-      if (b200lb_grad7(h)) return -1;
+      if (h->opt_gradient == 27) { if (b200lb_grad27(h)) return -1; }
+      else if (b200lb_grad7(h)) return -1;
     }
     if (b200lb_hydro_u_zero(h, zero)) return -1;
     if (b200lb_collide(h)) return -1;
@@ -1262,6 +1328,99 @@ extern "C" int b200lb_f_upload(b200lb_t * h, const double * f, int layout) {
     h->pushed_valid = false;
   }
   return 0;
+}
+
+// ---------------------------------------------------------------------------
+// isothermal fluctuations: generator state (noise_t, src/noise.c)
+// ---------------------------------------------------------------------------
+
+extern "C" int b200lb_noise_init(b200lb_t * h, int master_seed) {
+  if (!h) return fail("null handle");
+  if (need_planes(h, &h->noise, 2)) return -1;
+  NoiseInit N;
+  memset(&N, 0, sizeof(N));
+  N.L = h->L;
+  for (int d = 0; d < 3; d++) N.dax[d] = h->ops->dax[d];
+  for (int a = 0; a < 3; a++) {
+    // uniform decomposition: cs_nlocal_offset = coords*nlocal (src/coords.c)
+    N.noffset[a] = h->desc.cartcoords[a]*h->desc.nlocal[a];
+    N.ntotal[a]  = h->desc.cartsz[a]*h->desc.nlocal[a];
+  }
+  const unsigned int seed0[4] = {13u, 12953u, 712357u, 22383979u};     // src/noise.c:147
+  for (int k = 0; k < 4; k++) N.seed0[k] = seed0[k];
+  if (master_seed > 0) N.seed0[0] = (unsigned int) master_seed;
+  dim3 block(128, 1, 1);
+  dim3 grid((h->L.na[2] + 127)/128, h->L.na[1], h->L.na[0]);
+  noise_init_kernel<<<grid, block, 0, h->s_main>>>(N, h->noise);
+  CU(cudaGetLastError());
+  h->launches++;
+  return 0;
+}
+
+extern "C" int b200lb_noise_present_set(b200lb_t * h, int on) {
+  if (!h) return fail("null handle");
+  if (on && h->ops->nvel - h->ops->nhydro > B200LB_MAXNOISE)
+    return fail("isothermal fluctuations: nvel %d has %d ghost modes, the site generator yields %d variates per draw (src/noise.h:18)",
+		h->ops->nvel, h->ops->nvel - h->ops->nhydro, B200LB_MAXNOISE);
+  h->noise_on = (on != 0);
+  return 0;
+}
+
+static int transfer(b200lb_s * h, double * dev, int nel, double * host, int layout, bool to_device);
+
+// noise_memcpy (src/noise.c:253-284). AOS: state[index*4 + ia] is two 64-bit elements
+// per site, which is the device's own pairing; SOA: four planes of 32-bit words.
+static int noise_transfer(b200lb_s * h, unsigned int * host, int layout, bool to_device) {
+  if (!h->noise) return fail("noise_init was never called");
+  if (layout == B200LB_HOST_AOS) {
+    return transfer(h, h->noise, 2, reinterpret_cast<double *>(host), layout, to_device);
+  }
+  if (layout != B200LB_HOST_SOA) return fail("unknown host layout %d", layout);
+  if (ensure_stage(h)) return -1;
+  if (join_comm(h)) return -1;
+  CU(cudaStreamSynchronize(h->s_main));
+  XferParams X;
+  memset(&X, 0, sizeof(X));
+  X.L = h->L;
+  for (int a = 0; a < 3; a++) { X.hostdim[a] = h->hostdim[a]; X.dax[a] = h->ops->dax[a]; }
+  X.dev = h->noise;
+  X.aos = 0; X.nel = 1;
+  const i64 ns = h->nsite_host;
+  const i64 chunk = (i64) (STAGE_BYTES/sizeof(unsigned int));
+  int turn = 0;
+  for (int ia = 0; ia < 4; ia++) {
+    for (i64 s0 = 0; s0 < ns; s0 += chunk, turn ^= 1) {
+      const i64 s1 = (s0 + chunk < ns) ? s0 + chunk : ns;
+      cudaStream_t st = h->s_x[turn];
+      X.stage = h->stage[turn]; X.hs0 = s0; X.hs1 = s1; X.e0 = ia/2; X.half = 1 + (ia & 1);
+      const size_t nb = (size_t) (s1 - s0)*sizeof(unsigned int);
+      const unsigned nblk = (unsigned) ((s1 - s0 + 255)/256);
+      if (to_device) {
+	CU(cudaMemcpyAsync(X.stage, host + ia*ns + s0, nb, cudaMemcpyHostToDevice, st));
+	xfer_kernel<1><<<nblk, 256, 0, st>>>(X);
+      }
+      else {
+	xfer_kernel<0><<<nblk, 256, 0, st>>>(X);
+	CU(cudaMemcpyAsync(host + ia*ns + s0, X.stage, nb, cudaMemcpyDeviceToHost, st));
+      }
+      CU(cudaGetLastError());
+      h->launches++;
+    }
+  }
+  CU(cudaStreamSynchronize(h->s_x[0]));
+  CU(cudaStreamSynchronize(h->s_x[1]));
+  return 0;
+}
+
+extern "C" int b200lb_noise_state_upload(b200lb_t * h, const unsigned int * state, int layout) {
+  if (!h || !state) return fail("null argument");
+  if (need_planes(h, &h->noise, 2)) return -1;
+  return noise_transfer(h, const_cast<unsigned int *>(state), layout, true);
+}
+
+extern "C" int b200lb_noise_state_download(b200lb_t * h, unsigned int * state, int layout) {
+  if (!h || !state) return fail("null argument");
+  return noise_transfer(h, state, layout, false);
 }
 
 extern "C" int b200lb_f_download(b200lb_t * h, double * f, int layout) {

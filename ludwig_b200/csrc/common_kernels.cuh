@@ -155,6 +155,137 @@ grad7_kernel(const Layout L, const int w0, const int w1, const int w2,
 }
 
 // ---------------------------------------------------------------------------
+// 27-point gradient and Laplacian (grad_3d_27pt_fluid_d2,
+// src/gradient_3d_27pt_fluid.c:75,223-352, nextra = 0):
+//   d_a phi = (1/2)(1/9) sum over the 9 neighbours in the plane normal to a of
+//             [phi(+a) - phi(-a)],   delsq = (1/9) [sum of 26 neighbours - 26 phi].
+// The terms are added in the reference's order so the results are bit-identical:
+//   d/dx (dy,dz) ascending; d/dy dx then dz ascending; d/dz dx then dy ascending,
+//   each pair as +phi(+a) then -phi(-a); delsq (dx,dy,dz) ascending, centre last.
+//
+// One block marches a (TY x TZ) tile of columns along x. Each z-y plane (with its
+// one-site apron, corners included) passes through shared memory once; a thread
+// keeps the 3 x 3 x 3 neighbourhood of its site in registers and shifts it by one
+// plane per step, so a site costs 9 shared loads instead of 80.
+// Traffic: 8 B read + 32 B written per site (+ 2/G27_NX plane re-reads).
+// ---------------------------------------------------------------------------
+
+#define G27_TZ 64
+#define G27_TY 4
+#define G27_NX 32
+#define G27_NE ((G27_TY + 2)*(G27_TZ + 2))
+
+__global__ void __launch_bounds__(G27_TZ*G27_TY)
+grad27_kernel(const Layout L, const int w0, const int w1, const int w2,
+	      const double * __restrict__ phi,
+	      double * __restrict__ grad, double * __restrict__ delsq) {
+
+  __shared__ double sm[2][G27_TY + 2][G27_TZ + 2];
+
+  const int tz = threadIdx.x, ty = threadIdx.y;
+  const int tid = ty*G27_TZ + tz;
+  const int i2 = blockIdx.x*G27_TZ + tz;           // interior coordinates, from 0
+  const int i1 = blockIdx.y*G27_TY + ty;
+  const int x0 = blockIdx.z*G27_NX;
+  const int x1 = min(x0 + G27_NX, L.n[0]);
+  const bool active = (i2 < L.n[2]) && (i1 < L.n[1]);
+
+  // The two tile elements this thread brings in per plane: halo-inclusive (y, z),
+  // clamped to the lattice, wrapped where the direction is periodic within the rank.
+  i64 off[2];
+  int er[2], ec[2];
+  #pragma unroll
+  for (int k = 0; k < 2; k++) {
+    const int e = min(tid + k*G27_TZ*G27_TY, G27_NE - 1);
+    er[k] = e/(G27_TZ + 2);
+    ec[k] = e - er[k]*(G27_TZ + 2);
+    int cy = min((int) blockIdx.y*G27_TY + er[k], L.n[1] + 1);
+    int cz = min((int) blockIdx.x*G27_TZ + ec[k], L.n[2] + 1);
+    if (w1) cy = (cy == 0) ? L.n[1] : ((cy == L.n[1] + 1) ? 1 : cy);
+    if (w2) cz = (cz == 0) ? L.n[2] : ((cz == L.n[2] + 1) ? 1 : cz);
+    off[k] = (i64) cy*L.s1 + L.z0 + cz;
+  }
+  const bool second = (tid + G27_TZ*G27_TY < G27_NE);
+
+  auto load_plane = [&](int slot, int xa) {
+    if (w0) xa = (xa == 0) ? L.n[0] : ((xa == L.n[0] + 1) ? 1 : xa);
+    const double * pl = phi + (i64) xa*L.s0;
+    sm[slot][er[0]][ec[0]] = __ldg(pl + off[0]);
+    if (second) sm[slot][er[1]][ec[1]] = __ldg(pl + off[1]);
+  };
+
+  double m[3][3], c[3][3], p[3][3];
+
+  load_plane(0, x0);                    // halo-inclusive plane of interior x0 - 1
+  __syncthreads();
+  #pragma unroll
+  for (int j = 0; j < 3; j++)
+    #pragma unroll
+    for (int k = 0; k < 3; k++) m[j][k] = sm[0][ty + j][tz + k];
+  load_plane(1, x0 + 1);
+  __syncthreads();
+  #pragma unroll
+  for (int j = 0; j < 3; j++)
+    #pragma unroll
+    for (int k = 0; k < 3; k++) c[j][k] = sm[1][ty + j][tz + k];
+
+  const double r9 = 1.0/9.0;
+  const double hr9 = 0.5*r9;
+
+  for (int x = x0; x < x1; x++) {
+    const int slot = (x - x0) & 1;
+    load_plane(slot, x + 2);
+    __syncthreads();
+    #pragma unroll
+    for (int j = 0; j < 3; j++)
+      #pragma unroll
+      for (int k = 0; k < 3; k++) p[j][k] = sm[slot][ty + j][tz + k];
+
+    if (active) {
+      double gx = p[0][0] - m[0][0];
+      double gy = m[2][0] - m[0][0];
+      double gz = m[0][2] - m[0][0];
+      double d2 = m[0][0];
+      #pragma unroll
+      for (int q = 1; q < 9; q++) {
+	const int a = q/3, b = q - 3*a;
+	gx = gx + p[a][b];  gx = gx - m[a][b];
+	d2 = d2 + m[a][b];
+      }
+      // d/dy: planes x-1, x, x+1; z ascending.  d/dz: planes, y ascending.
+      #pragma unroll
+      for (int k = 1; k < 3; k++) { gy = gy + m[2][k]; gy = gy - m[0][k]; }
+      #pragma unroll
+      for (int k = 0; k < 3; k++) { gy = gy + c[2][k]; gy = gy - c[0][k]; }
+      #pragma unroll
+      for (int k = 0; k < 3; k++) { gy = gy + p[2][k]; gy = gy - p[0][k]; }
+      #pragma unroll
+      for (int j = 1; j < 3; j++) { gz = gz + m[j][2]; gz = gz - m[j][0]; }
+      #pragma unroll
+      for (int j = 0; j < 3; j++) { gz = gz + c[j][2]; gz = gz - c[j][0]; }
+      #pragma unroll
+      for (int j = 0; j < 3; j++) { gz = gz + p[j][2]; gz = gz - p[j][0]; }
+      #pragma unroll
+      for (int q = 0; q < 9; q++) { if (q != 4) d2 = d2 + c[q/3][q - 3*(q/3)]; }
+      #pragma unroll
+      for (int q = 0; q < 9; q++) d2 = d2 + p[q/3][q - 3*(q/3)];
+      // separately rounded product (no FMA contraction): bit parity
+      d2 = d2 - __dmul_rn(26.0, c[1][1]);
+
+      const i64 site = (i64)(x + L.h[0])*L.s0 + (i64)(i1 + L.h[1])*L.s1 + L.z0 + L.h[2] + i2;
+      grad[site]           = hr9*gx;
+      grad[L.nsd + site]   = hr9*gy;
+      grad[2*L.nsd + site] = hr9*gz;
+      delsq[site]          = r9*d2;
+    }
+    #pragma unroll
+    for (int j = 0; j < 3; j++)
+      #pragma unroll
+      for (int k = 0; k < 3; k++) { m[j][k] = c[j][k]; c[j][k] = p[j][k]; }
+  }
+}
+
+// ---------------------------------------------------------------------------
 // fills (hydro_field_set, src/hydro.c:381-398) and uniform-plane helpers
 // ---------------------------------------------------------------------------
 
@@ -203,6 +334,8 @@ struct XferParams {
   int nel;            // planes per site in an AOS piece
   int e0;             // first device plane (SOA piece: the plane)
   int aos;
+  int half;           // SOA piece of 32-bit words: 1 = low, 2 = high half of the 64-bit device
+                      // element, stage holds unsigned ints (noise state); 0 = doubles
 };
 
 template <int TO_DEVICE>
@@ -233,10 +366,67 @@ xfer_kernel(const XferParams X) {
       else st[e] = X.dev[(i64)(X.e0 + e)*L.nsd + site];
     }
   }
+  else if (X.half) {
+    unsigned int * dv = reinterpret_cast<unsigned int *>(X.dev + (i64) X.e0*L.nsd + site) + (X.half - 1);
+    unsigned int * st = reinterpret_cast<unsigned int *>(X.stage) + (hs - X.hs0);
+    if (TO_DEVICE) *dv = *st;
+    else *st = *dv;
+  }
   else {
     if (TO_DEVICE) X.dev[(i64) X.e0*L.nsd + site] = X.stage[hs - X.hs0];
     else X.stage[hs - X.hs0] = X.dev[(i64) X.e0*L.nsd + site];
   }
+}
+
+// ---------------------------------------------------------------------------
+// noise_init (src/noise.c:136-233): decomposition-independent seeding of the per-site
+// generators. A site's first state is seed0 + its GLOBAL periodic position (1-based);
+// four outputs of KISS99 from there become the state it keeps. Halo sites included.
+// State words are stored pairwise as 64-bit elements: plane 0 = (s0,s1), plane 1 = (s2,s3).
+// ---------------------------------------------------------------------------
+
+struct NoiseInit {
+  Layout L;
+  int dax[3];          // device axis -> physical axis
+  int noffset[3];      // physical: global offset of this rank's interior
+  int ntotal[3];       // physical: global extent
+  unsigned int seed0[4];
+};
+
+__device__ __forceinline__ unsigned int noise_kiss99(unsigned int (&w)[4]) {
+  w[0] = 69069u*w[0] + 1234567u;
+  unsigned int x = w[1];
+  x ^= x << 17; x ^= x >> 13; x ^= x << 5;
+  w[1] = x;
+  w[2] = 36969u*(w[2] & 65535u) + (w[2] >> 16);
+  w[3] = 18000u*(w[3] & 65535u) + (w[3] >> 16);
+  return w[1] + (w[0] ^ ((w[2] << 16) + w[3]));
+}
+
+__global__ void __launch_bounds__(128)
+noise_init_kernel(const NoiseInit N, double * __restrict__ state) {
+  const Layout & L = N.L;
+  const int d2 = blockIdx.x*blockDim.x + threadIdx.x;
+  const int d1 = blockIdx.y, d0 = blockIdx.z;
+  if (d2 >= L.na[2]) return;
+  const int dc[3] = {d0, d1, d2};
+  unsigned int w[4] = {N.seed0[0], N.seed0[1], N.seed0[2], N.seed0[3]};
+  #pragma unroll
+  for (int d = 0; d < 3; d++) {
+    const int a = N.dax[d];
+    // local physical coordinate, 0 .. nlocal + 1; the unit axis of a 2-d lattice sits at 1
+    const int c = (L.h[d] == 0) ? 1 : dc[d];
+    int g = N.noffset[a] + c;
+    if (g < 1) g += N.ntotal[a];
+    if (g > N.ntotal[a]) g -= N.ntotal[a];
+    w[a] += (unsigned int) g;
+  }
+  unsigned int o[4];
+  #pragma unroll
+  for (int k = 0; k < 4; k++) o[k] = noise_kiss99(w);
+  const i64 site = (i64) d0*L.s0 + (i64) d1*L.s1 + L.z0 + d2;
+  state[site]         = __hiloint2double((int) o[1], (int) o[0]);
+  state[L.nsd + site] = __hiloint2double((int) o[3], (int) o[2]);
 }
 
 // ---------------------------------------------------------------------------

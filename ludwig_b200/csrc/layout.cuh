@@ -26,6 +26,7 @@ struct Layout {
 };
 
 #define B200LB_MAXGHOST 17
+#define B200LB_MAXNOISE 10     // variates per draw of the site generator (NNOISE_MAX, src/noise.h:18)
 
 // Per-launch parameters (passed by value: they live in the constant bank).
 struct KParams {
@@ -48,6 +49,12 @@ struct KParams {
   double fg[3];           // uniform part of the force: force_global + constant field value
   double rtau2, A, B, kappa;
   double gkeep[B200LB_MAXGHOST];   // 1 - rtau_k for each ghost mode
+  // isothermal fluctuations (src/noise.c, src/collision.c:476-515,1663-1745)
+  double * noise;         // [2][nsd]: KISS99 words (s0,s1) and (s2,s3) of every site as 64-bit pairs
+  double nv_diag, nv_off; // stress variance: var_eta sqrt(2) on the diagonal, var_eta off it
+  double nv_bulk;         // variance of the trace
+  double nv_ghost[B200LB_MAXNOISE];  // per ghost mode
+  double nlv_big, nlv_small;         // sqrt(2 + sqrt 2), sqrt(2 - sqrt 2): the discrete levels
 };
 
 // Ghost-mode projectors (host-built, one __constant__ copy per model).

@@ -13,8 +13,9 @@ static __constant__ GhostTab c_ghost;
 
 typedef B200LB_MODEL MODEL;
 
-template <int VEC, bool PULL, bool COLLIDE, bool BINARY, bool GHOST>
+template <int VEC, bool PULL, bool COLLIDE, bool BINARY, int GM>
 static cudaError_t launch_one(SweepArgs & a) {
+  constexpr bool GHOST = (GM != 0);
   const KParams & P = a.P;
   const int n2 = P.hi[2] - P.lo[2], n1 = P.hi[1] - P.lo[1], n0 = P.hi[0] - P.lo[0];
   a.nblocks = 0;
@@ -29,11 +30,11 @@ static cudaError_t launch_one(SweepArgs & a) {
   dim3 grid((nt2 + bx - 1)/bx, (n1 + by - 1)/by, n0);
   a.nblocks = (long long) grid.x*grid.y*grid.z;
   if (COLLIDE && a.diag) {
-    lb_sweep_kernel<MODEL, VEC, PULL, COLLIDE, BINARY, GHOST, COLLIDE>
+    lb_sweep_kernel<MODEL, VEC, PULL, COLLIDE, BINARY, GM, COLLIDE>
       <<<grid, block, 0, a.stream>>>(P);
   }
   else {
-    lb_sweep_kernel<MODEL, VEC, PULL, COLLIDE, BINARY, GHOST, false>
+    lb_sweep_kernel<MODEL, VEC, PULL, COLLIDE, BINARY, GM, false>
       <<<grid, block, 0, a.stream>>>(P);
   }
   return cudaGetLastError();
@@ -42,25 +43,43 @@ static cudaError_t launch_one(SweepArgs & a) {
 template <bool PULL, bool COLLIDE>
 static cudaError_t launch_pc(SweepArgs & a) {
   constexpr bool HAVE_BINARY = (MODEL::NDIM == 3);
+  constexpr bool HAVE_NOISE = (MODEL::NVEL - MODEL::NHYDRO <= B200LB_MAXNOISE);
   if constexpr (!COLLIDE) {
     // pure streaming: collision flags are irrelevant
     if (a.binary) {
       if (!HAVE_BINARY) return cudaErrorInvalidValue;
-      if (a.vec == 2) return launch_one<2, PULL, false, HAVE_BINARY, false>(a);
-      return launch_one<1, PULL, false, HAVE_BINARY, false>(a);
+      if (a.vec == 2) return launch_one<2, PULL, false, HAVE_BINARY, 0>(a);
+      return launch_one<1, PULL, false, HAVE_BINARY, 0>(a);
     }
-    if (a.vec == 2) return launch_one<2, PULL, false, false, false>(a);
-    return launch_one<1, PULL, false, false, false>(a);
+    if (a.vec == 2) return launch_one<2, PULL, false, false, 0>(a);
+    return launch_one<1, PULL, false, false, 0>(a);
   }
   else {
+  if (a.noise) {
+    // fluctuating collision: ghost back-projection always, forward projection when the
+    // scheme keeps ghost modes. One draw of the site generator yields ten variates
+    // (src/noise.h:18), which is not enough for the 17 ghost modes of D3Q27.
+    if constexpr (HAVE_NOISE) {
+      if (a.binary) {
+	if (!HAVE_BINARY) return cudaErrorInvalidValue;
+	if (a.ghost) return launch_one<1, PULL, COLLIDE, HAVE_BINARY, 3>(a);
+	return launch_one<1, PULL, COLLIDE, HAVE_BINARY, 2>(a);
+      }
+      if (a.ghost) return launch_one<1, PULL, COLLIDE, false, 3>(a);
+      return launch_one<1, PULL, COLLIDE, false, 2>(a);
+    }
+    else {
+      return cudaErrorInvalidValue;
+    }
+  }
   if (a.binary) {
     if (!HAVE_BINARY) return cudaErrorInvalidValue;
-    if (a.ghost) return launch_one<1, PULL, COLLIDE, HAVE_BINARY, true>(a);
-    return launch_one<1, PULL, COLLIDE, HAVE_BINARY, false>(a);
+    if (a.ghost) return launch_one<1, PULL, COLLIDE, HAVE_BINARY, 1>(a);
+    return launch_one<1, PULL, COLLIDE, HAVE_BINARY, 0>(a);
   }
-  if (a.ghost) return launch_one<1, PULL, COLLIDE, false, true>(a);
-  if (a.vec == 2) return launch_one<2, PULL, COLLIDE, false, false>(a);
-  return launch_one<1, PULL, COLLIDE, false, false>(a);
+  if (a.ghost) return launch_one<1, PULL, COLLIDE, false, 1>(a);
+  if (a.vec == 2) return launch_one<2, PULL, COLLIDE, false, 0>(a);
+  return launch_one<1, PULL, COLLIDE, false, 0>(a);
   }
 }
 
@@ -112,6 +131,17 @@ const ModelOps * B200LB_OPS_FN(void) {
     for (int p = 0; p < MODEL::NVEL; p++) {
       for (int a = 0; a < 3; a++) ops.cv[p][a] = MODEL::cv(p, a);
       ops.wv[p] = MODEL::wv(p);
+    }
+    // sum_p w_p ma[m][p]^2 of the ghost rows: the reference's rna[] = 1/na[]
+    // (src/model.c:378), which scales the ghost-mode noise (src/collision.c:1811)
+    for (int k = 0; k < MODEL::NVEL - MODEL::NHYDRO; k++) {
+      double wip = 0.0;
+      for (int p = 0; p < MODEL::NVEL; p++) {
+	const int c[3] = {MODEL::cv(p, 0), MODEL::cv(p, 1), MODEL::cv(p, 2)};
+	const double r = ghost_row(MODEL::NVEL, k, c);
+	wip += MODEL::wv(p)*r*r;
+      }
+      ops.ghost_norm[k] = wip;
     }
     ops.sweep = sweep_impl;
     ops.phi_from_g = phi_impl;

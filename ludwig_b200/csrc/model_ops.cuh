@@ -10,6 +10,7 @@
 struct SweepArgs {
   KParams P;
   bool pull, collide, binary, ghost;
+  bool noise;         // isothermal fluctuations on (collide only)
   bool diag;          // accumulate conserved sums in the sweep (collide only)
   long long nblocks;  // out: blocks launched (= diagnostic partials written)
   int vec;            // sites per thread (1 or 2)
@@ -22,6 +23,7 @@ struct ModelOps {
   int dax[3];                                   // device axis -> physical axis
   int cv[27][3];
   double wv[27];
+  double ghost_norm[B200LB_MAXGHOST];           // sum_p w_p ma[k][p]^2 per ghost mode
   cudaError_t (*sweep)(SweepArgs &);
   cudaError_t (*phi_from_g)(const Layout &, const int wrap[3], const double * g,
 			    double * phi, bool pull, cudaStream_t);

@@ -39,12 +39,20 @@ template <bool NC> __device__ __forceinline__ double2 ld2(const double * p) {
 //   sth    thermodynamic stress added to the equilibrium stress (binary fluid,
 //          src/collision.c:833-848), symmetric storage, or nullptr
 // Writes rho and u = (rho u + F/2)/rho (src/collision.c:355-382).
+//   GM     ghost-mode handling: bit 0 = the scheme keeps a fraction of the incoming
+//          ghost modes (BGK, TRT), bit 1 = fluctuations: shat (symmetric storage) is
+//          added to the relaxed stress and ghat[k] to ghost mode k
+//          (src/collision.c:526-544)
 // ---------------------------------------------------------------------------
 
-template <class M, bool GHOST, bool STH>
+template <class M, int GM, bool STH>
 __device__ __forceinline__ void
 mrt_site(double (&f)[M::NVEL], const double (&F)[3], const double * sth,
+	 const double * shat, const double * ghat,
 	 const KParams & P, double & rho_out, double (&u)[3]) {
+
+  constexpr bool GHOST = (GM & 1) != 0;
+  constexpr bool NOISE = (GM & 2) != 0;
 
   constexpr int Q  = M::NVEL;
   constexpr int ND = M::NDIM;
@@ -54,7 +62,7 @@ mrt_site(double (&f)[M::NVEL], const double (&F)[3], const double * sth,
   constexpr double rdim = 1.0/ND;
 
   // ghost modes of the incoming state (only when some are kept)
-  double mg[GHOST ? NG : 1];
+  double mg[(GM != 0) ? NG : 1];
   if (GHOST) {
     const GhostTab & T = ghost_tab<M>();
     #pragma unroll
@@ -131,6 +139,7 @@ mrt_site(double (&f)[M::NVEL], const double (&F)[3], const double * sth,
       double s = S[k] - P.rtau_shear*(S[k] - seq[k]);
       if (a == b) s += rdim*tr_s;
       s += fcorr*(u[a]*F[b] + F[a]*u[b]);
+      if (NOISE) s += shat[k];
       S[k] = s;
     }
   }
@@ -165,7 +174,11 @@ mrt_site(double (&f)[M::NVEL], const double (&F)[3], const double * sth,
     f[Q - p] = M::wv(p)*(ev - od);
   }
 
-  if (GHOST) {
+  if (NOISE) {
+    #pragma unroll
+    for (int k = 0; k < NG; k++) mg[k] = GHOST ? mg[k] + ghat[k] : ghat[k];
+  }
+  if (GM != 0) {
     const GhostTab & T = ghost_tab<M>();
     #pragma unroll
     for (int p = 0; p < Q; p++) {
@@ -239,13 +252,73 @@ phi_site(double (&g)[M::NVEL], double phi, double mu, const double (&u)[3],
 }
 
 // ---------------------------------------------------------------------------
+// Isothermal fluctuations. Every site owns a KISS99 generator (Marsaglia 1999; four
+// 32-bit words: a linear congruential word, a three-shift xorshift word and two 16-bit
+// multiply-with-carry words, src/noise.c:456-472); one 32-bit output, with its two
+// low bits dropped, yields up to ten three-bit indices into Ladd's eight-level
+// discrete unit-variance distribution (src/noise.c:70-77,398-425).
+// ---------------------------------------------------------------------------
+
+__device__ __forceinline__ unsigned int kiss99(unsigned int (&w)[4]) {
+  w[0] = 69069u*w[0] + 1234567u;
+  unsigned int x = w[1];
+  x ^= x << 17; x ^= x >> 13; x ^= x << 5;
+  w[1] = x;
+  w[2] = 36969u*(w[2] & 65535u) + (w[2] >> 16);
+  w[3] = 18000u*(w[3] & 65535u) + (w[3] >> 16);
+  return w[1] + (w[0] ^ ((w[2] << 16) + w[3]));
+}
+
+// level b of {-big, -small, 0, 0, 0, 0, +small, +big}
+__device__ __forceinline__ double noise_level(unsigned int b, double big, double small) {
+  b &= 7u;
+  const double mag = (b == 0u || b == 7u) ? big : ((b == 1u || b == 6u) ? small : 0.0);
+  return (b < 2u) ? -mag : mag;
+}
+
+// Random stress (symmetric storage) and ghost terms for one site: two draws of the
+// site's generator, six variates for the stress (always six, also in two dimensions)
+// and NVEL - NHYDRO for the ghosts (src/collision.c:1826-1920). w is advanced.
+template <class M>
+__device__ __forceinline__ void
+fluctuations(unsigned int (&w)[4], const KParams & P,
+	     double (&shat)[NSym<M>::value], double (&ghat)[M::NVEL - M::NHYDRO]) {
+
+  constexpr int ND = M::NDIM;
+  constexpr int NG = M::NVEL - M::NHYDRO;
+  static_assert(NG <= B200LB_MAXNOISE, "one draw yields at most ten variates");
+
+  unsigned int bits = kiss99(w) >> 2;
+  double r[6];
+  #pragma unroll
+  for (int k = 0; k < 6; k++) { r[k] = noise_level(bits, P.nlv_big, P.nlv_small); bits >>= 3; }
+  // r = xx xy xz yy yz zz
+  const double dg[3] = {r[0], r[3], r[5]};
+  const double od[3] = {r[1], r[2], r[4]};        // xy xz yz
+  const double tr = (1.0/ND)*(dg[0] + dg[1] + (ND - 2.0)*dg[2]);
+  #pragma unroll
+  for (int a = 0; a < ND; a++) {
+    shat[sidx<M>(a, a)] = (dg[a] - tr)*P.nv_diag + tr*P.nv_bulk;
+    #pragma unroll
+    for (int b = a + 1; b < ND; b++) shat[sidx<M>(a, b)] = od[a + b - 1]*P.nv_off;
+  }
+
+  bits = kiss99(w) >> 2;
+  #pragma unroll
+  for (int k = 0; k < NG; k++) {
+    ghat[k] = P.nv_ghost[k]*noise_level(bits, P.nlv_big, P.nlv_small);
+    bits >>= 3;
+  }
+}
+
+// ---------------------------------------------------------------------------
 // The sweep. Thread (x) covers VEC consecutive sites of the contiguous axis,
 // thread (y) a row; blockIdx.z is the slowest axis. With VEC = 2 populations
 // moving along the contiguous axis are read as two 64-bit loads (they straddle
 // the aligned pair), all others and every store are 128-bit.
 // ---------------------------------------------------------------------------
 
-template <class M, int VEC, bool PULL, bool COLLIDE, bool BINARY, bool GHOST, bool DIAG>
+template <class M, int VEC, bool PULL, bool COLLIDE, bool BINARY, int GM, bool DIAG>
 __global__ void __launch_bounds__(256)
 lb_sweep_kernel(const KParams P) {
 
@@ -340,6 +413,20 @@ lb_sweep_kernel(const KParams P) {
 	for (int a = 0; a < ND; a++) F[a] += P.force[a*L.nsd + s];
       }
       double rho, u[3];
+      constexpr int NGH = (Q > M::NHYDRO) ? Q - M::NHYDRO : 1;
+      double shat[NSym<M>::value], ghat[NGH];
+      if constexpr ((GM & 2) != 0) {
+	// the site's generator: words (s0,s1) and (s2,s3) travel as two 64-bit values
+	double * ns = P.noise + s;
+	const double w01 = ns[0], w23 = ns[L.nsd];
+	unsigned int w[4] = {(unsigned int) __double2loint(w01), (unsigned int) __double2hiint(w01),
+			     (unsigned int) __double2loint(w23), (unsigned int) __double2hiint(w23)};
+	fluctuations<M>(w, P, shat, ghat);
+	if (v < nv) {
+	  ns[0]     = __hiloint2double((int) w[1], (int) w[0]);
+	  ns[L.nsd] = __hiloint2double((int) w[3], (int) w[2]);
+	}
+      }
       if (BINARY) {
 	const double phi = P.phi[s];
 	double dsq;
@@ -373,11 +460,11 @@ lb_sweep_kernel(const KParams P) {
 	  }
 	}
 	const double mu = P.A*phi + P.B*phi*phi*phi - P.kappa*dsq;
-	mrt_site<M, GHOST, true>(f[0][v], F, sth, P, rho, u);
+	mrt_site<M, GM, true>(f[0][v], F, sth, shat, ghat, P, rho, u);
 	phi_site<M>(f[NDIST - 1][v], phi, mu, u, P.rtau2);
       }
       else {
-	mrt_site<M, GHOST, false>(f[0][v], F, nullptr, P, rho, u);
+	mrt_site<M, GM, false>(f[0][v], F, nullptr, shat, ghat, P, rho, u);
       }
       if (DIAG && (v < nv)) {
 	// conserved sums of the state that entered this collision: rho, rho^2, min,

@@ -90,7 +90,7 @@ int lb_collide(lb_t * lb, hydro_t * hydro, map_t * map, noise_t * noise, fe_t * 
 
   b200lb_param_t p;
 
-  (void) map; (void) noise; (void) visc;
+  (void) map; (void) visc;
   if (hydro == NULL) return 0;               /* src/collision.c:149 */
 
   memset(&p, 0, sizeof(p));
@@ -108,8 +108,54 @@ int lb_collide(lb_t * lb, hydro_t * hydro, map_t * map, noise_t * noise, fe_t * 
     }
     p.a = fs->param.a; p.b = fs->param.b; p.kappa = fs->param.kappa;
   }
+  /* lb_collision_noise_var_set (src/collision.c:1572): variances follow kt */
+  p.kt = lb->phys->kt;
+  TRY(b200lb_noise_present_set(lb->target, (noise != NULL) && noise->on[NOISE_RHO]));
   TRY(b200lb_set_param(lb->target, &p));
   TRY(b200lb_collide(lb->target));
+  return 0;
+}
+
+/* noise_t: the generator state lives on the device; the host array is the interchange
+ * copy noise_memcpy moves, as for lb->f. */
+
+int noise_create(lb_t * lb, noise_t ** pnoise) {
+  noise_t * obj = (noise_t *) calloc(1, sizeof(noise_t));
+  if (obj == NULL) return -1;
+  obj->lb = lb;
+  obj->nsites = lb->nsite;
+  *pnoise = obj;
+  return 0;
+}
+
+int noise_free(noise_t * obj) { if (obj) { free(obj->state); free(obj); } return 0; }
+
+int noise_init(noise_t * obj, int master_seed) {
+  if (obj->state == NULL) {
+    obj->state = (unsigned int *) calloc((size_t) NNOISE_STATE*obj->nsites, sizeof(unsigned int));
+    if (obj->state == NULL) return -1;
+  }
+  TRY(b200lb_noise_init(obj->lb->target, master_seed));
+  return noise_memcpy(obj, tdpMemcpyDeviceToHost);
+}
+
+int noise_present_set(noise_t * obj, noise_enum_t type, int present) {
+  obj->on[type] = present;
+  return 0;
+}
+
+int noise_present(noise_t * obj, noise_enum_t type, int * present) {
+  *present = obj->on[type];
+  return 0;
+}
+
+int noise_memcpy(noise_t * obj, tdpMemcpyKind flag) {
+  if (flag == tdpMemcpyHostToDevice) {
+    TRY(b200lb_noise_state_upload(obj->lb->target, obj->state, B200LB_HOST_AOS));
+  }
+  else {
+    TRY(b200lb_noise_state_download(obj->lb->target, obj->state, B200LB_HOST_AOS));
+  }
   return 0;
 }
 
@@ -214,6 +260,7 @@ int field_grad_create(field_t * phi, field_grad_t ** pg) {
   field_grad_t * g = (field_grad_t *) calloc(1, sizeof(field_grad_t));
   if (g == NULL) return -1;
   g->field = phi; g->lb = phi->lb;
+  g->d2 = grad_3d_7pt_fluid_d2;
   g->grad = (double *) calloc((size_t) 3*phi->nsites, sizeof(double));
   g->delsq = (double *) calloc((size_t) phi->nsites, sizeof(double));
   if (g->grad == NULL || g->delsq == NULL) return -1;
@@ -223,10 +270,28 @@ int field_grad_create(field_t * phi, field_grad_t ** pg) {
 
 int field_grad_free(field_grad_t * g) { if (g) { free(g->grad); free(g->delsq); free(g); } return 0; }
 
-int field_grad_compute(field_grad_t * g) {
-  /* obj->d2(obj) with d2 = grad_3d_7pt_fluid_d2 (src/field_grad.c:312) */
+/* The reference's function-pointer plug point (src/field_grad.h:22,47): gradient_rt.c
+ * registers one of these per "fd_gradient_calculation" key. */
+int grad_3d_7pt_fluid_d2(field_grad_t * g) {
   TRY(b200lb_grad7(g->lb->target));
   return 0;
+}
+
+int grad_3d_27pt_fluid_d2(field_grad_t * g) {
+  TRY(b200lb_grad27(g->lb->target));
+  return 0;
+}
+
+int field_grad_set(field_grad_t * g, grad_ft d2, grad_ft d4) {
+  (void) d4;                      /* no fourth-order consumer on this path */
+  if (g == NULL || d2 == NULL) return -1;
+  g->d2 = d2;
+  return 0;
+}
+
+int field_grad_compute(field_grad_t * g) {
+  /* obj->d2(obj) (src/field_grad.c:312) */
+  return g->d2(g);
 }
 
 int field_grad_memcpy(field_grad_t * g, tdpMemcpyKind flag) {

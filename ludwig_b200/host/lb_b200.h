@@ -52,6 +52,7 @@ typedef struct physics_s {
   double eta_bulk;
   double fbody[3];
   double mobility;
+  double kt;                       /* physics_kt: isothermal fluctuations */
 } physics_t;
 
 typedef struct lb_data_options_s {
@@ -82,12 +83,22 @@ typedef struct hydro_s {
   lb_t * lb;
 } hydro_t;
 
-typedef struct field_grad_s { field_t * field; double * grad; double * delsq; lb_t * lb; } field_grad_t;
+typedef struct field_grad_s field_grad_t;
+typedef int (* grad_ft)(field_grad_t * fgrad);           /* src/field_grad.h:22 */
+struct field_grad_s { field_t * field; double * grad; double * delsq; lb_t * lb; grad_ft d2; };
 
 typedef struct fe_symm_s { fe_symm_param_t param; field_t * phi; field_grad_t * dphi; } fe_symm_t;
 
 typedef void map_t;     /* configs are all-fluid: not consulted */
-typedef void noise_t;   /* isothermal fluctuations off */
+/* noise_t (src/noise.h:38-50): per-site generator state and the on/off switches */
+typedef enum {NOISE_RHO = 0, NOISE_PHI, NOISE_QAB, NOISE_END} noise_enum_t;
+#define NNOISE_STATE 4
+typedef struct noise_s {
+  int nsites;
+  int on[NOISE_END];
+  unsigned int * state;            /* host copy, state[index*NNOISE_STATE + ia] */
+  lb_t * lb;
+} noise_t;
 typedef void visc_t;    /* no viscosity model */
 typedef void fe_t;
 
@@ -103,6 +114,13 @@ int lb_collide(lb_t * lb, hydro_t * hydro, map_t * map, noise_t * noise, fe_t * 
 int lb_halo(lb_t * lb);
 int lb_halo_swap(lb_t * lb, lb_halo_enum_t flag);
 int lb_propagation(lb_t * lb);
+
+int noise_create(lb_t * lb, noise_t ** noise);                      /* src/noise.c:56 */
+int noise_free(noise_t * noise);
+int noise_init(noise_t * noise, int master_seed);                  /* src/noise.c:136 */
+int noise_present_set(noise_t * noise, noise_enum_t type, int present);   /* src/noise.c:557 */
+int noise_present(noise_t * noise, noise_enum_t type, int * present);
+int noise_memcpy(noise_t * noise, tdpMemcpyKind flag);             /* src/noise.c:253 */
 
 int hydro_create(lb_t * lb, hydro_t ** hydro);
 int hydro_free(hydro_t * hydro);
@@ -121,6 +139,9 @@ int phi_lb_to_field(field_t * phi, lb_t * lb);
 int field_grad_create(field_t * phi, field_grad_t ** grad);           /* d2 = grad_3d_7pt_fluid_d2 */
 int field_grad_free(field_grad_t * grad);
 int field_grad_compute(field_grad_t * grad);
+int field_grad_set(field_grad_t * grad, grad_ft d2, grad_ft d4);   /* src/field_grad.h:47 */
+int grad_3d_7pt_fluid_d2(field_grad_t * grad);            /* src/gradient_3d_7pt_fluid.c:75 (default) */
+int grad_3d_27pt_fluid_d2(field_grad_t * grad);           /* src/gradient_3d_27pt_fluid.c:75 */
 int field_grad_memcpy(field_grad_t * grad, tdpMemcpyKind flag);
 
 int fe_symm_create(field_t * phi, field_grad_t * dphi, fe_symm_t ** fe);

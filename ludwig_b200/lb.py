@@ -31,7 +31,9 @@ ABI_SYMBOLS = [
     "b200lb_f_upload", "b200lb_f_download", "b200lb_field_upload",
     "b200lb_field_download", "b200lb_set_param", "b200lb_hydro_f_zero",
     "b200lb_hydro_u_zero", "b200lb_hydro_rho0", "b200lb_hydro_correct_momentum", "b200lb_collide", "b200lb_halo", "b200lb_halo_swap",
-    "b200lb_propagate", "b200lb_phi_from_g", "b200lb_phi_halo", "b200lb_grad7",
+    "b200lb_propagate", "b200lb_phi_from_g", "b200lb_phi_halo", "b200lb_grad7", "b200lb_grad27",
+    "b200lb_noise_init", "b200lb_noise_present_set", "b200lb_noise_state_upload",
+    "b200lb_noise_state_download",
     "b200lb_step", "b200lb_stats", "b200lb_step_diag", "b200lb_sync", "b200lb_nccl_unique_id",
     "b200lb_comm_init", "b200lb_p2p_export", "b200lb_p2p_import", "b200lb_timer_start", "b200lb_timer_stop",
     "b200lb_launch_count", "b200lb_host_alloc", "b200lb_host_free",
@@ -59,6 +61,7 @@ class Param(ctypes.Structure):
         ("eta_bulk", ctypes.c_double), ("force_global", ctypes.c_double * 3),
         ("nrelax", ctypes.c_int), ("mobility", ctypes.c_double),
         ("a", ctypes.c_double), ("b", ctypes.c_double), ("kappa", ctypes.c_double),
+        ("kt", ctypes.c_double),
     ]
 
 
@@ -101,10 +104,14 @@ def load():
     for name in ("b200lb_field_upload", "b200lb_field_download"):
         getattr(L, name).argtypes = [vp, ctypes.c_int, vp, ctypes.c_int]
     for name in ("b200lb_destroy", "b200lb_collide", "b200lb_halo", "b200lb_propagate",
-                 "b200lb_phi_from_g", "b200lb_phi_halo", "b200lb_grad7", "b200lb_sync",
+                 "b200lb_phi_from_g", "b200lb_phi_halo", "b200lb_grad7", "b200lb_grad27", "b200lb_sync",
                  "b200lb_hydro_correct_momentum", "b200lb_timer_start", "b200lb_nsite", "b200lb_launch_count"):
         getattr(L, name).argtypes = [vp]
     L.b200lb_halo_swap.argtypes = [vp, ctypes.c_int]
+    L.b200lb_noise_init.argtypes = [vp, ctypes.c_int]
+    L.b200lb_noise_present_set.argtypes = [vp, ctypes.c_int]
+    L.b200lb_noise_state_upload.argtypes = [vp, vp, ctypes.c_int]
+    L.b200lb_noise_state_download.argtypes = [vp, vp, ctypes.c_int]
     L.b200lb_hydro_rho0.argtypes = [vp, ctypes.c_double]
     L.b200lb_step.argtypes = [vp, ctypes.c_int]
     L.b200lb_hydro_f_zero.argtypes = [vp, ctypes.POINTER(ctypes.c_double)]
@@ -212,8 +219,9 @@ class Lattice:
         return int(self.L.b200lb_get_option(self.h, name.encode()))
 
     def set_param(self, rho0=1.0, eta_shear=0.1, eta_bulk=0.1, force=(0.0, 0.0, 0.0),
-                  nrelax=RELAX_M10, mobility=0.0, a=0.0, b=0.0, kappa=0.0):
+                  nrelax=RELAX_M10, mobility=0.0, a=0.0, b=0.0, kappa=0.0, kt=0.0):
         p = Param()
+        p.kt = kt
         p.rho0, p.eta_shear, p.eta_bulk = rho0, eta_shear, eta_bulk
         p.force_global[:] = force
         p.nrelax, p.mobility, p.a, p.b, p.kappa = nrelax, mobility, a, b, kappa
@@ -275,8 +283,35 @@ class Lattice:
     def field_halo(self):
         self._ck(self.L.b200lb_phi_halo(self.h))
 
+    def field_grad_set(self, npt):
+        """Which d2 stencil field_grad_compute() and step() run: 7 (grad_3d_7pt_fluid_d2)
+        or 27 (grad_3d_27pt_fluid_d2); the reference's field_grad_set plug point."""
+        self.set_option("gradient", int(npt))
+
     def field_grad_compute(self):
-        self._ck(self.L.b200lb_grad7(self.h))
+        if self.get_option("gradient") == 27:
+            self._ck(self.L.b200lb_grad27(self.h))
+        else:
+            self._ck(self.L.b200lb_grad7(self.h))
+
+    # -- isothermal fluctuations (noise_t, src/noise.h) ------------------------------
+    def noise_init(self, master_seed=0):
+        self._ck(self.L.b200lb_noise_init(self.h, int(master_seed)))
+
+    def noise_present_set(self, on=1):
+        self._ck(self.L.b200lb_noise_present_set(self.h, int(on)))
+
+    def noise_memcpy_h2d(self, state, layout=HOST_AOS):
+        assert state.dtype == np.uint32 and state.flags["C_CONTIGUOUS"]
+        self._ck(self.L.b200lb_noise_state_upload(self.h, state.ctypes.data_as(ctypes.c_void_p),
+                                                  layout))
+
+    def noise_memcpy_d2h(self, layout=HOST_AOS):
+        shape = (self.nsite, 4) if layout == HOST_AOS else (4, self.nsite)
+        state = np.zeros(shape, dtype=np.uint32)
+        self._ck(self.L.b200lb_noise_state_download(self.h, state.ctypes.data_as(ctypes.c_void_p),
+                                                    layout))
+        return state
 
     def step(self, nsteps=1):
         self._ck(self.L.b200lb_step(self.h, nsteps))

@@ -248,10 +248,12 @@ int orc_equilib_set(const orc_model_t * model, int ndist, double * f,
  * local force, compute velocity, relax the stress towards
  * rho u u + extra, add the force correction, relax the ghosts, and leave
  * post-collision modes in m[]. src/collision.c:350-544 and :800-925.
+ * shat / ghat: random stress and ghost terms (lb_oracle_noise.c) or NULL.
  * ---------------------------------------------------------------------- */
 
 void orc_relax_modes(const orc_model_t * model, const double * rtau,
 			const double force[3], const double sextra[3][3],
+			const double shat[3][3], const double * ghat,
 			double * m, double * rho_out, double u[3]) {
 
   const int nd = model->ndim;
@@ -305,12 +307,14 @@ void orc_relax_modes(const orc_model_t * model, const double * rtau,
   for (int a = 0; a < nd; a++) {
     for (int b = a; b < nd; b++) {
       m[1 + nd + k] = s[a][b];
+      if (shat) m[1 + nd + k] += shat[a][b];      /* src/collision.c:529 */
       k++;
     }
   }
 
   for (k = model->nhydro; k < model->nvel; k++) {
     m[k] = m[k] - rtau[k]*(m[k] - 0.0);
+    if (ghat) m[k] += ghat[k];                    /* src/collision.c:541 */
   }
 
   *rho_out = rho;
@@ -350,8 +354,11 @@ int orc_collide_mrt(const orc_model_t * model, const orc_box_t * box,
   const long last  = orc_index(box, box->nlocal[0] + 1, 0, 0);
   double rtau[ORC_NVELMAX];
   const double zero33[3][3] = {{0.0}};
+  double kt = 0.0;
+  unsigned int * nstate = orc_noise_attached(&kt);
 
   if (orc_rtau(model, prm, rtau) != 0) return -1;
+  if (nstate && nvel - model->nhydro > 10) return -1;
 
   #pragma omp parallel for schedule(static)
   for (long index = first; index < last; index++) {
@@ -362,7 +369,14 @@ int orc_collide_mrt(const orc_model_t * model, const orc_box_t * box,
       fl[a] = prm->force_global[a] + force[3*index + a];
     }
     orc_f_to_modes(model, fs, m);
-    orc_relax_modes(model, rtau, fl, zero33, m, &rl, ul);
+    if (nstate) {
+      double shat[3][3], ghat[ORC_NVELMAX];
+      orc_fluctuations(model, rtau, kt, nstate, index, shat, ghat);
+      orc_relax_modes(model, rtau, fl, zero33, (const double (*)[3]) shat, ghat, m, &rl, ul);
+    }
+    else {
+      orc_relax_modes(model, rtau, fl, zero33, NULL, NULL, m, &rl, ul);
+    }
     orc_modes_to_f(model, m, fs);
     rho[index] = rl;
     for (int a = 0; a < 3; a++) u[3*index + a] = ul[a];

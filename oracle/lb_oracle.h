@@ -96,6 +96,22 @@ int orc_grad_27pt(const orc_box_t * box, const double * phi,
 /* which stencil orc_step uses for the binary fluid: 7 (default) or 27 */
 int orc_gradient_select(int npt);
 
+/* Isothermal fluctuations (lb_oracle_noise.c). state[index*4 + ia] holds the
+ * KISS99 words of every site of the halo-inclusive box. While a state is
+ * attached, orc_collide_mrt / orc_collide_binary / orc_step add the random stress
+ * and ghost-mode terms at temperature kt and advance the generators of the
+ * sites they visit; orc_noise_attach(NULL, 0) switches them off again. */
+unsigned int orc_noise_uniform(unsigned int state[4]);
+int orc_noise_init(const orc_box_t * box, int master_seed,
+		   const int noffset[3], const int ntotal[3],
+		   unsigned int * state);
+int orc_noise_reap_n(unsigned int * state, long index, int nmax, double * reap);
+int orc_noise_attach(unsigned int * state, double kt);
+unsigned int * orc_noise_attached(double * kt);
+int orc_fluctuations(const orc_model_t * model, const double * rtau, double kt,
+		     unsigned int * state, long index,
+		     double shat[3][3], double * ghat);
+
 int orc_fill(const orc_box_t * box, int nf, const double * v, double * data);
 
 /* stats[0..7] = sum rho, sum rho^2 (about mean is left to caller), min, max,

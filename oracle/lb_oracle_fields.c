@@ -13,6 +13,7 @@
 
 void orc_relax_modes(const orc_model_t * model, const double * rtau,
 		     const double force[3], const double sextra[3][3],
+		     const double shat[3][3], const double * ghat,
 		     double * m, double * rho_out, double u[3]);
 void orc_f_to_modes(const orc_model_t * model, const double * fs, double * m);
 void orc_modes_to_f(const orc_model_t * model, const double * m, double * fs);
@@ -38,9 +39,12 @@ int orc_collide_binary(const orc_model_t * model, const orc_box_t * box,
   const long last  = orc_index(box, box->nlocal[0] + 1, 0, 0);
   const double rtau2 = 2.0/(1.0 + 2.0*prm->mobility);
   double rtau[ORC_NVELMAX];
+  double kt = 0.0;
+  unsigned int * nstate = orc_noise_attached(&kt);
 
   if (model->ndim != 3) return -1;
   if (orc_rtau(model, prm, rtau) != 0) return -1;
+  if (nstate && nvel - model->nhydro > 10) return -1;
 
   #pragma omp parallel for schedule(static)
   for (long index = first; index < last; index++) {
@@ -71,7 +75,16 @@ int orc_collide_binary(const orc_model_t * model, const orc_box_t * box,
     }
 
     orc_f_to_modes(model, fs, m);
-    orc_relax_modes(model, rtau, fl, (const double (*)[3]) sth, m, &rl, ul);
+    if (nstate) {
+      /* src/collision.c:884-900 */
+      double shat[3][3], ghat[ORC_NVELMAX];
+      orc_fluctuations(model, rtau, kt, nstate, index, shat, ghat);
+      orc_relax_modes(model, rtau, fl, (const double (*)[3]) sth,
+		      (const double (*)[3]) shat, ghat, m, &rl, ul);
+    }
+    else {
+      orc_relax_modes(model, rtau, fl, (const double (*)[3]) sth, NULL, NULL, m, &rl, ul);
+    }
     orc_modes_to_f(model, m, fs);
     for (int a = 0; a < 3; a++) u[3*index + a] = ul[a];
 

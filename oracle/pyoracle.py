@@ -73,6 +73,10 @@ def lib():
             build()
         _lib = ctypes.CDLL(_LIB)
         _lib.orc_index.restype = ctypes.c_long
+        _lib.orc_noise_uniform.restype = ctypes.c_uint
+        _lib.orc_noise_attach.argtypes = [ctypes.c_void_p, ctypes.c_double]
+        _lib.orc_noise_reap_n.argtypes = [ctypes.c_void_p, ctypes.c_long, ctypes.c_int,
+                                          c_double_p]
     return _lib
 
 
@@ -187,6 +191,32 @@ class Oracle:
 
     def gradient_select(self, npt):
         assert self.L.orc_gradient_select(int(npt)) == 0
+
+    # -- isothermal fluctuations (oracle/lb_oracle_noise.c) ------------------------
+    def noise_init(self, master_seed=0, noffset=(0, 0, 0), ntotal=None):
+        """KISS99 state of every site, state[index, 0:4] (uint32)."""
+        ntotal = self.nlocal if ntotal is None else ntotal
+        state = np.zeros((self.nsite, 4), dtype=np.uint32)
+        rc = self.L.orc_noise_init(ctypes.byref(self.box), int(master_seed),
+                                   (ctypes.c_int * 3)(*noffset), (ctypes.c_int * 3)(*ntotal),
+                                   state.ctypes.data_as(ctypes.c_void_p))
+        assert rc == 0
+        return state
+
+    def noise_attach(self, state, kt):
+        """Collisions from now on fluctuate at temperature kt (state=None: off)."""
+        if state is None:
+            self.L.orc_noise_attach(None, 0.0)
+        else:
+            assert state.dtype == np.uint32 and state.flags["C_CONTIGUOUS"]
+            self.L.orc_noise_attach(state.ctypes.data_as(ctypes.c_void_p), float(kt))
+
+    def noise_reap_n(self, state, index, nmax):
+        out = np.zeros(nmax)
+        rc = self.L.orc_noise_reap_n(state.ctypes.data_as(ctypes.c_void_p), int(index),
+                                     int(nmax), _p(out))
+        assert rc == 0
+        return out
 
     def stats(self, f):
         out = (ctypes.c_double * 8)()

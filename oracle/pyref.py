@@ -47,6 +47,9 @@ def _lib(nvel):
             getattr(L, name).restype = c_double_p
         L.refdrv_status.restype = ctypes.POINTER(ctypes.c_char)
         L.refdrv_step.restype = ctypes.c_double
+        L.refdrv_noise_state.restype = ctypes.POINTER(ctypes.c_uint)
+        L.refdrv_noise.argtypes = [ctypes.c_int, ctypes.c_double, ctypes.c_int]
+        L.refdrv_noise_reap_n.argtypes = [ctypes.c_int, ctypes.c_int, c_double_p]
         _libs[nvel] = L
     return _libs[nvel]
 
@@ -161,6 +164,20 @@ class Ref:
 
     def grad_compute(self):
         self.L.refdrv_grad_compute()
+
+    def noise(self, on, kt, reseed=0):
+        """isothermal_fluctuations on/off at temperature kt (reseed > 0: noise_init
+        again with that master seed)."""
+        assert self.L.refdrv_noise(int(on), float(kt), int(reseed)) == 0
+
+    def noise_state(self):
+        return self._arr(self.L.refdrv_noise_state(), (self.nsite, 4))
+
+    def noise_reap_n(self, index, nmax):
+        out = np.zeros(nmax)
+        self.L.refdrv_noise_reap_n(int(index), int(nmax),
+                                   out.ctypes.data_as(c_double_p))
+        return out
 
     def grad_select(self, npt):
         assert self.L.refdrv_grad_select(int(npt)) == 0

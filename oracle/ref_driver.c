@@ -16,6 +16,7 @@
  *    field_halo           src/field.c:434
  *    grad_3d_7pt_fluid_d2 src/gradient_3d_7pt_fluid.c:75
  *    grad_3d_27pt_fluid_d2 src/gradient_3d_27pt_fluid.c:75 (refdrv_grad_select(27))
+ *    noise_init / noise_reap_n / noise_present_set  src/noise.c:136,398,557
  *    hydro_f_zero/u_zero  src/hydro.c:306,279
  *
  *  The step sequence of refdrv_step() follows src/ludwig.c:530-862 for the
@@ -236,6 +237,25 @@ int refdrv_grad_select(int npt) {
   if (npt == 7)  return field_grad_set(rd.phi_grad, grad_3d_7pt_fluid_d2, NULL);
   if (npt == 27) return field_grad_set(rd.phi_grad, grad_3d_27pt_fluid_d2, NULL);
   return -1;
+}
+
+/* Isothermal fluctuations: what "isothermal_fluctuations on" + "temperature kt" do
+ * (src/collision_rt.c:55, src/physics_rt.c) and the per-site generator state
+ * (src/noise.c:136-233), host layout state[index*4 + ia] in an AOS build.
+ * reseed > 0 re-runs noise_init with that master seed. */
+int refdrv_noise(int on, double kt, int reseed) {
+  if (reseed > 0) {
+    free(rd.noise->state);
+    rd.noise->state = NULL;
+    noise_init(rd.noise, reseed);
+  }
+  physics_kt_set(rd.phys, kt);
+  return noise_present_set(rd.noise, NOISE_RHO, on);
+}
+unsigned int * refdrv_noise_state(void) { return rd.noise->state; }
+unsigned int refdrv_noise_uniform(unsigned int state[4]) { return noise_uniform(state); }
+int refdrv_noise_reap_n(int index, int nmax, double * reap) {
+  return noise_reap_n(rd.noise, index, nmax, reap);
 }
 
 int refdrv_hydro_f_zero(const double f[3]) { return hydro_f_zero(rd.hydro, f); }

@@ -1,6 +1,6 @@
 """Extracts the statistics block printed after the last time step from the reference's own
-regression golden logs (tests/regression/d3q19-short/serial-dist-*.log and d2q9/serial-2khz-bm1.log,
-Ludwig v0.20.1)
+regression golden logs (tests/regression/d3q19-short/serial-dist-*.log, d2q9/serial-2khz-bm1.log
+and the fluctuating-hydrodynamics case d2q9/serial-flct-t01.log, Ludwig v0.20.1)
 into tests/golden/regression_logs.json, together with the input keys that define each
 case. Run in the build container (needs /root/reference)."""
 
@@ -11,7 +11,8 @@ import re
 REF = "/root/reference/tests/regression"
 HERE = os.path.dirname(os.path.abspath(__file__))
 CASES = ["d3q19-short/serial-dist-3du", "d3q19-short/serial-dist-1dp",
-         "d3q19-short/serial-dist-2kh", "d3q19-short/serial-dist-2sw", "d2q9/serial-2khz-bm1"]
+         "d3q19-short/serial-dist-2kh", "d3q19-short/serial-dist-2sw", "d2q9/serial-2khz-bm1",
+         "d2q9/serial-flct-t01"]
 NVEL = {"d3q19-short": 19, "d2q9": 9}
 
 
@@ -31,7 +32,7 @@ def main():
             inp[parts[0]] = parts[1] if len(parts) > 1 else ""
         lines = open(os.path.join(REF, case + ".log")).read().splitlines()
         start = max(i for i, l in enumerate(lines) if l.startswith("Scalars - total"))
-        blk = lines[start:start + 12]
+        blk = lines[start:start + 16]
         rec = {"input": inp, "nvel": NVEL[case.split("/")[0]],
                "source": "tests/regression/%s.log:%d-%d" % (case, start + 1, start + 10)}
         for l in blk:
@@ -43,6 +44,10 @@ def main():
                 rec["umin"] = floats(l)
             if l.startswith("[maximum ]"):
                 rec["umax"] = floats(l)
+            if l.startswith("[eqipart.]"):
+                rec["eqipart"] = floats(l)             # isothermal fluctuations
+            if l.startswith("[measd/kT]"):
+                rec["measd_kt"] = floats(l)
         out[case.split('/')[1]] = rec
     with open(os.path.join(HERE, "regression_logs.json"), "w") as fh:
         json.dump(out, fh, indent=1)

@@ -40,3 +40,21 @@ def inputs_grad27(nvel):
     nlocal = tuple(int(x) for x in g["q%d_nlocal" % nvel])
     f0 = lbinit.make_state(models_host.cv(nvel), models_host.wv(nvel), nlocal, ndist=2)
     return g, nlocal, f0
+
+
+NOISE_CASES = {"q19": (19, 1), "q9": (9, 1), "q19b": (19, 2)}
+NOISE_PHYS = {1: dict(eta_shear=0.05, eta_bulk=0.12),
+              2: dict(eta_shear=0.00625, eta_bulk=0.00625, mobility=3.75)}
+
+
+def inputs_noise(tag):
+    """ref_noise.npz (tests/golden/make_golden_noise.py) and the seeded inputs of a case."""
+    from ludwig_b200 import models_host
+    g = np.load(os.path.join(HERE, "golden", "ref_noise.npz"))
+    nvel, ndist = NOISE_CASES[tag]
+    nlocal = tuple(int(x) for x in g[tag + "_nlocal"])
+    ndim = 2 if nvel == 9 else 3
+    f0 = lbinit.make_state(models_host.cv(nvel), models_host.wv(nvel), nlocal, ndist=ndist,
+                           ndim=ndim)
+    force = lbinit.make_force(nlocal, ndim=ndim)
+    return g, nvel, ndist, nlocal, f0, force

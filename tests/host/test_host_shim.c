@@ -98,11 +98,13 @@ static double urand(unsigned long * s) {
   return (double) ((*s >> 11) & 0xFFFFFFFFFFFFFUL)/4503599627370496.0 - 0.5;
 }
 
-static void test_loop(int ndist, int nsteps) {
+static void test_loop(int ndist, int nsteps, int npt, double kt) {
   cs_t cs;
-  physics_t phys = {1.0, 0.1, 0.1, {0.0, 0.0, 0.0}, 0.0};
+  physics_t phys = {1.0, 0.1, 0.1, {0.0, 0.0, 0.0}, 0.0, 0.0};
   lb_data_options_t opts = lb_data_options_default();
   lb_t * lb = NULL; hydro_t * hydro = NULL;
+  noise_t * noise = NULL;
+  unsigned int * ostate = NULL;
   field_t * phi = NULL; field_grad_t * dphi = NULL; fe_symm_t * fe = NULL;
   orc_model_t model; orc_box_t box; orc_param_t prm;
   const int nl[3] = {10, 8, 6};
@@ -114,10 +116,19 @@ static void test_loop(int ndist, int nsteps) {
   if (ndist == 2) { phys.eta_shear = phys.eta_bulk = 0.00625; phys.mobility = 3.75; }
   OK(lb_data_create(&cs, &phys, &opts, &lb));
   OK(hydro_create(lb, &hydro));
+  /* ludwig.c:242-243 creates the generator always; collision_rt.c:55 switches it on */
+  OK(noise_create(lb, &noise));
+  OK(noise_init(noise, 0));
+  if (kt > 0.0) {
+    phys.kt = kt;
+    OK(noise_present_set(noise, NOISE_RHO, 1));
+  }
   if (ndist == 2) {
     fe_symm_param_t fp = {-0.00625, 0.00625, 0.004, 0.0, 0.0};
     OK(field_create(lb, "phi", &phi));
     OK(field_grad_create(phi, &dphi));
+    /* the plug point gradient_rt.c uses (src/gradient_rt.c:81-98) */
+    if (npt == 27) OK(field_grad_set(dphi, grad_3d_27pt_fluid_d2, NULL));
     OK(fe_symm_create(phi, dphi, &fe));
     OK(fe_symm_param_set(fe, fp));
   }
@@ -159,14 +170,34 @@ static void test_loop(int ndist, int nsteps) {
       OK(field_grad_compute(dphi));
     }
     OK(hydro_u_zero(hydro, zero));
-    OK(lb_collide(lb, hydro, NULL, NULL, (fe_t *) fe, NULL));
+    OK(lb_collide(lb, hydro, NULL, noise, (fe_t *) fe, NULL));
     OK(lb_halo(lb));
     OK(lb_propagation(lb));
   }
   OK(lb_memcpy(lb, tdpMemcpyDeviceToHost));
   OK(hydro_memcpy(hydro, tdpMemcpyDeviceToHost));
+  OK(noise_memcpy(noise, tdpMemcpyDeviceToHost));
 
+  if (kt > 0.0) {
+    const int noffset[3] = {0, 0, 0};
+    ostate = (unsigned int *) calloc(4*(size_t) lb->nsite, sizeof(unsigned int));
+    orc_noise_init(&box, 0, noffset, nl, ostate);
+    orc_noise_attach(ostate, kt);
+  }
+
+  orc_gradient_select(npt);
   orc_step(&model, &box, &prm, ndist, nsteps, f, fprime, rho, u, force, ph, gr, dsq);
+  orc_gradient_select(7);
+  orc_noise_attach(NULL, 0.0);
+  if (kt > 0.0) {
+    int nbad = 0;
+    for (int ic = 1; ic <= nl[0]; ic++) for (int jc = 1; jc <= nl[1]; jc++) for (int kc = 1; kc <= nl[2]; kc++) {
+      long index = cs_index(&cs, ic, jc, kc);
+      for (int ia = 0; ia < 4; ia++) nbad += (noise->state[4*index + ia] != ostate[4*index + ia]);
+    }
+    CHECK(nbad == 0, "generator state of interior sites, bit for bit");
+    free(ostate);
+  }
 
   double emax = 0.0, fmax = 0.0, umax = 0.0, mass0 = 0.0, mass1 = 0.0;
   for (int ic = 1; ic <= nl[0]; ic++) for (int jc = 1; jc <= nl[1]; jc++) for (int kc = 1; kc <= nl[2]; kc++) {
@@ -182,8 +213,8 @@ static void test_loop(int ndist, int nsteps) {
       if (d > umax) umax = d;
     }
   }
-  printf("test_loop ndist %d: %d steps, max|df|/max|f| = %.3e, max|du| = %.3e, mass diff %.3e\n",
-	 ndist, nsteps, emax/fmax, umax, fabs(mass1 - mass0));
+  printf("test_loop ndist %d (%d-pt gradient, kT %.3e): %d steps, max|df|/max|f| = %.3e, max|du| = %.3e, mass diff %.3e\n",
+	 ndist, npt, kt, nsteps, emax/fmax, umax, fabs(mass1 - mass0));
   CHECK(emax/fmax < 1.0e-12, "time loop vs oracle");
   CHECK(umax < 1.0e-12, "hydro u vs oracle");
   CHECK(fabs(mass1 - mass0) < 1.0e-10, "mass");
@@ -197,6 +228,7 @@ static void test_loop(int ndist, int nsteps) {
   if (fe) fe_symm_free(fe);
   if (dphi) field_grad_free(dphi);
   if (phi) field_free(phi);
+  noise_free(noise);
   hydro_free(hydro);
   lb_free(lb);
 }
@@ -205,8 +237,11 @@ int main(void) {
   test_prop(1, LB_HALO_TARGET);
   test_prop(2, LB_HALO_TARGET);
   test_prop(1, LB_HALO_OPENMP_REDUCED);
-  test_loop(1, 7);
-  test_loop(2, 7);
+  test_loop(1, 7, 7, 0.0);
+  test_loop(2, 7, 7, 0.0);
+  test_loop(2, 7, 27, 0.0);
+  test_loop(1, 7, 7, 2.13333e-05);          /* isothermal fluctuations */
+  test_loop(2, 7, 7, 2.13333e-05);
   if (nfail) { printf("%d check(s) FAILED\n", nfail); return 1; }
   printf("host shim: all passed\n");
   return 0;

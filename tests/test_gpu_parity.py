@@ -7,6 +7,8 @@ Bars (BASELINE.json north_star): propagation, halo, layout conversion, phi and t
 mass conserved to round-off.
 """
 
+import os
+
 import numpy as np
 import pytest
 
@@ -607,4 +609,208 @@ def test_peer_memory_halo_loopback(nvel, nlocal, ndist, fused):
     m = orc.interior_mask()
     assert np.array_equal(lat.lb_memcpy_d2h()[m], ref[m])
     lat.sync()
+    lat.close()
+
+
+@pytest.mark.parametrize("nvel,nlocal", [(19, (10, 8, 6)), (27, (5, 7, 6)), (19, (3, 70, 130)),
+                                         (19, (40, 5, 64)), (19, (2, 1, 3))])
+@pytest.mark.parametrize("mode", ["wrap", "halo", "loopback"])
+def test_gradient_27pt_bit_exact(nvel, nlocal, mode):
+    """grad_3d_27pt_fluid_d2: bit-exact against the oracle on random phi, with the
+    periodic directions wrapped inside the kernel (halo_lazy), read from the halo
+    planes after the eager local copies, and after a loopback exchange (corners must
+    arrive through the x, y, z sequence). Tile-edge and ragged extents included."""
+    import ludwig_b200 as lb
+    lat, orc = mk(nvel, nlocal, 2)
+    n = orc.nsite
+    m = orc.interior_mask()
+    rng = np.random.default_rng(2727)
+    phi = rng.standard_normal(n)
+    orc.halo(phi, 1)
+    grad, delsq = np.zeros((n, 3)), np.zeros(n)
+    orc.grad_27pt(phi, grad, delsq)
+    if mode == "halo":
+        lat.set_option("halo_lazy", 0)
+    if mode == "loopback":
+        lat.set_option("loopback", 1)
+    lat.field_grad_set(27)
+    # upload interior values only (halo zeroed): field_halo has to provide the rest
+    phi_in = np.where(m, phi, 0.0)
+    lat.field_h2d(lb.FIELD_PHI, phi_in)
+    lat.field_halo()
+    lat.field_grad_compute()
+    assert np.array_equal(lat.field_d2h(lb.FIELD_GRAD)[m], grad[m])
+    assert np.array_equal(lat.field_d2h(lb.FIELD_DELSQ)[m], delsq[m])
+    assert np.array_equal(lat.field_d2h(lb.FIELD_PHI), phi)
+    lat.close()
+
+
+@pytest.mark.parametrize("nvel", [19, 27])
+def test_gradient_27pt_reference_golden(nvel):
+    """Reference-produced vectors (tests/golden/ref_grad27.npz): the stencil alone, the
+    binary collision fed by it, and ten time steps with "gradient" = 27."""
+    import ludwig_b200 as lb
+    g, nlocal, f0 = goldenlib.inputs_grad27(nvel)
+    tag = "q%d_" % nvel
+    B = goldenlib.BIN
+    lat, orc = mk(nvel, nlocal, 2)
+    m = orc.interior_mask()
+    lat.set_param(eta_shear=B["eta"], eta_bulk=B["eta"], mobility=B["mobility"],
+                  a=B["a"], b=B["b"], kappa=B["kappa"])
+    lat.field_grad_set(27)
+    lat.lb_memcpy_h2d(f0)
+    lat.phi_lb_to_field()
+    lat.field_halo()
+    assert np.array_equal(lat.field_d2h(lb.FIELD_PHI), g[tag + "phi"])
+    lat.field_grad_compute()
+    assert np.array_equal(lat.field_d2h(lb.FIELD_GRAD)[m], g[tag + "grad"])
+    assert np.array_equal(lat.field_d2h(lb.FIELD_DELSQ)[m], g[tag + "delsq"])
+    lat.hydro_f_zero()
+    lat.lb_collide()
+    assert relerr(lat.lb_memcpy_d2h()[m], g[tag + "collide_f"]) < TOL
+    for fused in (1, 0):
+        lat.set_option("fused", fused)
+        lat.lb_memcpy_h2d(f0)
+        lat.step(10)
+        assert relerr(lat.lb_memcpy_d2h()[m], g[tag + "step10_f"]) < TOL
+        assert np.max(np.abs(lat.field_d2h(lb.FIELD_PHI)[m] - g[tag + "step10_phi"])) < 1e-13
+    lat.close()
+
+
+# ---------------------------------------------------------------------------
+# isothermal fluctuations
+# ---------------------------------------------------------------------------
+
+@pytest.mark.parametrize("nvel,nlocal", [(19, (6, 5, 4)), (9, (8, 7, 1)), (19, (3, 70, 130))])
+@pytest.mark.parametrize("seed", [0, 8361235])
+def test_noise_init_and_memcpy(nvel, nlocal, seed):
+    """noise_init on the device: every site of the halo-inclusive box, bit for bit; and
+    noise_memcpy both ways in both host layouts."""
+    import ludwig_b200 as lb
+    lat, orc = mk(nvel, nlocal)
+    lat.noise_init(seed)
+    want = orc.noise_init(seed)
+    got = lat.noise_memcpy_d2h()
+    assert got.dtype == np.uint32 and np.array_equal(got, want)
+    assert np.array_equal(lat.noise_memcpy_d2h(lb.HOST_SOA), np.ascontiguousarray(want.T))
+    rng = np.random.default_rng(5)
+    st = rng.integers(0, 2**32, size=(orc.nsite, 4), dtype=np.uint32)
+    if nvel == 9:
+        s3 = st.reshape(orc.nall + (4,))
+        s3[:, :, 0] = s3[:, :, 1]
+        s3[:, :, 2] = s3[:, :, 1]
+    lat.noise_memcpy_h2d(st)
+    assert np.array_equal(lat.noise_memcpy_d2h(), st)
+    assert np.array_equal(lat.noise_memcpy_d2h(lb.HOST_SOA), np.ascontiguousarray(st.T))
+    lat.noise_memcpy_h2d(np.ascontiguousarray(want.T), lb.HOST_SOA)
+    assert np.array_equal(lat.noise_memcpy_d2h(), want)
+    lat.close()
+
+
+def test_noise_golden_state():
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_noise.npz"))
+    lat, orc = mk(19, (4, 3, 5))
+    lat.noise_init(8361235)
+    assert np.array_equal(lat.noise_memcpy_d2h(), g["seeded_state0"])
+    lat.close()
+
+
+@pytest.mark.parametrize("tag", ["q19", "q9", "q19b"])
+@pytest.mark.parametrize("mode", ["plain", "loopback", "diag"])
+def test_fluctuating_collision_golden(tag, mode):
+    """Fluctuating lb_collide against reference-produced vectors (ref_noise.npz): one
+    collision and ten time steps (fused and unfused), M10 and BGK; generator state of
+    interior sites bit for bit, populations to TOL. `loopback` sends the sweep through
+    the boundary-slab split (every site must still draw exactly once), `diag` through
+    the kernels that also gather the conserved sums."""
+    import ludwig_b200 as lb
+    g, nvel, ndist, nlocal, f0, force = goldenlib.inputs_noise(tag)
+    kt = float(g["kt"])
+    lat, orc = mk(nvel, nlocal, ndist)
+    m = orc.interior_mask()
+    kw = dict(goldenlib.NOISE_PHYS[ndist])
+    if ndist == 2:
+        kw.update(a=-0.00625, b=0.00625, kappa=0.004)
+    if mode == "loopback":
+        lat.set_option("loopback", 1)
+    if mode == "diag":
+        lat.set_option("diag", 1)
+    lat.noise_present_set(1)
+    for nrelax, name in ((0, "m10"), (1, "bgk")):
+        if tag + "_%s_collide_f" % name not in g:
+            continue
+        lat.set_param(nrelax=nrelax, kt=kt, **kw)
+        lat.set_option("fused", 1)
+        lat.noise_init(0)
+        lat.lb_memcpy_h2d(f0)
+        lat.field_h2d(lb.FIELD_FORCE, force)
+        if ndist == 2:
+            lat.phi_lb_to_field()
+            lat.field_halo()
+            lat.field_grad_compute()
+        lat.lb_collide()
+        assert np.array_equal(lat.noise_memcpy_d2h()[m], g[tag + "_%s_collide_state" % name])
+        assert relerr(lat.lb_memcpy_d2h()[m], g[tag + "_%s_collide_f" % name]) < TOL
+        assert np.max(np.abs(lat.field_d2h(lb.FIELD_U)[m] - g[tag + "_%s_collide_u" % name])) < TOL
+        for fused in (1, 0):
+            lat.set_option("fused", fused)
+            lat.noise_init(0)
+            lat.lb_memcpy_h2d(f0)
+            lat.hydro_f_zero()
+            lat.step(10)
+            assert np.array_equal(lat.noise_memcpy_d2h()[m], g[tag + "_%s_step10_state" % name])
+            assert relerr(lat.lb_memcpy_d2h()[m], g[tag + "_%s_step10_f" % name]) < TOL
+            if mode == "diag":
+                d = lat.step_diag()
+                assert abs(d[0] - f0[m][:, 0].sum()) < 1e-9        # mass untouched by the noise
+    lat.close()
+
+
+@pytest.mark.parametrize("nvel,nlocal,nrelax", [(19, (12, 10, 34), 0), (19, (12, 10, 34), 2),
+                                                (9, (40, 36, 1), 0)])
+def test_fluctuating_steps_vs_oracle(nvel, nlocal, nrelax):
+    """Twenty fluctuating steps against the oracle on a lattice large enough for
+    several blocks, TRT included (ghost modes kept AND driven)."""
+    from oracle import pyoracle
+    lat, orc = mk(nvel, nlocal)
+    kt = 1.0e-4
+    f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal, ndim=orc.ndim)
+    prm = pyoracle.make_param(eta_shear=0.02, eta_bulk=0.3, nrelax=nrelax)
+    m = orc.interior_mask()
+    n = orc.nsite
+    state = orc.noise_init(77)
+    orc.noise_attach(state, kt)
+    try:
+        f, fp = f0.copy(), np.zeros_like(f0)
+        rho, u, frc = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
+        orc.step(prm, 20, f, fp, rho, u, frc)
+    finally:
+        orc.noise_attach(None, 0.0)
+    lat.set_param(eta_shear=0.02, eta_bulk=0.3, nrelax=nrelax, kt=kt)
+    lat.noise_init(77)
+    lat.noise_present_set(1)
+    lat.lb_memcpy_h2d(f0)
+    lat.step(20)
+    assert np.array_equal(lat.noise_memcpy_d2h()[m], state[m])
+    assert relerr(lat.lb_memcpy_d2h()[m], f[m]) < TOL
+    assert np.max(np.abs(lat.field_d2h(1)[m] - u[m])) < TOL
+    # switched off again: deterministic collision, generators untouched
+    lat.noise_present_set(0)
+    lat.step(1)
+    assert np.array_equal(lat.noise_memcpy_d2h()[m], state[m])
+    lat.close()
+
+
+def test_noise_refused_where_the_reference_cannot():
+    """D3Q27 has 17 ghost modes; one draw yields ten variates (src/noise.h:18)."""
+    import ludwig_b200 as lb
+    lat, orc = mk(27, (4, 4, 4))
+    with pytest.raises(lb.B200LBError, match="ghost modes"):
+        lat.noise_present_set(1)
+    lat.close()
+    lat, orc = mk(19, (4, 4, 4))
+    lat.noise_present_set(1)
+    lat.lb_memcpy_h2d(np.ones((orc.nsite, 1, 19)))
+    with pytest.raises(lb.B200LBError, match="noise_init"):
+        lat.lb_collide()
     lat.close()

@@ -115,3 +115,50 @@ def test_gradient_27pt_golden(nvel):
         orc.gradient_select(7)
     assert relerr(f[m], g[tag + "step10_f"]) < 1e-12
     assert np.max(np.abs(phi[m] - g[tag + "step10_phi"])) < 1e-13
+
+
+@pytest.mark.parametrize("tag", ["q19", "q9", "q19b"])
+def test_fluctuations_golden(tag):
+    """Isothermal fluctuations against reference-produced vectors
+    (tests/golden/ref_noise.npz): generator state bit for bit, populations to round-off."""
+    g, nvel, ndist, nlocal, f0, force = goldenlib.inputs_noise(tag)
+    kt = float(g["kt"])
+    orc = pyoracle.Oracle(nvel, nlocal, ndist=ndist)
+    m = orc.interior_mask()
+    n = orc.nsite
+    kw = dict(goldenlib.NOISE_PHYS[ndist])
+    if ndist == 2:
+        kw.update(a=-0.00625, b=0.00625, kappa=0.004)
+    assert np.array_equal(orc.noise_init(0), g[tag + "_state0"])
+    if tag == "q19":
+        o2 = pyoracle.Oracle(19, (4, 3, 5))
+        assert np.array_equal(o2.noise_init(8361235), g["seeded_state0"])
+    try:
+        for nrelax, name in ((0, "m10"), (1, "bgk")):
+            if tag + "_%s_collide_f" % name not in g:
+                continue
+            prm = pyoracle.make_param(nrelax=nrelax, **kw)
+            state = orc.noise_init(0)
+            orc.noise_attach(state, kt)
+            f = f0.copy()
+            rho, u = np.zeros(n), np.zeros((n, 3))
+            phi, grad, delsq = np.zeros(n), np.zeros((n, 3)), np.zeros(n)
+            if ndist == 2:
+                orc.phi_from_g(f, phi)
+                orc.halo(phi, 1)
+                orc.grad_7pt(phi, grad, delsq)
+                orc.collide_binary(prm, f, force, u, phi, grad, delsq)
+            else:
+                orc.collide_mrt(prm, f, force, rho, u)
+            assert np.array_equal(state[m], g[tag + "_%s_collide_state" % name])
+            assert relerr(f[m], g[tag + "_%s_collide_f" % name]) < 1e-13
+            assert np.max(np.abs(u[m] - g[tag + "_%s_collide_u" % name])) < 1e-15
+            state = orc.noise_init(0)
+            orc.noise_attach(state, kt)
+            f = f0.copy()
+            fp, frc = np.zeros_like(f), np.zeros((n, 3))
+            orc.step(prm, 10, f, fp, rho, u, frc, phi, grad, delsq)
+            assert np.array_equal(state[m], g[tag + "_%s_step10_state" % name])
+            assert relerr(f[m], g[tag + "_%s_step10_f" % name]) < 1e-12
+    finally:
+        orc.noise_attach(None, 0.0)

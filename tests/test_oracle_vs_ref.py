@@ -215,3 +215,98 @@ def test_gradient_27pt(nvel, nlocal):
         finally:
             orc.gradient_select(7)
         assert relerr(f[m], ref.f()[m]) < 1e-12
+
+
+KT = 2.13333e-05       # temperature of tests/regression/d2q9/serial-flct-t01.inp
+
+
+@pytest.mark.parametrize("nvel,nlocal", [(19, (6, 5, 4)), (9, (8, 7, 1))])
+@pytest.mark.parametrize("seed", [0, 8361235])
+def test_noise_generator(nvel, nlocal, seed):
+    """noise_init / noise_uniform / noise_reap_n (src/noise.c): integer state and the
+    discrete variates, bit for bit, every site of the halo-inclusive box."""
+    need_ref(nvel)
+    orc = pyoracle.Oracle(nvel, nlocal)
+    state = orc.noise_init(seed)
+    with pyref.Ref(nvel, nlocal) as ref:
+        ref.noise(1, KT, reseed=seed)
+        assert np.array_equal(state, ref.noise_state())
+        for index in (0, 7, orc.nsite - 1):
+            for nmax in (6, 10, 3):
+                a = orc.noise_reap_n(state, index, nmax)
+                b = ref.noise_reap_n(index, nmax)
+                assert np.array_equal(a, b)
+        assert np.array_equal(state, ref.noise_state())
+    # levels have zero mean and unit variance over the eight equally likely indices
+    lv = np.array([-np.sqrt(2 + np.sqrt(2)), -np.sqrt(2 - np.sqrt(2)), 0, 0, 0, 0,
+                   np.sqrt(2 - np.sqrt(2)), np.sqrt(2 + np.sqrt(2))])
+    assert abs(lv.mean()) < 1e-15 and abs((lv**2).mean() - 1.0) < 1e-15
+
+
+@pytest.mark.parametrize("nvel,nlocal,ndist,nrelax", [
+    (19, (6, 5, 4), 1, 0), (19, (6, 5, 4), 1, 1), (19, (6, 5, 4), 1, 2),
+    (9, (8, 7, 1), 1, 0), (9, (8, 7, 1), 1, 1), (19, (6, 5, 4), 2, 0)])
+def test_fluctuating_collision(nvel, nlocal, ndist, nrelax):
+    """lb_collide with isothermal fluctuations on: one collision, then the time loop;
+    generator state stays bit-identical, populations to round-off."""
+    need_ref(nvel)
+    orc = pyoracle.Oracle(nvel, nlocal, ndist=ndist)
+    f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal, ndist=ndist, ndim=orc.ndim)
+    force = lbinit.make_force(nlocal, ndim=orc.ndim)
+    kw = dict(eta_shear=0.1, eta_bulk=0.07)
+    if ndist == 2:
+        kw = dict(eta_shear=0.00625, eta_bulk=0.00625, mobility=3.75)
+    prm = pyoracle.make_param(a=-0.00625, b=0.00625, kappa=0.004, nrelax=nrelax, **kw)
+    m = orc.interior_mask()
+    n = orc.nsite
+    state = orc.noise_init(0)
+    orc.noise_attach(state, KT)
+    try:
+        with pyref.Ref(nvel, nlocal, ndist=ndist) as ref:
+            ref.physics(**kw)
+            ref.relaxation(nrelax)
+            if ndist == 2:
+                ref.fe_symm(-0.00625, 0.00625, 0.004)
+            ref.noise(1, KT)
+            ref.f()[...] = f0
+            ref.force()[...] = force
+            f = f0.copy()
+            rho, u = np.zeros(n), np.zeros((n, 3))
+            phi, grad, delsq = np.zeros(n), np.zeros((n, 3)), np.zeros(n)
+            if ndist == 2:
+                ref.phi_from_lb()
+                ref.phi_halo()
+                ref.grad_compute()
+                orc.phi_from_g(f, phi)
+                orc.halo(phi, 1)
+                orc.grad_7pt(phi, grad, delsq)
+                ref.collide()
+                orc.collide_binary(prm, f, force, u, phi, grad, delsq)
+            else:
+                ref.collide()
+                orc.collide_mrt(prm, f, force, rho, u)
+            assert np.array_equal(state, ref.noise_state())
+            assert relerr(f[m], ref.f()[m]) < 1e-13
+            # the noise is there: compare with the deterministic collision
+            orc.noise_attach(None, 0.0)
+            fd = f0.copy()
+            if ndist == 2:
+                orc.collide_binary(prm, fd, force, u, phi, grad, delsq)
+            else:
+                orc.collide_mrt(prm, fd, force, rho, u)
+            assert relerr(fd[m][:, 0], f[m][:, 0]) > 1e-4
+            # mass and momentum are untouched by the fluctuations
+            assert np.max(np.abs(fd[m][:, 0].sum(-1) - f[m][:, 0].sum(-1))) < 1e-14
+            cv = orc.cv().astype(float)
+            assert np.max(np.abs((fd[m][:, 0] - f[m][:, 0]) @ cv)) < 1e-15
+            # time loop
+            orc.noise_attach(state, KT)
+            ref.f()[...] = f0
+            ref.step(8)
+            f = f0.copy()
+            fp, frc = np.zeros_like(f), np.zeros((n, 3))
+            orc.step(prm, 8, f, fp, rho, u, frc, phi, grad, delsq)
+            assert np.array_equal(state, ref.noise_state())
+            assert relerr(f[m], ref.f()[m]) < 1e-12
+    finally:
+        orc.noise_attach(None, 0.0)

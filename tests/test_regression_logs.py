@@ -1,5 +1,6 @@
 """Ludwig's own regression logs for the single-fluid path (tests/regression/d3q19-short/
-serial-dist-{3du,1dp,2kh,2sw}.{inp,log} and d2q9/serial-2khz-bm1, 2560 steps of D2Q9): the statistics printed after the last step,
+serial-dist-{3du,1dp,2kh,2sw}.{inp,log}, d2q9/serial-2khz-bm1, 2560 steps of D2Q9, and
+d2q9/serial-flct-t01, 200 fluctuating steps): the statistics printed after the last step,
 reproduced the way tests/test-diff.sh + tests/awk-fp-diff.sh judge them -- every printed
 float, in the reference's printf format, within an ABSOLUTE 1e-12.
 
@@ -33,8 +34,10 @@ def initial_state(inp, cv, wv):
     jc = np.arange(1, nt[1] + 1)[None, :, None] * np.ones(nt)
     kc = np.arange(1, nt[2] + 1)[None, None, :] * np.ones(nt)
     u = np.zeros(nt + (3,))
-    key = inp["distribution_initialisation"]
-    if key == "3d_uniform_u":
+    key = inp.get("distribution_initialisation", "rest")
+    if key == "rest":
+        pass                       # default: rho0 everywhere, fluid at rest (src/distribution_rt.c:398)
+    elif key == "3d_uniform_u":
         u[...] = [float(x) for x in inp["distribution_uniform_u"].split("_")]
     elif key == "1d_poiseuille":
         umax = [float(x) for x in inp["distribution_poiseuille_umax"].split("_")]
@@ -87,6 +90,31 @@ def check(rec, nt, sums, u_interior):
         assert abs(a - b) <= 1e-12, ("umax", umax, rec["umax"])
 
 
+def check_equipartition(rec, f_interior, cv):
+    """lb_collision_stats_kt (src/collision.c:1038-1113): <g_a^2/rho> per direction and
+    their sum against NDIM kT, as printed under "Isothermal fluctuations"."""
+    rho = f_interior.sum(-1)
+    g = f_interior @ cv.astype(float)
+    eq = [(g[:, a]**2/rho).sum()/len(rho) for a in range(3)]
+    mine = [printed("%14.7e", x) for x in eq]
+    for a, b in zip(mine, rec["eqipart"]):
+        assert abs(a - b) <= 1e-12, ("eqipart", mine, rec["eqipart"])
+    ndim = 2 if rec["nvel"] == 9 else 3
+    kt = float(rec["input"]["temperature"])
+    mine = [printed("%14.7e", sum(eq)), printed("%14.7e", ndim*kt)]
+    for a, b in zip(mine, rec["measd_kt"]):
+        assert abs(a - b) <= 1e-12, ("measd/kT", mine, rec["measd_kt"])
+
+
+def noisy(rec):
+    return rec["input"].get("isothermal_fluctuations") == "on"
+
+
+def viscosities(inp):
+    eta = float(inp["viscosity"])
+    return eta, float(inp.get("viscosity_bulk", eta))
+
+
 @pytest.mark.parametrize("case", CASES)
 def test_oracle_reproduces_reference_log(case):
     from oracle import pyoracle
@@ -95,14 +123,22 @@ def test_oracle_reproduces_reference_log(case):
     o0 = pyoracle.Oracle(nvel, (2, 2, 1 if nvel == 9 else 2))
     nt, f = initial_state(rec["input"], o0.cv(), o0.wv())
     orc = pyoracle.Oracle(nvel, nt)
-    eta = float(rec["input"]["viscosity"])
-    prm = pyoracle.make_param(eta_shear=eta, eta_bulk=eta)
+    eta, zeta = viscosities(rec["input"])
+    prm = pyoracle.make_param(eta_shear=eta, eta_bulk=zeta)
     n = orc.nsite
     fp = np.zeros_like(f)
     rho, u, frc = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
-    orc.step(prm, int(rec["input"]["N_cycles"]), f, fp, rho, u, frc)
+    if noisy(rec):
+        # ludwig.c:243 noise_init(noise_rho, 0): the input's random_seed is for colloids
+        orc.noise_attach(orc.noise_init(0), float(rec["input"]["temperature"]))
+    try:
+        orc.step(prm, int(rec["input"]["N_cycles"]), f, fp, rho, u, frc)
+    finally:
+        orc.noise_attach(None, 0.0)
     m = orc.interior_mask()
     check(rec, nt, orc.stats(f), u[m])
+    if noisy(rec):
+        check_equipartition(rec, f[m][:, 0], orc.cv())
 
 
 @pytest.mark.gpu
@@ -114,11 +150,15 @@ def test_cuda_reproduces_reference_log(case, hydro_write):
     rec = GOLD[case]
     nvel = rec["nvel"]
     nt, f = initial_state(rec["input"], models_host.cv(nvel), models_host.wv(nvel))
-    eta = float(rec["input"]["viscosity"])
+    eta, zeta = viscosities(rec["input"])
     lat = lb.Lattice(nvel, nt)
     lat.set_option("hydro_write", hydro_write)
     lat.set_option("halo", lb.HALO_REDUCED)          # lb_halo_openmp_reduced in the input
-    lat.set_param(eta_shear=eta, eta_bulk=eta)
+    kt = float(rec["input"].get("temperature", 0.0)) if noisy(rec) else 0.0
+    lat.set_param(eta_shear=eta, eta_bulk=zeta, kt=kt)
+    if noisy(rec):
+        lat.noise_init(0)
+        lat.noise_present_set(1)
     lat.lb_memcpy_h2d(f)
     lat.step(int(rec["input"]["N_cycles"]))
     sums = lat.stats()                               # lb_memcpy D2H + stats_distribution_print
@@ -127,4 +167,6 @@ def test_cuda_reproduces_reference_log(case, hydro_write):
     m = np.zeros(nall, dtype=bool)
     m[1:-1, 1:-1, 1:-1] = True
     check(rec, nt, sums, u[m.reshape(-1)])
+    if noisy(rec):
+        check_equipartition(rec, lat.lb_memcpy_d2h()[m.reshape(-1)][:, 0], models_host.cv(nvel))
     lat.close()
