@@ -85,6 +85,9 @@ typedef struct b200lb_param_s {
   double mobility;           /* binary: rtau2 = 2/(1 + 2 mobility) */
   double a, b, kappa;        /* symmetric free energy */
   double kt;                 /* physics_kt: temperature of the isothermal fluctuations */
+  int    ghost_off;          /* lb_collision_ghost_modes_off (src/collision.c:1137, key
+                              * "lb_ghost_modes off"): no ghost-mode noise; the binary
+                              * collision relaxes the ghosts fully (src/collision.c:1607) */
 } b200lb_param_t;
 
 const char * b200lb_last_error(void);

@@ -199,6 +199,7 @@ static int site_kparams(b200lb_s * h, KParams & P) {
   P.noise = h->noise;
   P.nv_diag = h->nv_diag; P.nv_off = h->nv_off; P.nv_bulk = h->nv_bulk;
   for (int k = 0; k < B200LB_MAXNOISE; k++) P.nv_ghost[k] = h->nv_ghost[k];
+  P.nghost_draw = h->prm.ghost_off ? 0 : 1;
   P.nlv_big = sqrt(2.0 + sqrt(2.0));          // rtable of src/noise.c:70-77
   P.nlv_small = sqrt(2.0 - sqrt(2.0));
   return 0;
@@ -250,6 +251,11 @@ static int derive_params(b200lb_s * h) {
   }
   else {
     return fail("unknown relaxation scheme %d", p.nrelax);
+  }
+  if (p.ghost_off && h->desc.ndist == 2) {
+    // lb_collision_noise_var_set (src/collision.c:1607-1614) resets lb->param->rtau of
+    // the ghosts, which only the binary collision reads (src/collision.c:918)
+    for (int k = 0; k < ng; k++) rt[k] = 1.0;
   }
   h->ghost = false;
   for (int k = 0; k < B200LB_MAXGHOST; k++) {

@@ -54,6 +54,7 @@ struct KParams {
   double nv_diag, nv_off; // stress variance: var_eta sqrt(2) on the diagonal, var_eta off it
   double nv_bulk;         // variance of the trace
   double nv_ghost[B200LB_MAXNOISE];  // per ghost mode
+  int nghost_draw;        // 0 = ghost modes off: no second draw, no ghost noise
   double nlv_big, nlv_small;         // sqrt(2 + sqrt 2), sqrt(2 - sqrt 2): the discrete levels
 };
 

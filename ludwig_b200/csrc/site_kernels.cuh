@@ -303,11 +303,17 @@ fluctuations(unsigned int (&w)[4], const KParams & P,
     for (int b = a + 1; b < ND; b++) shat[sidx<M>(a, b)] = od[a + b - 1]*P.nv_off;
   }
 
-  bits = kiss99(w) >> 2;
-  #pragma unroll
-  for (int k = 0; k < NG; k++) {
-    ghat[k] = P.nv_ghost[k]*noise_level(bits, P.nlv_big, P.nlv_small);
-    bits >>= 3;
+  if (P.nghost_draw) {          // uniform branch
+    bits = kiss99(w) >> 2;
+    #pragma unroll
+    for (int k = 0; k < NG; k++) {
+      ghat[k] = P.nv_ghost[k]*noise_level(bits, P.nlv_big, P.nlv_small);
+      bits >>= 3;
+    }
+  }
+  else {
+    #pragma unroll
+    for (int k = 0; k < NG; k++) ghat[k] = 0.0;
   }
 }
 

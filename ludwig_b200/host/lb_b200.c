@@ -110,11 +110,15 @@ int lb_collide(lb_t * lb, hydro_t * hydro, map_t * map, noise_t * noise, fe_t * 
   }
   /* lb_collision_noise_var_set (src/collision.c:1572): variances follow kt */
   p.kt = lb->phys->kt;
+  p.ghost_off = (lb->isghost == LB_GHOST_OFF);
   TRY(b200lb_noise_present_set(lb->target, (noise != NULL) && noise->on[NOISE_RHO]));
   TRY(b200lb_set_param(lb->target, &p));
   TRY(b200lb_collide(lb->target));
   return 0;
 }
+
+int lb_collision_ghost_modes_on(lb_t * lb)  { lb->isghost = LB_GHOST_ON;  return 0; }
+int lb_collision_ghost_modes_off(lb_t * lb) { lb->isghost = LB_GHOST_OFF; return 0; }
 
 /* noise_t: the generator state lives on the device; the host array is the interchange
  * copy noise_memcpy moves, as for lb->f. */

@@ -63,6 +63,8 @@ typedef struct lb_data_options_s {
   lb_halo_enum_t halo;
 } lb_data_options_t;
 
+typedef enum lb_mode_enum_type {LB_GHOST_ON = 0, LB_GHOST_OFF = 1} lb_mode_enum_t;
+
 typedef struct fe_symm_param_s { double a, b, kappa, c, h; } fe_symm_param_t;
 
 typedef struct lb_data_s {
@@ -70,6 +72,7 @@ typedef struct lb_data_s {
   cs_t * cs;
   double * f;                      /* host distributions, LB_ADDR(nsite,ndist,nvel,index,n,p) */
   lb_relaxation_enum_t nrelax;
+  int isghost;                     /* LB_GHOST_ON / LB_GHOST_OFF (src/lb_data.h:152) */
   lb_halo_enum_t haloscheme;
   physics_t * phys;                /* stands in for physics_ref() */
   b200lb_t * target;               /* the device side (reference: lb->target) */
@@ -109,6 +112,8 @@ int lb_data_create(cs_t * cs, physics_t * phys, const lb_data_options_t * opts, 
 int lb_free(lb_t * lb);
 int lb_memcpy(lb_t * lb, tdpMemcpyKind flag);
 int lb_collision_relaxation_set(lb_t * lb, lb_relaxation_enum_t nrelax);
+int lb_collision_ghost_modes_on(lb_t * lb);                        /* src/collision.c:1120 */
+int lb_collision_ghost_modes_off(lb_t * lb);                       /* src/collision.c:1137 */
 
 int lb_collide(lb_t * lb, hydro_t * hydro, map_t * map, noise_t * noise, fe_t * fe, visc_t * visc);
 int lb_halo(lb_t * lb);

@@ -61,7 +61,7 @@ class Param(ctypes.Structure):
         ("eta_bulk", ctypes.c_double), ("force_global", ctypes.c_double * 3),
         ("nrelax", ctypes.c_int), ("mobility", ctypes.c_double),
         ("a", ctypes.c_double), ("b", ctypes.c_double), ("kappa", ctypes.c_double),
-        ("kt", ctypes.c_double),
+        ("kt", ctypes.c_double), ("ghost_off", ctypes.c_int),
     ]
 
 
@@ -219,9 +219,11 @@ class Lattice:
         return int(self.L.b200lb_get_option(self.h, name.encode()))
 
     def set_param(self, rho0=1.0, eta_shear=0.1, eta_bulk=0.1, force=(0.0, 0.0, 0.0),
-                  nrelax=RELAX_M10, mobility=0.0, a=0.0, b=0.0, kappa=0.0, kt=0.0):
+                  nrelax=RELAX_M10, mobility=0.0, a=0.0, b=0.0, kappa=0.0, kt=0.0,
+                  ghost_off=0):
         p = Param()
         p.kt = kt
+        p.ghost_off = ghost_off
         p.rho0, p.eta_shear, p.eta_bulk = rho0, eta_shear, eta_bulk
         p.force_global[:] = force
         p.nrelax, p.mobility, p.a, p.b, p.kappa = nrelax, mobility, a, b, kappa

@@ -371,7 +371,7 @@ int orc_collide_mrt(const orc_model_t * model, const orc_box_t * box,
     orc_f_to_modes(model, fs, m);
     if (nstate) {
       double shat[3][3], ghat[ORC_NVELMAX];
-      orc_fluctuations(model, rtau, kt, nstate, index, shat, ghat);
+      orc_fluctuations(model, rtau, kt, prm->ghost_off, nstate, index, shat, ghat);
       orc_relax_modes(model, rtau, fl, zero33, (const double (*)[3]) shat, ghat, m, &rl, ul);
     }
     else {

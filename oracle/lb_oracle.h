@@ -55,6 +55,10 @@ typedef struct orc_param_s {
   /* binary fluid (symmetric free energy) */
   double mobility;
   double a, b, kappa;
+  /* lb_collision_ghost_modes_off (src/collision.c:1137, input key "lb_ghost_modes off"):
+   * no ghost-mode noise is drawn, and the binary collision relaxes the ghosts
+   * fully whatever the scheme (src/collision.c:1607-1614). 0 = ghost modes on. */
+  int ghost_off;
 } orc_param_t;
 
 typedef struct orc_box_s {
@@ -109,7 +113,7 @@ int orc_noise_reap_n(unsigned int * state, long index, int nmax, double * reap);
 int orc_noise_attach(unsigned int * state, double kt);
 unsigned int * orc_noise_attached(double * kt);
 int orc_fluctuations(const orc_model_t * model, const double * rtau, double kt,
-		     unsigned int * state, long index,
+		     int ghost_off, unsigned int * state, long index,
 		     double shat[3][3], double * ghat);
 
 int orc_fill(const orc_box_t * box, int nf, const double * v, double * data);

@@ -45,6 +45,11 @@ int orc_collide_binary(const orc_model_t * model, const orc_box_t * box,
   if (model->ndim != 3) return -1;
   if (orc_rtau(model, prm, rtau) != 0) return -1;
   if (nstate && nvel - model->nhydro > 10) return -1;
+  if (prm->ghost_off) {
+    /* lb_collision_noise_var_set, src/collision.c:1607-1614: lb->param->rtau, which
+     * only this collision reads for the ghosts (src/collision.c:918) */
+    for (int k = model->nhydro; k < nvel; k++) rtau[k] = 1.0;
+  }
 
   #pragma omp parallel for schedule(static)
   for (long index = first; index < last; index++) {
@@ -78,7 +83,7 @@ int orc_collide_binary(const orc_model_t * model, const orc_box_t * box,
     if (nstate) {
       /* src/collision.c:884-900 */
       double shat[3][3], ghat[ORC_NVELMAX];
-      orc_fluctuations(model, rtau, kt, nstate, index, shat, ghat);
+      orc_fluctuations(model, rtau, kt, prm->ghost_off, nstate, index, shat, ghat);
       orc_relax_modes(model, rtau, fl, (const double (*)[3]) sth,
 		      (const double (*)[3]) shat, ghat, m, &rl, ul);
     }

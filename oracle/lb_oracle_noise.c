@@ -116,10 +116,10 @@ int orc_noise_reap_n(unsigned int * state, long index, int nmax, double * reap) 
  * binary collision's lb_collision_fluctuations (:1663-1745) evaluates the same
  * expressions from lb->param->var_shear / var_bulk (:1601-1604).
  * Six variates are always drawn for the stress (also in two dimensions), then
- * nvel - nhydro for the ghosts from a second draw. */
+ * nvel - nhydro for the ghosts from a second draw unless ghost modes are off. */
 
 int orc_fluctuations(const orc_model_t * model, const double * rtau, double kt,
-		     unsigned int * state, long index,
+		     int ghost_off, unsigned int * state, long index,
 		     double shat[3][3], double * ghat) {
 
   const int nd = model->ndim;
@@ -154,6 +154,9 @@ int orc_fluctuations(const orc_model_t * model, const double * rtau, double kt,
   for (int a = 0; a < 3; a++) shat[a][a] += tr;
 
   for (int k = 0; k < model->nvel; k++) ghat[k] = 0.0;
+
+  /* ghost modes off: no second draw (src/collision.c:503, :1730) */
+  if (ghost_off) return 0;
 
   orc_noise_reap_n(state, index, model->nvel - model->nhydro, r);
 

@@ -47,6 +47,7 @@ class Param(ctypes.Structure):
         ("a", ctypes.c_double),
         ("b", ctypes.c_double),
         ("kappa", ctypes.c_double),
+        ("ghost_off", ctypes.c_int),
     ]
 
 
@@ -88,8 +89,9 @@ def _p(a):
 
 
 def make_param(rho0=1.0, eta_shear=0.1, eta_bulk=0.1, force=(0.0, 0.0, 0.0),
-               nrelax=RELAX_M10, mobility=0.0, a=0.0, b=0.0, kappa=0.0):
+               nrelax=RELAX_M10, mobility=0.0, a=0.0, b=0.0, kappa=0.0, ghost_off=0):
     prm = Param()
+    prm.ghost_off = ghost_off
     prm.rho0, prm.eta_shear, prm.eta_bulk = rho0, eta_shear, eta_bulk
     prm.force_global[:] = force
     prm.nrelax = nrelax

@@ -170,6 +170,9 @@ class Ref:
         again with that master seed)."""
         assert self.L.refdrv_noise(int(on), float(kt), int(reseed)) == 0
 
+    def ghost_modes(self, on):
+        assert self.L.refdrv_ghost_modes(int(on)) == 0
+
     def noise_state(self):
         return self._arr(self.L.refdrv_noise_state(), (self.nsite, 4))
 

@@ -252,6 +252,10 @@ int refdrv_noise(int on, double kt, int reseed) {
   physics_kt_set(rd.phys, kt);
   return noise_present_set(rd.noise, NOISE_RHO, on);
 }
+/* "lb_ghost_modes off" (src/collision_rt.c:87-102) */
+int refdrv_ghost_modes(int on) {
+  return on ? lb_collision_ghost_modes_on(rd.lb) : lb_collision_ghost_modes_off(rd.lb);
+}
 unsigned int * refdrv_noise_state(void) { return rd.noise->state; }
 unsigned int refdrv_noise_uniform(unsigned int state[4]) { return noise_uniform(state); }
 int refdrv_noise_reap_n(int index, int nmax, double * reap) {

@@ -1,6 +1,8 @@
 """Extracts the statistics block printed after the last time step from the reference's own
 regression golden logs (tests/regression/d3q19-short/serial-dist-*.log, d2q9/serial-2khz-bm1.log
-and the fluctuating-hydrodynamics case d2q9/serial-flct-t01.log, Ludwig v0.20.1)
+the fluctuating-hydrodynamics case d2q9/serial-flct-t01.log and the binary-fluid spinodal
+cases d3q19-short/serial-spin-lb{1,3,4}.log (symmetric_lb, 27-point gradient, lb3/lb4 with
+fluctuations, lb1/lb4 with ghost modes off), Ludwig v0.20.1)
 into tests/golden/regression_logs.json, together with the input keys that define each
 case. Run in the build container (needs /root/reference)."""
 
@@ -12,7 +14,8 @@ REF = "/root/reference/tests/regression"
 HERE = os.path.dirname(os.path.abspath(__file__))
 CASES = ["d3q19-short/serial-dist-3du", "d3q19-short/serial-dist-1dp",
          "d3q19-short/serial-dist-2kh", "d3q19-short/serial-dist-2sw", "d2q9/serial-2khz-bm1",
-         "d2q9/serial-flct-t01"]
+         "d2q9/serial-flct-t01", "d3q19-short/serial-spin-lb1", "d3q19-short/serial-spin-lb3",
+         "d3q19-short/serial-spin-lb4"]
 NVEL = {"d3q19-short": 19, "d2q9": 9}
 
 
@@ -32,12 +35,16 @@ def main():
             inp[parts[0]] = parts[1] if len(parts) > 1 else ""
         lines = open(os.path.join(REF, case + ".log")).read().splitlines()
         start = max(i for i, l in enumerate(lines) if l.startswith("Scalars - total"))
-        blk = lines[start:start + 16]
+        blk = lines[start:start + 20]
         rec = {"input": inp, "nvel": NVEL[case.split("/")[0]],
                "source": "tests/regression/%s.log:%d-%d" % (case, start + 1, start + 10)}
         for l in blk:
             if l.startswith("[rho]"):
                 rec["rho"] = floats(l)                 # total mean variance min max
+            if l.startswith("[phi]"):
+                rec["phi"] = floats(l)                 # total mean variance min max
+            if l.startswith("[fed]"):
+                rec["fed"] = floats(l)                 # total/volume, fluid mean
             if l.startswith("[total   ]"):
                 rec["momentum"] = floats(l)
             if l.startswith("[minimum ]"):

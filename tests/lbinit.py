@@ -76,3 +76,52 @@ def make_force(nlocal, ntotal=None, offset=(0, 0, 0), amp=1.0e-3, ndim=3):
     for a in range(ndim):
         force[:, a] = amp * uniform(ids, 80 + a)
     return force
+
+
+# ---------------------------------------------------------------------------
+# Ludwig's own initial conditions that draw from its lattice generator
+# ---------------------------------------------------------------------------
+
+def kiss99(s):
+    """One step of the per-site generator (src/noise.c:456-472) for every row of the
+    uint32 array s[n, 4], in place; returns the n outputs (uint32)."""
+    assert s.dtype == np.uint32
+    m16 = np.uint32(65535)
+    s[:, 0] = np.uint32(69069) * s[:, 0] + np.uint32(1234567)
+    x = s[:, 1].copy()
+    x ^= x << np.uint32(17)
+    x ^= x >> np.uint32(13)
+    x ^= x << np.uint32(5)
+    s[:, 1] = x
+    s[:, 2] = np.uint32(36969) * (s[:, 2] & m16) + (s[:, 2] >> np.uint32(16))
+    s[:, 3] = np.uint32(18000) * (s[:, 3] & m16) + (s[:, 3] >> np.uint32(16))
+    return s[:, 1] + (s[:, 0] ^ ((s[:, 2] << np.uint32(16)) + s[:, 3]))
+
+
+def noise_state_interior(nt, master_seed):
+    """noise_init (src/noise.c:136-233) for the interior sites of a one-rank box nt, in
+    cs_index order: state[n, 4]."""
+    seed0 = np.array([13, 12953, 712357, 22383979], dtype=np.uint32)
+    if master_seed > 0:
+        seed0[0] = np.uint32(master_seed)
+    ig, jg, kg = np.meshgrid(np.arange(1, nt[0] + 1), np.arange(1, nt[1] + 1),
+                             np.arange(1, nt[2] + 1), indexing="ij")
+    n = ig.size
+    local = np.empty((n, 4), dtype=np.uint32)
+    local[:, 0] = seed0[0] + ig.reshape(-1).astype(np.uint32)
+    local[:, 1] = seed0[1] + jg.reshape(-1).astype(np.uint32)
+    local[:, 2] = seed0[2] + kg.reshape(-1).astype(np.uint32)
+    local[:, 3] = seed0[3]
+    state = np.empty((n, 4), dtype=np.uint32)
+    for ia in range(4):
+        state[:, ia] = kiss99(local)
+    return state
+
+
+def spinodal_phi(nt, seed, phi0, amp):
+    """field_phi_init_spinodal (src/field_phi_init.c:484-519): phi = phi0 + amp (r - 1/2),
+    r one full-precision uniform per interior site from a generator seeded with `seed`
+    (noise_uniform_double_reap, src/noise.c:436-452). Returns phi[nt]."""
+    state = noise_state_interior(nt, seed)
+    r = (1.0 / 4294967295.0) * kiss99(state).astype(np.float64)
+    return (phi0 + amp * (r - 0.5)).reshape(nt)

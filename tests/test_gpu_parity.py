@@ -768,11 +768,14 @@ def test_fluctuating_collision_golden(tag, mode):
 
 @pytest.mark.parametrize("nvel,nlocal,nrelax", [(19, (12, 10, 34), 0), (19, (12, 10, 34), 2),
                                                 (9, (40, 36, 1), 0)])
-def test_fluctuating_steps_vs_oracle(nvel, nlocal, nrelax):
+@pytest.mark.parametrize("loopback", [0, 1])
+def test_fluctuating_steps_vs_oracle(nvel, nlocal, nrelax, loopback):
     """Twenty fluctuating steps against the oracle on a lattice large enough for
-    several blocks, TRT included (ghost modes kept AND driven)."""
+    several blocks, TRT included (ghost modes kept AND driven). With loopback the
+    sweep is split into boundary slabs and interior: every site must still draw once."""
     from oracle import pyoracle
     lat, orc = mk(nvel, nlocal)
+    lat.set_option("loopback", loopback)
     kt = 1.0e-4
     f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal, ndim=orc.ndim)
     prm = pyoracle.make_param(eta_shear=0.02, eta_bulk=0.3, nrelax=nrelax)

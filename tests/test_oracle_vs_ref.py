@@ -243,10 +243,12 @@ def test_noise_generator(nvel, nlocal, seed):
     assert abs(lv.mean()) < 1e-15 and abs((lv**2).mean() - 1.0) < 1e-15
 
 
-@pytest.mark.parametrize("nvel,nlocal,ndist,nrelax", [
-    (19, (6, 5, 4), 1, 0), (19, (6, 5, 4), 1, 1), (19, (6, 5, 4), 1, 2),
-    (9, (8, 7, 1), 1, 0), (9, (8, 7, 1), 1, 1), (19, (6, 5, 4), 2, 0)])
-def test_fluctuating_collision(nvel, nlocal, ndist, nrelax):
+@pytest.mark.parametrize("nvel,nlocal,ndist,nrelax,ghost_off", [
+    (19, (6, 5, 4), 1, 0, 0), (19, (6, 5, 4), 1, 1, 0), (19, (6, 5, 4), 1, 2, 0),
+    (9, (8, 7, 1), 1, 0, 0), (9, (8, 7, 1), 1, 1, 0), (19, (6, 5, 4), 2, 0, 0),
+    (19, (6, 5, 4), 1, 0, 1), (19, (6, 5, 4), 1, 1, 1), (19, (6, 5, 4), 2, 0, 1),
+    (19, (6, 5, 4), 2, 1, 1), (9, (8, 7, 1), 1, 0, 1)])
+def test_fluctuating_collision(nvel, nlocal, ndist, nrelax, ghost_off):
     """lb_collide with isothermal fluctuations on: one collision, then the time loop;
     generator state stays bit-identical, populations to round-off."""
     need_ref(nvel)
@@ -256,7 +258,8 @@ def test_fluctuating_collision(nvel, nlocal, ndist, nrelax):
     kw = dict(eta_shear=0.1, eta_bulk=0.07)
     if ndist == 2:
         kw = dict(eta_shear=0.00625, eta_bulk=0.00625, mobility=3.75)
-    prm = pyoracle.make_param(a=-0.00625, b=0.00625, kappa=0.004, nrelax=nrelax, **kw)
+    prm = pyoracle.make_param(a=-0.00625, b=0.00625, kappa=0.004, nrelax=nrelax,
+                              ghost_off=ghost_off, **kw)
     m = orc.interior_mask()
     n = orc.nsite
     state = orc.noise_init(0)
@@ -265,6 +268,7 @@ def test_fluctuating_collision(nvel, nlocal, ndist, nrelax):
         with pyref.Ref(nvel, nlocal, ndist=ndist) as ref:
             ref.physics(**kw)
             ref.relaxation(nrelax)
+            ref.ghost_modes(not ghost_off)
             if ndist == 2:
                 ref.fe_symm(-0.00625, 0.00625, 0.004)
             ref.noise(1, KT)

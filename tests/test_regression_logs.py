@@ -1,6 +1,8 @@
 """Ludwig's own regression logs for the single-fluid path (tests/regression/d3q19-short/
 serial-dist-{3du,1dp,2kh,2sw}.{inp,log}, d2q9/serial-2khz-bm1, 2560 steps of D2Q9, and
-d2q9/serial-flct-t01, 200 fluctuating steps): the statistics printed after the last step,
+d2q9/serial-flct-t01, 200 fluctuating steps; and for the binary fluid d3q19-short/
+serial-spin-lb{1,3,4}: symmetric_lb spinodal decomposition with the 27-point gradient, lb3
+and lb4 fluctuating, lb1 and lb4 with ghost modes off): the statistics printed after the last step,
 reproduced the way tests/test-diff.sh + tests/awk-fp-diff.sh judge them -- every printed
 float, in the reference's printf format, within an ABSOLUTE 1e-12.
 
@@ -60,9 +62,17 @@ def initial_state(inp, cv, wv):
     if "2d_kelvin_helmholtz_rho0" in inp:
         raise ValueError("rho0 key not handled")
     feq = lbinit.equilibrium(cv, wv, np.ones(int(np.prod(nt))), u.reshape(-1, 3))
-    f = np.zeros(nall + (1, len(wv)))
+    ndist = 2 if inp.get("free_energy") == "symmetric_lb" else 1
+    f = np.zeros(nall + (ndist, len(wv)))
     f[1:-1, 1:-1, 1:-1, 0, :] = feq.reshape(nt + (len(wv),))
-    return nt, np.ascontiguousarray(f.reshape(-1, 1, len(wv)))
+    if ndist == 2:
+        # phi_initialisation spinodal (src/field_phi_init_rt.c:57-65), then phi_lb_from_field
+        # (src/phi_lb_coupler.c:114): phi into the rest population, the others zero
+        assert inp.get("phi_initialisation", "spinodal") == "spinodal"
+        phi = lbinit.spinodal_phi(nt, int(inp.get("random_seed", 13)), float(inp.get("phi0", 0.0)),
+                                  float(inp.get("noise", 0.1)))
+        f[1:-1, 1:-1, 1:-1, 1, 0] = phi
+    return nt, np.ascontiguousarray(f.reshape(-1, ndist, len(wv)))
 
 
 def printed(fmt, x):
@@ -107,7 +117,43 @@ def check_equipartition(rec, f_interior, cv):
 
 
 def noisy(rec):
-    return rec["input"].get("isothermal_fluctuations") == "on"
+    inp = rec["input"]          # src/collision_rt.c:49-62: either key
+    return inp.get("isothermal_fluctuations") == "on" or inp.get("lb_fluctuations") in ("yes", "on", "1")
+
+
+def ghost_off(rec):
+    inp = rec["input"]          # src/collision_rt.c:87-102: either key
+    return inp.get("lb_ghost_modes") in ("off", "no", "0") or inp.get("ghost_modes") == "off"
+
+
+def gradient_points(rec):
+    return 27 if rec["input"].get("fd_gradient_calculation") == "3d_27pt_fluid" else 7
+
+
+def binary_params(inp):
+    return dict(a=float(inp["A"]), b=float(inp["B"]), kappa=float(inp["K"]),
+                mobility=float(inp["mobility"]))
+
+
+def check_binary(rec, nt, f_interior, grad_interior):
+    """[phi] line (stats_field_info_bbl, src/phi_stats.c:295-341) and [fed] line
+    (stats_free_energy_density, src/stats_free_energy.c:38-133 with fe_symm_fed,
+    src/symmetric.c:285-299). As in ludwig_report_statistics (src/ludwig.c:2334-2342) phi
+    is recomputed from the distributions at the end of the step, while the gradient is
+    the one the last time step computed."""
+    vol = float(np.prod(nt))
+    phi = f_interior[:, 1, :].sum(-1)
+    mean = phi.sum()/vol
+    var = (phi*phi).sum()/vol - mean*mean
+    mine = [printed("%14.7e", x) for x in (phi.sum(), mean, var, phi.min(), phi.max())]
+    for a, b in zip(mine, rec["phi"]):
+        assert abs(a - b) <= 1e-12, ("phi", mine, rec["phi"])
+    p = binary_params(rec["input"])
+    fed = (0.5*p["a"] + 0.25*p["b"]*phi*phi)*phi*phi \
+        + 0.5*p["kappa"]*(grad_interior*grad_interior).sum(-1)
+    mine = [printed("%17.10e", fed.sum()/vol), printed("%17.10e", fed.sum()/vol)]
+    for a, b in zip(mine, rec["fed"]):
+        assert abs(a - b) <= 1e-12, ("fed", mine, rec["fed"])
 
 
 def viscosities(inp):
@@ -122,21 +168,29 @@ def test_oracle_reproduces_reference_log(case):
     nvel = rec["nvel"]
     o0 = pyoracle.Oracle(nvel, (2, 2, 1 if nvel == 9 else 2))
     nt, f = initial_state(rec["input"], o0.cv(), o0.wv())
-    orc = pyoracle.Oracle(nvel, nt)
     eta, zeta = viscosities(rec["input"])
-    prm = pyoracle.make_param(eta_shear=eta, eta_bulk=zeta)
+    ndist = f.shape[1]
+    orc = pyoracle.Oracle(nvel, nt, ndist=ndist)
+    kw = binary_params(rec["input"]) if ndist == 2 else {}
+    prm = pyoracle.make_param(eta_shear=eta, eta_bulk=zeta, ghost_off=int(ghost_off(rec)), **kw)
     n = orc.nsite
     fp = np.zeros_like(f)
     rho, u, frc = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
+    phi, grad, delsq = np.zeros(n), np.zeros((n, 3)), np.zeros(n)
     if noisy(rec):
         # ludwig.c:243 noise_init(noise_rho, 0): the input's random_seed is for colloids
+        # and the order-parameter initialisation
         orc.noise_attach(orc.noise_init(0), float(rec["input"]["temperature"]))
+    orc.gradient_select(gradient_points(rec))
     try:
-        orc.step(prm, int(rec["input"]["N_cycles"]), f, fp, rho, u, frc)
+        orc.step(prm, int(rec["input"]["N_cycles"]), f, fp, rho, u, frc, phi, grad, delsq)
     finally:
         orc.noise_attach(None, 0.0)
+        orc.gradient_select(7)
     m = orc.interior_mask()
     check(rec, nt, orc.stats(f), u[m])
+    if ndist == 2:
+        check_binary(rec, nt, f[m], grad[m])
     if noisy(rec):
         check_equipartition(rec, f[m][:, 0], orc.cv())
 
@@ -151,11 +205,15 @@ def test_cuda_reproduces_reference_log(case, hydro_write):
     nvel = rec["nvel"]
     nt, f = initial_state(rec["input"], models_host.cv(nvel), models_host.wv(nvel))
     eta, zeta = viscosities(rec["input"])
-    lat = lb.Lattice(nvel, nt)
+    ndist = f.shape[1]
+    lat = lb.Lattice(nvel, nt, ndist=ndist)
     lat.set_option("hydro_write", hydro_write)
     lat.set_option("halo", lb.HALO_REDUCED)          # lb_halo_openmp_reduced in the input
     kt = float(rec["input"].get("temperature", 0.0)) if noisy(rec) else 0.0
-    lat.set_param(eta_shear=eta, eta_bulk=zeta, kt=kt)
+    kw = binary_params(rec["input"]) if ndist == 2 else {}
+    lat.set_param(eta_shear=eta, eta_bulk=zeta, kt=kt, ghost_off=int(ghost_off(rec)), **kw)
+    if ndist == 2:
+        lat.field_grad_set(gradient_points(rec))
     if noisy(rec):
         lat.noise_init(0)
         lat.noise_present_set(1)
@@ -167,6 +225,9 @@ def test_cuda_reproduces_reference_log(case, hydro_write):
     m = np.zeros(nall, dtype=bool)
     m[1:-1, 1:-1, 1:-1] = True
     check(rec, nt, sums, u[m.reshape(-1)])
+    fh = lat.lb_memcpy_d2h()[m.reshape(-1)]
+    if ndist == 2:
+        check_binary(rec, nt, fh, lat.field_d2h(lb.FIELD_GRAD)[m.reshape(-1)])
     if noisy(rec):
-        check_equipartition(rec, lat.lb_memcpy_d2h()[m.reshape(-1)][:, 0], models_host.cv(nvel))
+        check_equipartition(rec, fh[:, 0], models_host.cv(nvel))
     lat.close()
