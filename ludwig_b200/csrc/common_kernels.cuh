@@ -207,34 +207,41 @@ grad27_kernel(const Layout L, const int w0, const int w1, const int w2,
   }
   const bool second = (tid + G27_TZ*G27_TY < G27_NE);
 
-  auto load_plane = [&](int slot, int xa) {
+  // global -> registers -> shared, so that the loads of plane x + 3 are in flight while
+  // plane x + 1 .. x - 1 is being worked on
+  auto fetch = [&](int xa, double (&r)[2]) {
     if (w0) xa = (xa == 0) ? L.n[0] : ((xa == L.n[0] + 1) ? 1 : xa);
     const double * pl = phi + (i64) xa*L.s0;
-    sm[slot][er[0]][ec[0]] = __ldg(pl + off[0]);
-    if (second) sm[slot][er[1]][ec[1]] = __ldg(pl + off[1]);
+    r[0] = __ldg(pl + off[0]);
+    r[1] = second ? __ldg(pl + off[1]) : 0.0;
+  };
+  auto stash = [&](int slot, const double (&r)[2]) {
+    sm[slot][er[0]][ec[0]] = r[0];
+    if (second) sm[slot][er[1]][ec[1]] = r[1];
   };
 
   double m[3][3], c[3][3], p[3][3];
+  double nxt[2];
 
-  load_plane(0, x0);                    // halo-inclusive plane of interior x0 - 1
+  fetch(x0, nxt);                       // halo-inclusive plane of interior x0 - 1
+  stash(0, nxt);
+  fetch(x0 + 1, nxt);
+  stash(1, nxt);
+  fetch(x0 + 2, nxt);
   __syncthreads();
   #pragma unroll
   for (int j = 0; j < 3; j++)
     #pragma unroll
-    for (int k = 0; k < 3; k++) m[j][k] = sm[0][ty + j][tz + k];
-  load_plane(1, x0 + 1);
+    for (int k = 0; k < 3; k++) { m[j][k] = sm[0][ty + j][tz + k]; c[j][k] = sm[1][ty + j][tz + k]; }
   __syncthreads();
-  #pragma unroll
-  for (int j = 0; j < 3; j++)
-    #pragma unroll
-    for (int k = 0; k < 3; k++) c[j][k] = sm[1][ty + j][tz + k];
 
   const double r9 = 1.0/9.0;
   const double hr9 = 0.5*r9;
 
   for (int x = x0; x < x1; x++) {
     const int slot = (x - x0) & 1;
-    load_plane(slot, x + 2);
+    stash(slot, nxt);
+    if (x + 1 < x1) fetch(x + 3, nxt);
     __syncthreads();
     #pragma unroll
     for (int j = 0; j < 3; j++)
