@@ -175,6 +175,21 @@ int  b200lb_stats(b200lb_t * h, double out[8]);
  * lb_propagation); momentum is sum_p c_p f_p. Costs no extra pass over the lattice. */
 int  b200lb_step_diag(b200lb_t * h, double out[8]);
 
+/* Device reductions of a field over the interior sites of this rank, per component c:
+ * out[4c + 0..3] = sum, sum of squares, min, max. B200LB_FIELD_U gives what
+ * stats_velocity_minmax reports (src/stats_velocity.c:43-107), B200LB_FIELD_PHI what
+ * stats_field_info / stats_field_q_reduce sums (src/phi_stats.c:89-230), without the
+ * full-field D2H of src/ludwig.c:955,2335; the caller finishes with its MPI_Reduce. */
+int  b200lb_field_stats(b200lb_t * h, int field, double * out);
+
+/* lb_io_aggr_pack / lb_io_aggr_unpack with binary records (src/model.c:1498-1560): the
+ * interior sites in (ic,jc,kc) order, kc fastest, b200lb_io_record_doubles() =
+ * ndist*nvel doubles per site ordered [n][p] (lb_write_buf, src/model.c:1385) -- the
+ * io_aggregator_t buffer lb_io_write hands to MPI-IO, filled straight from the device. */
+long b200lb_io_record_doubles(const b200lb_t * h);
+int  b200lb_io_pack(b200lb_t * h, double * buf);
+int  b200lb_io_unpack(b200lb_t * h, const double * buf);
+
 int  b200lb_sync(b200lb_t * h);          /* tdpDeviceSynchronize for this handle */
 
 /* Multi-GPU: one rank per GPU; halo planes go device-to-device with NCCL

@@ -1474,10 +1474,8 @@ extern "C" int b200lb_field_upload(b200lb_t * h, int field, const double * host,
   return transfer(h, dev, nf, const_cast<double *>(host), layout, true);
 }
 
-extern "C" int b200lb_field_download(b200lb_t * h, int field, double * host, int layout) {
-  if (!h || !host) return fail("null argument");
-  double * dev; int nf;
-  if (field_info(h, field, &dev, &nf)) return -1;
+// bring the device arrays of `field` up to date with everything recorded lazily
+static int field_current(b200lb_s * h, int field) {
   if (field == B200LB_FIELD_FORCE && h->force_uniform) {
     if (fill3(h, h->force, 3, h->fconst)) return -1;
   }
@@ -1493,7 +1491,109 @@ extern "C" int b200lb_field_download(b200lb_t * h, int field, double * host, int
     if (h->grad_state == 2) return fail("the gradient of the previous order parameter was never materialised (option grad_lazy = 0 keeps the arrays current)");
     if (h->grad_state == 1) { if (run_grad7(h)) return -1; }
   }
+  return 0;
+}
+
+extern "C" int b200lb_field_download(b200lb_t * h, int field, double * host, int layout) {
+  if (!h || !host) return fail("null argument");
+  double * dev; int nf;
+  if (field_info(h, field, &dev, &nf)) return -1;
+  if (field_current(h, field)) return -1;
   return transfer(h, dev, nf, host, layout, false);
+}
+
+// Device reductions over the interior sites of this rank, per component:
+// out[4*c + 0..3] = sum, sum of squares, min, max. What stats_velocity_minmax
+// (src/stats_velocity.c:43-107) and stats_field_info (src/phi_stats.c:89-132,145-230)
+// compute on the host after a full-field D2H; the caller finishes with the same
+// MPI_Reduce over ranks as the reference.
+extern "C" int b200lb_field_stats(b200lb_t * h, int field, double * out) {
+  if (!h || !out) return fail("null argument");
+  double * dev; int nf;
+  if (field_info(h, field, &dev, &nf)) return -1;
+  if (field_current(h, field)) return -1;
+  if (join_comm(h)) return -1;
+  const Layout & L = h->L;
+  dim3 block(128, 2, 1);
+  dim3 grid((L.n[2] + 127)/128, (L.n[1] + 1)/2, L.n[0]);
+  for (int c = 0; c < nf; c++) {
+    field_stats_kernel<<<grid, block, 0, h->s_main>>>(L, dev + (i64) c*L.nsd, h->partial);
+    stats_final_kernel<<<1, 256, 0, h->s_main>>>(h->partial, h->npartial, h->stats_dev);
+    CU(cudaGetLastError());
+    h->launches += 2;
+    CU(cudaMemcpyAsync(h->stats_host, h->stats_dev, 8*sizeof(double), cudaMemcpyDeviceToHost, h->s_main));
+    CU(cudaStreamSynchronize(h->s_main));
+    for (int k = 0; k < 4; k++) out[4*c + k] = h->stats_host[k];
+  }
+  return 0;
+}
+
+// lb_io_aggr_pack / lb_io_aggr_unpack with binary records (src/model.c:1498-1560,
+// lb_write_buf :1385): the interior sites in (ic,jc,kc) order, kc fastest, each record
+// [n][p] doubles -- packed straight from the device layout, so the halo shell never
+// crosses PCIe and the host does no repacking pass.
+static int io_transfer(b200lb_s * h, double * buf, bool to_device) {
+  if (ensure_stage(h)) return -1;
+  if (join_comm(h)) return -1;
+  CU(cudaStreamSynchronize(h->s_main));
+  XferParams X;
+  memset(&X, 0, sizeof(X));
+  X.L = h->L;
+  for (int a = 0; a < 3; a++) { X.hostdim[a] = h->desc.nlocal[a]; X.dax[a] = h->ops->dax[a]; X.hoff[a] = 1; }
+  X.dev = h->lat[h->cur];
+  const int nel = h->nplane;
+  const i64 ns = (i64) h->desc.nlocal[0]*h->desc.nlocal[1]*h->desc.nlocal[2];
+  const i64 chunk = (i64) (STAGE_BYTES/sizeof(double))/nel;
+  X.aos = 1; X.nel = nel; X.e0 = 0;
+  int turn = 0;
+  for (i64 s0 = 0; s0 < ns; s0 += chunk, turn ^= 1) {
+    const i64 s1 = (s0 + chunk < ns) ? s0 + chunk : ns;
+    cudaStream_t st = h->s_x[turn];
+    X.stage = h->stage[turn]; X.hs0 = s0; X.hs1 = s1;
+    const size_t nb = (size_t) (s1 - s0)*nel*sizeof(double);
+    const unsigned nblk = (unsigned) ((s1 - s0 + 255)/256);
+    if (to_device) {
+      CU(cudaMemcpyAsync(X.stage, buf + s0*nel, nb, cudaMemcpyHostToDevice, st));
+      xfer_kernel<1><<<nblk, 256, 0, st>>>(X);
+    }
+    else {
+      xfer_kernel<0><<<nblk, 256, 0, st>>>(X);
+      CU(cudaMemcpyAsync(buf + s0*nel, X.stage, nb, cudaMemcpyDeviceToHost, st));
+    }
+    CU(cudaGetLastError());
+    h->launches++;
+  }
+  CU(cudaStreamSynchronize(h->s_x[0]));
+  CU(cudaStreamSynchronize(h->s_x[1]));
+  return 0;
+}
+
+extern "C" long b200lb_io_record_doubles(const b200lb_t * h) {
+  return h ? (long) h->nplane : 0;
+}
+
+extern "C" int b200lb_io_pack(b200lb_t * h, double * buf) {
+  if (!h || !buf) return fail("null argument");
+  if (h->prop_pending) { if (materialise(h)) return -1; }
+  return io_transfer(h, buf, false);
+}
+
+extern "C" int b200lb_io_unpack(b200lb_t * h, const double * buf) {
+  if (!h || !buf) return fail("null argument");
+  if (ensure_hydro(h)) return -1;
+  h->prop_pending = false;
+  h->halo_deferred = false;
+  if (io_transfer(h, const_cast<double *>(buf), true)) return -1;
+  if (h->p2p_ready && h->opt_p2p) {
+    // like lb_memcpy H2D: the restart read takes part in the signal/wait protocol
+    h->push_step++;
+    p2p_signal_kernel<<<1, 32, 0, h->s_main>>>(h->p2p, h->push_step);
+    CU(cudaGetLastError());
+    h->launches++;
+    h->push_wait_pending = true;
+    h->pushed_valid = false;
+  }
+  return 0;
 }
 
 // ---------------------------------------------------------------------------

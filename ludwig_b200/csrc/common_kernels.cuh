@@ -305,6 +305,22 @@ __global__ void fill_kernel(double * __restrict__ data, i64 n, i64 plane, int nf
   if (nf > 2) data[2*plane + i] = v2;
 }
 
+// sum, sum of squares, min, max of one field component over interior sites
+__global__ void __launch_bounds__(256)
+field_stats_kernel(const Layout L, const double * __restrict__ data, double * __restrict__ partial) {
+  const int i2 = blockIdx.x*blockDim.x + threadIdx.x;
+  const int i1 = blockIdx.y*blockDim.y + threadIdx.y;
+  const int i0 = blockIdx.z;
+  double q[8] = {0.0, 0.0, 1.0e300, -1.0e300, 0.0, 0.0, 0.0, 0.0};
+  if (i2 < L.n[2] && i1 < L.n[1]) {
+    const i64 site = (i64)(i0 + L.h[0])*L.s0 + (i64)(i1 + L.h[1])*L.s1 + L.z0 + L.h[2] + i2;
+    const double v = __ldg(data + site);
+    q[0] = v; q[1] = v*v; q[2] = v; q[3] = v;
+  }
+  const i64 b = ((i64) blockIdx.z*gridDim.y + blockIdx.y)*gridDim.x + blockIdx.x;
+  block_reduce8(q, partial + 8*b);
+}
+
 __global__ void __launch_bounds__(256)
 stats_final_kernel(const double * __restrict__ partial, i64 nblock, double * __restrict__ out) {
   double q[8] = {0.0, 0.0, 1.0e300, -1.0e300, 0.0, 0.0, 0.0, 0.0};
@@ -341,6 +357,8 @@ struct XferParams {
   int nel;            // planes per site in an AOS piece
   int e0;             // first device plane (SOA piece: the plane)
   int aos;
+  int hoff[3];        // added to the decoded host coordinates: 0 = the host index space is
+                      // the halo-inclusive box, 1 = interior sites only (file records)
   int half;           // SOA piece of 32-bit words: 1 = low, 2 = high half of the 64-bit device
                       // element, stage holds unsigned ints (noise state); 0 = doubles
 };
@@ -352,10 +370,10 @@ xfer_kernel(const XferParams X) {
   if (hs >= X.hs1) return;
   const Layout & L = X.L;
   int pc[3];
-  pc[2] = (int) (hs % X.hostdim[2]);
+  pc[2] = (int) (hs % X.hostdim[2]) + X.hoff[2];
   const i64 r = hs / X.hostdim[2];
-  pc[1] = (int) (r % X.hostdim[1]);
-  pc[0] = (int) (r / X.hostdim[1]);
+  pc[1] = (int) (r % X.hostdim[1]) + X.hoff[1];
+  pc[0] = (int) (r / X.hostdim[1]) + X.hoff[0];
   int dc[3];
   bool primary = true;     // false for replicated planes of the unit axis
   #pragma unroll

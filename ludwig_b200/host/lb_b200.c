@@ -3,6 +3,7 @@
  * libb200lb.so. No arithmetic on lattice data happens on the host.
  */
 
+#include <float.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -323,5 +324,49 @@ int fe_symm_param_set(fe_symm_t * fe, fe_symm_param_t values) { fe->param = valu
 
 int stats_distribution_sums(lb_t * lb, double sums[8]) {
   TRY(b200lb_stats(lb->target, sums));
+  return 0;
+}
+
+/* stats_velocity_minmax (src/stats_velocity.c:53-130) without hydro_memcpy: extrema
+ * start from FLT_MAX / FLT_MIN as there (:75-76); usum is the volume flux. */
+int stats_velocity_minmax(stats_vel_t * stat, hydro_t * hydro, map_t * map) {
+  double q[12];
+  (void) map;
+  TRY(b200lb_field_stats(hydro->lb->target, B200LB_FIELD_U, q));
+  for (int ia = 0; ia < 3; ia++) {
+    stat->usum[ia] = q[4*ia + 0];
+    stat->umin[ia] = (q[4*ia + 2] < FLT_MAX) ? q[4*ia + 2] : FLT_MAX;
+    stat->umax[ia] = (q[4*ia + 3] > FLT_MIN) ? q[4*ia + 3] : FLT_MIN;
+  }
+  return 0;
+}
+
+/* stats_field_info for a scalar (src/phi_stats.c:89-132): sum, mean, variance, min, max */
+int stats_field_info_scalar(field_t * phi, map_t * map, double out[5]) {
+  double q[4];
+  const cs_t * cs = phi->lb->cs;
+  const double vol = (double) cs->nlocal[0]*cs->nlocal[1]*cs->nlocal[2];
+  (void) map;
+  TRY(b200lb_field_stats(phi->lb->target, phi->id, q));
+  out[0] = q[0];
+  out[1] = q[0]/vol;
+  out[2] = q[1]/vol - out[1]*out[1];
+  out[3] = q[2];
+  out[4] = q[3];
+  return 0;
+}
+
+/* lb_io_aggr_pack / _unpack, binary records (src/model.c:1498-1560) */
+int lb_io_aggr_pack(const lb_t * lb, io_aggregator_t * aggr) {
+  if (aggr->szelement != (size_t) b200lb_io_record_doubles(lb->target)*sizeof(double)) {
+    snprintf(host_err, sizeof(host_err), "lb_io_aggr_pack: record size %zu", aggr->szelement);
+    return -1;
+  }
+  TRY(b200lb_io_pack(lb->target, (double *) aggr->buf));
+  return 0;
+}
+
+int lb_io_aggr_unpack(lb_t * lb, const io_aggregator_t * aggr) {
+  TRY(b200lb_io_unpack(lb->target, (const double *) aggr->buf));
   return 0;
 }

@@ -153,6 +153,17 @@ int fe_symm_create(field_t * phi, field_grad_t * dphi, fe_symm_t ** fe);
 int fe_symm_free(fe_symm_t * fe);
 int fe_symm_param_set(fe_symm_t * fe, fe_symm_param_t values);
 
+/* stats_vel_t as filled by stats_velocity_minmax (src/stats_velocity.h) */
+typedef struct stats_vel_s { double umin[3], umax[3], usum[3]; } stats_vel_t;
+int stats_velocity_minmax(stats_vel_t * stat, hydro_t * hydro, map_t * map);
+/* the numbers stats_field_info prints for a scalar field: total mean variance min max */
+int stats_field_info_scalar(field_t * phi, map_t * map, double out[5]);
+
+/* io_aggregator_t (src/io_aggregator.h:23-29), the members the LB records use */
+typedef struct io_aggregator_s { size_t szelement; size_t szbuf; char * buf; } io_aggregator_t;
+int lb_io_aggr_pack(const lb_t * lb, io_aggregator_t * aggr);      /* src/model.c:1498 */
+int lb_io_aggr_unpack(lb_t * lb, const io_aggregator_t * aggr);    /* src/model.c:1534 */
+
 /* stats_distribution_print / stats_distribution_momentum sums (src/stats_distribution.c) */
 int stats_distribution_sums(lb_t * lb, double sums[8]);
 

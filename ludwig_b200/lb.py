@@ -34,6 +34,7 @@ ABI_SYMBOLS = [
     "b200lb_propagate", "b200lb_phi_from_g", "b200lb_phi_halo", "b200lb_grad7", "b200lb_grad27",
     "b200lb_noise_init", "b200lb_noise_present_set", "b200lb_noise_state_upload",
     "b200lb_noise_state_download",
+    "b200lb_field_stats", "b200lb_io_record_doubles", "b200lb_io_pack", "b200lb_io_unpack",
     "b200lb_step", "b200lb_stats", "b200lb_step_diag", "b200lb_sync", "b200lb_nccl_unique_id",
     "b200lb_comm_init", "b200lb_p2p_export", "b200lb_p2p_import", "b200lb_timer_start", "b200lb_timer_stop",
     "b200lb_launch_count", "b200lb_host_alloc", "b200lb_host_free",
@@ -108,6 +109,11 @@ def load():
                  "b200lb_hydro_correct_momentum", "b200lb_timer_start", "b200lb_nsite", "b200lb_launch_count"):
         getattr(L, name).argtypes = [vp]
     L.b200lb_halo_swap.argtypes = [vp, ctypes.c_int]
+    L.b200lb_field_stats.argtypes = [vp, ctypes.c_int, vp]
+    L.b200lb_io_record_doubles.argtypes = [vp]
+    L.b200lb_io_record_doubles.restype = ctypes.c_long
+    L.b200lb_io_pack.argtypes = [vp, vp]
+    L.b200lb_io_unpack.argtypes = [vp, vp]
     L.b200lb_noise_init.argtypes = [vp, ctypes.c_int]
     L.b200lb_noise_present_set.argtypes = [vp, ctypes.c_int]
     L.b200lb_noise_state_upload.argtypes = [vp, vp, ctypes.c_int]
@@ -295,6 +301,26 @@ class Lattice:
             self._ck(self.L.b200lb_grad27(self.h))
         else:
             self._ck(self.L.b200lb_grad7(self.h))
+
+    # -- statistics and file records without the full-field D2H ---------------------
+    def field_stats(self, field):
+        """[nf, 4]: sum, sum of squares, min, max of each component over interior sites."""
+        nf = _FIELD_NF[field]
+        out = np.zeros((nf, 4))
+        self._ck(self.L.b200lb_field_stats(self.h, field, _ptr(out)))
+        return out
+
+    def lb_io_aggr_pack(self, buf=None):
+        """Binary records of lb_io_write: [interior site (kc fastest), n, p]."""
+        if buf is None:
+            buf = np.zeros((int(np.prod(self.nlocal)), self.ndist, self.nvel))
+        assert buf.size == int(np.prod(self.nlocal)) * self.L.b200lb_io_record_doubles(self.h)
+        self._ck(self.L.b200lb_io_pack(self.h, _ptr(buf)))
+        return buf
+
+    def lb_io_aggr_unpack(self, buf):
+        assert buf.size == int(np.prod(self.nlocal)) * self.L.b200lb_io_record_doubles(self.h)
+        self._ck(self.L.b200lb_io_unpack(self.h, _ptr(buf)))
 
     # -- isothermal fluctuations (noise_t, src/noise.h) ------------------------------
     def noise_init(self, master_seed=0):

@@ -116,6 +116,21 @@ int orc_fluctuations(const orc_model_t * model, const double * rtau, double kt,
 		     int ghost_off, unsigned int * state, long index,
 		     double shat[3][3], double * ghat);
 
+/* Flat no-slip walls (lb_oracle_wall.c; src/wall.c). While a wall is attached
+ * orc_step runs the bounce-back on links between halo and propagation. */
+typedef struct orc_wall_s {
+  int isboundary[3];      /* boundary_walls */
+  double ubot[3];         /* boundary_speed_bottom (used for a single pair of walls) */
+  double utop[3];
+  double fnet[3];         /* momentum handed to the walls so far (wall_momentum) */
+} orc_wall_t;
+int orc_wall_attach(orc_wall_t * wall);
+orc_wall_t * orc_wall_attached(void);
+int orc_wall_nlink(const orc_model_t * model, const orc_box_t * box,
+		   const orc_wall_t * wall);
+int orc_wall_bbl(const orc_model_t * model, const orc_box_t * box,
+		 const orc_param_t * prm, int ndist, orc_wall_t * wall, double * f);
+
 int orc_fill(const orc_box_t * box, int nf, const double * v, double * data);
 
 /* stats[0..7] = sum rho, sum rho^2 (about mean is left to caller), min, max,

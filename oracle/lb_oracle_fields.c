@@ -413,6 +413,12 @@ int orc_step(const orc_model_t * model, const orc_box_t * box,
       }
     }
     orc_halo_periodic(box, ndist*model->nvel, a);
+    if (orc_wall_attached()) {
+      /* src/ludwig.c:837-842. The periodic copies above also filled the wall layers,
+       * which the reference leaves alone; every population a fluid site pulls out of
+       * a wall layer is overwritten here, so it makes no difference. */
+      orc_wall_bbl(model, box, prm, ndist, orc_wall_attached(), a);
+    }
     orc_propagate(model, box, ndist, a, b);
     t = a; a = b; b = t;
   }

@@ -51,6 +51,15 @@ class Param(ctypes.Structure):
     ]
 
 
+class Wall(ctypes.Structure):
+    _fields_ = [
+        ("isboundary", ctypes.c_int * 3),
+        ("ubot", ctypes.c_double * 3),
+        ("utop", ctypes.c_double * 3),
+        ("fnet", ctypes.c_double * 3),
+    ]
+
+
 class Box(ctypes.Structure):
     _fields_ = [
         ("nlocal", ctypes.c_int * 3),
@@ -193,6 +202,27 @@ class Oracle:
 
     def gradient_select(self, npt):
         assert self.L.orc_gradient_select(int(npt)) == 0
+
+    # -- flat walls (oracle/lb_oracle_wall.c) ---------------------------------------
+    def wall(self, isboundary, ubot=(0.0, 0.0, 0.0), utop=(0.0, 0.0, 0.0)):
+        w = Wall()
+        w.isboundary[:] = isboundary
+        w.ubot[:] = ubot
+        w.utop[:] = utop
+        return w
+
+    def wall_attach(self, wall):
+        """orc_step applies bounce-back on links while a wall is attached (None: off)."""
+        self._wall = wall                      # keep it alive
+        self.L.orc_wall_attach(None if wall is None else ctypes.byref(wall))
+
+    def wall_nlink(self, wall):
+        return self.L.orc_wall_nlink(ctypes.byref(self.model), ctypes.byref(self.box),
+                                     ctypes.byref(wall))
+
+    def wall_bbl(self, prm, wall, f):
+        self.L.orc_wall_bbl(ctypes.byref(self.model), ctypes.byref(self.box), ctypes.byref(prm),
+                            self.ndist, ctypes.byref(wall), _p(f))
 
     # -- isothermal fluctuations (oracle/lb_oracle_noise.c) ------------------------
     def noise_init(self, master_seed=0, noffset=(0, 0, 0), ntotal=None):

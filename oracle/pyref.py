@@ -57,10 +57,11 @@ def _lib(nvel):
 class Ref:
     """Reference objects on a periodic one-rank box ntotal, halo width 1."""
 
-    def __init__(self, nvel, ntotal, ndist=1, halo=HALO_TARGET):
+    def __init__(self, nvel, ntotal, ndist=1, halo=HALO_TARGET, periodic=(1, 1, 1)):
         self.L = _lib(nvel)
         assert self.L.refdrv_nvel() == nvel
         self.nvel, self.ndist = nvel, ndist
+        self.L.refdrv_periodicity((ctypes.c_int * 3)(*periodic))
         self.L.refdrv_init((ctypes.c_int * 3)(*ntotal), ndist, halo)
         nall = (ctypes.c_int * 3)()
         self.L.refdrv_nall(nall)
@@ -169,6 +170,21 @@ class Ref:
         """isothermal_fluctuations on/off at temperature kt (reseed > 0: noise_init
         again with that master seed)."""
         assert self.L.refdrv_noise(int(on), float(kt), int(reseed)) == 0
+
+    def wall(self, isboundary, ubot=(0.0, 0.0, 0.0), utop=(0.0, 0.0, 0.0)):
+        """boundary_walls / boundary_speed_bottom,_top: wall_create + wall_commit."""
+        rc = self.L.refdrv_wall((ctypes.c_int * 3)(*isboundary), (ctypes.c_double * 3)(*ubot),
+                                (ctypes.c_double * 3)(*utop))
+        assert rc == 0
+        return self.L.refdrv_wall_nlink()
+
+    def wall_bbl(self):
+        assert self.L.refdrv_wall_bbl() == 0
+
+    def wall_momentum(self):
+        out = (ctypes.c_double * 3)()
+        self.L.refdrv_wall_momentum(out)
+        return np.array(out[:])
 
     def ghost_modes(self, on):
         assert self.L.refdrv_ghost_modes(int(on)) == 0

@@ -17,6 +17,7 @@
  *    grad_3d_7pt_fluid_d2 src/gradient_3d_7pt_fluid.c:75
  *    grad_3d_27pt_fluid_d2 src/gradient_3d_27pt_fluid.c:75 (refdrv_grad_select(27))
  *    noise_init / noise_reap_n / noise_present_set  src/noise.c:136,398,557
+ *    wall_create / wall_commit / wall_bbl / wall_momentum  src/wall.c:59,168,960,1299
  *    hydro_f_zero/u_zero  src/hydro.c:306,279
  *
  *  The step sequence of refdrv_step() follows src/ludwig.c:530-862 for the
@@ -48,6 +49,7 @@
 #include "gradient_3d_7pt_fluid.h"
 #include "gradient_3d_27pt_fluid.h"
 #include "timer.h"
+#include "wall.h"
 
 typedef struct refdrv_s {
   pe_t * pe;
@@ -61,6 +63,7 @@ typedef struct refdrv_s {
   field_t * phi;
   field_grad_t * phi_grad;
   fe_symm_t * fe;
+  wall_t * wall;
   int ndist;
   int mpi_up;
 } refdrv_t;
@@ -71,6 +74,14 @@ int refdrv_nvel(void) { return NVEL; }
 int refdrv_ndim(void) { return NDIM; }
 
 /* Create everything for a periodic box ntotal[3], halo width 1. */
+
+static int next_periodic[3] = {1, 1, 1};
+
+/* periodicity of the NEXT refdrv_init ("periodicity" input key, src/coords_rt.c) */
+int refdrv_periodicity(const int periodic[3]) {
+  for (int ia = 0; ia < 3; ia++) next_periodic[ia] = periodic[ia];
+  return 0;
+}
 
 int refdrv_init(const int ntotal[3], int ndist, int halo_scheme) {
 
@@ -85,6 +96,8 @@ int refdrv_init(const int ntotal[3], int ndist, int halo_scheme) {
   cs_create(rd.pe, &rd.cs);
   cs_nhalo_set(rd.cs, nhalo);
   cs_ntotal_set(rd.cs, ntotal);
+  cs_periodicity_set(rd.cs, next_periodic);
+  next_periodic[0] = next_periodic[1] = next_periodic[2] = 1;
   cs_init(rd.cs);
   lees_edw_create(rd.pe, rd.cs, NULL, &rd.le);
 
@@ -122,6 +135,7 @@ int refdrv_init(const int ntotal[3], int ndist, int halo_scheme) {
 
 int refdrv_finish(void) {
 
+  if (rd.wall) wall_free(rd.wall);
   if (rd.fe) fe_symm_free(rd.fe);
   if (rd.phi_grad) field_grad_free(rd.phi_grad);
   if (rd.phi) field_free(rd.phi);
@@ -252,6 +266,26 @@ int refdrv_noise(int on, double kt, int reseed) {
   physics_kt_set(rd.phys, kt);
   return noise_present_set(rd.noise, NOISE_RHO, on);
 }
+/* Flat walls: what wall_rt_init does for "boundary_walls" / "boundary_speed_*"
+ * (src/wall_rt.c:40-120): wall_create + wall_commit (map, links, wall velocities). */
+int refdrv_wall(const int isboundary[3], const double ubot[3], const double utop[3]) {
+  wall_param_t p = {0};
+  for (int ia = 0; ia < 3; ia++) {
+    p.isboundary[ia] = isboundary[ia];
+    p.ubot[ia] = ubot[ia];
+    p.utop[ia] = utop[ia];
+  }
+  p.iswall = (p.isboundary[0] || p.isboundary[1] || p.isboundary[2]);
+  wall_create(rd.pe, rd.cs, rd.map, rd.lb, &rd.wall);
+  return wall_commit(rd.wall, &p);
+}
+int refdrv_wall_nlink(void) { return rd.wall ? rd.wall->nlink : 0; }
+int refdrv_wall_bbl(void) {
+  wall_set_wall_distributions(rd.wall);
+  return wall_bbl(rd.wall);
+}
+int refdrv_wall_momentum(double f[3]) { return wall_momentum(rd.wall, f); }
+
 /* "lb_ghost_modes off" (src/collision_rt.c:87-102) */
 int refdrv_ghost_modes(int on) {
   return on ? lb_collision_ghost_modes_on(rd.lb) : lb_collision_ghost_modes_off(rd.lb);
@@ -286,6 +320,10 @@ double refdrv_step(int nsteps) {
     hydro_u_zero(rd.hydro, zero);
     lb_collide(rd.lb, rd.hydro, rd.map, rd.noise, (fe_t *) rd.fe, NULL);
     lb_halo(rd.lb);
+    if (rd.wall) {                      /* src/ludwig.c:837-842 */
+      wall_set_wall_distributions(rd.wall);
+      wall_bbl(rd.wall);
+    }
     lb_propagation(rd.lb);
   }
 

@@ -2,7 +2,9 @@
 regression golden logs (tests/regression/d3q19-short/serial-dist-*.log, d2q9/serial-2khz-bm1.log
 the fluctuating-hydrodynamics case d2q9/serial-flct-t01.log and the binary-fluid spinodal
 cases d3q19-short/serial-spin-lb{1,3,4}.log (symmetric_lb, 27-point gradient, lb3/lb4 with
-fluctuations, lb1/lb4 with ghost modes off), Ludwig v0.20.1)
+fluctuations, lb1/lb4 with ghost modes off), and the wall cases d3q19-short/serial-rect-ct1
+(body-force driven duct flow between y and z walls) and serial-wall-st1 (closed box with
+fluctuations), Ludwig v0.20.1)
 into tests/golden/regression_logs.json, together with the input keys that define each
 case. Run in the build container (needs /root/reference)."""
 
@@ -15,7 +17,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CASES = ["d3q19-short/serial-dist-3du", "d3q19-short/serial-dist-1dp",
          "d3q19-short/serial-dist-2kh", "d3q19-short/serial-dist-2sw", "d2q9/serial-2khz-bm1",
          "d2q9/serial-flct-t01", "d3q19-short/serial-spin-lb1", "d3q19-short/serial-spin-lb3",
-         "d3q19-short/serial-spin-lb4"]
+         "d3q19-short/serial-spin-lb4", "d3q19-short/serial-rect-ct1",
+         "d3q19-short/serial-wall-st1"]
 NVEL = {"d3q19-short": 19, "d2q9": 9}
 
 
@@ -47,6 +50,12 @@ def main():
                 rec["fed"] = floats(l)                 # total/volume, fluid mean
             if l.startswith("[total   ]"):
                 rec["momentum"] = floats(l)
+            if l.startswith("[fluid   ]"):
+                rec["momentum_fluid"] = floats(l)
+            if l.startswith("[walls   ]"):
+                rec["momentum_walls"] = floats(l)
+            if l.startswith("[vol flux]"):
+                rec["vol_flux"] = floats(l)
             if l.startswith("[minimum ]"):
                 rec["umin"] = floats(l)
             if l.startswith("[maximum ]"):

@@ -11,6 +11,7 @@
  * Build and run: see tests/test_host_shim.py. Exit code 0 = pass.
  */
 
+#include <float.h>
 #include <math.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -222,6 +223,38 @@ static void test_loop(int ndist, int nsteps, int npt, double kt) {
     double sums[8];
     OK(stats_distribution_sums(lb, sums));
     CHECK(fabs(sums[0] - mass1) < 1.0e-9, "device mass sum");
+  }
+  {
+    /* stats_velocity_minmax as a device reduction against the host copy of u, and the
+     * binary file records of lb_io_write against lb->f (src/model.c:1498-1525) */
+    stats_vel_t sv;
+    io_aggregator_t aggr;
+    double hmin[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hmax[3] = {FLT_MIN, FLT_MIN, FLT_MIN};
+    int nbad = 0;
+    long ib = 0;
+    OK(stats_velocity_minmax(&sv, hydro, NULL));
+    aggr.szelement = (size_t) ndist*lb->nvel*sizeof(double);
+    aggr.szbuf = aggr.szelement*nl[0]*nl[1]*nl[2];
+    aggr.buf = (char *) malloc(aggr.szbuf);
+    OK(lb_io_aggr_pack(lb, &aggr));
+    for (int ic = 1; ic <= nl[0]; ic++) for (int jc = 1; jc <= nl[1]; jc++) for (int kc = 1; kc <= nl[2]; kc++) {
+      long index = cs_index(&cs, ic, jc, kc);
+      const double * rec = (const double *) (aggr.buf + ib*aggr.szelement);
+      for (int a = 0; a < 3; a++) {
+	double ua = hydro->u.data[3*index + a];
+	if (ua < hmin[a]) hmin[a] = ua;
+	if (ua > hmax[a]) hmax[a] = ua;
+      }
+      for (int n = 0; n < ndist; n++) for (int p = 0; p < lb->nvel; p++) {
+	nbad += (rec[n*lb->nvel + p] != lb->f[LB_ADDR(lb->nsite, ndist, lb->nvel, index, n, p)]);
+      }
+      ib++;
+    }
+    for (int a = 0; a < 3; a++) {
+      CHECK(sv.umin[a] == hmin[a] && sv.umax[a] == hmax[a], "stats_velocity_minmax on the device");
+    }
+    CHECK(nbad == 0, "lb_io_aggr_pack records");
+    free(aggr.buf);
   }
 
   free(f); free(fprime); free(rho); free(u); free(force); free(ph); free(gr); free(dsq);

@@ -817,3 +817,79 @@ def test_noise_refused_where_the_reference_cannot():
     with pytest.raises(lb.B200LBError, match="noise_init"):
         lat.lb_collide()
     lat.close()
+
+
+# ---------------------------------------------------------------------------
+# statistics and file records straight from the device layout
+# ---------------------------------------------------------------------------
+
+@pytest.mark.parametrize("nvel,nlocal,ndist", [(19, (12, 10, 8), 1), (9, (16, 12, 1), 1),
+                                               (19, (5, 7, 33), 2), (27, (8, 6, 10), 1)])
+def test_field_stats_device_reductions(nvel, nlocal, ndist):
+    """stats_velocity_minmax / stats_field_info as device reductions: min and max are
+    exact, sums agree with the host sums over the downloaded field to round-off."""
+    import ludwig_b200 as lb
+    lat, orc = mk(nvel, nlocal, ndist)
+    m = orc.interior_mask()
+    f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal, ndist=ndist, ndim=orc.ndim)
+    kw = dict(eta_shear=0.1, eta_bulk=0.1)
+    if ndist == 2:
+        kw = dict(eta_shear=0.00625, eta_bulk=0.00625, mobility=3.75, a=-0.00625,
+                  b=0.00625, kappa=0.004)
+    lat.set_param(**kw)
+    lat.lb_memcpy_h2d(f0)
+    for hydro_write in (1, 0):
+        lat.set_option("hydro_write", hydro_write)
+        lat.step(3)
+        fields = [lb.FIELD_U, lb.FIELD_RHO] if ndist == 1 else [lb.FIELD_U, lb.FIELD_PHI,
+                                                                lb.FIELD_GRAD, lb.FIELD_DELSQ]
+        for field in fields:
+            q = lat.field_stats(field)
+            a = lat.field_d2h(field)[m]
+            a = a.reshape(len(a), -1)
+            for c in range(a.shape[1]):
+                assert q[c, 2] == a[:, c].min() and q[c, 3] == a[:, c].max()
+                assert abs(q[c, 0] - a[:, c].sum()) <= 1e-12*max(1.0, np.abs(a[:, c]).sum())
+                assert abs(q[c, 1] - (a[:, c]**2).sum()) <= 1e-12*max(1.0, (a[:, c]**2).sum())
+    lat.close()
+
+
+@pytest.mark.parametrize("nvel,nlocal,ndist", [(19, (12, 10, 8), 1), (9, (16, 12, 1), 1),
+                                               (19, (5, 7, 33), 2), (27, (8, 6, 10), 1)])
+def test_io_records_from_device(nvel, nlocal, ndist):
+    """lb_io_aggr_pack / _unpack (binary records): interior sites, kc fastest, [n][p] --
+    bit-identical to packing the downloaded host array as src/model.c:1498-1525 does,
+    also while a propagation is pending; unpack + halo restores the full lattice."""
+    import ludwig_b200 as lb
+    lat, orc = mk(nvel, nlocal, ndist)
+    m = orc.interior_mask()
+    rng = np.random.default_rng(11)
+    f0 = rng.standard_normal((orc.nsite, ndist, nvel))
+    if nvel == 9:
+        f3 = f0.reshape(orc.nall + (ndist, nvel))
+        f3[:, :, 0] = f3[:, :, 1]
+        f3[:, :, 2] = f3[:, :, 1]
+    lat.lb_memcpy_h2d(f0)
+    rec = lat.lb_io_aggr_pack()
+    assert rec.shape == (int(np.prod(nlocal)), ndist, nvel)
+    assert np.array_equal(rec, f0[m])
+    # restart: records in, halo swap, compare with the same done on the host array
+    lat2, _ = mk(nvel, nlocal, ndist)
+    lat2.lb_io_aggr_unpack(rec)
+    lat2.lb_halo_swap(lb.HALO_FULL)
+    fh = np.where(m[:, None, None], f0, 0.0)
+    orc.halo(fh, ndist*nvel)
+    assert np.array_equal(lat2.lb_memcpy_d2h(), fh)
+    # with a pending (lazy) propagation the records are those of the streamed lattice
+    f1 = lbinit.make_state(orc.cv(), orc.wv(), nlocal, ndist=ndist, ndim=orc.ndim)
+    kw = dict(eta_shear=0.1, eta_bulk=0.1)
+    if ndist == 2:
+        kw = dict(eta_shear=0.00625, eta_bulk=0.00625, mobility=3.75, a=-0.00625,
+                  b=0.00625, kappa=0.004)
+    lat.set_param(**kw)
+    lat.lb_memcpy_h2d(f1)
+    lat.step(2)
+    rec = lat.lb_io_aggr_pack()
+    assert np.array_equal(rec, lat.lb_memcpy_d2h()[m])
+    lat.close()
+    lat2.close()

@@ -314,3 +314,63 @@ def test_fluctuating_collision(nvel, nlocal, ndist, nrelax, ghost_off):
             assert relerr(f[m], ref.f()[m]) < 1e-12
     finally:
         orc.noise_attach(None, 0.0)
+
+
+@pytest.mark.parametrize("nvel,nlocal,walls,ubot,utop", [
+    (19, (6, 5, 4), (1, 1, 1), (0, 0, 0), (0, 0, 0)),
+    (19, (4, 7, 6), (0, 1, 1), (0, 0, 0), (0, 0, 0)),
+    (19, (5, 4, 6), (0, 0, 1), (-0.01, 0, 0), (0.02, 0, 0)),
+    (27, (4, 5, 4), (1, 0, 1), (0, 0, 0), (0, 0, 0)),
+    (9, (8, 7, 1), (0, 1, 0), (0.015, 0, 0), (-0.005, 0, 0)),
+    (9, (8, 7, 1), (1, 1, 0), (0, 0, 0), (0, 0, 0))])
+def test_wall_bounce_back(nvel, nlocal, walls, ubot, utop):
+    """wall_commit + wall_bbl (src/wall.c): link count, the populations written into
+    the wall layer, the momentum account, and the time loop with walls (collide, halo,
+    bbl, propagate) with a body force driving a flow."""
+    need_ref(nvel)
+    periodic = tuple(0 if w else 1 for w in walls)
+    orc = pyoracle.Oracle(nvel, nlocal)
+    f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal, ndim=orc.ndim)
+    fg = (2e-4, 0.0, 0.0) if not walls[0] else (0.0, 0.0, 0.0)
+    kw = dict(eta_shear=0.1666, eta_bulk=0.1)
+    prm = pyoracle.make_param(force=fg, **kw)
+    m = orc.interior_mask()
+    n = orc.nsite
+    with pyref.Ref(nvel, nlocal, periodic=periodic) as ref:
+        ref.physics(force=fg, **kw)
+        nlink = ref.wall(walls, ubot, utop)
+        w = orc.wall(walls, ubot, utop)
+        assert orc.wall_nlink(w) == nlink and nlink > 0
+        # one bounce-back on a post-collision state: the reversed populations of the wall
+        # layer are exactly what the reference writes there (lb->param->rho0, which
+        # scales the moving-wall term, is only set by a collision: src/collision.c:1200)
+        ref.f()[...] = f0
+        ref.collide()
+        ref.f()[...] = f0
+        ref.wall_bbl()
+        f = f0.copy()
+        orc.wall_bbl(prm, w, f)
+        assert np.array_equal(f, ref.f())
+        assert np.allclose(np.array(w.fnet[:]), ref.wall_momentum(), rtol=1e-12, atol=1e-15)
+        # time loop
+        ref.f()[...] = f0
+        ref.step(12)
+        f = f0.copy()
+        fp = np.zeros_like(f)
+        rho, u, frc = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
+        w = orc.wall(walls, ubot, utop)
+        orc.wall_attach(w)
+        try:
+            orc.step(prm, 12, f, fp, rho, u, frc)
+        finally:
+            orc.wall_attach(None)
+        assert relerr(f[m], ref.f()[m]) < 1e-12
+        assert np.max(np.abs(u[m] - ref.u()[m])) < 1e-14
+        # wall_momentum() above moved the account of the single bbl to the host total;
+        # the twelve steps add to it
+        fn = ref.wall_momentum()
+        w1 = orc.wall(walls, ubot, utop)
+        orc.wall_bbl(prm, w1, f0.copy())
+        assert np.allclose(np.array(w.fnet[:]) + np.array(w1.fnet[:]), fn, rtol=1e-10, atol=1e-14)
+        # mass of the fluid is conserved by the bounce-back
+        assert abs(f[m].sum() - f0[m].sum()) < 1e-10

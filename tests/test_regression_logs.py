@@ -79,8 +79,9 @@ def printed(fmt, x):
     return float(fmt % x)
 
 
-def check(rec, nt, sums, u_interior):
-    """sums = [sum rho, sum rho^2, min, max, gx, gy, gz]; u_interior [n,3]."""
+def check(rec, nt, sums, u_interior, gwall=None):
+    """sums = [sum rho, sum rho^2, min, max, gx, gy, gz]; u_interior [n,3]; gwall = the
+    walls' momentum account (wall_momentum) when there are walls."""
     vol = float(np.prod(nt))
     mean = sums[0] / vol
     var = abs(sums[1] / vol - mean * mean)
@@ -88,9 +89,21 @@ def check(rec, nt, sums, u_interior):
             printed("%14.11f", sums[2]), printed("%14.11f", sums[3])]
     for a, b in zip(mine, rec["rho"]):
         assert abs(a - b) <= 1e-12, ("rho", mine, rec["rho"])
-    mom = [printed("%14.7e", g) for g in sums[4:7]]
-    for a, b in zip(mom, rec["momentum"]):
-        assert abs(a - b) <= 1e-12, ("momentum", mom, rec["momentum"])
+    if gwall is None:
+        mom = [printed("%14.7e", g) for g in sums[4:7]]
+        for a, b in zip(mom, rec["momentum"]):
+            assert abs(a - b) <= 1e-12, ("momentum", mom, rec["momentum"])
+    else:
+        # [total] = [fluid] + [walls] (src/ludwig.c:1066-1090)
+        for key, val in (("momentum_fluid", sums[4:7]), ("momentum_walls", gwall),
+                         ("momentum", [sums[4 + a] + gwall[a] for a in range(3)])):
+            mom = [printed("%14.7e", g) for g in val]
+            for a, b in zip(mom, rec[key]):
+                assert abs(a - b) <= 1e-12, (key, mom, rec[key])
+    if "vol_flux" in rec:          # stats_vel_print_vol_flux: sum of u over fluid sites
+        flux = [printed("%14.7e", u_interior[:, a].sum()) for a in range(3)]
+        for a, b in zip(flux, rec["vol_flux"]):
+            assert abs(a - b) <= 1e-12, ("vol flux", flux, rec["vol_flux"])
     # stats_velocity_minmax starts from FLT_MAX / FLT_MIN (src/stats_velocity.c:75-76)
     umin = [printed("%14.7e", min(FLT_MAX, u_interior[:, a].min())) for a in range(3)]
     umax = [printed("%14.7e", max(FLT_MIN, u_interior[:, a].max())) for a in range(3)]
@@ -128,6 +141,16 @@ def ghost_off(rec):
 
 def gradient_points(rec):
     return 27 if rec["input"].get("fd_gradient_calculation") == "3d_27pt_fluid" else 7
+
+
+def walls(rec):
+    inp = rec["input"]
+    w = tuple(int(x) for x in inp.get("boundary_walls", "0_0_0").split("_"))
+    return w if any(w) else None
+
+
+def body_force(inp):
+    return tuple(float(x) for x in inp.get("force", "0_0_0").split("_"))
 
 
 def binary_params(inp):
@@ -172,7 +195,13 @@ def test_oracle_reproduces_reference_log(case):
     ndist = f.shape[1]
     orc = pyoracle.Oracle(nvel, nt, ndist=ndist)
     kw = binary_params(rec["input"]) if ndist == 2 else {}
-    prm = pyoracle.make_param(eta_shear=eta, eta_bulk=zeta, ghost_off=int(ghost_off(rec)), **kw)
+    prm = pyoracle.make_param(eta_shear=eta, eta_bulk=zeta, ghost_off=int(ghost_off(rec)),
+                              force=body_force(rec["input"]), **kw)
+    wall = None
+    if walls(rec):
+        ub = (float(rec["input"].get("boundary_speed_bottom", 0.0)), 0.0, 0.0)
+        ut = (float(rec["input"].get("boundary_speed_top", 0.0)), 0.0, 0.0)
+        wall = orc.wall(walls(rec), ub, ut)
     n = orc.nsite
     fp = np.zeros_like(f)
     rho, u, frc = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
@@ -182,13 +211,15 @@ def test_oracle_reproduces_reference_log(case):
         # and the order-parameter initialisation
         orc.noise_attach(orc.noise_init(0), float(rec["input"]["temperature"]))
     orc.gradient_select(gradient_points(rec))
+    orc.wall_attach(wall)
     try:
         orc.step(prm, int(rec["input"]["N_cycles"]), f, fp, rho, u, frc, phi, grad, delsq)
     finally:
         orc.noise_attach(None, 0.0)
         orc.gradient_select(7)
+        orc.wall_attach(None)
     m = orc.interior_mask()
-    check(rec, nt, orc.stats(f), u[m])
+    check(rec, nt, orc.stats(f), u[m], gwall=None if wall is None else list(wall.fnet))
     if ndist == 2:
         check_binary(rec, nt, f[m], grad[m])
     if noisy(rec):
