@@ -57,6 +57,8 @@ def parse():
                     help="binary fluid: order-parameter gradient stencil")
     ap.add_argument("--kt", type=float, default=0.0,
                     help="> 0: isothermal fluctuations at this temperature (not the headline workload)")
+    ap.add_argument("--walls", type=int, nargs=3, default=None,
+                    help="flat no-slip walls in these directions, e.g. 0 1 1 (not the headline workload)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--ref-size", type=int, nargs=3, default=None)
@@ -279,7 +281,8 @@ def main():
     if ndim == 2 and grid[2] != 1:
         grid = (grid[0], grid[1] * grid[2], 1)
     ntotal = tuple(local[a] * grid[a] for a in range(3))
-    dec = lb.Decomposition(ntotal, rank, world, grid=grid)
+    periodic = tuple(0 if w else 1 for w in args.walls) if args.walls else (1, 1, 1)
+    dec = lb.Decomposition(ntotal, rank, world, grid=grid, periodic=periodic)
 
     lat = lb.Lattice(nvel, local, ndist=ndist, decomp=dec, device=local_rank,
                      zalign=args.zalign)
@@ -300,6 +303,8 @@ def main():
         lat.field_grad_set(args.gradient)
     else:
         lat.set_param(eta_shear=0.1, eta_bulk=0.1, kt=args.kt)
+    if args.walls:
+        lat.wall_commit(args.walls)
     if args.kt > 0.0:
         lat.noise_init(0)
         lat.noise_present_set(1)
@@ -451,6 +456,7 @@ def main():
                 "fused": bool(args.fused), "vec": args.vec, "halo": args.halo,
                 "hydro_write": bool(args.hydro_write), "overlap": bool(args.overlap), "direct_halo": bool(args.direct), "p2p_halo": bool(args.p2p and (world > 1 or args.loopback)), "loopback": bool(args.loopback),
                 "gradient_points": args.gradient if ndist == 2 else None,
+                "walls": args.walls,
                 "isothermal_fluctuations_kt": args.kt if args.kt > 0.0 else None,
                 "l2": "lattice %.2f GB per GPU >> 126 MB L2 (no flush needed)" % (2 * lattice_bytes / 1e9),
             },

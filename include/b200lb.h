@@ -143,6 +143,21 @@ int  b200lb_phi_halo(b200lb_t * h);                          /* field_halo(phi) 
 int  b200lb_grad7(b200lb_t * h);                             /* grad_3d_7pt_fluid_d2 src/gradient_3d_7pt_fluid.c:75 */
 int  b200lb_grad27(b200lb_t * h);                            /* grad_3d_27pt_fluid_d2 src/gradient_3d_27pt_fluid.c:75 */
 
+/* Flat no-slip walls ("boundary_walls", "boundary_speed_bottom/_top"; src/wall.c,
+ * src/wall_rt.c:40-120). A wall in a non-periodic direction occupies the halo layer at
+ * global coordinate 0 and ntotal + 1 (wall_init_map). wall_bbl belongs between lb_halo
+ * and lb_propagation (src/ludwig.c:837-842): the propagation that follows -- on its own
+ * or fused into the next collision -- bounces the populations that would cross into a
+ * wall back to the site they left (bounce-back on links, wall_bbl_kernel
+ * src/wall.c:997-1107, moving-wall term for a single pair of walls included), and the
+ * momentum handed to the walls is tallied (wall->fnet). Single fluid only; slip walls,
+ * porous media and colloids are not on this path. */
+int  b200lb_wall_commit(b200lb_t * h, const int isboundary[3], const double ubot[3],
+                        const double utop[3]);                         /* wall_create + wall_commit src/wall.c:59,168 */
+int  b200lb_wall_bbl(b200lb_t * h);                                    /* wall_bbl src/wall.c:960 */
+int  b200lb_wall_momentum(b200lb_t * h, double f[3]);                  /* wall_momentum src/wall.c:1299 */
+int  b200lb_wall_momentum_add(b200lb_t * h, const double f[3]);        /* wall_momentum_add src/wall.c:1279 */
+
 /* Isothermal fluctuations ("isothermal_fluctuations on", src/collision_rt.c:55):
  * every site owns a KISS99 generator seeded from its global position, so results do
  * not depend on the decomposition (noise_create + noise_init, src/noise.c:56,136;
@@ -160,7 +175,8 @@ int  b200lb_noise_state_upload(b200lb_t * h, const unsigned int * state, int hos
 int  b200lb_noise_state_download(b200lb_t * h, unsigned int * state, int host_layout);       /* noise_memcpy D2H */
 
 /* nsteps iterations of the src/ludwig.c:530-862 loop restricted to the hot
- * path: f_zero; [phi_from_g; phi_halo; grad7 | grad27]; u_zero; collide; halo; propagate */
+ * path: f_zero; [phi_from_g; phi_halo; grad7 | grad27]; u_zero; collide; halo;
+ * [wall_bbl]; propagate */
 int  b200lb_step(b200lb_t * h, int nsteps);
 
 /* Conserved-quantity diagnostics over interior sites of this rank

@@ -103,6 +103,14 @@ struct b200lb_s {
   double * lat[2];           // two lattices; lat[cur] is "f", the other "fprime"
   int cur;
   double * rho, * u, * force, * phi, * grad, * delsq;
+  // flat walls (wall_t, src/wall.h)
+  int wall_is[3];            // physical: isboundary
+  double wall_ubot[3], wall_utop[3];
+  bool wall_on;              // wall_commit was called with at least one boundary
+  bool bbl_armed;            // wall_bbl was called: the next lb_propagation bounces at the walls
+  bool prop_wall;            // ... and that propagation is the pending / running one
+  double * fnet_dev;         // [3] momentum handed to the walls since the last wall_momentum
+  double fnet_host[3];       // running total on the host (wall_momentum_add and read-outs)
   double * noise;            // [2][nsd] per-site generator state (noise_init), or null
   bool noise_on;             // noise_present_set(NOISE_RHO)
   double nv_diag, nv_off, nv_bulk, nv_ghost[B200LB_MAXNOISE];
@@ -196,6 +204,30 @@ static int site_kparams(b200lb_s * h, KParams & P) {
   P.rtau_shear = h->rtau_shear; P.rtau_bulk = h->rtau_bulk;
   P.rtau2 = h->rtau2; P.A = h->prm.a; P.B = h->prm.b; P.kappa = h->prm.kappa;
   for (int k = 0; k < B200LB_MAXGHOST; k++) P.gkeep[k] = h->gkeep[k];
+  if (h->wall_on) {
+    // wall_init_uw (src/wall.c:864-893): wall velocities only for a single pair of walls
+    const int nwall = h->wall_is[0] + h->wall_is[1] + h->wall_is[2];
+    int iw = -1;
+    if (nwall == 1) { for (int a = 0; a < 3; a++) if (h->wall_is[a]) iw = a; }
+    for (int d = 0; d < 3; d++) {
+      const int a = h->ops->dax[d];
+      const bool is = h->wall_is[a] && h->L.h[d] == 1;
+      P.wall_lo[d] = is && h->desc.cartcoords[a] == 0;
+      P.wall_hi[d] = is && h->desc.cartcoords[a] == h->desc.cartsz[a] - 1;
+    }
+    const int Q = h->ops->nvel;
+    for (int q = 1; q < Q; q++) {
+      // incoming q = reversed outgoing link ij = Q - q; the link points into the bottom
+      // wall when c_ij[iw] = -1 (src/wall.c:886-887)
+      const int ij = Q - q;
+      const double * uw = nullptr;
+      if (iw >= 0 && h->ops->cv[ij][iw] == -1) uw = h->wall_ubot;
+      if (iw >= 0 && h->ops->cv[ij][iw] == +1) uw = h->wall_utop;
+      double cdotu = 0.0;
+      if (uw) cdotu = h->ops->cv[ij][0]*uw[0] + h->ops->cv[ij][1]*uw[1] + h->ops->cv[ij][2]*uw[2];
+      P.wall_corr[q] = -(2.0*3.0*h->ops->wv[ij]*h->prm.rho0*cdotu);
+    }
+  }
   P.noise = h->noise;
   P.nv_diag = h->nv_diag; P.nv_off = h->nv_off; P.nv_bulk = h->nv_bulk;
   for (int k = 0; k < B200LB_MAXNOISE; k++) P.nv_ghost[k] = h->nv_ghost[k];
@@ -430,7 +462,7 @@ extern "C" int b200lb_destroy(b200lb_t * h) {
     cudaEventDestroy(h->ev_x[i]);
   }
   cudaFree(h->rho); cudaFree(h->u); cudaFree(h->force);
-  cudaFree(h->phi); cudaFree(h->grad); cudaFree(h->delsq); cudaFree(h->noise);
+  cudaFree(h->phi); cudaFree(h->grad); cudaFree(h->delsq); cudaFree(h->noise); cudaFree(h->fnet_dev);
   cudaFree(h->partial); cudaFree(h->diag); cudaFree(h->stats_dev); cudaFreeHost(h->stats_host);
   cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
   cudaStreamDestroy(h->s_main);
@@ -582,6 +614,41 @@ static int split_boxes(const b200lb_s * h, int lo[7][3], int hi[7][3]) {
   return nb + 1;
 }
 
+// Sub-boxes when a bounce-back is folded into the pull: the slabs next to the walls this
+// rank holds (one site thick; sixteen along the contiguous axis to keep rows line-aligned)
+// run the wall variant of the kernel, the interior -- the LAST box -- the plain one.
+// iswall[b] says which. Lattices too thin to split are swept whole by the wall variant.
+static int wall_boxes(const b200lb_s * h, const KParams & P, int lo[7][3], int hi[7][3], bool iswall[7]) {
+  const Layout & L = h->L;
+  int ilo[3] = {0, 0, 0}, ihi[3] = {L.n[0], L.n[1], L.n[2]};
+  int nb = 0;
+  for (int d = 0; d < 3; d++) {
+    if (!P.wall_lo[d] && !P.wall_hi[d]) continue;
+    const int t = (d == 2) ? 16 : 1;
+    if (L.n[d] < 2*t + 1 || (d == 2 && (L.n[2] % 2))) {
+      for (int e = 0; e < 3; e++) { lo[0][e] = 0; hi[0][e] = L.n[e]; }
+      iswall[0] = true;
+      return 1;
+    }
+  }
+  for (int d = 0; d < 3; d++) {
+    const int t = (d == 2) ? 16 : 1;
+    for (int side = 0; side < 2; side++) {
+      if (!(side == 0 ? P.wall_lo[d] : P.wall_hi[d])) continue;
+      for (int e = 0; e < 3; e++) { lo[nb][e] = ilo[e]; hi[nb][e] = ihi[e]; }
+      if (side == 0) { lo[nb][d] = 0; hi[nb][d] = t; }
+      else { lo[nb][d] = L.n[d] - t; hi[nb][d] = L.n[d]; }
+      iswall[nb] = true;
+      nb++;
+    }
+    if (P.wall_lo[d]) ilo[d] = t;
+    if (P.wall_hi[d]) ihi[d] = L.n[d] - t;
+  }
+  for (int e = 0; e < 3; e++) { lo[nb][e] = ilo[e]; hi[nb][e] = ihi[e]; }
+  iswall[nb] = false;
+  return nb + 1;
+}
+
 static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
 		     double * dst) {
   if (join_comm(h)) return -1;
@@ -620,8 +687,12 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
     if (h->grad_state == 0) { a.P.grad = h->grad; a.P.delsq = h->delsq; }
   }
   int lo[7][3], hi[7][3];
+  bool iswall[7] = {false, false, false, false, false, false, false};
   const bool push = collide && h->p2p_ready && h->opt_p2p;
-  const int nbox = push ? 1 : split_boxes(h, lo, hi);
+  const bool walls = pull && h->prop_wall && h->wall_on;
+  if (walls && a.binary) return fail("walls with the binary fluid need the solid gradient stencils: not on this path");
+  const int nbox = walls ? wall_boxes(h, a.P, lo, hi, iswall) : (push ? 1 : split_boxes(h, lo, hi));
+  const int vec0 = a.vec;
   h->bnd_valid = false;
   h->pushed_valid = false;
   if (push) {
@@ -634,9 +705,11 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
   a.P.diag_base = 0;
   if (collide) h->diag_count = 0;
   for (int b = 0; b < nbox; b++) {
-    if (nbox > 1) {
+    a.wall = walls && iswall[b];
+    a.vec = a.wall ? 1 : vec0;
+    if (nbox > 1 || walls) {
       for (int e = 0; e < 3; e++) { a.P.lo[e] = lo[b][e]; a.P.hi[e] = hi[b][e]; }
-      if (b == nbox - 1) {
+      if (b == nbox - 1 && !walls) {
 	// everything a neighbour needs is written: the exchange may start now
 	CU(cudaEventRecord(h->ev_bnd, h->s_main));
 	h->bnd_valid = true;
@@ -658,6 +731,7 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
     h->push_wait_pending = true;
     h->pushed_valid = true;
   }
+  if (pull) h->prop_wall = false;  // the bounce-back belonged to this propagation
   h->halo_deferred = false;        // whatever was written has stale halos until the next lb_halo
   if (collide) {
     if (h->opt_hydro_write) { h->u_fill_pending = false; h->hydro_stale = false; }
@@ -705,6 +779,8 @@ extern "C" int b200lb_collide(b200lb_t * h) {
 extern "C" int b200lb_propagate(b200lb_t * h) {
   if (!h) return fail("null handle");
   if (h->prop_pending) { if (materialise(h)) return -1; }
+  h->prop_wall = h->bbl_armed;      // wall_bbl ran since the collision: this streaming bounces
+  h->bbl_armed = false;
   if (h->opt_fused) {
     // Lazy: the streaming is folded into the next collision (or done on demand
     // by the first call that observes the lattice).
@@ -714,6 +790,101 @@ extern "C" int b200lb_propagate(b200lb_t * h) {
   if (ensure_hydro(h)) return -1;
   if (run_sweep(h, true, false, h->lat[h->cur], h->lat[1 - h->cur])) return -1;
   h->cur = 1 - h->cur;
+  return 0;
+}
+
+// ---------------------------------------------------------------------------
+// flat walls: wall_create + wall_commit, wall_bbl, wall_momentum (src/wall.c)
+// ---------------------------------------------------------------------------
+
+extern "C" int b200lb_wall_commit(b200lb_t * h, const int isboundary[3], const double ubot[3],
+				  const double utop[3]) {
+  if (!h || !isboundary) return fail("null argument");
+  if (h->desc.ndist != 1) return fail("walls with the binary fluid need the solid gradient stencils: not on this path");
+  bool any = false;
+  for (int a = 0; a < 3; a++) {
+    if (!isboundary[a]) continue;
+    any = true;
+    if (h->desc.periodic[a]) return fail("boundary_walls: direction %d is periodic", a);
+    if (a >= h->desc.ndim) return fail("boundary_walls: direction %d of a %d-d lattice", a, h->desc.ndim);
+  }
+  if (h->prop_pending) { if (materialise(h)) return -1; }
+  for (int a = 0; a < 3; a++) {
+    h->wall_is[a] = isboundary[a] ? 1 : 0;
+    h->wall_ubot[a] = ubot ? ubot[a] : 0.0;
+    h->wall_utop[a] = utop ? utop[a] : 0.0;
+    h->fnet_host[a] = 0.0;
+  }
+  // src/wall_rt.c:56-60: a wall that moves along x cannot be an x wall
+  if (isboundary[0] && (h->wall_ubot[0] != 0.0 || h->wall_utop[0] != 0.0))
+    return fail("cannot have non-zero u_x wall velocity if the wall is in x");
+  h->wall_on = any;
+  h->bbl_armed = false;
+  h->prop_wall = false;
+  if (!h->fnet_dev) CU(cudaMalloc(&h->fnet_dev, 3*sizeof(double)));
+  CU(cudaMemsetAsync(h->fnet_dev, 0, 3*sizeof(double), h->s_main));
+  return 0;
+}
+
+// wall_bbl (src/wall.c:960-991), called between lb_halo and lb_propagation
+// (src/ludwig.c:842). The wall's share of the momentum is tallied now, from the
+// post-collision populations of the sites on the wall faces; the reversed populations
+// themselves are not written into the wall layer: the propagation that follows (fused
+// into the next collision, or on its own) takes them from the site they left.
+extern "C" int b200lb_wall_bbl(b200lb_t * h) {
+  if (!h) return fail("null handle");
+  if (!h->wall_on) return 0;                       // wall->nlink == 0: nothing to do
+  if (h->prop_pending) return fail("wall_bbl: called after lb_propagation (it belongs between lb_halo and lb_propagation)");
+  if (join_comm(h)) return -1;
+  KParams P;
+  site_kparams(h, P);
+  WallTab W;
+  memset(&W, 0, sizeof(W));
+  W.L = h->L;
+  W.nvel = h->ops->nvel;
+  for (int d = 0; d < 3; d++) { W.wall_lo[d] = P.wall_lo[d]; W.wall_hi[d] = P.wall_hi[d]; }
+  for (int p = 0; p < W.nvel; p++) {
+    for (int d = 0; d < 3; d++) W.dcv[p][d] = (signed char) h->ops->cv[p][h->ops->dax[d]];
+    for (int a = 0; a < 3; a++) W.pcv[p][a] = (signed char) h->ops->cv[p][a];
+    W.wv[p] = h->ops->wv[p];
+    // x_p of the outgoing link p is minus the correction of the incoming Q - p
+    W.xout[p] = (p > 0) ? -P.wall_corr[W.nvel - p] : 0.0;
+  }
+  for (int d = 0; d < 3; d++) {
+    for (int side = 0; side < 2; side++) {
+      if (!(side == 0 ? W.wall_lo[d] : W.wall_hi[d])) continue;
+      const int da = (d == 0) ? 1 : 0, db = (d == 2) ? 1 : 2;
+      W.face_axis = d; W.face_hi = side;
+      dim3 block(128, 1, 1);
+      dim3 grid((h->L.n[db] + 127)/128, h->L.n[da], 1);
+      wall_fnet_kernel<<<grid, block, 0, h->s_main>>>(W, h->lat[h->cur], h->fnet_dev);
+      CU(cudaGetLastError());
+      h->launches++;
+    }
+  }
+  h->bbl_armed = true;
+  return 0;
+}
+
+// wall_momentum (src/wall.c:1299-1340): this rank's share; the device tally is moved
+// to the host total and zeroed, as there. wall_momentum_add: b200lb_wall_momentum_add.
+extern "C" int b200lb_wall_momentum(b200lb_t * h, double f[3]) {
+  if (!h || !f) return fail("null argument");
+  if (h->fnet_dev) {
+    double tmp[3];
+    if (join_comm(h)) return -1;
+    CU(cudaMemcpyAsync(tmp, h->fnet_dev, 3*sizeof(double), cudaMemcpyDeviceToHost, h->s_main));
+    CU(cudaMemsetAsync(h->fnet_dev, 0, 3*sizeof(double), h->s_main));
+    CU(cudaStreamSynchronize(h->s_main));
+    for (int a = 0; a < 3; a++) h->fnet_host[a] += tmp[a];
+  }
+  for (int a = 0; a < 3; a++) f[a] = h->fnet_host[a];
+  return 0;
+}
+
+extern "C" int b200lb_wall_momentum_add(b200lb_t * h, const double f[3]) {
+  if (!h || !f) return fail("null argument");
+  for (int a = 0; a < 3; a++) h->fnet_host[a] += f[a];
   return 0;
 }
 
@@ -1183,6 +1354,7 @@ extern "C" int b200lb_step(b200lb_t * h, int nsteps) {
     if (b200lb_collide(h)) return -1;
     if (h->prop_pending) return fail("internal: propagation pending after collide");
     if (lattice_halo(h, h->opt_halo)) return -1;
+    if (h->wall_on) { if (b200lb_wall_bbl(h)) return -1; }      // src/ludwig.c:837-842
     if (b200lb_propagate(h)) return -1;
   }
   return 0;
@@ -1320,6 +1492,8 @@ extern "C" int b200lb_f_upload(b200lb_t * h, const double * f, int layout) {
   if (!h || !f) return fail("null argument");
   if (ensure_hydro(h)) return -1;   // hydro of the state being replaced stays available
   h->prop_pending = false;          // the host copy replaces whatever was in flight
+  h->bbl_armed = false;
+  h->prop_wall = false;
   h->halo_deferred = false;
   if (transfer(h, h->lat[h->cur], h->nplane, const_cast<double *>(f), layout, true)) return -1;
   if (h->p2p_ready && h->opt_p2p) {
@@ -1582,6 +1756,8 @@ extern "C" int b200lb_io_unpack(b200lb_t * h, const double * buf) {
   if (!h || !buf) return fail("null argument");
   if (ensure_hydro(h)) return -1;
   h->prop_pending = false;
+  h->bbl_armed = false;
+  h->prop_wall = false;
   h->halo_deferred = false;
   if (io_transfer(h, const_cast<double *>(buf), true)) return -1;
   if (h->p2p_ready && h->opt_p2p) {

@@ -305,6 +305,74 @@ __global__ void fill_kernel(double * __restrict__ data, i64 n, i64 plane, int nf
   if (nf > 2) data[2*plane + i] = v2;
 }
 
+// ---------------------------------------------------------------------------
+// Momentum handed to the walls by one bounce-back (the fnet tally of
+// wall_bbl_kernel, src/wall.c:1073-1081,1096-1106): for every link (fluid site i on
+// a wall face, velocity p pointing into a wall layer)
+//   fnet += (2 f_p(i) - x_p - 2 w_p) c_p,   x_p = 2 rcs2 w_p rho0 (c_p . u_wall)
+// from the post-collision populations. One launch per wall face; a site on several
+// faces (edges, corners) is handled by the first face in the order 0lo 0hi 1lo 1hi 2lo 2hi.
+// ---------------------------------------------------------------------------
+
+struct WallTab {
+  Layout L;
+  int nvel;
+  int wall_lo[3], wall_hi[3];     // device axes
+  signed char dcv[27][3];         // device-axis components of c_p
+  signed char pcv[27][3];         // physical components of c_p
+  double wv[27];
+  double xout[27];                // x_p for the outgoing link p
+  int face_axis, face_hi;         // the face this launch covers
+};
+
+__global__ void __launch_bounds__(128)
+wall_fnet_kernel(const WallTab W, const double * __restrict__ f, double * __restrict__ fnet) {
+  const Layout & L = W.L;
+  const int d = W.face_axis;
+  const int da = (d == 0) ? 1 : 0, db = (d == 2) ? 1 : 2;      // the two in-face axes, db fastest
+  const int ib = blockIdx.x*blockDim.x + threadIdx.x;
+  const int ia = blockIdx.y;
+  double acc[3] = {0.0, 0.0, 0.0};
+  if (ib < L.n[db] && ia < L.n[da]) {
+    int ic[3];
+    ic[d] = W.face_hi ? L.n[d] - 1 : 0;
+    ic[da] = ia; ic[db] = ib;
+    bool lo[3], hi[3];
+    bool earlier = false;
+    #pragma unroll
+    for (int e = 0; e < 3; e++) {
+      lo[e] = W.wall_lo[e] && ic[e] == 0;
+      hi[e] = W.wall_hi[e] && ic[e] == L.n[e] - 1;
+      if (e < d && (lo[e] || hi[e])) earlier = true;
+    }
+    if (W.face_hi && lo[d]) earlier = true;                  // n = 1: both faces are this site
+    if (!earlier) {
+      const i64 site = (i64)(ic[0] + L.h[0])*L.s0 + (i64)(ic[1] + L.h[1])*L.s1 + L.z0 + L.h[2] + ic[2];
+      for (int p = 1; p < W.nvel; p++) {
+	bool link = false;
+	#pragma unroll
+	for (int e = 0; e < 3; e++) {
+	  if (W.dcv[p][e] == -1 && lo[e]) link = true;
+	  if (W.dcv[p][e] ==  1 && hi[e]) link = true;
+	}
+	if (link) {
+	  const double fp = __ldg(f + (i64) p*L.nsd + site);
+	  const double force = 2.0*fp - W.xout[p];
+	  #pragma unroll
+	  for (int a = 0; a < 3; a++) acc[a] += (force - 2.0*W.wv[p])*W.pcv[p][a];
+	}
+      }
+    }
+  }
+  #pragma unroll
+  for (int a = 0; a < 3; a++) {
+    double v = acc[a];
+    #pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0 && v != 0.0) atomicAdd(fnet + a, v);
+  }
+}
+
 // sum, sum of squares, min, max of one field component over interior sites
 __global__ void __launch_bounds__(256)
 field_stats_kernel(const Layout L, const double * __restrict__ data, double * __restrict__ partial) {

@@ -49,6 +49,11 @@ struct KParams {
   double fg[3];           // uniform part of the force: force_global + constant field value
   double rtau2, A, B, kappa;
   double gkeep[B200LB_MAXGHOST];   // 1 - rtau_k for each ghost mode
+  // flat no-slip walls (src/wall.c): the wall occupies the halo layer of a non-periodic
+  // direction; populations a pull would fetch from there are this site's own reversed
+  // post-collision populations (+ the moving-wall term): wall_bbl folded into the pull
+  int wall_lo[3], wall_hi[3];   // per device axis: this rank holds the low / high wall
+  double wall_corr[27];         // per incoming population q: -2 rcs2 w rho0 (c_{Q-q} . u_wall)
   // isothermal fluctuations (src/noise.c, src/collision.c:476-515,1663-1745)
   double * noise;         // [2][nsd]: KISS99 words (s0,s1) and (s2,s3) of every site as 64-bit pairs
   double nv_diag, nv_off; // stress variance: var_eta sqrt(2) on the diagonal, var_eta off it

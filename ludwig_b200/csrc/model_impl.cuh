@@ -13,8 +13,15 @@ static __constant__ GhostTab c_ghost;
 
 typedef B200LB_MODEL MODEL;
 
-template <int VEC, bool PULL, bool COLLIDE, bool BINARY, int GM>
+template <int VEC, bool PULL, bool COLLIDE, bool BINARY, int GM, bool WALL = false>
 static cudaError_t launch_one(SweepArgs & a) {
+  // walls are folded into the pull of the single-fluid kernels only
+  if constexpr (!WALL && PULL && !BINARY) {
+    if (a.wall) return launch_one<VEC, PULL, COLLIDE, BINARY, GM, true>(a);
+  }
+  else if constexpr (!WALL) {
+    if (a.wall) return cudaErrorInvalidValue;
+  }
   constexpr bool GHOST = (GM != 0);
   const KParams & P = a.P;
   const int n2 = P.hi[2] - P.lo[2], n1 = P.hi[1] - P.lo[1], n0 = P.hi[0] - P.lo[0];
@@ -30,11 +37,11 @@ static cudaError_t launch_one(SweepArgs & a) {
   dim3 grid((nt2 + bx - 1)/bx, (n1 + by - 1)/by, n0);
   a.nblocks = (long long) grid.x*grid.y*grid.z;
   if (COLLIDE && a.diag) {
-    lb_sweep_kernel<MODEL, VEC, PULL, COLLIDE, BINARY, GM, COLLIDE>
+    lb_sweep_kernel<MODEL, VEC, PULL, COLLIDE, BINARY, GM, COLLIDE, WALL>
       <<<grid, block, 0, a.stream>>>(P);
   }
   else {
-    lb_sweep_kernel<MODEL, VEC, PULL, COLLIDE, BINARY, GM, false>
+    lb_sweep_kernel<MODEL, VEC, PULL, COLLIDE, BINARY, GM, false, WALL>
       <<<grid, block, 0, a.stream>>>(P);
   }
   return cudaGetLastError();

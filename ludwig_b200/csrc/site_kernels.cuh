@@ -324,7 +324,7 @@ fluctuations(unsigned int (&w)[4], const KParams & P,
 // the aligned pair), all others and every store are 128-bit.
 // ---------------------------------------------------------------------------
 
-template <class M, int VEC, bool PULL, bool COLLIDE, bool BINARY, int GM, bool DIAG>
+template <class M, int VEC, bool PULL, bool COLLIDE, bool BINARY, int GM, bool DIAG, bool WALL = false>
 __global__ void __launch_bounds__(256)
 lb_sweep_kernel(const KParams P) {
 
@@ -377,20 +377,46 @@ lb_sweep_kernel(const KParams P) {
 
   double f[NDIST][VEC][Q];
 
+  // Walls: is this site next to a wall layer, per device axis and side? (axes 0 and 1
+  // are uniform over a row of threads; the contiguous axis differs per site)
+  bool w0lo = false, w0hi = false, w1lo = false, w1hi = false;
+  bool w2lo[VEC], w2hi[VEC];
+  #pragma unroll
+  for (int v = 0; v < VEC; v++) { w2lo[v] = false; w2hi[v] = false; }
+  if (WALL && PULL) {
+    w0lo = P.wall_lo[0] && (i0 == 0);  w0hi = P.wall_hi[0] && (i0 == L.n[0] - 1);
+    w1lo = P.wall_lo[1] && (i1 == 0);  w1hi = P.wall_hi[1] && (i1 == L.n[1] - 1);
+    #pragma unroll
+    for (int v = 0; v < VEC; v++) {
+      w2lo[v] = P.wall_lo[2] && (i2 + v == 0);
+      w2hi[v] = P.wall_hi[2] && (i2 + v == L.n[2] - 1);
+    }
+  }
+
   #pragma unroll
   for (int n = 0; n < NDIST; n++) {
     #pragma unroll
     for (int p = 0; p < Q; p++) {
       const double * src = P.src + (i64)(n*Q + p)*L.nsd + site;
       int c2 = 0;
+      // bounce-back on links (wall_bbl_kernel, src/wall.c:997-1107, in pull form): a
+      // population that would come out of a wall layer is the one that left this very
+      // site in the opposite direction, still sitting here in the source lattice
+      bool bounce01 = false;
+      const double * rev = P.src + (i64)(n*Q + (Q - p) % Q)*L.nsd + site;
       if (PULL) {
 	if (dcv<M>(p, 0) ==  1) src += om[0];
 	if (dcv<M>(p, 0) == -1) src += op[0];
 	if (dcv<M>(p, 1) ==  1) src += om[1];
 	if (dcv<M>(p, 1) == -1) src += op[1];
 	c2 = dcv<M>(p, 2);
+	if (WALL && p > 0) {
+	  bounce01 = (dcv<M>(p, 0) == 1 && w0lo) || (dcv<M>(p, 0) == -1 && w0hi)
+	          || (dcv<M>(p, 1) == 1 && w1lo) || (dcv<M>(p, 1) == -1 && w1hi);
+	}
       }
       if (c2 == 0) {
+	if (WALL && bounce01) src = rev;
 	if (VEC == 2) {
 	  const double2 v = ld2<NC>(src);
 	  f[n][0][p] = v.x; f[n][VEC - 1][p] = v.y;
@@ -398,12 +424,20 @@ lb_sweep_kernel(const KParams P) {
 	else {
 	  f[n][0][p] = ld1<NC>(src);
 	}
+	if (WALL && bounce01) {
+	  #pragma unroll
+	  for (int v = 0; v < VEC; v++) f[n][v][p] += P.wall_corr[p];
+	}
       }
       else {
 	// moving along the contiguous axis: the pair straddles the aligned one
 	#pragma unroll
 	for (int v = 0; v < VEC; v++) {
-	  f[n][v][p] = ld1<NC>(src + v + (c2 == 1 ? zm[v] : zp[v]));
+	  const bool bounce = WALL && (bounce01 || (c2 == 1 && w2lo[v]) || (c2 == -1 && w2hi[v]));
+	  const double * a = bounce ? rev + v : src + v + (c2 == 1 ? zm[v] : zp[v]);
+	  double val = ld1<NC>(a);
+	  if (bounce) val += P.wall_corr[p];
+	  f[n][v][p] = val;
 	}
       }
     }

@@ -118,6 +118,47 @@ int lb_collide(lb_t * lb, hydro_t * hydro, map_t * map, noise_t * noise, fe_t * 
   return 0;
 }
 
+/* wall_t: links, map and the momentum tally live in the library */
+
+int wall_create(lb_t * lb, wall_t ** pwall) {
+  wall_t * wall = (wall_t *) calloc(1, sizeof(wall_t));
+  if (wall == NULL) return -1;
+  wall->lb = lb;
+  *pwall = wall;
+  return 0;
+}
+
+int wall_free(wall_t * wall) { free(wall); return 0; }
+
+int wall_commit(wall_t * wall, wall_param_t * param) {
+  wall->param = *param;
+  wall->param.iswall = (param->isboundary[0] || param->isboundary[1] || param->isboundary[2]);
+  TRY(b200lb_wall_commit(wall->lb->target, param->isboundary, param->ubot, param->utop));
+  return 0;
+}
+
+int wall_present(wall_t * wall) { return wall != NULL && wall->param.iswall; }
+
+/* The reference seeds the wall layer for colloid-wall exchange here; wall_bbl then
+ * overwrites every one of those populations (same site, same velocity). Nothing to do. */
+int wall_set_wall_distributions(wall_t * wall) { (void) wall; return 0; }
+
+int wall_bbl(wall_t * wall) {
+  if (!wall_present(wall)) return 0;
+  TRY(b200lb_wall_bbl(wall->lb->target));
+  return 0;
+}
+
+int wall_momentum(wall_t * wall, double f[3]) {
+  TRY(b200lb_wall_momentum(wall->lb->target, f));
+  return 0;
+}
+
+int wall_momentum_add(wall_t * wall, const double f[3]) {
+  TRY(b200lb_wall_momentum_add(wall->lb->target, f));
+  return 0;
+}
+
 int lb_collision_ghost_modes_on(lb_t * lb)  { lb->isghost = LB_GHOST_ON;  return 0; }
 int lb_collision_ghost_modes_off(lb_t * lb) { lb->isghost = LB_GHOST_OFF; return 0; }
 

@@ -120,6 +120,23 @@ int lb_halo(lb_t * lb);
 int lb_halo_swap(lb_t * lb, lb_halo_enum_t flag);
 int lb_propagation(lb_t * lb);
 
+/* wall_t (src/wall.h:47-76): flat no-slip walls */
+typedef struct wall_param_s {
+  int iswall;
+  int isboundary[3];
+  double ubot[3];
+  double utop[3];
+} wall_param_t;
+typedef struct wall_s { wall_param_t param; lb_t * lb; } wall_t;
+int wall_create(lb_t * lb, wall_t ** wall);                        /* src/wall.c:59 */
+int wall_free(wall_t * wall);
+int wall_commit(wall_t * wall, wall_param_t * param);              /* src/wall.c:168 */
+int wall_present(wall_t * wall);
+int wall_set_wall_distributions(wall_t * wall);                    /* src/wall.c:901 */
+int wall_bbl(wall_t * wall);                                       /* src/wall.c:960 */
+int wall_momentum(wall_t * wall, double f[3]);                     /* src/wall.c:1299 */
+int wall_momentum_add(wall_t * wall, const double f[3]);           /* src/wall.c:1279 */
+
 int noise_create(lb_t * lb, noise_t ** noise);                      /* src/noise.c:56 */
 int noise_free(noise_t * noise);
 int noise_init(noise_t * noise, int master_seed);                  /* src/noise.c:136 */

@@ -34,6 +34,7 @@ ABI_SYMBOLS = [
     "b200lb_propagate", "b200lb_phi_from_g", "b200lb_phi_halo", "b200lb_grad7", "b200lb_grad27",
     "b200lb_noise_init", "b200lb_noise_present_set", "b200lb_noise_state_upload",
     "b200lb_noise_state_download",
+    "b200lb_wall_commit", "b200lb_wall_bbl", "b200lb_wall_momentum", "b200lb_wall_momentum_add",
     "b200lb_field_stats", "b200lb_io_record_doubles", "b200lb_io_pack", "b200lb_io_unpack",
     "b200lb_step", "b200lb_stats", "b200lb_step_diag", "b200lb_sync", "b200lb_nccl_unique_id",
     "b200lb_comm_init", "b200lb_p2p_export", "b200lb_p2p_import", "b200lb_timer_start", "b200lb_timer_stop",
@@ -109,6 +110,10 @@ def load():
                  "b200lb_hydro_correct_momentum", "b200lb_timer_start", "b200lb_nsite", "b200lb_launch_count"):
         getattr(L, name).argtypes = [vp]
     L.b200lb_halo_swap.argtypes = [vp, ctypes.c_int]
+    L.b200lb_wall_commit.argtypes = [vp, vp, vp, vp]
+    L.b200lb_wall_bbl.argtypes = [vp]
+    L.b200lb_wall_momentum.argtypes = [vp, vp]
+    L.b200lb_wall_momentum_add.argtypes = [vp, vp]
     L.b200lb_field_stats.argtypes = [vp, ctypes.c_int, vp]
     L.b200lb_io_record_doubles.argtypes = [vp]
     L.b200lb_io_record_doubles.restype = ctypes.c_long
@@ -168,7 +173,8 @@ class Lattice:
     """One rank's lattice on one B200: the lb_t + hydro_t (+ phi, grad) of the
     reference, device-resident in the library's private layout."""
 
-    def __init__(self, nvel, nlocal, ndist=1, decomp=None, device=-1, zalign=0):
+    def __init__(self, nvel, nlocal, ndist=1, decomp=None, device=-1, zalign=0,
+                 periodic=(1, 1, 1)):
         self.L = load()
         self.nvel, self.ndist = nvel, ndist
         self.ndim = 2 if nvel == 9 else 3
@@ -179,9 +185,9 @@ class Lattice:
         if decomp is None:
             d.cartsz[:] = (1, 1, 1)
             d.cartcoords[:] = (0, 0, 0)
-            d.periodic[:] = (1, 1, 1)
-            d.nbr_lo[:] = (0, 0, 0)
-            d.nbr_hi[:] = (0, 0, 0)
+            d.periodic[:] = tuple(int(bool(x)) for x in periodic)
+            d.nbr_lo[:] = tuple(0 if x else -1 for x in periodic)
+            d.nbr_hi[:] = tuple(0 if x else -1 for x in periodic)
             d.rank, d.nranks = 0, 1
         else:
             d.cartsz[:] = decomp.cartsz
@@ -301,6 +307,20 @@ class Lattice:
             self._ck(self.L.b200lb_grad27(self.h))
         else:
             self._ck(self.L.b200lb_grad7(self.h))
+
+    # -- flat walls (wall_t, src/wall.h) ---------------------------------------------
+    def wall_commit(self, isboundary, ubot=(0.0, 0.0, 0.0), utop=(0.0, 0.0, 0.0)):
+        self._ck(self.L.b200lb_wall_commit(self.h, (ctypes.c_int * 3)(*isboundary),
+                                           (ctypes.c_double * 3)(*ubot),
+                                           (ctypes.c_double * 3)(*utop)))
+
+    def wall_bbl(self):
+        self._ck(self.L.b200lb_wall_bbl(self.h))
+
+    def wall_momentum(self):
+        out = (ctypes.c_double * 3)()
+        self._ck(self.L.b200lb_wall_momentum(self.h, out))
+        return np.array(out[:])
 
     # -- statistics and file records without the full-field D2H ---------------------
     def field_stats(self, field):

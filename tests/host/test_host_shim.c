@@ -266,6 +266,95 @@ static void test_loop(int ndist, int nsteps, int npt, double kt) {
   lb_free(lb);
 }
 
+/* The loop of src/ludwig.c:795-860 with flat walls: collide, halo, wall_bbl, propagate --
+ * a body-force driven duct flow between y and z walls, against the oracle. */
+static void test_walls(int nsteps) {
+  cs_t cs;
+  physics_t phys = {1.0, 0.1666, 0.1666, {1.0e-4, 0.0, 0.0}, 0.0, 0.0};
+  lb_data_options_t opts = lb_data_options_default();
+  lb_t * lb = NULL; hydro_t * hydro = NULL; wall_t * wall = NULL;
+  wall_param_t wp;
+  orc_model_t model; orc_box_t box; orc_param_t prm; orc_wall_t owall;
+  const int nl[3] = {6, 9, 34};
+  const double zero[3] = {0.0, 0.0, 0.0};
+  unsigned long seed = 20200424;
+  double gw[3];
+
+  cs_serial(&cs, nl[0], nl[1], nl[2]);
+  cs.periodic[1] = 0; cs.periodic[2] = 0;
+  for (int a = 1; a < 3; a++) { cs.mpi_cart_neighbours[0][a] = -1; cs.mpi_cart_neighbours[1][a] = -1; }
+  OK(lb_data_create(&cs, &phys, &opts, &lb));
+  OK(hydro_create(lb, &hydro));
+  memset(&wp, 0, sizeof(wp));
+  wp.isboundary[1] = 1; wp.isboundary[2] = 1;
+  OK(wall_create(lb, &wall));
+  OK(wall_commit(wall, &wp));
+
+  orc_model_init(lb->nvel, &model);
+  orc_box_init(nl, &box);
+  memset(&prm, 0, sizeof(prm));
+  prm.rho0 = phys.rho0; prm.eta_shear = phys.eta_shear; prm.eta_bulk = phys.eta_bulk;
+  for (int a = 0; a < 3; a++) prm.force_global[a] = phys.fbody[a];
+  memset(&owall, 0, sizeof(owall));
+  owall.isboundary[1] = 1; owall.isboundary[2] = 1;
+
+  size_t nf = (size_t) lb->nsite*lb->nvel;
+  double * f = (double *) calloc(nf, sizeof(double));
+  double * fprime = (double *) calloc(nf, sizeof(double));
+  double * rho = (double *) calloc(lb->nsite, sizeof(double));
+  double * u = (double *) calloc(3*(size_t) lb->nsite, sizeof(double));
+  double * force = (double *) calloc(3*(size_t) lb->nsite, sizeof(double));
+  for (int ic = 1; ic <= nl[0]; ic++) for (int jc = 1; jc <= nl[1]; jc++) for (int kc = 1; kc <= nl[2]; kc++) {
+    long index = cs_index(&cs, ic, jc, kc);
+    double r = 1.0 + 0.02*urand(&seed);
+    double uu[3] = {0.02*urand(&seed), 0.02*urand(&seed), 0.02*urand(&seed)};
+    orc_equilib_set(&model, 1, f, index, r, uu);
+  }
+  memcpy(lb->f, f, nf*sizeof(double));
+  OK(lb_memcpy(lb, tdpMemcpyHostToDevice));
+
+  for (int n = 0; n < nsteps; n++) {
+    OK(hydro_f_zero(hydro, zero));
+    OK(hydro_u_zero(hydro, zero));
+    OK(lb_collide(lb, hydro, NULL, NULL, NULL, NULL));
+    OK(lb_halo(lb));
+    OK(wall_set_wall_distributions(wall));
+    OK(wall_bbl(wall));
+    OK(lb_propagation(lb));
+  }
+  OK(lb_memcpy(lb, tdpMemcpyDeviceToHost));
+  OK(hydro_memcpy(hydro, tdpMemcpyDeviceToHost));
+  OK(wall_momentum(wall, gw));
+
+  orc_wall_attach(&owall);
+  orc_step(&model, &box, &prm, 1, nsteps, f, fprime, rho, u, force, NULL, NULL, NULL);
+  orc_wall_attach(NULL);
+
+  double emax = 0.0, fmax = 0.0, umax = 0.0;
+  for (int ic = 1; ic <= nl[0]; ic++) for (int jc = 1; jc <= nl[1]; jc++) for (int kc = 1; kc <= nl[2]; kc++) {
+    long index = cs_index(&cs, ic, jc, kc);
+    for (int p = 0; p < lb->nvel; p++) {
+      long i = LB_ADDR(lb->nsite, 1, lb->nvel, index, 0, p);
+      if (fabs(lb->f[i] - f[i]) > emax) emax = fabs(lb->f[i] - f[i]);
+      if (fabs(f[i]) > fmax) fmax = fabs(f[i]);
+    }
+    for (int a = 0; a < 3; a++) {
+      double d = fabs(hydro->u.data[3*index + a] - u[3*index + a]);
+      if (d > umax) umax = d;
+    }
+  }
+  printf("test_walls: %d steps, max|df|/max|f| = %.3e, max|du| = %.3e, wall momentum %.6e %.3e %.3e (oracle %.6e)\n",
+	 nsteps, emax/fmax, umax, gw[0], gw[1], gw[2], owall.fnet[0]);
+  CHECK(emax/fmax < 1.0e-12, "walls: time loop vs oracle");
+  CHECK(umax < 1.0e-12, "walls: hydro u vs oracle");
+  for (int a = 0; a < 3; a++) CHECK(fabs(gw[a] - owall.fnet[a]) < 1.0e-10, "wall momentum account");
+
+  free(f); free(fprime); free(rho); free(u); free(force);
+  wall_free(wall);
+  hydro_free(hydro);
+  lb_free(lb);
+}
+
 int main(void) {
   test_prop(1, LB_HALO_TARGET);
   test_prop(2, LB_HALO_TARGET);
@@ -275,6 +364,7 @@ int main(void) {
   test_loop(2, 7, 27, 0.0);
   test_loop(1, 7, 7, 2.13333e-05);          /* isothermal fluctuations */
   test_loop(2, 7, 7, 2.13333e-05);
+  test_walls(9);
   if (nfail) { printf("%d check(s) FAILED\n", nfail); return 1; }
   printf("host shim: all passed\n");
   return 0;

@@ -2,7 +2,8 @@
 serial-dist-{3du,1dp,2kh,2sw}.{inp,log}, d2q9/serial-2khz-bm1, 2560 steps of D2Q9, and
 d2q9/serial-flct-t01, 200 fluctuating steps; and for the binary fluid d3q19-short/
 serial-spin-lb{1,3,4}: symmetric_lb spinodal decomposition with the 27-point gradient, lb3
-and lb4 fluctuating, lb1 and lb4 with ghost modes off): the statistics printed after the last step,
+and lb4 fluctuating, lb1 and lb4 with ghost modes off; and with walls serial-rect-ct1 (duct flow
+driven by a body force) and serial-wall-st1 (closed box, fluctuating): the statistics printed after the last step,
 reproduced the way tests/test-diff.sh + tests/awk-fp-diff.sh judge them -- every printed
 float, in the reference's printf format, within an ABSOLUTE 1e-12.
 
@@ -237,12 +238,17 @@ def test_cuda_reproduces_reference_log(case, hydro_write):
     nt, f = initial_state(rec["input"], models_host.cv(nvel), models_host.wv(nvel))
     eta, zeta = viscosities(rec["input"])
     ndist = f.shape[1]
-    lat = lb.Lattice(nvel, nt, ndist=ndist)
+    periodic = tuple(int(x) for x in rec["input"].get("periodicity", "1_1_1").split("_"))
+    lat = lb.Lattice(nvel, nt, ndist=ndist, periodic=periodic)
     lat.set_option("hydro_write", hydro_write)
     lat.set_option("halo", lb.HALO_REDUCED)          # lb_halo_openmp_reduced in the input
     kt = float(rec["input"].get("temperature", 0.0)) if noisy(rec) else 0.0
     kw = binary_params(rec["input"]) if ndist == 2 else {}
-    lat.set_param(eta_shear=eta, eta_bulk=zeta, kt=kt, ghost_off=int(ghost_off(rec)), **kw)
+    lat.set_param(eta_shear=eta, eta_bulk=zeta, kt=kt, ghost_off=int(ghost_off(rec)),
+                  force=body_force(rec["input"]), **kw)
+    if walls(rec):
+        lat.wall_commit(walls(rec), (float(rec["input"].get("boundary_speed_bottom", 0.0)), 0.0, 0.0),
+                        (float(rec["input"].get("boundary_speed_top", 0.0)), 0.0, 0.0))
     if ndist == 2:
         lat.field_grad_set(gradient_points(rec))
     if noisy(rec):
@@ -255,7 +261,8 @@ def test_cuda_reproduces_reference_log(case, hydro_write):
     nall = tuple(n + 2 for n in nt)
     m = np.zeros(nall, dtype=bool)
     m[1:-1, 1:-1, 1:-1] = True
-    check(rec, nt, sums, u[m.reshape(-1)])
+    check(rec, nt, sums, u[m.reshape(-1)],
+          gwall=list(lat.wall_momentum()) if walls(rec) else None)
     fh = lat.lb_memcpy_d2h()[m.reshape(-1)]
     if ndist == 2:
         check_binary(rec, nt, fh, lat.field_d2h(lb.FIELD_GRAD)[m.reshape(-1)])
