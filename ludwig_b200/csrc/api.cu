@@ -850,17 +850,23 @@ extern "C" int b200lb_wall_bbl(b200lb_t * h) {
     // x_p of the outgoing link p is minus the correction of the incoming Q - p
     W.xout[p] = (p > 0) ? -P.wall_corr[W.nvel - p] : 0.0;
   }
+  int nb = 1, na = 1;
   for (int d = 0; d < 3; d++) {
     for (int side = 0; side < 2; side++) {
       if (!(side == 0 ? W.wall_lo[d] : W.wall_hi[d])) continue;
       const int da = (d == 0) ? 1 : 0, db = (d == 2) ? 1 : 2;
-      W.face_axis = d; W.face_hi = side;
-      dim3 block(128, 1, 1);
-      dim3 grid((h->L.n[db] + 127)/128, h->L.n[da], 1);
-      wall_fnet_kernel<<<grid, block, 0, h->s_main>>>(W, h->lat[h->cur], h->fnet_dev);
-      CU(cudaGetLastError());
-      h->launches++;
+      W.face_axis[W.nface] = d; W.face_hi[W.nface] = side;
+      W.nface++;
+      if (h->L.n[db] > nb) nb = h->L.n[db];
+      if (h->L.n[da] > na) na = h->L.n[da];
     }
+  }
+  if (W.nface > 0) {
+    dim3 block(128, 1, 1);
+    dim3 grid((nb + 127)/128, na, W.nface);
+    wall_fnet_kernel<<<grid, block, 0, h->s_main>>>(W, h->lat[h->cur], h->fnet_dev);
+    CU(cudaGetLastError());
+    h->launches++;
   }
   h->bbl_armed = true;
   return 0;

@@ -310,7 +310,7 @@ __global__ void fill_kernel(double * __restrict__ data, i64 n, i64 plane, int nf
 // wall_bbl_kernel, src/wall.c:1073-1081,1096-1106): for every link (fluid site i on
 // a wall face, velocity p pointing into a wall layer)
 //   fnet += (2 f_p(i) - x_p - 2 w_p) c_p,   x_p = 2 rcs2 w_p rho0 (c_p . u_wall)
-// from the post-collision populations. One launch per wall face; a site on several
+// from the post-collision populations. blockIdx.z walks the wall faces; a site on several
 // faces (edges, corners) is handled by the first face in the order 0lo 0hi 1lo 1hi 2lo 2hi.
 // ---------------------------------------------------------------------------
 
@@ -322,20 +322,22 @@ struct WallTab {
   signed char pcv[27][3];         // physical components of c_p
   double wv[27];
   double xout[27];                // x_p for the outgoing link p
-  int face_axis, face_hi;         // the face this launch covers
+  int nface;                      // wall faces this rank holds; blockIdx.z picks one
+  int face_axis[6], face_hi[6];
 };
 
 __global__ void __launch_bounds__(128)
 wall_fnet_kernel(const WallTab W, const double * __restrict__ f, double * __restrict__ fnet) {
   const Layout & L = W.L;
-  const int d = W.face_axis;
+  const int d = W.face_axis[blockIdx.z];
+  const int face_hi = W.face_hi[blockIdx.z];
   const int da = (d == 0) ? 1 : 0, db = (d == 2) ? 1 : 2;      // the two in-face axes, db fastest
   const int ib = blockIdx.x*blockDim.x + threadIdx.x;
   const int ia = blockIdx.y;
   double acc[3] = {0.0, 0.0, 0.0};
   if (ib < L.n[db] && ia < L.n[da]) {
     int ic[3];
-    ic[d] = W.face_hi ? L.n[d] - 1 : 0;
+    ic[d] = face_hi ? L.n[d] - 1 : 0;
     ic[da] = ia; ic[db] = ib;
     bool lo[3], hi[3];
     bool earlier = false;
@@ -345,7 +347,7 @@ wall_fnet_kernel(const WallTab W, const double * __restrict__ f, double * __rest
       hi[e] = W.wall_hi[e] && ic[e] == L.n[e] - 1;
       if (e < d && (lo[e] || hi[e])) earlier = true;
     }
-    if (W.face_hi && lo[d]) earlier = true;                  // n = 1: both faces are this site
+    if (face_hi && lo[d]) earlier = true;                    // n = 1: both faces are this site
     if (!earlier) {
       const i64 site = (i64)(ic[0] + L.h[0])*L.s0 + (i64)(ic[1] + L.h[1])*L.s1 + L.z0 + L.h[2] + ic[2];
       for (int p = 1; p < W.nvel; p++) {
