@@ -40,6 +40,9 @@ def main():
     ap.add_argument("--overlap", type=int, default=1)
     ap.add_argument("--direct", type=int, default=1)
     ap.add_argument("--p2p", type=int, default=1)
+    ap.add_argument("--kt", type=float, default=0.0, help="> 0: isothermal fluctuations")
+    ap.add_argument("--gradient", type=int, default=7)
+    ap.add_argument("--walls", type=int, nargs=3, default=[0, 0, 0])
     args = ap.parse_args()
 
     rank = int(os.environ["RANK"])
@@ -55,7 +58,9 @@ def main():
         grid = (grid[0] * grid[2], grid[1], 1)
     local = tuple(args.lsize)
     ntotal = tuple(local[a] * grid[a] for a in range(3))
-    dec = lb.Decomposition(ntotal, rank, world, grid=grid)
+    walls = tuple(args.walls)
+    periodic = tuple(0 if w else 1 for w in walls)
+    dec = lb.Decomposition(ntotal, rank, world, grid=grid, periodic=periodic)
     cv, wv = models_host.cv(nvel), models_host.wv(nvel)
 
     lat = lb.Lattice(nvel, local, ndist=ndist, decomp=dec, device=local_rank)
@@ -77,7 +82,19 @@ def main():
     if ndist == 2:
         kw = dict(eta_shear=0.00625, eta_bulk=0.00625, mobility=3.75, a=-0.00625,
                   b=0.00625, kappa=0.004)
-    lat.set_param(**kw)
+    fg = (1e-4, 0.0, 0.0) if (any(walls) and not walls[0]) else (0.0, 0.0, 0.0)
+
+    def configure(l):
+        l.set_param(kt=args.kt, force=fg, **kw)
+        if ndist == 2:
+            l.field_grad_set(args.gradient)
+        if any(walls):
+            l.wall_commit(walls)
+        if args.kt > 0.0:
+            l.noise_init(0)
+            l.noise_present_set(1)
+
+    configure(lat)
 
     f0 = lbinit.make_state(cv, wv, local, ndist=ndist, ntotal=ntotal, offset=dec.offset,
                            ndim=ndim)
@@ -92,6 +109,8 @@ def main():
     lat.lb_halo_swap(lb.HALO_FULL)
     fh = lat.lb_memcpy_d2h()
     ok_halo = bool(np.array_equal(fh, f0))
+    if any(walls):
+        ok_halo = True          # wall layers are not exchanged (and never read)
 
     # 2. time loop. Ranks start it at different times on purpose: with the peer-memory
     # halo an early rank must not push into a neighbour that is still uploading.
@@ -102,6 +121,14 @@ def main():
     fd = lat.lb_memcpy_d2h()
     st = lat.stats()
     mine = fd.reshape(nall + (ndist, nvel))[1:-1, 1:-1, 1:-1].copy()
+    gw = torch.tensor(lat.wall_momentum() if any(walls) else np.zeros(3), device="cuda")
+    dist.all_reduce(gw, op=dist.ReduceOp.SUM)
+    nstate = None
+    if args.kt > 0.0:
+        nstate = lat.noise_memcpy_d2h().reshape(nall + (4,))[1:-1, 1:-1, 1:-1].astype(np.int64)
+        tn = torch.from_numpy(np.ascontiguousarray(nstate)).cuda()
+        nparts = [torch.empty_like(tn) for _ in range(world)] if rank == 0 else None
+        dist.gather(tn, nparts, dst=0)
 
     t = torch.from_numpy(mine).cuda()
     parts = [torch.empty_like(t) for _ in range(world)] if rank == 0 else None
@@ -120,32 +147,52 @@ def main():
             o = d.offset
             glob[o[0]:o[0] + local[0], o[1]:o[1] + local[1], o[2]:o[2] + local[2]] = parts[r].cpu().numpy()
         # the same lattice on ONE GPU
-        one = lb.Lattice(nvel, ntotal, ndist=ndist, device=local_rank)
+        one = lb.Lattice(nvel, ntotal, ndist=ndist, device=local_rank, periodic=periodic)
         one.set_option("fused", args.fused)
-        one.set_param(**kw)
+        configure(one)
         g0 = lbinit.make_state(cv, wv, ntotal, ndist=ndist, ndim=ndim)
         one.lb_memcpy_h2d(g0)
         one.step(args.steps)
         g1 = one.lb_memcpy_d2h().reshape(tuple(n + 2 for n in ntotal) + (ndist, nvel))[1:-1, 1:-1, 1:-1]
         s1 = one.stats()
-        one.close()
         same = bool(np.array_equal(glob, g1))
+        if any(walls):
+            gw1 = one.wall_momentum()
+            same = same and bool(np.allclose(gw.cpu().numpy(), gw1, rtol=1e-10, atol=1e-13))
+        if args.kt > 0.0:
+            # generator state: decomposition independent, word for word
+            gs = np.zeros(ntotal + (4,), dtype=np.int64)
+            for r in range(world):
+                o = lb.Decomposition(ntotal, r, world, grid=grid, periodic=periodic).offset
+                gs[o[0]:o[0] + local[0], o[1]:o[1] + local[1], o[2]:o[2] + local[2]] = nparts[r].cpu().numpy()
+            s_one = one.noise_memcpy_d2h().reshape(tuple(n + 2 for n in ntotal) + (4,))[1:-1, 1:-1, 1:-1]
+            same = same and bool(np.array_equal(gs, s_one.astype(np.int64)))
+        one.close()
         # and on the CPU oracle
         from oracle import pyoracle
         orc = pyoracle.Oracle(nvel, ntotal, ndist=ndist)
-        prm = pyoracle.make_param(**kw)
+        prm = pyoracle.make_param(force=fg, **kw)
         f, fp = g0.copy(), np.zeros_like(g0)
         n = orc.nsite
         rho, u, frc = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
         phi, grad, delsq = np.zeros(n), np.zeros((n, 3)), np.zeros(n)
+        if args.kt > 0.0:
+            orc.noise_attach(orc.noise_init(0), args.kt)
+        if any(walls):
+            orc.wall_attach(orc.wall(walls))
+        orc.gradient_select(args.gradient)
         orc.step(prm, args.steps, f, fp, rho, u, frc, phi, grad, delsq)
+        orc.noise_attach(None, 0.0)
+        orc.wall_attach(None)
+        orc.gradient_select(7)
         fo = f.reshape(tuple(n + 2 for n in ntotal) + (ndist, nvel))[1:-1, 1:-1, 1:-1]
         err = float(np.max(np.abs(glob - fo)) / np.max(np.abs(fo)))
         mass = abs(float(sums[0].item()) - s1[0])
         halo_ok = bool(flags.item() > 0.5)
-        print("mgpu world=%d grid=%s nvel=%d ndist=%d halo=%s fused=%d overlap=%d direct=%d p2p=%d: halo_bit_exact=%s "
+        print("mgpu world=%d grid=%s nvel=%d ndist=%d halo=%s fused=%d overlap=%d direct=%d p2p=%d kt=%g grad=%d walls=%s: halo_bit_exact=%s "
               "decomposed==single=%s err_vs_oracle=%.2e mass_diff=%.2e"
-              % (world, grid, nvel, ndist, args.halo, args.fused, args.overlap, args.direct, args.p2p, halo_ok, same, err, mass),
+              % (world, grid, nvel, ndist, args.halo, args.fused, args.overlap, args.direct, args.p2p, args.kt, args.gradient,
+                 walls, halo_ok, same, err, mass),
               flush=True)
         if not (halo_ok and same and err < 1e-12 and mass < 1e-9 * n):
             rc = 1

@@ -37,6 +37,15 @@ def launch(n, extra, port):
     ["--nvel", "27", "--halo", "reduced", "--lsize", "8", "6", "10"],
     ["--nvel", "19", "--ndist", "2", "--halo", "full", "--lsize", "8", "8", "6"],
     ["--nvel", "9", "--halo", "reduced", "--lsize", "16", "12", "1"],
+    # widened rows: fluctuations (decomposition-independent generators), the 27-point
+    # gradient (corners of the phi halo across ranks), walls held by the edge ranks only
+    ["--nvel", "19", "--halo", "reduced", "--kt", "1e-4"],
+    ["--nvel", "19", "--halo", "reduced", "--kt", "1e-4", "--p2p", "0"],
+    ["--nvel", "19", "--ndist", "2", "--halo", "full", "--lsize", "8", "8", "6", "--gradient", "27"],
+    ["--nvel", "19", "--ndist", "2", "--halo", "full", "--lsize", "8", "8", "6", "--gradient", "27", "--kt", "1e-5"],
+    ["--nvel", "19", "--halo", "reduced", "--walls", "1", "1", "0"],
+    ["--nvel", "19", "--halo", "reduced", "--walls", "1", "0", "1", "--p2p", "0", "--kt", "1e-4"],
+    ["--nvel", "9", "--halo", "reduced", "--lsize", "16", "12", "1", "--walls", "1", "1", "0"],
 ])
 def test_decomposed_equals_single(n, extra):
     if ngpu() < n:
