@@ -989,3 +989,146 @@ def test_walls_fused_equals_unfused_and_refusals():
     with pytest.raises(lb.B200LBError, match="binary"):
         lat.wall_commit((0, 0, 1))
     lat.close()
+
+
+# ---------------------------------------------------------------------------
+# the lazy state machine under random call sequences
+# ---------------------------------------------------------------------------
+
+@pytest.mark.parametrize("nvel,nlocal,ndist,walls,kt", [
+    (19, (10, 8, 6), 1, None, 0.0), (19, (6, 7, 36), 1, None, 1e-4), (9, (14, 12, 1), 1, None, 0.0),
+    (19, (8, 6, 34), 2, None, 0.0), (19, (8, 6, 6), 2, None, 1e-5), (19, (6, 7, 36), 1, (0, 1, 1), 0.0),
+    (19, (5, 6, 8), 1, (1, 1, 1), 1e-4), (27, (6, 5, 7), 1, None, 0.0)])
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_random_call_sequences(nvel, nlocal, ndist, walls, kt, seed):
+    """Stages of the time step interleaved at random with observations (lb_memcpy,
+    hydro_memcpy, statistics, file records), option changes (fused, hydro_write, halo
+    scheme, in-sweep diagnostics, gradient stencil) and re-uploads; after every
+    observation the device must agree with the oracle driven through the same stages.
+    Lazy propagation, deferred halos, hydro on demand, the in-register gradient and the
+    armed bounce-back must never show through the reference's call surface."""
+    import ludwig_b200 as lb
+    from oracle import pyoracle
+    rng = np.random.default_rng(1000*seed + nvel + ndist)
+    periodic = tuple(0 if w else 1 for w in walls) if walls else (1, 1, 1)
+    lat = lb.Lattice(nvel, nlocal, ndist=ndist, periodic=periodic)
+    orc = pyoracle.Oracle(nvel, nlocal, ndist=ndist)
+    m = orc.interior_mask()
+    n = orc.nsite
+    kw = dict(eta_shear=0.08, eta_bulk=0.11)
+    if ndist == 2:
+        kw = dict(eta_shear=0.00625, eta_bulk=0.00625, mobility=3.75, a=-0.00625,
+                  b=0.00625, kappa=0.004)
+    fg = (1e-4, 0.0, 0.0) if (walls and not walls[0]) else (0.0, 0.0, 0.0)
+    prm = pyoracle.make_param(force=fg, **kw)
+    lat.set_param(force=fg, kt=kt, **kw)
+    f = lbinit.make_state(orc.cv(), orc.wv(), nlocal, ndist=ndist, ndim=orc.ndim)
+    fp = np.zeros_like(f)
+    rho, u, frc = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
+    phi, grad, delsq = np.zeros(n), np.zeros((n, 3)), np.zeros(n)
+    state = None
+    wall = None
+    if kt > 0.0:
+        state = orc.noise_init(0)
+        lat.noise_init(0)
+        lat.noise_present_set(1)
+    if walls:
+        wall = orc.wall(walls)
+        lat.wall_commit(walls)
+    lat.lb_memcpy_h2d(f)
+    npt = 7
+    collided = False
+    full_halo = True            # the library's default scheme moves every population
+
+    def check_f():
+        assert relerr(lat.lb_memcpy_d2h()[m], f[m]) < TOL
+
+    try:
+        for it in range(14):
+            # ---- one time step, with observations between its stages -------------
+            orc.noise_attach(state, kt)
+            lat.hydro_f_zero()
+            frc[...] = 0.0
+            if ndist == 2:
+                lat.phi_lb_to_field()
+                orc.phi_from_g(f, phi)
+                if rng.random() < 0.3:
+                    assert np.array_equal(lat.field_d2h(lb.FIELD_PHI)[m], phi[m])
+                lat.field_halo()
+                orc.halo(phi, 1)
+                lat.field_grad_compute()
+                (orc.grad_27pt if npt == 27 else orc.grad_7pt)(phi, grad, delsq)
+                if rng.random() < 0.3:
+                    assert np.array_equal(lat.field_d2h(lb.FIELD_GRAD)[m], grad[m])
+                    assert np.array_equal(lat.field_d2h(lb.FIELD_DELSQ)[m], delsq[m])
+            lat.hydro_u_zero()
+            lat.lb_collide()
+            if ndist == 2:
+                orc.collide_binary(prm, f, frc, u, phi, grad, delsq)
+            else:
+                orc.collide_mrt(prm, f, frc, rho, u)
+            orc.noise_attach(None, 0.0)
+            collided = True
+            r = rng.random()
+            if r < 0.25:
+                check_f()                                    # post-collision populations
+            elif r < 0.4:
+                assert np.max(np.abs(lat.field_d2h(lb.FIELD_U)[m] - u[m])) < TOL
+            lat.lb_halo()
+            orc.halo(f, ndist*nvel)
+            if wall is not None:
+                lat.wall_bbl()
+                orc.wall_bbl(prm, wall, f)
+            if rng.random() < 0.2 and wall is None and full_halo:
+                # halo planes are pure data movement of the device's own interior values
+                fd = lat.lb_memcpy_d2h()
+                assert relerr(fd, f) < TOL
+            lat.lb_propagation()
+            orc.propagate(f, fp)
+            f, fp = fp, f
+            # ---- between steps: observations, option changes, re-uploads ---------
+            for _ in range(int(rng.integers(0, 3))):
+                op = rng.choice(["f", "u", "stats", "io", "fstats", "fused", "hydro_write",
+                                 "halo", "diag", "gradient", "upload", "state"])
+                if op == "f":
+                    check_f()
+                elif op == "u" and collided:
+                    assert np.max(np.abs(lat.field_d2h(lb.FIELD_U)[m] - u[m])) < TOL
+                    if ndist == 1:
+                        assert np.max(np.abs(lat.field_d2h(lb.FIELD_RHO)[m] - rho[m])) < TOL
+                elif op == "stats":
+                    s = lat.stats()
+                    assert abs(s[0] - f[m][:, 0].sum()) < 1e-9
+                    assert abs(s[2] - f[m][:, 0].sum(-1).min()) < TOL
+                elif op == "io":
+                    assert relerr(lat.lb_io_aggr_pack(), f[m]) < TOL
+                elif op == "fstats" and collided:
+                    q = lat.field_stats(lb.FIELD_U)
+                    assert np.max(np.abs(q[:, 2] - u[m].min(0))) < TOL
+                    assert np.max(np.abs(q[:, 3] - u[m].max(0))) < TOL
+                elif op == "fused":
+                    lat.set_option("fused", int(rng.integers(0, 2)))
+                elif op == "hydro_write":
+                    lat.set_option("hydro_write", int(rng.integers(0, 2)))
+                elif op == "halo":
+                    full_halo = bool(rng.random() < 0.5)
+                    lat.set_option("halo", lb.HALO_FULL if full_halo else lb.HALO_REDUCED)
+                elif op == "diag":
+                    lat.set_option("diag", int(rng.integers(0, 2)))
+                elif op == "gradient" and ndist == 2:
+                    npt = 27 if rng.random() < 0.5 else 7
+                    lat.field_grad_set(npt)
+                elif op == "upload":
+                    # hand the device the oracle's lattice: differences cannot pile up
+                    lat.lb_memcpy_h2d(f)
+                    collided = False
+                elif op == "state" and state is not None:
+                    assert np.array_equal(lat.noise_memcpy_d2h()[m], state[m])
+        check_f()
+        if wall is not None:
+            assert np.allclose(lat.wall_momentum(), np.array(wall.fnet[:]), rtol=1e-9, atol=1e-12)
+        if state is not None:
+            assert np.array_equal(lat.noise_memcpy_d2h()[m], state[m])
+    finally:
+        orc.noise_attach(None, 0.0)
+        lat.close()
