@@ -123,6 +123,12 @@ typedef struct orc_wall_s {
   double ubot[3];         /* boundary_speed_bottom (used for a single pair of walls) */
   double utop[3];
   double fnet[3];         /* momentum handed to the walls so far (wall_momentum) */
+  /* partial slip (boundary_walls_slip_*; src/wall.c:284-322,489-600,1118-1210): fraction
+   * s of specular reflection per wall; edges take the mean of their two walls, corners
+   * and links without a tangential component stay no-slip. Walls do not move then. */
+  int slip_active;
+  double sbot[3];
+  double stop[3];
 } orc_wall_t;
 int orc_wall_attach(orc_wall_t * wall);
 orc_wall_t * orc_wall_attached(void);

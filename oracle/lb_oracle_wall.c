@@ -51,6 +51,80 @@ int orc_wall_nlink(const orc_model_t * model, const orc_box_t * box,
   return nlink;
 }
 
+/* wall_bbl_slip_kernel, src/wall.c:1118-1210, with the link geometry of
+ * wall_init_boundaries_slip (src/wall.c:489-600): for a link (i, p) the wall normal
+ * collects the axes along which the step c_p alone already lands in a wall; the
+ * remaining (tangential) part of c_p leads to the fluid site k whose population q --
+ * c_p with its tangential components reversed -- slips along the wall and arrives at i
+ * together with the bounced one:  f(j, -p) = (1 - s) f(i, p) + s f(k, q). */
+
+static int wall_bbl_slip(const orc_model_t * model, const orc_box_t * box,
+			 int ndist, orc_wall_t * wall, double * f) {
+
+  const int nvel = model->nvel;
+
+  if (ndist != 1) return -1;
+
+  for (int ic = 1; ic <= box->nlocal[0]; ic++) {
+    for (int jc = 1; jc <= box->nlocal[1]; jc++) {
+      for (int kc = 1; kc <= box->nlocal[2]; kc++) {
+	const int r0[3] = {ic, jc, kc};
+	const long i = orc_index(box, ic, jc, kc);
+	for (int p = 1; p < nvel; p++) {
+	  const int * c = model->cv[p];
+	  const int r[3] = {ic + c[0], jc + c[1], kc + c[2]};
+	  int wn[3] = {0, 0, 0}, wt[3], cq[3], rk[3];
+	  int modwn = 0, modwt = 0, q = -1;
+	  double s = 0.0, fi, fk;
+	  long j, k;
+	  if (!in_wall(box, wall, r)) continue;
+	  j = orc_index(box, r[0], r[1], r[2]);
+	  for (int a = 0; a < 3; a++) {
+	    int ra[3] = {r0[0], r0[1], r0[2]};
+	    ra[a] += c[a];
+	    if (c[a] != 0 && in_wall(box, wall, ra)) wn[a] = -c[a];
+	    modwn += wn[a]*wn[a];
+	  }
+	  for (int a = 0; a < 3; a++) {
+	    wt[a] = wn[a] ? 0 : c[a];
+	    modwt += wt[a]*wt[a];
+	    cq[a] = -2*wn[a] - c[a];
+	    rk[a] = r0[a] + wt[a];
+	  }
+	  k = i; q = p;
+	  if (modwt != 0) {
+	    k = orc_index(box, rk[0], rk[1], rk[2]);
+	    for (int pp = 0; pp < nvel; pp++) {
+	      if (model->cv[pp][0] == cq[0] && model->cv[pp][1] == cq[1] && model->cv[pp][2] == cq[2]) q = pp;
+	    }
+	    if (modwn == 1) {
+	      for (int a = 0; a < 3; a++) {
+		if (wn[a] == +1) s = wall->sbot[a];
+		if (wn[a] == -1) s = wall->stop[a];
+	      }
+	    }
+	    if (modwn == 2) {
+	      for (int a = 0; a < 3; a++) {
+		if (wn[a] == +1) s += 0.5*wall->sbot[a];
+		if (wn[a] == -1) s += 0.5*wall->stop[a];
+	      }
+	    }
+	  }
+	  fi = f[i*nvel + p];
+	  fk = f[k*nvel + q];
+	  f[j*nvel + (nvel - p)] = (1.0 - s)*fi + s*fk;
+	  for (int a = 0; a < 3; a++) {
+	    double w = -(c[a] + model->cv[q][a])/2;
+	    wall->fnet[a] += 2.0*(1.0 - s)*(fi - model->wv[p])*c[a];
+	    wall->fnet[a] += 2.0*w*w*s*(fk - model->wv[q])*model->cv[q][a];
+	  }
+	}
+      }
+    }
+  }
+  return 0;
+}
+
 int orc_wall_bbl(const orc_model_t * model, const orc_box_t * box,
 		 const orc_param_t * prm, int ndist, orc_wall_t * wall,
 		 double * f) {
@@ -59,6 +133,8 @@ int orc_wall_bbl(const orc_model_t * model, const orc_box_t * box,
   const double rcs2 = 3.0;
   const int nwall = wall->isboundary[0] + wall->isboundary[1] + wall->isboundary[2];
   int iw = -1;
+
+  if (wall->slip_active) return wall_bbl_slip(model, box, ndist, wall, f);
 
   /* wall_init_uw, src/wall.c:864-893: wall velocities only for a single pair */
   if (nwall == 1) {

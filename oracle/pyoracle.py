@@ -57,6 +57,9 @@ class Wall(ctypes.Structure):
         ("ubot", ctypes.c_double * 3),
         ("utop", ctypes.c_double * 3),
         ("fnet", ctypes.c_double * 3),
+        ("slip_active", ctypes.c_int),
+        ("sbot", ctypes.c_double * 3),
+        ("stop", ctypes.c_double * 3),
     ]
 
 
@@ -204,11 +207,17 @@ class Oracle:
         assert self.L.orc_gradient_select(int(npt)) == 0
 
     # -- flat walls (oracle/lb_oracle_wall.c) ---------------------------------------
-    def wall(self, isboundary, ubot=(0.0, 0.0, 0.0), utop=(0.0, 0.0, 0.0)):
+    def wall(self, isboundary, ubot=(0.0, 0.0, 0.0), utop=(0.0, 0.0, 0.0), sbot=None, stop=None,
+             slip_active=None):
         w = Wall()
         w.isboundary[:] = isboundary
         w.ubot[:] = ubot
         w.utop[:] = utop
+        w.sbot[:] = sbot or (0.0, 0.0, 0.0)
+        w.stop[:] = stop or (0.0, 0.0, 0.0)
+        # wall_slip(), src/wall.c:284-294: active if any fraction is non-zero (or forced)
+        active = any(x != 0.0 for x in list(w.sbot) + list(w.stop))
+        w.slip_active = int(active if slip_active is None else slip_active)
         return w
 
     def wall_attach(self, wall):

@@ -178,6 +178,13 @@ class Ref:
         assert rc == 0
         return self.L.refdrv_wall_nlink()
 
+    def wall_slip(self, isboundary, sbot, stop, force_active=0):
+        """boundary_walls with boundary_walls_slip_fraction_bot/_top (/_active)."""
+        rc = self.L.refdrv_wall_slip((ctypes.c_int * 3)(*isboundary), (ctypes.c_double * 3)(*sbot),
+                                     (ctypes.c_double * 3)(*stop), int(force_active))
+        assert rc == 0
+        return self.L.refdrv_wall_nlink()
+
     def wall_bbl(self):
         assert self.L.refdrv_wall_bbl() == 0
 

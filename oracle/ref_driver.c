@@ -279,6 +279,21 @@ int refdrv_wall(const int isboundary[3], const double ubot[3], const double utop
   wall_create(rd.pe, rd.cs, rd.map, rd.lb, &rd.wall);
   return wall_commit(rd.wall, &p);
 }
+/* the same with partial slip: wall_slip() table + "boundary_walls_slip_active"
+ * (src/wall_rt.c:86-104) */
+int refdrv_wall_slip(const int isboundary[3], const double sbot[3], const double stop[3],
+		     int force_active) {
+  wall_param_t p = {0};
+  double sb[3] = {sbot[0], sbot[1], sbot[2]};
+  double st[3] = {stop[0], stop[1], stop[2]};
+  for (int ia = 0; ia < 3; ia++) p.isboundary[ia] = isboundary[ia];
+  p.iswall = (p.isboundary[0] || p.isboundary[1] || p.isboundary[2]);
+  p.slip = wall_slip(sb, st);
+  if (wall_slip_valid(&p.slip) == 0) return -1;
+  if (force_active) p.slip.active = 1;
+  wall_create(rd.pe, rd.cs, rd.map, rd.lb, &rd.wall);
+  return wall_commit(rd.wall, &p);
+}
 int refdrv_wall_nlink(void) { return rd.wall ? rd.wall->nlink : 0; }
 int refdrv_wall_bbl(void) {
   wall_set_wall_distributions(rd.wall);

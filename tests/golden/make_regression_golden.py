@@ -4,7 +4,7 @@ the fluctuating-hydrodynamics case d2q9/serial-flct-t01.log and the binary-fluid
 cases d3q19-short/serial-spin-lb{1,3,4}.log (symmetric_lb, 27-point gradient, lb3/lb4 with
 fluctuations, lb1/lb4 with ghost modes off), and the wall cases d3q19-short/serial-rect-ct1
 (body-force driven duct flow between y and z walls) and serial-wall-st1 (closed box with
-fluctuations), and the 400-step, eight-rank spinodal case d3q19/pmpi08-spin-lb1 (its log does
+fluctuations), serial-rect-ct2..5 (the duct with partial-slip walls), and the 400-step, eight-rank spinodal case d3q19/pmpi08-spin-lb1 (its log does
 not depend on the decomposition), Ludwig v0.20.1)
 into tests/golden/regression_logs.json, together with the input keys that define each
 case. Run in the build container (needs /root/reference)."""
@@ -19,7 +19,9 @@ CASES = ["d3q19-short/serial-dist-3du", "d3q19-short/serial-dist-1dp",
          "d3q19-short/serial-dist-2kh", "d3q19-short/serial-dist-2sw", "d2q9/serial-2khz-bm1",
          "d2q9/serial-flct-t01", "d3q19-short/serial-spin-lb1", "d3q19-short/serial-spin-lb3",
          "d3q19-short/serial-spin-lb4", "d3q19-short/serial-rect-ct1",
-         "d3q19-short/serial-wall-st1", "d3q19/pmpi08-spin-lb1"]
+         "d3q19-short/serial-wall-st1", "d3q19/pmpi08-spin-lb1",
+         "d3q19-short/serial-rect-ct2", "d3q19-short/serial-rect-ct3",
+         "d3q19-short/serial-rect-ct4", "d3q19-short/serial-rect-ct5"]
 NVEL = {"d3q19-short": 19, "d3q19": 19, "d2q9": 9}
 
 

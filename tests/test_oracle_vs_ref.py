@@ -374,3 +374,48 @@ def test_wall_bounce_back(nvel, nlocal, walls, ubot, utop):
         assert np.allclose(np.array(w.fnet[:]) + np.array(w1.fnet[:]), fn, rtol=1e-10, atol=1e-14)
         # mass of the fluid is conserved by the bounce-back
         assert abs(f[m].sum() - f0[m].sum()) < 1e-10
+
+
+@pytest.mark.parametrize("nvel,nlocal,walls,sbot,stop,force_active", [
+    (19, (4, 7, 6), (0, 1, 1), (0, 0, 0), (0, 0, 0), 1),            # serial-rect-ct2: slip code, s = 0
+    (19, (4, 7, 6), (0, 1, 1), (0, 0, 0), (0, 1.0, 1.0), 0),        # serial-rect-ct3
+    (19, (6, 5, 4), (1, 1, 0), (0, 0, 0), (1.0, 1.0, 0), 0),        # serial-rect-ct4
+    (19, (6, 5, 4), (1, 1, 1), (0.3, 0.1, 0.7), (0.2, 0.9, 0.5), 0),
+    (27, (4, 5, 4), (1, 0, 1), (0.25, 0, 0.5), (1.0, 0, 0.75), 0),
+    (9, (8, 7, 1), (1, 1, 0), (0.5, 0.2, 0), (0.4, 1.0, 0), 0)])
+def test_wall_slip(nvel, nlocal, walls, sbot, stop, force_active):
+    """wall_bbl_slip_kernel with the link geometry of wall_init_boundaries_slip: faces,
+    edges (mean of the two walls) and corners (no slip), alone and in the time loop."""
+    need_ref(nvel)
+    periodic = tuple(0 if w else 1 for w in walls)
+    orc = pyoracle.Oracle(nvel, nlocal)
+    f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal, ndim=orc.ndim)
+    fg = (2e-4, 0.0, 0.0) if not walls[0] else (0.0, 0.0, 0.0)
+    kw = dict(eta_shear=0.1666, eta_bulk=0.1)
+    prm = pyoracle.make_param(force=fg, **kw)
+    m = orc.interior_mask()
+    n = orc.nsite
+    with pyref.Ref(nvel, nlocal, periodic=periodic) as ref:
+        ref.physics(force=fg, **kw)
+        nlink = ref.wall_slip(walls, sbot, stop, force_active)
+        w = orc.wall(walls, sbot=sbot, stop=stop, slip_active=1)
+        assert orc.wall_nlink(w) == nlink
+        ref.f()[...] = f0
+        ref.wall_bbl()
+        f = f0.copy()
+        orc.wall_bbl(prm, w, f)
+        assert relerr(f, ref.f()) < 1e-15        # (1-s) fi + s fk: same expression
+        assert np.allclose(np.array(w.fnet[:]), ref.wall_momentum(), rtol=1e-12, atol=1e-15)
+        ref.f()[...] = f0
+        ref.step(12)
+        f = f0.copy()
+        fp = np.zeros_like(f)
+        rho, u, frc = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
+        w = orc.wall(walls, sbot=sbot, stop=stop, slip_active=1)
+        orc.wall_attach(w)
+        try:
+            orc.step(prm, 12, f, fp, rho, u, frc)
+        finally:
+            orc.wall_attach(None)
+        assert relerr(f[m], ref.f()[m]) < 1e-12
+        assert abs(f[m].sum() - f0[m].sum()) < 1e-10

@@ -167,6 +167,15 @@ def walls(rec):
     return w if any(w) else None
 
 
+def wall_slip(inp):
+    """(sbot, stop, active) from boundary_walls_slip_* (src/wall_rt.c:86-104)."""
+    def vec(key):
+        return tuple(float(x) for x in inp.get(key, "0_0_0").split("_"))
+    sbot, stop = vec("boundary_walls_slip_fraction_bot"), vec("boundary_walls_slip_fraction_top")
+    active = any(x != 0.0 for x in sbot + stop) or inp.get("boundary_walls_slip_active") in ("yes", "on", "1")
+    return sbot, stop, int(active)
+
+
 def body_force(inp):
     return tuple(float(x) for x in inp.get("force", "0_0_0").split("_"))
 
@@ -224,7 +233,8 @@ def test_oracle_reproduces_reference_log(case):
     if walls(rec):
         ub = (float(rec["input"].get("boundary_speed_bottom", 0.0)), 0.0, 0.0)
         ut = (float(rec["input"].get("boundary_speed_top", 0.0)), 0.0, 0.0)
-        wall = orc.wall(walls(rec), ub, ut)
+        sbot, stop, active = wall_slip(rec["input"])
+        wall = orc.wall(walls(rec), ub, ut, sbot=sbot, stop=stop, slip_active=active)
     n = orc.nsite
     fp = np.zeros_like(f)
     rho, u, frc = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
