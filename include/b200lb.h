@@ -150,10 +150,15 @@ int  b200lb_grad27(b200lb_t * h);                            /* grad_3d_27pt_flu
  * or fused into the next collision -- bounces the populations that would cross into a
  * wall back to the site they left (bounce-back on links, wall_bbl_kernel
  * src/wall.c:997-1107, moving-wall term for a single pair of walls included), and the
- * momentum handed to the walls is tallied (wall->fnet). Single fluid only; slip walls,
- * porous media and colloids are not on this path. */
+ * momentum handed to the walls is tallied (wall->fnet). Single fluid only; porous media
+ * and colloids are not on this path. */
 int  b200lb_wall_commit(b200lb_t * h, const int isboundary[3], const double ubot[3],
                         const double utop[3]);                         /* wall_create + wall_commit src/wall.c:59,168 */
+/* partial slip, "boundary_walls_slip_fraction_bot/_top", "boundary_walls_slip_active":
+ * fraction s of specular reflection per wall (faces: that wall's s, edges: the mean of
+ * the two, corners: none), wall_bbl_slip_kernel src/wall.c:1118-1210. After wall_commit. */
+int  b200lb_wall_slip_set(b200lb_t * h, const double sbot[3], const double stop[3],
+                          int force_active);                           /* wall_slip src/wall.c:284 */
 int  b200lb_wall_bbl(b200lb_t * h);                                    /* wall_bbl src/wall.c:960 */
 int  b200lb_wall_momentum(b200lb_t * h, double f[3]);                  /* wall_momentum src/wall.c:1299 */
 int  b200lb_wall_momentum_add(b200lb_t * h, const double f[3]);        /* wall_momentum_add src/wall.c:1279 */

@@ -106,6 +106,8 @@ struct b200lb_s {
   // flat walls (wall_t, src/wall.h)
   int wall_is[3];            // physical: isboundary
   double wall_ubot[3], wall_utop[3];
+  int wall_slip;             // wall->param->slip.active
+  double wall_sbot[3], wall_stop[3];
   bool wall_on;              // wall_commit was called with at least one boundary
   bool bbl_armed;            // wall_bbl was called: the next lb_propagation bounces at the walls
   bool prop_wall;            // ... and that propagation is the pending / running one
@@ -226,6 +228,29 @@ static int site_kparams(b200lb_s * h, KParams & P) {
       double cdotu = 0.0;
       if (uw) cdotu = h->ops->cv[ij][0]*uw[0] + h->ops->cv[ij][1]*uw[1] + h->ops->cv[ij][2]*uw[2];
       P.wall_corr[q] = -(2.0*3.0*h->ops->wv[ij]*h->prm.rho0*cdotu);
+    }
+    P.wall_slip = h->wall_slip;
+    for (int d = 0; d < 3; d++) {
+      const int a = h->ops->dax[d];
+      P.wall_s_lo[d] = h->wall_sbot[a];
+      P.wall_s_hi[d] = h->wall_stop[a];
+    }
+    // mirror images: the velocity index of c_p with the masked device-axis components reversed
+    for (int p = 0; p < Q; p++) {
+      for (int mask = 0; mask < 8; mask++) {
+	int want[3];
+	for (int d = 0; d < 3; d++) {
+	  const int c = h->ops->cv[p][h->ops->dax[d]];
+	  want[d] = (mask & (1 << d)) ? -c : c;
+	}
+	int found = p;
+	for (int q = 0; q < Q; q++) {
+	  bool same = true;
+	  for (int d = 0; d < 3; d++) if (h->ops->cv[q][h->ops->dax[d]] != want[d]) same = false;
+	  if (same) found = q;
+	}
+	P.wall_q[p][mask] = (signed char) found;
+      }
     }
   }
   P.noise = h->noise;
@@ -819,10 +844,36 @@ extern "C" int b200lb_wall_commit(b200lb_t * h, const int isboundary[3], const d
   if (isboundary[0] && (h->wall_ubot[0] != 0.0 || h->wall_utop[0] != 0.0))
     return fail("cannot have non-zero u_x wall velocity if the wall is in x");
   h->wall_on = any;
+  h->wall_slip = 0;
+  for (int a = 0; a < 3; a++) { h->wall_sbot[a] = 0.0; h->wall_stop[a] = 0.0; }
   h->bbl_armed = false;
   h->prop_wall = false;
   if (!h->fnet_dev) CU(cudaMalloc(&h->fnet_dev, 3*sizeof(double)));
   CU(cudaMemsetAsync(h->fnet_dev, 0, 3*sizeof(double), h->s_main));
+  return 0;
+}
+
+// wall_slip() + param.slip (src/wall.c:284-343, src/wall_rt.c:86-104): fraction of
+// specular reflection per wall, bottom and top, after b200lb_wall_commit
+extern "C" int b200lb_wall_slip_set(b200lb_t * h, const double sbot[3], const double stop[3],
+				    int force_active) {
+  if (!h || !sbot || !stop) return fail("null argument");
+  if (!h->wall_on) return fail("wall slip: no walls committed");
+  bool active = (force_active != 0);
+  for (int a = 0; a < 3; a++) {
+    if (sbot[a] < 0.0 || sbot[a] > 1.0 || stop[a] < 0.0 || stop[a] > 1.0)
+      return fail("wall slip parameters must be 0 <= s <= 1 everywhere");
+    if (sbot[a] != 0.0 || stop[a] != 0.0) active = true;
+  }
+  if (active) {
+    for (int a = 0; a < 3; a++) {
+      if (h->wall_ubot[a] != 0.0 || h->wall_utop[a] != 0.0)
+	return fail("wall slip: the slip bounce-back does not allow a wall velocity (src/wall.c:1114)");
+    }
+  }
+  if (h->prop_pending) { if (materialise(h)) return -1; }
+  h->wall_slip = active ? 1 : 0;
+  for (int a = 0; a < 3; a++) { h->wall_sbot[a] = sbot[a]; h->wall_stop[a] = stop[a]; }
   return 0;
 }
 
@@ -849,7 +900,10 @@ extern "C" int b200lb_wall_bbl(b200lb_t * h) {
     W.wv[p] = h->ops->wv[p];
     // x_p of the outgoing link p is minus the correction of the incoming Q - p
     W.xout[p] = (p > 0) ? -P.wall_corr[W.nvel - p] : 0.0;
+    for (int mask = 0; mask < 8; mask++) W.qflip[p][mask] = P.wall_q[p][mask];
   }
+  W.slip = P.wall_slip;
+  for (int d = 0; d < 3; d++) { W.s_lo[d] = P.wall_s_lo[d]; W.s_hi[d] = P.wall_s_hi[d]; W.wrap[d] = h->selfper[d]; }
   int nb = 1, na = 1;
   for (int d = 0; d < 3; d++) {
     for (int side = 0; side < 2; side++) {

@@ -322,6 +322,10 @@ struct WallTab {
   signed char pcv[27][3];         // physical components of c_p
   double wv[27];
   double xout[27];                // x_p for the outgoing link p
+  int slip;                       // partial slip (no wall velocity then)
+  double s_lo[3], s_hi[3];        // device axes
+  signed char qflip[27][8];       // velocity index with the masked device-axis components reversed
+  int wrap[3];                    // device axis periodic within this rank (tangential steps wrap)
   int nface;                      // wall faces this rank holds; blockIdx.z picks one
   int face_axis[6], face_hi[6];
 };
@@ -357,11 +361,45 @@ wall_fnet_kernel(const WallTab W, const double * __restrict__ f, double * __rest
 	  if (W.dcv[p][e] == -1 && lo[e]) link = true;
 	  if (W.dcv[p][e] ==  1 && hi[e]) link = true;
 	}
-	if (link) {
+	if (link && !W.slip) {
 	  const double fp = __ldg(f + (i64) p*L.nsd + site);
 	  const double force = 2.0*fp - W.xout[p];
 	  #pragma unroll
 	  for (int a = 0; a < 3; a++) acc[a] += (force - 2.0*W.wv[p])*W.pcv[p][a];
+	}
+	if (link && W.slip) {
+	  // src/wall.c:1166-1192: the bounced share hands over its full momentum, the
+	  // slipping share only the component along the wall normal
+	  bool nrm[3];
+	  int nn = 0, mask = 0;
+	  bool tang = false;
+	  double sl = 0.0;
+	  i64 koff = 0;
+	  #pragma unroll
+	  for (int e = 0; e < 3; e++) {
+	    nrm[e] = (W.dcv[p][e] == -1 && lo[e]) || (W.dcv[p][e] == 1 && hi[e]);
+	    if (nrm[e]) { nn++; sl += (W.dcv[p][e] == -1) ? W.s_lo[e] : W.s_hi[e]; }
+	    else if (W.dcv[p][e] != 0) {
+	      tang = true;
+	      mask |= (1 << e);
+	      // tangential step; a direction periodic within the rank wraps around
+	      int c = ic[e] + W.dcv[p][e];
+	      if (W.wrap[e]) c = (c + L.n[e]) % L.n[e];
+	      koff += (i64)(c - ic[e])*((e == 0) ? L.s0 : ((e == 1) ? L.s1 : 1));
+	    }
+	  }
+	  if (nn == 2) sl *= 0.5;
+	  if (!tang || nn == 3) sl = 0.0;
+	  const double fi = __ldg(f + (i64) p*L.nsd + site);
+	  // q: c_p with its tangential components reversed
+	  const int q = (sl != 0.0) ? W.qflip[p][mask] : p;
+	  const double fk = (sl != 0.0) ? __ldg(f + (i64) q*L.nsd + site + koff) : 0.0;
+	  #pragma unroll
+	  for (int a = 0; a < 3; a++) {
+	    acc[a] += 2.0*(1.0 - sl)*(fi - W.wv[p])*W.pcv[p][a];
+	    const double w = -(W.pcv[p][a] + W.pcv[q][a])/2;
+	    acc[a] += 2.0*w*w*sl*(fk - W.wv[q])*W.pcv[q][a];
+	  }
 	}
       }
     }

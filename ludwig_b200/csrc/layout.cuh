@@ -54,6 +54,12 @@ struct KParams {
   // post-collision populations (+ the moving-wall term): wall_bbl folded into the pull
   int wall_lo[3], wall_hi[3];   // per device axis: this rank holds the low / high wall
   double wall_corr[27];         // per incoming population q: -2 rcs2 w rho0 (c_{Q-q} . u_wall)
+  // partial slip (wall_bbl_slip_kernel, src/wall.c:1118-1210): fraction of specular
+  // reflection per wall; no wall velocity then
+  int wall_slip;
+  double wall_s_lo[3], wall_s_hi[3];   // per device axis
+  signed char wall_q[27][8];    // velocity index of c_p with the device-axis components in
+                                // the bit mask reversed (mirror image in those walls)
   // isothermal fluctuations (src/noise.c, src/collision.c:476-515,1663-1745)
   double * noise;         // [2][nsd]: KISS99 words (s0,s1) and (s2,s3) of every site as 64-bit pairs
   double nv_diag, nv_off; // stress variance: var_eta sqrt(2) on the diagonal, var_eta off it

@@ -16,7 +16,7 @@ typedef B200LB_MODEL MODEL;
 template <int VEC, bool PULL, bool COLLIDE, bool BINARY, int GM, bool WALL = false>
 static cudaError_t launch_one(SweepArgs & a) {
   // walls are folded into the pull of the single-fluid kernels only
-  if constexpr (!WALL && PULL && !BINARY) {
+  if constexpr (!WALL && PULL && !BINARY && VEC == 1) {
     if (a.wall) return launch_one<VEC, PULL, COLLIDE, BINARY, GM, true>(a);
   }
   else if constexpr (!WALL) {

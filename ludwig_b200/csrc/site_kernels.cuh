@@ -393,30 +393,72 @@ lb_sweep_kernel(const KParams P) {
     }
   }
 
+  if constexpr (WALL && PULL) {
+    // Wall slabs (one site per thread). A population whose pull would reach into a wall
+    // layer along some axes (the wall normal of that link) is instead
+    //   no slip:  the one that left this site in the opposite direction (+ moving wall)
+    //   slip s:   (1 - s) of that + s of its mirror image in the wall, taken from the
+    //             site reached by the tangential part of the step alone
+    // (wall_bbl_kernel / wall_bbl_slip_kernel, src/wall.c:997-1210, in pull form).
+    static_assert(!WALL || VEC == 1, "wall slabs are swept one site per thread");
+    #pragma unroll
+    for (int n = 0; n < NDIST; n++) {
+      #pragma unroll
+      for (int p = 0; p < Q; p++) {
+	const int c0 = dcv<M>(p, 0), c1 = dcv<M>(p, 1), c2 = dcv<M>(p, 2);
+	const i64 o0 = (c0 == 1) ? om[0] : ((c0 == -1) ? op[0] : 0);
+	const i64 o1 = (c1 == 1) ? om[1] : ((c1 == -1) ? op[1] : 0);
+	const i64 o2 = (c2 == 1) ? zm[0] : ((c2 == -1) ? zp[0] : 0);
+	const bool n0 = (c0 == 1 && w0lo) || (c0 == -1 && w0hi);
+	const bool n1 = (c1 == 1 && w1lo) || (c1 == -1 && w1hi);
+	const bool n2 = (c2 == 1 && w2lo[0]) || (c2 == -1 && w2hi[0]);
+	const double * plane = P.src + (i64)(n*Q)*L.nsd + site;
+	double val;
+	if (p == 0 || !(n0 || n1 || n2)) {
+	  val = ld1<NC>(plane + (i64) p*L.nsd + o0 + o1 + o2);
+	}
+	else {
+	  val = ld1<NC>(plane + (i64)(Q - p)*L.nsd);
+	  if (!P.wall_slip) {
+	    val += P.wall_corr[p];
+	  }
+	  else {
+	    const int nn = (n0 ? 1 : 0) + (n1 ? 1 : 0) + (n2 ? 1 : 0);
+	    const bool tang = (c0 != 0 && !n0) || (c1 != 0 && !n1) || (c2 != 0 && !n2);
+	    if (tang && nn < 3) {
+	      // a face takes its wall's fraction, an edge the mean of its two walls
+	      double sl = (n0 ? ((c0 == 1) ? P.wall_s_lo[0] : P.wall_s_hi[0]) : 0.0)
+		        + (n1 ? ((c1 == 1) ? P.wall_s_lo[1] : P.wall_s_hi[1]) : 0.0)
+		        + (n2 ? ((c2 == 1) ? P.wall_s_lo[2] : P.wall_s_hi[2]) : 0.0);
+	      if (nn == 2) sl *= 0.5;
+	      if (sl != 0.0) {
+		const int q = P.wall_q[p][(n0 ? 1 : 0) | (n1 ? 2 : 0) | (n2 ? 4 : 0)];
+		const double fk = ld1<NC>(plane + (i64) q*L.nsd + (n0 ? 0 : o0) + (n1 ? 0 : o1) + (n2 ? 0 : o2));
+		// separately rounded, as the reference's (1 - s) fi + s fk without contraction
+		val = __dadd_rn(__dmul_rn(1.0 - sl, val), __dmul_rn(sl, fk));
+	      }
+	    }
+	  }
+	}
+	f[n][0][p] = val;
+      }
+    }
+  }
+  else {
   #pragma unroll
   for (int n = 0; n < NDIST; n++) {
     #pragma unroll
     for (int p = 0; p < Q; p++) {
       const double * src = P.src + (i64)(n*Q + p)*L.nsd + site;
       int c2 = 0;
-      // bounce-back on links (wall_bbl_kernel, src/wall.c:997-1107, in pull form): a
-      // population that would come out of a wall layer is the one that left this very
-      // site in the opposite direction, still sitting here in the source lattice
-      bool bounce01 = false;
-      const double * rev = P.src + (i64)(n*Q + (Q - p) % Q)*L.nsd + site;
       if (PULL) {
 	if (dcv<M>(p, 0) ==  1) src += om[0];
 	if (dcv<M>(p, 0) == -1) src += op[0];
 	if (dcv<M>(p, 1) ==  1) src += om[1];
 	if (dcv<M>(p, 1) == -1) src += op[1];
 	c2 = dcv<M>(p, 2);
-	if (WALL && p > 0) {
-	  bounce01 = (dcv<M>(p, 0) == 1 && w0lo) || (dcv<M>(p, 0) == -1 && w0hi)
-	          || (dcv<M>(p, 1) == 1 && w1lo) || (dcv<M>(p, 1) == -1 && w1hi);
-	}
       }
       if (c2 == 0) {
-	if (WALL && bounce01) src = rev;
 	if (VEC == 2) {
 	  const double2 v = ld2<NC>(src);
 	  f[n][0][p] = v.x; f[n][VEC - 1][p] = v.y;
@@ -424,23 +466,16 @@ lb_sweep_kernel(const KParams P) {
 	else {
 	  f[n][0][p] = ld1<NC>(src);
 	}
-	if (WALL && bounce01) {
-	  #pragma unroll
-	  for (int v = 0; v < VEC; v++) f[n][v][p] += P.wall_corr[p];
-	}
       }
       else {
 	// moving along the contiguous axis: the pair straddles the aligned one
 	#pragma unroll
 	for (int v = 0; v < VEC; v++) {
-	  const bool bounce = WALL && (bounce01 || (c2 == 1 && w2lo[v]) || (c2 == -1 && w2hi[v]));
-	  const double * a = bounce ? rev + v : src + v + (c2 == 1 ? zm[v] : zp[v]);
-	  double val = ld1<NC>(a);
-	  if (bounce) val += P.wall_corr[p];
-	  f[n][v][p] = val;
+	  f[n][v][p] = ld1<NC>(src + v + (c2 == 1 ? zm[v] : zp[v]));
 	}
       }
     }
+  }
   }
 
   if (COLLIDE) {

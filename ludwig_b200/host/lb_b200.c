@@ -130,10 +130,30 @@ int wall_create(lb_t * lb, wall_t ** pwall) {
 
 int wall_free(wall_t * wall) { free(wall); return 0; }
 
+/* the face entries of the reference's table; the library derives edges and corners */
+wall_slip_t wall_slip(double sbot[3], double stop[3]) {
+  wall_slip_t ws;
+  memset(&ws, 0, sizeof(ws));
+  for (int a = 0; a < 3; a++) {
+    ws.s[WALL_SLIP_XBOT + 2*a] = sbot[a];
+    ws.s[WALL_SLIP_XTOP + 2*a] = stop[a];
+    if (sbot[a] != 0.0 || stop[a] != 0.0) ws.active = 1;
+  }
+  return ws;
+}
+
 int wall_commit(wall_t * wall, wall_param_t * param) {
   wall->param = *param;
   wall->param.iswall = (param->isboundary[0] || param->isboundary[1] || param->isboundary[2]);
   TRY(b200lb_wall_commit(wall->lb->target, param->isboundary, param->ubot, param->utop));
+  if (param->slip.active) {
+    double sbot[3], stop[3];
+    for (int a = 0; a < 3; a++) {
+      sbot[a] = param->slip.s[WALL_SLIP_XBOT + 2*a];
+      stop[a] = param->slip.s[WALL_SLIP_XTOP + 2*a];
+    }
+    TRY(b200lb_wall_slip_set(wall->lb->target, sbot, stop, 1));
+  }
   return 0;
 }
 

@@ -121,12 +121,17 @@ int lb_halo_swap(lb_t * lb, lb_halo_enum_t flag);
 int lb_propagation(lb_t * lb);
 
 /* wall_t (src/wall.h:47-76): flat no-slip walls */
+enum { WALL_NO_SLIP = 0, WALL_SLIP_XBOT, WALL_SLIP_XTOP, WALL_SLIP_YBOT, WALL_SLIP_YTOP,
+       WALL_SLIP_ZBOT, WALL_SLIP_ZTOP, WALL_SLIP_MAX = 19 };        /* src/wall.h:25-45 */
+typedef struct wall_slip_s { int active; double s[WALL_SLIP_MAX]; } wall_slip_t;
 typedef struct wall_param_s {
   int iswall;
   int isboundary[3];
   double ubot[3];
   double utop[3];
+  wall_slip_t slip;
 } wall_param_t;
+wall_slip_t wall_slip(double sbot[3], double stop[3]);             /* src/wall.c:284 */
 typedef struct wall_s { wall_param_t param; lb_t * lb; } wall_t;
 int wall_create(lb_t * lb, wall_t ** wall);                        /* src/wall.c:59 */
 int wall_free(wall_t * wall);

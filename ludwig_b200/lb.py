@@ -34,7 +34,7 @@ ABI_SYMBOLS = [
     "b200lb_propagate", "b200lb_phi_from_g", "b200lb_phi_halo", "b200lb_grad7", "b200lb_grad27",
     "b200lb_noise_init", "b200lb_noise_present_set", "b200lb_noise_state_upload",
     "b200lb_noise_state_download",
-    "b200lb_wall_commit", "b200lb_wall_bbl", "b200lb_wall_momentum", "b200lb_wall_momentum_add",
+    "b200lb_wall_commit", "b200lb_wall_slip_set", "b200lb_wall_bbl", "b200lb_wall_momentum", "b200lb_wall_momentum_add",
     "b200lb_field_stats", "b200lb_io_record_doubles", "b200lb_io_pack", "b200lb_io_unpack",
     "b200lb_step", "b200lb_stats", "b200lb_step_diag", "b200lb_sync", "b200lb_nccl_unique_id",
     "b200lb_comm_init", "b200lb_p2p_export", "b200lb_p2p_import", "b200lb_timer_start", "b200lb_timer_stop",
@@ -111,6 +111,7 @@ def load():
         getattr(L, name).argtypes = [vp]
     L.b200lb_halo_swap.argtypes = [vp, ctypes.c_int]
     L.b200lb_wall_commit.argtypes = [vp, vp, vp, vp]
+    L.b200lb_wall_slip_set.argtypes = [vp, vp, vp, ctypes.c_int]
     L.b200lb_wall_bbl.argtypes = [vp]
     L.b200lb_wall_momentum.argtypes = [vp, vp]
     L.b200lb_wall_momentum_add.argtypes = [vp, vp]
@@ -313,6 +314,10 @@ class Lattice:
         self._ck(self.L.b200lb_wall_commit(self.h, (ctypes.c_int * 3)(*isboundary),
                                            (ctypes.c_double * 3)(*ubot),
                                            (ctypes.c_double * 3)(*utop)))
+
+    def wall_slip_set(self, sbot, stop, force_active=0):
+        self._ck(self.L.b200lb_wall_slip_set(self.h, (ctypes.c_double * 3)(*sbot),
+                                             (ctypes.c_double * 3)(*stop), int(force_active)))
 
     def wall_bbl(self):
         self._ck(self.L.b200lb_wall_bbl(self.h))

@@ -1132,3 +1132,51 @@ def test_random_call_sequences(nvel, nlocal, ndist, walls, kt, seed):
     finally:
         orc.noise_attach(None, 0.0)
         lat.close()
+
+
+@pytest.mark.parametrize("nvel,nlocal,walls,sbot,stop", [
+    (19, (4, 7, 6), (0, 1, 1), (0, 0, 0), (0, 0, 0)),                 # slip code, s = 0
+    (19, (4, 7, 6), (0, 1, 1), (0, 0, 0), (0, 1.0, 1.0)),
+    (19, (6, 5, 4), (1, 1, 0), (0, 0, 0), (1.0, 1.0, 0)),
+    (19, (6, 5, 4), (1, 1, 1), (0.3, 0.1, 0.7), (0.2, 0.9, 0.5)),
+    (19, (7, 6, 70), (1, 1, 1), (0.3, 0.1, 0.7), (0.2, 0.9, 0.5)),    # slabs + interior
+    (19, (5, 6, 68), (0, 1, 1), (0, 0.5, 0.25), (0, 1.0, 0.0)),
+    (27, (4, 5, 4), (1, 0, 1), (0.25, 0, 0.5), (1.0, 0, 0.75)),
+    (9, (8, 7, 1), (1, 1, 0), (0.5, 0.2, 0), (0.4, 1.0, 0)),
+    (9, (40, 36, 1), (0, 1, 0), (0, 0.6, 0), (0, 0.1, 0))])
+@pytest.mark.parametrize("fused", [1, 0])
+def test_wall_slip_vs_oracle(nvel, nlocal, walls, sbot, stop, fused):
+    """Partial-slip walls (faces, edges with the mean fraction, no-slip corners) folded
+    into the pull, against the oracle: populations, velocity, wall momentum."""
+    import ludwig_b200 as lb
+    from oracle import pyoracle
+    periodic = tuple(0 if w else 1 for w in walls)
+    lat = lb.Lattice(nvel, nlocal, periodic=periodic)
+    orc = pyoracle.Oracle(nvel, nlocal)
+    f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal, ndim=orc.ndim)
+    fg = (2e-4, 0.0, 0.0) if not walls[0] else (0.0, 0.0, 0.0)
+    kw = dict(eta_shear=0.1666, eta_bulk=0.1)
+    prm = pyoracle.make_param(force=fg, **kw)
+    m = orc.interior_mask()
+    n = orc.nsite
+    nsteps = 11
+    w = orc.wall(walls, sbot=sbot, stop=stop, slip_active=1)
+    orc.wall_attach(w)
+    try:
+        f, fp = f0.copy(), np.zeros_like(f0)
+        rho, u, frc = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
+        orc.step(prm, nsteps, f, fp, rho, u, frc)
+    finally:
+        orc.wall_attach(None)
+    lat.set_param(force=fg, **kw)
+    lat.set_option("fused", fused)
+    lat.wall_commit(walls)
+    lat.wall_slip_set(sbot, stop, 1)
+    lat.lb_memcpy_h2d(f0)
+    lat.step(nsteps)
+    fd = lat.lb_memcpy_d2h()
+    assert relerr(fd[m], f[m]) < TOL
+    assert np.max(np.abs(lat.field_d2h(lb.FIELD_U)[m] - u[m])) < TOL
+    assert np.allclose(lat.wall_momentum(), np.array(w.fnet[:]), rtol=1e-10, atol=1e-13)
+    assert abs(fd[m].sum() - f0[m].sum()) < 1e-9
+    lat.close()

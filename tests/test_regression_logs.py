@@ -3,7 +3,7 @@ serial-dist-{3du,1dp,2kh,2sw}.{inp,log}, d2q9/serial-2khz-bm1, 2560 steps of D2Q
 d2q9/serial-flct-t01, 200 fluctuating steps; and for the binary fluid d3q19-short/
 serial-spin-lb{1,3,4}: symmetric_lb spinodal decomposition with the 27-point gradient, lb3
 and lb4 fluctuating, lb1 and lb4 with ghost modes off; and with walls serial-rect-ct1 (duct flow
-driven by a body force) and serial-wall-st1 (closed box, fluctuating): the statistics printed after the last step,
+driven by a body force) serial-wall-st1 (closed box, fluctuating) and serial-rect-ct2..5 (partial-slip walls): the statistics printed after the last step,
 reproduced the way tests/test-diff.sh + tests/awk-fp-diff.sh judge them -- every printed
 float, in the reference's printf format, within an ABSOLUTE 1e-12.
 
@@ -285,6 +285,9 @@ def test_cuda_reproduces_reference_log(case, hydro_write):
     if walls(rec):
         lat.wall_commit(walls(rec), (float(rec["input"].get("boundary_speed_bottom", 0.0)), 0.0, 0.0),
                         (float(rec["input"].get("boundary_speed_top", 0.0)), 0.0, 0.0))
+        sbot, stop, active = wall_slip(rec["input"])
+        if active:
+            lat.wall_slip_set(sbot, stop, 1)
     if ndist == 2:
         lat.field_grad_set(gradient_points(rec))
     if noisy(rec):
