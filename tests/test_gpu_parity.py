@@ -1052,15 +1052,18 @@ def test_random_call_sequences(nvel, nlocal, ndist, walls, kt, seed):
             if ndist == 2:
                 lat.phi_lb_to_field()
                 orc.phi_from_g(f, phi)
+                # (device and oracle populations differ by round-off after the first
+                # collision, so derived fields are compared to TOL here; bit-exactness
+                # on identical inputs is what the dedicated tests above establish)
                 if rng.random() < 0.3:
-                    assert np.array_equal(lat.field_d2h(lb.FIELD_PHI)[m], phi[m])
+                    assert np.max(np.abs(lat.field_d2h(lb.FIELD_PHI)[m] - phi[m])) < TOL
                 lat.field_halo()
                 orc.halo(phi, 1)
                 lat.field_grad_compute()
                 (orc.grad_27pt if npt == 27 else orc.grad_7pt)(phi, grad, delsq)
                 if rng.random() < 0.3:
-                    assert np.array_equal(lat.field_d2h(lb.FIELD_GRAD)[m], grad[m])
-                    assert np.array_equal(lat.field_d2h(lb.FIELD_DELSQ)[m], delsq[m])
+                    assert np.max(np.abs(lat.field_d2h(lb.FIELD_GRAD)[m] - grad[m])) < TOL
+                    assert np.max(np.abs(lat.field_d2h(lb.FIELD_DELSQ)[m] - delsq[m])) < TOL
             lat.hydro_u_zero()
             lat.lb_collide()
             if ndist == 2:
