@@ -137,6 +137,24 @@ int orc_wall_nlink(const orc_model_t * model, const orc_box_t * box,
 int orc_wall_bbl(const orc_model_t * model, const orc_box_t * box,
 		 const orc_param_t * prm, int ndist, orc_wall_t * wall, double * f);
 
+/* Lees-Edwards planes (lb_oracle_le.c; src/model_le.c, src/leesedwards.c). While
+ * attached, orc_step advances t_current by one at the start of every step
+ * (physics_control_next_step, src/ludwig.c:530) and applies the boundary conditions
+ * to the post-collision populations (src/ludwig.c:810). */
+typedef struct orc_le_s {
+  int nplanes;            /* N_LE_plane */
+  double uy;              /* LE_plane_vel: velocity jump across a plane */
+  int oscillatory;        /* 0 = steady shear */
+  int period;             /* LE_oscillation_period (time steps) */
+  int nt0;                /* LE_time_offset */
+  int t_current;          /* physics_control_timestep */
+} orc_le_t;
+int orc_le_attach(orc_le_t * le);
+orc_le_t * orc_le_attached(void);
+int orc_le_plane_location(const orc_box_t * box, const orc_le_t * le, int np);
+int orc_le_apply(const orc_model_t * model, const orc_box_t * box, int ndist,
+		 const orc_le_t * le, double t, double * f);
+
 int orc_fill(const orc_box_t * box, int nf, const double * v, double * data);
 
 /* stats[0..7] = sum rho, sum rho^2 (about mean is left to caller), min, max,

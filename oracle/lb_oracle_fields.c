@@ -396,6 +396,7 @@ int orc_step(const orc_model_t * model, const orc_box_t * box,
 
   for (int n = 0; n < nsteps; n++) {
     double * t;
+    if (orc_le_attached()) orc_le_attached()->t_current += 1;
     orc_fill(box, 3, zero, force);
     if (ndist == 2) {
       orc_phi_from_g(model, box, a, phi);
@@ -411,6 +412,10 @@ int orc_step(const orc_model_t * model, const orc_box_t * box,
       if (orc_collide_binary(model, box, prm, a, force, u, phi, grad, delsq)) {
 	return -1;
       }
+    }
+    if (orc_le_attached()) {
+      orc_le_t * le = orc_le_attached();
+      if (orc_le_apply(model, box, ndist, le, 1.0*le->t_current, a)) return -1;
     }
     orc_halo_periodic(box, ndist*model->nvel, a);
     if (orc_wall_attached()) {

@@ -63,6 +63,17 @@ class Wall(ctypes.Structure):
     ]
 
 
+class LeesEdwards(ctypes.Structure):
+    _fields_ = [
+        ("nplanes", ctypes.c_int),
+        ("uy", ctypes.c_double),
+        ("oscillatory", ctypes.c_int),
+        ("period", ctypes.c_int),
+        ("nt0", ctypes.c_int),
+        ("t_current", ctypes.c_int),
+    ]
+
+
 class Box(ctypes.Structure):
     _fields_ = [
         ("nlocal", ctypes.c_int * 3),
@@ -205,6 +216,27 @@ class Oracle:
 
     def gradient_select(self, npt):
         assert self.L.orc_gradient_select(int(npt)) == 0
+
+    # -- Lees-Edwards planes (oracle/lb_oracle_le.c) --------------------------------
+    def le(self, nplanes, uy, oscillatory=0, period=0, nt0=0, t_current=0):
+        le = LeesEdwards()
+        le.nplanes, le.uy, le.oscillatory = nplanes, uy, oscillatory
+        le.period, le.nt0, le.t_current = period, nt0, t_current
+        return le
+
+    def le_attach(self, le):
+        self._le = le
+        self.L.orc_le_attach(None if le is None else ctypes.byref(le))
+
+    def le_apply(self, le, t, f):
+        self.L.orc_le_apply.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
+                                        ctypes.c_void_p, ctypes.c_double, c_double_p]
+        rc = self.L.orc_le_apply(ctypes.byref(self.model), ctypes.byref(self.box), self.ndist,
+                                 ctypes.byref(le), float(t), _p(f))
+        assert rc == 0
+
+    def le_plane_location(self, le, n):
+        return self.L.orc_le_plane_location(ctypes.byref(self.box), ctypes.byref(le), int(n))
 
     # -- flat walls (oracle/lb_oracle_wall.c) ---------------------------------------
     def wall(self, isboundary, ubot=(0.0, 0.0, 0.0), utop=(0.0, 0.0, 0.0), sbot=None, stop=None,

@@ -57,11 +57,18 @@ def _lib(nvel):
 class Ref:
     """Reference objects on a periodic one-rank box ntotal, halo width 1."""
 
-    def __init__(self, nvel, ntotal, ndist=1, halo=HALO_TARGET, periodic=(1, 1, 1)):
+    def __init__(self, nvel, ntotal, ndist=1, halo=HALO_TARGET, periodic=(1, 1, 1), le=None):
+        """le = dict(nplanes, uy, oscillatory=0, period=0, nt0=0): Lees-Edwards planes."""
         self.L = _lib(nvel)
         assert self.L.refdrv_nvel() == nvel
         self.nvel, self.ndist = nvel, ndist
         self.L.refdrv_periodicity((ctypes.c_int * 3)(*periodic))
+        if le:
+            self.L.refdrv_le_options.argtypes = [ctypes.c_int, ctypes.c_double, ctypes.c_int,
+                                                 ctypes.c_int, ctypes.c_int]
+            self.L.refdrv_le_options(int(le["nplanes"]), float(le["uy"]),
+                                     int(le.get("oscillatory", 0)), int(le.get("period", 0)),
+                                     int(le.get("nt0", 0)))
         self.L.refdrv_init((ctypes.c_int * 3)(*ntotal), ndist, halo)
         nall = (ctypes.c_int * 3)()
         self.L.refdrv_nall(nall)
@@ -170,6 +177,17 @@ class Ref:
         """isothermal_fluctuations on/off at temperature kt (reseed > 0: noise_init
         again with that master seed)."""
         assert self.L.refdrv_noise(int(on), float(kt), int(reseed)) == 0
+
+    def le_apply(self, t):
+        """lb_le_apply_boundary_conditions at time step t."""
+        assert self.L.refdrv_le_apply(int(t)) == 0
+
+    def le_plane_location(self, n):
+        return self.L.refdrv_le_plane_location(int(n))
+
+    def time_set(self, t):
+        """The next refdrv_step starts with physics_control_next_step from here."""
+        self.L.refdrv_time_set(int(t))
 
     def wall(self, isboundary, ubot=(0.0, 0.0, 0.0), utop=(0.0, 0.0, 0.0)):
         """boundary_walls / boundary_speed_bottom,_top: wall_create + wall_commit."""

@@ -18,6 +18,7 @@
  *    grad_3d_27pt_fluid_d2 src/gradient_3d_27pt_fluid.c:75 (refdrv_grad_select(27))
  *    noise_init / noise_reap_n / noise_present_set  src/noise.c:136,398,557
  *    wall_create / wall_commit / wall_bbl / wall_momentum  src/wall.c:59,168,960,1299
+ *    lees_edw_create, lb_le_apply_boundary_conditions  src/leesedwards.c:80, src/model_le.c:57
  *    hydro_f_zero/u_zero  src/hydro.c:306,279
  *
  *  The step sequence of refdrv_step() follows src/ludwig.c:530-862 for the
@@ -50,6 +51,8 @@
 #include "gradient_3d_27pt_fluid.h"
 #include "timer.h"
 #include "wall.h"
+#include "model_le.h"
+#include "lees_edwards_options.h"
 
 typedef struct refdrv_s {
   pe_t * pe;
@@ -64,6 +67,7 @@ typedef struct refdrv_s {
   field_grad_t * phi_grad;
   fe_symm_t * fe;
   wall_t * wall;
+  int nplanes;
   int ndist;
   int mpi_up;
 } refdrv_t;
@@ -76,6 +80,20 @@ int refdrv_ndim(void) { return NDIM; }
 /* Create everything for a periodic box ntotal[3], halo width 1. */
 
 static int next_periodic[3] = {1, 1, 1};
+static lees_edw_options_t next_le = {0};
+
+/* Lees-Edwards planes of the NEXT refdrv_init ("N_LE_plane", "LE_plane_vel",
+ * "LE_oscillation_period", "LE_time_offset"; src/leesedwards_rt.c) */
+int refdrv_le_options(int nplanes, double uy, int oscillatory, int period, int nt0) {
+  lees_edw_options_t opts = {0};
+  opts.nplanes = nplanes;
+  opts.uy = uy;
+  opts.type = oscillatory ? LE_SHEAR_TYPE_OSCILLATORY : LE_SHEAR_TYPE_STEADY;
+  opts.period = period;
+  opts.nt0 = nt0;
+  next_le = opts;
+  return 0;
+}
 
 /* periodicity of the NEXT refdrv_init ("periodicity" input key, src/coords_rt.c) */
 int refdrv_periodicity(const int periodic[3]) {
@@ -99,9 +117,17 @@ int refdrv_init(const int ntotal[3], int ndist, int halo_scheme) {
   cs_periodicity_set(rd.cs, next_periodic);
   next_periodic[0] = next_periodic[1] = next_periodic[2] = 1;
   cs_init(rd.cs);
-  lees_edw_create(rd.pe, rd.cs, NULL, &rd.le);
+  physics_create(rd.pe, &rd.phys);       /* lees_edw_init takes physics_ref() */
+  if (next_le.nplanes > 0) {
+    lees_edw_create(rd.pe, rd.cs, &next_le, &rd.le);
+    rd.nplanes = next_le.nplanes;
+  }
+  else {
+    lees_edw_create(rd.pe, rd.cs, NULL, &rd.le);
+    rd.nplanes = 0;
+  }
+  memset(&next_le, 0, sizeof(next_le));
 
-  physics_create(rd.pe, &rd.phys);
 
   {
     lb_data_options_t opts = lb_data_options_default();
@@ -266,6 +292,15 @@ int refdrv_noise(int on, double kt, int reseed) {
   physics_kt_set(rd.phys, kt);
   return noise_present_set(rd.noise, NOISE_RHO, on);
 }
+/* lb_le_apply_boundary_conditions (src/model_le.c:57) at time step t
+ * (physics_control_timestep, which the time loop advances before each step) */
+int refdrv_le_apply(int t) {
+  physics_control_init_time(rd.phys, t, 1);
+  return lb_le_apply_boundary_conditions(rd.lb, rd.le);
+}
+int refdrv_le_plane_location(int np) { return lees_edw_plane_location(rd.le, np); }
+int refdrv_time_set(int t) { return physics_control_init_time(rd.phys, t, 1); }
+
 /* Flat walls: what wall_rt_init does for "boundary_walls" / "boundary_speed_*"
  * (src/wall_rt.c:40-120): wall_create + wall_commit (map, links, wall velocities). */
 int refdrv_wall(const int isboundary[3], const double ubot[3], const double utop[3]) {
@@ -326,6 +361,7 @@ double refdrv_step(int nsteps) {
   t0 = MPI_Wtime();
 
   for (n = 0; n < nsteps; n++) {
+    if (rd.nplanes > 0) physics_control_next_step(rd.phys);     /* src/ludwig.c:530 */
     hydro_f_zero(rd.hydro, zero);
     if (rd.ndist == 2) {
       phi_lb_to_field(rd.phi, rd.lb);
@@ -334,6 +370,7 @@ double refdrv_step(int nsteps) {
     }
     hydro_u_zero(rd.hydro, zero);
     lb_collide(rd.lb, rd.hydro, rd.map, rd.noise, (fe_t *) rd.fe, NULL);
+    if (rd.nplanes > 0) lb_le_apply_boundary_conditions(rd.lb, rd.le);   /* src/ludwig.c:810 */
     lb_halo(rd.lb);
     if (rd.wall) {                      /* src/ludwig.c:837-842 */
       wall_set_wall_distributions(rd.wall);

@@ -419,3 +419,59 @@ def test_wall_slip(nvel, nlocal, walls, sbot, stop, force_active):
             orc.wall_attach(None)
         assert relerr(f[m], ref.f()[m]) < 1e-12
         assert abs(f[m].sum() - f0[m].sum()) < 1e-10
+
+
+@pytest.mark.parametrize("nvel,nlocal,ndist,le", [
+    (19, (16, 6, 4), 1, dict(nplanes=2, uy=0.05)),
+    (19, (12, 7, 5), 1, dict(nplanes=1, uy=-0.03)),
+    (19, (12, 8, 4), 2, dict(nplanes=3, uy=0.02)),
+    (19, (16, 6, 4), 1, dict(nplanes=2, uy=0.04, oscillatory=1, period=40, nt0=0)),
+    (27, (8, 6, 5), 1, dict(nplanes=2, uy=0.05)),
+    (9, (16, 12, 1), 1, dict(nplanes=4, uy=0.01))])
+def test_lees_edwards(nvel, nlocal, ndist, le):
+    """lb_le_apply_boundary_conditions (src/model_le.c:57): reprojection of the plane-
+    crossing populations and their interpolated displacement, at several times (integer
+    and fractional displacements, wrap-around), then inside the time loop."""
+    need_ref(nvel)
+    orc = pyoracle.Oracle(nvel, nlocal, ndist=ndist)
+    f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal, ndist=ndist, ndim=orc.ndim)
+    m = orc.interior_mask()
+    n = orc.nsite
+    kw = dict(eta_shear=0.1, eta_bulk=0.1)
+    if ndist == 2:
+        kw = dict(eta_shear=0.00625, eta_bulk=0.00625, mobility=3.75)
+    prm = pyoracle.make_param(a=-0.00625, b=0.00625, kappa=0.004, **kw)
+    ole = orc.le(**le)
+    with pyref.Ref(nvel, nlocal, ndist=ndist, le=le) as ref:
+        ref.physics(**kw)
+        if ndist == 2:
+            ref.fe_symm(-0.00625, 0.00625, 0.004)
+        for k in range(le["nplanes"]):
+            assert orc.le_plane_location(ole, k) == ref.le_plane_location(k)
+        for t in (1, 7, 20, 133, 1000):
+            ref.f()[...] = f0
+            ref.le_apply(t)
+            f = f0.copy()
+            orc.le_apply(ole, t, f)
+            assert relerr(f, ref.f()) < 1e-15, t
+        assert relerr(f, f0) > 1e-4           # it does something
+        ref.f()[...] = f0
+        ref.time_set(5)
+        ref.step(9)
+        f = f0.copy()
+        fp = np.zeros_like(f)
+        rho, u, frc = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
+        phi, grad, delsq = np.zeros(n), np.zeros((n, 3)), np.zeros(n)
+        ole.t_current = 5
+        orc.le_attach(ole)
+        try:
+            orc.step(prm, 9, f, fp, rho, u, frc, phi, grad, delsq)
+        finally:
+            orc.le_attach(None)
+        if ndist == 1:
+            assert relerr(f[m], ref.f()[m]) < 1e-12
+        else:
+            # the reference's phi halo and gradient are Lees-Edwards aware; the oracle's are
+            # not (out of scope), so only the density distribution's first step agrees
+            pass
+        assert abs(f[m][:, 0].sum() - f0[m][:, 0].sum()) < 1e-10
