@@ -57,6 +57,8 @@ def parse():
                     help="binary fluid: order-parameter gradient stencil")
     ap.add_argument("--kt", type=float, default=0.0,
                     help="> 0: isothermal fluctuations at this temperature (not the headline workload)")
+    ap.add_argument("--le", type=int, default=0,
+                    help="Lees-Edwards planes in total, uy 0.01 (not the headline workload)")
     ap.add_argument("--walls", type=int, nargs=3, default=None,
                     help="flat no-slip walls in these directions, e.g. 0 1 1 (not the headline workload)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
@@ -308,6 +310,8 @@ def main():
     if args.kt > 0.0:
         lat.noise_init(0)
         lat.noise_present_set(1)
+    if args.le:
+        lat.le_commit(args.le, 0.01)
 
     if world > 1:
         uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
@@ -457,6 +461,7 @@ def main():
                 "hydro_write": bool(args.hydro_write), "overlap": bool(args.overlap), "direct_halo": bool(args.direct), "p2p_halo": bool(args.p2p and (world > 1 or args.loopback)), "loopback": bool(args.loopback),
                 "gradient_points": args.gradient if ndist == 2 else None,
                 "walls": args.walls,
+                "lees_edwards_planes": args.le or None,
                 "isothermal_fluctuations_kt": args.kt if args.kt > 0.0 else None,
                 "l2": "lattice %.2f GB per GPU >> 126 MB L2 (no flush needed)" % (2 * lattice_bytes / 1e9),
             },

@@ -163,6 +163,26 @@ int  b200lb_wall_bbl(b200lb_t * h);                                    /* wall_b
 int  b200lb_wall_momentum(b200lb_t * h, double f[3]);                  /* wall_momentum src/wall.c:1299 */
 int  b200lb_wall_momentum_add(b200lb_t * h, const double f[3]);        /* wall_momentum_add src/wall.c:1279 */
 
+/* Lees-Edwards sliding periodic boundaries for the distributions ("N_LE_plane",
+ * "LE_plane_vel", "LE_oscillation_period", "LE_time_offset": lees_edw_options_t,
+ * src/lees_edwards_options.h:25-34; lees_edw_create src/leesedwards.c:80).
+ * nplanes_total planes normal to x, uniformly spaced, velocity jump uy along y;
+ * oscillatory != 0: uy cos(2 pi (t - nt0)/period). b200lb_le_apply replaces
+ * lb_le_apply_boundary_conditions (src/model_le.c:57): called between lb_collide and
+ * lb_halo (src/ludwig.c:810) with t = the physics time (the step number), it reprojects
+ * and displaces the populations about to cross a plane -- on the device, where the
+ * reference copies the whole lattice to the host and back. Refused, as the checks of
+ * src/leesedwards.c:416-456 do: planes that do not divide the system or the ranks in x,
+ * a plane within a halo width of a rank boundary; and a decomposition in y (the
+ * reference's message-passing variant, src/model_le.c:399) which is not on this path.
+ * b200lb_step advances its own step counter (b200lb_le_time_set, 0 at le_commit) and
+ * applies the planes after every collision, as the time loop of src/ludwig.c does. */
+int  b200lb_le_commit(b200lb_t * h, int nplanes_total, double uy, int oscillatory,
+                      int period, int nt0);
+int  b200lb_le_apply(b200lb_t * h, double t);                          /* lb_le_apply_boundary_conditions src/model_le.c:57 */
+int  b200lb_le_plane_location(const b200lb_t * h, int np);             /* lees_edw_plane_location src/leesedwards.c:599 */
+int  b200lb_le_time_set(b200lb_t * h, int nstep);                      /* physics_control_time: steps taken so far */
+
 /* Isothermal fluctuations ("isothermal_fluctuations on", src/collision_rt.c:55):
  * every site owns a KISS99 generator seeded from its global position, so results do
  * not depend on the decomposition (noise_create + noise_init, src/noise.c:56,136;

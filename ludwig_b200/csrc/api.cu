@@ -113,6 +113,13 @@ struct b200lb_s {
   bool prop_wall;            // ... and that propagation is the pending / running one
   double * fnet_dev;         // [3] momentum handed to the walls since the last wall_momentum
   double fnet_host[3];       // running total on the host (wall_momentum_add and read-outs)
+  // Lees-Edwards planes (lees_edw_t, src/leesedwards.c)
+  int le_nplanes;            // total over the system; 0 = none
+  int le_nlocal;             // per rank
+  double le_uy;
+  int le_osc, le_period, le_nt0;
+  long le_step;              // physics time step counter of b200lb_step
+  double * le_buf;           // crossing populations of the plane sites
   double * noise;            // [2][nsd] per-site generator state (noise_init), or null
   bool noise_on;             // noise_present_set(NOISE_RHO)
   double nv_diag, nv_off, nv_bulk, nv_ghost[B200LB_MAXNOISE];
@@ -487,7 +494,7 @@ extern "C" int b200lb_destroy(b200lb_t * h) {
     cudaEventDestroy(h->ev_x[i]);
   }
   cudaFree(h->rho); cudaFree(h->u); cudaFree(h->force);
-  cudaFree(h->phi); cudaFree(h->grad); cudaFree(h->delsq); cudaFree(h->noise); cudaFree(h->fnet_dev);
+  cudaFree(h->phi); cudaFree(h->grad); cudaFree(h->delsq); cudaFree(h->noise); cudaFree(h->fnet_dev); cudaFree(h->le_buf);
   cudaFree(h->partial); cudaFree(h->diag); cudaFree(h->stats_dev); cudaFreeHost(h->stats_host);
   cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
   cudaStreamDestroy(h->s_main);
@@ -713,7 +720,9 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
   }
   int lo[7][3], hi[7][3];
   bool iswall[7] = {false, false, false, false, false, false, false};
-  const bool push = collide && h->p2p_ready && h->opt_p2p;
+  // Lees-Edwards planes rewrite post-collision populations (also on the y and z faces
+  // of the rank) after this sweep: nothing is pushed to the neighbours ahead of that
+  const bool push = collide && h->p2p_ready && h->opt_p2p && h->le_nplanes == 0;
   const bool walls = pull && h->prop_wall && h->wall_on;
   if (walls && a.binary) return fail("walls with the binary fluid need the solid gradient stencils: not on this path");
   const int nbox = walls ? wall_boxes(h, a.P, lo, hi, iswall) : (push ? 1 : split_boxes(h, lo, hi));
@@ -945,6 +954,122 @@ extern "C" int b200lb_wall_momentum(b200lb_t * h, double f[3]) {
 extern "C" int b200lb_wall_momentum_add(b200lb_t * h, const double f[3]) {
   if (!h || !f) return fail("null argument");
   for (int a = 0; a < 3; a++) h->fnet_host[a] += f[a];
+  return 0;
+}
+
+// ---------------------------------------------------------------------------
+// Lees-Edwards planes (src/leesedwards.c, src/model_le.c)
+// ---------------------------------------------------------------------------
+
+static int le_location(const b200lb_s * h, int np) {
+  // src/leesedwards.c:599-617 with the uniform decomposition's offset
+  const int ntotal = h->desc.cartsz[0]*h->desc.nlocal[0];
+  const double dx_sep = 1.0*ntotal/h->le_nplanes;
+  const double dx_min = 0.5*dx_sep;
+  const int offset = h->desc.cartcoords[0]*h->desc.nlocal[0];
+  return (int) (dx_min + (np + h->desc.cartcoords[0]*h->le_nlocal)*dx_sep - offset);
+}
+
+extern "C" int b200lb_le_commit(b200lb_t * h, int nplanes, double uy, int oscillatory,
+				int period, int nt0) {
+  if (!h) return fail("null handle");
+  if (nplanes < 0) return fail("N_LE_plane must not be negative");
+  if (h->prop_pending) { if (materialise(h)) return -1; }
+  h->le_nplanes = 0; h->le_nlocal = 0; h->le_step = 0;
+  if (nplanes == 0) return 0;
+  const int ntotal = h->desc.cartsz[0]*h->desc.nlocal[0];
+  if (ntotal % nplanes) return fail("Number of planes must divide system size");
+  if (nplanes % h->desc.cartsz[0]) return fail("Must have a uniform number of planes per process");
+  if (oscillatory && period <= 0) return fail("Oscillatory shear must have period > 0");
+  if (!h->desc.periodic[0] || !h->desc.periodic[1])
+    return fail("Lees-Edwards planes need periodic x and y");
+  if (h->desc.cartsz[1] > 1)
+    return fail("Lees-Edwards planes with a decomposition in y (src/model_le.c:399) are not on this path");
+  if (nplanes/h->desc.cartsz[0] > B200LB_LE_MAXPLANE)
+    return fail("more than %d Lees-Edwards planes per rank", B200LB_LE_MAXPLANE);
+  h->le_nplanes = nplanes; h->le_nlocal = nplanes/h->desc.cartsz[0];
+  h->le_uy = uy; h->le_osc = (oscillatory != 0); h->le_period = period; h->le_nt0 = nt0;
+  for (int np = 0; np < h->le_nlocal; np++) {
+    const int ic = le_location(h, np);
+    if (ic <= h->desc.nhalo || ic > h->desc.nlocal[0] - h->desc.nhalo) {
+      h->le_nplanes = 0; h->le_nlocal = 0;
+      return fail("Wall at domain boundary");        // sic, src/leesedwards.c:443
+    }
+  }
+  // crossing populations: those with c_x = +1 below each plane, -1 above it
+  int nprop = 0;
+  for (int p = 1; p < h->ops->nvel; p++) nprop += (h->ops->cv[p][0] == 1);
+  const size_t nbuf = (size_t) 2*h->le_nlocal*h->desc.ndist*nprop*h->desc.nlocal[1]*h->desc.nlocal[2];
+  if (h->le_buf) { CU(cudaFree(h->le_buf)); h->le_buf = nullptr; }
+  CU(cudaMalloc(&h->le_buf, nbuf*sizeof(double)));
+  return 0;
+}
+
+extern "C" int b200lb_le_plane_location(const b200lb_t * h, int np) {
+  if (!h || h->le_nlocal == 0 || np < 0 || np >= h->le_nlocal) { fail("no such Lees-Edwards plane"); return -1; }
+  return le_location(h, np);
+}
+
+extern "C" int b200lb_le_time_set(b200lb_t * h, int nstep) {
+  if (!h) return fail("null handle");
+  h->le_step = nstep;
+  return 0;
+}
+
+extern "C" int b200lb_le_apply(b200lb_t * h, double t) {
+  if (!h) return fail("null handle");
+  if (h->le_nlocal == 0) return 0;                 // lees_edw_nplane_local(le) == 0
+  if (h->prop_pending) return fail("lb_le_apply_boundary_conditions: called after lb_propagation (it belongs between lb_collide and lb_halo)");
+  if (ensure_hydro(h)) return -1;                  // rho, u of the collision, before its populations change
+  if (join_comm(h)) return -1;
+  // velocity jump and displacement now: src/leesedwards.c:572-587, 633-655
+  const double tle = ((t < 0.0) ? 0.0 : t) - 1.0*h->le_nt0;
+  double uy_now = h->le_uy, dy_now = tle*h->le_uy;
+  if (h->le_osc) {
+    const double omega = 2.0*4.0*atan(1.0)/h->le_period;
+    uy_now = h->le_uy*cos(omega*(t - 1.0*h->le_nt0));
+    dy_now = h->le_uy*sin(omega*tle)/omega;
+  }
+  LeTab T;
+  memset(&T, 0, sizeof(T));
+  T.L = h->L;
+  T.nvel = h->ops->nvel; T.ndist = h->desc.ndist;
+  for (int p = 0; p < T.nvel; p++) {
+    for (int a = 0; a < 3; a++) T.pcv[p][a] = (signed char) h->ops->cv[p][a];
+    T.wv[p] = h->ops->wv[p];
+    if (p > 0 && h->ops->cv[p][0] == 1) T.nprop++;
+  }
+  for (int d = 0; d < 3; d++) {
+    if (h->ops->dax[d] == 0) T.dx = d;
+    if (h->ops->dax[d] == 1) T.dy = d;
+  }
+  T.da = (T.dx == 0) ? 1 : 0;
+  T.db = (T.dx == 2) ? 1 : 2;
+  const int ny = h->desc.nlocal[1];
+  T.nside = 2*h->le_nlocal;
+  for (int np = 0; np < h->le_nlocal; np++) {
+    for (int side = 0; side < 2; side++) {
+      const int k = 2*np + side;
+      T.ic[k] = le_location(h, np) + side - 1;     // 0-based interior coordinate
+      T.cx[k] = (side == 0) ? +1 : -1;
+      T.duy[k] = (side == 0) ? -1.0*uy_now : uy_now;
+      const double dy = fmod((side == 0) ? dy_now : -dy_now, 1.0*ny);
+      const int jdy = (int) floor(dy);
+      T.jdy[k] = jdy;
+      T.fr[k] = dy - jdy;
+    }
+  }
+  dim3 block(128, 1, 1);
+  dim3 grid((h->L.n[T.db] + 127)/128, h->L.n[T.da], T.nside);
+  le_reproject_kernel<<<grid, block, 0, h->s_main>>>(T, h->lat[h->cur], h->le_buf);
+  CU(cudaGetLastError());
+  le_interp_kernel<<<grid, block, 0, h->s_main>>>(T, h->le_buf, h->lat[h->cur]);
+  CU(cudaGetLastError());
+  h->launches += 2;
+  // the boundary slabs changed after the sweep recorded them: a halo exchange waits for this
+  h->bnd_valid = false;
+  h->pushed_valid = false;
+  h->halo_deferred = false;
   return 0;
 }
 
@@ -1402,6 +1527,8 @@ extern "C" int b200lb_hydro_correct_momentum(b200lb_t * h) {
 extern "C" int b200lb_step(b200lb_t * h, int nsteps) {
   if (!h) return fail("null handle");
   const double zero[3] = {0.0, 0.0, 0.0};
+  if (h->le_nlocal && h->desc.ndist == 2)
+    return fail("time loop: the order parameter and its gradient across Lees-Edwards planes (src/field.c, src/gradient_3d_7pt_fluid.c) are not on this path");
   for (int n = 0; n < nsteps; n++) {
     if (b200lb_hydro_f_zero(h, zero)) return -1;
     if (h->desc.ndist == 2) {
@@ -1411,8 +1538,10 @@ extern "C" int b200lb_step(b200lb_t * h, int nsteps) {
       else if (b200lb_grad7(h)) return -1;
     }
     if (b200lb_hydro_u_zero(h, zero)) return -1;
+    h->le_step++;                                   // physics_control_next_step, src/ludwig.c:552
     if (b200lb_collide(h)) return -1;
     if (h->prop_pending) return fail("internal: propagation pending after collide");
+    if (h->le_nlocal) { if (b200lb_le_apply(h, 1.0*h->le_step)) return -1; }   // src/ludwig.c:810
     if (lattice_halo(h, h->opt_halo)) return -1;
     if (h->wall_on) { if (b200lb_wall_bbl(h)) return -1; }      // src/ludwig.c:837-842
     if (b200lb_propagate(h)) return -1;

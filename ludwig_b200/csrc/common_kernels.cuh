@@ -413,6 +413,111 @@ wall_fnet_kernel(const WallTab W, const double * __restrict__ f, double * __rest
   }
 }
 
+// ---------------------------------------------------------------------------
+// Lees-Edwards planes: lb_le_apply_boundary_conditions (src/model_le.c:57-390), which
+// the reference runs on the HOST between two full-lattice copies every step. Here two
+// small kernels touch only the two x-planes next to each Lees-Edwards plane:
+//   le_reproject_kernel   the plane-crossing populations of a site, corrected for the
+//                         velocity jump through the equilibrium projection of the change
+//                         in momentum and stress (src/model_le.c:113-208), go to a buffer;
+//   le_interp_kernel      they come back displaced along y by the distance the plane has
+//                         slid, linearly interpolated (src/model_le.c:220-390).
+// One thread per (plane side, site of the x-plane).
+// ---------------------------------------------------------------------------
+
+#define B200LB_LE_MAXPLANE 32
+
+struct LeTab {
+  Layout L;
+  int nvel, ndist;
+  signed char pcv[27][3];         // physical components of c_p
+  double wv[27];
+  int dx, dy;                     // device axes of physical x and y
+  int da, db;                     // the two device axes spanning an x-plane, db fastest
+  int nside;                      // 2 x local planes
+  int ic[2*B200LB_LE_MAXPLANE];   // interior (0-based) device coordinate along dx of each plane side
+  int cx[2*B200LB_LE_MAXPLANE];   // +1 below a plane, -1 above it: which populations cross
+  double duy[2*B200LB_LE_MAXPLANE];
+  int jdy[2*B200LB_LE_MAXPLANE];  // integer part of the displacement
+  double fr[2*B200LB_LE_MAXPLANE];
+  int nprop;                      // populations with c_x = +1 (= those with -1)
+};
+
+__device__ __forceinline__ i64 le_site(const LeTab & T, int side, int ia, int ib) {
+  const Layout & L = T.L;
+  int c[3];
+  c[T.dx] = T.ic[side] + L.h[T.dx];
+  c[T.da] = ia + L.h[T.da];
+  c[T.db] = ib + L.h[T.db];
+  return (i64) c[0]*L.s0 + (i64) c[1]*L.s1 + L.z0 + c[2];
+}
+
+__global__ void __launch_bounds__(128)
+le_reproject_kernel(const LeTab T, const double * __restrict__ f, double * __restrict__ tmp) {
+  const Layout & L = T.L;
+  const int ib = blockIdx.x*blockDim.x + threadIdx.x;
+  const int ia = blockIdx.y;
+  const int side = blockIdx.z;
+  if (ib >= L.n[T.db] || ia >= L.n[T.da]) return;
+  const i64 site = le_site(T, side, ia, ib);
+  const i64 nps = (i64) L.n[T.da]*L.n[T.db];
+  const i64 ps = (i64) ia*L.n[T.db] + ib;
+  const double cs2 = 1.0/3.0, rcs2 = 3.0;
+  const double du[3] = {0.0, T.duy[side], 0.0};
+  for (int n = 0; n < T.ndist; n++) {
+    const double * fs = f + (i64) n*T.nvel*L.nsd + site;
+    double rho = 0.0, g[3] = {0.0, 0.0, 0.0};
+    for (int p = 0; p < T.nvel; p++) {
+      const double fp = fs[(i64) p*L.nsd];
+      rho += fp;
+      for (int a = 0; a < 3; a++) g[a] += T.pcv[p][a]*fp;
+    }
+    double ds[3][3];
+    for (int a = 0; a < 3; a++)
+      for (int b = 0; b < 3; b++) ds[a][b] = g[a]*du[b] + du[a]*g[b] + rho*du[a]*du[b];
+    int k = 0;
+    for (int p = 1; p < T.nvel; p++) {
+      if (T.pcv[p][0] != T.cx[side]) continue;
+      const double udotc = du[1]*T.pcv[p][1];
+      double sdotq = 0.0;
+      for (int a = 0; a < 3; a++)
+	for (int b = 0; b < 3; b++)
+	  sdotq += ds[a][b]*(T.pcv[p][a]*T.pcv[p][b] - ((a == b) ? cs2 : 0.0));
+      const double fnew = fs[(i64) p*L.nsd] + T.wv[p]*(rho*udotc*rcs2 + 0.5*sdotq*rcs2*rcs2);
+      tmp[(((i64) side*T.ndist + n)*T.nprop + k)*nps + ps] = fnew;
+      k++;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(128)
+le_interp_kernel(const LeTab T, const double * __restrict__ tmp, double * __restrict__ f) {
+  const Layout & L = T.L;
+  const int ib = blockIdx.x*blockDim.x + threadIdx.x;
+  const int ia = blockIdx.y;
+  const int side = blockIdx.z;
+  if (ib >= L.n[T.db] || ia >= L.n[T.da]) return;
+  const i64 site = le_site(T, side, ia, ib);
+  const i64 nps = (i64) L.n[T.da]*L.n[T.db];
+  // this site's 0-based y coordinate and the two it interpolates between
+  const int ny = L.n[T.dy];
+  const int jc = (T.dy == T.da) ? ia : ib;
+  const int j1 = ((jc + T.jdy[side]) % ny + 2*ny) % ny;
+  const int j2 = (j1 + 1) % ny;
+  const i64 ps1 = (T.dy == T.da) ? (i64) j1*L.n[T.db] + ib : (i64) ia*L.n[T.db] + j1;
+  const i64 ps2 = (T.dy == T.da) ? (i64) j2*L.n[T.db] + ib : (i64) ia*L.n[T.db] + j2;
+  const double fr = T.fr[side];
+  for (int n = 0; n < T.ndist; n++) {
+    int k = 0;
+    for (int p = 1; p < T.nvel; p++) {
+      if (T.pcv[p][0] != T.cx[side]) continue;
+      const double * t0 = tmp + (((i64) side*T.ndist + n)*T.nprop + k)*nps;
+      f[(i64)(n*T.nvel + p)*L.nsd + site] = (1.0 - fr)*t0[ps1] + fr*t0[ps2];
+      k++;
+    }
+  }
+}
+
 // sum, sum of squares, min, max of one field component over interior sites
 __global__ void __launch_bounds__(256)
 field_stats_kernel(const Layout L, const double * __restrict__ data, double * __restrict__ partial) {

@@ -118,6 +118,45 @@ int lb_collide(lb_t * lb, hydro_t * hydro, map_t * map, noise_t * noise, fe_t * 
   return 0;
 }
 
+/* physics time, as far as the hot path reads it */
+
+int physics_control_next_step(physics_t * phys) { phys->t_current += 1; return 0; }
+int physics_control_time(physics_t * phys, double * t) { *t = 1.0*phys->t_current; return 0; }
+
+/* lees_edw_t: plane positions, reprojection and displacement live in the library */
+
+int lees_edw_create(lb_t * lb, const lees_edw_options_t * opts, lees_edw_t ** ple) {
+  lees_edw_t * le = (lees_edw_t *) calloc(1, sizeof(lees_edw_t));
+  if (le == NULL) return -1;
+  le->lb = lb;
+  if (opts) le->opts = *opts;
+  if (b200lb_le_commit(lb->target, le->opts.nplanes, le->opts.uy,
+		       le->opts.type == LE_SHEAR_TYPE_OSCILLATORY, le->opts.period, le->opts.nt0)) {
+    free(le);
+    return host_fail("b200lb_le_commit");
+  }
+  le->nplanelocal = le->opts.nplanes/lb->cs->mpi_cartsz[0];
+  *ple = le;
+  return 0;
+}
+
+int lees_edw_free(lees_edw_t * le) { free(le); return 0; }
+int lees_edw_nplane_total(lees_edw_t * le) { return le->opts.nplanes; }
+int lees_edw_nplane_local(lees_edw_t * le) { return le->nplanelocal; }
+int lees_edw_plane_location(lees_edw_t * le, int plane) {
+  return b200lb_le_plane_location(le->lb->target, plane);
+}
+
+/* The reference copies the lattice to the host, works there and copies it back
+ * (src/model_le.c:70-83); here the planes are handled where the lattice is. */
+int lb_le_apply_boundary_conditions(lb_t * lb, lees_edw_t * le) {
+  double t = 0.0;
+  if (lees_edw_nplane_local(le) == 0) return 0;
+  physics_control_time(lb->phys, &t);
+  TRY(b200lb_le_apply(lb->target, t));
+  return 0;
+}
+
 /* wall_t: links, map and the momentum tally live in the library */
 
 int wall_create(lb_t * lb, wall_t ** pwall) {

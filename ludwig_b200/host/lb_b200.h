@@ -53,7 +53,10 @@ typedef struct physics_s {
   double fbody[3];
   double mobility;
   double kt;                       /* physics_kt: isothermal fluctuations */
+  int t_current;                   /* physics_control_timestep (src/physics.c) */
 } physics_t;
+int physics_control_next_step(physics_t * phys);                   /* src/physics.h:34 */
+int physics_control_time(physics_t * phys, double * t);            /* src/physics.h:54 */
 
 typedef struct lb_data_options_s {
   int ndim;
@@ -141,6 +144,23 @@ int wall_set_wall_distributions(wall_t * wall);                    /* src/wall.c
 int wall_bbl(wall_t * wall);                                       /* src/wall.c:960 */
 int wall_momentum(wall_t * wall, double f[3]);                     /* src/wall.c:1299 */
 int wall_momentum_add(wall_t * wall, const double f[3]);           /* src/wall.c:1279 */
+
+/* lees_edw_t (src/leesedwards.c): the planes live in the library; the host side keeps the options */
+typedef enum lees_edw_enum {LE_SHEAR_TYPE_INVALID, LE_SHEAR_TYPE_STEADY, LE_SHEAR_TYPE_OSCILLATORY} lees_edw_enum_t;
+typedef struct lees_edw_options_s {                                /* src/lees_edwards_options.h:25-34 */
+  int nplanes;
+  lees_edw_enum_t type;
+  int period;
+  int nt0;
+  double uy;
+} lees_edw_options_t;
+typedef struct lees_edw_s { lees_edw_options_t opts; int nplanelocal; lb_t * lb; } lees_edw_t;
+int lees_edw_create(lb_t * lb, const lees_edw_options_t * opts, lees_edw_t ** le);   /* src/leesedwards.c:80 */
+int lees_edw_free(lees_edw_t * le);
+int lees_edw_nplane_total(lees_edw_t * le);
+int lees_edw_nplane_local(lees_edw_t * le);
+int lees_edw_plane_location(lees_edw_t * le, int plane);           /* src/leesedwards.c:599 */
+int lb_le_apply_boundary_conditions(lb_t * lb, lees_edw_t * le);   /* src/model_le.c:57 */
 
 int noise_create(lb_t * lb, noise_t ** noise);                      /* src/noise.c:56 */
 int noise_free(noise_t * noise);

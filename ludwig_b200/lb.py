@@ -35,6 +35,7 @@ ABI_SYMBOLS = [
     "b200lb_noise_init", "b200lb_noise_present_set", "b200lb_noise_state_upload",
     "b200lb_noise_state_download",
     "b200lb_wall_commit", "b200lb_wall_slip_set", "b200lb_wall_bbl", "b200lb_wall_momentum", "b200lb_wall_momentum_add",
+    "b200lb_le_commit", "b200lb_le_apply", "b200lb_le_plane_location", "b200lb_le_time_set",
     "b200lb_field_stats", "b200lb_io_record_doubles", "b200lb_io_pack", "b200lb_io_unpack",
     "b200lb_step", "b200lb_stats", "b200lb_step_diag", "b200lb_sync", "b200lb_nccl_unique_id",
     "b200lb_comm_init", "b200lb_p2p_export", "b200lb_p2p_import", "b200lb_timer_start", "b200lb_timer_stop",
@@ -115,6 +116,10 @@ def load():
     L.b200lb_wall_bbl.argtypes = [vp]
     L.b200lb_wall_momentum.argtypes = [vp, vp]
     L.b200lb_wall_momentum_add.argtypes = [vp, vp]
+    L.b200lb_le_commit.argtypes = [vp, ctypes.c_int, ctypes.c_double, ctypes.c_int, ctypes.c_int, ctypes.c_int]
+    L.b200lb_le_apply.argtypes = [vp, ctypes.c_double]
+    L.b200lb_le_plane_location.argtypes = [vp, ctypes.c_int]
+    L.b200lb_le_time_set.argtypes = [vp, ctypes.c_int]
     L.b200lb_field_stats.argtypes = [vp, ctypes.c_int, vp]
     L.b200lb_io_record_doubles.argtypes = [vp]
     L.b200lb_io_record_doubles.restype = ctypes.c_long
@@ -326,6 +331,27 @@ class Lattice:
         out = (ctypes.c_double * 3)()
         self._ck(self.L.b200lb_wall_momentum(self.h, out))
         return np.array(out[:])
+
+    # -- Lees-Edwards planes (lees_edw_create src/leesedwards.c:80,
+    #    lb_le_apply_boundary_conditions src/model_le.c:57) --------------------------
+
+    def le_commit(self, nplanes, uy, oscillatory=False, period=0, nt0=0):
+        """lees_edw_options_t {nplanes, type, period, nt0, uy} (src/lees_edwards_options.h)."""
+        self._ck(self.L.b200lb_le_commit(self.h, int(nplanes), float(uy), int(bool(oscillatory)),
+                                         int(period), int(nt0)))
+
+    def le_apply_boundary_conditions(self, t):
+        """Between collide() and halo(), t = physics time (the step number)."""
+        self._ck(self.L.b200lb_le_apply(self.h, float(t)))
+
+    def le_plane_location(self, n):
+        ic = self.L.b200lb_le_plane_location(self.h, int(n))
+        if ic < 0:
+            raise RuntimeError(self.L.b200lb_last_error().decode())
+        return ic
+
+    def le_time_set(self, nstep):
+        self._ck(self.L.b200lb_le_time_set(self.h, int(nstep)))
 
     # -- statistics and file records without the full-field D2H ---------------------
     def field_stats(self, field):

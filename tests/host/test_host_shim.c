@@ -355,6 +355,89 @@ static void test_walls(int nsteps) {
   lb_free(lb);
 }
 
+/* Lees-Edwards planes through the reference's call order (src/ludwig.c:552, 800-845) */
+static void test_lees_edwards(int nsteps, int oscillatory) {
+  cs_t cs;
+  physics_t phys = {1.0, 0.1666, 0.1666, {0.0, 0.0, 0.0}, 0.0, 0.0};
+  lb_data_options_t opts = lb_data_options_default();
+  lb_t * lb = NULL; hydro_t * hydro = NULL; lees_edw_t * le = NULL;
+  lees_edw_options_t leopts = {2, LE_SHEAR_TYPE_STEADY, 0, 0, 0.0375};
+  orc_model_t model; orc_box_t box; orc_param_t prm; orc_le_t ole;
+  const int nl[3] = {12, 10, 7};
+  const double zero[3] = {0.0, 0.0, 0.0};
+  unsigned long seed = 20101208;
+
+  if (oscillatory) { leopts.type = LE_SHEAR_TYPE_OSCILLATORY; leopts.period = 17; leopts.nt0 = 2; }
+  cs_serial(&cs, nl[0], nl[1], nl[2]);
+  OK(lb_data_create(&cs, &phys, &opts, &lb));
+  OK(hydro_create(lb, &hydro));
+  OK(lees_edw_create(lb, &leopts, &le));
+  CHECK(lees_edw_nplane_local(le) == 2, "planes per rank");
+  CHECK(lees_edw_plane_location(le, 0) == 3 && lees_edw_plane_location(le, 1) == 9, "plane location");
+
+  orc_model_init(lb->nvel, &model);
+  orc_box_init(nl, &box);
+  memset(&prm, 0, sizeof(prm));
+  prm.rho0 = phys.rho0; prm.eta_shear = phys.eta_shear; prm.eta_bulk = phys.eta_bulk;
+  memset(&ole, 0, sizeof(ole));
+  ole.nplanes = leopts.nplanes; ole.uy = leopts.uy; ole.oscillatory = oscillatory;
+  ole.period = leopts.period; ole.nt0 = leopts.nt0;
+
+  size_t nf = (size_t) lb->nsite*lb->nvel;
+  double * f = (double *) calloc(nf, sizeof(double));
+  double * fprime = (double *) calloc(nf, sizeof(double));
+  double * rho = (double *) calloc(lb->nsite, sizeof(double));
+  double * u = (double *) calloc(3*(size_t) lb->nsite, sizeof(double));
+  double * force = (double *) calloc(3*(size_t) lb->nsite, sizeof(double));
+  for (int ic = 1; ic <= nl[0]; ic++) for (int jc = 1; jc <= nl[1]; jc++) for (int kc = 1; kc <= nl[2]; kc++) {
+    long index = cs_index(&cs, ic, jc, kc);
+    double r = 1.0 + 0.02*urand(&seed);
+    double uu[3] = {0.02*urand(&seed), 0.02*urand(&seed), 0.02*urand(&seed)};
+    orc_equilib_set(&model, 1, f, index, r, uu);
+  }
+  memcpy(lb->f, f, nf*sizeof(double));
+  OK(lb_memcpy(lb, tdpMemcpyHostToDevice));
+
+  for (int n = 0; n < nsteps; n++) {
+    OK(physics_control_next_step(&phys));
+    OK(hydro_f_zero(hydro, zero));
+    OK(hydro_u_zero(hydro, zero));
+    OK(lb_collide(lb, hydro, NULL, NULL, NULL, NULL));
+    OK(lb_le_apply_boundary_conditions(lb, le));
+    OK(lb_halo(lb));
+    OK(lb_propagation(lb));
+  }
+  OK(lb_memcpy(lb, tdpMemcpyDeviceToHost));
+  OK(hydro_memcpy(hydro, tdpMemcpyDeviceToHost));
+
+  orc_le_attach(&ole);
+  orc_step(&model, &box, &prm, 1, nsteps, f, fprime, rho, u, force, NULL, NULL, NULL);
+  orc_le_attach(NULL);
+
+  double emax = 0.0, fmax = 0.0, umax = 0.0;
+  for (int ic = 1; ic <= nl[0]; ic++) for (int jc = 1; jc <= nl[1]; jc++) for (int kc = 1; kc <= nl[2]; kc++) {
+    long index = cs_index(&cs, ic, jc, kc);
+    for (int p = 0; p < lb->nvel; p++) {
+      long i = LB_ADDR(lb->nsite, 1, lb->nvel, index, 0, p);
+      if (fabs(lb->f[i] - f[i]) > emax) emax = fabs(lb->f[i] - f[i]);
+      if (fabs(f[i]) > fmax) fmax = fabs(f[i]);
+    }
+    for (int a = 0; a < 3; a++) {
+      double d = fabs(hydro->u.data[3*index + a] - u[3*index + a]);
+      if (d > umax) umax = d;
+    }
+  }
+  printf("test_lees_edwards (%s): %d steps, max|df|/max|f| = %.3e, max|du| = %.3e\n",
+	 oscillatory ? "oscillatory" : "steady", nsteps, emax/fmax, umax);
+  CHECK(emax/fmax < 1.0e-12, "Lees-Edwards: time loop vs oracle");
+  CHECK(umax < 1.0e-12, "Lees-Edwards: hydro u vs oracle");
+
+  free(f); free(fprime); free(rho); free(u); free(force);
+  lees_edw_free(le);
+  hydro_free(hydro);
+  lb_free(lb);
+}
+
 int main(void) {
   test_prop(1, LB_HALO_TARGET);
   test_prop(2, LB_HALO_TARGET);
@@ -365,6 +448,8 @@ int main(void) {
   test_loop(1, 7, 7, 2.13333e-05);          /* isothermal fluctuations */
   test_loop(2, 7, 7, 2.13333e-05);
   test_walls(9);
+  test_lees_edwards(9, 0);
+  test_lees_edwards(23, 1);
   if (nfail) { printf("%d check(s) FAILED\n", nfail); return 1; }
   printf("host shim: all passed\n");
   return 0;

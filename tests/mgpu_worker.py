@@ -43,6 +43,7 @@ def main():
     ap.add_argument("--kt", type=float, default=0.0, help="> 0: isothermal fluctuations")
     ap.add_argument("--gradient", type=int, default=7)
     ap.add_argument("--walls", type=int, nargs=3, default=[0, 0, 0])
+    ap.add_argument("--le", type=int, default=0, help="Lees-Edwards planes per rank in x (uy 0.03)")
     args = ap.parse_args()
 
     rank = int(os.environ["RANK"])
@@ -56,6 +57,11 @@ def main():
     grid = {1: (1, 1, 1), 2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}[world]
     if ndim == 2 and grid[2] != 1:
         grid = (grid[0] * grid[2], grid[1], 1)
+    if args.le:
+        # no decomposition in y with planes (src/model_le.c:399 is not on this path)
+        grid = {1: (1, 1, 1), 2: (2, 1, 1), 4: (2, 1, 2), 8: (4, 1, 2)}[world]
+        if ndim == 2:
+            grid = (world, 1, 1)
     local = tuple(args.lsize)
     ntotal = tuple(local[a] * grid[a] for a in range(3))
     walls = tuple(args.walls)
@@ -93,6 +99,8 @@ def main():
         if args.kt > 0.0:
             l.noise_init(0)
             l.noise_present_set(1)
+        if args.le:
+            l.le_commit(args.le*grid[0], 0.03)
 
     configure(lat)
 
@@ -180,8 +188,11 @@ def main():
             orc.noise_attach(orc.noise_init(0), args.kt)
         if any(walls):
             orc.wall_attach(orc.wall(walls))
+        if args.le:
+            orc.le_attach(orc.le(args.le*grid[0], 0.03))
         orc.gradient_select(args.gradient)
         orc.step(prm, args.steps, f, fp, rho, u, frc, phi, grad, delsq)
+        orc.le_attach(None)
         orc.noise_attach(None, 0.0)
         orc.wall_attach(None)
         orc.gradient_select(7)
@@ -189,10 +200,10 @@ def main():
         err = float(np.max(np.abs(glob - fo)) / np.max(np.abs(fo)))
         mass = abs(float(sums[0].item()) - s1[0])
         halo_ok = bool(flags.item() > 0.5)
-        print("mgpu world=%d grid=%s nvel=%d ndist=%d halo=%s fused=%d overlap=%d direct=%d p2p=%d kt=%g grad=%d walls=%s: halo_bit_exact=%s "
+        print("mgpu world=%d grid=%s nvel=%d ndist=%d halo=%s fused=%d overlap=%d direct=%d p2p=%d kt=%g grad=%d walls=%s le=%d: halo_bit_exact=%s "
               "decomposed==single=%s err_vs_oracle=%.2e mass_diff=%.2e"
               % (world, grid, nvel, ndist, args.halo, args.fused, args.overlap, args.direct, args.p2p, args.kt, args.gradient,
-                 walls, halo_ok, same, err, mass),
+                 walls, args.le, halo_ok, same, err, mass),
               flush=True)
         if not (halo_ok and same and err < 1e-12 and mass < 1e-9 * n):
             rc = 1

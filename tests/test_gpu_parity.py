@@ -1183,3 +1183,115 @@ def test_wall_slip_vs_oracle(nvel, nlocal, walls, sbot, stop, fused):
     assert np.allclose(lat.wall_momentum(), np.array(w.fnet[:]), rtol=1e-10, atol=1e-13)
     assert abs(fd[m].sum() - f0[m].sum()) < 1e-9
     lat.close()
+
+
+LE_CASES = [
+    (19, (12, 10, 8), 1, dict(nplanes=2, uy=0.0375)),
+    (19, (8, 6, 70), 1, dict(nplanes=1, uy=-0.05)),
+    (19, (16, 9, 5), 2, dict(nplanes=4, uy=0.0131)),
+    (27, (8, 7, 6), 1, dict(nplanes=2, uy=0.021, oscillatory=1, period=17, nt0=2)),
+    (9, (16, 12, 1), 1, dict(nplanes=2, uy=0.0375)),
+    (9, (8, 131, 1), 1, dict(nplanes=1, uy=0.011, oscillatory=1, period=40, nt0=0)),
+]
+
+
+@pytest.mark.parametrize("nvel,nlocal,ndist,le", LE_CASES)
+def test_lees_edwards_apply_vs_oracle(nvel, nlocal, ndist, le):
+    """lb_le_apply_boundary_conditions (src/model_le.c:57) on the device: the reprojection
+    agrees within the collision bar; at times where the planes have slid a whole number of
+    sites the displacement is a pure copy."""
+    lat, orc = mk(nvel, nlocal, ndist)
+    f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal, ndist=ndist, ndim=orc.ndim)
+    m = orc.interior_mask()
+    ole = orc.le(**le)
+    lat.le_commit(le["nplanes"], le["uy"], le.get("oscillatory", 0), le.get("period", 0), le.get("nt0", 0))
+    for k in range(le["nplanes"]):
+        assert lat.le_plane_location(k) == orc.le_plane_location(ole, k)
+    for t in (0, 1, 7, 20, 133, 1000, 12345):
+        f = f0.copy()
+        orc.le_apply(ole, t, f)
+        lat.lb_memcpy_h2d(f0)
+        lat.le_apply_boundary_conditions(t)
+        fd = lat.lb_memcpy_d2h()
+        assert relerr(fd[m], f[m]) < 1e-14, t
+        # only the plane sites change, and there only the crossing populations
+        changed = np.argwhere(np.abs(fd - f0).reshape(orc.nall + (ndist, nvel)) > 0)
+        planes = {orc.le_plane_location(ole, k) + s for k in range(le["nplanes"]) for s in (0, 1)}
+        assert set(changed[:, 0]) <= planes
+    assert relerr(fd[m], f0[m]) > 1e-5
+    lat.close()
+
+
+@pytest.mark.parametrize("nvel,nlocal,ndist,le", [c for c in LE_CASES if c[2] == 1])
+@pytest.mark.parametrize("fused", [1, 0])
+@pytest.mark.parametrize("loopback", [0, 1])
+def test_lees_edwards_time_loop_vs_oracle(nvel, nlocal, ndist, le, fused, loopback):
+    """The time loop with planes (src/ludwig.c:552, 800-845), from step 5 on; with the
+    lazy hydro path and through the multi-rank exchange machinery as well."""
+    import ludwig_b200 as lb
+    from oracle import pyoracle
+    lat, orc = mk(nvel, nlocal)
+    f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal, ndim=orc.ndim)
+    m = orc.interior_mask()
+    n = orc.nsite
+    kw = dict(eta_shear=0.1, eta_bulk=0.07)
+    prm = pyoracle.make_param(**kw)
+    ole = orc.le(t_current=5, **le)
+    nsteps = 13
+    f, fp = f0.copy(), np.zeros_like(f0)
+    rho, u, frc = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
+    orc.le_attach(ole)
+    try:
+        orc.step(prm, nsteps, f, fp, rho, u, frc)
+    finally:
+        orc.le_attach(None)
+    lat.set_param(**kw)
+    lat.set_option("fused", fused)
+    lat.set_option("loopback", loopback)
+    if loopback:
+        lat.set_option("hydro_write", 0)
+    lat.le_commit(le["nplanes"], le["uy"], le.get("oscillatory", 0), le.get("period", 0), le.get("nt0", 0))
+    lat.le_time_set(5)
+    lat.lb_memcpy_h2d(f0)
+    lat.step(nsteps)
+    fd = lat.lb_memcpy_d2h()
+    assert relerr(fd[m], f[m]) < TOL
+    assert np.max(np.abs(lat.field_d2h(lb.FIELD_U)[m] - u[m])) < TOL
+    assert np.max(np.abs(lat.field_d2h(lb.FIELD_RHO)[m] - rho[m])) < TOL
+    assert abs(fd[m].sum() - f0[m].sum()) < 1e-9
+    # the same through the separate calls, in the reference's order
+    lat.lb_memcpy_h2d(f0)
+    for s in range(nsteps):
+        lat.hydro_f_zero()
+        lat.hydro_u_zero()
+        lat.lb_collide()
+        lat.le_apply_boundary_conditions(6 + s)
+        lat.lb_halo()
+        lat.lb_propagation()
+    assert np.array_equal(lat.lb_memcpy_d2h()[m], fd[m])
+    lat.close()
+
+
+def test_lees_edwards_refusals():
+    """The checks of lees_edw_init / lees_edw_checks (src/leesedwards.c:232-456)."""
+    import ludwig_b200 as lb
+    lat = lb.Lattice(19, (12, 8, 4))
+    for bad in (dict(nplanes=5, uy=0.01), dict(nplanes=6, uy=0.01),       # 12 % 5; plane at x = 1
+                dict(nplanes=2, uy=0.01, oscillatory=1, period=0)):
+        with pytest.raises(RuntimeError):
+            lat.le_commit(**bad)
+    lat.le_commit(2, 0.01)
+    lat.lb_collide()
+    lat.lb_propagation()
+    with pytest.raises(RuntimeError):
+        lat.le_apply_boundary_conditions(1)       # after the propagation: wrong place
+    lat.close()
+    lat = lb.Lattice(19, (12, 8, 4), ndist=2)
+    lat.le_commit(2, 0.01)
+    with pytest.raises(RuntimeError):
+        lat.step(1)                               # binary time loop needs the sheared phi halo
+    lat.close()
+    lat = lb.Lattice(19, (12, 8, 4), periodic=(1, 0, 1))
+    with pytest.raises(RuntimeError):
+        lat.le_commit(2, 0.01)
+    lat.close()

@@ -46,6 +46,10 @@ def launch(n, extra, port):
     ["--nvel", "19", "--halo", "reduced", "--walls", "1", "1", "0"],
     ["--nvel", "19", "--halo", "reduced", "--walls", "1", "0", "1", "--p2p", "0", "--kt", "1e-4"],
     ["--nvel", "9", "--halo", "reduced", "--lsize", "16", "12", "1", "--walls", "1", "1", "0"],
+    # Lees-Edwards planes inside every rank's block (x and z decomposed)
+    ["--nvel", "19", "--halo", "reduced", "--le", "1", "--steps", "9"],
+    ["--nvel", "19", "--halo", "full", "--le", "1", "--p2p", "0", "--overlap", "0", "--steps", "9"],
+    ["--nvel", "9", "--halo", "reduced", "--lsize", "16", "12", "1", "--le", "2", "--steps", "9"],
 ])
 def test_decomposed_equals_single(n, extra):
     if ngpu() < n:
