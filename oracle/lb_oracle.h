@@ -155,6 +155,37 @@ int orc_le_plane_location(const orc_box_t * box, const orc_le_t * le, int np);
 int orc_le_apply(const orc_model_t * model, const orc_box_t * box, int ndist,
 		 const orc_le_t * le, double t, double * f);
 
+/* Finite-difference order parameter (lb_oracle_ch.c; "free_energy symmetric":
+ * src/phi_force.c, src/phi_force_stress.c, src/phi_grad_mu.c, src/advection.c,
+ * src/phi_cahn_hilliard.c). While attached, orc_step with ndist = 1 runs field_halo,
+ * the gradient, phi_force_calculation and phi_cahn_hilliard ahead of the collision;
+ * A, B, kappa and the mobility come from orc_param_t. */
+enum { ORC_FORCE_NONE = 1, ORC_FORCE_STRESS_DIVERGENCE = 2, ORC_FORCE_PHI_GRADMU = 3 };  /* fe_force_method_enum_t */
+typedef struct orc_ch_s {
+  int order;              /* fd_advection_scheme_order: 1, 2 or 3 */
+  int method;             /* fe_force_method */
+  double grad_mu[3];      /* external chemical potential gradient ("grad_mu") */
+} orc_ch_t;
+int orc_ch_attach(orc_ch_t * ch);
+orc_ch_t * orc_ch_attached(void);
+int orc_ch_stress(const orc_box_t * box, const orc_param_t * prm,
+		  const double * phi, const double * grad, const double * delsq,
+		  double * pth);
+int orc_ch_force_divergence(const orc_box_t * box, const double * pth, double * force);
+int orc_ch_force_gradmu(const orc_box_t * box, const orc_param_t * prm,
+			const double grad_mu[3], const double * phi,
+			const double * delsq, double * force);
+int orc_ch_advection(const orc_box_t * box, int order, const double * u,
+		     const double * phi, double * flux);
+int orc_ch_flux_mu(const orc_box_t * box, const orc_param_t * prm,
+		   const double grad_mu[3], const double * phi, const double * delsq,
+		   double * flux);
+int orc_ch_update(const orc_box_t * box, const double * flux, double * phi);
+int orc_phi_force(const orc_box_t * box, const orc_param_t * prm, const orc_ch_t * ch,
+		  const double * phi, double * grad, double * delsq, double * force);
+int orc_cahn_hilliard(const orc_box_t * box, const orc_param_t * prm, const orc_ch_t * ch,
+		      double * phi, double * delsq, double * u);
+
 int orc_fill(const orc_box_t * box, int nf, const double * v, double * data);
 
 /* stats[0..7] = sum rho, sum rho^2 (about mean is left to caller), min, max,

@@ -404,6 +404,15 @@ int orc_step(const orc_model_t * model, const orc_box_t * box,
       if (grad_select_npt == 27) orc_grad_27pt(box, phi, grad, delsq);
       else orc_grad_7pt(box, phi, grad, delsq);
     }
+    if (ndist == 1 && orc_ch_attached()) {
+      /* finite-difference order parameter ("free_energy symmetric"), src/ludwig.c:558-575,727-768 */
+      const orc_ch_t * ch = orc_ch_attached();
+      orc_halo_periodic(box, 1, phi);
+      if (grad_select_npt == 27) orc_grad_27pt(box, phi, grad, delsq);
+      else orc_grad_7pt(box, phi, grad, delsq);
+      if (orc_phi_force(box, prm, ch, phi, grad, delsq, force)) return -1;
+      if (orc_cahn_hilliard(box, prm, ch, phi, delsq, u)) return -1;
+    }
     orc_fill(box, 3, zero, u);
     if (ndist == 1) {
       if (orc_collide_mrt(model, box, prm, 1, a, force, rho, u)) return -1;

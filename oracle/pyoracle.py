@@ -74,6 +74,17 @@ class LeesEdwards(ctypes.Structure):
     ]
 
 
+FORCE_NONE, FORCE_STRESS_DIVERGENCE, FORCE_PHI_GRADMU = 1, 2, 3
+
+
+class CahnHilliard(ctypes.Structure):
+    _fields_ = [
+        ("order", ctypes.c_int),
+        ("method", ctypes.c_int),
+        ("grad_mu", ctypes.c_double * 3),
+    ]
+
+
 class Box(ctypes.Structure):
     _fields_ = [
         ("nlocal", ctypes.c_int * 3),
@@ -237,6 +248,42 @@ class Oracle:
 
     def le_plane_location(self, le, n):
         return self.L.orc_le_plane_location(ctypes.byref(self.box), ctypes.byref(le), int(n))
+
+    # -- finite-difference order parameter (oracle/lb_oracle_ch.c) -------------------
+    def ch(self, order=1, method=FORCE_STRESS_DIVERGENCE, grad_mu=(0.0, 0.0, 0.0)):
+        c = CahnHilliard()
+        c.order, c.method = order, method
+        c.grad_mu[:] = grad_mu
+        return c
+
+    def ch_attach(self, ch):
+        """orc_step (ndist = 1) runs the "free_energy symmetric" route while attached."""
+        self._ch = ch
+        self.L.orc_ch_attach(None if ch is None else ctypes.byref(ch))
+
+    def ch_stress(self, prm, phi, grad, delsq):
+        pth = np.zeros((self.nsite, 3, 3))
+        self.L.orc_ch_stress(ctypes.byref(self.box), ctypes.byref(prm), _p(phi), _p(grad),
+                             _p(delsq), _p(pth))
+        return pth
+
+    def ch_advection(self, order, u, phi):
+        flux = np.zeros((4, self.nsite))
+        rc = self.L.orc_ch_advection(ctypes.byref(self.box), int(order), _p(u), _p(phi), _p(flux))
+        assert rc == 0
+        return flux
+
+    def phi_force(self, prm, ch, phi, grad, delsq, force):
+        """phi_force_calculation: adds to force; fills the halos of grad and delsq."""
+        rc = self.L.orc_phi_force(ctypes.byref(self.box), ctypes.byref(prm), ctypes.byref(ch),
+                                  _p(phi), _p(grad), _p(delsq), _p(force))
+        assert rc == 0
+
+    def cahn_hilliard(self, prm, ch, phi, delsq, u):
+        """phi_cahn_hilliard: u halo, fluxes, forward step of phi (interior)."""
+        rc = self.L.orc_cahn_hilliard(ctypes.byref(self.box), ctypes.byref(prm), ctypes.byref(ch),
+                                      _p(phi), _p(delsq), _p(u))
+        assert rc == 0
 
     # -- flat walls (oracle/lb_oracle_wall.c) ---------------------------------------
     def wall(self, isboundary, ubot=(0.0, 0.0, 0.0), utop=(0.0, 0.0, 0.0), sbot=None, stop=None,

@@ -57,8 +57,12 @@ def _lib(nvel):
 class Ref:
     """Reference objects on a periodic one-rank box ntotal, halo width 1."""
 
-    def __init__(self, nvel, ntotal, ndist=1, halo=HALO_TARGET, periodic=(1, 1, 1), le=None):
-        """le = dict(nplanes, uy, oscillatory=0, period=0, nt0=0): Lees-Edwards planes."""
+    def __init__(self, nvel, ntotal, ndist=1, halo=HALO_TARGET, periodic=(1, 1, 1), le=None,
+                 fd=None):
+        """le = dict(nplanes, uy, oscillatory=0, period=0, nt0=0): Lees-Edwards planes.
+        fd = dict(order=1, method=2): "free_energy symmetric" -- halo width 2, phi a
+        finite-difference field (phi_cahn_hilliard + phi_force_calculation);
+        method = fe_force_method_enum_t (1 none, 2 stress divergence, 3 phi grad mu)."""
         self.L = _lib(nvel)
         assert self.L.refdrv_nvel() == nvel
         self.nvel, self.ndist = nvel, ndist
@@ -69,7 +73,10 @@ class Ref:
             self.L.refdrv_le_options(int(le["nplanes"]), float(le["uy"]),
                                      int(le.get("oscillatory", 0)), int(le.get("period", 0)),
                                      int(le.get("nt0", 0)))
+        if fd:
+            self.L.refdrv_fd_options(int(fd.get("order", 1)), int(fd.get("method", 2)))
         self.L.refdrv_init((ctypes.c_int * 3)(*ntotal), ndist, halo)
+        self.nhalo = self.L.refdrv_nhalo()
         nall = (ctypes.c_int * 3)()
         self.L.refdrv_nall(nall)
         self.nall = tuple(nall)
@@ -222,6 +229,32 @@ class Ref:
         self.L.refdrv_noise_reap_n(int(index), int(nmax),
                                    out.ctypes.data_as(c_double_p))
         return out
+
+    def interior(self, a):
+        """a[nsite, ...] of the reference -> the interior block [nx, ny, nz, ...]."""
+        h = self.nhalo
+        b = a.reshape(self.nall + a.shape[1:])
+        return b[h:-h, h:-h, h:-h]
+
+    def inner(self, a, width=1):
+        """the interior plus `width` halo layers: what a halo-1 array holds."""
+        h = self.nhalo - width
+        b = a.reshape(self.nall + a.shape[1:])
+        if h == 0:
+            return b
+        return b[h:-h, h:-h, h:-h]
+
+    def phi_force(self):
+        assert self.L.refdrv_phi_force() == 0
+
+    def cahn_hilliard(self):
+        assert self.L.refdrv_cahn_hilliard() == 0
+
+    def u_halo(self):
+        self.L.refdrv_u_halo()
+
+    def grad_mu(self, gm):
+        self.L.refdrv_grad_mu((ctypes.c_double * 3)(*gm))
 
     def grad_select(self, npt):
         assert self.L.refdrv_grad_select(int(npt)) == 0

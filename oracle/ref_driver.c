@@ -20,9 +20,14 @@
  *    wall_create / wall_commit / wall_bbl / wall_momentum  src/wall.c:59,168,960,1299
  *    lees_edw_create, lb_le_apply_boundary_conditions  src/leesedwards.c:80, src/model_le.c:57
  *    hydro_f_zero/u_zero  src/hydro.c:306,279
+ *    phi_force_calculation  src/phi_force.c:74 (pth_stress_compute src/phi_force_stress.c:171,
+ *                           pth_force_fluid_driver src/phi_force_colloid.c:280, phi_grad_mu_fluid
+ *                           src/phi_grad_mu.c:52)
+ *    phi_cahn_hilliard      src/phi_cahn_hilliard.c:206 (hydro_u_halo, advection_x, phi_ch_flux_mu1 ...)
  *
  *  The step sequence of refdrv_step() follows src/ludwig.c:530-862 for the
- *  "free_energy none" and "symmetric_lb" cases (periodic, no colloids).
+ *  "free_energy none", "symmetric_lb" and (refdrv_fd_options) the finite-difference
+ *  "symmetric" cases (periodic, no colloids).
  *
  *  Nothing under ludwig_b200/ links or loads this file.
  *
@@ -53,6 +58,11 @@
 #include "wall.h"
 #include "model_le.h"
 #include "lees_edwards_options.h"
+#include "phi_cahn_hilliard.h"
+#include "phi_force.h"
+#include "phi_force_stress.h"
+#include "advection.h"
+#include "fe_force_method.h"
 
 typedef struct refdrv_s {
   pe_t * pe;
@@ -67,6 +77,9 @@ typedef struct refdrv_s {
   field_grad_t * phi_grad;
   fe_symm_t * fe;
   wall_t * wall;
+  pth_t * pth;
+  phi_ch_t * pch;
+  int nhalo;
   int nplanes;
   int ndist;
   int mpi_up;
@@ -101,9 +114,23 @@ int refdrv_periodicity(const int periodic[3]) {
   return 0;
 }
 
+/* "free_energy symmetric" for the NEXT refdrv_init (src/ludwig.c:1159-1250): nhalo = 2,
+ * the order parameter is a finite-difference field updated by phi_cahn_hilliard, the
+ * fluid feels it through phi_force_calculation. order = "fd_advection_scheme_order",
+ * method = "fe_force_method" (fe_force_method_enum_t). */
+static int next_fd = 0, next_fd_order = 1, next_fd_method = FE_FORCE_METHOD_STRESS_DIVERGENCE;
+int refdrv_fd_options(int order, int method) {
+  next_fd = 1;
+  next_fd_order = order;
+  next_fd_method = method;
+  return 0;
+}
+int refdrv_nhalo(void) { return rd.nhalo; }
+
 int refdrv_init(const int ntotal[3], int ndist, int halo_scheme) {
 
-  int nhalo = 1;
+  int nhalo = next_fd ? 2 : 1;
+  rd.nhalo = nhalo;
 
   if (rd.mpi_up == 0) {
     MPI_Init(NULL, NULL);
@@ -148,12 +175,23 @@ int refdrv_init(const int ntotal[3], int ndist, int halo_scheme) {
   noise_create(rd.pe, rd.cs, &rd.noise);
   noise_init(rd.noise, 0);
 
-  if (ndist == 2) {
+  if (ndist == 2 || next_fd) {
     field_options_t fopts = field_options_ndata_nhalo(1, nhalo);
     field_create(rd.pe, rd.cs, rd.le, "phi", &fopts, &rd.phi);
     field_grad_create(rd.pe, rd.phi, 2, &rd.phi_grad);
     field_grad_set(rd.phi_grad, grad_3d_7pt_fluid_d2, NULL);
     fe_symm_create(rd.pe, rd.cs, rd.phi, rd.phi_grad, &rd.fe);
+  }
+  if (next_fd) {
+    phi_ch_info_t ch_options = {0};
+    assert(ndist == 1);
+    phi_ch_create(rd.pe, rd.cs, rd.le, &ch_options, &rd.pch);
+    pth_create(rd.pe, rd.cs, next_fd_method, &rd.pth);
+    advection_order_set(next_fd_order);
+    /* phi_force_calculation asks the wall object whether there are walls
+     * (wall_create leaves wall->param zeroed: none) */
+    wall_create(rd.pe, rd.cs, rd.map, rd.lb, &rd.wall);
+    next_fd = 0;
   }
 
   return 0;
@@ -161,6 +199,8 @@ int refdrv_init(const int ntotal[3], int ndist, int halo_scheme) {
 
 int refdrv_finish(void) {
 
+  if (rd.pch) phi_ch_free(rd.pch);
+  if (rd.pth) pth_free(rd.pth);
   if (rd.wall) wall_free(rd.wall);
   if (rd.fe) fe_symm_free(rd.fe);
   if (rd.phi_grad) field_grad_free(rd.phi_grad);
@@ -346,6 +386,20 @@ int refdrv_noise_reap_n(int index, int nmax, double * reap) {
   return noise_reap_n(rd.noise, index, nmax, reap);
 }
 
+/* The finite-difference order parameter: stage by stage (src/ludwig.c:727-768) */
+int refdrv_phi_force(void) {
+  return phi_force_calculation(rd.pe, rd.cs, rd.le, rd.wall, rd.pth, (fe_t *) rd.fe,
+			       rd.map, rd.phi, rd.hydro);
+}
+int refdrv_cahn_hilliard(void) {
+  return phi_cahn_hilliard(rd.pch, (fe_t *) rd.fe, rd.phi, rd.hydro, rd.map, NULL);
+}
+int refdrv_u_halo(void) { return hydro_u_halo(rd.hydro); }
+int refdrv_grad_mu(const double gm[3]) {       /* "grad_mu" key, src/physics_rt.c */
+  double g[3] = {gm[0], gm[1], gm[2]};
+  return physics_grad_mu_set(rd.phys, g);
+}
+
 int refdrv_hydro_f_zero(const double f[3]) { return hydro_f_zero(rd.hydro, f); }
 int refdrv_hydro_u_zero(const double u[3]) { return hydro_u_zero(rd.hydro, u); }
 
@@ -368,11 +422,18 @@ double refdrv_step(int nsteps) {
       field_halo(rd.phi);
       field_grad_compute(rd.phi_grad);
     }
+    if (rd.pch) {                       /* src/ludwig.c:558-575, 727-768 */
+      field_halo(rd.phi);
+      field_grad_compute(rd.phi_grad);
+      phi_force_calculation(rd.pe, rd.cs, rd.le, rd.wall, rd.pth, (fe_t *) rd.fe,
+			    rd.map, rd.phi, rd.hydro);
+      phi_cahn_hilliard(rd.pch, (fe_t *) rd.fe, rd.phi, rd.hydro, rd.map, NULL);
+    }
     hydro_u_zero(rd.hydro, zero);
     lb_collide(rd.lb, rd.hydro, rd.map, rd.noise, (fe_t *) rd.fe, NULL);
     if (rd.nplanes > 0) lb_le_apply_boundary_conditions(rd.lb, rd.le);   /* src/ludwig.c:810 */
     lb_halo(rd.lb);
-    if (rd.wall) {                      /* src/ludwig.c:837-842 */
+    if (rd.wall && wall_present(rd.wall)) {                      /* src/ludwig.c:837-842 */
       wall_set_wall_distributions(rd.wall);
       wall_bbl(rd.wall);
     }

@@ -475,3 +475,116 @@ def test_lees_edwards(nvel, nlocal, ndist, le):
             # not (out of scope), so only the density distribution's first step agrees
             pass
         assert abs(f[m][:, 0].sum() - f0[m][:, 0].sum()) < 1e-10
+
+
+# ---------------------------------------------------------------------------
+# "free_energy symmetric": the order parameter as a finite-difference field
+# (phi_force_calculation + phi_cahn_hilliard), reference built with nhalo = 2
+# ---------------------------------------------------------------------------
+
+def fd_fields(nlocal):
+    """phi, u on the halo-1 box (interior values; halos are filled by the codes)."""
+    ids = lbinit.global_ids(nlocal).reshape(-1)
+    phi = 0.4 * lbinit.uniform(ids, 50)
+    u = np.zeros((ids.size, 3))
+    for a in range(3):
+        u[:, a] = 0.02 * lbinit.uniform(ids, 2 + a)
+    return phi, u
+
+
+FD_CASES = [
+    (1, pyoracle.FORCE_STRESS_DIVERGENCE, 27, (0.0, 0.0, 0.0)),
+    (2, pyoracle.FORCE_STRESS_DIVERGENCE, 7, (0.0, 0.0, 0.0)),
+    (3, pyoracle.FORCE_STRESS_DIVERGENCE, 27, (0.0, 0.0, 0.0)),
+    (1, pyoracle.FORCE_PHI_GRADMU, 27, (1e-5, 2e-5, 3e-5)),
+    (3, pyoracle.FORCE_PHI_GRADMU, 7, (-2e-5, 0.0, 1e-5)),
+    (2, pyoracle.FORCE_NONE, 7, (0.0, 0.0, 0.0)),
+]
+
+
+@pytest.mark.parametrize("order,method,npt,gmu", FD_CASES)
+def test_cahn_hilliard_stages(order, method, npt, gmu):
+    nvel, nlocal = 19, (10, 8, 6)
+    need_ref(nvel)
+    A, B, K, M, eta = -0.00625, 0.00625, 0.004, 1.25, 0.00625
+    orc = pyoracle.Oracle(nvel, nlocal)
+    prm = pyoracle.make_param(eta_shear=eta, eta_bulk=eta, mobility=M, a=A, b=B, kappa=K)
+    ch = orc.ch(order, method, gmu)
+    phi, u = fd_fields(nlocal)
+    n = orc.nsite
+    with pyref.Ref(nvel, nlocal, fd=dict(order=order, method=method)) as ref:
+        assert ref.nhalo == 2
+        ref.physics(eta_shear=eta, eta_bulk=eta, mobility=M)
+        ref.fe_symm(A, B, K)
+        ref.grad_mu(gmu)
+        ref.grad_select(npt)
+        ref.inner(ref.phi())[...] = phi.reshape(orc.nall)
+        ref.inner(ref.u())[...] = u.reshape(orc.nall + (3,))
+        m = orc.interior_mask()
+
+        # field_halo + field_grad_compute (region nextra = 1 in the reference)
+        ref.phi_halo()
+        ref.grad_compute()
+        orc.halo(phi, 1)
+        grad, delsq = np.zeros((n, 3)), np.zeros(n)
+        (orc.grad_27pt if npt == 27 else orc.grad_7pt)(phi, grad, delsq)
+        assert np.array_equal(phi, ref.inner(ref.phi()).reshape(-1))
+
+        # phi_force_calculation
+        ref.hydro_f_zero()
+        ref.phi_force()
+        force = np.zeros((n, 3))
+        orc.phi_force(prm, ch, phi, grad, delsq, force)
+        if method != pyoracle.FORCE_NONE:
+            # the gradient one site into the halo is the gradient of the periodic image
+            assert np.array_equal(grad, ref.inner(ref.grad()).reshape(-1, 3))
+            assert np.array_equal(delsq, ref.inner(ref.delsq()).reshape(-1))
+            assert np.max(np.abs(force[m])) > 0.0
+        fr = ref.inner(ref.force()).reshape(-1, 3)
+        assert np.array_equal(force[m], fr[m])
+
+        # phi_cahn_hilliard
+        ref.cahn_hilliard()
+        phi0 = phi.copy()
+        orc.cahn_hilliard(prm, ch, phi, delsq, u)
+        pr = ref.inner(ref.phi()).reshape(-1)
+        assert np.max(np.abs(phi[m] - phi0[m])) > 1e-6
+        assert np.array_equal(phi[m], pr[m])
+        # conservation to round-off
+        assert abs(phi[m].sum() - phi0[m].sum()) < 1e-13 * m.sum()
+
+
+@pytest.mark.parametrize("order,method,npt,gmu", FD_CASES[:4])
+def test_cahn_hilliard_time_loop(order, method, npt, gmu):
+    nvel, nlocal, nsteps = 19, (8, 8, 8), 6
+    need_ref(nvel)
+    A, B, K, M, eta = -0.00625, 0.00625, 0.004, 1.25, 0.00625
+    orc = pyoracle.Oracle(nvel, nlocal)
+    prm = pyoracle.make_param(eta_shear=eta, eta_bulk=eta, mobility=M, a=A, b=B, kappa=K)
+    ch = orc.ch(order, method, gmu)
+    f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal)
+    phi, _ = fd_fields(nlocal)
+    n = orc.nsite
+    with pyref.Ref(nvel, nlocal, fd=dict(order=order, method=method)) as ref:
+        ref.physics(eta_shear=eta, eta_bulk=eta, mobility=M)
+        ref.fe_symm(A, B, K)
+        ref.grad_mu(gmu)
+        ref.grad_select(npt)
+        ref.inner(ref.f())[...] = f0.reshape(orc.nall + (1, nvel))
+        ref.inner(ref.phi())[...] = phi.reshape(orc.nall)
+        ref.step(nsteps)
+        f, fp = f0.copy(), np.zeros_like(f0)
+        rho, u, force = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
+        grad, delsq = np.zeros((n, 3)), np.zeros(n)
+        orc.gradient_select(npt)
+        orc.ch_attach(ch)
+        try:
+            orc.step(prm, nsteps, f, fp, rho, u, force, phi, grad, delsq)
+        finally:
+            orc.ch_attach(None)
+            orc.gradient_select(7)
+        m = orc.interior_mask()
+        fr = ref.inner(ref.f()).reshape(n, 1, nvel)
+        assert relerr(f[m], fr[m]) < 1e-12
+        assert relerr(phi[m], ref.inner(ref.phi()).reshape(-1)[m]) < 1e-13
+        assert relerr(u[m], ref.inner(ref.u()).reshape(-1, 3)[m]) < 1e-11
