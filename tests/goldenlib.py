@@ -58,3 +58,29 @@ def inputs_noise(tag):
                            ndim=ndim)
     force = lbinit.make_force(nlocal, ndim=ndim)
     return g, nvel, ndist, nlocal, f0, force
+
+
+# "free_energy symmetric" (tests/golden/make_golden_ch.py): nlocal, advection order,
+# fe_force_method (2 stress divergence, 3 phi grad mu), gradient stencil, external grad mu
+CH_PHYS = dict(a=-0.00625, b=0.00625, kappa=0.004, mobility=1.25, eta=0.00625)
+CH_CASES = {
+    "o1s27": ((8, 7, 6), 1, 2, 27, (0.0, 0.0, 0.0)),
+    "o2s7": ((8, 7, 6), 2, 2, 7, (0.0, 0.0, 0.0)),
+    "o3s27": ((8, 7, 6), 3, 2, 27, (0.0, 0.0, 0.0)),
+    "o1g27": ((6, 8, 7), 1, 3, 27, (1e-5, 2e-5, 3e-5)),
+    "o3g7": ((6, 8, 7), 3, 3, 7, (-2e-5, 0.0, 1e-5)),
+}
+
+
+def ch_fields(nlocal):
+    """phi [nsite], u [nsite,3] on the halo-1 box (seeded, decomposition independent)."""
+    ids = lbinit.global_ids(nlocal).reshape(-1)
+    phi = 0.4 * lbinit.uniform(ids, 50)
+    u = np.zeros((ids.size, 3))
+    for a in range(3):
+        u[:, a] = 0.02 * lbinit.uniform(ids, 2 + a)
+    return phi, u
+
+
+def load_ch():
+    return np.load(os.path.join(HERE, "golden", "ref_ch.npz"))

@@ -125,3 +125,24 @@ def spinodal_phi(nt, seed, phi0, amp):
     state = noise_state_interior(nt, seed)
     r = (1.0 / 4294967295.0) * kiss99(state).astype(np.float64)
     return (phi0 + amp * (r - 0.5)).reshape(nt)
+
+
+def drop_phi(nt, xi0, radius, phistar=1.0, centred=0):
+    """field_phi_init_drop (src/field_phi_init.c:38-82): phistar tanh((r - radius)/xi0)
+    about the centre of the system (Lmin = 1/2 left out unless centred)."""
+    ax = [np.arange(1, nt[a] + 1) - (centred*0.5 + 0.5*nt[a]) for a in range(3)]
+    x, y, z = np.meshgrid(*ax, indexing="ij")
+    r = np.sqrt(x*x + y*y + z*z)
+    return phistar*np.tanh((1.0/xi0)*(r - radius))
+
+
+def patches_phi(nt, seed, patch, volminus1):
+    """field_phi_init_spinodal_patches (src/field_phi_init.c:538-591): cubes of side
+    `patch` at +1 or, with probability volminus1, -1; one uniform from the generator of
+    the first site of each cube."""
+    state = noise_state_interior(nt, seed)
+    r = ((1.0/4294967295.0)*kiss99(state).astype(np.float64)).reshape(nt)
+    corner = r[::patch, ::patch, ::patch]
+    val = np.where(corner < volminus1, -1.0, 1.0)
+    phi = np.repeat(np.repeat(np.repeat(val, patch, 0), patch, 1), patch, 2)
+    return np.ascontiguousarray(phi[:nt[0], :nt[1], :nt[2]])

@@ -6,6 +6,7 @@ import pytest
 
 from oracle import pyoracle
 import goldenlib
+import lbinit
 from goldenlib import relerr
 
 
@@ -162,3 +163,42 @@ def test_fluctuations_golden(tag):
             assert relerr(f[m], g[tag + "_%s_step10_f" % name]) < 1e-12
     finally:
         orc.noise_attach(None, 0.0)
+
+
+@pytest.mark.parametrize("tag", sorted(goldenlib.CH_CASES))
+def test_cahn_hilliard_golden(tag):
+    """The finite-difference order parameter (oracle/lb_oracle_ch.c) against
+    reference-produced vectors (tests/golden/ref_ch.npz): force and updated phi bit for
+    bit, eight time steps to 1e-12."""
+    g = goldenlib.load_ch()
+    nlocal, order, method, npt, gmu = goldenlib.CH_CASES[tag]
+    P = goldenlib.CH_PHYS
+    orc = pyoracle.Oracle(19, nlocal)
+    prm = pyoracle.make_param(eta_shear=P["eta"], eta_bulk=P["eta"], mobility=P["mobility"],
+                              a=P["a"], b=P["b"], kappa=P["kappa"])
+    ch = orc.ch(order, method, gmu)
+    m = orc.interior_mask()
+    n = orc.nsite
+    phi, u = goldenlib.ch_fields(nlocal)
+    orc.halo(phi, 1)
+    grad, delsq, force = np.zeros((n, 3)), np.zeros(n), np.zeros((n, 3))
+    (orc.grad_27pt if npt == 27 else orc.grad_7pt)(phi, grad, delsq)
+    orc.phi_force(prm, ch, phi, grad, delsq, force)
+    assert np.array_equal(force[m], g[tag + "_force"])
+    orc.cahn_hilliard(prm, ch, phi, delsq, u)
+    assert np.array_equal(phi[m], g[tag + "_phi1"])
+
+    phi, _ = goldenlib.ch_fields(nlocal)
+    f = lbinit.make_state(orc.cv(), orc.wv(), nlocal)
+    fp = np.zeros_like(f)
+    rho, u, force = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
+    orc.gradient_select(npt)
+    orc.ch_attach(ch)
+    try:
+        orc.step(prm, 8, f, fp, rho, u, force, phi, grad, delsq)
+    finally:
+        orc.ch_attach(None)
+        orc.gradient_select(7)
+    assert goldenlib.relerr(f[m], g[tag + "_step8_f"]) < 1e-12
+    assert goldenlib.relerr(phi[m], g[tag + "_step8_phi"]) < 1e-13
+    assert goldenlib.relerr(u[m], g[tag + "_step8_u"]) < 1e-11

@@ -206,18 +206,67 @@ def check_binary(rec, nt, f_interior, grad_interior):
         assert abs(a - b) <= 1e-12, ("fed", mine, rec["fed"])
 
 
+def fd_route(rec):
+    """free_energy symmetric: phi is a finite-difference field (src/ludwig.c:1159-1250)."""
+    return rec["input"].get("free_energy") == "symmetric"
+
+
+def fd_options(inp):
+    """(advection order, fe_force_method, external grad mu)"""
+    method = {"stress_divergence": 2, "phi_gradmu": 3, "no_force": 1}[inp.get("fe_force_method", "stress_divergence")]
+    gmu = tuple(float(x) for x in inp.get("grad_mu", "0_0_0").split("_"))
+    return int(inp.get("fd_advection_scheme_order", 1)), method, gmu
+
+
+def initial_phi(inp, nt):
+    """phi_initialisation (src/field_phi_init_rt.c:40-160) on the interior, [nt]."""
+    key = inp.get("phi_initialisation", "spinodal")
+    seed = int(inp.get("random_seed", 13))
+    if key == "spinodal":
+        return lbinit.spinodal_phi(nt, seed, float(inp.get("phi0", 0.0)), float(inp.get("noise", 0.1)))
+    if key == "drop":
+        xi0 = math.sqrt(-2.0*float(inp["K"])/float(inp["A"]))      # fe_symm_interfacial_width
+        return lbinit.drop_phi(nt, xi0, float(inp.get("phi_init_drop_radius", 0.0)),
+                               float(inp.get("phi_init_drop_amplitude", 1.0)))
+    if key == "patches":
+        return lbinit.patches_phi(nt, seed, int(inp.get("phi_init_patch_size", 1)),
+                                  float(inp.get("phi_init_patch_vol", 0.5)))
+    raise ValueError(key)
+
+
+def check_fd(rec, nt, phi_interior, grad_interior):
+    """[phi] (cahn_hilliard_stats, src/cahn_hilliard_stats.c:80-112: compensated sum) and
+    [fed] lines for the finite-difference order parameter: phi after the last update,
+    the gradient the last time step computed (src/ludwig.c:2303-2306)."""
+    vol = float(np.prod(nt))
+    phi = phi_interior
+    tot = math.fsum(phi)
+    mean = tot/vol
+    var = math.fsum(phi*phi)/vol - mean*mean
+    mine = [printed("%14.7e", x) for x in (tot, mean, var, phi.min(), phi.max())]
+    for a, b in zip(mine, rec["phi"]):
+        assert abs(a - b) <= 1e-12, ("phi", mine, rec["phi"])
+    p = binary_params(rec["input"])
+    fed = (0.5*p["a"] + 0.25*p["b"]*phi*phi)*phi*phi \
+        + 0.5*p["kappa"]*(grad_interior*grad_interior).sum(-1)
+    mine = [printed("%17.10e", fed.sum()/vol), printed("%17.10e", fed.sum()/vol)]
+    for a, b in zip(mine, rec["fed"]):
+        assert abs(a - b) <= 1e-12, ("fed", mine, rec["fed"])
+
+
 def viscosities(inp):
     eta = float(inp["viscosity"])
     return eta, float(inp.get("viscosity_bulk", eta))
 
 
-LONG = {"pmpi08-spin-lb1"}      # minutes on the CPU oracle: opt in with B200LB_LONG=1
+LONG = {"pmpi08-spin-lb1", "pmpi08-spin-fd1"}      # 400 steps: the momentum line is accumulated round-off
+SLOW = {"pmpi08-spin-lb1"}      # minutes on the CPU oracle: opt in with B200LB_LONG=1 (fd1 takes half a minute)
 
 
 @pytest.mark.parametrize("case", CASES)
 def test_oracle_reproduces_reference_log(case):
     from oracle import pyoracle
-    if case in LONG and not os.environ.get("B200LB_LONG"):
+    if case in SLOW and not os.environ.get("B200LB_LONG"):
         pytest.skip("long case: set B200LB_LONG=1 (the CUDA path runs it under -m gpu)")
     rec = GOLD[case]
     nvel = rec["nvel"]
@@ -226,7 +275,7 @@ def test_oracle_reproduces_reference_log(case):
     eta, zeta = viscosities(rec["input"])
     ndist = f.shape[1]
     orc = pyoracle.Oracle(nvel, nt, ndist=ndist)
-    kw = binary_params(rec["input"]) if ndist == 2 else {}
+    kw = binary_params(rec["input"]) if (ndist == 2 or fd_route(rec)) else {}
     prm = pyoracle.make_param(eta_shear=eta, eta_bulk=zeta, ghost_off=int(ghost_off(rec)),
                               force=body_force(rec["input"]), **kw)
     wall = None
@@ -245,12 +294,16 @@ def test_oracle_reproduces_reference_log(case):
         orc.noise_attach(orc.noise_init(0), float(rec["input"]["temperature"]))
     orc.gradient_select(gradient_points(rec))
     orc.wall_attach(wall)
+    if fd_route(rec):
+        phi.reshape(orc.nall)[1:-1, 1:-1, 1:-1] = initial_phi(rec["input"], nt)
+        orc.ch_attach(orc.ch(*fd_options(rec["input"])))
     try:
         orc.step(prm, int(rec["input"]["N_cycles"]), f, fp, rho, u, frc, phi, grad, delsq)
     finally:
         orc.noise_attach(None, 0.0)
         orc.gradient_select(7)
         orc.wall_attach(None)
+        orc.ch_attach(None)
     m = orc.interior_mask()
     sums = orc.stats(f)
     if case in LONG:
@@ -259,6 +312,8 @@ def test_oracle_reproduces_reference_log(case):
     check(rec, nt, sums, u[m], gwall=None if wall is None else list(wall.fnet))
     if ndist == 2:
         check_binary(rec, nt, f[m], grad[m])
+    if fd_route(rec):
+        check_fd(rec, nt, phi[m], grad[m])
     if noisy(rec):
         check_equipartition(rec, f[m][:, 0], orc.cv())
 
