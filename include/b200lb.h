@@ -113,6 +113,8 @@ long b200lb_nsite(const b200lb_t * h);                          /* host nsite = 
  *                      and fill the grad/delsq arrays only when they are asked for
  *   "gradient"    7/27 which stencil b200lb_step uses for the order parameter
  *                      (fd_gradient_calculation 3d_7pt_fluid / 3d_27pt_fluid, src/gradient_rt.c:81-98)
+ *   "ch_fuse"     0/1  finite-difference order parameter: phi_force_calculation is
+ *                      evaluated by the pass of the phi_cahn_hilliard that follows it
  *   "loopback"    0/1  single rank: send periodic directions through the exchange
  *                      buffers with this GPU as its own neighbour (tests, profiling) */
 int  b200lb_set_option(b200lb_t * h, const char * name, long value);
@@ -183,6 +185,31 @@ int  b200lb_le_apply(b200lb_t * h, double t);                          /* lb_le_
 int  b200lb_le_plane_location(const b200lb_t * h, int np);             /* lees_edw_plane_location src/leesedwards.c:599 */
 int  b200lb_le_time_set(b200lb_t * h, int nstep);                      /* physics_control_time: steps taken so far */
 
+/* The order parameter as a finite-difference field ("free_energy symmetric",
+ * src/ludwig.c:1159-1250): ndist = 1, phi is a field_t that follows Cahn-Hilliard with the
+ * velocity of the previous collision, the fluid feels it as a body force. Per time step
+ * (src/ludwig.c:558-575, 727-768):
+ *   field_halo(phi); field_grad_compute; phi_force_calculation; phi_cahn_hilliard
+ * = b200lb_phi_halo; b200lb_grad7 | b200lb_grad27; b200lb_phi_force; b200lb_cahn_hilliard.
+ * The reference makes seven passes over the lattice for the last two (stress, its
+ * divergence, advective fluxes, diffusive fluxes twice, no-flux mask, update) and keeps
+ * a halo two sites wide for them; here they are ONE kernel reading phi, grad phi,
+ * delsq phi and u at a site and its six neighbours (option "ch_fuse" = 0: two
+ * launches). Free-energy parameters A, B, kappa and the mobility are those of
+ * b200lb_set_param. Results are bit-identical to the reference's.
+ * On this path: three dimensions, fully periodic, fluid only, no Lees-Edwards planes;
+ * advection orders 1-3 (3 only where every direction is periodic within the rank: it
+ * reads phi two sites away); force methods no_force, stress_divergence, phi_gradmu.
+ * Fields: B200LB_FIELD_PHI / _GRAD / _DELSQ move the order parameter and its gradient,
+ * index over the usual one-site halo box (the interior is what the reference's
+ * nhalo = 2 arrays hold inside their halo). */
+enum { B200LB_FORCE_NONE = 1, B200LB_FORCE_STRESS_DIVERGENCE = 2, B200LB_FORCE_PHI_GRADMU = 3 };  /* fe_force_method_enum_t src/fe_force_method.h:20-28 */
+int  b200lb_ch_create(b200lb_t * h, int advection_order, int force_method);   /* phi_ch_create src/phi_cahn_hilliard.c:121, pth_create src/phi_force_stress.c:41, advection_order_set src/advection.c:93 */
+int  b200lb_ch_grad_mu_set(b200lb_t * h, const double grad_mu[3]);            /* physics_grad_mu_set ("grad_mu") */
+int  b200lb_phi_force(b200lb_t * h);                                          /* phi_force_calculation src/phi_force.c:74 */
+int  b200lb_cahn_hilliard(b200lb_t * h);                                      /* phi_cahn_hilliard src/phi_cahn_hilliard.c:206 */
+int  b200lb_hydro_u_halo(b200lb_t * h);                                       /* hydro_u_halo src/hydro.c */
+
 /* Isothermal fluctuations ("isothermal_fluctuations on", src/collision_rt.c:55):
  * every site owns a KISS99 generator seeded from its global position, so results do
  * not depend on the decomposition (noise_create + noise_init, src/noise.c:56,136;
@@ -200,8 +227,8 @@ int  b200lb_noise_state_upload(b200lb_t * h, const unsigned int * state, int hos
 int  b200lb_noise_state_download(b200lb_t * h, unsigned int * state, int host_layout);       /* noise_memcpy D2H */
 
 /* nsteps iterations of the src/ludwig.c:530-862 loop restricted to the hot
- * path: f_zero; [phi_from_g; phi_halo; grad7 | grad27]; u_zero; collide; halo;
- * [wall_bbl]; propagate */
+ * path: f_zero; [phi_from_g; phi_halo; grad7 | grad27]; [after b200lb_ch_create: phi_halo;
+ * grad7 | grad27; phi_force; cahn_hilliard]; u_zero; collide; halo; [wall_bbl]; propagate */
 int  b200lb_step(b200lb_t * h, int nsteps);
 
 /* Conserved-quantity diagnostics over interior sites of this rank

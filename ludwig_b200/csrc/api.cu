@@ -17,6 +17,7 @@
 #include "../../include/b200lb.h"
 #include "common_kernels.cuh"
 #include "model_ops.cuh"
+#include "ch_kernels.cuh"
 
 // ---------------------------------------------------------------------------
 // errors
@@ -120,6 +121,15 @@ struct b200lb_s {
   int le_osc, le_period, le_nt0;
   long le_step;              // physics time step counter of b200lb_step
   double * le_buf;           // crossing populations of the plane sites
+  // the order parameter as a finite-difference field ("free_energy symmetric":
+  // phi_ch_t src/phi_cahn_hilliard.h:33, pth_t src/phi_force_stress.h)
+  bool ch_on;
+  int ch_order, ch_method;   // fd_advection_scheme_order, fe_force_method
+  double ch_gmu[3];          // physics_grad_mu: external chemical potential gradient
+  double * phi2;             // the buffer the next Cahn-Hilliard update writes
+  bool ch_force_pending;     // phi_force_calculation recorded; evaluated by the update's pass
+  bool ch_grad_valid;        // grad/delsq belong to the current phi
+  bool ch_halo_done;         // ... and their halos in decomposed directions are current
   double * noise;            // [2][nsd] per-site generator state (noise_init), or null
   bool noise_on;             // noise_present_set(NOISE_RHO)
   double nv_diag, nv_off, nv_bulk, nv_ghost[B200LB_MAXNOISE];
@@ -147,7 +157,7 @@ struct b200lb_s {
   bool ghost;
 
   // options
-  int opt_fused, opt_halo, opt_hydro_write, opt_vec, opt_block, opt_halo_lazy, opt_overlap, opt_direct, opt_diag, opt_loopback, opt_grad_lazy, opt_p2p, opt_gradient;
+  int opt_fused, opt_halo, opt_hydro_write, opt_vec, opt_block, opt_halo_lazy, opt_overlap, opt_direct, opt_diag, opt_loopback, opt_grad_lazy, opt_p2p, opt_gradient, opt_ch_fuse;
 
   cudaStream_t s_main, s_x[2];
   cudaStream_t s_comm;       // halo exchange of decomposed directions (overlaps the interior sweep)
@@ -465,6 +475,7 @@ static int create_impl(const b200lb_desc_t * desc, b200lb_s * h, const ModelOps 
   h->opt_grad_lazy = 1;
   h->opt_gradient = 7;
   h->opt_p2p = 1;
+  h->opt_ch_fuse = 1;
 
   b200lb_param_t p0;
   memset(&p0, 0, sizeof(p0));
@@ -494,6 +505,7 @@ extern "C" int b200lb_destroy(b200lb_t * h) {
     cudaEventDestroy(h->ev_x[i]);
   }
   cudaFree(h->rho); cudaFree(h->u); cudaFree(h->force);
+  cudaFree(h->phi2);
   cudaFree(h->phi); cudaFree(h->grad); cudaFree(h->delsq); cudaFree(h->noise); cudaFree(h->fnet_dev); cudaFree(h->le_buf);
   cudaFree(h->partial); cudaFree(h->diag); cudaFree(h->stats_dev); cudaFreeHost(h->stats_host);
   cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
@@ -509,6 +521,7 @@ extern "C" long b200lb_nsite(const b200lb_t * h) { return h ? h->nsite_host : 0;
 static int materialise(b200lb_s * h);
 static int join_comm(b200lb_s * h);
 static int flush_halo(b200lb_s * h);
+static int resolve_ch_force(b200lb_s * h);
 
 extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
   if (!h || !name) return fail("null argument");
@@ -527,6 +540,11 @@ extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
   if (!strcmp(name, "direct")) { h->opt_direct = (v != 0); return 0; }
   if (!strcmp(name, "diag")) { h->opt_diag = (v != 0); return 0; }
   if (!strcmp(name, "grad_lazy")) { h->opt_grad_lazy = (v != 0); return 0; }
+  if (!strcmp(name, "ch_fuse")) {
+    if (!v) { if (resolve_ch_force(h)) return -1; }
+    h->opt_ch_fuse = (v != 0);
+    return 0;
+  }
   if (!strcmp(name, "gradient")) {
     if (v != 7 && v != 27) return fail("gradient: 7 or 27 points");
     if (v == 27 && h->desc.ndim != 3) return fail("the 27-point gradient is three-dimensional");
@@ -571,6 +589,7 @@ extern "C" long b200lb_get_option(const b200lb_t * h, const char * name) {
   if (!strcmp(name, "diag")) return h->opt_diag;
   if (!strcmp(name, "grad_lazy")) return h->opt_grad_lazy;
   if (!strcmp(name, "gradient")) return h->opt_gradient;
+  if (!strcmp(name, "ch_fuse")) return h->opt_ch_fuse;
   if (!strcmp(name, "p2p")) return h->opt_p2p;
   if (!strcmp(name, "p2p_ready")) return h->p2p_ready;
   if (!strcmp(name, "loopback")) return h->opt_loopback;
@@ -586,6 +605,9 @@ extern "C" long b200lb_get_option(const b200lb_t * h, const char * name) {
 
 extern "C" int b200lb_set_param(b200lb_t * h, const b200lb_param_t * prm) {
   if (!h || !prm) return fail("null argument");
+  if (h->ch_force_pending && (prm->a != h->prm.a || prm->b != h->prm.b || prm->kappa != h->prm.kappa)) {
+    if (resolve_ch_force(h)) return -1;      // the recorded force belongs to the old free energy
+  }
   b200lb_param_t keep = h->prm;
   h->prm = *prm;
   if (derive_params(h)) { h->prm = keep; derive_params(h); return -1; }
@@ -800,6 +822,7 @@ static int materialise(b200lb_s * h) {
 
 extern "C" int b200lb_collide(b200lb_t * h) {
   if (!h) return fail("null handle");
+  if (resolve_ch_force(h)) return -1;     // phi_force_calculation without a Cahn-Hilliard update after it
   if (h->prop_pending) {
     // stream-then-collide in one pass over the lattice
     if (run_sweep(h, true, true, h->lat[h->cur], h->lat[1 - h->cur])) return -1;
@@ -974,6 +997,7 @@ extern "C" int b200lb_le_commit(b200lb_t * h, int nplanes, double uy, int oscill
 				int period, int nt0) {
   if (!h) return fail("null handle");
   if (nplanes < 0) return fail("N_LE_plane must not be negative");
+  if (nplanes > 0 && h->ch_on) return fail("Lees-Edwards planes for the finite-difference order parameter (src/phi_cahn_hilliard.c:618) are not on this path");
   if (h->prop_pending) { if (materialise(h)) return -1; }
   h->le_nplanes = 0; h->le_nlocal = 0; h->le_step = 0;
   if (nplanes == 0) return 0;
@@ -1389,6 +1413,7 @@ static int run_grad7(b200lb_s * h) {
   CU(cudaGetLastError());
   h->launches++;
   h->grad_state = 0;
+  h->ch_grad_valid = true; h->ch_halo_done = false;
   return 0;
 }
 
@@ -1404,6 +1429,7 @@ static int run_grad27(b200lb_s * h) {
   CU(cudaGetLastError());
   h->launches++;
   h->grad_state = 0;
+  h->ch_grad_valid = true; h->ch_halo_done = false;
   return 0;
 }
 
@@ -1431,7 +1457,7 @@ static int flush_phi_halo(b200lb_s * h) {
 
 extern "C" int b200lb_phi_from_g(b200lb_t * h) {
   if (!h) return fail("null handle");
-  if (!h->phi) return fail("no order parameter (ndist = 1)");
+  if (!h->phi || h->desc.ndist != 2) return fail("no order parameter distribution (ndist = 1)");
   if (join_comm(h)) return -1;
   const double * g = h->lat[h->cur] + (i64) h->desc.nvel*h->L.nsd;
   CU(h->ops->phi_from_g(h->L, h->selfper, g, h->phi, h->prop_pending, h->s_main));
@@ -1444,7 +1470,8 @@ extern "C" int b200lb_phi_from_g(b200lb_t * h) {
 extern "C" int b200lb_grad7(b200lb_t * h) {
   if (!h) return fail("null handle");
   if (!h->phi) return fail("no order parameter (ndist = 1)");
-  if (h->opt_grad_lazy) {
+  if (resolve_ch_force(h)) return -1;     // a recorded force wants the gradient being replaced
+  if (h->opt_grad_lazy && h->desc.ndist == 2) {
     // The only consumer on the path is the binary collision, which evaluates the same
     // 7-point stencil in registers; the arrays are filled when somebody asks for them.
     h->grad_state = 1;
@@ -1456,6 +1483,7 @@ extern "C" int b200lb_grad7(b200lb_t * h) {
 extern "C" int b200lb_grad27(b200lb_t * h) {
   if (!h) return fail("null handle");
   if (!h->phi) return fail("no order parameter (ndist = 1)");
+  if (resolve_ch_force(h)) return -1;
   // 40 B/site, against ~650 B/site of the binary collision that consumes it: the arrays
   // are always written (the collision reads them; no in-register variant).
   return run_grad27(h);
@@ -1476,6 +1504,7 @@ extern "C" int b200lb_hydro_f_zero(b200lb_t * h, const double f[3]) {
   if (h->hydro_stale && h->last_ffield) { if (ensure_hydro(h)) return -1; }
   for (int i = 0; i < 3; i++) h->fconst[i] = f ? f[i] : 0.0;
   h->force_uniform = true;
+  h->ch_force_pending = false;            // a recorded phi_force_calculation is wiped with the field
   return 0;
 }
 
@@ -1496,6 +1525,7 @@ extern "C" int b200lb_hydro_rho0(b200lb_t * h, double rho0) {
 
 extern "C" int b200lb_hydro_correct_momentum(b200lb_t * h) {
   if (!h) return fail("null handle");
+  if (resolve_ch_force(h)) return -1;
   if (h->hydro_stale && h->last_ffield) { if (ensure_hydro(h)) return -1; }
   if (need_planes(h, &h->force, 3)) return -1;
   if (h->force_uniform) {                 // make the constant field real first
@@ -1521,6 +1551,137 @@ extern "C" int b200lb_hydro_correct_momentum(b200lb_t * h) {
 }
 
 // ---------------------------------------------------------------------------
+// the order parameter as a finite-difference field ("free_energy symmetric",
+// src/ludwig.c:1159-1250): phi_force_calculation + phi_cahn_hilliard in one pass
+// (ch_kernels.cu)
+// ---------------------------------------------------------------------------
+
+static int field_current(b200lb_s * h, int field);
+
+extern "C" int b200lb_ch_create(b200lb_t * h, int order, int method) {
+  if (!h) return fail("null handle");
+  if (h->desc.ndist != 1) return fail("phi_ch_create: the finite-difference order parameter goes with ndist = 1 (symmetric_lb carries it as a second distribution)");
+  if (h->desc.ndim != 3 || h->desc.nlocal[2] == 1) return fail("phi_ch_create: two-dimensional systems (2d_5pt_fluid gradient, wz = 0) are not on this path");
+  for (int a = 0; a < 3; a++) {
+    if (!h->desc.periodic[a]) return fail("phi_ch_create: walls need the solid gradient stencils and the no-flux masks of src/advection_bcs.c: not on this path");
+  }
+  if (h->le_nplanes) return fail("phi_ch_create: Lees-Edwards planes for the order parameter (src/phi_cahn_hilliard.c:618) are not on this path");
+  if (order < 1 || order > 3) return fail("fd_advection_scheme_order %d: orders 1 to 3 are on this path (4 and 5 are host loops in the reference, src/advection.c:465-477)", order);
+  if (method != CH_FORCE_NONE && method != CH_FORCE_STRESS_DIVERGENCE && method != CH_FORCE_PHI_GRADMU) {
+    return fail("fe_force_method %d: no_force (1), stress_divergence (2) and phi_gradmu (3) are on this path", method);
+  }
+  if (need_planes(h, &h->phi, 1) || need_planes(h, &h->phi2, 1)) return -1;
+  if (need_planes(h, &h->grad, 3) || need_planes(h, &h->delsq, 1)) return -1;
+  if (need_hydro(h)) return -1;
+  h->ch_on = true;
+  h->ch_order = order;
+  h->ch_method = method;
+  h->ch_force_pending = false;
+  h->ch_grad_valid = false;
+  h->ch_halo_done = false;
+  return 0;
+}
+
+extern "C" int b200lb_ch_grad_mu_set(b200lb_t * h, const double gm[3]) {
+  if (!h || !gm) return fail("null argument");
+  if (gm[0] != h->ch_gmu[0] || gm[1] != h->ch_gmu[1] || gm[2] != h->ch_gmu[2]) {
+    if (resolve_ch_force(h)) return -1;     // a recorded force belongs to the old gradient
+  }
+  for (int a = 0; a < 3; a++) h->ch_gmu[a] = gm[a];
+  return 0;
+}
+
+// One pass over the lattice: the force on the fluid (do_force), the update of phi
+// (do_update), or both.
+static int ch_run(b200lb_s * h, bool do_force, bool do_update) {
+  if (!h->ch_on) return fail("no finite-difference order parameter: call b200lb_ch_create first");
+  if (do_force && h->ch_method == CH_FORCE_NONE) do_force = false;
+  if (do_force) h->ch_force_pending = false;
+  if (!do_force && !do_update) return 0;
+  if (!h->ch_grad_valid) return fail("phi_force_calculation / phi_cahn_hilliard: field_grad_compute has not run for the current order parameter");
+  if (join_comm(h)) return -1;
+  bool any_dec = false;
+  for (int d = 0; d < 3; d++) {
+    if (decomposed(h, d)) any_dec = true;
+    if (do_update && h->ch_order == 3 && !h->selfper[d]) {
+      return fail("third-order advection reads phi two sites away (nhalo = 2): on this path only around directions that are periodic within the rank");
+    }
+  }
+  if (any_dec && !h->ch_halo_done) {
+    // The reference evaluates gradient and stress one site into a halo two sites wide;
+    // here the neighbours' own values cross instead (same arithmetic on the same
+    // operands: identical)
+    if (halo_exchange(h, h->grad, false, 3, B200LB_HALO_FULL, 1, h->s_main)) return -1;
+    if (halo_exchange(h, h->delsq, false, 1, B200LB_HALO_FULL, 1, h->s_main)) return -1;
+    h->ch_halo_done = true;
+  }
+  if (do_update) {
+    // hydro_u_halo, src/phi_cahn_hilliard.c:228: the velocity of the last collision
+    if (field_current(h, B200LB_FIELD_U)) return -1;
+    if (any_dec) { if (halo_exchange(h, h->u, false, 3, B200LB_HALO_FULL, 1, h->s_main)) return -1; }
+  }
+  if (do_force) {
+    // the force the last collision read is about to change: rho,u it did not store
+    // have to be recovered first
+    if (h->hydro_stale && h->last_ffield) { if (ensure_hydro(h)) return -1; }
+    if (need_planes(h, &h->force, 3)) return -1;
+  }
+  ChParams P;
+  memset(&P, 0, sizeof(P));
+  P.L = h->L;
+  for (int d = 0; d < 3; d++) P.wrap[d] = h->selfper[d];
+  P.phi = h->phi; P.grad = h->grad; P.delsq = h->delsq; P.u = h->u;
+  P.force = h->force; P.phi_out = h->phi2;
+  P.A = h->prm.a; P.B = h->prm.b; P.kappa = h->prm.kappa; P.mobility = h->prm.mobility;
+  for (int a = 0; a < 3; a++) { P.gmu[a] = h->ch_gmu[a]; P.fconst[a] = h->fconst[a]; }
+  P.accumulate = h->force_uniform ? 0 : 1;
+  P.order = h->ch_order;
+  P.method = h->ch_method;
+  CU(ch_launch(P, do_force, do_update, h->s_main));
+  h->launches++;
+  if (do_force) h->force_uniform = false;
+  if (do_update) {
+    double * t = h->phi; h->phi = h->phi2; h->phi2 = t;
+    h->phi_halo_deferred = false;       // halos of the new phi are stale until the next field_halo
+    h->ch_grad_valid = false;
+    h->ch_halo_done = false;
+  }
+  return 0;
+}
+
+static int resolve_ch_force(b200lb_s * h) {
+  if (!h->ch_force_pending) return 0;
+  return ch_run(h, true, false);
+}
+
+extern "C" int b200lb_phi_force(b200lb_t * h) {
+  if (!h) return fail("null handle");
+  if (!h->ch_on) return fail("no finite-difference order parameter: call b200lb_ch_create first");
+  if (h->ch_method == CH_FORCE_NONE) return 0;
+  if (!h->ch_grad_valid) return fail("phi_force_calculation: field_grad_compute has not run for the current order parameter");
+  if (h->opt_ch_fuse) {
+    // evaluated by the pass of the Cahn-Hilliard update that follows (same inputs), or
+    // by whoever looks at the force field first
+    h->ch_force_pending = true;
+    return 0;
+  }
+  return ch_run(h, true, false);
+}
+
+extern "C" int b200lb_cahn_hilliard(b200lb_t * h) {
+  if (!h) return fail("null handle");
+  return ch_run(h, h->ch_force_pending, true);
+}
+
+extern "C" int b200lb_hydro_u_halo(b200lb_t * h) {
+  if (!h) return fail("null handle");
+  if (need_hydro(h)) return -1;
+  if (field_current(h, B200LB_FIELD_U)) return -1;
+  if (join_comm(h)) return -1;
+  return halo_exchange(h, h->u, false, 3, B200LB_HALO_FULL, 0, h->s_main);
+}
+
+// ---------------------------------------------------------------------------
 // the time loop of src/ludwig.c:530-862 restricted to the hot path
 // ---------------------------------------------------------------------------
 
@@ -1536,6 +1697,13 @@ extern "C" int b200lb_step(b200lb_t * h, int nsteps) {
       if (b200lb_phi_halo(h)) return -1;
       if (h->opt_gradient == 27) { if (b200lb_grad27(h)) return -1; }
       else if (b200lb_grad7(h)) return -1;
+    }
+    if (h->ch_on) {                                 // src/ludwig.c:558-575, 727-768
+      if (b200lb_phi_halo(h)) return -1;
+      if (h->opt_gradient == 27) { if (b200lb_grad27(h)) return -1; }
+      else if (b200lb_grad7(h)) return -1;
+      if (b200lb_phi_force(h)) return -1;
+      if (b200lb_cahn_hilliard(h)) return -1;
     }
     if (b200lb_hydro_u_zero(h, zero)) return -1;
     h->le_step++;                                   // physics_control_next_step, src/ludwig.c:552
@@ -1804,8 +1972,8 @@ extern "C" int b200lb_f_download(b200lb_t * h, double * f, int layout) {
 }
 
 static int field_info(b200lb_s * h, int field, double ** dev, int * nf) {
-  if (field >= B200LB_FIELD_PHI && field <= B200LB_FIELD_DELSQ && h->desc.ndist != 2) {
-    return fail("field %d needs the binary fluid (ndist = 2)", field);
+  if (field >= B200LB_FIELD_PHI && field <= B200LB_FIELD_DELSQ && h->desc.ndist != 2 && !h->ch_on) {
+    return fail("field %d needs an order parameter (ndist = 2, or b200lb_ch_create)", field);
   }
   switch (field) {
   case B200LB_FIELD_RHO:   if (need_hydro(h)) return -1; *dev = h->rho; *nf = 1; break;
@@ -1826,19 +1994,26 @@ extern "C" int b200lb_field_upload(b200lb_t * h, int field, const double * host,
   if (field == B200LB_FIELD_FORCE) {
     if (h->hydro_stale && h->last_ffield) { if (ensure_hydro(h)) return -1; }
     h->force_uniform = false;
+    h->ch_force_pending = false;          // overwritten by this upload
   }
+  if (field >= B200LB_FIELD_PHI && field <= B200LB_FIELD_DELSQ) { if (resolve_ch_force(h)) return -1; }
   if ((field == B200LB_FIELD_U || field == B200LB_FIELD_RHO) && h->hydro_stale) h->hydro_stale = false;
   if (field == B200LB_FIELD_PHI) {
     h->phi_halo_deferred = false;
     if (h->grad_state == 1) h->grad_state = 2;
+    h->ch_grad_valid = false;
   }
-  if (field == B200LB_FIELD_GRAD || field == B200LB_FIELD_DELSQ) h->grad_state = 0;
+  if (field == B200LB_FIELD_GRAD || field == B200LB_FIELD_DELSQ) {
+    h->grad_state = 0;
+    h->ch_grad_valid = true; h->ch_halo_done = false;    // the caller's gradient (field_grad_memcpy H2D)
+  }
   if (field == B200LB_FIELD_U) h->u_fill_pending = false;
   return transfer(h, dev, nf, const_cast<double *>(host), layout, true);
 }
 
 // bring the device arrays of `field` up to date with everything recorded lazily
 static int field_current(b200lb_s * h, int field) {
+  if (field == B200LB_FIELD_FORCE) { if (resolve_ch_force(h)) return -1; }
   if (field == B200LB_FIELD_FORCE && h->force_uniform) {
     if (fill3(h, h->force, 3, h->fconst)) return -1;
   }

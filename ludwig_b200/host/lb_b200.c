@@ -87,6 +87,29 @@ int lb_collision_relaxation_set(lb_t * lb, lb_relaxation_enum_t nrelax) {
 /* lb_collide: gathers the parameters the reference commits every step
  * (src/collision.c:144-163, :1181-1264, :1928-1980) and runs the collision. */
 
+/* what the reference commits from physics_ref() and the free energy */
+static int gather_params(lb_t * lb, fe_t * fe, b200lb_param_t * p) {
+  memset(p, 0, sizeof(*p));
+  p->rho0 = lb->phys->rho0;
+  p->eta_shear = lb->phys->eta_shear;
+  p->eta_bulk = lb->phys->eta_bulk;
+  for (int a = 0; a < 3; a++) p->force_global[a] = lb->phys->fbody[a];
+  p->nrelax = (int) lb->nrelax;
+  p->mobility = lb->phys->mobility;
+  if (lb->ndist == 2 && fe == NULL) {
+    snprintf(host_err, sizeof(host_err), "lb_collide: ndist = 2 needs the symmetric free energy");
+    return -1;
+  }
+  if (fe != NULL) {
+    fe_symm_t * fs = (fe_symm_t *) fe;     /* src/collision.c:160 */
+    p->a = fs->param.a; p->b = fs->param.b; p->kappa = fs->param.kappa;
+  }
+  /* lb_collision_noise_var_set (src/collision.c:1572): variances follow kt */
+  p->kt = lb->phys->kt;
+  p->ghost_off = (lb->isghost == LB_GHOST_OFF);
+  return 0;
+}
+
 int lb_collide(lb_t * lb, hydro_t * hydro, map_t * map, noise_t * noise, fe_t * fe, visc_t * visc) {
 
   b200lb_param_t p;
@@ -94,24 +117,7 @@ int lb_collide(lb_t * lb, hydro_t * hydro, map_t * map, noise_t * noise, fe_t * 
   (void) map; (void) visc;
   if (hydro == NULL) return 0;               /* src/collision.c:149 */
 
-  memset(&p, 0, sizeof(p));
-  p.rho0 = lb->phys->rho0;
-  p.eta_shear = lb->phys->eta_shear;
-  p.eta_bulk = lb->phys->eta_bulk;
-  for (int a = 0; a < 3; a++) p.force_global[a] = lb->phys->fbody[a];
-  p.nrelax = (int) lb->nrelax;
-  p.mobility = lb->phys->mobility;
-  if (lb->ndist == 2) {
-    fe_symm_t * fs = (fe_symm_t *) fe;     /* src/collision.c:160 */
-    if (fs == NULL) {
-      snprintf(host_err, sizeof(host_err), "lb_collide: ndist = 2 needs the symmetric free energy");
-      return -1;
-    }
-    p.a = fs->param.a; p.b = fs->param.b; p.kappa = fs->param.kappa;
-  }
-  /* lb_collision_noise_var_set (src/collision.c:1572): variances follow kt */
-  p.kt = lb->phys->kt;
-  p.ghost_off = (lb->isghost == LB_GHOST_OFF);
+  if (gather_params(lb, fe, &p)) return -1;
   TRY(b200lb_noise_present_set(lb->target, (noise != NULL) && noise->on[NOISE_RHO]));
   TRY(b200lb_set_param(lb->target, &p));
   TRY(b200lb_collide(lb->target));
@@ -338,6 +344,88 @@ int hydro_correct_momentum(hydro_t * h) {
 }
 
 /* order parameter, gradient, free energy */
+
+/* The order parameter as a finite-difference field ("free_energy symmetric"):
+ * phi_ch_t + pth_t of the reference are one object in the library (b200lb_ch_create). */
+
+static int advection_order_ = 1;             /* src/advection.c:85: a file-scope default */
+
+int advection_order_set(const int order) { advection_order_ = order; return 0; }
+int advection_order(int * order) { *order = advection_order_; return 0; }
+
+static int fd_commit(lb_t * lb) {
+  const int method = lb->fd_method ? lb->fd_method : FE_FORCE_METHOD_STRESS_DIVERGENCE;
+  if (lb->fd_committed && lb->fd_order == advection_order_ && lb->fd_method_applied == method) return 0;
+  TRY(b200lb_ch_create(lb->target, advection_order_, method));
+  lb->fd_committed = 1; lb->fd_order = advection_order_; lb->fd_method_applied = method;
+  return 0;
+}
+
+int phi_ch_create(lb_t * lb, phi_ch_info_t * info, phi_ch_t ** ppch) {
+  phi_ch_t * pch = NULL;
+  if (info != NULL && info->conserve != 0) {
+    snprintf(host_err, sizeof(host_err), "phi_ch_create: the compensated update (conserve = %d) is not on this path", info->conserve);
+    return -1;
+  }
+  if (fd_commit(lb)) return -1;
+  pch = (phi_ch_t *) calloc(1, sizeof(phi_ch_t));
+  if (pch == NULL) return -1;
+  pch->lb = lb;
+  *ppch = pch;
+  return 0;
+}
+int phi_ch_free(phi_ch_t * pch) { free(pch); return 0; }
+
+int pth_create(lb_t * lb, int method, pth_t ** ppth) {
+  pth_t * pth = (pth_t *) calloc(1, sizeof(pth_t));
+  if (pth == NULL) return -1;
+  pth->method = method; pth->lb = lb;
+  lb->fd_method = method;
+  if (lb->fd_committed) { if (fd_commit(lb)) { free(pth); return -1; } }
+  *ppth = pth;
+  return 0;
+}
+int pth_free(pth_t * pth) { free(pth); return 0; }
+
+static int fd_params(lb_t * lb, fe_t * fe) {
+  b200lb_param_t p;
+  if (fd_commit(lb)) return -1;
+  if (gather_params(lb, fe, &p)) return -1;
+  TRY(b200lb_set_param(lb->target, &p));
+  TRY(b200lb_ch_grad_mu_set(lb->target, lb->phys->grad_mu));
+  return 0;
+}
+
+/* src/phi_force.c:74; without hydrodynamics or with "no_force" there is nothing to do */
+int phi_force_calculation(pth_t * pth, fe_t * fe, field_t * phi, hydro_t * hydro) {
+  (void) phi;
+  if (hydro == NULL) return 0;
+  if (pth->method == FE_FORCE_METHOD_NO_FORCE) return 0;
+  if (fd_params(pth->lb, fe)) return -1;
+  TRY(b200lb_phi_force(pth->lb->target));
+  return 0;
+}
+
+/* src/phi_cahn_hilliard.c:206 (no order-parameter noise, all-fluid map) */
+int phi_cahn_hilliard(phi_ch_t * pch, fe_t * fe, field_t * phi, hydro_t * hydro, map_t * map, noise_t * noise) {
+  (void) phi; (void) map;
+  if (noise != NULL && noise->on[NOISE_PHI]) {
+    snprintf(host_err, sizeof(host_err), "phi_cahn_hilliard: order-parameter noise is not on this path");
+    return -1;
+  }
+  if (hydro == NULL) {
+    snprintf(host_err, sizeof(host_err), "phi_cahn_hilliard: the purely diffusive case (no hydrodynamics) is not on this path");
+    return -1;
+  }
+  if (fd_params(pch->lb, fe)) return -1;
+  TRY(b200lb_cahn_hilliard(pch->lb->target));
+  return 0;
+}
+
+int hydro_u_halo(hydro_t * hydro) {
+  TRY(b200lb_hydro_u_halo(hydro->lb->target));
+  return 0;
+}
 
 int field_create(lb_t * lb, const char * name, field_t ** pphi) {
   field_t * phi = (field_t *) calloc(1, sizeof(field_t));

@@ -54,6 +54,7 @@ typedef struct physics_s {
   double mobility;
   double kt;                       /* physics_kt: isothermal fluctuations */
   int t_current;                   /* physics_control_timestep (src/physics.c) */
+  double grad_mu[3];               /* physics_grad_mu: external chemical potential gradient */
 } physics_t;
 int physics_control_next_step(physics_t * phys);                   /* src/physics.h:34 */
 int physics_control_time(physics_t * phys, double * t);            /* src/physics.h:54 */
@@ -79,6 +80,9 @@ typedef struct lb_data_s {
   lb_halo_enum_t haloscheme;
   physics_t * phys;                /* stands in for physics_ref() */
   b200lb_t * target;               /* the device side (reference: lb->target) */
+  /* finite-difference order parameter: what phi_ch_create / pth_create / advection_order_set
+   * have asked for and what the library has been told */
+  int fd_method, fd_committed, fd_order, fd_method_applied;
 } lb_t;
 
 typedef struct field_s { int nf; int nsites; double * data; lb_t * lb; int id; } field_t;
@@ -190,6 +194,28 @@ int field_grad_set(field_grad_t * grad, grad_ft d2, grad_ft d4);   /* src/field_
 int grad_3d_7pt_fluid_d2(field_grad_t * grad);            /* src/gradient_3d_7pt_fluid.c:75 (default) */
 int grad_3d_27pt_fluid_d2(field_grad_t * grad);           /* src/gradient_3d_27pt_fluid.c:75 */
 int field_grad_memcpy(field_grad_t * grad, tdpMemcpyKind flag);
+
+/* The order parameter as a finite-difference field ("free_energy symmetric",
+ * src/ludwig.c:1159-1250, time step src/ludwig.c:727-768). Create the phi_ch_t before the
+ * field_t of the order parameter (the library allocates phi with it). */
+typedef enum fe_force_method_enum {                                /* src/fe_force_method.h:20-28 */
+  FE_FORCE_METHOD_INVALID, FE_FORCE_METHOD_NO_FORCE, FE_FORCE_METHOD_STRESS_DIVERGENCE,
+  FE_FORCE_METHOD_PHI_GRADMU, FE_FORCE_METHOD_PHI_GRADMU_CORRECTION,
+  FE_FORCE_METHOD_RELAXATION_SYMM, FE_FORCE_METHOD_RELAXATION_ANTI, FE_FORCE_METHOD_MAX
+} fe_force_method_enum_t;
+typedef struct phi_ch_info_s { int conserve; } phi_ch_info_t;     /* src/phi_cahn_hilliard.h:29 */
+typedef struct phi_ch_s { phi_ch_info_t info; lb_t * lb; } phi_ch_t;
+typedef struct pth_s { int method; lb_t * lb; } pth_t;            /* src/phi_force_stress.h */
+int advection_order_set(const int order);                          /* src/advection.c:93 */
+int advection_order(int * order);
+int phi_ch_create(lb_t * lb, phi_ch_info_t * info, phi_ch_t ** pch);            /* src/phi_cahn_hilliard.c:121 */
+int phi_ch_free(phi_ch_t * pch);
+int pth_create(lb_t * lb, int method, pth_t ** pth);                            /* src/phi_force_stress.c:41 */
+int pth_free(pth_t * pth);
+int phi_force_calculation(pth_t * pth, fe_t * fe, field_t * phi, hydro_t * hydro);   /* src/phi_force.c:74 */
+int phi_cahn_hilliard(phi_ch_t * pch, fe_t * fe, field_t * phi, hydro_t * hydro,
+		      map_t * map, noise_t * noise);                             /* src/phi_cahn_hilliard.c:206 */
+int hydro_u_halo(hydro_t * hydro);                                              /* src/hydro.c */
 
 int fe_symm_create(field_t * phi, field_grad_t * dphi, fe_symm_t ** fe);
 int fe_symm_free(fe_symm_t * fe);

@@ -5,7 +5,8 @@ lb_collide (src/collision.c:144), lb_halo / lb_halo_swap (src/model.c:553,570),
 lb_propagation (src/propagation.c:43), lb_memcpy (src/model.c:228),
 hydro_f_zero / hydro_u_zero (src/hydro.c:306,279), phi_lb_to_field
 (src/phi_lb_coupler.c:39), field_halo (src/field.c:434), field_grad_compute ->
-grad_3d_7pt_fluid_d2 (src/gradient_3d_7pt_fluid.c:75).
+grad_3d_7pt_fluid_d2 (src/gradient_3d_7pt_fluid.c:75), phi_force_calculation
+(src/phi_force.c:74), phi_cahn_hilliard (src/phi_cahn_hilliard.c:206).
 """
 
 import ctypes
@@ -21,6 +22,7 @@ HOST_AOS, HOST_SOA = 0, 1
 RELAX_M10, RELAX_BGK, RELAX_TRT = 0, 1, 2
 HALO_FULL, HALO_REDUCED = 0, 2
 FIELD_RHO, FIELD_U, FIELD_FORCE, FIELD_PHI, FIELD_GRAD, FIELD_DELSQ = range(6)
+FORCE_NONE, FORCE_STRESS_DIVERGENCE, FORCE_PHI_GRADMU = 1, 2, 3      # fe_force_method_enum_t
 _FIELD_NF = {FIELD_RHO: 1, FIELD_U: 3, FIELD_FORCE: 3, FIELD_PHI: 1, FIELD_GRAD: 3,
              FIELD_DELSQ: 1}
 
@@ -36,6 +38,8 @@ ABI_SYMBOLS = [
     "b200lb_noise_state_download",
     "b200lb_wall_commit", "b200lb_wall_slip_set", "b200lb_wall_bbl", "b200lb_wall_momentum", "b200lb_wall_momentum_add",
     "b200lb_le_commit", "b200lb_le_apply", "b200lb_le_plane_location", "b200lb_le_time_set",
+    "b200lb_ch_create", "b200lb_ch_grad_mu_set", "b200lb_phi_force", "b200lb_cahn_hilliard",
+    "b200lb_hydro_u_halo",
     "b200lb_field_stats", "b200lb_io_record_doubles", "b200lb_io_pack", "b200lb_io_unpack",
     "b200lb_step", "b200lb_stats", "b200lb_step_diag", "b200lb_sync", "b200lb_nccl_unique_id",
     "b200lb_comm_init", "b200lb_p2p_export", "b200lb_p2p_import", "b200lb_timer_start", "b200lb_timer_stop",
@@ -120,6 +124,10 @@ def load():
     L.b200lb_le_apply.argtypes = [vp, ctypes.c_double]
     L.b200lb_le_plane_location.argtypes = [vp, ctypes.c_int]
     L.b200lb_le_time_set.argtypes = [vp, ctypes.c_int]
+    L.b200lb_ch_create.argtypes = [vp, ctypes.c_int, ctypes.c_int]
+    L.b200lb_ch_grad_mu_set.argtypes = [vp, vp]
+    for name in ("b200lb_phi_force", "b200lb_cahn_hilliard", "b200lb_hydro_u_halo"):
+        getattr(L, name).argtypes = [vp]
     L.b200lb_field_stats.argtypes = [vp, ctypes.c_int, vp]
     L.b200lb_io_record_doubles.argtypes = [vp]
     L.b200lb_io_record_doubles.restype = ctypes.c_long
@@ -313,6 +321,23 @@ class Lattice:
             self._ck(self.L.b200lb_grad27(self.h))
         else:
             self._ck(self.L.b200lb_grad7(self.h))
+
+    # -- the order parameter as a finite-difference field ("free_energy symmetric") ----
+    def phi_ch_create(self, order=1, method=FORCE_STRESS_DIVERGENCE, grad_mu=None):
+        """phi_ch_create + pth_create + advection_order_set: order = fd_advection_scheme_order,
+        method = fe_force_method; grad_mu = the external chemical potential gradient."""
+        self._ck(self.L.b200lb_ch_create(self.h, int(order), int(method)))
+        if grad_mu is not None:
+            self._ck(self.L.b200lb_ch_grad_mu_set(self.h, (ctypes.c_double * 3)(*grad_mu)))
+
+    def phi_force_calculation(self):
+        self._ck(self.L.b200lb_phi_force(self.h))
+
+    def phi_cahn_hilliard(self):
+        self._ck(self.L.b200lb_cahn_hilliard(self.h))
+
+    def hydro_u_halo(self):
+        self._ck(self.L.b200lb_hydro_u_halo(self.h))
 
     # -- flat walls (wall_t, src/wall.h) ---------------------------------------------
     def wall_commit(self, isboundary, ubot=(0.0, 0.0, 0.0), utop=(0.0, 0.0, 0.0)):

@@ -438,7 +438,125 @@ static void test_lees_edwards(int nsteps, int oscillatory) {
   lb_free(lb);
 }
 
-int main(void) {
+/* The order parameter as a finite-difference field ("free_energy symmetric") through the
+ * reference's call order (src/ludwig.c:537-575, 727-768, 791-862) */
+static void test_cahn_hilliard(int nsteps, int order, int method, int npt) {
+  cs_t cs;
+  physics_t phys = {1.0, 0.00625, 0.00625, {0.0, 0.0, 0.0}, 1.25, 0.0};
+  lb_data_options_t opts = lb_data_options_default();
+  lb_t * lb = NULL; hydro_t * hydro = NULL; field_t * phi = NULL; field_grad_t * grad = NULL;
+  fe_symm_t * fe = NULL; phi_ch_t * pch = NULL; pth_t * pth = NULL;
+  phi_ch_info_t info = {0};
+  fe_symm_param_t fp = {-0.00625, 0.00625, 0.004, 0.0, 0.0};
+  orc_model_t model; orc_box_t box; orc_param_t prm; orc_ch_t och;
+  const int nl[3] = {10, 8, 6};
+  const double zero[3] = {0.0, 0.0, 0.0};
+  unsigned long seed = 20240229;
+
+  if (method == FE_FORCE_METHOD_PHI_GRADMU) { phys.grad_mu[0] = 1.0e-5; phys.grad_mu[1] = -2.0e-5; phys.grad_mu[2] = 3.0e-5; }
+  cs_serial(&cs, nl[0], nl[1], nl[2]);
+  OK(lb_data_create(&cs, &phys, &opts, &lb));
+  OK(hydro_create(lb, &hydro));
+  OK(advection_order_set(order));
+  OK(phi_ch_create(lb, &info, &pch));
+  OK(pth_create(lb, method, &pth));
+  OK(field_create(lb, "phi", &phi));
+  OK(field_grad_create(phi, &grad));
+  OK(field_grad_set(grad, npt == 27 ? grad_3d_27pt_fluid_d2 : grad_3d_7pt_fluid_d2, NULL));
+  OK(fe_symm_create(phi, grad, &fe));
+  OK(fe_symm_param_set(fe, fp));
+
+  orc_model_init(lb->nvel, &model);
+  orc_box_init(nl, &box);
+  memset(&prm, 0, sizeof(prm));
+  prm.rho0 = phys.rho0; prm.eta_shear = phys.eta_shear; prm.eta_bulk = phys.eta_bulk;
+  prm.mobility = phys.mobility; prm.a = fp.a; prm.b = fp.b; prm.kappa = fp.kappa;
+  memset(&och, 0, sizeof(och));
+  och.order = order; och.method = method;
+  for (int a = 0; a < 3; a++) och.grad_mu[a] = phys.grad_mu[a];
+
+  size_t nf = (size_t) lb->nsite*lb->nvel;
+  double * f = (double *) calloc(nf, sizeof(double));
+  double * fprime = (double *) calloc(nf, sizeof(double));
+  double * rho = (double *) calloc(lb->nsite, sizeof(double));
+  double * u = (double *) calloc(3*(size_t) lb->nsite, sizeof(double));
+  double * force = (double *) calloc(3*(size_t) lb->nsite, sizeof(double));
+  double * ophi = (double *) calloc(lb->nsite, sizeof(double));
+  double * ograd = (double *) calloc(3*(size_t) lb->nsite, sizeof(double));
+  double * odelsq = (double *) calloc(lb->nsite, sizeof(double));
+  for (int ic = 1; ic <= nl[0]; ic++) for (int jc = 1; jc <= nl[1]; jc++) for (int kc = 1; kc <= nl[2]; kc++) {
+    long index = cs_index(&cs, ic, jc, kc);
+    double r = 1.0 + 0.01*urand(&seed);
+    double uu[3] = {0.01*urand(&seed), 0.01*urand(&seed), 0.01*urand(&seed)};
+    orc_equilib_set(&model, 1, f, index, r, uu);
+    ophi[index] = 0.4*urand(&seed);
+  }
+  memcpy(lb->f, f, nf*sizeof(double));
+  memcpy(phi->data, ophi, lb->nsite*sizeof(double));
+  OK(lb_memcpy(lb, tdpMemcpyHostToDevice));
+  OK(field_memcpy(phi, tdpMemcpyHostToDevice));
+
+  for (int n = 0; n < nsteps; n++) {
+    OK(hydro_f_zero(hydro, zero));
+    OK(field_halo(phi));
+    OK(field_grad_compute(grad));
+    OK(phi_force_calculation(pth, (fe_t *) fe, phi, hydro));
+    OK(phi_cahn_hilliard(pch, (fe_t *) fe, phi, hydro, NULL, NULL));
+    OK(hydro_u_zero(hydro, zero));
+    OK(lb_collide(lb, hydro, NULL, NULL, (fe_t *) fe, NULL));
+    OK(lb_halo(lb));
+    OK(lb_propagation(lb));
+  }
+  OK(lb_memcpy(lb, tdpMemcpyDeviceToHost));
+  OK(hydro_memcpy(hydro, tdpMemcpyDeviceToHost));
+  OK(field_memcpy(phi, tdpMemcpyDeviceToHost));
+
+  orc_gradient_select(npt);
+  orc_ch_attach(&och);
+  orc_step(&model, &box, &prm, 1, nsteps, f, fprime, rho, u, force, ophi, ograd, odelsq);
+  orc_ch_attach(NULL);
+  orc_gradient_select(7);
+
+  double emax = 0.0, fmax = 0.0, umax = 0.0, pmax = 0.0;
+  for (int ic = 1; ic <= nl[0]; ic++) for (int jc = 1; jc <= nl[1]; jc++) for (int kc = 1; kc <= nl[2]; kc++) {
+    long index = cs_index(&cs, ic, jc, kc);
+    for (int p = 0; p < lb->nvel; p++) {
+      long i = LB_ADDR(lb->nsite, 1, lb->nvel, index, 0, p);
+      if (fabs(lb->f[i] - f[i]) > emax) emax = fabs(lb->f[i] - f[i]);
+      if (fabs(f[i]) > fmax) fmax = fabs(f[i]);
+    }
+    for (int a = 0; a < 3; a++) {
+      double d = fabs(hydro->u.data[3*index + a] - u[3*index + a]);
+      if (d > umax) umax = d;
+    }
+    if (fabs(phi->data[index] - ophi[index]) > pmax) pmax = fabs(phi->data[index] - ophi[index]);
+  }
+  printf("test_cahn_hilliard (order %d, method %d, %d-point gradient): %d steps, max|df|/max|f| = %.3e, "
+	 "max|du| = %.3e, max|dphi| = %.3e\n", order, method, npt, nsteps, emax/fmax, umax, pmax);
+  CHECK(emax/fmax < 1.0e-12, "Cahn-Hilliard: distributions vs oracle");
+  CHECK(umax < 1.0e-12, "Cahn-Hilliard: hydro u vs oracle");
+  CHECK(pmax < 1.0e-13, "Cahn-Hilliard: order parameter vs oracle");
+
+  free(f); free(fprime); free(rho); free(u); free(force); free(ophi); free(ograd); free(odelsq);
+  fe_symm_free(fe);
+  field_grad_free(grad);
+  field_free(phi);
+  pth_free(pth);
+  phi_ch_free(pch);
+  hydro_free(hydro);
+  lb_free(lb);
+}
+
+int main(int argc, char ** argv) {
+  if (argc > 1 && strcmp(argv[1], "fd") == 0) {
+    /* the finite-difference order parameter on its own (tests/test_host_shim.py) */
+    test_cahn_hilliard(6, 1, FE_FORCE_METHOD_STRESS_DIVERGENCE, 27);
+    test_cahn_hilliard(6, 2, FE_FORCE_METHOD_STRESS_DIVERGENCE, 7);
+    test_cahn_hilliard(6, 3, FE_FORCE_METHOD_PHI_GRADMU, 27);
+    if (nfail) { printf("%d check(s) FAILED\n", nfail); return 1; }
+    printf("host shim (fd): all passed\n");
+    return 0;
+  }
   test_prop(1, LB_HALO_TARGET);
   test_prop(2, LB_HALO_TARGET);
   test_prop(1, LB_HALO_OPENMP_REDUCED);

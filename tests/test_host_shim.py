@@ -39,3 +39,13 @@ def test_host_mirror_on_gpu():
     print(r.stdout)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "all passed" in r.stdout
+
+
+@pytest.mark.gpu
+def test_host_mirror_cahn_hilliard_on_gpu():
+    """"free_energy symmetric" through phi_force_calculation / phi_cahn_hilliard in C."""
+    build_exe()
+    r = subprocess.run([EXE, "fd"], capture_output=True, text=True, timeout=300)
+    print(r.stdout)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "all passed" in r.stdout

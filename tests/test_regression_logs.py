@@ -3,7 +3,10 @@ serial-dist-{3du,1dp,2kh,2sw}.{inp,log}, d2q9/serial-2khz-bm1, 2560 steps of D2Q
 d2q9/serial-flct-t01, 200 fluctuating steps; and for the binary fluid d3q19-short/
 serial-spin-lb{1,3,4}: symmetric_lb spinodal decomposition with the 27-point gradient, lb3
 and lb4 fluctuating, lb1 and lb4 with ghost modes off; and with walls serial-rect-ct1 (duct flow
-driven by a body force) serial-wall-st1 (closed box, fluctuating) and serial-rect-ct2..5 (partial-slip walls): the statistics printed after the last step,
+driven by a body force) serial-wall-st1 (closed box, fluctuating) and serial-rect-ct2..5 (partial-slip walls); and the finite-difference order parameter
+(free_energy symmetric) serial-spin-fd1, serial-symm-dr1, serial-symm-pat, serial-muex-st1
+(phi grad mu force with an external chemical-potential gradient) and the 400-step
+d3q19/pmpi08-spin-fd1: the statistics printed after the last step,
 reproduced the way tests/test-diff.sh + tests/awk-fp-diff.sh judge them -- every printed
 float, in the reference's printf format, within an ABSOLUTE 1e-12.
 
@@ -25,7 +28,8 @@ import lbinit
 HERE = os.path.dirname(os.path.abspath(__file__))
 GOLD = json.load(open(os.path.join(HERE, "golden", "regression_logs.json")))
 FLT_MAX, FLT_MIN = 3.4028234663852886e+38, 1.1754943508222875e-38
-CASES = sorted(GOLD)
+# the finite-difference order-parameter cases (the newest kernels) last
+CASES = sorted(GOLD, key=lambda c: (GOLD[c]["input"].get("free_energy") == "symmetric", c))
 
 
 def initial_state(inp, cv, wv):
@@ -334,7 +338,7 @@ def test_cuda_reproduces_reference_log(case, hydro_write):
     lat.set_option("hydro_write", hydro_write)
     lat.set_option("halo", lb.HALO_REDUCED)          # lb_halo_openmp_reduced in the input
     kt = float(rec["input"].get("temperature", 0.0)) if noisy(rec) else 0.0
-    kw = binary_params(rec["input"]) if ndist == 2 else {}
+    kw = binary_params(rec["input"]) if (ndist == 2 or fd_route(rec)) else {}
     lat.set_param(eta_shear=eta, eta_bulk=zeta, kt=kt, ghost_off=int(ghost_off(rec)),
                   force=body_force(rec["input"]), **kw)
     if walls(rec):
@@ -349,6 +353,12 @@ def test_cuda_reproduces_reference_log(case, hydro_write):
         lat.noise_init(0)
         lat.noise_present_set(1)
     lat.lb_memcpy_h2d(f)
+    if fd_route(rec):
+        lat.phi_ch_create(*fd_options(rec["input"]))
+        lat.field_grad_set(gradient_points(rec))
+        phi0 = np.zeros(tuple(n + 2 for n in nt))
+        phi0[1:-1, 1:-1, 1:-1] = initial_phi(rec["input"], nt)
+        lat.field_h2d(lb.FIELD_PHI, np.ascontiguousarray(phi0.reshape(-1)))
     lat.step(int(rec["input"]["N_cycles"]))
     sums = lat.stats()                               # lb_memcpy D2H + stats_distribution_print
     u = lat.field_d2h(lb.FIELD_U)                    # hydro_memcpy D2H + stats_velocity_minmax
@@ -364,6 +374,10 @@ def test_cuda_reproduces_reference_log(case, hydro_write):
           gwall=list(lat.wall_momentum()) if walls(rec) else None)
     if ndist == 2:
         check_binary(rec, nt, fh, lat.field_d2h(lb.FIELD_GRAD)[m.reshape(-1)])
+    if fd_route(rec):
+        # phi after the last update, the gradient the last step computed (src/ludwig.c:2303)
+        check_fd(rec, nt, lat.field_d2h(lb.FIELD_PHI)[m.reshape(-1)],
+                 lat.field_d2h(lb.FIELD_GRAD)[m.reshape(-1)])
     if noisy(rec):
         check_equipartition(rec, fh[:, 0], models_host.cv(nvel))
     lat.close()
