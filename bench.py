@@ -59,6 +59,9 @@ def parse():
                     help="> 0: isothermal fluctuations at this temperature (not the headline workload)")
     ap.add_argument("--le", type=int, default=0,
                     help="Lees-Edwards planes in total, uy 0.01 (not the headline workload)")
+    ap.add_argument("--fd", type=int, default=0, choices=[0, 1, 2, 3],
+                    help="free_energy symmetric: the order parameter as a finite-difference field, "
+                         "advection scheme of this order (phi_force_calculation + phi_cahn_hilliard)")
     ap.add_argument("--walls", type=int, nargs=3, default=None,
                     help="flat no-slip walls in these directions, e.g. 0 1 1 (not the headline workload)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
@@ -312,6 +315,11 @@ def main():
         lat.noise_present_set(1)
     if args.le:
         lat.le_commit(args.le, 0.01)
+    if args.fd:
+        lat.set_param(eta_shear=0.00625, eta_bulk=0.00625, mobility=1.25, a=-0.00625,
+                      b=0.00625, kappa=0.004, kt=args.kt)
+        lat.phi_ch_create(args.fd, lb.FORCE_STRESS_DIVERGENCE)
+        lat.field_grad_set(args.gradient)
 
     if world > 1:
         uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
@@ -344,6 +352,14 @@ def main():
     # synthetic input, host side in the reference's AOS layout
     f0 = synthetic_state(nvel, local, ntotal, dec.offset, ndist)
     lat.lb_memcpy_h2d(f0)
+    if args.fd:
+        # spinodal start: phi = 0.1 (r - 1/2), as phi_initialisation spinodal does
+        import numpy as np
+        rng = np.random.default_rng(8361235 + rank)
+        phi0 = np.zeros(tuple(n + 2 for n in local))
+        phi0[1:-1, 1:-1, 1:-1] = 0.1 * (rng.random(local) - 0.5)
+        lat.field_h2d(lb.FIELD_PHI, np.ascontiguousarray(phi0.reshape(-1)))
+        del phi0
     sites_local = float(local[0]) * local[1] * local[2]
     sites_total = sites_local * world
     lattice_bytes = f0.nbytes
@@ -376,6 +392,27 @@ def main():
         kms = lat.timer_stop()
         nk = lat.launch_count() - k0
         kernel_ms = kms / max(nk, 1)
+    # ---- finite-difference order parameter: its passes alone ------------------------
+    fd = None
+    if args.fd:
+        lat.step(1)
+        barrier()
+        k0 = lat.launch_count()
+        lat.timer_start()
+        for _ in range(args.steps):
+            lat.field_halo()
+            lat.field_grad_compute()
+            lat.phi_force_calculation()
+            lat.phi_cahn_hilliard()
+        fms = lat.timer_stop() / args.steps
+        nk = (lat.launch_count() - k0) / args.steps
+        fd_bytes = 40.0 + 96.0      # gradient: phi in, grad + delsq out; update: 8 doubles in, force + phi out
+        fd = {"advection_order": args.fd, "ms_per_step": fms, "launches_per_step": nk,
+              "bytes_per_site": fd_bytes,
+              "achieved_gbs": fd_bytes * sites_local / (fms * 1e-3) / 1e9,
+              "frac": fd_bytes * sites_local / (fms * 1e-3) / 1e9 / peaks()[0],
+              "what": "field_halo + field_grad_compute + phi_force_calculation + phi_cahn_hilliard "
+                      "(gradient kernel + one fused force/update kernel), timed without the LB step"}
     # ---- the same step with rho,u produced on demand instead of every step --------
     lazy = None
     if args.hydro_write and args.fused and world == 1:
@@ -462,6 +499,7 @@ def main():
                 "gradient_points": args.gradient if ndist == 2 else None,
                 "walls": args.walls,
                 "lees_edwards_planes": args.le or None,
+                "fd_order_parameter": fd,
                 "isothermal_fluctuations_kt": args.kt if args.kt > 0.0 else None,
                 "l2": "lattice %.2f GB per GPU >> 126 MB L2 (no flush needed)" % (2 * lattice_bytes / 1e9),
             },

@@ -1,5 +1,15 @@
 #!/bin/bash
+# one short call: the finite-difference order-parameter kernels (tests, host mirror,
+# regression logs, one bench line)
 mkdir -p gpurun_out
-timeout 300 python -m pytest tests/test_gpu_parity.py tests/test_host_shim.py -q -m gpu -k "lees or host_mirror" > gpurun_out/t_le.log 2>&1; echo "rc=$?" >> gpurun_out/t_le.log
-tail -40 gpurun_out/t_le.log
-timeout 120 python bench.py --le 4 --steps 50 --warmup 3 --no-cpu --no-e2e > gpurun_out/bench_le.json 2> gpurun_out/bench_le.err; tail -3 gpurun_out/bench_le.err; cat gpurun_out/bench_le.json
+export B200LB_ASSUME_GPU=1
+nvidia-smi -L > gpurun_out/gpu.txt 2>&1
+timeout 170 python -m pytest tests/test_zz_gpu_cahn_hilliard.py -q -m gpu --maxfail=8 --tb=short -p no:cacheprovider > gpurun_out/t_ch.log 2>&1; echo "rc=$?" >> gpurun_out/t_ch.log
+tail -30 gpurun_out/t_ch.log
+timeout 60 tests/host/test_host_shim.exe fd > gpurun_out/t_shim_fd.log 2>&1; echo "rc=$?" >> gpurun_out/t_shim_fd.log
+tail -6 gpurun_out/t_shim_fd.log
+timeout 150 python -m pytest tests/test_regression_logs.py -q -m gpu -k "fd1 or dr1 or pat or muex" --tb=short -p no:cacheprovider > gpurun_out/t_reg_fd.log 2>&1; echo "rc=$?" >> gpurun_out/t_reg_fd.log
+tail -12 gpurun_out/t_reg_fd.log
+timeout 150 python bench.py --fd 1 --gradient 27 --steps 50 --warmup 3 --no-cpu --no-e2e > gpurun_out/bench_fd1.json 2> gpurun_out/bench_fd1.err; tail -3 gpurun_out/bench_fd1.err; cat gpurun_out/bench_fd1.json
+timeout 100 python -m pytest tests/test_gpu_parity.py -q -m gpu -x -k "binary or gradient or time_loop" -p no:cacheprovider > gpurun_out/t_sanity.log 2>&1; echo "rc=$?" >> gpurun_out/t_sanity.log
+tail -4 gpurun_out/t_sanity.log

@@ -224,6 +224,8 @@ ch_kernel(const ChParams P) {
   }
 }
 
+#ifndef B200LB_KERNEL_SOURCE_ONLY      // tools/ch_emulate.cpp steps through the kernel source on the host
+
 template <int METHOD, int ORDER>
 static cudaError_t launch(const ChParams & P, cudaStream_t st) {
   const Layout & L = P.L;
@@ -256,3 +258,5 @@ cudaError_t ch_launch(const ChParams & P, bool do_force, bool do_update, cudaStr
   }
   return cudaErrorInvalidValue;
 }
+
+#endif

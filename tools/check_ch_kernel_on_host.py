@@ -1,0 +1,98 @@
+"""DEVELOPMENT TOOL (no GPU in the build container): steps through the source of ch_kernel
+on the host (tools/ch_emulate.cpp) and compares force and updated order parameter with
+the reference-produced golden vectors tests/golden/ref_ch.npz, bit for bit -- with the
+periodic wrap inside the kernel and with filled halo planes (what a decomposed direction
+or the loopback exchange gives). Proves indexing and order of operations of the kernel
+source before GPU time is spent on it; the GPU tests (tests/test_zz_gpu_cahn_hilliard.py)
+are the parity evidence proper.
+
+    python tools/check_ch_kernel_on_host.py
+"""
+
+import ctypes
+import os
+import subprocess
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import goldenlib                      # noqa: E402
+from oracle import pyoracle           # noqa: E402
+
+SO = os.path.join(ROOT, "tools", "_ch_emulate.so")
+
+
+def build():
+    subprocess.check_call(["g++", "-O1", "-ffp-contract=off", "-w", "-I/usr/local/cuda/include",
+                           "-shared", "-fPIC", "-o", SO, os.path.join(ROOT, "tools", "ch_emulate.cpp")])
+
+
+def main():
+    build()
+    E = ctypes.CDLL(SO)
+    dp = ctypes.POINTER(ctypes.c_double)
+    g = goldenlib.load_ch()
+    P = goldenlib.CH_PHYS
+    bad = 0
+    for tag, (nlocal, order, method, npt, gmu) in sorted(goldenlib.CH_CASES.items()):
+        orc = pyoracle.Oracle(19, nlocal)
+        n = orc.nsite
+        m = orc.interior_mask()
+        for wrap in ((1, 1, 1), (0, 0, 0), (1, 0, 1)):
+            if order == 3 and wrap != (1, 1, 1):
+                continue          # refused by b200lb_cahn_hilliard
+            phi, u = goldenlib.ch_fields(nlocal)
+            orc.halo(phi, 1)
+            grad, delsq = np.zeros((n, 3)), np.zeros(n)
+            (orc.grad_27pt if npt == 27 else orc.grad_7pt)(phi, grad, delsq)
+            if wrap != (1, 1, 1):
+                orc.halo(grad, 3)
+                orc.halo(delsq, 1)
+            else:
+                # the kernel must not depend on halo values around wrapped directions
+                hal = ~m
+                for a in (phi, delsq):
+                    a[hal] = np.nan
+                grad[hal] = np.nan
+                u[hal] = np.nan
+            force = np.zeros((n, 3))
+            out = np.zeros(n)
+            for fused in (1, 0):
+                force[...] = 0.0
+                args = ((ctypes.c_int * 3)(*nlocal), (ctypes.c_int * 3)(*wrap))
+                prm = (ctypes.c_double * 4)(P["a"], P["b"], P["kappa"], P["mobility"])
+                gm = (ctypes.c_double * 3)(*gmu)
+                fc = (ctypes.c_double * 3)(0.0, 0.0, 0.0)
+                ptrs = [a.ctypes.data_as(dp) for a in (phi, grad, delsq, u, force, out)]
+                if fused:
+                    rc = E.ch_emulate(*args, method, order, prm, gm, fc, 0, *ptrs)
+                else:
+                    rc = E.ch_emulate(*args, method, 0, prm, gm, fc, 0, *ptrs)
+                    f1 = force.copy()
+                    rc |= E.ch_emulate(*args, 0, order, prm, gm, fc, 0, *ptrs)
+                    assert np.array_equal(f1[m], force[m])
+                assert rc == 0
+                okf = np.array_equal(force[m], g[tag + "_force"])
+                okp = np.array_equal(out[m], g[tag + "_phi1"])
+                print("%-6s wrap %s %-6s force %s  phi %s" % (tag, wrap, "fused" if fused else "split",
+                                                             "ok" if okf else "DIFF", "ok" if okp else "DIFF"))
+                bad += (not okf) + (not okp)
+            # accumulate onto an existing force field
+            base = np.random.default_rng(1).standard_normal((n, 3)) * 1e-3
+            force[...] = base
+            E.ch_emulate((ctypes.c_int * 3)(*nlocal), (ctypes.c_int * 3)(*wrap), method, 0, prm, gm, fc, 1,
+                         *[a.ctypes.data_as(dp) for a in (phi, grad, delsq, u, force, out)])
+            if method == 2:
+                ok = np.array_equal(force[m], base[m] + g[tag + "_force"])
+                print("%-6s wrap %s accumulate %s" % (tag, wrap, "ok" if ok else "DIFF"))
+                bad += (not ok)
+    print("FAILED" if bad else "all identical to the reference")
+    return bad
+
+
+if __name__ == "__main__":
+    sys.exit(1 if main() else 0)
