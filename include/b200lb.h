@@ -115,6 +115,7 @@ long b200lb_nsite(const b200lb_t * h);                          /* host nsite = 
  *                      (fd_gradient_calculation 3d_7pt_fluid / 3d_27pt_fluid, src/gradient_rt.c:81-98)
  *   "ch_fuse"     0/1  finite-difference order parameter: phi_force_calculation is
  *                      evaluated by the pass of the phi_cahn_hilliard that follows it
+ *   "ch_planes"   n    ... x-planes one block of that kernel marches (default 8)
  *   "loopback"    0/1  single rank: send periodic directions through the exchange
  *                      buffers with this GPU as its own neighbour (tests, profiling) */
 int  b200lb_set_option(b200lb_t * h, const char * name, long value);

@@ -157,7 +157,7 @@ struct b200lb_s {
   bool ghost;
 
   // options
-  int opt_fused, opt_halo, opt_hydro_write, opt_vec, opt_block, opt_halo_lazy, opt_overlap, opt_direct, opt_diag, opt_loopback, opt_grad_lazy, opt_p2p, opt_gradient, opt_ch_fuse;
+  int opt_fused, opt_halo, opt_hydro_write, opt_vec, opt_block, opt_halo_lazy, opt_overlap, opt_direct, opt_diag, opt_loopback, opt_grad_lazy, opt_p2p, opt_gradient, opt_ch_fuse, opt_ch_planes;
 
   cudaStream_t s_main, s_x[2];
   cudaStream_t s_comm;       // halo exchange of decomposed directions (overlaps the interior sweep)
@@ -476,6 +476,7 @@ static int create_impl(const b200lb_desc_t * desc, b200lb_s * h, const ModelOps 
   h->opt_gradient = 7;
   h->opt_p2p = 1;
   h->opt_ch_fuse = 1;
+  h->opt_ch_planes = 8;
 
   b200lb_param_t p0;
   memset(&p0, 0, sizeof(p0));
@@ -545,6 +546,11 @@ extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
     h->opt_ch_fuse = (v != 0);
     return 0;
   }
+  if (!strcmp(name, "ch_planes")) {
+    if (v < 1 || v > 4096) return fail("ch_planes: x-planes marched by one block of the order-parameter kernel, 1..4096");
+    h->opt_ch_planes = (int) v;
+    return 0;
+  }
   if (!strcmp(name, "gradient")) {
     if (v != 7 && v != 27) return fail("gradient: 7 or 27 points");
     if (v == 27 && h->desc.ndim != 3) return fail("the 27-point gradient is three-dimensional");
@@ -590,6 +596,7 @@ extern "C" long b200lb_get_option(const b200lb_t * h, const char * name) {
   if (!strcmp(name, "grad_lazy")) return h->opt_grad_lazy;
   if (!strcmp(name, "gradient")) return h->opt_gradient;
   if (!strcmp(name, "ch_fuse")) return h->opt_ch_fuse;
+  if (!strcmp(name, "ch_planes")) return h->opt_ch_planes;
   if (!strcmp(name, "p2p")) return h->opt_p2p;
   if (!strcmp(name, "p2p_ready")) return h->p2p_ready;
   if (!strcmp(name, "loopback")) return h->opt_loopback;
@@ -1637,6 +1644,7 @@ static int ch_run(b200lb_s * h, bool do_force, bool do_update) {
   P.accumulate = h->force_uniform ? 0 : 1;
   P.order = h->ch_order;
   P.method = h->ch_method;
+  P.nx = h->opt_ch_planes;
   CU(ch_launch(P, do_force, do_update, h->s_main));
   h->launches++;
   if (do_force) h->force_uniform = false;

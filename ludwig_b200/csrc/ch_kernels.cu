@@ -24,7 +24,7 @@
 
 #define CH_TZ 64
 #define CH_TY 4
-#define CH_NX 8      // x-planes per block: neighbours along x are re-read through L1
+#define CH_NX 8      // default x-planes per block (ChParams.nx): neighbours along x are re-read through L1
 
 struct Symm { double a, b, kappa; };
 
@@ -88,8 +88,8 @@ ch_kernel(const ChParams P) {
   const int i2 = blockIdx.x*CH_TZ + threadIdx.x;
   const int i1 = blockIdx.y*CH_TY + threadIdx.y;
   if (i2 >= L.n[2] || i1 >= L.n[1]) return;
-  const int x0 = blockIdx.z*CH_NX;
-  const int x1 = min(x0 + CH_NX, L.n[0]);
+  const int x0 = blockIdx.z*P.nx;
+  const int x1 = min(x0 + P.nx, L.n[0]);
 
   const Symm S = {P.A, P.B, P.kappa};
   const int c1 = i1 + L.h[1], c2 = i2 + L.h[2];
@@ -230,7 +230,8 @@ template <int METHOD, int ORDER>
 static cudaError_t launch(const ChParams & P, cudaStream_t st) {
   const Layout & L = P.L;
   dim3 block(CH_TZ, CH_TY, 1);
-  dim3 grid((L.n[2] + CH_TZ - 1)/CH_TZ, (L.n[1] + CH_TY - 1)/CH_TY, (L.n[0] + CH_NX - 1)/CH_NX);
+  if (P.nx < 1) return cudaErrorInvalidValue;
+  dim3 grid((L.n[2] + CH_TZ - 1)/CH_TZ, (L.n[1] + CH_TY - 1)/CH_TY, (L.n[0] + P.nx - 1)/P.nx);
   ch_kernel<METHOD, ORDER><<<grid, block, 0, st>>>(P);
   return cudaGetLastError();
 }

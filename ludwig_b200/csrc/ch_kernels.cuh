@@ -27,6 +27,7 @@ struct ChParams {
   int accumulate;         // 1: force += , 0: force = fconst +
   int order;              // advection scheme: 1, 2, 3
   int method;             // CH_FORCE_*
+  int nx;                 // x-planes marched by one block
 };
 
 // do_force: phi_force_calculation; do_update: phi_cahn_hilliard. One pass does both.

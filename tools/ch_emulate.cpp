@@ -57,7 +57,7 @@ static void to_host(const Layout & L, const std::vector<double> & dev, int nf, d
 template <int METHOD, int ORDER>
 static void run(const ChParams & P) {
   const Layout & L = P.L;
-  const unsigned gx = (L.n[2] + CH_TZ - 1)/CH_TZ, gy = (L.n[1] + CH_TY - 1)/CH_TY, gz = (L.n[0] + CH_NX - 1)/CH_NX;
+  const unsigned gx = (L.n[2] + CH_TZ - 1)/CH_TZ, gy = (L.n[1] + CH_TY - 1)/CH_TY, gz = (L.n[0] + P.nx - 1)/P.nx;
   for (unsigned bz = 0; bz < gz; bz++) for (unsigned by = 0; by < gy; by++) for (unsigned bx = 0; bx < gx; bx++)
     for (unsigned ty = 0; ty < CH_TY; ty++) for (unsigned tx = 0; tx < CH_TZ; tx++) {
       blockIdx.x = bx; blockIdx.y = by; blockIdx.z = bz;
@@ -95,7 +95,7 @@ extern "C" int ch_emulate(const int nlocal[3], const int wrap[3], int method, in
   P.phi = dphi.data(); P.grad = dgrad.data(); P.delsq = ddelsq.data(); P.u = du.data();
   P.force = dforce.data(); P.phi_out = dout.data();
   P.A = prm[0]; P.B = prm[1]; P.kappa = prm[2]; P.mobility = prm[3];
-  P.accumulate = accumulate; P.order = order; P.method = method;
+  P.accumulate = accumulate; P.order = order; P.method = method; P.nx = 3;
   int rc = -1;
   if (method == 0 || method == CH_FORCE_NONE) rc = run_order<0>(P, order);
   if (method == CH_FORCE_STRESS_DIVERGENCE) rc = run_order<CH_FORCE_STRESS_DIVERGENCE>(P, order);
