@@ -157,7 +157,7 @@ struct b200lb_s {
   bool ghost;
 
   // options
-  int opt_fused, opt_halo, opt_hydro_write, opt_vec, opt_block, opt_halo_lazy, opt_overlap, opt_direct, opt_diag, opt_loopback, opt_grad_lazy, opt_p2p, opt_gradient, opt_ch_fuse, opt_ch_planes;
+  int opt_fused, opt_halo, opt_hydro_write, opt_vec, opt_block, opt_halo_lazy, opt_overlap, opt_direct, opt_diag, opt_loopback, opt_grad_lazy, opt_p2p, opt_gradient, opt_ch_fuse, opt_ch_planes, opt_ch_exact;
 
   cudaStream_t s_main, s_x[2];
   cudaStream_t s_comm;       // halo exchange of decomposed directions (overlaps the interior sweep)
@@ -477,6 +477,7 @@ static int create_impl(const b200lb_desc_t * desc, b200lb_s * h, const ModelOps 
   h->opt_p2p = 1;
   h->opt_ch_fuse = 1;
   h->opt_ch_planes = 8;
+  h->opt_ch_exact = 0;
 
   b200lb_param_t p0;
   memset(&p0, 0, sizeof(p0));
@@ -546,6 +547,11 @@ extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
     h->opt_ch_fuse = (v != 0);
     return 0;
   }
+  if (!strcmp(name, "ch_exact")) {
+    if (resolve_ch_force(h)) return -1;
+    h->opt_ch_exact = (v != 0);
+    return 0;
+  }
   if (!strcmp(name, "ch_planes")) {
     if (v < 1 || v > 4096) return fail("ch_planes: x-planes marched by one block of the order-parameter kernel, 1..4096");
     h->opt_ch_planes = (int) v;
@@ -597,6 +603,7 @@ extern "C" long b200lb_get_option(const b200lb_t * h, const char * name) {
   if (!strcmp(name, "gradient")) return h->opt_gradient;
   if (!strcmp(name, "ch_fuse")) return h->opt_ch_fuse;
   if (!strcmp(name, "ch_planes")) return h->opt_ch_planes;
+  if (!strcmp(name, "ch_exact")) return h->opt_ch_exact;
   if (!strcmp(name, "p2p")) return h->opt_p2p;
   if (!strcmp(name, "p2p_ready")) return h->p2p_ready;
   if (!strcmp(name, "loopback")) return h->opt_loopback;
@@ -1645,7 +1652,8 @@ static int ch_run(b200lb_s * h, bool do_force, bool do_update) {
   P.order = h->ch_order;
   P.method = h->ch_method;
   P.nx = h->opt_ch_planes;
-  CU(ch_launch(P, do_force, do_update, h->s_main));
+  CU(h->opt_ch_exact ? ch_launch_exact(P, do_force, do_update, h->s_main)
+     : ch_launch_fast(P, do_force, do_update, h->s_main));
   h->launches++;
   if (do_force) h->force_uniform = false;
   if (do_update) {

@@ -13,14 +13,28 @@
 // neighbours (phi two sites out for the third-order scheme), evaluates stress,
 // chemical potential and the six face fluxes in registers, and writes the force (24 B)
 // and the new phi (8 B): 64 B read + 32 B written per site, nothing else touches HBM.
-// A face flux is evaluated by both sites that share the face from the same operands in
-// the same order, so the two values are identical and phi is conserved exactly as in
-// the reference (which also stores fw and fe separately).
 //
-// Compiled with -fmad=false: every operation is rounded on its own and the expressions
-// keep the reference's order, so force and phi agree with it bit for bit.
+// Conservation. A face flux is evaluated by both sites that share the face, by the same
+// function (ch_face) from the same operands, every operation in it an explicit
+// intrinsic: the two values are identical bit for bit, whatever the compiler does
+// around them, and phi is conserved to round-off with no flux arrays. (The reference
+// stores "west" and "east" fluxes separately and relies on the same identity.)
+//
+// This file is compiled twice (csrc/Makefile):
+//   CH_EXACT = 1, -fmad=false   every operation rounded on its own, in the reference's
+//       order: force and phi agree with the reference BIT FOR BIT (option "ch_exact").
+//       348 FP64 instructions per site: the FP64 pipe, not HBM, is the floor (ncu:
+//       profiles/r1_ncu_ch_kernel_exact_256.txt).
+//   CH_EXACT = 0   the default: fused multiply-add, and the divergence of the stress
+//       taken as -(1/2) sum_b [P_ab(r + b) - P_ab(r - b)] -- the central value, which the
+//       reference adds and subtracts (src/phi_force_colloid.c:386-466), never formed.
+//       Agrees with the exact build to a few ulp.
 
 #include "ch_kernels.cuh"
+
+#ifndef CH_EXACT
+#define CH_EXACT 1
+#endif
 
 #define CH_TZ 64
 #define CH_TY 4
@@ -28,9 +42,21 @@
 
 struct Symm { double a, b, kappa; };
 
-// fe_symm_mu, src/symmetric.c:307-320
+// a*b + c: one rounding in the fast build, two (as the reference's C) in the exact one.
+// Used with __dmul_rn / __dadd_rn, which no compiler pass fuses or reorders.
+__device__ __forceinline__ double ch_mad(double a, double b, double c) {
+#if CH_EXACT
+  return __dadd_rn(__dmul_rn(a, b), c);
+#else
+  return __fma_rn(a, b, c);
+#endif
+}
+
+// fe_symm_mu, src/symmetric.c:307-320: a phi + b phi phi phi - kappa delsq
 __device__ __forceinline__ double ch_mu(const Symm & s, double phi, double delsq) {
-  return s.a*phi + s.b*phi*phi*phi - s.kappa*delsq;
+  const double t1 = __dmul_rn(s.a, phi);
+  const double t2 = __dmul_rn(__dmul_rn(s.b, phi), phi);
+  return ch_mad(-s.kappa, delsq, ch_mad(t2, phi, t1));
 }
 
 // the isotropic part of fe_symm_str_v, src/symmetric.c:404-407
@@ -44,30 +70,33 @@ __device__ __forceinline__ double ch_pab(const Symm & s, double p0, const double
   return ((ia == ib) ? p0 : 0.0) + s.kappa*g[ia]*g[ib];
 }
 
-// One face of advection_x (src/advection.c). The flux is stored at the site whose
-// order parameter is phi0; the face lies between it and the site of phi1; phim and phi2
-// are the sites beyond (behind phi0, beyond phi1). west: the face is the lower x face
-// (upwind of it is phi1's side when u > 0), otherwise an upper face (when u < 0).
+// The flux through the face between site A and the next site B along an axis:
+// advection_x (src/advection.c: first order upwind :542, centred :790, the three-point
+// upwind-biased stencil :977), then - M (mu_B - mu_A) (phi_ch_flux_mu1_kernel,
+// src/phi_cahn_hilliard.c:349) and - M grad mu^ext (:1404). Am and Bp are the sites
+// beyond A and B. The reference computes this twice per face -- as the "east"/y/z flux
+// of A and as the "west" flux of B, or as the y/z flux fy[index - ys] read back -- with
+// the operands in these roles; sums are commutative, so the one function serves both.
 template <int ORDER>
-__device__ __forceinline__ double ch_adv(bool west, double u0, double u1, double phim,
-					 double phi0, double phi1, double phi2) {
+__device__ __forceinline__ double ch_face(double uA, double uB, double phAm, double phA,
+					  double phB, double phBp, double muA, double muB,
+					  double M, double Mgmu) {
+  double adv;
   if (ORDER == 1) {
-    const double u = 0.5*(u0 + u1);
-    double ph = phi0;
-    if (west ? (u > 0.0) : (u < 0.0)) ph = phi1;
-    return u*ph;
+    const double u = __dmul_rn(0.5, __dadd_rn(uA, uB));
+    adv = __dmul_rn(u, (u > 0.0) ? phA : phB);
   }
-  if (ORDER == 2) {
-    if (west) return 0.5*(u0 + u1)*0.5*(phi1 + phi0);
-    return 0.5*(u0 + u1)*0.5*(phi0 + phi1);
+  else if (ORDER == 2) {
+    adv = __dmul_rn(__dmul_rn(__dmul_rn(0.5, __dadd_rn(uA, uB)), 0.5), __dadd_rn(phA, phB));
   }
-  {
+  else {
     const double a1 = -0.213933, a2 = 0.927865, a3 = 0.286067;
-    const double u = 0.5*(u0 + u1);
-    double fd1 = phim, fd2 = phi0, fd3 = phi1;
-    if (west ? (u > 0.0) : (u < 0.0)) { fd1 = phi2; fd2 = phi1; fd3 = phi0; }
-    return u*(a1*fd1 + a2*fd2 + a3*fd3);
+    const double u = __dmul_rn(0.5, __dadd_rn(uA, uB));
+    const bool up = (u > 0.0);
+    const double fd1 = up ? phAm : phBp, fd2 = up ? phA : phB, fd3 = up ? phB : phA;
+    adv = __dmul_rn(u, ch_mad(a3, fd3, ch_mad(a2, fd2, __dmul_rn(a1, fd1))));
   }
+  return __dadd_rn(ch_mad(-M, __dadd_rn(muB, -muA), adv), -Mgmu);
 }
 
 // offset (in sites) from halo-inclusive coordinate c to c + o along an axis of interior
@@ -81,7 +110,7 @@ __device__ __forceinline__ int ch_off(int c, int n, int wrap, int o) {
 // METHOD: 0 = no force pass, CH_FORCE_STRESS_DIVERGENCE, CH_FORCE_PHI_GRADMU
 // ORDER:  0 = no update pass, 1..3 = advection scheme of the Cahn-Hilliard update
 template <int METHOD, int ORDER>
-__global__ void __launch_bounds__(CH_TZ*CH_TY)
+__global__ void __launch_bounds__(CH_TZ*CH_TY, CH_EXACT ? 2 : 3)
 ch_kernel(const ChParams P) {
 
   const Layout & L = P.L;
@@ -135,7 +164,9 @@ ch_kernel(const ChParams P) {
     if (METHOD == CH_FORCE_STRESS_DIVERGENCE) {
       // F_a = - d_b P_ab, the stress interpolated to the faces:
       // pth_force_fluid_kernel_v, src/phi_force_colloid.c:366-468
-      double g0[3], g1[3], f[3];
+      double g1[3], f[3];
+#if CH_EXACT
+      double g0[3];
       #pragma unroll
       for (int a = 0; a < 3; a++) g0[a] = __ldg(grad + a*nsd + site);
       const double p00 = ch_p0(S, ph0, dq0, g0);
@@ -158,6 +189,28 @@ ch_kernel(const ChParams P) {
 	  f[a] += 0.5*(ch_pab(S, p0m, g1, a, b) + ch_pab(S, p00, g0, a, b));
 	}
       }
+#else
+      // the central stress cancels between the two faces of a direction:
+      // F_a = -(1/2) sum_b [P_ab(r + b) - P_ab(r - b)]
+      f[0] = f[1] = f[2] = 0.0;
+      #pragma unroll
+      for (int b = 0; b < 3; b++) {
+	#pragma unroll
+	for (int a = 0; a < 3; a++) g1[a] = __ldg(grad + a*nsd + site + d[b][2]);
+	const double kgp = S.kappa*g1[b];
+	f[b] += ch_p0(S, php[b], dqp[b], g1);
+	#pragma unroll
+	for (int a = 0; a < 3; a++) f[a] += kgp*g1[a];
+	#pragma unroll
+	for (int a = 0; a < 3; a++) g1[a] = __ldg(grad + a*nsd + site + d[b][1]);
+	const double kgm = S.kappa*g1[b];
+	f[b] -= ch_p0(S, phm[b], dqm[b], g1);
+	#pragma unroll
+	for (int a = 0; a < 3; a++) f[a] -= kgm*g1[a];
+      }
+      #pragma unroll
+      for (int a = 0; a < 3; a++) f[a] *= -0.5;
+#endif
       #pragma unroll
       for (int a = 0; a < 3; a++) {
 	const double base = P.accumulate ? P.force[a*nsd + site] : P.fconst[a];
@@ -180,46 +233,28 @@ ch_kernel(const ChParams P) {
     }
 
     if (ORDER > 0) {
-      // the six face fluxes of this site: advection_x, then phi_ch_flux_mu1_kernel and
-      // phi_ch_flux_mu_ext_kernel accumulated on top, then phi_ch_ufs_kernel
+      // the six faces of this site, then phi_ch_ufs_kernel (src/phi_cahn_hilliard.c:1025)
       const double M = P.mobility;
       const double mu0 = ch_mu(S, ph0, dq0);
-      double u0[3], um[3], up[3], phm2[3], php2[3];
+      double flo[3], fhi[3];
       #pragma unroll
       for (int a = 0; a < 3; a++) {
-	u0[a] = __ldg(u + a*nsd + site);
-	um[a] = __ldg(u + a*nsd + site + d[a][1]);
-	up[a] = __ldg(u + a*nsd + site + d[a][2]);
-	phm2[a] = (ORDER == 3) ? __ldg(phi + site + d[a][0]) : 0.0;
-	php2[a] = (ORDER == 3) ? __ldg(phi + site + d[a][3]) : 0.0;
+	const double u0 = __ldg(u + a*nsd + site);
+	const double um = __ldg(u + a*nsd + site + d[a][1]);
+	const double up = __ldg(u + a*nsd + site + d[a][2]);
+	const double phm2 = (ORDER == 3) ? __ldg(phi + site + d[a][0]) : 0.0;
+	const double php2 = (ORDER == 3) ? __ldg(phi + site + d[a][3]) : 0.0;
+	const double Mg = __dmul_rn(M, P.gmu[a]);
+	flo[a] = ch_face<ORDER>(um, u0, phm2, phm[a], ph0, php[a], ch_mu(S, phm[a], dqm[a]), mu0, M, Mg);
+	fhi[a] = ch_face<ORDER>(u0, up, phm[a], ph0, php[a], php2, mu0, ch_mu(S, php[a], dqp[a]), M, Mg);
       }
-
-      double fw = ch_adv<ORDER>(true, u0[0], um[0], php[0], ph0, phm[0], phm2[0]);
-      fw -= M*(mu0 - ch_mu(S, phm[0], dqm[0]));
-      fw -= M*P.gmu[0];
-      double fe = ch_adv<ORDER>(false, u0[0], up[0], phm[0], ph0, php[0], php2[0]);
-      fe -= M*(ch_mu(S, php[0], dqp[0]) - mu0);
-      fe -= M*P.gmu[0];
-
-      // upper faces in y and z belong to this site, the lower ones to the site below:
-      // the same expressions with that site in the role of "this"
-      double fhi[3], flo[3];
-      #pragma unroll
-      for (int a = 1; a < 3; a++) {
-	double fl = ch_adv<ORDER>(false, u0[a], up[a], phm[a], ph0, php[a], php2[a]);
-	fl -= M*(ch_mu(S, php[a], dqp[a]) - mu0);
-	fl -= M*P.gmu[a];
-	fhi[a] = fl;
-	fl = ch_adv<ORDER>(false, um[a], u0[a], phm2[a], phm[a], ph0, php[a]);
-	fl -= M*(mu0 - ch_mu(S, phm[a], dqm[a]));
-	fl -= M*P.gmu[a];
-	flo[a] = fl;
-      }
-
-      const double wz = 1.0;
-      double ph = ph0;
-      ph -= (+ fe - fw + fhi[1] - flo[1] + wz*fhi[2] - wz*flo[2]);
-      P.phi_out[site] = ph;
+      // phi -= (+ fe - fw + fy - fy[index - ys] + wz*fz - wz*fz[index - 1]), wz = 1
+      double dphi = __dadd_rn(fhi[0], -flo[0]);
+      dphi = __dadd_rn(dphi, fhi[1]);
+      dphi = __dadd_rn(dphi, -flo[1]);
+      dphi = __dadd_rn(dphi, fhi[2]);
+      dphi = __dadd_rn(dphi, -flo[2]);
+      P.phi_out[site] = __dadd_rn(ph0, -dphi);
     }
   }
 }
@@ -247,7 +282,13 @@ static cudaError_t launch_order(const ChParams & P, int order, cudaStream_t st) 
   return cudaErrorInvalidValue;
 }
 
-cudaError_t ch_launch(const ChParams & P, bool do_force, bool do_update, cudaStream_t st) {
+#if CH_EXACT
+#define CH_LAUNCH ch_launch_exact
+#else
+#define CH_LAUNCH ch_launch_fast
+#endif
+
+cudaError_t CH_LAUNCH(const ChParams & P, bool do_force, bool do_update, cudaStream_t st) {
   const int order = do_update ? P.order : 0;
   int method = do_force ? P.method : 0;
   if (method == CH_FORCE_NONE) method = 0;

@@ -1,6 +1,6 @@
-// ch_kernels.cuh -- launcher of the finite-difference order-parameter kernel
-// (ch_kernels.cu, compiled with -fmad=false so that every product and sum is rounded
-// on its own, as the reference's plain C is).
+// ch_kernels.cuh -- launchers of the finite-difference order-parameter kernel
+// (ch_kernels.cu, compiled twice: ch_launch_exact with -fmad=false and the reference's
+// order of operations -- bit parity --, ch_launch_fast with fused multiply-add).
 
 #pragma once
 
@@ -31,4 +31,5 @@ struct ChParams {
 };
 
 // do_force: phi_force_calculation; do_update: phi_cahn_hilliard. One pass does both.
-cudaError_t ch_launch(const ChParams & P, bool do_force, bool do_update, cudaStream_t st);
+cudaError_t ch_launch_exact(const ChParams & P, bool do_force, bool do_update, cudaStream_t st);
+cudaError_t ch_launch_fast(const ChParams & P, bool do_force, bool do_update, cudaStream_t st);

@@ -5,10 +5,11 @@
 // arithmetic can be compared with the oracle in a container without a GPU
 // (tools/check_ch_kernel_on_host.py). Nothing in ludwig_b200/ links this.
 //
-//   g++ -O1 -ffp-contract=off -w -I/usr/local/cuda/include -shared -fPIC \
-//       -o tools/_ch_emulate.so tools/ch_emulate.cpp
+//   g++ -O1 -ffp-contract=off -w -I/usr/local/cuda/include -shared -fPIC -DCH_EXACT=1 \
+//       -o tools/_ch_emulate_exact.so tools/ch_emulate.cpp        (and -DCH_EXACT=0: _fast.so)
 
 #include <algorithm>
+#include <cmath>
 #include <cstring>
 #include <vector>
 
@@ -16,6 +17,9 @@
 
 static uint3 blockIdx, threadIdx;
 template <class T> static inline T __ldg(const T * p) { return *p; }
+static inline double __dmul_rn(double a, double b) { return a*b; }
+static inline double __dadd_rn(double a, double b) { return a + b; }
+static inline double __fma_rn(double a, double b, double c) { return std::fma(a, b, c); }
 using std::min;
 #ifndef __launch_bounds__
 #define __launch_bounds__(...)

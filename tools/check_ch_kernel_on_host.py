@@ -23,17 +23,24 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 import goldenlib                      # noqa: E402
 from oracle import pyoracle           # noqa: E402
 
-SO = os.path.join(ROOT, "tools", "_ch_emulate.so")
-
-
-def build():
+def build(exact):
+    so = os.path.join(ROOT, "tools", "_ch_emulate_%s.so" % ("exact" if exact else "fast"))
     subprocess.check_call(["g++", "-O1", "-ffp-contract=off", "-w", "-I/usr/local/cuda/include",
-                           "-shared", "-fPIC", "-o", SO, os.path.join(ROOT, "tools", "ch_emulate.cpp")])
+                           "-DCH_EXACT=%d" % exact, "-shared", "-fPIC", "-o", so,
+                           os.path.join(ROOT, "tools", "ch_emulate.cpp")])
+    return so
 
 
-def main():
-    build()
-    E = ctypes.CDLL(SO)
+def same(a, b, exact):
+    """exact build: bit for bit; fast build (fused multiply-add, central stress never
+    formed): a few ulp of the largest value"""
+    if exact:
+        return np.array_equal(a, b)
+    return np.max(np.abs(a - b)) <= 4e-16 * max(np.max(np.abs(b)), 1e-300) + 1e-19
+
+
+def main(exact=1):
+    E = ctypes.CDLL(build(exact))
     dp = ctypes.POINTER(ctypes.c_double)
     g = goldenlib.load_ch()
     P = goldenlib.CH_PHYS
@@ -76,8 +83,11 @@ def main():
                     rc |= E.ch_emulate(*args, 0, order, prm, gm, fc, 0, *ptrs)
                     assert np.array_equal(f1[m], force[m])
                 assert rc == 0
-                okf = np.array_equal(force[m], g[tag + "_force"])
-                okp = np.array_equal(out[m], g[tag + "_phi1"])
+                okf = same(force[m], g[tag + "_force"], exact)
+                okp = same(out[m], g[tag + "_phi1"], exact)
+                if not exact:
+                    # conservation is exact in either build: both sides of a face agree
+                    okp = okp and abs(out[m].sum() - phi[m].sum()) < 1e-13 * m.sum()
                 print("%-6s wrap %s %-6s force %s  phi %s" % (tag, wrap, "fused" if fused else "split",
                                                              "ok" if okf else "DIFF", "ok" if okp else "DIFF"))
                 bad += (not okf) + (not okp)
@@ -87,12 +97,13 @@ def main():
             E.ch_emulate((ctypes.c_int * 3)(*nlocal), (ctypes.c_int * 3)(*wrap), method, 0, prm, gm, fc, 1,
                          *[a.ctypes.data_as(dp) for a in (phi, grad, delsq, u, force, out)])
             if method == 2:
-                ok = np.array_equal(force[m], base[m] + g[tag + "_force"])
+                ok = same(force[m], base[m] + g[tag + "_force"], exact)
                 print("%-6s wrap %s accumulate %s" % (tag, wrap, "ok" if ok else "DIFF"))
                 bad += (not ok)
-    print("FAILED" if bad else "all identical to the reference")
+    print("FAILED" if bad else ("exact build: all identical to the reference" if exact
+                                else "fast build: all within a few ulp of the reference"))
     return bad
 
 
 if __name__ == "__main__":
-    sys.exit(1 if main() else 0)
+    sys.exit(1 if (main(1) + main(0)) else 0)

@@ -1,7 +1,7 @@
 """A few time steps of the finite-difference order-parameter workload (free_energy
 symmetric) on one GPU, without torch: the command ncu wraps for profiles/*_fd_*.csv.
 
-    python tools/run_fd_steps.py [n] [order] [gradient points] [steps] [ch_planes]
+    python tools/run_fd_steps.py [n] [order] [gradient points] [steps] [ch_planes] [ch_exact]
 """
 
 import os
@@ -22,6 +22,7 @@ def main():
     npt = int(sys.argv[3]) if len(sys.argv) > 3 else 27
     steps = int(sys.argv[4]) if len(sys.argv) > 4 else 5
     planes = int(sys.argv[5]) if len(sys.argv) > 5 else 0
+    exact = int(sys.argv[6]) if len(sys.argv) > 6 else 0
     nt = (n, n, n)
     lat = lb.Lattice(19, nt)
     lat.set_option("halo", lb.HALO_REDUCED)
@@ -29,6 +30,7 @@ def main():
                   kappa=0.004)
     lat.phi_ch_create(order, lb.FORCE_STRESS_DIVERGENCE)
     lat.field_grad_set(npt)
+    lat.set_option("ch_exact", exact)
     if planes:
         lat.set_option("ch_planes", planes)
     nall = tuple(x + 2 for x in nt)
@@ -53,9 +55,9 @@ def main():
         lat.phi_force_calculation()
         lat.phi_cahn_hilliard()
     ms_fd = lat.timer_stop()
-    print("fd order %d, %d-point gradient, %d^3, ch_planes %d: %.3f ms/step, %.0f MLUPS, "
+    print("fd order %d, %d-point gradient, %d^3, ch_planes %d, ch_exact %d: %.3f ms/step, %.0f MLUPS, "
           "gradient + force/update alone %.3f ms, sum phi %.10e"
-          % (order, npt, n, lat.get_option("ch_planes"), ms / steps, n**3 * steps / ms / 1e3,
+          % (order, npt, n, lat.get_option("ch_planes"), lat.get_option("ch_exact"), ms / steps, n**3 * steps / ms / 1e3,
              ms_fd / steps, s[0]))
     lat.close()
 
