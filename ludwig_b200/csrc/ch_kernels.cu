@@ -40,6 +40,11 @@
 #define CH_TY 4
 #define CH_NX 8      // default x-planes per block (ChParams.nx): neighbours along x are re-read through L1
 
+// Everything below has internal linkage: the two builds of this file live in one library
+// and must not share a host stub (the kernel also carries CH_EXACT in its name, which is
+// what a profiler shows: ch_kernel<1, ...> is the exact build).
+namespace {
+
 struct Symm { double a, b, kappa; };
 
 // a*b + c: one rounding in the fast build, two (as the reference's C) in the exact one.
@@ -109,8 +114,8 @@ __device__ __forceinline__ int ch_off(int c, int n, int wrap, int o) {
 
 // METHOD: 0 = no force pass, CH_FORCE_STRESS_DIVERGENCE, CH_FORCE_PHI_GRADMU
 // ORDER:  0 = no update pass, 1..3 = advection scheme of the Cahn-Hilliard update
-template <int METHOD, int ORDER>
-__global__ void __launch_bounds__(CH_TZ*CH_TY, CH_EXACT ? 2 : 3)
+template <int EXACT, int METHOD, int ORDER>
+__global__ void __launch_bounds__(CH_TZ*CH_TY, EXACT ? 2 : 3)
 ch_kernel(const ChParams P) {
 
   const Layout & L = P.L;
@@ -259,6 +264,8 @@ ch_kernel(const ChParams P) {
   }
 }
 
+}   // namespace
+
 #ifndef B200LB_KERNEL_SOURCE_ONLY      // tools/ch_emulate.cpp steps through the kernel source on the host
 
 template <int METHOD, int ORDER>
@@ -267,7 +274,7 @@ static cudaError_t launch(const ChParams & P, cudaStream_t st) {
   dim3 block(CH_TZ, CH_TY, 1);
   if (P.nx < 1) return cudaErrorInvalidValue;
   dim3 grid((L.n[2] + CH_TZ - 1)/CH_TZ, (L.n[1] + CH_TY - 1)/CH_TY, (L.n[0] + P.nx - 1)/P.nx);
-  ch_kernel<METHOD, ORDER><<<grid, block, 0, st>>>(P);
+  ch_kernel<CH_EXACT, METHOD, ORDER><<<grid, block, 0, st>>>(P);
   return cudaGetLastError();
 }
 

@@ -66,7 +66,7 @@ static void run(const ChParams & P) {
     for (unsigned ty = 0; ty < CH_TY; ty++) for (unsigned tx = 0; tx < CH_TZ; tx++) {
       blockIdx.x = bx; blockIdx.y = by; blockIdx.z = bz;
       threadIdx.x = tx; threadIdx.y = ty; threadIdx.z = 0;
-      ch_kernel<METHOD, ORDER>(P);
+      ch_kernel<CH_EXACT, METHOD, ORDER>(P);
     }
 }
 
