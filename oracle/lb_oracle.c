@@ -345,6 +345,42 @@ void orc_modes_to_f(const orc_model_t * model, const double * m,
  * All sites are fluid. Writes rho and u (src/collision.c:570-579).
  * ---------------------------------------------------------------------- */
 
+/* Viscosity model (src/collision.c:386-404 with hydro->eta; visc_arrhenius.c): while an
+ * eta array is attached the single-fluid collision takes the shear viscosity of each
+ * site from it, the bulk viscosity in the Newtonian ratio, and every relaxation time
+ * that depends on them (lb_relaxation_time_shear_v/_bulk_v/_ghosts_v). */
+static const double * visc_eta_ = NULL;
+static const orc_visc_t * visc_ = NULL;
+
+int orc_visc_attach(const orc_visc_t * visc, const double * eta) {
+  visc_ = visc;
+  visc_eta_ = eta;
+  return 0;
+}
+const orc_visc_t * orc_visc_attached(const double ** eta) {
+  if (eta) *eta = visc_eta_;
+  return visc_;
+}
+
+/* visc_update_kernel, src/visc_arrhenius.c:185-220 (interior sites) */
+int orc_visc_arrhenius_update(const orc_box_t * box, const orc_visc_t * visc,
+			      const double * phi, double * eta) {
+  for (int ic = 1; ic <= box->nlocal[0]; ic++) {
+    for (int jc = 1; jc <= box->nlocal[1]; jc++) {
+      for (int kc = 1; kc <= box->nlocal[2]; kc++) {
+	const long index = orc_index(box, ic, jc, kc);
+	double phi0 = phi[index];
+	double etaplus, etaminus;
+	phi0 = phi0/visc->phistar;
+	etaminus = pow(visc->eta_minus, 0.5*(1.0 - phi0));
+	etaplus  = pow(visc->eta_plus,  0.5*(1.0 + phi0));
+	eta[index] = etaminus*etaplus;
+      }
+    }
+  }
+  return 0;
+}
+
 int orc_collide_mrt(const orc_model_t * model, const orc_box_t * box,
 		    const orc_param_t * prm, int ndist, double * f,
 		    const double * force, double * rho, double * u) {
@@ -359,14 +395,21 @@ int orc_collide_mrt(const orc_model_t * model, const orc_box_t * box,
 
   if (orc_rtau(model, prm, rtau) != 0) return -1;
   if (nstate && nvel - model->nhydro > 10) return -1;
+  if (nstate && visc_eta_) return -1;     /* noise variances follow one viscosity */
 
-  #pragma omp parallel for schedule(static)
+  #pragma omp parallel for schedule(static) firstprivate(rtau)
   for (long index = first; index < last; index++) {
     double m[ORC_NVELMAX];
     double fl[3], ul[3], rl;
     double * fs = f + (index*ndist + 0)*nvel;
     for (int a = 0; a < 3; a++) {
       fl[a] = prm->force_global[a] + force[3*index + a];
+    }
+    if (visc_eta_) {
+      orc_param_t local = *prm;
+      local.eta_shear = visc_eta_[index];
+      local.eta_bulk = (prm->eta_bulk/prm->eta_shear)*visc_eta_[index];
+      orc_rtau(model, &local, rtau);
     }
     orc_f_to_modes(model, fs, m);
     if (nstate) {

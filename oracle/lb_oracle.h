@@ -186,6 +186,20 @@ int orc_phi_force(const orc_box_t * box, const orc_param_t * prm, const orc_ch_t
 int orc_cahn_hilliard(const orc_box_t * box, const orc_param_t * prm, const orc_ch_t * ch,
 		      double * phi, double * delsq, double * u);
 
+/* Viscosity model "arrhenius" (src/visc_arrhenius.c): eta = eta_minus^((1 - phi/phistar)/2)
+ * eta_plus^((1 + phi/phistar)/2). While an eta array is attached, orc_collide_mrt takes each
+ * site's viscosity from it (src/collision.c:386-404); with parameters attached as well,
+ * orc_step refreshes eta from phi ahead of every collision (src/ludwig.c:794). */
+typedef struct orc_visc_s {
+  double eta_plus;
+  double eta_minus;
+  double phistar;
+} orc_visc_t;
+int orc_visc_attach(const orc_visc_t * visc, const double * eta);
+const orc_visc_t * orc_visc_attached(const double ** eta);
+int orc_visc_arrhenius_update(const orc_box_t * box, const orc_visc_t * visc,
+			      const double * phi, double * eta);
+
 int orc_fill(const orc_box_t * box, int nf, const double * v, double * data);
 
 /* stats[0..7] = sum rho, sum rho^2 (about mean is left to caller), min, max,

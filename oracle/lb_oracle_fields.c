@@ -414,6 +414,12 @@ int orc_step(const orc_model_t * model, const orc_box_t * box,
       if (orc_cahn_hilliard(box, prm, ch, phi, delsq, u)) return -1;
     }
     orc_fill(box, 3, zero, u);
+    {
+      const double * eta = NULL;
+      const orc_visc_t * visc = orc_visc_attached(&eta);
+      /* src/ludwig.c:794: the model's update ahead of the collision */
+      if (visc && eta && phi) orc_visc_arrhenius_update(box, visc, phi, (double *) eta);
+    }
     if (ndist == 1) {
       if (orc_collide_mrt(model, box, prm, 1, a, force, rho, u)) return -1;
     }

@@ -85,6 +85,11 @@ class CahnHilliard(ctypes.Structure):
     ]
 
 
+class Visc(ctypes.Structure):
+    _fields_ = [("eta_plus", ctypes.c_double), ("eta_minus", ctypes.c_double),
+                ("phistar", ctypes.c_double)]
+
+
 class Box(ctypes.Structure):
     _fields_ = [
         ("nlocal", ctypes.c_int * 3),
@@ -284,6 +289,23 @@ class Oracle:
         rc = self.L.orc_cahn_hilliard(ctypes.byref(self.box), ctypes.byref(prm), ctypes.byref(ch),
                                       _p(phi), _p(delsq), _p(u))
         assert rc == 0
+
+    # -- viscosity model (src/visc_arrhenius.c, src/collision.c:386-404) --------------
+    def visc_attach(self, eta, eta_plus=None, eta_minus=None, phistar=1.0):
+        """Collisions take each site's viscosity from eta[nsite] (None: off); with the
+        Arrhenius parameters orc_step refreshes eta from phi ahead of each collision."""
+        self._eta = eta
+        self._visc = None
+        if eta is None:
+            self.L.orc_visc_attach(None, None)
+            return
+        if eta_plus is not None:
+            self._visc = Visc(eta_plus, eta_minus, phistar)
+        self.L.orc_visc_attach(None if self._visc is None else ctypes.byref(self._visc), _p(eta))
+
+    def visc_arrhenius_update(self, eta_plus, eta_minus, phistar, phi, eta):
+        v = Visc(eta_plus, eta_minus, phistar)
+        self.L.orc_visc_arrhenius_update(ctypes.byref(self.box), ctypes.byref(v), _p(phi), _p(eta))
 
     # -- flat walls (oracle/lb_oracle_wall.c) ---------------------------------------
     def wall(self, isboundary, ubot=(0.0, 0.0, 0.0), utop=(0.0, 0.0, 0.0), sbot=None, stop=None,

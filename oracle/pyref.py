@@ -43,7 +43,7 @@ def _lib(nvel):
     if nvel not in _libs:
         L = ctypes.CDLL(_path(nvel))
         for name in ("refdrv_f", "refdrv_rho", "refdrv_u", "refdrv_force",
-                     "refdrv_phi", "refdrv_grad", "refdrv_delsq"):
+                     "refdrv_phi", "refdrv_grad", "refdrv_delsq", "refdrv_eta"):
             getattr(L, name).restype = c_double_p
         L.refdrv_status.restype = ctypes.POINTER(ctypes.c_char)
         L.refdrv_step.restype = ctypes.c_double
@@ -255,6 +255,17 @@ class Ref:
 
     def grad_mu(self, gm):
         self.L.refdrv_grad_mu((ctypes.c_double * 3)(*gm))
+
+    def visc_arrhenius(self, eta_plus, eta_minus, phistar):
+        """viscosity_model arrhenius (needs the order parameter: fd=... or ndist=2)."""
+        self.L.refdrv_visc_arrhenius.argtypes = [ctypes.c_double] * 3
+        assert self.L.refdrv_visc_arrhenius(eta_plus, eta_minus, phistar) == 0
+
+    def visc_update(self):
+        self.L.refdrv_visc_update()
+
+    def eta(self):
+        return self._arr(self.L.refdrv_eta(), (self.nsite,))
 
     def grad_select(self, npt):
         assert self.L.refdrv_grad_select(int(npt)) == 0

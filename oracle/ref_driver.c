@@ -63,6 +63,8 @@
 #include "phi_force_stress.h"
 #include "advection.h"
 #include "fe_force_method.h"
+#include "visc.h"
+#include "visc_arrhenius.h"
 
 typedef struct refdrv_s {
   pe_t * pe;
@@ -79,6 +81,7 @@ typedef struct refdrv_s {
   wall_t * wall;
   pth_t * pth;
   phi_ch_t * pch;
+  visc_t * visc;
   int nhalo;
   int nplanes;
   int ndist;
@@ -199,6 +202,7 @@ int refdrv_init(const int ntotal[3], int ndist, int halo_scheme) {
 
 int refdrv_finish(void) {
 
+  if (rd.visc) rd.visc->func->free(rd.visc);
   if (rd.pch) phi_ch_free(rd.pch);
   if (rd.pth) pth_free(rd.pth);
   if (rd.wall) wall_free(rd.wall);
@@ -297,8 +301,21 @@ int refdrv_equilib_set(int index, double rho, const double u[3]) {
 /* Individual stages: each is the reference's public entry point */
 
 int refdrv_collide(void) {
-  return lb_collide(rd.lb, rd.hydro, rd.map, rd.noise, (fe_t *) rd.fe, NULL);
+  return lb_collide(rd.lb, rd.hydro, rd.map, rd.noise, (fe_t *) rd.fe, rd.visc);
 }
+
+/* "viscosity_model arrhenius" (src/ludwig.c:2001-2040): needs the order parameter */
+int refdrv_visc_arrhenius(double eta_plus, double eta_minus, double phistar) {
+  visc_arrhenius_param_t param = {0};
+  visc_arrhenius_t * visc = NULL;
+  if (rd.phi == NULL) return -1;
+  param.eta_plus = eta_plus; param.eta_minus = eta_minus; param.phistar = phistar;
+  visc_arrhenius_create(rd.pe, rd.cs, rd.phi, param, &visc);
+  rd.visc = (visc_t *) visc;
+  return 0;
+}
+int refdrv_visc_update(void) { return rd.visc->func->update(rd.visc, rd.hydro); }
+double * refdrv_eta(void) { return rd.hydro->eta->data; }
 
 int refdrv_halo(int scheme) {
   if (scheme < 0) return lb_halo(rd.lb);
@@ -430,7 +447,8 @@ double refdrv_step(int nsteps) {
       phi_cahn_hilliard(rd.pch, (fe_t *) rd.fe, rd.phi, rd.hydro, rd.map, NULL);
     }
     hydro_u_zero(rd.hydro, zero);
-    lb_collide(rd.lb, rd.hydro, rd.map, rd.noise, (fe_t *) rd.fe, NULL);
+    if (rd.visc) rd.visc->func->update(rd.visc, rd.hydro);      /* src/ludwig.c:794 */
+    lb_collide(rd.lb, rd.hydro, rd.map, rd.noise, (fe_t *) rd.fe, rd.visc);
     if (rd.nplanes > 0) lb_le_apply_boundary_conditions(rd.lb, rd.le);   /* src/ludwig.c:810 */
     lb_halo(rd.lb);
     if (rd.wall && wall_present(rd.wall)) {                      /* src/ludwig.c:837-842 */

@@ -588,3 +588,95 @@ def test_cahn_hilliard_time_loop(order, method, npt, gmu):
         assert relerr(f[m], fr[m]) < 1e-12
         assert relerr(phi[m], ref.inner(ref.phi()).reshape(-1)[m]) < 1e-13
         assert relerr(u[m], ref.inner(ref.u()).reshape(-1, 3)[m]) < 1e-11
+
+
+# ---------------------------------------------------------------------------
+# viscosity model: lb_collide with hydro->eta (src/collision.c:386-404), visc_arrhenius.c
+# ---------------------------------------------------------------------------
+
+VISC = dict(eta_plus=0.625, eta_minus=0.00625, phistar=1.0)
+
+
+@pytest.mark.parametrize("nrelax", [pyoracle.RELAX_M10, pyoracle.RELAX_BGK, pyoracle.RELAX_TRT])
+def test_viscosity_model_collision(nrelax):
+    """visc_arrhenius_update + one collision with a per-site viscosity, every scheme."""
+    nvel, nlocal = 19, (10, 8, 6)
+    need_ref(nvel)
+    A, B, K, M, eta, zeta = -0.00625, 0.00625, 0.004, 1.25, 0.00625, 0.0125
+    orc = pyoracle.Oracle(nvel, nlocal)
+    prm = pyoracle.make_param(eta_shear=eta, eta_bulk=zeta, mobility=M, a=A, b=B, kappa=K,
+                              nrelax=nrelax)
+    f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal)
+    force = lbinit.make_force(nlocal)
+    phi, _ = fd_fields(nlocal)
+    phi *= 2.0                                      # spans most of (-phistar, phistar)
+    n = orc.nsite
+    m = orc.interior_mask()
+    with pyref.Ref(nvel, nlocal, fd=dict(order=1, method=2)) as ref:
+        ref.physics(eta_shear=eta, eta_bulk=zeta, mobility=M)
+        ref.fe_symm(A, B, K)
+        ref.relaxation(nrelax)
+        ref.visc_arrhenius(**VISC)
+        ref.inner(ref.f())[...] = f0.reshape(orc.nall + (1, nvel))
+        ref.inner(ref.force())[...] = force.reshape(orc.nall + (3,))
+        ref.inner(ref.phi())[...] = phi.reshape(orc.nall)
+        ref.visc_update()
+        eta_site = np.zeros(n)
+        orc.visc_arrhenius_update(VISC["eta_plus"], VISC["eta_minus"], VISC["phistar"], phi, eta_site)
+        er = ref.inner(ref.eta()).reshape(-1)
+        assert np.array_equal(eta_site[m], er[m])
+        assert eta_site[m].max() / eta_site[m].min() > 10.0
+        ref.collide()
+        f = f0.copy()
+        rho, u = np.zeros(n), np.zeros((n, 3))
+        orc.visc_attach(eta_site)
+        try:
+            orc.collide_mrt(prm, f, force, rho, u)
+        finally:
+            orc.visc_attach(None)
+        fr = ref.inner(ref.f()).reshape(n, 1, nvel)
+        assert relerr(f[m], fr[m]) < 1e-13
+        # and it matters: the uniform-viscosity collision differs
+        g = f0.copy()
+        orc.collide_mrt(prm, g, force, rho, u)
+        assert relerr(g[m], fr[m]) > 1e-6
+
+
+def test_viscosity_model_time_loop():
+    """free_energy symmetric + viscosity_model arrhenius, six steps (src/ludwig.c:727-803)."""
+    nvel, nlocal, nsteps = 19, (8, 8, 8), 6
+    need_ref(nvel)
+    A, B, K, M, eta = -0.00625, 0.00625, 0.004, 1.25, 0.00625
+    orc = pyoracle.Oracle(nvel, nlocal)
+    prm = pyoracle.make_param(eta_shear=eta, eta_bulk=eta, mobility=M, a=A, b=B, kappa=K)
+    ch = orc.ch(2, pyoracle.FORCE_STRESS_DIVERGENCE)
+    f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal)
+    phi, _ = fd_fields(nlocal)
+    phi *= 2.0
+    n = orc.nsite
+    with pyref.Ref(nvel, nlocal, fd=dict(order=2, method=2)) as ref:
+        ref.physics(eta_shear=eta, eta_bulk=eta, mobility=M)
+        ref.fe_symm(A, B, K)
+        ref.grad_select(27)
+        ref.visc_arrhenius(**VISC)
+        ref.inner(ref.f())[...] = f0.reshape(orc.nall + (1, nvel))
+        ref.inner(ref.phi())[...] = phi.reshape(orc.nall)
+        ref.step(nsteps)
+        f, fp = f0.copy(), np.zeros_like(f0)
+        rho, u, force = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
+        grad, delsq, eta_site = np.zeros((n, 3)), np.zeros(n), np.zeros(n)
+        orc.gradient_select(27)
+        orc.ch_attach(ch)
+        orc.visc_attach(eta_site, **VISC)
+        try:
+            orc.step(prm, nsteps, f, fp, rho, u, force, phi, grad, delsq)
+        finally:
+            orc.ch_attach(None)
+            orc.visc_attach(None)
+            orc.gradient_select(7)
+        m = orc.interior_mask()
+        fr = ref.inner(ref.f()).reshape(n, 1, nvel)
+        assert relerr(f[m], fr[m]) < 1e-12
+        assert relerr(phi[m], ref.inner(ref.phi()).reshape(-1)[m]) < 1e-13
+        assert np.array_equal(eta_site[m], ref.inner(ref.eta()).reshape(-1)[m]) or \
+            relerr(eta_site[m], ref.inner(ref.eta()).reshape(-1)[m]) < 1e-13

@@ -237,6 +237,15 @@ def fd_options(inp):
     return int(inp.get("fd_advection_scheme_order", 1)), method, gmu
 
 
+def visc_model(inp):
+    """viscosity_model arrhenius (src/ludwig.c:2001-2040) or None"""
+    if inp.get("viscosity_model") != "arrhenius":
+        return None
+    return dict(eta_plus=float(inp["viscosity_arrhenius_eta_plus"]),
+                eta_minus=float(inp["viscosity_arrhenius_eta_minus"]),
+                phistar=float(inp["viscosity_arrhenius_phistar"]))
+
+
 def initial_phi(inp, nt):
     """phi_initialisation (src/field_phi_init_rt.c:40-160) on the interior, [nt]."""
     key = inp.get("phi_initialisation", "spinodal")
@@ -316,6 +325,8 @@ def test_oracle_reproduces_reference_log(case):
     if fd_route(rec):
         phi.reshape(orc.nall)[1:-1, 1:-1, 1:-1] = initial_phi(rec["input"], nt)
         orc.ch_attach(orc.ch(*fd_options(rec["input"])))
+    if visc_model(rec["input"]):
+        orc.visc_attach(np.zeros(n), **visc_model(rec["input"]))
     try:
         orc.step(prm, int(rec["input"]["N_cycles"]), f, fp, rho, u, frc, phi, grad, delsq)
     finally:
@@ -323,6 +334,7 @@ def test_oracle_reproduces_reference_log(case):
         orc.gradient_select(7)
         orc.wall_attach(None)
         orc.ch_attach(None)
+        orc.visc_attach(None)
     m = orc.interior_mask()
     sums = orc.stats(f)
     if case in LONG:
@@ -374,6 +386,8 @@ def test_cuda_reproduces_reference_log(case, hydro_write):
         phi0 = np.zeros(tuple(n + 2 for n in nt))
         phi0[1:-1, 1:-1, 1:-1] = initial_phi(rec["input"], nt)
         lat.field_h2d(lb.FIELD_PHI, np.ascontiguousarray(phi0.reshape(-1)))
+    if visc_model(rec["input"]):
+        lat.visc_arrhenius_commit(**visc_model(rec["input"]))
     lat.step(int(rec["input"]["N_cycles"]))
     sums = lat.stats()                               # lb_memcpy D2H + stats_distribution_print
     u = lat.field_d2h(lb.FIELD_U)                    # hydro_memcpy D2H + stats_velocity_minmax
