@@ -50,7 +50,8 @@ enum {
   B200LB_FIELD_FORCE = 2,    /* 3 */
   B200LB_FIELD_PHI = 3,      /* 1 */
   B200LB_FIELD_GRAD = 4,     /* 3 */
-  B200LB_FIELD_DELSQ = 5     /* 1 */
+  B200LB_FIELD_DELSQ = 5,    /* 1 */
+  B200LB_FIELD_ETA = 6       /* 1: hydro->eta, the per-site shear viscosity of a viscosity model */
 };
 
 typedef struct b200lb_s b200lb_t;        /* opaque handle: one local lattice */
@@ -214,6 +215,20 @@ int  b200lb_ch_grad_mu_set(b200lb_t * h, const double grad_mu[3]);            /*
 int  b200lb_phi_force(b200lb_t * h);                                          /* phi_force_calculation src/phi_force.c:74 */
 int  b200lb_cahn_hilliard(b200lb_t * h);                                      /* phi_cahn_hilliard src/phi_cahn_hilliard.c:206 */
 int  b200lb_hydro_u_halo(b200lb_t * h);                                       /* hydro_u_halo src/hydro.c */
+
+/* Viscosity model ("viscosity_model arrhenius", src/ludwig.c:2001-2040; visc_t src/visc.h).
+ * While a model is present lb_collide (single fluid) takes the shear viscosity of every
+ * site from hydro->eta, the bulk viscosity in the Newtonian ratio eta_bulk/eta_shear, and
+ * all relaxation times that depend on them (src/collision.c:386-404,
+ * lb_relaxation_time_shear_v/_bulk_v/_ghosts_v). b200lb_visc_update is the model's update
+ * (visc->func->update, src/ludwig.c:794): eta = eta_minus^((1 - phi/phistar)/2)
+ * eta_plus^((1 + phi/phistar)/2) from the order parameter (src/visc_arrhenius.c:185-220).
+ * b200lb_visc_model_set(h, 1) alone makes the collision read whatever the caller put in
+ * B200LB_FIELD_ETA (a model evaluated on the host). Not with isothermal fluctuations
+ * (their variances follow one viscosity). b200lb_step runs the update before each collision. */
+int  b200lb_visc_arrhenius_commit(b200lb_t * h, double eta_plus, double eta_minus, double phistar);   /* visc_arrhenius_create src/visc_arrhenius.c:52 */
+int  b200lb_visc_update(b200lb_t * h);                                  /* visc_arrhenius_update src/visc_arrhenius.c:149 */
+int  b200lb_visc_model_set(b200lb_t * h, int on);                       /* lb_collide(..., visc): p.have_visc_model src/collision.c:1954 */
 
 /* Isothermal fluctuations ("isothermal_fluctuations on", src/collision_rt.c:55):
  * every site owns a KISS99 generator seeded from its global position, so results do

@@ -9,6 +9,6 @@ from .lb import (Lattice, Param, B200LBError, build, library_path, load,  # noqa
                  pinned_empty, pinned_free,
                  HOST_AOS, HOST_SOA, RELAX_M10, RELAX_BGK, RELAX_TRT,
                  HALO_FULL, HALO_REDUCED, FIELD_RHO, FIELD_U, FIELD_FORCE,
-                 FIELD_PHI, FIELD_GRAD, FIELD_DELSQ, ABI_SYMBOLS,
+                 FIELD_PHI, FIELD_GRAD, FIELD_DELSQ, FIELD_ETA, ABI_SYMBOLS,
                  FORCE_NONE, FORCE_STRESS_DIVERGENCE, FORCE_PHI_GRADMU)
 from .decomp import Decomposition  # noqa: F401

@@ -130,6 +130,11 @@ struct b200lb_s {
   bool ch_force_pending;     // phi_force_calculation recorded; evaluated by the update's pass
   bool ch_grad_valid;        // grad/delsq belong to the current phi
   bool ch_halo_done;         // ... and their halos in decomposed directions are current
+  // viscosity model (visc_t, src/visc.h; hydro->eta)
+  double * eta;              // [nsd] per-site shear viscosity, or null
+  bool visc_on;              // lb_collide reads eta (p.have_visc_model)
+  bool visc_arrhenius;       // b200lb_visc_update evaluates the Arrhenius model from phi
+  double visc_eta_plus, visc_eta_minus, visc_phistar;
   double * noise;            // [2][nsd] per-site generator state (noise_init), or null
   bool noise_on;             // noise_present_set(NOISE_RHO)
   double nv_diag, nv_off, nv_bulk, nv_ghost[B200LB_MAXNOISE];
@@ -507,7 +512,7 @@ extern "C" int b200lb_destroy(b200lb_t * h) {
     cudaEventDestroy(h->ev_x[i]);
   }
   cudaFree(h->rho); cudaFree(h->u); cudaFree(h->force);
-  cudaFree(h->phi2);
+  cudaFree(h->phi2); cudaFree(h->eta);
   cudaFree(h->phi); cudaFree(h->grad); cudaFree(h->delsq); cudaFree(h->noise); cudaFree(h->fnet_dev); cudaFree(h->le_buf);
   cudaFree(h->partial); cudaFree(h->diag); cudaFree(h->stats_dev); cudaFreeHost(h->stats_host);
   cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
@@ -727,6 +732,7 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
   a.binary = (h->desc.ndist == 2);
   a.ghost = h->ghost;
   a.noise = collide && h->noise_on;
+  a.visc = false;
   if (a.noise) {
     if (h->ops->nvel - h->ops->nhydro > B200LB_MAXNOISE)
       return fail("isothermal fluctuations: the site generator yields %d variates per draw, nvel %d has %d ghost modes (src/noise.h:18)",
@@ -743,6 +749,16 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
     if (h->opt_hydro_write) { if (need_hydro(h)) return -1; }
     if (h->desc.ndist == 2 && h->grad_state == 0) {
       if (need_planes(h, &h->grad, 3) || need_planes(h, &h->delsq, 1)) return -1;
+    }
+    if (h->visc_on) {
+      if (a.binary) return fail("lb_collide: the viscosity model belongs to the single-fluid collision (src/collision.c:386-404)");
+      if (h->noise_on) return fail("lb_collide: a viscosity model with isothermal fluctuations is not on this path");
+      if (need_planes(h, &h->eta, 1)) return -1;
+      a.P.eta = h->eta;
+      a.visc = true;
+      a.P.rho0cs2 = h->prm.rho0*(1.0/3.0);
+      a.P.eta_ratio = h->prm.eta_bulk/h->prm.eta_shear;
+      a.P.visc_relax = h->prm.nrelax;
     }
     a.P.force = h->force_uniform ? nullptr : h->force;
     h->last_ffield = !h->force_uniform;
@@ -1698,6 +1714,42 @@ extern "C" int b200lb_hydro_u_halo(b200lb_t * h) {
 }
 
 // ---------------------------------------------------------------------------
+// viscosity model (src/visc_arrhenius.c; the collision's side is in run_sweep)
+// ---------------------------------------------------------------------------
+
+extern "C" int b200lb_visc_model_set(b200lb_t * h, int on) {
+  if (!h) return fail("null handle");
+  if (on && h->desc.ndist != 1) return fail("viscosity model: the single-fluid collision only (src/collision.c:386-404)");
+  if (on) { if (need_planes(h, &h->eta, 1)) return -1; }
+  h->visc_on = (on != 0);
+  return 0;
+}
+
+extern "C" int b200lb_visc_arrhenius_commit(b200lb_t * h, double eta_plus, double eta_minus, double phistar) {
+  if (!h) return fail("null handle");
+  if (!h->phi) return fail("viscosity_model arrhenius requires a composition (src/ludwig.c:2019): create the order parameter first");
+  if (!(eta_plus > 0.0) || !(eta_minus > 0.0) || phistar == 0.0) return fail("viscosity_model arrhenius: eta_plus, eta_minus > 0 and phistar != 0");
+  if (b200lb_visc_model_set(h, 1)) return -1;
+  h->visc_arrhenius = true;
+  h->visc_eta_plus = eta_plus; h->visc_eta_minus = eta_minus; h->visc_phistar = phistar;
+  return 0;
+}
+
+extern "C" int b200lb_visc_update(b200lb_t * h) {
+  if (!h) return fail("null handle");
+  if (!h->visc_arrhenius) return fail("no viscosity model to update: call b200lb_visc_arrhenius_commit first");
+  if (need_planes(h, &h->eta, 1)) return -1;
+  const Layout & L = h->L;
+  dim3 block(128, 2, 1);
+  dim3 grid((L.n[2] + 127)/128, (L.n[1] + 1)/2, L.n[0]);
+  visc_arrhenius_kernel<<<grid, block, 0, h->s_main>>>(L, h->phi, h->eta, h->visc_eta_plus,
+						       h->visc_eta_minus, h->visc_phistar);
+  CU(cudaGetLastError());
+  h->launches++;
+  return 0;
+}
+
+// ---------------------------------------------------------------------------
 // the time loop of src/ludwig.c:530-862 restricted to the hot path
 // ---------------------------------------------------------------------------
 
@@ -1722,6 +1774,7 @@ extern "C" int b200lb_step(b200lb_t * h, int nsteps) {
       if (b200lb_cahn_hilliard(h)) return -1;
     }
     if (b200lb_hydro_u_zero(h, zero)) return -1;
+    if (h->visc_on && h->visc_arrhenius) { if (b200lb_visc_update(h)) return -1; }     // src/ludwig.c:794
     h->le_step++;                                   // physics_control_next_step, src/ludwig.c:552
     if (b200lb_collide(h)) return -1;
     if (h->prop_pending) return fail("internal: propagation pending after collide");
@@ -1998,6 +2051,7 @@ static int field_info(b200lb_s * h, int field, double ** dev, int * nf) {
   case B200LB_FIELD_PHI:   *dev = h->phi; *nf = 1; break;
   case B200LB_FIELD_GRAD:  if (need_planes(h, &h->grad, 3)) return -1; *dev = h->grad; *nf = 3; break;
   case B200LB_FIELD_DELSQ: if (need_planes(h, &h->delsq, 1)) return -1; *dev = h->delsq; *nf = 1; break;
+  case B200LB_FIELD_ETA:   if (need_planes(h, &h->eta, 1)) return -1; *dev = h->eta; *nf = 1; break;
   default: return fail("unknown field %d", field);
   }
   return 0;

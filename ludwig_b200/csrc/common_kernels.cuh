@@ -293,6 +293,27 @@ grad27_kernel(const Layout L, const int w0, const int w1, const int w2,
 }
 
 // ---------------------------------------------------------------------------
+// viscosity_model arrhenius (visc_update_kernel, src/visc_arrhenius.c:185-220):
+//   eta = eta_minus^((1 - phi/phistar)/2) eta_plus^((1 + phi/phistar)/2), interior sites.
+// 8 B read + 8 B written per site; the collision that follows reads eta back
+// (src/collision.c:397). Device pow is within 2 ulp of the host's.
+// ---------------------------------------------------------------------------
+
+__global__ void __launch_bounds__(256)
+visc_arrhenius_kernel(const Layout L, const double * __restrict__ phi, double * __restrict__ eta,
+		      const double eta_plus, const double eta_minus, const double phistar) {
+  const int i2 = blockIdx.x*blockDim.x + threadIdx.x;
+  const int i1 = blockIdx.y*blockDim.y + threadIdx.y;
+  const int i0 = blockIdx.z;
+  if (i2 >= L.n[2] || i1 >= L.n[1]) return;
+  const i64 site = (i64)(i0 + L.h[0])*L.s0 + (i64)(i1 + L.h[1])*L.s1 + L.z0 + L.h[2] + i2;
+  const double phi0 = __ldg(phi + site)/phistar;
+  const double etaminus = pow(eta_minus, 0.5*(1.0 - phi0));
+  const double etaplus  = pow(eta_plus,  0.5*(1.0 + phi0));
+  eta[site] = etaminus*etaplus;
+}
+
+// ---------------------------------------------------------------------------
 // fills (hydro_field_set, src/hydro.c:381-398) and uniform-plane helpers
 // ---------------------------------------------------------------------------
 

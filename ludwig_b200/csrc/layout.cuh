@@ -46,6 +46,11 @@ struct KParams {
   int lo[3], hi[3];       // sub-box of the interior, 0-based interior coordinates, [lo,hi)
   int wrap[3];            // device axis is periodic within this rank: pulls wrap instead of reading halos
   double rtau_shear, rtau_bulk;
+  // viscosity model (src/collision.c:386-404): per-site shear viscosity, or nullptr
+  const double * eta;     // [nsd] hydro->eta
+  double rho0cs2;         // rho0 cs^2: rtau = 1/(1/2 + eta/(rho0 cs^2))
+  double eta_ratio;       // (eta_bulk/eta_shear) of the Newtonian fluid
+  int visc_relax;         // relaxation scheme, for the ghost rates that follow eta (BGK, TRT)
   double fg[3];           // uniform part of the force: force_global + constant field value
   double rtau2, A, B, kappa;
   double gkeep[B200LB_MAXGHOST];   // 1 - rtau_k for each ghost mode

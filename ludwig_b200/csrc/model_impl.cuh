@@ -22,7 +22,7 @@ static cudaError_t launch_one(SweepArgs & a) {
   else if constexpr (!WALL) {
     if (a.wall) return cudaErrorInvalidValue;
   }
-  constexpr bool GHOST = (GM != 0);
+  constexpr bool GHOST = ((GM & 3) != 0);
   const KParams & P = a.P;
   const int n2 = P.hi[2] - P.lo[2], n1 = P.hi[1] - P.lo[1], n0 = P.hi[0] - P.lo[0];
   a.nblocks = 0;
@@ -83,6 +83,11 @@ static cudaError_t launch_pc(SweepArgs & a) {
     if (!HAVE_BINARY) return cudaErrorInvalidValue;
     if (a.ghost) return launch_one<1, PULL, COLLIDE, HAVE_BINARY, 1>(a);
     return launch_one<1, PULL, COLLIDE, HAVE_BINARY, 0>(a);
+  }
+  if (a.visc) {
+    // viscosity model: one site per thread (two more divides and the site's eta live)
+    if (a.ghost) return launch_one<1, PULL, COLLIDE, false, 5>(a);
+    return launch_one<1, PULL, COLLIDE, false, 4>(a);
   }
   if (a.ghost) return launch_one<1, PULL, COLLIDE, false, 1>(a);
   if (a.vec == 2) return launch_one<2, PULL, COLLIDE, false, 0>(a);

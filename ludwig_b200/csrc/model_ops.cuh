@@ -11,6 +11,7 @@ struct SweepArgs {
   KParams P;
   bool pull, collide, binary, ghost;
   bool noise;         // isothermal fluctuations on (collide only)
+  bool visc;          // viscosity model: per-site relaxation times from P.eta (collide, single fluid)
   bool wall;          // bounce-back on links folded into the pull (pull only)
   bool diag;          // accumulate conserved sums in the sweep (collide only)
   long long nblocks;  // out: blocks launched (= diagnostic partials written)

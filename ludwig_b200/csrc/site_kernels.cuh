@@ -39,17 +39,24 @@ template <bool NC> __device__ __forceinline__ double2 ld2(const double * p) {
 //   sth    thermodynamic stress added to the equilibrium stress (binary fluid,
 //          src/collision.c:833-848), symmetric storage, or nullptr
 // Writes rho and u = (rho u + F/2)/rho (src/collision.c:355-382).
-//   GM     ghost-mode handling: bit 0 = the scheme keeps a fraction of the incoming
+//   GM     bit 2 = viscosity model: relaxation times from the site's viscosity P.eta
+//          (src/collision.c:393-404); ghost-mode handling: bit 0 = the scheme keeps a fraction of the incoming
 //          ghost modes (BGK, TRT), bit 1 = fluctuations: shat (symmetric storage) is
 //          added to the relaxed stress and ghat[k] to ghost mode k
 //          (src/collision.c:526-544)
 // ---------------------------------------------------------------------------
 
+//   rts, rtb   inverse relaxation times of shear and bulk stress at this site
+//   gk2    nullptr: ghost mode k keeps the fraction P.gkeep[k]; with a viscosity model
+//          the fractions follow the site's viscosity: gk2[0] for the modes that relax
+//          with the shear rate (all of them for BGK; k = 0, 4, 8 for TRT), gk2[1] for
+//          the others (lb_relaxation_time_ghosts_v, src/collision.c:1443-1538)
 template <class M, int GM, bool STH>
 __device__ __forceinline__ void
 mrt_site(double (&f)[M::NVEL], const double (&F)[3], const double * sth,
 	 const double * shat, const double * ghat,
-	 const KParams & P, double & rho_out, double (&u)[3]) {
+	 const KParams & P, const double rts, const double rtb, const double * gk2,
+	 double & rho_out, double (&u)[3]) {
 
   constexpr bool GHOST = (GM & 1) != 0;
   constexpr bool NOISE = (GM & 2) != 0;
@@ -62,7 +69,7 @@ mrt_site(double (&f)[M::NVEL], const double (&F)[3], const double * sth,
   constexpr double rdim = 1.0/ND;
 
   // ghost modes of the incoming state (only when some are kept)
-  double mg[(GM != 0) ? NG : 1];
+  double mg[((GM & 3) != 0) ? NG : 1];
   if (GHOST) {
     const GhostTab & T = ghost_tab<M>();
     #pragma unroll
@@ -70,7 +77,8 @@ mrt_site(double (&f)[M::NVEL], const double (&F)[3], const double * sth,
       double s = 0.0;
       #pragma unroll
       for (int p = 0; p < Q; p++) s = fma(T.fwd[k][p], f[p], s);
-      mg[k] = P.gkeep[k]*s;
+      const double keep = (gk2 == nullptr) ? P.gkeep[k] : gk2[(k % 4 == 0) ? 0 : 1];
+      mg[k] = keep*s;
     }
   }
 
@@ -129,14 +137,14 @@ mrt_site(double (&f)[M::NVEL], const double (&F)[3], const double * sth,
     S[sidx<M>(a, a)]   -= rdim*tr_s;
     seq[sidx<M>(a, a)] -= rdim*tr_seq;
   }
-  tr_s = tr_s - P.rtau_bulk*(tr_s - tr_seq);
-  const double fcorr = 2.0 - P.rtau_shear;
+  tr_s = tr_s - rtb*(tr_s - tr_seq);
+  const double fcorr = 2.0 - rts;
   #pragma unroll
   for (int a = 0; a < ND; a++) {
     #pragma unroll
     for (int b = a; b < ND; b++) {
       const int k = sidx<M>(a, b);
-      double s = S[k] - P.rtau_shear*(S[k] - seq[k]);
+      double s = S[k] - rts*(S[k] - seq[k]);
       if (a == b) s += rdim*tr_s;
       s += fcorr*(u[a]*F[b] + F[a]*u[b]);
       if (NOISE) s += shat[k];
@@ -178,7 +186,7 @@ mrt_site(double (&f)[M::NVEL], const double (&F)[3], const double * sth,
     #pragma unroll
     for (int k = 0; k < NG; k++) mg[k] = GHOST ? mg[k] + ghat[k] : ghat[k];
   }
-  if (GM != 0) {
+  if ((GM & 3) != 0) {
     const GhostTab & T = ghost_tab<M>();
     #pragma unroll
     for (int p = 0; p < Q; p++) {
@@ -535,11 +543,25 @@ lb_sweep_kernel(const KParams P) {
 	  }
 	}
 	const double mu = P.A*phi + P.B*phi*phi*phi - P.kappa*dsq;
-	mrt_site<M, GM, true>(f[0][v], F, sth, shat, ghat, P, rho, u);
+	mrt_site<M, GM, true>(f[0][v], F, sth, shat, ghat, P, P.rtau_shear, P.rtau_bulk, nullptr, rho, u);
 	phi_site<M>(f[NDIST - 1][v], phi, mu, u, P.rtau2);
       }
       else {
-	mrt_site<M, GM, false>(f[0][v], F, nullptr, shat, ghat, P, rho, u);
+	if constexpr ((GM & 4) != 0) {   // viscosity model: its own instantiations (GM bit 2)
+	  // lb_relaxation_time_shear_v / _bulk_v / _ghosts_v with the site's viscosity
+	  const double eta = P.eta[s];
+	  const double rts = 1.0/(0.5 + eta/P.rho0cs2);
+	  const double rtb = (P.visc_relax == 1) ? rts : 1.0/(0.5 + (P.eta_ratio*eta)/P.rho0cs2);
+	  double gk2[2] = {1.0 - rts, 1.0 - rts};
+	  if (P.visc_relax == 2) {
+	    const double tau = eta/P.rho0cs2;
+	    gk2[1] = 1.0 - fmin(0.5 + 2.0*tau/(tau + 3.0/8.0), 2.0);
+	  }
+	  mrt_site<M, GM, false>(f[0][v], F, nullptr, shat, ghat, P, rts, rtb, gk2, rho, u);
+	}
+	else {
+	  mrt_site<M, GM, false>(f[0][v], F, nullptr, shat, ghat, P, P.rtau_shear, P.rtau_bulk, nullptr, rho, u);
+	}
       }
       if (DIAG && (v < nv)) {
 	// conserved sums of the state that entered this collision: rho, rho^2, min,

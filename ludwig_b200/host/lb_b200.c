@@ -114,10 +114,11 @@ int lb_collide(lb_t * lb, hydro_t * hydro, map_t * map, noise_t * noise, fe_t * 
 
   b200lb_param_t p;
 
-  (void) map; (void) visc;
+  (void) map;
   if (hydro == NULL) return 0;               /* src/collision.c:149 */
 
   if (gather_params(lb, fe, &p)) return -1;
+  TRY(b200lb_visc_model_set(lb->target, visc != NULL));       /* p.have_visc_model, src/collision.c:1954 */
   TRY(b200lb_noise_present_set(lb->target, (noise != NULL) && noise->on[NOISE_RHO]));
   TRY(b200lb_set_param(lb->target, &p));
   TRY(b200lb_collide(lb->target));
@@ -419,6 +420,27 @@ int phi_cahn_hilliard(phi_ch_t * pch, fe_t * fe, field_t * phi, hydro_t * hydro,
   }
   if (fd_params(pch->lb, fe)) return -1;
   TRY(b200lb_cahn_hilliard(pch->lb->target));
+  return 0;
+}
+
+/* viscosity_model arrhenius (src/visc_arrhenius.c): needs the order parameter */
+int visc_arrhenius_create(lb_t * lb, field_t * phi, visc_arrhenius_param_t param, visc_t ** pvisc) {
+  visc_t * visc = NULL;
+  if (phi == NULL) {
+    snprintf(host_err, sizeof(host_err), "visc_arrhenius_create: requires a composition");
+    return -1;
+  }
+  TRY(b200lb_visc_arrhenius_commit(lb->target, param.eta_plus, param.eta_minus, param.phistar));
+  visc = (visc_t *) calloc(1, sizeof(visc_t));
+  if (visc == NULL) return -1;
+  visc->param = param; visc->lb = lb;
+  *pvisc = visc;
+  return 0;
+}
+int visc_arrhenius_free(visc_t * visc) { free(visc); return 0; }
+int visc_arrhenius_update(visc_t * visc, hydro_t * hydro) {
+  (void) hydro;
+  TRY(b200lb_visc_update(visc->lb->target));
   return 0;
 }
 

@@ -109,7 +109,9 @@ typedef struct noise_s {
   unsigned int * state;            /* host copy, state[index*NNOISE_STATE + ia] */
   lb_t * lb;
 } noise_t;
-typedef void visc_t;    /* no viscosity model */
+/* visc_t (src/visc.h) with the one model of the reference, visc_arrhenius_t */
+typedef struct visc_arrhenius_param_s { double eta_minus, eta_plus, phistar; } visc_arrhenius_param_t;   /* src/visc_arrhenius.h */
+typedef struct visc_s { visc_arrhenius_param_t param; struct lb_data_s * lb; } visc_t;
 typedef void fe_t;
 
 const char * lb_b200_error(void);
@@ -216,6 +218,10 @@ int phi_force_calculation(pth_t * pth, fe_t * fe, field_t * phi, hydro_t * hydro
 int phi_cahn_hilliard(phi_ch_t * pch, fe_t * fe, field_t * phi, hydro_t * hydro,
 		      map_t * map, noise_t * noise);                             /* src/phi_cahn_hilliard.c:206 */
 int hydro_u_halo(hydro_t * hydro);                                              /* src/hydro.c */
+
+int visc_arrhenius_create(lb_t * lb, field_t * phi, visc_arrhenius_param_t param, visc_t ** visc);   /* src/visc_arrhenius.c:52 */
+int visc_arrhenius_free(visc_t * visc);
+int visc_arrhenius_update(visc_t * visc, hydro_t * hydro);          /* src/visc_arrhenius.c:149; visc->func->update */
 
 int fe_symm_create(field_t * phi, field_grad_t * dphi, fe_symm_t ** fe);
 int fe_symm_free(fe_symm_t * fe);

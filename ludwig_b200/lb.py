@@ -21,10 +21,10 @@ _LIBPATH = os.path.join(_HERE, "libb200lb.so")
 HOST_AOS, HOST_SOA = 0, 1
 RELAX_M10, RELAX_BGK, RELAX_TRT = 0, 1, 2
 HALO_FULL, HALO_REDUCED = 0, 2
-FIELD_RHO, FIELD_U, FIELD_FORCE, FIELD_PHI, FIELD_GRAD, FIELD_DELSQ = range(6)
+FIELD_RHO, FIELD_U, FIELD_FORCE, FIELD_PHI, FIELD_GRAD, FIELD_DELSQ, FIELD_ETA = range(7)
 FORCE_NONE, FORCE_STRESS_DIVERGENCE, FORCE_PHI_GRADMU = 1, 2, 3      # fe_force_method_enum_t
 _FIELD_NF = {FIELD_RHO: 1, FIELD_U: 3, FIELD_FORCE: 3, FIELD_PHI: 1, FIELD_GRAD: 3,
-             FIELD_DELSQ: 1}
+             FIELD_DELSQ: 1, FIELD_ETA: 1}
 
 # every symbol include/b200lb.h declares (checked by tests/test_abi.py)
 ABI_SYMBOLS = [
@@ -39,7 +39,7 @@ ABI_SYMBOLS = [
     "b200lb_wall_commit", "b200lb_wall_slip_set", "b200lb_wall_bbl", "b200lb_wall_momentum", "b200lb_wall_momentum_add",
     "b200lb_le_commit", "b200lb_le_apply", "b200lb_le_plane_location", "b200lb_le_time_set",
     "b200lb_ch_create", "b200lb_ch_grad_mu_set", "b200lb_phi_force", "b200lb_cahn_hilliard",
-    "b200lb_hydro_u_halo",
+    "b200lb_hydro_u_halo", "b200lb_visc_arrhenius_commit", "b200lb_visc_update", "b200lb_visc_model_set",
     "b200lb_field_stats", "b200lb_io_record_doubles", "b200lb_io_pack", "b200lb_io_unpack",
     "b200lb_step", "b200lb_stats", "b200lb_step_diag", "b200lb_sync", "b200lb_nccl_unique_id",
     "b200lb_comm_init", "b200lb_p2p_export", "b200lb_p2p_import", "b200lb_timer_start", "b200lb_timer_stop",
@@ -128,6 +128,9 @@ def load():
     L.b200lb_ch_grad_mu_set.argtypes = [vp, vp]
     for name in ("b200lb_phi_force", "b200lb_cahn_hilliard", "b200lb_hydro_u_halo"):
         getattr(L, name).argtypes = [vp]
+    L.b200lb_visc_arrhenius_commit.argtypes = [vp, ctypes.c_double, ctypes.c_double, ctypes.c_double]
+    L.b200lb_visc_update.argtypes = [vp]
+    L.b200lb_visc_model_set.argtypes = [vp, ctypes.c_int]
     L.b200lb_field_stats.argtypes = [vp, ctypes.c_int, vp]
     L.b200lb_io_record_doubles.argtypes = [vp]
     L.b200lb_io_record_doubles.restype = ctypes.c_long
@@ -338,6 +341,19 @@ class Lattice:
 
     def hydro_u_halo(self):
         self._ck(self.L.b200lb_hydro_u_halo(self.h))
+
+    # -- viscosity model (visc_t, src/visc.h; src/visc_arrhenius.c) -------------------
+    def visc_arrhenius_commit(self, eta_plus, eta_minus, phistar=1.0):
+        """viscosity_model arrhenius: lb_collide reads a per-site viscosity from now on."""
+        self._ck(self.L.b200lb_visc_arrhenius_commit(self.h, float(eta_plus), float(eta_minus),
+                                                     float(phistar)))
+
+    def visc_update(self):
+        self._ck(self.L.b200lb_visc_update(self.h))
+
+    def visc_model_set(self, on=1):
+        """lb_collide(..., visc != NULL): take eta from FIELD_ETA (uploaded by the caller)."""
+        self._ck(self.L.b200lb_visc_model_set(self.h, int(on)))
 
     # -- flat walls (wall_t, src/wall.h) ---------------------------------------------
     def wall_commit(self, isboundary, ubot=(0.0, 0.0, 0.0), utop=(0.0, 0.0, 0.0)):

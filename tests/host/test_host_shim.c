@@ -440,7 +440,7 @@ static void test_lees_edwards(int nsteps, int oscillatory) {
 
 /* The order parameter as a finite-difference field ("free_energy symmetric") through the
  * reference's call order (src/ludwig.c:537-575, 727-768, 791-862) */
-static void test_cahn_hilliard(int nsteps, int order, int method, int npt) {
+static void test_cahn_hilliard(int nsteps, int order, int method, int npt, int with_visc) {
   cs_t cs;
   physics_t phys = {1.0, 0.00625, 0.00625, {0.0, 0.0, 0.0}, 1.25, 0.0};
   lb_data_options_t opts = lb_data_options_default();
@@ -448,6 +448,9 @@ static void test_cahn_hilliard(int nsteps, int order, int method, int npt) {
   fe_symm_t * fe = NULL; phi_ch_t * pch = NULL; pth_t * pth = NULL;
   phi_ch_info_t info = {0};
   fe_symm_param_t fp = {-0.00625, 0.00625, 0.004, 0.0, 0.0};
+  visc_t * visc = NULL;
+  visc_arrhenius_param_t vp = {0};
+  orc_visc_t ovisc = {0.625, 0.00625, 1.0};
   orc_model_t model; orc_box_t box; orc_param_t prm; orc_ch_t och;
   const int nl[3] = {10, 8, 6};
   const double zero[3] = {0.0, 0.0, 0.0};
@@ -465,6 +468,10 @@ static void test_cahn_hilliard(int nsteps, int order, int method, int npt) {
   OK(field_grad_set(grad, npt == 27 ? grad_3d_27pt_fluid_d2 : grad_3d_7pt_fluid_d2, NULL));
   OK(fe_symm_create(phi, grad, &fe));
   OK(fe_symm_param_set(fe, fp));
+  if (with_visc) {                      /* viscosity_model arrhenius, src/ludwig.c:2001-2040 */
+    vp.eta_plus = ovisc.eta_plus; vp.eta_minus = ovisc.eta_minus; vp.phistar = ovisc.phistar;
+    OK(visc_arrhenius_create(lb, phi, vp, &visc));
+  }
 
   orc_model_init(lb->nvel, &model);
   orc_box_init(nl, &box);
@@ -503,7 +510,8 @@ static void test_cahn_hilliard(int nsteps, int order, int method, int npt) {
     OK(phi_force_calculation(pth, (fe_t *) fe, phi, hydro));
     OK(phi_cahn_hilliard(pch, (fe_t *) fe, phi, hydro, NULL, NULL));
     OK(hydro_u_zero(hydro, zero));
-    OK(lb_collide(lb, hydro, NULL, NULL, (fe_t *) fe, NULL));
+    if (visc) OK(visc_arrhenius_update(visc, hydro));         /* src/ludwig.c:794 */
+    OK(lb_collide(lb, hydro, NULL, NULL, (fe_t *) fe, visc));
     OK(lb_halo(lb));
     OK(lb_propagation(lb));
   }
@@ -511,9 +519,13 @@ static void test_cahn_hilliard(int nsteps, int order, int method, int npt) {
   OK(hydro_memcpy(hydro, tdpMemcpyDeviceToHost));
   OK(field_memcpy(phi, tdpMemcpyDeviceToHost));
 
+  double * oeta = (double *) calloc(lb->nsite, sizeof(double));
   orc_gradient_select(npt);
   orc_ch_attach(&och);
+  if (with_visc) orc_visc_attach(&ovisc, oeta);
   orc_step(&model, &box, &prm, 1, nsteps, f, fprime, rho, u, force, ophi, ograd, odelsq);
+  orc_visc_attach(NULL, NULL);
+  free(oeta);
   orc_ch_attach(NULL);
   orc_gradient_select(7);
 
@@ -531,13 +543,15 @@ static void test_cahn_hilliard(int nsteps, int order, int method, int npt) {
     }
     if (fabs(phi->data[index] - ophi[index]) > pmax) pmax = fabs(phi->data[index] - ophi[index]);
   }
-  printf("test_cahn_hilliard (order %d, method %d, %d-point gradient): %d steps, max|df|/max|f| = %.3e, "
-	 "max|du| = %.3e, max|dphi| = %.3e\n", order, method, npt, nsteps, emax/fmax, umax, pmax);
+  printf("test_cahn_hilliard (order %d, method %d, %d-point gradient%s): %d steps, max|df|/max|f| = %.3e, "
+	 "max|du| = %.3e, max|dphi| = %.3e\n", order, method, npt, with_visc ? ", viscosity model" : "",
+	 nsteps, emax/fmax, umax, pmax);
   CHECK(emax/fmax < 1.0e-12, "Cahn-Hilliard: distributions vs oracle");
   CHECK(umax < 1.0e-12, "Cahn-Hilliard: hydro u vs oracle");
   CHECK(pmax < 1.0e-13, "Cahn-Hilliard: order parameter vs oracle");
 
   free(f); free(fprime); free(rho); free(u); free(force); free(ophi); free(ograd); free(odelsq);
+  if (visc) visc_arrhenius_free(visc);
   fe_symm_free(fe);
   field_grad_free(grad);
   field_free(phi);
@@ -550,9 +564,10 @@ static void test_cahn_hilliard(int nsteps, int order, int method, int npt) {
 int main(int argc, char ** argv) {
   if (argc > 1 && strcmp(argv[1], "fd") == 0) {
     /* the finite-difference order parameter on its own (tests/test_host_shim.py) */
-    test_cahn_hilliard(6, 1, FE_FORCE_METHOD_STRESS_DIVERGENCE, 27);
-    test_cahn_hilliard(6, 2, FE_FORCE_METHOD_STRESS_DIVERGENCE, 7);
-    test_cahn_hilliard(6, 3, FE_FORCE_METHOD_PHI_GRADMU, 27);
+    test_cahn_hilliard(6, 1, FE_FORCE_METHOD_STRESS_DIVERGENCE, 27, 0);
+    test_cahn_hilliard(6, 2, FE_FORCE_METHOD_STRESS_DIVERGENCE, 7, 0);
+    test_cahn_hilliard(6, 3, FE_FORCE_METHOD_PHI_GRADMU, 27, 0);
+    test_cahn_hilliard(6, 2, FE_FORCE_METHOD_STRESS_DIVERGENCE, 27, 1);
     if (nfail) { printf("%d check(s) FAILED\n", nfail); return 1; }
     printf("host shim (fd): all passed\n");
     return 0;
