@@ -1,6 +1,5 @@
 #!/bin/bash
-# the whole GPU suite (with the viscosity-model tests) and a short default bench line
+# two GPUs: the finite-difference order parameter across a rank boundary
 mkdir -p gpurun_out
-timeout 150 python -m pytest tests -q -m gpu -p no:cacheprovider --tb=short > gpurun_out/t_full.log 2>&1; echo "rc=$?" >> gpurun_out/t_full.log
-tail -25 gpurun_out/t_full.log
-timeout 60 python bench.py --steps 100 --no-cpu --no-e2e > gpurun_out/bench_quick.json 2> gpurun_out/bench_quick.err; tail -2 gpurun_out/bench_quick.err; cut -c1-330 gpurun_out/bench_quick.json
+timeout 30 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29602 tests/mgpu_worker.py --nvel 19 --halo reduced --fd 2 --gradient 27 --visc 1 --steps 8 > gpurun_out/mgpu2_fd.log 2>&1; echo "rc=$?" >> gpurun_out/mgpu2_fd.log
+grep -E "mgpu world|rc=|Error|error" gpurun_out/mgpu2_fd.log | tail -8

@@ -44,6 +44,9 @@ def main():
     ap.add_argument("--gradient", type=int, default=7)
     ap.add_argument("--walls", type=int, nargs=3, default=[0, 0, 0])
     ap.add_argument("--le", type=int, default=0, help="Lees-Edwards planes per rank in x (uy 0.03)")
+    ap.add_argument("--fd", type=int, default=0,
+                    help="free_energy symmetric: finite-difference order parameter, advection of this order")
+    ap.add_argument("--visc", type=int, default=0, help="with --fd: viscosity_model arrhenius")
     args = ap.parse_args()
 
     rank = int(os.environ["RANK"])
@@ -88,6 +91,9 @@ def main():
     if ndist == 2:
         kw = dict(eta_shear=0.00625, eta_bulk=0.00625, mobility=3.75, a=-0.00625,
                   b=0.00625, kappa=0.004)
+    if args.fd:
+        kw = dict(eta_shear=0.00625, eta_bulk=0.00625, mobility=1.25, a=-0.00625,
+                  b=0.00625, kappa=0.004)
     fg = (1e-4, 0.0, 0.0) if (any(walls) and not walls[0]) else (0.0, 0.0, 0.0)
 
     def configure(l):
@@ -101,6 +107,15 @@ def main():
             l.noise_present_set(1)
         if args.le:
             l.le_commit(args.le*grid[0], 0.03)
+        if args.fd:
+            l.phi_ch_create(args.fd, lb.FORCE_STRESS_DIVERGENCE)
+            l.field_grad_set(args.gradient)
+            if args.visc:
+                l.visc_arrhenius_commit(0.625, 0.00625, 1.0)
+
+    def fd_phi(nl, nt=None, offset=(0, 0, 0)):
+        # the order parameter, keyed on the global site id: any decomposition sees the same
+        return 0.8 * lbinit.uniform(lbinit.global_ids(nl, nt, offset).reshape(-1), 50)
 
     configure(lat)
 
@@ -125,9 +140,16 @@ def main():
     import time
     time.sleep(0.3 * (rank % 3))
     lat.lb_memcpy_h2d(f0)
+    if args.fd:
+        lat.field_h2d(lb.FIELD_PHI, fd_phi(local, ntotal, dec.offset))
     lat.step(args.steps)
     fd = lat.lb_memcpy_d2h()
     st = lat.stats()
+    if args.fd:
+        tp = torch.from_numpy(np.ascontiguousarray(
+            lat.field_d2h(lb.FIELD_PHI).reshape(nall)[1:-1, 1:-1, 1:-1])).cuda()
+        pparts = [torch.empty_like(tp) for _ in range(world)] if rank == 0 else None
+        dist.gather(tp, pparts, dst=0)
     mine = fd.reshape(nall + (ndist, nvel))[1:-1, 1:-1, 1:-1].copy()
     gw = torch.tensor(lat.wall_momentum() if any(walls) else np.zeros(3), device="cuda")
     dist.all_reduce(gw, op=dist.ReduceOp.SUM)
@@ -160,10 +182,20 @@ def main():
         configure(one)
         g0 = lbinit.make_state(cv, wv, ntotal, ndist=ndist, ndim=ndim)
         one.lb_memcpy_h2d(g0)
+        if args.fd:
+            one.field_h2d(lb.FIELD_PHI, fd_phi(ntotal))
         one.step(args.steps)
         g1 = one.lb_memcpy_d2h().reshape(tuple(n + 2 for n in ntotal) + (ndist, nvel))[1:-1, 1:-1, 1:-1]
         s1 = one.stats()
         same = bool(np.array_equal(glob, g1))
+        if args.fd:
+            # the order parameter: decomposed == single GPU, bit for bit
+            gphi = np.zeros(ntotal)
+            for r in range(world):
+                o = lb.Decomposition(ntotal, r, world, grid=grid).offset
+                gphi[o[0]:o[0] + local[0], o[1]:o[1] + local[1], o[2]:o[2] + local[2]] = pparts[r].cpu().numpy()
+            phi1 = one.field_d2h(lb.FIELD_PHI).reshape(tuple(n + 2 for n in ntotal))[1:-1, 1:-1, 1:-1]
+            same = same and bool(np.array_equal(gphi, phi1))
         if any(walls):
             gw1 = one.wall_momentum()
             same = same and bool(np.allclose(gw.cpu().numpy(), gw1, rtol=1e-10, atol=1e-13))
@@ -191,19 +223,29 @@ def main():
         if args.le:
             orc.le_attach(orc.le(args.le*grid[0], 0.03))
         orc.gradient_select(args.gradient)
+        if args.fd:
+            phi[...] = fd_phi(ntotal)
+            orc.ch_attach(orc.ch(args.fd, pyoracle.FORCE_STRESS_DIVERGENCE))
+            if args.visc:
+                orc.visc_attach(np.zeros(n), 0.625, 0.00625, 1.0)
         orc.step(prm, args.steps, f, fp, rho, u, frc, phi, grad, delsq)
+        orc.ch_attach(None)
+        orc.visc_attach(None)
         orc.le_attach(None)
         orc.noise_attach(None, 0.0)
         orc.wall_attach(None)
         orc.gradient_select(7)
         fo = f.reshape(tuple(n + 2 for n in ntotal) + (ndist, nvel))[1:-1, 1:-1, 1:-1]
         err = float(np.max(np.abs(glob - fo)) / np.max(np.abs(fo)))
+        if args.fd:
+            po = phi.reshape(tuple(n + 2 for n in ntotal))[1:-1, 1:-1, 1:-1]
+            err = max(err, float(np.max(np.abs(gphi - po)) / np.max(np.abs(po))))
         mass = abs(float(sums[0].item()) - s1[0])
         halo_ok = bool(flags.item() > 0.5)
-        print("mgpu world=%d grid=%s nvel=%d ndist=%d halo=%s fused=%d overlap=%d direct=%d p2p=%d kt=%g grad=%d walls=%s le=%d: halo_bit_exact=%s "
+        print("mgpu world=%d grid=%s nvel=%d ndist=%d halo=%s fused=%d overlap=%d direct=%d p2p=%d kt=%g grad=%d walls=%s le=%d fd=%d visc=%d: halo_bit_exact=%s "
               "decomposed==single=%s err_vs_oracle=%.2e mass_diff=%.2e"
               % (world, grid, nvel, ndist, args.halo, args.fused, args.overlap, args.direct, args.p2p, args.kt, args.gradient,
-                 walls, args.le, halo_ok, same, err, mass),
+                 walls, args.le, args.fd, args.visc, halo_ok, same, err, mass),
               flush=True)
         if not (halo_ok and same and err < 1e-12 and mass < 1e-9 * n):
             rc = 1

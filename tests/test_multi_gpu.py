@@ -50,6 +50,12 @@ def launch(n, extra, port):
     ["--nvel", "19", "--halo", "reduced", "--le", "1", "--steps", "9"],
     ["--nvel", "19", "--halo", "full", "--le", "1", "--p2p", "0", "--overlap", "0", "--steps", "9"],
     ["--nvel", "9", "--halo", "reduced", "--lsize", "16", "12", "1", "--le", "2", "--steps", "9"],
+    # free_energy symmetric: the order parameter as a finite-difference field (phi, its
+    # gradient and u cross the rank boundaries one site wide), with and without the
+    # viscosity model
+    ["--nvel", "19", "--halo", "reduced", "--fd", "1", "--gradient", "27", "--steps", "8"],
+    ["--nvel", "19", "--halo", "reduced", "--fd", "2", "--gradient", "7", "--p2p", "0", "--steps", "8"],
+    ["--nvel", "27", "--halo", "full", "--lsize", "8", "6", "10", "--fd", "2", "--gradient", "27", "--visc", "1", "--steps", "8"],
 ])
 def test_decomposed_equals_single(n, extra):
     if ngpu() < n:
