@@ -1,5 +1,5 @@
 #!/bin/bash
-# two GPUs: the finite-difference order parameter across a rank boundary
 mkdir -p gpurun_out
-timeout 30 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29602 tests/mgpu_worker.py --nvel 19 --halo reduced --fd 2 --gradient 27 --visc 1 --steps 8 > gpurun_out/mgpu2_fd.log 2>&1; echo "rc=$?" >> gpurun_out/mgpu2_fd.log
-grep -E "mgpu world|rc=|Error|error" gpurun_out/mgpu2_fd.log | tail -8
+export B200LB_ASSUME_GPU=1
+timeout 9 python -m pytest tests/test_zzz_gpu_g_moment.py -x -q -m gpu > gpurun_out/gmoment_pytest2.log 2>&1; echo "rc=$?" >> gpurun_out/gmoment_pytest2.log
+tail -5 gpurun_out/gmoment_pytest2.log

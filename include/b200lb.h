@@ -120,6 +120,11 @@ long b200lb_nsite(const b200lb_t * h);                          /* host nsite = 
  *   "ch_exact"    0/1  ... 1: the kernel build without fused multiply-add that keeps the
  *                      reference's order of operations (force and phi bit-identical to
  *                      the reference's); 0 (default): fused multiply-add, a few ulp away
+ *   "g_moment"    0/1  binary fluid, fused mode: phi_lb_to_field also stores the first
+ *                      moment of the (pulled) order-parameter populations, and the
+ *                      collision that streams in the same pass reads that instead of
+ *                      pulling g a second time (same bits, 104 B/site less traffic;
+ *                      default 1)
  *   "loopback"    0/1  single rank: send periodic directions through the exchange
  *                      buffers with this GPU as its own neighbour (tests, profiling) */
 int  b200lb_set_option(b200lb_t * h, const char * name, long value);

@@ -141,6 +141,8 @@ struct b200lb_s {
 
   // state machine (see b200lb_propagate)
   bool prop_pending;         // lat[cur] holds post-collision values still to be streamed
+  double * jphi;             // [3][nsd] first moment of the pulled g (option g_moment), or null
+  bool jphi_valid;           // ... written by phi_from_g from the pending lattice, which is unchanged since
   bool force_uniform;        // force field == fconst everywhere (hydro_f_zero)
   double fconst[3];
   bool u_fill_pending;       // hydro_u_zero recorded but not yet applied
@@ -162,7 +164,7 @@ struct b200lb_s {
   bool ghost;
 
   // options
-  int opt_fused, opt_halo, opt_hydro_write, opt_vec, opt_block, opt_halo_lazy, opt_overlap, opt_direct, opt_diag, opt_loopback, opt_grad_lazy, opt_p2p, opt_gradient, opt_ch_fuse, opt_ch_planes, opt_ch_exact;
+  int opt_fused, opt_halo, opt_hydro_write, opt_vec, opt_block, opt_halo_lazy, opt_overlap, opt_direct, opt_diag, opt_loopback, opt_grad_lazy, opt_p2p, opt_gradient, opt_ch_fuse, opt_ch_planes, opt_ch_exact, opt_g_moment;
 
   cudaStream_t s_main, s_x[2];
   cudaStream_t s_comm;       // halo exchange of decomposed directions (overlaps the interior sweep)
@@ -483,6 +485,7 @@ static int create_impl(const b200lb_desc_t * desc, b200lb_s * h, const ModelOps 
   h->opt_ch_fuse = 1;
   h->opt_ch_planes = 8;
   h->opt_ch_exact = 0;
+  h->opt_g_moment = 1;
 
   b200lb_param_t p0;
   memset(&p0, 0, sizeof(p0));
@@ -512,7 +515,7 @@ extern "C" int b200lb_destroy(b200lb_t * h) {
     cudaEventDestroy(h->ev_x[i]);
   }
   cudaFree(h->rho); cudaFree(h->u); cudaFree(h->force);
-  cudaFree(h->phi2); cudaFree(h->eta);
+  cudaFree(h->phi2); cudaFree(h->eta); cudaFree(h->jphi);
   cudaFree(h->phi); cudaFree(h->grad); cudaFree(h->delsq); cudaFree(h->noise); cudaFree(h->fnet_dev); cudaFree(h->le_buf);
   cudaFree(h->partial); cudaFree(h->diag); cudaFree(h->stats_dev); cudaFreeHost(h->stats_host);
   cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
@@ -532,6 +535,7 @@ static int resolve_ch_force(b200lb_s * h);
 
 extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
   if (!h || !name) return fail("null argument");
+  h->jphi_valid = false;   // an option may change how the lattice is addressed (loopback) or swept
   if (!strcmp(name, "fused")) {
     if (!v && h->prop_pending) { if (materialise(h)) return -1; }
     h->opt_fused = (v != 0);
@@ -557,6 +561,7 @@ extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
     h->opt_ch_exact = (v != 0);
     return 0;
   }
+  if (!strcmp(name, "g_moment")) { h->opt_g_moment = (v != 0); h->jphi_valid = false; return 0; }
   if (!strcmp(name, "ch_planes")) {
     if (v < 1 || v > 4096) return fail("ch_planes: x-planes marched by one block of the order-parameter kernel, 1..4096");
     h->opt_ch_planes = (int) v;
@@ -609,6 +614,8 @@ extern "C" long b200lb_get_option(const b200lb_t * h, const char * name) {
   if (!strcmp(name, "ch_fuse")) return h->opt_ch_fuse;
   if (!strcmp(name, "ch_planes")) return h->opt_ch_planes;
   if (!strcmp(name, "ch_exact")) return h->opt_ch_exact;
+  if (!strcmp(name, "g_moment")) return h->opt_g_moment;
+  if (!strcmp(name, "jphi_valid")) return h->jphi_valid;
   if (!strcmp(name, "p2p")) return h->opt_p2p;
   if (!strcmp(name, "p2p_ready")) return h->p2p_ready;
   if (!strcmp(name, "loopback")) return h->opt_loopback;
@@ -733,6 +740,10 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
   a.ghost = h->ghost;
   a.noise = collide && h->noise_on;
   a.visc = false;
+  // the flux of the order parameter left by phi_from_g stands in for the pulled g
+  a.gmom = pull && collide && a.binary && h->prop_pending && h->jphi_valid;
+  a.P.jphi = a.gmom ? h->jphi : nullptr;
+  h->jphi_valid = false;           // this sweep consumes or replaces the lattice it described
   if (a.noise) {
     if (h->ops->nvel - h->ops->nhydro > B200LB_MAXNOISE)
       return fail("isothermal fluctuations: the site generator yields %d variates per draw, nvel %d has %d ghost modes (src/noise.h:18)",
@@ -872,6 +883,7 @@ extern "C" int b200lb_propagate(b200lb_t * h) {
     // Lazy: the streaming is folded into the next collision (or done on demand
     // by the first call that observes the lattice).
     h->prop_pending = true;
+    h->jphi_valid = false;
     return 0;
   }
   if (ensure_hydro(h)) return -1;
@@ -1490,8 +1502,14 @@ extern "C" int b200lb_phi_from_g(b200lb_t * h) {
   if (!h->phi || h->desc.ndist != 2) return fail("no order parameter distribution (ndist = 1)");
   if (join_comm(h)) return -1;
   const double * g = h->lat[h->cur] + (i64) h->desc.nvel*h->L.nsd;
-  CU(h->ops->phi_from_g(h->L, h->selfper, g, h->phi, h->prop_pending, h->s_main));
+  // The collision that follows, if it streams in the same pass, would pull the same g
+  // again only to form its first moment: leave that here (24 B/site out, 24 in, against
+  // the 8*nvel of g)
+  const bool mom = h->opt_g_moment && h->prop_pending && h->opt_fused;
+  if (mom) { if (need_planes(h, &h->jphi, 3)) return -1; }
+  CU(h->ops->phi_from_g(h->L, h->selfper, g, h->phi, mom ? h->jphi : nullptr, h->prop_pending, h->s_main));
   h->launches++;
+  h->jphi_valid = mom;
   h->phi_halo_deferred = false;
   if (h->grad_state == 1) h->grad_state = 2;      // the pending gradient belonged to the old phi
   return 0;
@@ -1918,6 +1936,7 @@ extern "C" int b200lb_f_upload(b200lb_t * h, const double * f, int layout) {
   if (!h || !f) return fail("null argument");
   if (ensure_hydro(h)) return -1;   // hydro of the state being replaced stays available
   h->prop_pending = false;          // the host copy replaces whatever was in flight
+  h->jphi_valid = false;
   h->bbl_armed = false;
   h->prop_wall = false;
   h->halo_deferred = false;
@@ -2190,6 +2209,7 @@ extern "C" int b200lb_io_unpack(b200lb_t * h, const double * buf) {
   if (!h || !buf) return fail("null argument");
   if (ensure_hydro(h)) return -1;
   h->prop_pending = false;
+  h->jphi_valid = false;
   h->bbl_armed = false;
   h->prop_wall = false;
   h->halo_deferred = false;

@@ -6,15 +6,43 @@
 #include "models.cuh"
 
 // ---------------------------------------------------------------------------
+// First moment sum_p c_p g_p of one site's order-parameter populations, physical
+// components, summed over the pairs (p, Q - p). The binary collision needs nothing
+// else of the incoming g (src/collision.c:956-1023 rebuilds g from phi, this flux,
+// u and mu), so whoever holds the pulled g may hand the flux on instead.
+// ---------------------------------------------------------------------------
+
+template <class M>
+__device__ __forceinline__ void
+g_first_moment(const double (&g)[M::NVEL], double (&j)[M::NDIM]) {
+  constexpr int Q = M::NVEL;
+  #pragma unroll
+  for (int a = 0; a < M::NDIM; a++) j[a] = 0.0;
+  #pragma unroll
+  for (int p = 1; p <= (Q - 1)/2; p++) {
+    const double d = g[p] - g[Q - p];
+    #pragma unroll
+    for (int a = 0; a < M::NDIM; a++) {
+      if (M::cv(p, a) ==  1) j[a] += d;
+      if (M::cv(p, a) == -1) j[a] -= d;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
 // phi = sum_p g_p, p in index order (src/phi_lb_coupler.c:72-102), interior.
 // PULL: the lattice holds post-collision values whose propagation is still
 // pending, so the sum runs over g_p(r - c_p): identical to propagating first.
+// MOM: also store the first moment of the same (pulled) populations, jphi[NDIM][nsd].
+// The next fused stream-and-collide sweep then reads phi and these three values
+// instead of pulling the Q populations of g a second time.
 // ---------------------------------------------------------------------------
 
-template <class M, bool PULL>
+template <class M, bool PULL, bool MOM>
 __global__ void __launch_bounds__(256)
 phi_from_g_kernel(const Layout L, const int w0, const int w1, const int w2,
-		  const double * __restrict__ g, double * __restrict__ phi) {
+		  const double * __restrict__ g, double * __restrict__ phi,
+		  double * __restrict__ jphi) {
 
   const int i2 = blockIdx.x*blockDim.x + threadIdx.x;
   const int i1 = blockIdx.y*blockDim.y + threadIdx.y;
@@ -41,6 +69,12 @@ phi_from_g_kernel(const Layout L, const int w0, const int w1, const int w2,
   #pragma unroll
   for (int p = 0; p < M::NVEL; p++) sum += v[p];
   phi[site] = sum;
+  if (MOM) {
+    double j[M::NDIM];
+    g_first_moment<M>(v, j);
+    #pragma unroll
+    for (int a = 0; a < M::NDIM; a++) jphi[a*L.nsd + site] = j[a];
+  }
 }
 
 // ---------------------------------------------------------------------------

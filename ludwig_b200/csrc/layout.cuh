@@ -47,6 +47,7 @@ struct KParams {
   int wrap[3];            // device axis is periodic within this rank: pulls wrap instead of reading halos
   double rtau_shear, rtau_bulk;
   // viscosity model (src/collision.c:386-404): per-site shear viscosity, or nullptr
+  const double * jphi;    // [ndim][nsd] first moment of the pulled g (sweep with GM bit 3)
   const double * eta;     // [nsd] hydro->eta
   double rho0cs2;         // rho0 cs^2: rtau = 1/(1/2 + eta/(rho0 cs^2))
   double eta_ratio;       // (eta_bulk/eta_shear) of the Newtonian fluid

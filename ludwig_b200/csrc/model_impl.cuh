@@ -69,6 +69,13 @@ static cudaError_t launch_pc(SweepArgs & a) {
     if constexpr (HAVE_NOISE) {
       if (a.binary) {
 	if (!HAVE_BINARY) return cudaErrorInvalidValue;
+	if constexpr (PULL && HAVE_BINARY) {
+	  if (a.gmom) {
+	    if (a.ghost) return launch_one<1, PULL, COLLIDE, HAVE_BINARY, 11>(a);
+	    return launch_one<1, PULL, COLLIDE, HAVE_BINARY, 10>(a);
+	  }
+	}
+	if (a.gmom) return cudaErrorInvalidValue;
 	if (a.ghost) return launch_one<1, PULL, COLLIDE, HAVE_BINARY, 3>(a);
 	return launch_one<1, PULL, COLLIDE, HAVE_BINARY, 2>(a);
       }
@@ -81,6 +88,13 @@ static cudaError_t launch_pc(SweepArgs & a) {
   }
   if (a.binary) {
     if (!HAVE_BINARY) return cudaErrorInvalidValue;
+    if constexpr (PULL && HAVE_BINARY) {
+      if (a.gmom) {
+	if (a.ghost) return launch_one<1, PULL, COLLIDE, HAVE_BINARY, 9>(a);
+	return launch_one<1, PULL, COLLIDE, HAVE_BINARY, 8>(a);
+      }
+    }
+    if (a.gmom) return cudaErrorInvalidValue;
     if (a.ghost) return launch_one<1, PULL, COLLIDE, HAVE_BINARY, 1>(a);
     return launch_one<1, PULL, COLLIDE, HAVE_BINARY, 0>(a);
   }
@@ -103,11 +117,12 @@ static cudaError_t sweep_impl(SweepArgs & a) {
 }
 
 static cudaError_t phi_impl(const Layout & L, const int w[3], const double * g,
-			    double * phi, bool pull, cudaStream_t s) {
+			    double * phi, double * jphi, bool pull, cudaStream_t s) {
   dim3 block(128, 2, 1);
   dim3 grid((L.n[2] + 127)/128, (L.n[1] + 1)/2, L.n[0]);
-  if (pull) phi_from_g_kernel<MODEL, true><<<grid, block, 0, s>>>(L, w[0], w[1], w[2], g, phi);
-  else phi_from_g_kernel<MODEL, false><<<grid, block, 0, s>>>(L, 0, 0, 0, g, phi);
+  if (pull && jphi) phi_from_g_kernel<MODEL, true, true><<<grid, block, 0, s>>>(L, w[0], w[1], w[2], g, phi, jphi);
+  else if (pull) phi_from_g_kernel<MODEL, true, false><<<grid, block, 0, s>>>(L, w[0], w[1], w[2], g, phi, nullptr);
+  else phi_from_g_kernel<MODEL, false, false><<<grid, block, 0, s>>>(L, 0, 0, 0, g, phi, nullptr);
   return cudaGetLastError();
 }
 

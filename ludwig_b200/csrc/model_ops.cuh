@@ -12,6 +12,7 @@ struct SweepArgs {
   bool pull, collide, binary, ghost;
   bool noise;         // isothermal fluctuations on (collide only)
   bool visc;          // viscosity model: per-site relaxation times from P.eta (collide, single fluid)
+  bool gmom;          // binary fluid, pull + collide: first moment of g from P.jphi, g not read
   bool wall;          // bounce-back on links folded into the pull (pull only)
   bool diag;          // accumulate conserved sums in the sweep (collide only)
   long long nblocks;  // out: blocks launched (= diagnostic partials written)
@@ -28,7 +29,7 @@ struct ModelOps {
   double ghost_norm[B200LB_MAXGHOST];           // sum_p w_p ma[k][p]^2 per ghost mode
   cudaError_t (*sweep)(SweepArgs &);
   cudaError_t (*phi_from_g)(const Layout &, const int wrap[3], const double * g,
-			    double * phi, bool pull, cudaStream_t);
+			    double * phi, double * jphi, bool pull, cudaStream_t);
   cudaError_t (*stats)(const Layout &, const double * f, int ndist,
 		       double * partial, dim3 grid, dim3 block, cudaStream_t);
   cudaError_t (*hydro)(const Layout &, const double * f, int ndist, const double * force,

@@ -43,7 +43,8 @@ template <bool NC> __device__ __forceinline__ double2 ld2(const double * p) {
 //          (src/collision.c:393-404); ghost-mode handling: bit 0 = the scheme keeps a fraction of the incoming
 //          ghost modes (BGK, TRT), bit 1 = fluctuations: shat (symmetric storage) is
 //          added to the relaxed stress and ghat[k] to ghost mode k
-//          (src/collision.c:526-544)
+//          (src/collision.c:526-544); bit 3 (sweep, binary fluid, PULL): the first
+//          moment of the pulled g comes from P.jphi and g itself is not read
 // ---------------------------------------------------------------------------
 
 //   rts, rtb   inverse relaxation times of shear and bulk stress at this site
@@ -205,10 +206,11 @@ mrt_site(double (&f)[M::NVEL], const double (&F)[3], const double * sth,
 // g is rebuilt from phi, the relaxed flux j_phi and phi u u + mu delta.
 // ---------------------------------------------------------------------------
 
+// jin: sum_p c_p g_p of the incoming populations; every g_p is written, none is read
 template <class M>
 __device__ __forceinline__ void
-phi_site(double (&g)[M::NVEL], double phi, double mu, const double (&u)[3],
-	 double rtau2) {
+phi_site_moment(double (&g)[M::NVEL], const double (&jin)[M::NDIM], double phi, double mu,
+		const double (&u)[3], double rtau2) {
 
   constexpr int Q  = M::NVEL;
   constexpr int ND = M::NDIM;
@@ -217,16 +219,7 @@ phi_site(double (&g)[M::NVEL], double phi, double mu, const double (&u)[3],
 
   double j[ND];
   #pragma unroll
-  for (int a = 0; a < ND; a++) j[a] = 0.0;
-  #pragma unroll
-  for (int p = 1; p <= H; p++) {
-    const double d = g[p] - g[Q - p];
-    #pragma unroll
-    for (int a = 0; a < ND; a++) {
-      if (M::cv(p, a) ==  1) j[a] += d;
-      if (M::cv(p, a) == -1) j[a] -= d;
-    }
-  }
+  for (int a = 0; a < ND; a++) j[a] = jin[a];
   double S[NS];
   double B0 = 0.0;
   #pragma unroll
@@ -257,6 +250,15 @@ phi_site(double (&g)[M::NVEL], double phi, double mu, const double (&u)[3],
     g[p]     = M::wv(p)*(ev + od);
     g[Q - p] = M::wv(p)*(ev - od);
   }
+}
+
+template <class M>
+__device__ __forceinline__ void
+phi_site(double (&g)[M::NVEL], double phi, double mu, const double (&u)[3],
+	 double rtau2) {
+  double j[M::NDIM];
+  g_first_moment<M>(g, j);
+  phi_site_moment<M>(g, j, phi, mu, u, rtau2);
 }
 
 // ---------------------------------------------------------------------------
@@ -340,6 +342,11 @@ lb_sweep_kernel(const KParams P) {
   constexpr int ND = M::NDIM;
   constexpr int NDIST = BINARY ? 2 : 1;
   constexpr bool NC = PULL;          // source is read-only when it is not the destination
+  // GM bit 3: phi_from_g_kernel<PULL, MOM> has left the first moment of the pulled g in
+  // P.jphi, which is all the binary collision takes from it: g is written, not read
+  constexpr bool GMOM = BINARY && PULL && COLLIDE && ((GM & 8) != 0);
+  constexpr int NLOAD = GMOM ? 1 : NDIST;
+  static_assert(((GM & 8) == 0) || GMOM, "GM bit 3 belongs to the fused binary sweep");
 
   const Layout & L = P.L;
 
@@ -454,7 +461,7 @@ lb_sweep_kernel(const KParams P) {
   }
   else {
   #pragma unroll
-  for (int n = 0; n < NDIST; n++) {
+  for (int n = 0; n < NLOAD; n++) {
     #pragma unroll
     for (int p = 0; p < Q; p++) {
       const double * src = P.src + (i64)(n*Q + p)*L.nsd + site;
@@ -544,7 +551,15 @@ lb_sweep_kernel(const KParams P) {
 	}
 	const double mu = P.A*phi + P.B*phi*phi*phi - P.kappa*dsq;
 	mrt_site<M, GM, true>(f[0][v], F, sth, shat, ghat, P, P.rtau_shear, P.rtau_bulk, nullptr, rho, u);
-	phi_site<M>(f[NDIST - 1][v], phi, mu, u, P.rtau2);
+	if constexpr (GMOM) {
+	  double jin[ND];
+	  #pragma unroll
+	  for (int a = 0; a < ND; a++) jin[a] = __ldg(P.jphi + a*L.nsd + s);
+	  phi_site_moment<M>(f[NDIST - 1][v], jin, phi, mu, u, P.rtau2);
+	}
+	else {
+	  phi_site<M>(f[NDIST - 1][v], phi, mu, u, P.rtau2);
+	}
       }
       else {
 	if constexpr ((GM & 4) != 0) {   // viscosity model: its own instantiations (GM bit 2)
