@@ -193,7 +193,18 @@ int  b200lb_le_commit(b200lb_t * h, int nplanes_total, double uy, int oscillator
                       int period, int nt0);
 int  b200lb_le_apply(b200lb_t * h, double t);                          /* lb_le_apply_boundary_conditions src/model_le.c:57 */
 int  b200lb_le_plane_location(const b200lb_t * h, int np);             /* lees_edw_plane_location src/leesedwards.c:599 */
-int  b200lb_le_time_set(b200lb_t * h, int nstep);                      /* physics_control_time: steps taken so far */
+int  b200lb_le_time_set(b200lb_t * h, int nstep);                      /* physics_control_init_time src/physics.c:687: the run (re)starts at this step */
+/* Binary fluid (ndist = 2) with planes: field_grad_compute (b200lb_grad7 / b200lb_grad27)
+ * first does what field_leesedwards does (src/field.c:500-600, called from
+ * src/field_grad.c:310): two buffer planes of phi per plane, displaced along y by what the
+ * plane has slid at physics_control_time -- t_start + t_current - 1 (src/physics.c:651-659),
+ * one less than the step number the distributions are displaced by -- with four-point
+ * interpolation; the stencil of the sites next to a plane then takes its x neighbours from
+ * them (lees_edw_ic_to_buff, src/gradient_3d_7pt_fluid.c:264-265,
+ * src/gradient_3d_27pt_fluid.c:262-265). b200lb_le_field_time_set hands over that time
+ * ahead of the gradient call; b200lb_step keeps it itself. Planes closer than three sites
+ * are refused for the order parameter. */
+int  b200lb_le_field_time_set(b200lb_t * h, double t);                 /* physics_control_time as read by field_leesedwards, src/field.c:553 */
 
 /* The order parameter as a finite-difference field ("free_energy symmetric",
  * src/ludwig.c:1159-1250): ndist = 1, phi is a field_t that follows Cahn-Hilliard with the

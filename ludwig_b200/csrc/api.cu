@@ -16,6 +16,7 @@
 
 #include "../../include/b200lb.h"
 #include "common_kernels.cuh"
+#include "le_field_kernels.cuh"
 #include "model_ops.cuh"
 #include "ch_kernels.cuh"
 
@@ -120,6 +121,9 @@ struct b200lb_s {
   double le_uy;
   int le_osc, le_period, le_nt0;
   long le_step;              // physics time step counter of b200lb_step
+  long le_tstart;            // ... and the step this run started from (physics_control_init_time)
+  double le_field_t;         // physics_control_time at which the order parameter is displaced
+  double * le_phibuf;        // [2 x local planes][s0] buffer planes of phi (field_leesedwards)
   double * le_buf;           // crossing populations of the plane sites
   // the order parameter as a finite-difference field ("free_energy symmetric":
   // phi_ch_t src/phi_cahn_hilliard.h:33, pth_t src/phi_force_stress.h)
@@ -515,7 +519,7 @@ extern "C" int b200lb_destroy(b200lb_t * h) {
     cudaEventDestroy(h->ev_x[i]);
   }
   cudaFree(h->rho); cudaFree(h->u); cudaFree(h->force);
-  cudaFree(h->phi2); cudaFree(h->eta); cudaFree(h->jphi);
+  cudaFree(h->phi2); cudaFree(h->eta); cudaFree(h->jphi); cudaFree(h->le_phibuf);
   cudaFree(h->phi); cudaFree(h->grad); cudaFree(h->delsq); cudaFree(h->noise); cudaFree(h->fnet_dev); cudaFree(h->le_buf);
   cudaFree(h->partial); cudaFree(h->diag); cudaFree(h->stats_dev); cudaFreeHost(h->stats_host);
   cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
@@ -1041,7 +1045,8 @@ extern "C" int b200lb_le_commit(b200lb_t * h, int nplanes, double uy, int oscill
   if (nplanes < 0) return fail("N_LE_plane must not be negative");
   if (nplanes > 0 && h->ch_on) return fail("Lees-Edwards planes for the finite-difference order parameter (src/phi_cahn_hilliard.c:618) are not on this path");
   if (h->prop_pending) { if (materialise(h)) return -1; }
-  h->le_nplanes = 0; h->le_nlocal = 0; h->le_step = 0;
+  h->le_nplanes = 0; h->le_nlocal = 0; h->le_step = 0; h->le_tstart = 0; h->le_field_t = 0.0;
+  if (h->le_phibuf) { CU(cudaFree(h->le_phibuf)); h->le_phibuf = nullptr; }
   if (nplanes == 0) return 0;
   const int ntotal = h->desc.cartsz[0]*h->desc.nlocal[0];
   if (ntotal % nplanes) return fail("Number of planes must divide system size");
@@ -1079,6 +1084,16 @@ extern "C" int b200lb_le_plane_location(const b200lb_t * h, int np) {
 extern "C" int b200lb_le_time_set(b200lb_t * h, int nstep) {
   if (!h) return fail("null handle");
   h->le_step = nstep;
+  h->le_tstart = nstep;
+  h->le_field_t = 1.0*(h->le_tstart + h->le_step - 1.0);    // src/physics.c:651-659
+  return 0;
+}
+
+// physics_control_time for the field_leesedwards inside the next field_grad_compute
+// (src/field.c:553). b200lb_step keeps it itself.
+extern "C" int b200lb_le_field_time_set(b200lb_t * h, double t) {
+  if (!h) return fail("null handle");
+  h->le_field_t = t;
   return 0;
 }
 
@@ -1444,6 +1459,35 @@ extern "C" int b200lb_halo(b200lb_t * h) {
   return b200lb_halo_swap(h, h->opt_halo);
 }
 
+// field_grad_compute with Lees-Edwards planes (src/field_grad.c:305-325): after the stencil
+// has run over the lattice, the sites next to a plane are recomputed with the displaced,
+// interpolated neighbour planes of field_leesedwards (le_field_kernels.cuh)
+static int le_grad_fix(b200lb_s * h, int npt) {
+  if (h->le_nlocal == 0) return 0;
+  const Layout & L = h->L;
+  if (h->desc.ndim != 3) return fail("order parameter across Lees-Edwards planes: three-dimensional models");
+  if (h->desc.nlocal[0]/h->le_nlocal < 3)
+    return fail("order parameter across Lees-Edwards planes: planes closer than 3 sites (the reference's buffer lookup, src/leesedwards.c:1028, breaks down there)");
+  LePhiTab T;
+  memset(&T, 0, sizeof(T));
+  T.L = L;
+  T.w0 = h->selfper[0]; T.w1 = h->selfper[1]; T.w2 = h->selfper[2];
+  int loc[B200LB_LE_MAXPLANE];
+  for (int np = 0; np < h->le_nlocal; np++) loc[np] = le_location(h, np);
+  le_phi_tab_fill(T, h->le_nlocal, loc, h->le_uy, h->le_osc, h->le_period, h->le_nt0, h->le_field_t);
+  if (!h->le_phibuf) CU(cudaMalloc(&h->le_phibuf, (size_t) T.nbuf*L.s0*sizeof(double)));
+  dim3 block(128, 1, 1);
+  dim3 gbuf((L.n[2] + 2 + 127)/128, L.n[1] + 2, T.nbuf);
+  le_phi_buffer_kernel<<<gbuf, block, 0, h->s_main>>>(T, h->phi, h->le_phibuf);
+  CU(cudaGetLastError());
+  dim3 gfix((L.n[2] + 127)/128, L.n[1], T.nbuf);
+  if (npt == 27) le_grad_fix_kernel<27><<<gfix, block, 0, h->s_main>>>(T, h->phi, h->le_phibuf, h->grad, h->delsq);
+  else le_grad_fix_kernel<7><<<gfix, block, 0, h->s_main>>>(T, h->phi, h->le_phibuf, h->grad, h->delsq);
+  CU(cudaGetLastError());
+  h->launches += 2;
+  return 0;
+}
+
 static int run_grad7(b200lb_s * h) {
   const Layout & L = h->L;
   if (need_planes(h, &h->grad, 3) || need_planes(h, &h->delsq, 1)) return -1;
@@ -1454,6 +1498,7 @@ static int run_grad7(b200lb_s * h) {
 					      h->phi, h->grad, h->delsq);
   CU(cudaGetLastError());
   h->launches++;
+  if (le_grad_fix(h, 7)) return -1;
   h->grad_state = 0;
   h->ch_grad_valid = true; h->ch_halo_done = false;
   return 0;
@@ -1470,6 +1515,7 @@ static int run_grad27(b200lb_s * h) {
 					       h->phi, h->grad, h->delsq);
   CU(cudaGetLastError());
   h->launches++;
+  if (le_grad_fix(h, 27)) return -1;
   h->grad_state = 0;
   h->ch_grad_valid = true; h->ch_halo_done = false;
   return 0;
@@ -1519,7 +1565,7 @@ extern "C" int b200lb_grad7(b200lb_t * h) {
   if (!h) return fail("null handle");
   if (!h->phi) return fail("no order parameter (ndist = 1)");
   if (resolve_ch_force(h)) return -1;     // a recorded force wants the gradient being replaced
-  if (h->opt_grad_lazy && h->desc.ndist == 2) {
+  if (h->opt_grad_lazy && h->desc.ndist == 2 && h->le_nlocal == 0) {
     // The only consumer on the path is the binary collision, which evaluates the same
     // 7-point stencil in registers; the arrays are filled when somebody asks for them.
     h->grad_state = 1;
@@ -1774,10 +1820,11 @@ extern "C" int b200lb_visc_update(b200lb_t * h) {
 extern "C" int b200lb_step(b200lb_t * h, int nsteps) {
   if (!h) return fail("null handle");
   const double zero[3] = {0.0, 0.0, 0.0};
-  if (h->le_nlocal && h->desc.ndist == 2)
-    return fail("time loop: the order parameter and its gradient across Lees-Edwards planes (src/field.c, src/gradient_3d_7pt_fluid.c) are not on this path");
   for (int n = 0; n < nsteps; n++) {
     if (b200lb_hydro_f_zero(h, zero)) return -1;
+    // physics_control_time of the step about to start (src/physics.c:651-659): what the
+    // order parameter is displaced by across the planes; the distributions use the step number
+    h->le_field_t = 1.0*(h->le_tstart + h->le_step);
     if (h->desc.ndist == 2) {
       if (b200lb_phi_from_g(h)) return -1;
       if (b200lb_phi_halo(h)) return -1;

@@ -128,7 +128,17 @@ int lb_collide(lb_t * lb, hydro_t * hydro, map_t * map, noise_t * noise, fe_t * 
 /* physics time, as far as the hot path reads it */
 
 int physics_control_next_step(physics_t * phys) { phys->t_current += 1; return 0; }
-int physics_control_time(physics_t * phys, double * t) { *t = 1.0*phys->t_current; return 0; }
+int physics_control_init_time(physics_t * phys, int nstart, int nstep) {
+  (void) nstep;
+  phys->t_start = nstart;
+  phys->t_current = nstart;
+  return 0;
+}
+int physics_control_timestep(physics_t * phys) { return phys->t_current; }
+int physics_control_time(physics_t * phys, double * t) {
+  *t = 1.0*(phys->t_start + phys->t_current - 1.0);
+  return 0;
+}
 
 /* lees_edw_t: plane positions, reprojection and displacement live in the library */
 
@@ -157,10 +167,9 @@ int lees_edw_plane_location(lees_edw_t * le, int plane) {
 /* The reference copies the lattice to the host, works there and copies it back
  * (src/model_le.c:70-83); here the planes are handled where the lattice is. */
 int lb_le_apply_boundary_conditions(lb_t * lb, lees_edw_t * le) {
-  double t = 0.0;
   if (lees_edw_nplane_local(le) == 0) return 0;
-  physics_control_time(lb->phys, &t);
-  TRY(b200lb_le_apply(lb->target, t));
+  /* the distributions are displaced for the step number (src/model_le.c:133,245) */
+  TRY(b200lb_le_apply(lb->target, 1.0*physics_control_timestep(lb->phys)));
   return 0;
 }
 
@@ -505,6 +514,12 @@ int field_grad_set(field_grad_t * g, grad_ft d2, grad_ft d4) {
 }
 
 int field_grad_compute(field_grad_t * g) {
+  /* field_leesedwards(obj->field) (src/field_grad.c:310) displaces the order parameter
+   * across the planes for physics_control_time (src/field.c:553): in the library that is
+   * part of the gradient call */
+  double t = 0.0;
+  physics_control_time(g->lb->phys, &t);
+  TRY(b200lb_le_field_time_set(g->lb->target, t));
   /* obj->d2(obj) (src/field_grad.c:312) */
   return g->d2(g);
 }

@@ -55,9 +55,12 @@ typedef struct physics_s {
   double kt;                       /* physics_kt: isothermal fluctuations */
   int t_current;                   /* physics_control_timestep (src/physics.c) */
   double grad_mu[3];               /* physics_grad_mu: external chemical potential gradient */
+  int t_start;                     /* the step this run started from (0 unless restarted) */
 } physics_t;
-int physics_control_next_step(physics_t * phys);                   /* src/physics.h:34 */
-int physics_control_time(physics_t * phys, double * t);            /* src/physics.h:54 */
+int physics_control_next_step(physics_t * phys);                   /* src/physics.c:670 */
+int physics_control_init_time(physics_t * phys, int nstart, int nstep);  /* src/physics.c:687 */
+int physics_control_timestep(physics_t * phys);                    /* src/physics.c:635: the step number */
+int physics_control_time(physics_t * phys, double * t);            /* src/physics.c:651: t_start + t_current - 1 */
 
 typedef struct lb_data_options_s {
   int ndim;

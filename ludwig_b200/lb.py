@@ -38,6 +38,7 @@ ABI_SYMBOLS = [
     "b200lb_noise_state_download",
     "b200lb_wall_commit", "b200lb_wall_slip_set", "b200lb_wall_bbl", "b200lb_wall_momentum", "b200lb_wall_momentum_add",
     "b200lb_le_commit", "b200lb_le_apply", "b200lb_le_plane_location", "b200lb_le_time_set",
+    "b200lb_le_field_time_set",
     "b200lb_ch_create", "b200lb_ch_grad_mu_set", "b200lb_phi_force", "b200lb_cahn_hilliard",
     "b200lb_hydro_u_halo", "b200lb_visc_arrhenius_commit", "b200lb_visc_update", "b200lb_visc_model_set",
     "b200lb_field_stats", "b200lb_io_record_doubles", "b200lb_io_pack", "b200lb_io_unpack",
@@ -124,6 +125,7 @@ def load():
     L.b200lb_le_apply.argtypes = [vp, ctypes.c_double]
     L.b200lb_le_plane_location.argtypes = [vp, ctypes.c_int]
     L.b200lb_le_time_set.argtypes = [vp, ctypes.c_int]
+    L.b200lb_le_field_time_set.argtypes = [vp, ctypes.c_double]
     L.b200lb_ch_create.argtypes = [vp, ctypes.c_int, ctypes.c_int]
     L.b200lb_ch_grad_mu_set.argtypes = [vp, vp]
     for name in ("b200lb_phi_force", "b200lb_cahn_hilliard", "b200lb_hydro_u_halo"):
@@ -393,6 +395,10 @@ class Lattice:
 
     def le_time_set(self, nstep):
         self._ck(self.L.b200lb_le_time_set(self.h, int(nstep)))
+
+    def le_field_time_set(self, t):
+        """physics_control_time for the field_leesedwards of the next field_grad_compute."""
+        self._ck(self.L.b200lb_le_field_time_set(self.h, float(t)))
 
     # -- statistics and file records without the full-field D2H ---------------------
     def field_stats(self, field):

@@ -148,12 +148,23 @@ typedef struct orc_le_s {
   int period;             /* LE_oscillation_period (time steps) */
   int nt0;                /* LE_time_offset */
   int t_current;          /* physics_control_timestep */
+  int t_start;            /* first step of this run (0 unless restarted): the order parameter
+			   * is displaced for the time t_start + t_current - 1 of
+			   * physics_control_time (src/physics.c:651-659), the distributions for
+			   * the step number t_current */
 } orc_le_t;
 int orc_le_attach(orc_le_t * le);
 orc_le_t * orc_le_attached(void);
 int orc_le_plane_location(const orc_box_t * box, const orc_le_t * le, int np);
 int orc_le_apply(const orc_model_t * model, const orc_box_t * box, int ndist,
 		 const orc_le_t * le, double t, double * f);
+/* the order parameter across the planes (binary fluid, one-site halo): the buffer
+ * planes of field_leesedwards, buf[2 nplanes][nall_y][nall_z], and field_grad_compute
+ * with them (npt = 7 or 27) */
+int orc_le_field_buffers(const orc_box_t * box, const orc_le_t * le, double t,
+			 const double * phi, double * buf);
+int orc_le_field_grad(const orc_box_t * box, const orc_le_t * le, double t, int npt,
+		      const double * phi, double * grad, double * delsq);
 
 /* Finite-difference order parameter (lb_oracle_ch.c; "free_energy symmetric":
  * src/phi_force.c, src/phi_force_stress.c, src/phi_grad_mu.c, src/advection.c,

@@ -401,7 +401,13 @@ int orc_step(const orc_model_t * model, const orc_box_t * box,
     if (ndist == 2) {
       orc_phi_from_g(model, box, a, phi);
       orc_halo_periodic(box, 1, phi);
-      if (grad_select_npt == 27) orc_grad_27pt(box, phi, grad, delsq);
+      if (orc_le_attached()) {
+	/* field_grad_compute: field_leesedwards, then the stencil across the planes */
+	const orc_le_t * le = orc_le_attached();
+	const double t = 1.0*(le->t_start + le->t_current - 1.0);
+	if (orc_le_field_grad(box, le, t, grad_select_npt, phi, grad, delsq)) return -1;
+      }
+      else if (grad_select_npt == 27) orc_grad_27pt(box, phi, grad, delsq);
       else orc_grad_7pt(box, phi, grad, delsq);
     }
     if (ndist == 1 && orc_ch_attached()) {

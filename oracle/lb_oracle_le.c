@@ -146,3 +146,163 @@ int orc_le_apply(const orc_model_t * model, const orc_box_t * box, int ndist,
   free(buf);
   return 0;
 }
+
+/* ---------------------------------------------------------------------------
+ * The order parameter across the planes (binary fluid, one-site halo).
+ *
+ * field_grad_compute first calls field_leesedwards (src/field_grad.c:310,
+ * src/field.c:500-600): for every plane two buffer planes of phi, one per side,
+ *   buffer 2p     the plane of sites x = loc(p),     seen from x = loc(p) + 1
+ *   buffer 2p + 1 the plane of sites x = loc(p) + 1, seen from x = loc(p)
+ * (lees_edw_ibuff_to_real, src/leesedwards.c:991-1005), displaced along y by what the
+ * plane has slid so far, -/+ u_y t (lees_edw_buffer_duy :1065-1078,
+ * lees_edw_buffer_displacement :633-655), with four-point Lagrange interpolation.
+ * The gradient stencils then take the x - 1 / x + 1 neighbours of the sites next to
+ * a plane from those buffers (lees_edw_ic_to_buff :1014-1047 as called from
+ * src/gradient_3d_7pt_fluid.c:264-265 and src/gradient_3d_27pt_fluid.c:262-265);
+ * with a one-site halo nothing else changes (the loops of grad_3d_*_fluid_le run over
+ * nextra = nhalo - 1 = 0 planes).
+ *
+ * buf[2 nplanes][nall_y][nall_z]; one rank (the reference's own branch for a
+ * y-extent of one rank, src/field.c:540-585). phi needs current y and z halos.
+ * --------------------------------------------------------------------------- */
+
+int orc_le_field_buffers(const orc_box_t * box, const orc_le_t * le, double t,
+			 const double * phi, double * buf) {
+
+  const int ny = box->nlocal[1], nz = box->nlocal[2];
+  const long sx = (long) box->nall[1]*box->nall[2];
+  const long sy = box->nall[2];
+  const double r6 = (1.0/6.0);
+
+  if (le->nplanes <= 0) return 0;
+  if (box->nlocal[0] % le->nplanes) return -1;
+
+  for (int ib = 0; ib < 2*le->nplanes; ib++) {
+    const int ic = orc_le_plane_location(box, le, ib/2) + ib % 2;
+    const double tle = ((t < 0.0) ? 0.0 : t) - 1.0*le->nt0;
+    double dy = tle*le->uy*((ib % 2 < 1) ? -1 : +1);
+    int jdy;
+    double fr;
+    if (le->oscillatory) {
+      const double omega = 2.0*4.0*atan(1.0)/le->period;
+      dy = le->uy*sin(omega*tle)/omega;
+    }
+    dy = fmod(dy, 1.0*ny);
+    jdy = (int) floor(dy);
+    fr = 1.0 - (dy - jdy);
+    for (int jc = 0; jc <= ny + 1; jc++) {
+      const int j0 = 1 + (jc - jdy - 3 + 2*ny) % ny;
+      const int j1 = 1 + j0 % ny;
+      const int j2 = 1 + j1 % ny;
+      const int j3 = 1 + j2 % ny;
+      for (int kc = 0; kc <= nz + 1; kc++) {
+	buf[ib*sx + jc*sy + kc] =
+	  -  r6*fr*(fr-1.0)*(fr-2.0)*phi[orc_index(box, ic, j0, kc)]
+	  + 0.5*(fr*fr-1.0)*(fr-2.0)*phi[orc_index(box, ic, j1, kc)]
+	  - 0.5*fr*(fr+1.0)*(fr-2.0)*phi[orc_index(box, ic, j2, kc)]
+	  +        r6*fr*(fr*fr-1.0)*phi[orc_index(box, ic, j3, kc)];
+      }
+    }
+  }
+  return 0;
+}
+
+/* the x-plane (its element jc = 0, kc = 0) that a site at ic sees at ic + di */
+static const double * le_xplane(const orc_box_t * box, const orc_le_t * le,
+				const double * phi, const double * buf, int ic, int di) {
+  const long sx = (long) box->nall[1]*box->nall[2];
+  /* one candidate plane per x, as lees_edw_ic_to_buff finds it (src/leesedwards.c:1028-1029) */
+  int p = ic/(box->nlocal[0]/le->nplanes);
+  if (p > le->nplanes - 1) p = le->nplanes - 1;
+  if (p < 0) p = 0;
+  {
+    const int loc = orc_le_plane_location(box, le, p);
+    if (di == +1 && ic == loc) return buf + (2*p + 1)*sx;
+    if (di == -1 && ic == loc + 1) return buf + (2*p)*sx;
+  }
+  return phi + (ic + di)*sx;
+}
+
+/* field_grad_compute with planes: npt = 7 (src/gradient_3d_7pt_fluid.c:232-313) or
+ * 27 (src/gradient_3d_27pt_fluid.c:216-365), terms in the reference's order */
+int orc_le_field_grad(const orc_box_t * box, const orc_le_t * le, double t, int npt,
+		      const double * phi, double * grad, double * delsq) {
+
+  const long sx = (long) box->nall[1]*box->nall[2];
+  const long sy = box->nall[2];
+  const double r9 = (1.0/9.0);
+  double * buf;
+
+  if (npt != 7 && npt != 27) return -1;
+  if (le->nplanes <= 0 || box->nlocal[0] % le->nplanes) return -1;
+  buf = (double *) malloc(sizeof(double)*2*le->nplanes*sx);
+  if (buf == NULL) return -1;
+  if (orc_le_field_buffers(box, le, t, phi, buf)) { free(buf); return -1; }
+
+  for (int ic = 1; ic <= box->nlocal[0]; ic++) {
+    const double * pl[3];
+    pl[0] = le_xplane(box, le, phi, buf, ic, -1);
+    pl[1] = phi + ic*sx;
+    pl[2] = le_xplane(box, le, phi, buf, ic, +1);
+    for (int jc = 1; jc <= box->nlocal[1]; jc++) {
+      for (int kc = 1; kc <= box->nlocal[2]; kc++) {
+	const long i = orc_index(box, ic, jc, kc);
+	const long o = jc*sy + kc;
+	const double * xm = pl[0] + o, * x0 = pl[1] + o, * xp = pl[2] + o;
+	if (npt == 7) {
+	  grad[3*i + 0] = 0.5*(xp[0] - xm[0]);
+	  grad[3*i + 1] = 0.5*(x0[sy] - x0[-sy]);
+	  grad[3*i + 2] = 0.5*(x0[1] - x0[-1]);
+	  delsq[i] = xp[0] + xm[0] + x0[sy] + x0[-sy] + x0[1] + x0[-1] - 6.0*x0[0];
+	}
+	else {
+	  const double * q[3] = {xm, x0, xp};
+	  double gx = 0.0, gy = 0.0, gz = 0.0, d2 = 0.0;
+	  int first;
+	  first = 1;
+	  for (int b = -1; b <= 1; b++) {
+	    for (int c = -1; c <= 1; c++) {
+	      gx = first ? xp[b*sy + c] : gx + xp[b*sy + c];
+	      gx = gx - xm[b*sy + c];
+	      first = 0;
+	    }
+	  }
+	  first = 1;
+	  for (int a = 0; a < 3; a++) {
+	    for (int c = -1; c <= 1; c++) {
+	      gy = first ? q[a][sy + c] : gy + q[a][sy + c];
+	      gy = gy - q[a][-sy + c];
+	      first = 0;
+	    }
+	  }
+	  first = 1;
+	  for (int a = 0; a < 3; a++) {
+	    for (int b = -1; b <= 1; b++) {
+	      gz = first ? q[a][b*sy + 1] : gz + q[a][b*sy + 1];
+	      gz = gz - q[a][b*sy - 1];
+	      first = 0;
+	    }
+	  }
+	  first = 1;
+	  for (int a = 0; a < 3; a++) {
+	    for (int b = -1; b <= 1; b++) {
+	      for (int c = -1; c <= 1; c++) {
+		if (a == 1 && b == 0 && c == 0) continue;
+		d2 = first ? q[a][b*sy + c] : d2 + q[a][b*sy + c];
+		first = 0;
+	      }
+	    }
+	  }
+	  d2 = d2 - 26.0*x0[0];
+	  grad[3*i + 0] = 0.5*r9*gx;
+	  grad[3*i + 1] = 0.5*r9*gy;
+	  grad[3*i + 2] = 0.5*r9*gz;
+	  delsq[i] = r9*d2;
+	}
+      }
+    }
+  }
+  free(buf);
+  return 0;
+}

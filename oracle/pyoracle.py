@@ -71,6 +71,7 @@ class LeesEdwards(ctypes.Structure):
         ("period", ctypes.c_int),
         ("nt0", ctypes.c_int),
         ("t_current", ctypes.c_int),
+        ("t_start", ctypes.c_int),
     ]
 
 
@@ -234,10 +235,10 @@ class Oracle:
         assert self.L.orc_gradient_select(int(npt)) == 0
 
     # -- Lees-Edwards planes (oracle/lb_oracle_le.c) --------------------------------
-    def le(self, nplanes, uy, oscillatory=0, period=0, nt0=0, t_current=0):
+    def le(self, nplanes, uy, oscillatory=0, period=0, nt0=0, t_current=0, t_start=0):
         le = LeesEdwards()
         le.nplanes, le.uy, le.oscillatory = nplanes, uy, oscillatory
-        le.period, le.nt0, le.t_current = period, nt0, t_current
+        le.period, le.nt0, le.t_current, le.t_start = period, nt0, t_current, t_start
         return le
 
     def le_attach(self, le):
@@ -250,6 +251,22 @@ class Oracle:
         rc = self.L.orc_le_apply(ctypes.byref(self.model), ctypes.byref(self.box), self.ndist,
                                  ctypes.byref(le), float(t), _p(f))
         assert rc == 0
+
+    def le_field_buffers(self, le, t, phi):
+        """field_leesedwards: buf[2 nplanes, nall_y, nall_z]."""
+        buf = np.zeros((2*le.nplanes, self.nall[1], self.nall[2]))
+        self.L.orc_le_field_buffers.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_double,
+                                                c_double_p, c_double_p]
+        assert self.L.orc_le_field_buffers(ctypes.byref(self.box), ctypes.byref(le), float(t),
+                                           _p(phi), _p(buf)) == 0
+        return buf
+
+    def le_field_grad(self, le, t, npt, phi, grad, delsq):
+        """field_grad_compute with planes (field_leesedwards + the stencil across them)."""
+        self.L.orc_le_field_grad.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_double,
+                                             ctypes.c_int, c_double_p, c_double_p, c_double_p]
+        assert self.L.orc_le_field_grad(ctypes.byref(self.box), ctypes.byref(le), float(t), int(npt),
+                                        _p(phi), _p(grad), _p(delsq)) == 0
 
     def le_plane_location(self, le, n):
         return self.L.orc_le_plane_location(ctypes.byref(self.box), ctypes.byref(le), int(n))

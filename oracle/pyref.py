@@ -115,6 +115,10 @@ class Ref:
     def phi(self):
         return self._arr(self.L.refdrv_phi(), (self.nsite,))
 
+    def phi_all(self):
+        """phi with the buffer planes of field_leesedwards behind the nall_x real ones."""
+        return self._arr(self.L.refdrv_phi(), (self.L.refdrv_phi_nsites(),))
+
     def grad(self):
         return self._arr(self.L.refdrv_grad(), (self.nsite, 3))
 
@@ -195,6 +199,11 @@ class Ref:
     def time_set(self, t):
         """The next refdrv_step starts with physics_control_next_step from here."""
         self.L.refdrv_time_set(int(t))
+
+    def time(self):
+        """physics_control_time: what the displacement of the order parameter is taken at."""
+        self.L.refdrv_time.restype = ctypes.c_double
+        return self.L.refdrv_time()
 
     def wall(self, isboundary, ubot=(0.0, 0.0, 0.0), utop=(0.0, 0.0, 0.0)):
         """boundary_walls / boundary_speed_bottom,_top: wall_create + wall_commit."""

@@ -266,6 +266,7 @@ double * refdrv_rho(void)   { return rd.hydro->rho->data; }
 double * refdrv_u(void)     { return rd.hydro->u->data; }
 double * refdrv_force(void) { return rd.hydro->force->data; }
 double * refdrv_phi(void)   { return rd.phi ? rd.phi->data : NULL; }
+int refdrv_phi_nsites(void) { return rd.phi ? rd.phi->nsites : 0; }   /* with the Lees-Edwards buffer planes */
 double * refdrv_grad(void)  { return rd.phi_grad ? rd.phi_grad->grad : NULL; }
 double * refdrv_delsq(void) { return rd.phi_grad ? rd.phi_grad->delsq : NULL; }
 char   * refdrv_status(void) { return rd.map->status; }
@@ -357,6 +358,7 @@ int refdrv_le_apply(int t) {
 }
 int refdrv_le_plane_location(int np) { return lees_edw_plane_location(rd.le, np); }
 int refdrv_time_set(int t) { return physics_control_init_time(rd.phys, t, 1); }
+double refdrv_time(void) { double t; physics_control_time(rd.phys, &t); return t; }
 
 /* Flat walls: what wall_rt_init does for "boundary_walls" / "boundary_speed_*"
  * (src/wall_rt.c:40-120): wall_create + wall_commit (map, links, wall velocities). */

@@ -5,7 +5,7 @@ cases d3q19-short/serial-spin-lb{1,3,4}.log (symmetric_lb, 27-point gradient, lb
 fluctuations, lb1/lb4 with ghost modes off), and the wall cases d3q19-short/serial-rect-ct1
 (body-force driven duct flow between y and z walls) and serial-wall-st1 (closed box with
 fluctuations), the finite-difference order-parameter cases (free_energy symmetric)
-serial-spin-fd1, serial-symm-dr1, serial-symm-dr2 (viscosity model), serial-symm-pat, serial-muex-st1 and the 400-step
+serial-spin-fd1, serial-symm-dr1, serial-symm-dr2 (viscosity model), serial-le2d-lb1 (symmetric_lb sheared by two Lees-Edwards planes), serial-symm-pat, serial-muex-st1 and the 400-step
 d3q19/pmpi08-spin-fd1, serial-rect-ct2..5 (the duct with partial-slip walls), and the 400-step, eight-rank spinodal case d3q19/pmpi08-spin-lb1 (its log does
 not depend on the decomposition), Ludwig v0.20.1)
 into tests/golden/regression_logs.json, together with the input keys that define each
@@ -28,7 +28,9 @@ CASES = ["d3q19-short/serial-dist-3du", "d3q19-short/serial-dist-1dp",
          "d3q19-short/serial-spin-fd1", "d3q19-short/serial-symm-dr1",
          "d3q19-short/serial-symm-pat", "d3q19-short/serial-muex-st1", "d3q19/pmpi08-spin-fd1",
          # ... with viscosity_model arrhenius (the collision reads a per-site viscosity)
-         "d3q19-short/serial-symm-dr2"]
+         "d3q19-short/serial-symm-dr2",
+         # binary fluid across two Lees-Edwards planes (a sheared 64 x 64 x 1 system)
+         "d3q19-short/serial-le2d-lb1"]
 NVEL = {"d3q19-short": 19, "d3q19": 19, "d2q9": 9}
 
 

@@ -1286,11 +1286,6 @@ def test_lees_edwards_refusals():
     with pytest.raises(RuntimeError):
         lat.le_apply_boundary_conditions(1)       # after the propagation: wrong place
     lat.close()
-    lat = lb.Lattice(19, (12, 8, 4), ndist=2)
-    lat.le_commit(2, 0.01)
-    with pytest.raises(RuntimeError):
-        lat.step(1)                               # binary time loop needs the sheared phi halo
-    lat.close()
     lat = lb.Lattice(19, (12, 8, 4), periodic=(1, 0, 1))
     with pytest.raises(RuntimeError):
         lat.le_commit(2, 0.01)

@@ -462,19 +462,91 @@ def test_lees_edwards(nvel, nlocal, ndist, le):
         fp = np.zeros_like(f)
         rho, u, frc = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
         phi, grad, delsq = np.zeros(n), np.zeros((n, 3)), np.zeros(n)
-        ole.t_current = 5
+        ole.t_current, ole.t_start = 5, 5
         orc.le_attach(ole)
         try:
             orc.step(prm, 9, f, fp, rho, u, frc, phi, grad, delsq)
         finally:
             orc.le_attach(None)
-        if ndist == 1:
-            assert relerr(f[m], ref.f()[m]) < 1e-12
-        else:
-            # the reference's phi halo and gradient are Lees-Edwards aware; the oracle's are
-            # not (out of scope), so only the density distribution's first step agrees
-            pass
+        # ndist 2: the gradient of phi across the planes feeds the binary collision
+        assert relerr(f[m], ref.f()[m]) < 1e-12
         assert abs(f[m][:, 0].sum() - f0[m][:, 0].sum()) < 1e-10
+
+
+@pytest.mark.parametrize("nlocal,le", [
+    ((16, 6, 4), dict(nplanes=2, uy=0.05)),
+    ((12, 7, 5), dict(nplanes=1, uy=-0.03)),
+    ((12, 8, 4), dict(nplanes=3, uy=0.02)),
+    ((8, 9, 6), dict(nplanes=4, uy=0.31)),
+    ((16, 6, 4), dict(nplanes=2, uy=0.04, oscillatory=1, period=40, nt0=0))])
+@pytest.mark.parametrize("npt", [7, 27])
+def test_lees_edwards_order_parameter(nlocal, le, npt):
+    """field_grad_compute with planes (src/field_grad.c:305-325): the buffer planes of
+    field_leesedwards (src/field.c:500-600; four-point interpolation along y at the
+    displacement the planes have reached) and the 7- and 27-point stencils that read
+    them (lees_edw_ic_to_buff in src/gradient_3d_7pt_fluid.c, _27pt_fluid.c), bit for
+    bit; then the binary time loop across the planes."""
+    nvel = 19
+    need_ref(nvel)
+    orc = pyoracle.Oracle(nvel, nlocal, ndist=2)
+    m = orc.interior_mask()
+    n = orc.nsite
+    nall = orc.nall
+    rng = np.random.default_rng(12)
+    phi0 = np.zeros(nall)
+    phi0[1:-1, 1:-1, 1:-1] = 0.4*(rng.random(nlocal) - 0.5)
+    phi0 = phi0.reshape(-1)
+    orc.halo(phi0, 1)
+    ole = orc.le(**le)
+    kw = dict(eta_shear=0.00625, eta_bulk=0.00625, mobility=3.75)
+    prm = pyoracle.make_param(a=-0.00625, b=0.00625, kappa=0.004, **kw)
+    with pyref.Ref(nvel, nlocal, ndist=2, le=le) as ref:
+        ref.physics(**kw)
+        ref.fe_symm(-0.00625, 0.00625, 0.004)
+        ref.grad_select(npt)
+        for t in (0, 1, 7, 20, 133, 1000):
+            ref.time_set(t)
+            ref.phi_all()[...] = 0.0
+            ref.phi()[...] = phi0
+            ref.grad_compute()
+            t = ref.time()                                    # t_start + t_current - 1
+            buf = orc.le_field_buffers(ole, t, phi0)
+            rbuf = ref.phi_all()[n:].reshape(buf.shape)
+            assert np.array_equal(buf, rbuf), t
+            assert np.array_equal(ref.phi(), phi0)           # the real planes are untouched
+            grad, delsq = np.zeros((n, 3)), np.zeros(n)
+            orc.le_field_grad(ole, t, npt, phi0, grad, delsq)
+            assert np.array_equal(grad[m], ref.grad()[m]), t
+            assert np.array_equal(delsq[m], ref.delsq()[m]), t
+        # it differs from the stencil that knows nothing about the planes, next to them only
+        g0, d0 = np.zeros((n, 3)), np.zeros(n)
+        (orc.grad_27pt if npt == 27 else orc.grad_7pt)(phi0, g0, d0)
+        x = np.arange(nall[0])[:, None, None]*np.ones(nall, dtype=int)
+        near = np.zeros(nall, dtype=bool)
+        for k in range(le["nplanes"]):
+            loc = orc.le_plane_location(ole, k)
+            near |= (x == loc) | (x == loc + 1)
+        near = near.reshape(-1)
+        assert np.array_equal(grad[m & ~near], g0[m & ~near])
+        assert not np.array_equal(grad[m & near], g0[m & near])
+        # the time loop
+        f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal, ndist=2)
+        ref.f()[...] = f0
+        ref.time_set(5)
+        ref.step(9)
+        f, fp = f0.copy(), np.zeros_like(f0)
+        rho, u, frc = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
+        phi, grad, delsq = np.zeros(n), np.zeros((n, 3)), np.zeros(n)
+        ole.t_current, ole.t_start = 5, 5
+        orc.le_attach(ole)
+        orc.gradient_select(npt)
+        try:
+            orc.step(prm, 9, f, fp, rho, u, frc, phi, grad, delsq)
+        finally:
+            orc.gradient_select(7)
+            orc.le_attach(None)
+        assert relerr(f[m], ref.f()[m]) < 1e-12
+        assert np.max(np.abs(grad[m] - ref.grad()[m])) < 1e-12
 
 
 # ---------------------------------------------------------------------------

@@ -6,7 +6,8 @@ and lb4 fluctuating, lb1 and lb4 with ghost modes off; and with walls serial-rec
 driven by a body force) serial-wall-st1 (closed box, fluctuating) and serial-rect-ct2..5 (partial-slip walls); and the finite-difference order parameter
 (free_energy symmetric) serial-spin-fd1, serial-symm-dr1, serial-symm-pat, serial-muex-st1
 (phi grad mu force with an external chemical-potential gradient) and the 400-step
-d3q19/pmpi08-spin-fd1: the statistics printed after the last step,
+d3q19/pmpi08-spin-fd1; and serial-le2d-lb1, the binary fluid sheared by two Lees-Edwards
+planes from the steady profile (LE_init_profile): the statistics printed after the last step,
 reproduced the way tests/test-diff.sh + tests/awk-fp-diff.sh judge them -- every printed
 float, in the reference's printf format, within an ABSOLUTE 1e-12.
 
@@ -70,6 +71,8 @@ def initial_state(inp, cv, wv):
     ndist = 2 if inp.get("free_energy") == "symmetric_lb" else 1
     f = np.zeros(nall + (ndist, len(wv)))
     f[1:-1, 1:-1, 1:-1, 0, :] = feq.reshape(nt + (len(wv),))
+    if le_options(inp) and int(inp.get("LE_init_profile", 0)):
+        f[1:-1, 1:-1, 1:-1, 0, :] = shear_profile(inp, nt, cv, wv)
     if ndist == 2:
         # phi_initialisation spinodal (src/field_phi_init_rt.c:57-65), then phi_lb_from_field
         # (src/phi_lb_coupler.c:114): phi into the rest population, the others zero
@@ -78,6 +81,41 @@ def initial_state(inp, cv, wv):
                                   float(inp.get("noise", 0.1)))
         f[1:-1, 1:-1, 1:-1, 1, 0] = phi
     return nt, np.ascontiguousarray(f.reshape(-1, ndist, len(wv)))
+
+
+def le_options(inp):
+    """N_LE_plane, LE_plane_vel (src/leesedwards_rt.c): steady shear, or None."""
+    if int(inp.get("N_LE_plane", 0)) == 0:
+        return None
+    assert "LE_oscillation_period" not in inp and "LE_time_offset" not in inp
+    return dict(nplanes=int(inp["N_LE_plane"]), uy=float(inp["LE_plane_vel"]))
+
+
+def shear_profile(inp, nt, cv, wv):
+    """lb_le_init_shear_profile (src/model_le.c:646-715): the steady linear profile between
+    the planes, u_y = x gammadot - (planes crossed) u_le (lees_edw_steady_uy,
+    src/leesedwards.c:492-516), with its viscous stress -eta gammadot in the xy moment."""
+    le = le_options(inp)
+    rho0, eta = 1.0, float(inp["viscosity"])
+    cs2, rcs2 = 1.0/3.0, 3.0
+    gammadot = le["uy"]*le["nplanes"]/nt[0]
+    dx_sep = 1.0*nt[0]/le["nplanes"]
+    dx_min = 0.5*dx_sep
+    out = np.zeros(nt + (len(wv),))
+    for ic in range(1, nt[0] + 1):
+        xglobal = 1.0*ic - 0.5
+        uy = xglobal*gammadot - le["uy"]*int((dx_min + xglobal)/dx_sep)
+        u = [0.0, uy, 0.0]
+        for p in range(len(wv)):
+            cdotu = sum(cv[p][i]*u[i] for i in range(3))
+            sdotq = 0.0
+            for i in range(3):
+                for j in range(3):
+                    gradu = gammadot if (i, j) == (0, 1) else 0.0
+                    qij = cv[p][i]*cv[p][j] - cs2*(i == j)
+                    sdotq += (rho0*u[i]*u[j] - eta*gradu)*qij
+            out[ic - 1, :, :, p] = wv[p]*(rho0 + rcs2*rho0*cdotu + 0.5*rcs2*rcs2*sdotq)
+    return out
 
 
 def printed(fmt, x):
@@ -287,6 +325,10 @@ def viscosities(inp):
     return eta, float(inp.get("viscosity_bulk", eta))
 
 
+# Written and checked on the host (tools/check_le_field_on_host.py steps through the kernel
+# source against the oracle) after the round's GPU allocation was spent: the device run
+# of these cases is opt-in until it has been seen to pass on a B200 once.
+UNVERIFIED_ON_GPU = {"serial-le2d-lb1"}
 LONG = {"pmpi08-spin-lb1", "pmpi08-spin-fd1"}      # 400 steps: the momentum line is accumulated round-off
 SLOW = {"pmpi08-spin-lb1"}      # minutes on the CPU oracle: opt in with B200LB_LONG=1 (fd1 takes half a minute)
 
@@ -322,6 +364,8 @@ def test_oracle_reproduces_reference_log(case):
         orc.noise_attach(orc.noise_init(0), float(rec["input"]["temperature"]))
     orc.gradient_select(gradient_points(rec))
     orc.wall_attach(wall)
+    if le_options(rec["input"]):
+        orc.le_attach(orc.le(**le_options(rec["input"])))
     if fd_route(rec):
         phi.reshape(orc.nall)[1:-1, 1:-1, 1:-1] = initial_phi(rec["input"], nt)
         orc.ch_attach(orc.ch(*fd_options(rec["input"])))
@@ -335,6 +379,7 @@ def test_oracle_reproduces_reference_log(case):
         orc.wall_attach(None)
         orc.ch_attach(None)
         orc.visc_attach(None)
+        orc.le_attach(None)
     m = orc.interior_mask()
     sums = orc.stats(f)
     if case in LONG:
@@ -355,6 +400,9 @@ def test_oracle_reproduces_reference_log(case):
 def test_cuda_reproduces_reference_log(case, hydro_write):
     import ludwig_b200 as lb
     from ludwig_b200 import models_host
+    if case in UNVERIFIED_ON_GPU and not os.environ.get("B200LB_UNVERIFIED"):
+        pytest.skip("order parameter across Lees-Edwards planes: device path not yet run on a GPU "
+                    "(set B200LB_UNVERIFIED=1); the oracle reproduces this log in the CPU suite")
     rec = GOLD[case]
     nvel = rec["nvel"]
     nt, f = initial_state(rec["input"], models_host.cv(nvel), models_host.wv(nvel))
@@ -376,6 +424,8 @@ def test_cuda_reproduces_reference_log(case, hydro_write):
             lat.wall_slip_set(sbot, stop, 1)
     if ndist == 2:
         lat.field_grad_set(gradient_points(rec))
+    if le_options(rec["input"]):
+        lat.le_commit(**le_options(rec["input"]))
     if noisy(rec):
         lat.noise_init(0)
         lat.noise_present_set(1)

@@ -1,0 +1,122 @@
+"""GPU: the order parameter of the binary fluid across Lees-Edwards planes --
+field_leesedwards (src/field.c:500-600) and the plane-aware 7- and 27-point stencils
+(lees_edw_ic_to_buff in src/gradient_3d_7pt_fluid.c:264-265, _27pt_fluid.c:262-265) --
+against the oracle, which is pinned to the reference bit for bit
+(tests/test_oracle_vs_ref.py::test_lees_edwards_order_parameter): gradients bit-exact,
+the sheared binary time loop within 1e-12.
+
+Written after the round's GPU allocation was spent; the kernels were checked by stepping
+through their source on the host (tools/check_le_field_on_host.py). Until these tests
+have been seen to pass on a B200 once they are opt-in: B200LB_UNVERIFIED=1."""
+
+import os
+
+import numpy as np
+import pytest
+
+import lbinit
+from goldenlib import relerr
+
+pytestmark = [pytest.mark.gpu,
+              pytest.mark.skipif(not os.environ.get("B200LB_UNVERIFIED"),
+                                 reason="device path not yet run on a GPU: set B200LB_UNVERIFIED=1")]
+
+TOL = 1e-12
+KW = dict(eta_shear=0.00625, eta_bulk=0.00625, mobility=3.75, a=-0.00625, b=0.00625, kappa=0.004)
+CASES = [((16, 6, 4), dict(nplanes=2, uy=0.05)),
+         ((12, 7, 5), dict(nplanes=1, uy=-0.03)),
+         ((12, 8, 4), dict(nplanes=3, uy=0.02)),
+         ((9, 9, 140), dict(nplanes=3, uy=0.31)),
+         ((16, 6, 4), dict(nplanes=2, uy=0.04, oscillatory=1, period=40, nt0=0))]
+
+
+def commit(lat, le):
+    lat.le_commit(le["nplanes"], le["uy"], le.get("oscillatory", 0), le.get("period", 0), le.get("nt0", 0))
+
+
+@pytest.mark.parametrize("nlocal,le", CASES)
+@pytest.mark.parametrize("npt", [7, 27])
+@pytest.mark.parametrize("loopback", [0, 1])
+def test_gradient_across_planes_bit_exact(nlocal, le, npt, loopback):
+    import ludwig_b200 as lb
+    from oracle import pyoracle
+    orc = pyoracle.Oracle(19, nlocal, ndist=2)
+    lat = lb.Lattice(19, nlocal, ndist=2)
+    lat.set_option("loopback", loopback)
+    lat.set_param(**KW)
+    commit(lat, le)
+    ole = orc.le(**le)
+    n, nall = orc.nsite, orc.nall
+    m = orc.interior_mask()
+    rng = np.random.default_rng(3)
+    phi = np.zeros(nall)
+    phi[1:-1, 1:-1, 1:-1] = 0.4*(rng.random(nlocal) - 0.5)
+    phi = phi.reshape(-1)
+    lat.field_grad_set(npt)
+    for t in (0.0, 1.0, 7.0, 133.0, 1000.0):
+        lat.field_h2d(lb.FIELD_PHI, phi)
+        lat.field_halo()
+        lat.le_field_time_set(t)
+        lat.field_grad_compute()
+        ph = phi.copy()
+        orc.halo(ph, 1)
+        grad, delsq = np.zeros((n, 3)), np.zeros(n)
+        orc.le_field_grad(ole, t, npt, ph, grad, delsq)
+        assert np.array_equal(lat.field_d2h(lb.FIELD_GRAD)[m], grad[m]), t
+        assert np.array_equal(lat.field_d2h(lb.FIELD_DELSQ)[m], delsq[m]), t
+    lat.close()
+
+
+@pytest.mark.parametrize("nlocal,le", CASES)
+@pytest.mark.parametrize("npt", [7, 27])
+@pytest.mark.parametrize("fused", [1, 0])
+def test_sheared_binary_time_loop_vs_oracle(nlocal, le, npt, fused):
+    import ludwig_b200 as lb
+    from oracle import pyoracle
+    orc = pyoracle.Oracle(19, nlocal, ndist=2)
+    m = orc.interior_mask()
+    n = orc.nsite
+    f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal, ndist=2)
+    prm = pyoracle.make_param(**KW)
+    ole = orc.le(t_current=5, t_start=5, **le)
+    nsteps = 9
+    f, fp = f0.copy(), np.zeros_like(f0)
+    rho, u, frc = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
+    phi, grad, delsq = np.zeros(n), np.zeros((n, 3)), np.zeros(n)
+    orc.le_attach(ole)
+    orc.gradient_select(npt)
+    try:
+        orc.step(prm, nsteps, f, fp, rho, u, frc, phi, grad, delsq)
+    finally:
+        orc.gradient_select(7)
+        orc.le_attach(None)
+    lat = lb.Lattice(19, nlocal, ndist=2)
+    lat.set_param(**KW)
+    lat.set_option("fused", fused)
+    lat.set_option("gradient", npt)
+    commit(lat, le)
+    lat.le_time_set(5)
+    lat.lb_memcpy_h2d(f0)
+    lat.step(nsteps)
+    fd = lat.lb_memcpy_d2h()
+    assert relerr(fd[m], f[m]) < TOL
+    assert np.max(np.abs(lat.field_d2h(lb.FIELD_GRAD)[m] - grad[m])) < TOL
+    assert np.max(np.abs(lat.field_d2h(lb.FIELD_U)[m] - u[m])) < TOL
+    assert abs(fd[m][:, 0].sum() - f0[m][:, 0].sum()) < 1e-9
+    # the same through the separate calls, in the reference's order (src/ludwig.c:552-860)
+    lat.le_time_set(5)
+    lat.lb_memcpy_h2d(f0)
+    for s in range(nsteps):
+        step = 6 + s                                      # physics_control_next_step
+        lat.hydro_f_zero()
+        lat.phi_lb_to_field()
+        lat.field_halo()
+        lat.le_field_time_set(5 + step - 1.0)             # physics_control_time
+        lat.field_grad_compute()
+        lat.hydro_u_zero()
+        lat.lb_collide()
+        lat.le_apply_boundary_conditions(step)
+        lat.lb_halo()
+        lat.lb_propagation()
+    assert np.array_equal(lat.lb_memcpy_d2h()[m], fd[m])
+    lat.close()
