@@ -196,6 +196,13 @@ int orc_phi_force(const orc_box_t * box, const orc_param_t * prm, const orc_ch_t
 		  const double * phi, double * grad, double * delsq, double * force);
 int orc_cahn_hilliard(const orc_box_t * box, const orc_param_t * prm, const orc_ch_t * ch,
 		      double * phi, double * delsq, double * u);
+/* the same route across Lees-Edwards planes (lb_oracle_ch.c, second half): one step's
+ * field_halo + field_grad_compute [+ phi_force_calculation] [+ phi_cahn_hilliard] at
+ * t = physics_control_time; interior values of phi, u, force in the halo-1 layout */
+int orc_ch_le_step(const orc_box_t * box, const orc_param_t * prm, const orc_ch_t * ch,
+		   const orc_le_t * le, double t, int npt, int do_force, int do_update,
+		   double * phi, const double * u, double * force, double * grad, double * delsq);
+
 
 /* Viscosity model "arrhenius" (src/visc_arrhenius.c): eta = eta_minus^((1 - phi/phistar)/2)
  * eta_plus^((1 + phi/phistar)/2). While an eta array is attached, orc_collide_mrt takes each

@@ -413,11 +413,18 @@ int orc_step(const orc_model_t * model, const orc_box_t * box,
     if (ndist == 1 && orc_ch_attached()) {
       /* finite-difference order parameter ("free_energy symmetric"), src/ludwig.c:558-575,727-768 */
       const orc_ch_t * ch = orc_ch_attached();
+      if (orc_le_attached()) {
+	const orc_le_t * le = orc_le_attached();
+	const double t = 1.0*(le->t_start + le->t_current - 1.0);
+	if (orc_ch_le_step(box, prm, ch, le, t, grad_select_npt, 1, 1, phi, u, force, grad, delsq)) return -1;
+      }
+      else {
       orc_halo_periodic(box, 1, phi);
       if (grad_select_npt == 27) orc_grad_27pt(box, phi, grad, delsq);
       else orc_grad_7pt(box, phi, grad, delsq);
       if (orc_phi_force(box, prm, ch, phi, grad, delsq, force)) return -1;
       if (orc_cahn_hilliard(box, prm, ch, phi, delsq, u)) return -1;
+      }
     }
     orc_fill(box, 3, zero, u);
     {

@@ -278,6 +278,15 @@ class Oracle:
         c.grad_mu[:] = grad_mu
         return c
 
+    def ch_le_step(self, prm, ch, le, t, npt, phi, u, force, grad, delsq, do_force=1, do_update=1):
+        """One step of the finite-difference order parameter across Lees-Edwards planes."""
+        self.L.orc_ch_le_step.argtypes = [ctypes.c_void_p]*4 + [ctypes.c_double, ctypes.c_int,
+                                                                ctypes.c_int, ctypes.c_int] + [c_double_p]*5
+        rc = self.L.orc_ch_le_step(ctypes.byref(self.box), ctypes.byref(prm), ctypes.byref(ch),
+                                   ctypes.byref(le), float(t), int(npt), int(do_force), int(do_update),
+                                   _p(phi), _p(u), _p(force), _p(grad), _p(delsq))
+        assert rc == 0
+
     def ch_attach(self, ch):
         """orc_step (ndist = 1) runs the "free_energy symmetric" route while attached."""
         self._ch = ch

@@ -626,6 +626,90 @@ def test_cahn_hilliard_stages(order, method, npt, gmu):
         assert abs(phi[m].sum() - phi0[m].sum()) < 1e-13 * m.sum()
 
 
+FD_LE_CASES = [
+    ((16, 8, 6), dict(nplanes=2, uy=0.05), 1, pyoracle.FORCE_STRESS_DIVERGENCE, 7, (0.0, 0.0, 0.0)),
+    ((16, 8, 6), dict(nplanes=2, uy=0.05), 2, pyoracle.FORCE_STRESS_DIVERGENCE, 27, (0.0, 0.0, 0.0)),
+    ((12, 7, 5), dict(nplanes=1, uy=-0.03), 3, pyoracle.FORCE_STRESS_DIVERGENCE, 27, (0.0, 0.0, 0.0)),
+    ((15, 9, 6), dict(nplanes=3, uy=0.31), 3, pyoracle.FORCE_PHI_GRADMU, 7, (1e-5, 2e-5, 3e-5)),
+    ((16, 12, 1), dict(nplanes=2, uy=0.02), 1, pyoracle.FORCE_STRESS_DIVERGENCE, 27, (0.0, 0.0, 0.0)),
+    ((16, 8, 6), dict(nplanes=2, uy=0.04, oscillatory=1, period=40, nt0=0), 2,
+     pyoracle.FORCE_STRESS_DIVERGENCE, 7, (0.0, 0.0, 0.0)),
+]
+
+
+@pytest.mark.parametrize("nlocal,le,order,method,npt,gmu", FD_LE_CASES)
+def test_cahn_hilliard_lees_edwards(nlocal, le, order, method, npt, gmu):
+    """The finite-difference order parameter across Lees-Edwards planes: the gradient in
+    the buffer region, the flux form of the force with its plane correction
+    (src/phi_force.c:289-340), the velocity buffers, plane-aware advection and diffusive
+    fluxes, phi_ch_le_fix_fluxes and the update, stage by stage at several times and in
+    the time loop."""
+    nvel = 19
+    need_ref(nvel)
+    A, B, K, M, eta = -0.00625, 0.00625, 0.004, 1.25, 0.00625
+    orc = pyoracle.Oracle(nvel, nlocal)
+    prm = pyoracle.make_param(eta_shear=eta, eta_bulk=eta, mobility=M, a=A, b=B, kappa=K)
+    ch = orc.ch(order, method, gmu)
+    ole = orc.le(**le)
+    phi0, u0 = fd_fields(nlocal)
+    n = orc.nsite
+    m = orc.interior_mask()
+    with pyref.Ref(nvel, nlocal, fd=dict(order=order, method=method), le=le) as ref:
+        assert ref.nhalo == 2
+        ref.physics(eta_shear=eta, eta_bulk=eta, mobility=M)
+        ref.fe_symm(A, B, K)
+        ref.grad_mu(gmu)
+        ref.grad_select(npt)
+        for ts in (0, 1, 4, 67):
+            ref.time_set(ts)
+            t = ref.time()
+            ref.inner(ref.phi())[...] = phi0.reshape(orc.nall)
+            ref.inner(ref.u())[...] = u0.reshape(orc.nall + (3,))
+            ref.phi_halo()
+            ref.grad_compute()
+            ref.hydro_f_zero()
+            ref.phi_force()
+            phi, u = phi0.copy(), u0.copy()
+            force, grad, delsq = np.zeros((n, 3)), np.zeros((n, 3)), np.zeros(n)
+            orc.ch_le_step(prm, ch, ole, t, npt, phi, u, force, grad, delsq, do_update=0)
+            assert np.array_equal(grad[m], ref.inner(ref.grad()).reshape(-1, 3)[m]), ts
+            assert np.array_equal(delsq[m], ref.inner(ref.delsq()).reshape(-1)[m]), ts
+            fr = ref.inner(ref.force()).reshape(-1, 3)
+            assert np.array_equal(force[m], fr[m]), ts
+            if method != pyoracle.FORCE_NONE:
+                assert np.max(np.abs(force[m])) > 0.0
+            ref.cahn_hilliard()
+            orc.ch_le_step(prm, ch, ole, t, npt, phi, u, force, grad, delsq, do_force=0)
+            pr = ref.inner(ref.phi()).reshape(-1)
+            assert np.max(np.abs(phi[m] - phi0[m])) > 1e-6
+            assert np.array_equal(phi[m], pr[m]), ts
+            assert abs(phi[m].sum() - phi0[m].sum()) < 1e-12 * m.sum()
+        # the time loop
+        nsteps = 6
+        f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal)
+        ref.inner(ref.f())[...] = f0.reshape(orc.nall + (1, nvel))
+        ref.inner(ref.phi())[...] = phi0.reshape(orc.nall)
+        ref.hydro_u_zero()              # the stages above left their velocity field behind
+        ref.time_set(3)
+        ref.step(nsteps)
+        f, fp = f0.copy(), np.zeros_like(f0)
+        rho, u, force = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
+        grad, delsq = np.zeros((n, 3)), np.zeros(n)
+        phi = phi0.copy()
+        ole.t_current, ole.t_start = 3, 3
+        orc.gradient_select(npt)
+        orc.ch_attach(ch)
+        orc.le_attach(ole)
+        try:
+            orc.step(prm, nsteps, f, fp, rho, u, force, phi, grad, delsq)
+        finally:
+            orc.gradient_select(7)
+            orc.ch_attach(None)
+            orc.le_attach(None)
+        assert relerr(f[m], ref.inner(ref.f()).reshape(f.shape)[m]) < 1e-12
+        assert np.max(np.abs(phi[m] - ref.inner(ref.phi()).reshape(-1)[m])) < 1e-12
+
+
 @pytest.mark.parametrize("order,method,npt,gmu", FD_CASES[:4])
 def test_cahn_hilliard_time_loop(order, method, npt, gmu):
     nvel, nlocal, nsteps = 19, (8, 8, 8), 6
