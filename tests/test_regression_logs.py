@@ -329,6 +329,9 @@ def viscosities(inp):
 # source against the oracle) after the round's GPU allocation was spent: the device run
 # of these cases is opt-in until it has been seen to pass on a B200 once.
 UNVERIFIED_ON_GPU = {"serial-le2d-lb1"}
+# free_energy symmetric with planes: oracle only so far (the library refuses the combination)
+NOT_ON_DEVICE = {"serial-le3d-st1", "serial-le3d-st2", "serial-le3d-st3", "serial-le3d-st5",
+                 "serial-le3d-st6", "serial-le3d-st7", "serial-le2d-fd1"}
 LONG = {"pmpi08-spin-lb1", "pmpi08-spin-fd1"}      # 400 steps: the momentum line is accumulated round-off
 SLOW = {"pmpi08-spin-lb1"}      # minutes on the CPU oracle: opt in with B200LB_LONG=1 (fd1 takes half a minute)
 
@@ -400,6 +403,9 @@ def test_oracle_reproduces_reference_log(case):
 def test_cuda_reproduces_reference_log(case, hydro_write):
     import ludwig_b200 as lb
     from ludwig_b200 import models_host
+    if case in NOT_ON_DEVICE:
+        pytest.skip("the finite-difference order parameter across Lees-Edwards planes is not on the "
+                    "device path yet (b200lb_le_commit refuses it); the oracle reproduces this log")
     if case in UNVERIFIED_ON_GPU and not os.environ.get("B200LB_UNVERIFIED"):
         pytest.skip("order parameter across Lees-Edwards planes: device path not yet run on a GPU "
                     "(set B200LB_UNVERIFIED=1); the oracle reproduces this log in the CPU suite")
