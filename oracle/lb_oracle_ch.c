@@ -179,6 +179,13 @@ static double adv_face(int order, int west, double u0, double u1,
     if (west) return 0.5*(u0 + u1)*1*0.5*(phi1 + phi0);
     return 0.5*(u0 + u1)*1*0.5*(phi0 + phi1);
   }
+  if (order == 4) {
+    /* advection_le_4th, src/advection.c:1188-1290: four-point centred interpolation */
+    const double b1 = (1.0/16.0), b2 = (9.0/16.0);
+    const double u = 0.5*(u0 + u1);
+    if (west) return u*(- b1*phi2 + b2*phi1 + b2*phi0 - b1*phim);
+    return u*(- b1*phim + b2*phi0 + b2*phi1 - b1*phi2);
+  }
   {
     const double u = 0.5*1*(u0 + u1);
     double fd1, fd2, fd3;
@@ -202,7 +209,7 @@ int orc_ch_advection(const orc_box_t * box, int order, const double * u,
   double * fw = flux, * fe = flux + box->nsite, * fy = flux + 2*box->nsite,
     * fz = flux + 3*box->nsite;
 
-  if (order < 1 || order > 3) return -1;
+  if (order < 1 || order > 4) return -1;
 
   #pragma omp parallel for
   for (ic = 1; ic <= box->nlocal[0]; ic++) {
@@ -363,14 +370,14 @@ int orc_cahn_hilliard(const orc_box_t * box, const orc_param_t * prm, const orc_
  *                       divergence of the face-interpolated stress, whatever the method
  *   hydro_u_halo, hydro_lees_edwards  src/hydro.c:190, 412-500 (time t + 1, linear
  *                       interpolation, velocity jump added) ........ le_u_buffers
- *   advection_le_{1st,2nd,3rd}  src/advection.c:542-1180 ........... le_advection
+ *   advection_le_{1st,2nd,3rd,4th}  src/advection.c:542-1290 ....... le_advection
  *   phi_ch_flux_mu1, phi_ch_flux_mu_ext  src/phi_cahn_hilliard.c:349, 1404
  *   phi_ch_le_fix_fluxes  src/phi_cahn_hilliard.c:618-735: the east flux of the sites
  *                       below a plane and the west flux of those above it are
  *                       averaged with their (interpolated) counterparts
  *   phi_ch_ufs_kernel   src/phi_cahn_hilliard.c:1025 (wz = 0 when n_z = 1)
  *
- * One rank; steady or oscillatory planes; advection orders 1-3.
+ * One rank; steady or oscillatory planes; advection orders 1-4.
  * Parity status: PINNED, tests/test_oracle_vs_ref.py::test_cahn_hilliard_lees_edwards.
  * =========================================================================== */
 
@@ -755,7 +762,7 @@ int orc_ch_le_step(const orc_box_t * box, const orc_param_t * prm, const orc_ch_
   int rc = 0;
 
   if (le->nplanes <= 0 || box->nlocal[0] % le->nplanes) return -1;
-  if (ch->order < 1 || ch->order > 3) return -1;
+  if (ch->order < 1 || ch->order > 4) return -1;
   if (npt != 7 && npt != 27) return -1;
   lebox_init(&E, box, le);
   pe = (double *) calloc(8*E.nall + 4*E.nreal, sizeof(double));

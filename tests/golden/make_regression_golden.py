@@ -32,11 +32,11 @@ CASES = ["d3q19-short/serial-dist-3du", "d3q19-short/serial-dist-1dp",
          # binary fluid across two Lees-Edwards planes (a sheared 64 x 64 x 1 system)
          "d3q19-short/serial-le2d-lb1",
          # the finite-difference order parameter sheared by two planes: 7- and 27-point
-         # gradients, advection orders 1-3 (st4 / st8 use the fourth-order scheme, a host
-         # loop in the reference that is not restated), and the two-dimensional case
+         # gradients, advection orders 1-4, and the two-dimensional case
          "d3q19-short/serial-le3d-st1", "d3q19-short/serial-le3d-st2",
-         "d3q19-short/serial-le3d-st3", "d3q19-short/serial-le3d-st5",
-         "d3q19-short/serial-le3d-st6", "d3q19-short/serial-le3d-st7",
+         "d3q19-short/serial-le3d-st3", "d3q19-short/serial-le3d-st4",
+         "d3q19-short/serial-le3d-st5", "d3q19-short/serial-le3d-st6",
+         "d3q19-short/serial-le3d-st7", "d3q19-short/serial-le3d-st8",
          "d3q19-short/serial-le2d-fd1"]
 NVEL = {"d3q19-short": 19, "d3q19": 19, "d2q9": 9}
 

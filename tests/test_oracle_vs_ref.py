@@ -571,6 +571,7 @@ FD_CASES = [
     (1, pyoracle.FORCE_PHI_GRADMU, 27, (1e-5, 2e-5, 3e-5)),
     (3, pyoracle.FORCE_PHI_GRADMU, 7, (-2e-5, 0.0, 1e-5)),
     (2, pyoracle.FORCE_NONE, 7, (0.0, 0.0, 0.0)),
+    (4, pyoracle.FORCE_STRESS_DIVERGENCE, 7, (0.0, 0.0, 0.0)),
 ]
 
 
@@ -632,6 +633,7 @@ FD_LE_CASES = [
     ((12, 7, 5), dict(nplanes=1, uy=-0.03), 3, pyoracle.FORCE_STRESS_DIVERGENCE, 27, (0.0, 0.0, 0.0)),
     ((15, 9, 6), dict(nplanes=3, uy=0.31), 3, pyoracle.FORCE_PHI_GRADMU, 7, (1e-5, 2e-5, 3e-5)),
     ((16, 12, 1), dict(nplanes=2, uy=0.02), 1, pyoracle.FORCE_STRESS_DIVERGENCE, 27, (0.0, 0.0, 0.0)),
+    ((12, 8, 6), dict(nplanes=2, uy=0.07), 4, pyoracle.FORCE_STRESS_DIVERGENCE, 7, (0.0, 0.0, 0.0)),
     ((16, 8, 6), dict(nplanes=2, uy=0.04, oscillatory=1, period=40, nt0=0), 2,
      pyoracle.FORCE_STRESS_DIVERGENCE, 7, (0.0, 0.0, 0.0)),
 ]
