@@ -220,8 +220,9 @@ int  b200lb_le_field_time_set(b200lb_t * h, double t);                 /* physic
  * b200lb_set_param. With option "ch_exact" results are bit-identical to the reference's;
  * the default build uses fused multiply-add (a few ulp away, 1.6x faster).
  * On this path: three dimensions, fully periodic, fluid only, no Lees-Edwards planes;
- * advection orders 1-3 (3 only where every direction is periodic within the rank: it
- * reads phi two sites away); force methods no_force, stress_divergence, phi_gradmu.
+ * advection orders 1-4 (3 and 4 only where every direction is periodic within the rank:
+ * they read phi two sites away; 4 is a host loop behind two copies of the flux arrays in
+ * the reference, src/advection.c:465-470); force methods no_force, stress_divergence, phi_gradmu.
  * Fields: B200LB_FIELD_PHI / _GRAD / _DELSQ move the order parameter and its gradient,
  * index over the usual one-site halo box (the interior is what the reference's
  * nhalo = 2 arrays hold inside their halo). */

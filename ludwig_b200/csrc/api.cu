@@ -1660,7 +1660,7 @@ extern "C" int b200lb_ch_create(b200lb_t * h, int order, int method) {
     if (!h->desc.periodic[a]) return fail("phi_ch_create: walls need the solid gradient stencils and the no-flux masks of src/advection_bcs.c: not on this path");
   }
   if (h->le_nplanes) return fail("phi_ch_create: Lees-Edwards planes for the order parameter (src/phi_cahn_hilliard.c:618) are not on this path");
-  if (order < 1 || order > 3) return fail("fd_advection_scheme_order %d: orders 1 to 3 are on this path (4 and 5 are host loops in the reference, src/advection.c:465-477)", order);
+  if (order < 1 || order > 4) return fail("fd_advection_scheme_order %d: orders 1 to 4 are on this path (5 is a host loop in the reference, src/advection.c:471-476)", order);
   if (method != CH_FORCE_NONE && method != CH_FORCE_STRESS_DIVERGENCE && method != CH_FORCE_PHI_GRADMU) {
     return fail("fe_force_method %d: no_force (1), stress_divergence (2) and phi_gradmu (3) are on this path", method);
   }
@@ -1697,8 +1697,9 @@ static int ch_run(b200lb_s * h, bool do_force, bool do_update) {
   bool any_dec = false;
   for (int d = 0; d < 3; d++) {
     if (decomposed(h, d)) any_dec = true;
-    if (do_update && h->ch_order == 3 && !h->selfper[d]) {
-      return fail("third-order advection reads phi two sites away (nhalo = 2): on this path only around directions that are periodic within the rank");
+    if (do_update && h->ch_order >= 3 && !h->selfper[d]) {
+      return fail("%s advection reads phi two sites away (nhalo = 2): on this path only around directions that are periodic within the rank",
+		  (h->ch_order == 3) ? "third-order" : "fourth-order");
     }
   }
   if (any_dec && !h->ch_halo_done) {

@@ -77,7 +77,7 @@ __device__ __forceinline__ double ch_pab(const Symm & s, double p0, const double
 
 // The flux through the face between site A and the next site B along an axis:
 // advection_x (src/advection.c: first order upwind :542, centred :790, the three-point
-// upwind-biased stencil :977), then - M (mu_B - mu_A) (phi_ch_flux_mu1_kernel,
+// upwind-biased stencil :977, four-point centred :1188), then - M (mu_B - mu_A) (phi_ch_flux_mu1_kernel,
 // src/phi_cahn_hilliard.c:349) and - M grad mu^ext (:1404). Am and Bp are the sites
 // beyond A and B. The reference computes this twice per face -- as the "east"/y/z flux
 // of A and as the "west" flux of B, or as the y/z flux fy[index - ys] read back -- with
@@ -93,6 +93,14 @@ __device__ __forceinline__ double ch_face(double uA, double uB, double phAm, dou
   }
   else if (ORDER == 2) {
     adv = __dmul_rn(__dmul_rn(__dmul_rn(0.5, __dadd_rn(uA, uB)), 0.5), __dadd_rn(phA, phB));
+  }
+  else if (ORDER == 4) {
+    // advection_le_4th, src/advection.c:1188-1290 (a host loop in the reference, behind a
+    // copy of the fluxes to the host and back): four-point centred interpolation,
+    // u (- phi_Am/16 + 9 phi_A/16 + 9 phi_B/16 - phi_Bp/16), summed in that order
+    const double b1 = (1.0/16.0), b2 = (9.0/16.0);
+    const double u = __dmul_rn(0.5, __dadd_rn(uA, uB));
+    adv = __dmul_rn(u, ch_mad(-b1, phBp, ch_mad(b2, phB, ch_mad(b2, phA, __dmul_rn(-b1, phAm)))));
   }
   else {
     const double a1 = -0.213933, a2 = 0.927865, a3 = 0.286067;
@@ -113,7 +121,7 @@ __device__ __forceinline__ int ch_off(int c, int n, int wrap, int o) {
 }
 
 // METHOD: 0 = no force pass, CH_FORCE_STRESS_DIVERGENCE, CH_FORCE_PHI_GRADMU
-// ORDER:  0 = no update pass, 1..3 = advection scheme of the Cahn-Hilliard update
+// ORDER:  0 = no update pass, 1..4 = advection scheme of the Cahn-Hilliard update
 template <int EXACT, int METHOD, int ORDER>
 __global__ void __launch_bounds__(CH_TZ*CH_TY, EXACT ? 2 : 3)
 ch_kernel(const ChParams P) {
@@ -247,8 +255,8 @@ ch_kernel(const ChParams P) {
 	const double u0 = __ldg(u + a*nsd + site);
 	const double um = __ldg(u + a*nsd + site + d[a][1]);
 	const double up = __ldg(u + a*nsd + site + d[a][2]);
-	const double phm2 = (ORDER == 3) ? __ldg(phi + site + d[a][0]) : 0.0;
-	const double php2 = (ORDER == 3) ? __ldg(phi + site + d[a][3]) : 0.0;
+	const double phm2 = (ORDER >= 3) ? __ldg(phi + site + d[a][0]) : 0.0;
+	const double php2 = (ORDER >= 3) ? __ldg(phi + site + d[a][3]) : 0.0;
 	const double Mg = __dmul_rn(M, P.gmu[a]);
 	flo[a] = ch_face<ORDER>(um, u0, phm2, phm[a], ph0, php[a], ch_mu(S, phm[a], dqm[a]), mu0, M, Mg);
 	fhi[a] = ch_face<ORDER>(u0, up, phm[a], ph0, php[a], php2, mu0, ch_mu(S, php[a], dqp[a]), M, Mg);
@@ -285,6 +293,7 @@ static cudaError_t launch_order(const ChParams & P, int order, cudaStream_t st) 
   case 1: return launch<METHOD, 1>(P, st);
   case 2: return launch<METHOD, 2>(P, st);
   case 3: return launch<METHOD, 3>(P, st);
+  case 4: return launch<METHOD, 4>(P, st);
   }
   return cudaErrorInvalidValue;
 }
@@ -299,7 +308,7 @@ cudaError_t CH_LAUNCH(const ChParams & P, bool do_force, bool do_update, cudaStr
   const int order = do_update ? P.order : 0;
   int method = do_force ? P.method : 0;
   if (method == CH_FORCE_NONE) method = 0;
-  if (do_update && (order < 1 || order > 3)) return cudaErrorInvalidValue;
+  if (do_update && (order < 1 || order > 4)) return cudaErrorInvalidValue;
   switch (method) {
   case 0: return launch_order<0>(P, order, st);
   case CH_FORCE_STRESS_DIVERGENCE: return launch_order<CH_FORCE_STRESS_DIVERGENCE>(P, order, st);

@@ -207,8 +207,8 @@ def test_refusals():
     lat = lb.Lattice(19, (8, 8, 8))
     with pytest.raises(lb.B200LBError, match="b200lb_ch_create"):
         lat.phi_force_calculation()
-    with pytest.raises(lb.B200LBError, match="orders 1 to 3"):
-        lat.phi_ch_create(4)
+    with pytest.raises(lb.B200LBError, match="orders 1 to 4"):
+        lat.phi_ch_create(5)
     lat.phi_ch_create(1)
     with pytest.raises(lb.B200LBError, match="field_grad_compute"):
         lat.phi_force_calculation()

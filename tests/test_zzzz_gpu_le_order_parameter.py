@@ -7,7 +7,8 @@ the sheared binary time loop within 1e-12.
 
 Written after the round's GPU allocation was spent; the kernels were checked by stepping
 through their source on the host (tools/check_le_field_on_host.py). Until these tests
-have been seen to pass on a B200 once they are opt-in: B200LB_UNVERIFIED=1."""
+have been seen to pass on a B200 once they are opt-in: B200LB_UNVERIFIED=1. The same goes
+for the fourth-order advection scheme of the finite-difference order parameter at the end."""
 
 import os
 
@@ -119,4 +120,56 @@ def test_sheared_binary_time_loop_vs_oracle(nlocal, le, npt, fused):
         lat.lb_halo()
         lat.lb_propagation()
     assert np.array_equal(lat.lb_memcpy_d2h()[m], fd[m])
+    lat.close()
+
+
+# ---------------------------------------------------------------------------
+# fourth-order advection of the finite-difference order parameter (ch_face<4>,
+# ludwig_b200/csrc/ch_kernels.cu): also written after the GPU allocation was spent,
+# checked on the host against the oracle (tools/check_ch_kernel_on_host.py)
+# ---------------------------------------------------------------------------
+
+@pytest.mark.parametrize("nlocal,npt", [((10, 8, 6), 7), ((6, 7, 9), 27)])
+@pytest.mark.parametrize("exact", [1, 0])
+def test_fourth_order_advection_vs_oracle(nlocal, npt, exact):
+    import ludwig_b200 as lb
+    import goldenlib
+    from oracle import pyoracle
+    P = goldenlib.CH_PHYS
+    gmu = (1e-5, -2e-5, 3e-5)
+    orc = pyoracle.Oracle(19, nlocal)
+    n = orc.nsite
+    m = orc.interior_mask()
+    prm = pyoracle.make_param(eta_shear=P["eta"], eta_bulk=P["eta"], mobility=P["mobility"],
+                              a=P["a"], b=P["b"], kappa=P["kappa"])
+    ch = orc.ch(4, pyoracle.FORCE_STRESS_DIVERGENCE, gmu)
+    phi, u = goldenlib.ch_fields(nlocal)
+    lat = lb.Lattice(19, nlocal)
+    lat.set_option("ch_exact", exact)
+    lat.set_param(eta_shear=P["eta"], eta_bulk=P["eta"], mobility=P["mobility"],
+                  a=P["a"], b=P["b"], kappa=P["kappa"])
+    lat.phi_ch_create(4, lb.FORCE_STRESS_DIVERGENCE, gmu)
+    lat.field_grad_set(npt)
+    lat.field_h2d(lb.FIELD_PHI, phi)
+    lat.field_h2d(lb.FIELD_U, u)
+    lat.hydro_f_zero()
+    lat.field_halo()
+    lat.field_grad_compute()
+    lat.phi_force_calculation()
+    lat.phi_cahn_hilliard()
+    force = lat.field_d2h(lb.FIELD_FORCE)
+    phi1 = lat.field_d2h(lb.FIELD_PHI)
+    po, uo = phi.copy(), u.copy()
+    orc.halo(po, 1)
+    grad, delsq, fo = np.zeros((n, 3)), np.zeros(n), np.zeros((n, 3))
+    (orc.grad_27pt if npt == 27 else orc.grad_7pt)(po, grad, delsq)
+    orc.phi_force(prm, ch, po, grad, delsq, fo)
+    orc.cahn_hilliard(prm, ch, po, delsq, uo)
+    if exact:
+        assert np.array_equal(force[m], fo[m])
+        assert np.array_equal(phi1[m], po[m])
+    else:
+        assert np.max(np.abs(force[m] - fo[m])) <= 1e-15*np.max(np.abs(fo[m]))
+        assert np.max(np.abs(phi1[m] - po[m])) <= 1e-15*np.max(np.abs(po[m]))
+    assert abs(phi1[m].sum() - phi[m].sum()) < 1e-13*m.sum()
     lat.close()

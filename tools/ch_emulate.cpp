@@ -77,6 +77,7 @@ static int run_order(const ChParams & P, int order) {
   case 1: run<METHOD, 1>(P); return 0;
   case 2: run<METHOD, 2>(P); return 0;
   case 3: run<METHOD, 3>(P); return 0;
+  case 4: run<METHOD, 4>(P); return 0;
   }
   return -1;
 }
