@@ -125,6 +125,11 @@ long b200lb_nsite(const b200lb_t * h);                          /* host nsite = 
  *                      collision that streams in the same pass reads that instead of
  *                      pulling g a second time (same bits, 104 B/site less traffic;
  *                      default 1)
+ *   "le_fd"       0/1  allow Lees-Edwards planes together with the finite-difference order
+ *                      parameter (buffer-region gradient, flux form of the force with its
+ *                      plane correction, phi_ch_le_fix_fluxes: ch_le_pass_a/_b). Default 0
+ *                      until that path has run on a GPU: b200lb_le_commit /
+ *                      b200lb_ch_create refuse the combination otherwise
  *   "loopback"    0/1  single rank: send periodic directions through the exchange
  *                      buffers with this GPU as its own neighbour (tests, profiling) */
 int  b200lb_set_option(b200lb_t * h, const char * name, long value);
@@ -219,7 +224,8 @@ int  b200lb_le_field_time_set(b200lb_t * h, double t);                 /* physic
  * launches). Free-energy parameters A, B, kappa and the mobility are those of
  * b200lb_set_param. With option "ch_exact" results are bit-identical to the reference's;
  * the default build uses fused multiply-add (a few ulp away, 1.6x faster).
- * On this path: three dimensions, fully periodic, fluid only, no Lees-Edwards planes;
+ * On this path: three dimensions, fully periodic, fluid only, Lees-Edwards planes behind
+ * option "le_fd";
  * advection orders 1-4 (3 and 4 only where every direction is periodic within the rank:
  * they read phi two sites away; 4 is a host loop behind two copies of the flux arrays in
  * the reference, src/advection.c:465-470); force methods no_force, stress_divergence, phi_gradmu.

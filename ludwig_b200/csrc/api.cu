@@ -124,6 +124,8 @@ struct b200lb_s {
   long le_tstart;            // ... and the step this run started from (physics_control_init_time)
   double le_field_t;         // physics_control_time at which the order parameter is displaced
   double * le_phibuf;        // [2 x local planes][s0] buffer planes of phi (field_leesedwards)
+  double * le_chbuf;         // finite-difference order parameter with planes: buffers and scratch (ch_le_run)
+  int last_grad_npt;         // stencil of the last field_grad_compute (7 or 27)
   double * le_buf;           // crossing populations of the plane sites
   // the order parameter as a finite-difference field ("free_energy symmetric":
   // phi_ch_t src/phi_cahn_hilliard.h:33, pth_t src/phi_force_stress.h)
@@ -168,7 +170,7 @@ struct b200lb_s {
   bool ghost;
 
   // options
-  int opt_fused, opt_halo, opt_hydro_write, opt_vec, opt_block, opt_halo_lazy, opt_overlap, opt_direct, opt_diag, opt_loopback, opt_grad_lazy, opt_p2p, opt_gradient, opt_ch_fuse, opt_ch_planes, opt_ch_exact, opt_g_moment;
+  int opt_fused, opt_halo, opt_hydro_write, opt_vec, opt_block, opt_halo_lazy, opt_overlap, opt_direct, opt_diag, opt_loopback, opt_grad_lazy, opt_p2p, opt_gradient, opt_ch_fuse, opt_ch_planes, opt_ch_exact, opt_g_moment, opt_le_fd;
 
   cudaStream_t s_main, s_x[2];
   cudaStream_t s_comm;       // halo exchange of decomposed directions (overlaps the interior sweep)
@@ -490,6 +492,7 @@ static int create_impl(const b200lb_desc_t * desc, b200lb_s * h, const ModelOps 
   h->opt_ch_planes = 8;
   h->opt_ch_exact = 0;
   h->opt_g_moment = 1;
+  h->opt_le_fd = 0;
 
   b200lb_param_t p0;
   memset(&p0, 0, sizeof(p0));
@@ -519,7 +522,7 @@ extern "C" int b200lb_destroy(b200lb_t * h) {
     cudaEventDestroy(h->ev_x[i]);
   }
   cudaFree(h->rho); cudaFree(h->u); cudaFree(h->force);
-  cudaFree(h->phi2); cudaFree(h->eta); cudaFree(h->jphi); cudaFree(h->le_phibuf);
+  cudaFree(h->phi2); cudaFree(h->eta); cudaFree(h->jphi); cudaFree(h->le_phibuf); cudaFree(h->le_chbuf);
   cudaFree(h->phi); cudaFree(h->grad); cudaFree(h->delsq); cudaFree(h->noise); cudaFree(h->fnet_dev); cudaFree(h->le_buf);
   cudaFree(h->partial); cudaFree(h->diag); cudaFree(h->stats_dev); cudaFreeHost(h->stats_host);
   cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
@@ -566,6 +569,7 @@ extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
     return 0;
   }
   if (!strcmp(name, "g_moment")) { h->opt_g_moment = (v != 0); h->jphi_valid = false; return 0; }
+  if (!strcmp(name, "le_fd")) { h->opt_le_fd = (v != 0); return 0; }
   if (!strcmp(name, "ch_planes")) {
     if (v < 1 || v > 4096) return fail("ch_planes: x-planes marched by one block of the order-parameter kernel, 1..4096");
     h->opt_ch_planes = (int) v;
@@ -619,6 +623,7 @@ extern "C" long b200lb_get_option(const b200lb_t * h, const char * name) {
   if (!strcmp(name, "ch_planes")) return h->opt_ch_planes;
   if (!strcmp(name, "ch_exact")) return h->opt_ch_exact;
   if (!strcmp(name, "g_moment")) return h->opt_g_moment;
+  if (!strcmp(name, "le_fd")) return h->opt_le_fd;
   if (!strcmp(name, "jphi_valid")) return h->jphi_valid;
   if (!strcmp(name, "p2p")) return h->opt_p2p;
   if (!strcmp(name, "p2p_ready")) return h->p2p_ready;
@@ -1043,10 +1048,11 @@ extern "C" int b200lb_le_commit(b200lb_t * h, int nplanes, double uy, int oscill
 				int period, int nt0) {
   if (!h) return fail("null handle");
   if (nplanes < 0) return fail("N_LE_plane must not be negative");
-  if (nplanes > 0 && h->ch_on) return fail("Lees-Edwards planes for the finite-difference order parameter (src/phi_cahn_hilliard.c:618) are not on this path");
+  if (nplanes > 0 && h->ch_on && !h->opt_le_fd) return fail("Lees-Edwards planes for the finite-difference order parameter (src/phi_cahn_hilliard.c:618): behind option le_fd until the device path has run on a GPU");
   if (h->prop_pending) { if (materialise(h)) return -1; }
   h->le_nplanes = 0; h->le_nlocal = 0; h->le_step = 0; h->le_tstart = 0; h->le_field_t = 0.0;
   if (h->le_phibuf) { CU(cudaFree(h->le_phibuf)); h->le_phibuf = nullptr; }
+  if (h->le_chbuf) { CU(cudaFree(h->le_chbuf)); h->le_chbuf = nullptr; }
   if (nplanes == 0) return 0;
   const int ntotal = h->desc.cartsz[0]*h->desc.nlocal[0];
   if (ntotal % nplanes) return fail("Number of planes must divide system size");
@@ -1499,6 +1505,7 @@ static int run_grad7(b200lb_s * h) {
   CU(cudaGetLastError());
   h->launches++;
   if (le_grad_fix(h, 7)) return -1;
+  h->last_grad_npt = 7;
   h->grad_state = 0;
   h->ch_grad_valid = true; h->ch_halo_done = false;
   return 0;
@@ -1516,6 +1523,7 @@ static int run_grad27(b200lb_s * h) {
   CU(cudaGetLastError());
   h->launches++;
   if (le_grad_fix(h, 27)) return -1;
+  h->last_grad_npt = 27;
   h->grad_state = 0;
   h->ch_grad_valid = true; h->ch_halo_done = false;
   return 0;
@@ -1659,7 +1667,7 @@ extern "C" int b200lb_ch_create(b200lb_t * h, int order, int method) {
   for (int a = 0; a < 3; a++) {
     if (!h->desc.periodic[a]) return fail("phi_ch_create: walls need the solid gradient stencils and the no-flux masks of src/advection_bcs.c: not on this path");
   }
-  if (h->le_nplanes) return fail("phi_ch_create: Lees-Edwards planes for the order parameter (src/phi_cahn_hilliard.c:618) are not on this path");
+  if (h->le_nplanes && !h->opt_le_fd) return fail("phi_ch_create: Lees-Edwards planes for the order parameter (src/phi_cahn_hilliard.c:618): behind option le_fd until the device path has run on a GPU");
   if (order < 1 || order > 4) return fail("fd_advection_scheme_order %d: orders 1 to 4 are on this path (5 is a host loop in the reference, src/advection.c:471-476)", order);
   if (method != CH_FORCE_NONE && method != CH_FORCE_STRESS_DIVERGENCE && method != CH_FORCE_PHI_GRADMU) {
     return fail("fe_force_method %d: no_force (1), stress_divergence (2) and phi_gradmu (3) are on this path", method);
@@ -1687,6 +1695,77 @@ extern "C" int b200lb_ch_grad_mu_set(b200lb_t * h, const double gm[3]) {
 
 // One pass over the lattice: the force on the fluid (do_force), the update of phi
 // (do_update), or both.
+// The layers of sites around every Lees-Edwards plane again, after ch_kernel has run over
+// the lattice (ch_kernels.cuh): buffer planes of phi (4 per plane, time t =
+// physics_control_time) and u_x (time t + 1), the gradient in the first buffer plane of
+// either side, then the two passes and the plane reduction.
+static int ch_le_run(b200lb_s * h, const ChParams & P, bool do_force, bool do_update) {
+  const Layout & L = h->L;
+  const int np = h->le_nlocal;
+  if (np > CH_LE_MAXPLANE) return fail("finite-difference order parameter: more than %d Lees-Edwards planes per rank", CH_LE_MAXPLANE);
+  if (h->desc.nlocal[0]/np < 4) return fail("finite-difference order parameter: Lees-Edwards planes closer than 4 sites");
+  int loc[B200LB_LE_MAXPLANE];
+  for (int p = 0; p < np; p++) {
+    loc[p] = le_location(h, p);
+    if (loc[p] - 1 < 1 || loc[p] + 2 > L.n[0]) return fail("finite-difference order parameter: a Lees-Edwards plane within two sites of the rank boundary");
+  }
+  const size_t per = (size_t) 22*np*L.s0;
+  if (!h->le_chbuf) {
+    CU(cudaMalloc(&h->le_chbuf, (per + 3*np)*sizeof(double)));
+    CU(cudaMemsetAsync(h->le_chbuf, 0, (per + 3*np)*sizeof(double), h->s_main));
+  }
+  double * bphi = h->le_chbuf;
+  double * bgrad = bphi + (size_t) 4*np*L.s0;
+  double * bdelsq = bgrad + (size_t) 6*np*L.s0;
+  double * bux = bdelsq + (size_t) 2*np*L.s0;
+  double * scr = bux + (size_t) 2*np*L.s0;
+  double * fbar = scr + (size_t) 8*np*L.s0;
+  const double t = h->le_field_t;
+
+  LePhiTab T;
+  memset(&T, 0, sizeof(T));
+  T.L = L;
+  T.w0 = h->selfper[0]; T.w1 = h->selfper[1]; T.w2 = h->selfper[2];
+  dim3 block(128, 1, 1);
+  le_phi_tab_fill4(T, np, loc, h->le_uy, h->le_osc, h->le_period, h->le_nt0, t);
+  le_phi_buffer_kernel<<<dim3((L.n[2] + 2 + 127)/128, L.n[1] + 2, T.nbuf), block, 0, h->s_main>>>(T, h->phi, bphi);
+  CU(cudaGetLastError());
+  LeBufGradTab G;
+  memset(&G, 0, sizeof(G));
+  G.L = L; G.w1 = h->selfper[1]; G.w2 = h->selfper[2]; G.nplanes = np;
+  for (int p = 0; p < np; p++) G.loc[p] = loc[p];
+  dim3 gplane((L.n[2] + 127)/128, L.n[1], 2*np);
+  if (h->last_grad_npt == 27) le_buffer_grad_kernel<27><<<gplane, block, 0, h->s_main>>>(G, h->phi, bphi, bgrad, bdelsq);
+  else le_buffer_grad_kernel<7><<<gplane, block, 0, h->s_main>>>(G, h->phi, bphi, bgrad, bdelsq);
+  CU(cudaGetLastError());
+  h->launches += 2;
+  if (do_update) {
+    le_u_tab_fill(T, np, loc, h->le_uy, h->le_osc, h->le_period, h->le_nt0, t);
+    le_u_buffer_kernel<<<gplane, block, 0, h->s_main>>>(T, h->u, bux);
+    CU(cudaGetLastError());
+    h->launches++;
+  }
+  ChLeParams Q;
+  memset(&Q, 0, sizeof(Q));
+  Q.nplanes = np;
+  for (int p = 0; p < np; p++) Q.loc[p] = loc[p];
+  Q.bphi = bphi; Q.bgrad = bgrad; Q.bdelsq = bdelsq; Q.bux = bux; Q.scr = scr; Q.fbar = fbar;
+  {
+    // lees_edw_plane_dy = t u_y (src/leesedwards.c:923-935), looking up and down
+    const int ny = L.n[1];
+    double dy = fmod(+(t*h->le_uy), 1.0*ny);
+    Q.jdy_up = (int) floor(dy); Q.fr_up = dy - Q.jdy_up;
+    dy = fmod(-(t*h->le_uy), 1.0*ny);
+    Q.jdy_dn = (int) floor(dy); Q.fr_dn = dy - Q.jdy_dn;
+    Q.ra = 0.5/(1.0*h->desc.nlocal[1]*h->desc.cartsz[1]*h->desc.nlocal[2]*h->desc.cartsz[2]);
+  }
+  if (decomposed(h, 2) && do_force) return fail("finite-difference order parameter with Lees-Edwards planes: the plane average of the force correction across ranks in z is not on this path");
+  CU(h->opt_ch_exact ? ch_le_launch_exact(P, Q, do_force, do_update, h->s_main)
+     : ch_le_launch_fast(P, Q, do_force, do_update, h->s_main));
+  h->launches += do_force ? 3 : 2;
+  return 0;
+}
+
 static int ch_run(b200lb_s * h, bool do_force, bool do_update) {
   if (!h->ch_on) return fail("no finite-difference order parameter: call b200lb_ch_create first");
   if (do_force && h->ch_method == CH_FORCE_NONE) do_force = false;
@@ -1733,9 +1812,16 @@ static int ch_run(b200lb_s * h, bool do_force, bool do_update) {
   P.order = h->ch_order;
   P.method = h->ch_method;
   P.nx = h->opt_ch_planes;
+  if (h->le_nlocal) {
+    // with planes the force is the divergence of the face-interpolated stress whatever
+    // the method (src/phi_force.c:89-96)
+    if (do_force && P.accumulate) return fail("phi_force_calculation with Lees-Edwards planes: onto a force field that is uniform (hydro_f_zero) only");
+    if (P.method != CH_FORCE_NONE) P.method = CH_FORCE_STRESS_DIVERGENCE;
+  }
   CU(h->opt_ch_exact ? ch_launch_exact(P, do_force, do_update, h->s_main)
      : ch_launch_fast(P, do_force, do_update, h->s_main));
   h->launches++;
+  if (h->le_nlocal) { if (ch_le_run(h, P, do_force, do_update)) return -1; }
   if (do_force) h->force_uniform = false;
   if (do_update) {
     double * t = h->phi; h->phi = h->phi2; h->phi2 = t;

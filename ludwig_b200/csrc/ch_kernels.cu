@@ -272,6 +272,265 @@ ch_kernel(const ChParams P) {
   }
 }
 
+// ---------------------------------------------------------------------------
+// Lees-Edwards planes (see ch_kernels.cuh). What a site of layer l = -1 .. 2 around plane
+// p (x = loc + l) sees at x = loc + r: a real plane, or -- looking across the plane --
+// buffer b = r + 1 (lees_edw_ic_to_buff, src/leesedwards.c:1014-1047 with nhalo = 2).
+// ---------------------------------------------------------------------------
+
+struct LeView {
+  const double * phi[5];      // x-planes of phi at r = l - 2 .. l + 2
+  const double * dsq[3];      // delsq at r = l - 1 .. l + 1
+  const double * g[3][3];     // [r][component] gradient planes, r = l - 1 .. l + 1
+  const double * ux[3];       // u_x planes
+};
+
+__device__ __forceinline__ int le_wrapx(const ChParams & P, int x) {
+  if (P.wrap[0]) { if (x < 1) x += P.L.n[0]; else if (x > P.L.n[0]) x -= P.L.n[0]; }
+  return x;
+}
+
+__device__ __forceinline__ void le_view(const ChParams & P, const ChLeParams & Q, int p, int l, LeView & V) {
+  const Layout & L = P.L;
+  const i64 s0 = L.s0;
+  #pragma unroll
+  for (int o = -2; o <= 2; o++) {
+    const int r = l + o;
+    const bool across = (l <= 0) ? (r >= 1) : (r <= 0);
+    if (across) V.phi[o + 2] = Q.bphi + ((i64) 4*p + (r + 1))*s0;
+    else V.phi[o + 2] = P.phi + (i64) le_wrapx(P, Q.loc[p] + r)*s0;
+    if (o >= -1 && o <= 1) {
+      if (across) {
+	const int e = 2*p + (r + 1) - 1;            // buffers b = 1, 2 only are ever asked for
+	V.dsq[o + 1] = Q.bdelsq + (i64) e*s0;
+	V.ux[o + 1] = Q.bux + (i64) e*s0;
+	#pragma unroll
+	for (int a = 0; a < 3; a++) V.g[o + 1][a] = Q.bgrad + ((i64) e*3 + a)*s0;
+      }
+      else {
+	const i64 x = le_wrapx(P, Q.loc[p] + r);
+	V.dsq[o + 1] = P.delsq + x*s0;
+	V.ux[o + 1] = P.u + x*s0;
+	#pragma unroll
+	for (int a = 0; a < 3; a++) V.g[o + 1][a] = P.grad + a*L.nsd + x*s0;
+      }
+    }
+  }
+}
+
+// P_ab e_x . at one site of a plane triple: the x column of the stress (ia = 0 .. 2)
+__device__ __forceinline__ void le_stress_col(const Symm & S, const double * phi, const double * dsq,
+					       const double * const g[3], i64 col, int ib, double (&out)[3]) {
+  double gg[3];
+  #pragma unroll
+  for (int a = 0; a < 3; a++) gg[a] = __ldg(g[a] + col);
+  const double p0 = ch_p0(S, __ldg(phi + col), __ldg(dsq + col), gg);
+  #pragma unroll
+  for (int a = 0; a < 3; a++) out[a] = ch_pab(S, p0, gg, a, ib);
+}
+
+// pass A: grid (z tiles, n_y, nplanes), block (128)
+template <int EXACT, int ORDER>
+__global__ void __launch_bounds__(128)
+ch_le_pass_a(const ChParams P, const ChLeParams Q, const int do_force) {
+  const Layout & L = P.L;
+  const int p = blockIdx.z;
+  const int c1 = blockIdx.y + 1;
+  const int c2 = blockIdx.x*blockDim.x + threadIdx.x + 1;
+  if (c2 > L.n[2]) return;
+  const i64 col = (i64) c1*L.s1 + L.z0 + c2;
+  const Symm S = {P.A, P.B, P.kappa};
+  double * scr = Q.scr + (i64) 8*p*L.s0;
+  const double M = P.mobility;
+  const double Mg = __dmul_rn(M, P.gmu[0]);
+
+  {
+    // the layer below the plane: its east face, looking up into buffers b = 2, 3
+    LeView V;
+    le_view(P, Q, p, 0, V);
+    if (do_force) {
+      double p0[3], p1[3];
+      le_stress_col(S, V.phi[2], V.dsq[1], V.g[1], col, 0, p0);
+      le_stress_col(S, V.phi[3], V.dsq[2], V.g[2], col, 0, p1);
+      #pragma unroll
+      for (int a = 0; a < 3; a++) scr[(2 + a)*L.s0 + col] = 0.5*(p1[a] + p0[a]);
+    }
+    if (ORDER > 0) {
+      const double phA = __ldg(V.phi[2] + col), phB = __ldg(V.phi[3] + col);
+      scr[col] = ch_face<(ORDER > 0 ? ORDER : 1)>(__ldg(V.ux[1] + col), __ldg(V.ux[2] + col),
+	  __ldg(V.phi[1] + col), phA, phB, __ldg(V.phi[4] + col),
+	  ch_mu(S, phA, __ldg(V.dsq[1] + col)), ch_mu(S, phB, __ldg(V.dsq[2] + col)), M, Mg);
+    }
+  }
+  {
+    // the layer above: its west face, looking down into buffers b = 1, 0
+    LeView V;
+    le_view(P, Q, p, 1, V);
+    if (do_force) {
+      double p0[3], p1[3];
+      le_stress_col(S, V.phi[2], V.dsq[1], V.g[1], col, 0, p0);
+      le_stress_col(S, V.phi[1], V.dsq[0], V.g[0], col, 0, p1);
+      #pragma unroll
+      for (int a = 0; a < 3; a++) scr[(5 + a)*L.s0 + col] = 0.5*(p1[a] + p0[a]);
+    }
+    if (ORDER > 0) {
+      const double phA = __ldg(V.phi[1] + col), phB = __ldg(V.phi[2] + col);
+      scr[L.s0 + col] = ch_face<(ORDER > 0 ? ORDER : 1)>(__ldg(V.ux[0] + col), __ldg(V.ux[1] + col),
+	  __ldg(V.phi[0] + col), phA, phB, __ldg(V.phi[3] + col),
+	  ch_mu(S, phA, __ldg(V.dsq[0] + col)), ch_mu(S, phB, __ldg(V.dsq[1] + col)), M, Mg);
+    }
+  }
+}
+
+// plane sums of -fluxe(loc) + fluxw(loc + 1): one block of 256 threads per (plane,
+// component), strided partial sums in a fixed order, then a tree (deterministic)
+__global__ void __launch_bounds__(256)
+ch_le_reduce(const ChParams P, const ChLeParams Q) {
+  __shared__ double sm[256];
+  const Layout & L = P.L;
+  const int p = blockIdx.x, a = blockIdx.y;
+  const double * scr = Q.scr + (i64) 8*p*L.s0;
+  const int n = L.n[1]*L.n[2];
+  double acc = 0.0;
+  for (int i = threadIdx.x; i < n; i += 256) {
+    const int jc = 1 + i/L.n[2], kc = 1 + i % L.n[2];
+    const i64 col = (i64) jc*L.s1 + L.z0 + kc;
+    acc += - scr[(2 + a)*L.s0 + col] + scr[(5 + a)*L.s0 + col];
+  }
+  sm[threadIdx.x] = acc;
+  __syncthreads();
+  for (int w = 128; w > 0; w >>= 1) {
+    if ((int) threadIdx.x < w) sm[threadIdx.x] += sm[threadIdx.x + w];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) Q.fbar[3*p + a] = sm[0];
+}
+
+// pass B: grid (z tiles, n_y, nplanes), block (128); layers l = -1 .. 2
+template <int EXACT, int ORDER>
+__global__ void __launch_bounds__(128)
+ch_le_pass_b(const ChParams P, const ChLeParams Q, const int do_force) {
+  const Layout & L = P.L;
+  const int p = blockIdx.z;
+  const int c1 = blockIdx.y + 1;
+  const int c2 = blockIdx.x*blockDim.x + threadIdx.x + 1;
+  if (c2 > L.n[2]) return;
+  const i64 col = (i64) c1*L.s1 + L.z0 + c2;
+  const Symm S = {P.A, P.B, P.kappa};
+  const double * scr = Q.scr + (i64) 8*p*L.s0;
+  const double M = P.mobility;
+  const i64 nsd = L.nsd;
+
+  // offsets within a plane: [axis 1, 2][-2, -1, +1, +2]
+  i64 d[3][4];
+  {
+    const int o[4] = {-2, -1, 1, 2};
+    #pragma unroll
+    for (int k = 0; k < 4; k++) {
+      d[0][k] = 0;
+      d[1][k] = (i64) ch_off(c1, L.n[1], P.wrap[1], o[k])*L.s1;
+      d[2][k] = (i64) ch_off(c2, L.n[2], P.wrap[2], o[k]);
+    }
+  }
+
+  #pragma unroll 1
+  for (int l = -1; l <= 2; l++) {
+    LeView V;
+    le_view(P, Q, p, l, V);
+    const int x = le_wrapx(P, Q.loc[p] + l);
+    const i64 site = (i64) x*L.s0 + col;
+    const double * phc = V.phi[2];
+    const double ph0 = __ldg(phc + col);
+    const double dq0 = __ldg(V.dsq[1] + col);
+
+    if (do_force && (l == 0 || l == 1)) {
+      // phi_force_flux_divergence, src/phi_force.c:431-476, with the corrected plane flux
+      double pc[3], pn[3], f[3];
+      double fe[3], fw[3];
+      le_stress_col(S, phc, V.dsq[1], V.g[1], col, 0, pc);
+      if (l == 0) {
+	#pragma unroll
+	for (int a = 0; a < 3; a++) fe[a] = scr[(2 + a)*L.s0 + col] + Q.ra*Q.fbar[3*p + a];
+	le_stress_col(S, V.phi[1], V.dsq[0], V.g[0], col, 0, pn);
+	#pragma unroll
+	for (int a = 0; a < 3; a++) fw[a] = 0.5*(pn[a] + pc[a]);
+      }
+      else {
+	le_stress_col(S, V.phi[3], V.dsq[2], V.g[2], col, 0, pn);
+	#pragma unroll
+	for (int a = 0; a < 3; a++) fe[a] = 0.5*(pn[a] + pc[a]);
+	#pragma unroll
+	for (int a = 0; a < 3; a++) fw[a] = scr[(5 + a)*L.s0 + col] - Q.ra*Q.fbar[3*p + a];
+      }
+      #pragma unroll
+      for (int a = 0; a < 3; a++) f[a] = fe[a] - fw[a];
+      #pragma unroll
+      for (int b = 1; b < 3; b++) {
+	double q0[3], qp[3], qm[3];
+	le_stress_col(S, phc, V.dsq[1], V.g[1], col, b, q0);
+	le_stress_col(S, phc, V.dsq[1], V.g[1], col + d[b][2], b, qp);
+	le_stress_col(S, phc, V.dsq[1], V.g[1], col + d[b][1], b, qm);
+	#pragma unroll
+	for (int a = 0; a < 3; a++) {
+	  f[a] = f[a] + 0.5*(qp[a] + q0[a]);
+	  f[a] = f[a] - 0.5*(q0[a] + qm[a]);
+	}
+      }
+      #pragma unroll
+      for (int a = 0; a < 3; a++) P.force[a*nsd + site] = P.fconst[a] + (-f[a]);
+    }
+
+    if (ORDER > 0) {
+      constexpr int O = (ORDER > 0) ? ORDER : 1;
+      const double mu0 = ch_mu(S, ph0, dq0);
+      double flo[3], fhi[3];
+      // x faces
+      {
+	const double Mg = __dmul_rn(M, P.gmu[0]);
+	const double phm = __ldg(V.phi[1] + col), php = __ldg(V.phi[3] + col);
+	flo[0] = ch_face<O>(__ldg(V.ux[0] + col), __ldg(V.ux[1] + col), __ldg(V.phi[0] + col), phm, ph0, php,
+			    ch_mu(S, phm, __ldg(V.dsq[0] + col)), mu0, M, Mg);
+	fhi[0] = ch_face<O>(__ldg(V.ux[1] + col), __ldg(V.ux[2] + col), phm, ph0, php, __ldg(V.phi[4] + col),
+			    mu0, ch_mu(S, php, __ldg(V.dsq[2] + col)), M, Mg);
+	// phi_ch_le_fix_fluxes, src/phi_cahn_hilliard.c:663-715
+	const int ny = L.n[1];
+	if (l == 0) {
+	  const int j1 = 1 + (c1 - Q.jdy_up - 2 + 2*ny) % ny, j2 = 1 + j1 % ny;
+	  const double * fwp = scr + L.s0 + L.z0 + c2;
+	  const double bw = __dadd_rn(__dmul_rn(fwp[(i64) j1*L.s1], Q.fr_up), __dmul_rn(fwp[(i64) j2*L.s1], 1.0 - Q.fr_up));
+	  fhi[0] = __dmul_rn(0.5, __dadd_rn(scr[col], bw));
+	}
+	if (l == 1) {
+	  const int j1 = 1 + (c1 - Q.jdy_dn - 2 + 2*ny) % ny, j2 = 1 + j1 % ny;
+	  const double * fep = scr + L.z0 + c2;
+	  const double be = __dadd_rn(__dmul_rn(fep[(i64) j1*L.s1], Q.fr_dn), __dmul_rn(fep[(i64) j2*L.s1], 1.0 - Q.fr_dn));
+	  flo[0] = __dmul_rn(0.5, __dadd_rn(scr[L.s0 + col], be));
+	}
+      }
+      // y and z faces: within the plane
+      const double * dsc = V.dsq[1];
+      #pragma unroll
+      for (int a = 1; a < 3; a++) {
+	const double * ua = P.u + a*nsd + (i64) x*L.s0;
+	const double u0 = __ldg(ua + col);
+	const double um = __ldg(ua + col + d[a][1]), up = __ldg(ua + col + d[a][2]);
+	const double phm = __ldg(phc + col + d[a][1]), php = __ldg(phc + col + d[a][2]);
+	const double phm2 = (O >= 3) ? __ldg(phc + col + d[a][0]) : 0.0;
+	const double php2 = (O >= 3) ? __ldg(phc + col + d[a][3]) : 0.0;
+	const double Mg = __dmul_rn(M, P.gmu[a]);
+	flo[a] = ch_face<O>(um, u0, phm2, phm, ph0, php, ch_mu(S, phm, __ldg(dsc + col + d[a][1])), mu0, M, Mg);
+	fhi[a] = ch_face<O>(u0, up, phm, ph0, php, php2, mu0, ch_mu(S, php, __ldg(dsc + col + d[a][2])), M, Mg);
+      }
+      double dphi = __dadd_rn(fhi[0], -flo[0]);
+      dphi = __dadd_rn(dphi, fhi[1]);
+      dphi = __dadd_rn(dphi, -flo[1]);
+      dphi = __dadd_rn(dphi, fhi[2]);
+      dphi = __dadd_rn(dphi, -flo[2]);
+      P.phi_out[site] = __dadd_rn(ph0, -dphi);
+    }
+  }
+}
+
 }   // namespace
 
 #ifndef B200LB_KERNEL_SOURCE_ONLY      // tools/ch_emulate.cpp steps through the kernel source on the host
@@ -303,6 +562,37 @@ static cudaError_t launch_order(const ChParams & P, int order, cudaStream_t st) 
 #else
 #define CH_LAUNCH ch_launch_fast
 #endif
+
+#if CH_EXACT
+#define CH_LE_LAUNCH ch_le_launch_exact
+#else
+#define CH_LE_LAUNCH ch_le_launch_fast
+#endif
+
+template <int ORDER>
+static cudaError_t le_launch(const ChParams & P, const ChLeParams & Q, bool do_force, cudaStream_t st) {
+  const Layout & L = P.L;
+  dim3 block(128, 1, 1);
+  dim3 grid((L.n[2] + 127)/128, L.n[1], Q.nplanes);
+  ch_le_pass_a<CH_EXACT, ORDER><<<grid, block, 0, st>>>(P, Q, do_force ? 1 : 0);
+  if (do_force) ch_le_reduce<<<dim3(Q.nplanes, 3, 1), 256, 0, st>>>(P, Q);
+  ch_le_pass_b<CH_EXACT, ORDER><<<grid, block, 0, st>>>(P, Q, do_force ? 1 : 0);
+  return cudaGetLastError();
+}
+
+cudaError_t CH_LE_LAUNCH(const ChParams & P, const ChLeParams & Q, bool do_force, bool do_update, cudaStream_t st) {
+  if (Q.nplanes < 1 || Q.nplanes > CH_LE_MAXPLANE) return cudaErrorInvalidValue;
+  if (P.accumulate) return cudaErrorInvalidValue;
+  if (do_force && P.method == CH_FORCE_NONE) do_force = false;
+  switch (do_update ? P.order : 0) {
+  case 0: return do_force ? le_launch<0>(P, Q, true, st) : cudaSuccess;
+  case 1: return le_launch<1>(P, Q, do_force, st);
+  case 2: return le_launch<2>(P, Q, do_force, st);
+  case 3: return le_launch<3>(P, Q, do_force, st);
+  case 4: return le_launch<4>(P, Q, do_force, st);
+  }
+  return cudaErrorInvalidValue;
+}
 
 cudaError_t CH_LAUNCH(const ChParams & P, bool do_force, bool do_update, cudaStream_t st) {
   const int order = do_update ? P.order : 0;

@@ -33,3 +33,33 @@ struct ChParams {
 // do_force: phi_force_calculation; do_update: phi_cahn_hilliard. One pass does both.
 cudaError_t ch_launch_exact(const ChParams & P, bool do_force, bool do_update, cudaStream_t st);
 cudaError_t ch_launch_fast(const ChParams & P, bool do_force, bool do_update, cudaStream_t st);
+
+// ---------------------------------------------------------------------------
+// ... across Lees-Edwards planes. ch_kernel runs over the whole lattice as if there were
+// none; the layers of sites around every plane (loc - 1 .. loc + 2) are then redone with the
+// buffer planes of le_field_kernels.cuh: pass A materialises the fluxes through the plane
+// as either side sees them (they differ: src/phi_cahn_hilliard.c:604-616), a reduction forms
+// the plane average of the stress-flux mismatch (phi_force_flux_fix_local,
+// src/phi_force.c:595-671), pass B applies both corrections and rewrites force and phi.
+// With planes the force is the divergence of face-interpolated stresses whatever the
+// method (src/phi_force.c:89-96).
+// ---------------------------------------------------------------------------
+
+#define CH_LE_MAXPLANE 16
+
+struct ChLeParams {
+  int nplanes;
+  int loc[CH_LE_MAXPLANE];    // halo-inclusive x of the layer of sites below plane p
+  const double * bphi;        // [nplanes][4][s0] buffer planes of phi
+  const double * bgrad;       // [nplanes][2][3][s0] gradient in buffers b = 1, 2
+  const double * bdelsq;      // [nplanes][2][s0]
+  const double * bux;         // [nplanes][2][s0] u_x in buffers b = 1, 2 (time t + 1)
+  double * scr;               // [nplanes][8][s0]: fe(loc), fw(loc + 1), stress fluxe[3](loc), fluxw[3](loc + 1)
+  double * fbar;              // [nplanes][3] sum over the plane of -fluxe(loc) + fluxw(loc + 1)
+  int jdy_up, jdy_dn;         // phi_ch_le_fix_fluxes: displacement +t u_y (looking up), -t u_y
+  double fr_up, fr_dn;
+  double ra;                  // 1/2 / (L_y L_z)
+};
+
+cudaError_t ch_le_launch_exact(const ChParams & P, const ChLeParams & Q, bool do_force, bool do_update, cudaStream_t st);
+cudaError_t ch_le_launch_fast(const ChParams & P, const ChLeParams & Q, bool do_force, bool do_update, cudaStream_t st);

@@ -10,6 +10,8 @@ and it is what checked the kernels written after a round's GPU allocation was sp
   ch_kernel                         vs tests/golden/ref_ch.npz (bit for bit; fma build: ulps)
   lb_sweep_kernel GM bit 3          vs the sweep that pulls g itself (bit for bit)
   le_phi_buffer / le_grad_fix       vs the oracle's field_leesedwards + stencils (bit for bit)
+  ch_kernel + buffer kernels + ch_le_pass_a/_b (finite-difference order parameter across
+  Lees-Edwards planes)              vs the oracle (phi bit for bit, force 1e-15)
 """
 
 import os
@@ -53,3 +55,10 @@ def test_binary_sweep_with_handed_over_flux_is_identical():
 def test_lees_edwards_order_parameter_kernels_match_oracle():
     out = run_tool("check_le_field_on_host.py")
     assert "all identical to the oracle" in out and "FAIL" not in out
+
+
+def test_finite_difference_order_parameter_across_planes_matches_oracle():
+    out = run_tool("check_ch_le_on_host.py")
+    assert "exact build: order parameter identical to the oracle, force within 1e-15" in out
+    assert "fast build: within a few ulp of the oracle" in out
+    assert "DIFF" not in out

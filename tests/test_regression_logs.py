@@ -328,9 +328,10 @@ def viscosities(inp):
 # Written and checked on the host (tools/check_le_field_on_host.py steps through the kernel
 # source against the oracle) after the round's GPU allocation was spent: the device run
 # of these cases is opt-in until it has been seen to pass on a B200 once.
-UNVERIFIED_ON_GPU = {"serial-le2d-lb1"}
-# free_energy symmetric with planes: oracle only so far (the library refuses the combination)
-NOT_ON_DEVICE = {"serial-le3d-st%d" % k for k in range(1, 9)} | {"serial-le2d-fd1"}
+UNVERIFIED_ON_GPU = {"serial-le2d-lb1"} | {"serial-le3d-st%d" % k for k in range(1, 9)}
+# free_energy symmetric with planes in two dimensions: oracle only (the library's
+# finite-difference order parameter is three-dimensional)
+NOT_ON_DEVICE = {"serial-le2d-fd1"}
 # The reference prints compensated sums (src/util_sum.c, src/stats_distribution.c:201-265);
 # over 6e5 populations a plain sum is 1e-12 away. That shows where a printed digit sits on a
 # rounding boundary: the y momentum of this log is 3.41278045e-04 printed as "%14.7e".
@@ -408,10 +409,10 @@ def test_cuda_reproduces_reference_log(case, hydro_write):
     import ludwig_b200 as lb
     from ludwig_b200 import models_host
     if case in NOT_ON_DEVICE:
-        pytest.skip("the finite-difference order parameter across Lees-Edwards planes is not on the "
-                    "device path yet (b200lb_le_commit refuses it); the oracle reproduces this log")
+        pytest.skip("a two-dimensional finite-difference order parameter is not on the device path "
+                    "(b200lb_ch_create refuses it); the oracle reproduces this log")
     if case in UNVERIFIED_ON_GPU and not os.environ.get("B200LB_UNVERIFIED"):
-        pytest.skip("order parameter across Lees-Edwards planes: device path not yet run on a GPU "
+        pytest.skip("order parameter across Lees-Edwards planes / fourth-order advection: device path not yet run on a GPU "
                     "(set B200LB_UNVERIFIED=1); the oracle reproduces this log in the CPU suite")
     rec = GOLD[case]
     nvel = rec["nvel"]
@@ -422,6 +423,8 @@ def test_cuda_reproduces_reference_log(case, hydro_write):
     lat = lb.Lattice(nvel, nt, ndist=ndist, periodic=periodic)
     lat.set_option("hydro_write", hydro_write)
     lat.set_option("halo", lb.HALO_REDUCED)          # lb_halo_openmp_reduced in the input
+    if fd_route(rec) and le_options(rec["input"]):
+        lat.set_option("le_fd", 1)                   # behind an option until run on a GPU
     kt = float(rec["input"].get("temperature", 0.0)) if noisy(rec) else 0.0
     kw = binary_params(rec["input"]) if (ndist == 2 or fd_route(rec)) else {}
     lat.set_param(eta_shear=eta, eta_bulk=zeta, kt=kt, ghost_off=int(ghost_off(rec)),

@@ -173,3 +173,88 @@ def test_fourth_order_advection_vs_oracle(nlocal, npt, exact):
         assert np.max(np.abs(phi1[m] - po[m])) <= 1e-15*np.max(np.abs(po[m]))
     assert abs(phi1[m].sum() - phi[m].sum()) < 1e-13*m.sum()
     lat.close()
+
+
+# ---------------------------------------------------------------------------
+# the finite-difference order parameter across the planes (option le_fd; ch_le_pass_a/_b,
+# checked on the host by tools/check_ch_le_on_host.py)
+# ---------------------------------------------------------------------------
+
+FD_LE = [((16, 8, 6), dict(nplanes=2, uy=0.05), 1, 7),
+         ((16, 8, 6), dict(nplanes=2, uy=0.05), 2, 27),
+         ((12, 7, 5), dict(nplanes=1, uy=-0.03), 3, 27),
+         ((12, 8, 6), dict(nplanes=2, uy=0.07), 4, 7),
+         ((16, 8, 140), dict(nplanes=2, uy=0.04, oscillatory=1, period=40, nt0=0), 2, 7)]
+
+
+@pytest.mark.parametrize("nlocal,le,order,npt", FD_LE)
+@pytest.mark.parametrize("exact,fuse", [(1, 1), (0, 1), (0, 0)])
+def test_finite_difference_order_parameter_across_planes(nlocal, le, order, npt, exact, fuse):
+    """Stage parity (force 1e-15 of its largest value, phi bit for bit with ch_exact) at
+    several times, then the sheared time loop within 1e-12."""
+    import ludwig_b200 as lb
+    import goldenlib
+    from oracle import pyoracle
+    P = goldenlib.CH_PHYS
+    gmu = (1e-5, -2e-5, 3e-5)
+    kw = dict(eta_shear=P["eta"], eta_bulk=P["eta"], mobility=P["mobility"], a=P["a"], b=P["b"], kappa=P["kappa"])
+    orc = pyoracle.Oracle(19, nlocal)
+    n = orc.nsite
+    m = orc.interior_mask()
+    prm = pyoracle.make_param(**kw)
+    ch = orc.ch(order, pyoracle.FORCE_STRESS_DIVERGENCE, gmu)
+    ole = orc.le(**le)
+    phi0, u0 = goldenlib.ch_fields(nlocal)
+    lat = lb.Lattice(19, nlocal)
+    lat.set_option("le_fd", 1)
+    lat.set_option("ch_exact", exact)
+    lat.set_option("ch_fuse", fuse)
+    lat.set_param(**kw)
+    commit(lat, le)
+    lat.phi_ch_create(order, lb.FORCE_STRESS_DIVERGENCE, gmu)
+    lat.field_grad_set(npt)
+    for t in (0.0, 1.0, 6.0, 133.0):
+        lat.field_h2d(lb.FIELD_PHI, phi0)
+        lat.field_h2d(lb.FIELD_U, u0)
+        lat.hydro_f_zero()
+        lat.field_halo()
+        lat.le_field_time_set(t)
+        lat.field_grad_compute()
+        lat.phi_force_calculation()
+        lat.phi_cahn_hilliard()
+        force = lat.field_d2h(lb.FIELD_FORCE)
+        phi1 = lat.field_d2h(lb.FIELD_PHI)
+        po, uo = phi0.copy(), u0.copy()
+        fo, grad, delsq = np.zeros((n, 3)), np.zeros((n, 3)), np.zeros(n)
+        orc.ch_le_step(prm, ch, ole, t, npt, po, uo, fo, grad, delsq)
+        assert np.max(np.abs(force[m] - fo[m])) <= 1e-15*np.max(np.abs(fo[m])), t
+        if exact:
+            assert np.array_equal(phi1[m], po[m]), t
+        else:
+            assert np.max(np.abs(phi1[m] - po[m])) <= 1e-15*np.max(np.abs(po[m])), t
+        assert abs(phi1[m].sum() - phi0[m].sum()) < 1e-13*m.sum()
+    # the time loop
+    nsteps = 6
+    f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal)
+    f, fp = f0.copy(), np.zeros_like(f0)
+    rho, u, force = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
+    grad, delsq = np.zeros((n, 3)), np.zeros(n)
+    phi = phi0.copy()
+    ole.t_current, ole.t_start = 3, 3
+    orc.gradient_select(npt)
+    orc.ch_attach(ch)
+    orc.le_attach(ole)
+    try:
+        orc.step(prm, nsteps, f, fp, rho, u, force, phi, grad, delsq)
+    finally:
+        orc.gradient_select(7)
+        orc.ch_attach(None)
+        orc.le_attach(None)
+    lat.le_time_set(3)
+    lat.lb_memcpy_h2d(f0)
+    lat.field_h2d(lb.FIELD_PHI, phi0)
+    lat.field_h2d(lb.FIELD_U, np.zeros((n, 3)))
+    lat.step(nsteps)
+    assert relerr(lat.lb_memcpy_d2h()[m], f[m]) < TOL
+    assert np.max(np.abs(lat.field_d2h(lb.FIELD_PHI)[m] - phi[m])) < TOL
+    lat.close()

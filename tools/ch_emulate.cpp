@@ -25,7 +25,14 @@ using std::min;
 #define __launch_bounds__(...)
 #endif
 
+static dim3 blockDim, gridDim;
+static inline void __syncthreads() {}
+using std::max;
+#undef __shared__
+#define __shared__ static
+
 #define B200LB_KERNEL_SOURCE_ONLY
+#include "../ludwig_b200/csrc/le_field_kernels.cuh"
 #include "../ludwig_b200/csrc/ch_kernels.cu"
 
 // the layout of b200lb create_impl (api.cu) for a three-dimensional lattice
@@ -108,4 +115,118 @@ extern "C" int ch_emulate(const int nlocal[3], const int wrap[3], int method, in
   to_host(L, dforce, 3, force);
   to_host(L, dout, 1, phi_out);
   return rc;
+}
+
+
+// ---------------------------------------------------------------------------
+// The same with Lees-Edwards planes: what ch_run + ch_le_run (api.cu) launch, in their
+// order. phi with its periodic halo; grad, delsq: the plane-aware gradient of the
+// interior (what grad*_kernel + le_grad_fix leave); u: the last collision's velocity.
+// loc[p]: 1-based x of the layer below plane p. t = physics_control_time.
+// The plane reduction (ch_le_reduce: shared memory + barriers) is restated as a loop.
+// ---------------------------------------------------------------------------
+
+template <class F> static void for_grid(dim3 grid, dim3 block, F body) {
+  gridDim = grid; blockDim = block;
+  for (unsigned bz = 0; bz < grid.z; bz++) for (unsigned by = 0; by < grid.y; by++) for (unsigned bx = 0; bx < grid.x; bx++) {
+    blockIdx.x = bx; blockIdx.y = by; blockIdx.z = bz;
+    for (unsigned ty = 0; ty < block.y; ty++) for (unsigned tx = 0; tx < block.x; tx++) {
+      threadIdx.x = tx; threadIdx.y = ty; threadIdx.z = 0;
+      body();
+    }
+  }
+}
+
+template <int ORDER>
+static void le_passes(const ChParams & P, const ChLeParams & Q, int do_force) {
+  const Layout & L = P.L;
+  dim3 block(128, 1, 1);
+  dim3 grid((L.n[2] + 127)/128, L.n[1], Q.nplanes);
+  for_grid(grid, block, [&]() { ch_le_pass_a<CH_EXACT, ORDER>(P, Q, do_force); });
+  if (do_force) {
+    for (int p = 0; p < Q.nplanes; p++) for (int a = 0; a < 3; a++) {
+      const double * scr = Q.scr + (i64) 8*p*L.s0;
+      double part[256];
+      const int n = L.n[1]*L.n[2];
+      for (int tid = 0; tid < 256; tid++) {
+	double acc = 0.0;
+	for (int i = tid; i < n; i += 256) {
+	  const int jc = 1 + i/L.n[2], kc = 1 + i % L.n[2];
+	  const i64 col = (i64) jc*L.s1 + L.z0 + kc;
+	  acc += - scr[(2 + a)*L.s0 + col] + scr[(5 + a)*L.s0 + col];
+	}
+	part[tid] = acc;
+      }
+      for (int w = 128; w > 0; w >>= 1) for (int tid = 0; tid < w; tid++) part[tid] += part[tid + w];
+      Q.fbar[3*p + a] = part[0];
+    }
+  }
+  for_grid(grid, block, [&]() { ch_le_pass_b<CH_EXACT, ORDER>(P, Q, do_force); });
+}
+
+extern "C" int ch_le_emulate(const int nlocal[3], int nplanes, const int * loc, double uy,
+			     int oscillatory, int period, int nt0, double t, int npt, int order,
+			     const double prm[4], const double gmu[3],
+			     const double * phi, const double * grad, const double * delsq,
+			     const double * u, double * force, double * phi_out) {
+  Layout L = make_layout(nlocal, 16);
+  std::vector<double> dphi, dgrad, ddelsq, du, dforce, dout;
+  to_device(L, phi, 1, dphi); to_device(L, grad, 3, dgrad); to_device(L, delsq, 1, ddelsq);
+  to_device(L, u, 3, du); to_device(L, force, 3, dforce); to_device(L, phi, 1, dout);
+  ChParams P;
+  memset(&P, 0, sizeof(P));
+  P.L = L;
+  for (int d = 0; d < 3; d++) { P.wrap[d] = 1; P.gmu[d] = gmu[d]; P.fconst[d] = 0.0; }
+  P.phi = dphi.data(); P.grad = dgrad.data(); P.delsq = ddelsq.data(); P.u = du.data();
+  P.force = dforce.data(); P.phi_out = dout.data();
+  P.A = prm[0]; P.B = prm[1]; P.kappa = prm[2]; P.mobility = prm[3];
+  P.accumulate = 0; P.order = order; P.method = CH_FORCE_STRESS_DIVERGENCE; P.nx = 3;
+  if (run_order<CH_FORCE_STRESS_DIVERGENCE>(P, order)) return -1;
+
+  const int np = nplanes;
+  std::vector<double> buf((size_t) 22*np*L.s0 + 3*np, 0.0);
+  double * bphi = buf.data();
+  double * bgrad = bphi + (size_t) 4*np*L.s0;
+  double * bdelsq = bgrad + (size_t) 6*np*L.s0;
+  double * bux = bdelsq + (size_t) 2*np*L.s0;
+  double * scr = bux + (size_t) 2*np*L.s0;
+  double * fbar = scr + (size_t) 8*np*L.s0;
+  LePhiTab T;
+  memset(&T, 0, sizeof(T));
+  T.L = L; T.w0 = T.w1 = T.w2 = 1;
+  dim3 block(128, 1, 1);
+  le_phi_tab_fill4(T, np, loc, uy, oscillatory, period, nt0, t);
+  for_grid(dim3((L.n[2] + 2 + 127)/128, L.n[1] + 2, T.nbuf), block, [&]() { le_phi_buffer_kernel(T, dphi.data(), bphi); });
+  LeBufGradTab G;
+  memset(&G, 0, sizeof(G));
+  G.L = L; G.w1 = 1; G.w2 = 1; G.nplanes = np;
+  for (int p = 0; p < np; p++) G.loc[p] = loc[p];
+  dim3 gplane((L.n[2] + 127)/128, L.n[1], 2*np);
+  if (npt == 27) for_grid(gplane, block, [&]() { le_buffer_grad_kernel<27>(G, dphi.data(), bphi, bgrad, bdelsq); });
+  else for_grid(gplane, block, [&]() { le_buffer_grad_kernel<7>(G, dphi.data(), bphi, bgrad, bdelsq); });
+  le_u_tab_fill(T, np, loc, uy, oscillatory, period, nt0, t);
+  for_grid(gplane, block, [&]() { le_u_buffer_kernel(T, du.data(), bux); });
+  ChLeParams Q;
+  memset(&Q, 0, sizeof(Q));
+  Q.nplanes = np;
+  for (int p = 0; p < np; p++) Q.loc[p] = loc[p];
+  Q.bphi = bphi; Q.bgrad = bgrad; Q.bdelsq = bdelsq; Q.bux = bux; Q.scr = scr; Q.fbar = fbar;
+  {
+    const int ny = L.n[1];
+    double dy = fmod(+(t*uy), 1.0*ny);
+    Q.jdy_up = (int) floor(dy); Q.fr_up = dy - Q.jdy_up;
+    dy = fmod(-(t*uy), 1.0*ny);
+    Q.jdy_dn = (int) floor(dy); Q.fr_dn = dy - Q.jdy_dn;
+    Q.ra = 0.5/(1.0*nlocal[1]*nlocal[2]);
+  }
+  switch (order) {
+  case 1: le_passes<1>(P, Q, 1); break;
+  case 2: le_passes<2>(P, Q, 1); break;
+  case 3: le_passes<3>(P, Q, 1); break;
+  case 4: le_passes<4>(P, Q, 1); break;
+  default: return -1;
+  }
+  to_host(L, dforce, 3, force);
+  to_host(L, dout, 1, phi_out);
+  return 0;
 }
