@@ -224,7 +224,7 @@ int  b200lb_le_field_time_set(b200lb_t * h, double t);                 /* physic
  * launches). Free-energy parameters A, B, kappa and the mobility are those of
  * b200lb_set_param. With option "ch_exact" results are bit-identical to the reference's;
  * the default build uses fused multiply-add (a few ulp away, 1.6x faster).
- * On this path: three dimensions, fully periodic, fluid only, Lees-Edwards planes behind
+ * On this path: three-dimensional models (the lattice may be one site thick), fully periodic, fluid only, Lees-Edwards planes behind
  * option "le_fd";
  * advection orders 1-4 (3 and 4 only where every direction is periodic within the rank:
  * they read phi two sites away; 4 is a host loop behind two copies of the flux arrays in

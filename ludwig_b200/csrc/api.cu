@@ -1663,7 +1663,8 @@ static int field_current(b200lb_s * h, int field);
 extern "C" int b200lb_ch_create(b200lb_t * h, int order, int method) {
   if (!h) return fail("null handle");
   if (h->desc.ndist != 1) return fail("phi_ch_create: the finite-difference order parameter goes with ndist = 1 (symmetric_lb carries it as a second distribution)");
-  if (h->desc.ndim != 3 || h->desc.nlocal[2] == 1) return fail("phi_ch_create: two-dimensional systems (2d_5pt_fluid gradient, wz = 0) are not on this path");
+  if (h->desc.ndim != 3) return fail("phi_ch_create: two-dimensional models (2d_5pt_fluid gradient) are not on this path");
+  if (h->desc.nlocal[2] == 1 && h->desc.cartsz[2] > 1) return fail("phi_ch_create: a lattice one site thick decomposed in z");
   for (int a = 0; a < 3; a++) {
     if (!h->desc.periodic[a]) return fail("phi_ch_create: walls need the solid gradient stencils and the no-flux masks of src/advection_bcs.c: not on this path");
   }
@@ -1812,6 +1813,7 @@ static int ch_run(b200lb_s * h, bool do_force, bool do_update) {
   P.order = h->ch_order;
   P.method = h->ch_method;
   P.nx = h->opt_ch_planes;
+  P.skipz = (h->desc.nlocal[2] == 1) ? 1 : 0;       // wz, src/phi_cahn_hilliard.c:999
   if (h->le_nlocal) {
     // with planes the force is the divergence of the face-interpolated stress whatever
     // the method (src/phi_force.c:89-96)

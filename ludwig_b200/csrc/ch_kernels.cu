@@ -261,12 +261,15 @@ ch_kernel(const ChParams P) {
 	flo[a] = ch_face<ORDER>(um, u0, phm2, phm[a], ph0, php[a], ch_mu(S, phm[a], dqm[a]), mu0, M, Mg);
 	fhi[a] = ch_face<ORDER>(u0, up, phm[a], ph0, php[a], php2, mu0, ch_mu(S, php[a], dqp[a]), M, Mg);
       }
-      // phi -= (+ fe - fw + fy - fy[index - ys] + wz*fz - wz*fz[index - 1]), wz = 1
+      // phi -= (+ fe - fw + fy - fy[index - ys] + wz*fz - wz*fz[index - 1]); wz = 0 for a
+      // lattice one site thick (uniform branch)
       double dphi = __dadd_rn(fhi[0], -flo[0]);
       dphi = __dadd_rn(dphi, fhi[1]);
       dphi = __dadd_rn(dphi, -flo[1]);
-      dphi = __dadd_rn(dphi, fhi[2]);
-      dphi = __dadd_rn(dphi, -flo[2]);
+      if (!P.skipz) {
+	dphi = __dadd_rn(dphi, fhi[2]);
+	dphi = __dadd_rn(dphi, -flo[2]);
+      }
       P.phi_out[site] = __dadd_rn(ph0, -dphi);
     }
   }
@@ -524,8 +527,10 @@ ch_le_pass_b(const ChParams P, const ChLeParams Q, const int do_force) {
       double dphi = __dadd_rn(fhi[0], -flo[0]);
       dphi = __dadd_rn(dphi, fhi[1]);
       dphi = __dadd_rn(dphi, -flo[1]);
-      dphi = __dadd_rn(dphi, fhi[2]);
-      dphi = __dadd_rn(dphi, -flo[2]);
+      if (!P.skipz) {
+	dphi = __dadd_rn(dphi, fhi[2]);
+	dphi = __dadd_rn(dphi, -flo[2]);
+      }
       P.phi_out[site] = __dadd_rn(ph0, -dphi);
     }
   }

@@ -28,6 +28,7 @@ struct ChParams {
   int order;              // advection scheme: 1, 2, 3
   int method;             // CH_FORCE_*
   int nx;                 // x-planes marched by one block
+  int skipz;              // n_z = 1: the z fluxes stay out of the update (wz = 0, src/phi_cahn_hilliard.c:999)
 };
 
 // do_force: phi_force_calculation; do_update: phi_cahn_hilliard. One pass does both.

@@ -288,10 +288,11 @@ int orc_ch_flux_mu(const orc_box_t * box, const orc_param_t * prm,
   return 0;
 }
 
-/* phi_ch_ufs_kernel, src/phi_cahn_hilliard.c:1025-1062 (three-dimensional: wz = 1) */
+/* phi_ch_ufs_kernel, src/phi_cahn_hilliard.c:1025-1062; wz = 0 when the lattice is one
+ * site thick (phi_ch_update_forward_step :999) */
 int orc_ch_update(const orc_box_t * box, const double * flux, double * phi) {
   int ic;
-  const double wz = 1.0;
+  const double wz = (box->nlocal[2] == 1) ? 0.0 : 1.0;
   const long ys = box->nall[2];
   const double * fw = flux, * fe = flux + box->nsite, * fy = flux + 2*box->nsite,
     * fz = flux + 3*box->nsite;

@@ -577,7 +577,18 @@ FD_CASES = [
 
 @pytest.mark.parametrize("order,method,npt,gmu", FD_CASES)
 def test_cahn_hilliard_stages(order, method, npt, gmu):
-    nvel, nlocal = 19, (10, 8, 6)
+    ch_stages((10, 8, 6), order, method, npt, gmu)
+
+
+@pytest.mark.parametrize("order,method,npt,gmu", [FD_CASES[0], FD_CASES[2], FD_CASES[4]])
+def test_cahn_hilliard_one_site_thick(order, method, npt, gmu):
+    """n_z = 1 with a three-dimensional model and stencil (as serial-le2d-fd1): the z
+    fluxes stay out of the update (wz = 0, src/phi_cahn_hilliard.c:999)."""
+    ch_stages((12, 9, 1), order, method, npt, gmu)
+
+
+def ch_stages(nlocal, order, method, npt, gmu):
+    nvel = 19
     need_ref(nvel)
     A, B, K, M, eta = -0.00625, 0.00625, 0.004, 1.25, 0.00625
     orc = pyoracle.Oracle(nvel, nlocal)

@@ -328,10 +328,8 @@ def viscosities(inp):
 # Written and checked on the host (tools/check_le_field_on_host.py steps through the kernel
 # source against the oracle) after the round's GPU allocation was spent: the device run
 # of these cases is opt-in until it has been seen to pass on a B200 once.
-UNVERIFIED_ON_GPU = {"serial-le2d-lb1"} | {"serial-le3d-st%d" % k for k in range(1, 9)}
-# free_energy symmetric with planes in two dimensions: oracle only (the library's
-# finite-difference order parameter is three-dimensional)
-NOT_ON_DEVICE = {"serial-le2d-fd1"}
+UNVERIFIED_ON_GPU = {"serial-le2d-lb1", "serial-le2d-fd1"} | {"serial-le3d-st%d" % k for k in range(1, 9)}
+NOT_ON_DEVICE = set()
 # The reference prints compensated sums (src/util_sum.c, src/stats_distribution.c:201-265);
 # over 6e5 populations a plain sum is 1e-12 away. That shows where a printed digit sits on a
 # rounding boundary: the y momentum of this log is 3.41278045e-04 printed as "%14.7e".

@@ -108,6 +108,7 @@ extern "C" int ch_emulate(const int nlocal[3], const int wrap[3], int method, in
   P.force = dforce.data(); P.phi_out = dout.data();
   P.A = prm[0]; P.B = prm[1]; P.kappa = prm[2]; P.mobility = prm[3];
   P.accumulate = accumulate; P.order = order; P.method = method; P.nx = 3;
+  P.skipz = (nlocal[2] == 1) ? 1 : 0;
   int rc = -1;
   if (method == 0 || method == CH_FORCE_NONE) rc = run_order<0>(P, order);
   if (method == CH_FORCE_STRESS_DIVERGENCE) rc = run_order<CH_FORCE_STRESS_DIVERGENCE>(P, order);
@@ -181,6 +182,7 @@ extern "C" int ch_le_emulate(const int nlocal[3], int nplanes, const int * loc, 
   P.force = dforce.data(); P.phi_out = dout.data();
   P.A = prm[0]; P.B = prm[1]; P.kappa = prm[2]; P.mobility = prm[3];
   P.accumulate = 0; P.order = order; P.method = CH_FORCE_STRESS_DIVERGENCE; P.nx = 3;
+  P.skipz = (nlocal[2] == 1) ? 1 : 0;
   if (run_order<CH_FORCE_STRESS_DIVERGENCE>(P, order)) return -1;
 
   const int np = nplanes;

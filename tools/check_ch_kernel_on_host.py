@@ -102,13 +102,14 @@ def main(exact=1):
                 bad += (not ok)
     # fourth-order advection: no golden vector, the oracle (pinned against the reference
     # for this order, tests/test_oracle_vs_ref.py FD_CASES) stands in
-    for nlocal, npt in (((10, 8, 6), 7), ((6, 7, 9), 27)):
+    # ... and a lattice one site thick (wz = 0), third order
+    for nlocal, npt, order4 in (((10, 8, 6), 7, 4), ((6, 7, 9), 27, 4), ((12, 9, 1), 27, 3)):
         orc = pyoracle.Oracle(19, nlocal)
         n = orc.nsite
         m = orc.interior_mask()
         prm_o = pyoracle.make_param(eta_shear=0.1, eta_bulk=0.1, mobility=P["mobility"], a=P["a"], b=P["b"],
                                     kappa=P["kappa"])
-        ch = orc.ch(4, 2, (1e-5, -2e-5, 3e-5))
+        ch = orc.ch(order4, 2, (1e-5, -2e-5, 3e-5))
         phi, u = goldenlib.ch_fields(nlocal)
         orc.halo(phi, 1)
         grad, delsq = np.zeros((n, 3)), np.zeros(n)
@@ -119,14 +120,14 @@ def main(exact=1):
         orc.phi_force(prm_o, ch, po, grad, delsq, fo)
         orc.cahn_hilliard(prm_o, ch, po, delsq, uo)
         force, out = np.zeros((n, 3)), np.zeros(n)
-        rc = E.ch_emulate((ctypes.c_int * 3)(*nlocal), (ctypes.c_int * 3)(1, 1, 1), 2, 4,
+        rc = E.ch_emulate((ctypes.c_int * 3)(*nlocal), (ctypes.c_int * 3)(1, 1, 1), 2, order4,
                           (ctypes.c_double * 4)(P["a"], P["b"], P["kappa"], P["mobility"]),
                           (ctypes.c_double * 3)(1e-5, -2e-5, 3e-5), (ctypes.c_double * 3)(0.0, 0.0, 0.0), 0,
                           *[a.ctypes.data_as(dp) for a in (phi, grad, delsq, u, force, out)])
         assert rc == 0
         okf, okp = same(force[m], fo[m], exact), same(out[m], po[m], exact)
         okp = okp and abs(out[m].sum() - phi[m].sum()) < 1e-13 * m.sum()
-        print("order 4 %s %d-point force %s  phi %s" % (nlocal, npt, "ok" if okf else "DIFF", "ok" if okp else "DIFF"))
+        print("order %d %s %d-point force %s  phi %s" % (order4, nlocal, npt, "ok" if okf else "DIFF", "ok" if okp else "DIFF"))
         bad += (not okf) + (not okp)
     print("FAILED" if bad else ("exact build: all identical to the reference" if exact
                                 else "fast build: all within a few ulp of the reference"))

@@ -41,6 +41,7 @@ CASES = [((16, 8, 6), dict(nplanes=2, uy=0.05), 1, 7),
          ((12, 7, 5), dict(nplanes=1, uy=-0.03), 3, 27),
          ((15, 9, 6), dict(nplanes=3, uy=0.31), 3, 7),
          ((12, 8, 6), dict(nplanes=2, uy=0.07), 4, 7),
+         ((16, 12, 1), dict(nplanes=2, uy=0.02), 3, 27),
          ((16, 8, 140), dict(nplanes=2, uy=0.04, oscillatory=1, period=40, nt0=0), 2, 7)]
 
 
