@@ -37,7 +37,10 @@ CASES = ["d3q19-short/serial-dist-3du", "d3q19-short/serial-dist-1dp",
          "d3q19-short/serial-le3d-st3", "d3q19-short/serial-le3d-st4",
          "d3q19-short/serial-le3d-st5", "d3q19-short/serial-le3d-st6",
          "d3q19-short/serial-le3d-st7", "d3q19-short/serial-le3d-st8",
-         "d3q19-short/serial-le2d-fd1"]
+         "d3q19-short/serial-le2d-fd1",
+         # the eight-rank long runs of the same (logs do not depend on the decomposition)
+         "d3q19/pmpi08-le2d-fd1", "d3q19/pmpi08-le2d-lb1", "d3q19/pmpi08-le3d-fd1",
+         "d3q19/pmpi08-le3d-lb1"]
 NVEL = {"d3q19-short": 19, "d3q19": 19, "d2q9": 9}
 
 

@@ -134,9 +134,11 @@ def check_long_momentum(rec, sums):
     accumulated round-off of the run (the log has 7e-14), which no other arithmetic
     reproduces digit for digit. It has to stay round-off; the line is then taken from the
     log so that every other printed number is still compared exactly."""
-    assert max(abs(x) for x in sums[4:7]) < 1e-10
-    assert max(abs(x) for x in rec["momentum"]) < 1e-10
-    sums[4:7] = rec["momentum"]
+    for a in range(3):
+        if abs(rec["momentum"][a]) < 1e-10:
+            assert abs(sums[4 + a]) < 1e-10
+            sums[4 + a] = rec["momentum"][a]
+    # (a component that carries real momentum -- y in the sheared runs -- is compared as printed)
 
 
 def roundoff_momentum(rec, sums):
@@ -328,14 +330,16 @@ def viscosities(inp):
 # Written and checked on the host (tools/check_le_field_on_host.py steps through the kernel
 # source against the oracle) after the round's GPU allocation was spent: the device run
 # of these cases is opt-in until it has been seen to pass on a B200 once.
-UNVERIFIED_ON_GPU = {"serial-le2d-lb1", "serial-le2d-fd1"} | {"serial-le3d-st%d" % k for k in range(1, 9)}
+UNVERIFIED_ON_GPU = ({"serial-le2d-lb1", "serial-le2d-fd1", "pmpi08-le2d-fd1", "pmpi08-le2d-lb1",
+                      "pmpi08-le3d-fd1", "pmpi08-le3d-lb1"}
+                     | {"serial-le3d-st%d" % k for k in range(1, 9)})
 NOT_ON_DEVICE = set()
 # The reference prints compensated sums (src/util_sum.c, src/stats_distribution.c:201-265);
 # over 6e5 populations a plain sum is 1e-12 away. That shows where a printed digit sits on a
 # rounding boundary: the y momentum of this log is 3.41278045e-04 printed as "%14.7e".
 HALFWAY = {"serial-le3d-st4"}
-LONG = {"pmpi08-spin-lb1", "pmpi08-spin-fd1"}      # 400 steps: the momentum line is accumulated round-off
-SLOW = {"pmpi08-spin-lb1"}      # minutes on the CPU oracle: opt in with B200LB_LONG=1 (fd1 takes half a minute)
+LONG = {"pmpi08-spin-lb1", "pmpi08-spin-fd1", "pmpi08-le3d-fd1", "pmpi08-le3d-lb1"}      # 400 steps: the momentum line is accumulated round-off
+SLOW = {"pmpi08-spin-lb1", "pmpi08-le3d-fd1", "pmpi08-le3d-lb1"}      # minutes on the CPU oracle: opt in with B200LB_LONG=1 (fd1 takes half a minute)
 
 
 @pytest.mark.parametrize("case", CASES)
