@@ -40,8 +40,10 @@ CASES = ["d3q19-short/serial-dist-3du", "d3q19-short/serial-dist-1dp",
          "d3q19-short/serial-le2d-fd1",
          # the eight-rank long runs of the same (logs do not depend on the decomposition)
          "d3q19/pmpi08-le2d-fd1", "d3q19/pmpi08-le2d-lb1", "d3q19/pmpi08-le3d-fd1",
-         "d3q19/pmpi08-le3d-lb1"]
-NVEL = {"d3q19-short": 19, "d3q19": 19, "d2q9": 9}
+         "d3q19/pmpi08-le3d-lb1",
+         # a drop relaxing for 20 steps (the run the reference's i/o tests restart from)
+         "d3q19-io/iodrop-mpi1-io1"]
+NVEL = {"d3q19-short": 19, "d3q19": 19, "d2q9": 9, "d3q19-io": 19}
 
 
 def floats(line):

@@ -331,7 +331,7 @@ def viscosities(inp):
 # source against the oracle) after the round's GPU allocation was spent: the device run
 # of these cases is opt-in until it has been seen to pass on a B200 once.
 UNVERIFIED_ON_GPU = ({"serial-le2d-lb1", "serial-le2d-fd1", "pmpi08-le2d-fd1", "pmpi08-le2d-lb1",
-                      "pmpi08-le3d-fd1", "pmpi08-le3d-lb1"}
+                      "pmpi08-le3d-fd1", "pmpi08-le3d-lb1", "iodrop-mpi1-io1"}
                      | {"serial-le3d-st%d" % k for k in range(1, 9)})
 NOT_ON_DEVICE = set()
 # The reference prints compensated sums (src/util_sum.c, src/stats_distribution.c:201-265);
