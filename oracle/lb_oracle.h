@@ -137,6 +137,19 @@ int orc_wall_nlink(const orc_model_t * model, const orc_box_t * box,
 int orc_wall_bbl(const orc_model_t * model, const orc_box_t * box,
 		 const orc_param_t * prm, int ndist, orc_wall_t * wall, double * f);
 
+/* Open boundaries for the fluid, inflow/outflow of type "rhou" along the one direction
+ * without walls (lb_oracle_wall.c; src/lb_bc_inflow_rhou.c, src/lb_bc_outflow_rhou.c).
+ * While attached, orc_step applies them after the halo swap (src/ludwig.c:820-831). */
+typedef struct orc_open_s {
+  int id;                 /* flow direction (0, 1, 2) */
+  double u0[3];           /* lb_bc_inflow_rhou_u0 */
+  double rho0;            /* lb_bc_outflow_rhou_rho0 */
+} orc_open_t;
+int orc_open_attach(orc_open_t * open);
+orc_open_t * orc_open_attached(void);
+int orc_open_apply(const orc_model_t * model, const orc_box_t * box, int ndist,
+		   const orc_open_t * open, double * rho, double * u, double * f);
+
 /* Lees-Edwards planes (lb_oracle_le.c; src/model_le.c, src/leesedwards.c). While
  * attached, orc_step advances t_current by one at the start of every step
  * (physics_control_next_step, src/ludwig.c:530) and applies the boundary conditions

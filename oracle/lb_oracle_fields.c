@@ -446,6 +446,9 @@ int orc_step(const orc_model_t * model, const orc_box_t * box,
       if (orc_le_apply(model, box, ndist, le, 1.0*le->t_current, a)) return -1;
     }
     orc_halo_periodic(box, ndist*model->nvel, a);
+    if (orc_open_attached()) {
+      if (orc_open_apply(model, box, ndist, orc_open_attached(), rho, u, a)) return -1;
+    }
     if (orc_wall_attached()) {
       /* src/ludwig.c:837-842. The periodic copies above also filled the wall layers,
        * which the reference leaves alone; every population a fluid site pulls out of

@@ -174,3 +174,86 @@ int orc_wall_bbl(const orc_model_t * model, const orc_box_t * box,
 
   return 0;
 }
+
+/* ---------------------------------------------------------------------------
+ * Open boundaries for the fluid ("lb_bc_open yes", lb_bc_inflow_type / _outflow_type
+ * rhou: src/lb_bc_inflow_rhou.c, src/lb_bc_outflow_rhou.c, selected in
+ * src/lb_bc_open_rt.c:48-170): the one direction without walls carries a flow. After
+ * lb_halo and ahead of the bounce-back and the propagation (src/ludwig.c:820-831)
+ *   update: the layer of halo sites in front of the inlet takes the density of the
+ *           fluid sites behind it and the prescribed velocity u0; the layer behind the
+ *           outlet takes the prescribed density rho0 and the velocity of the fluid
+ *           sites in front of it (:235-281 of either file);
+ *   impose: every population that the propagation will carry from such a halo site
+ *           into the fluid is set to the equilibrium of the halo site's (rho, u)
+ *           (:478-531; links whose halo end lies behind a wall are left to the walls).
+ * One rank. rho, u: the hydrodynamic fields the collision has just written.
+ * --------------------------------------------------------------------------- */
+
+static orc_open_t * attached_open = NULL;
+
+int orc_open_attach(orc_open_t * open) { attached_open = open; return 0; }
+orc_open_t * orc_open_attached(void) { return attached_open; }
+
+int orc_open_apply(const orc_model_t * model, const orc_box_t * box, int ndist,
+		   const orc_open_t * open, double * rho, double * u, double * f) {
+  const int id = open->id;
+  const int id1 = (id + 1) % 3, id2 = (id + 2) % 3;
+  const int nvel = model->nvel;
+  const double cs2 = 1.0/3.0, rcs2 = 3.0;
+
+  if (id < 0 || id > 2) return -1;
+
+  for (int side = 0; side < 2; side++) {          /* 0: inflow (low end), 1: outflow */
+    const int dir = (side == 0) ? -1 : +1;        /* where the halo layer is */
+    int lo[3] = {1, 1, 1}, hi[3] = {box->nlocal[0], box->nlocal[1], box->nlocal[2]};
+    if (side == 0) hi[id] = 1; else lo[id] = box->nlocal[id];
+
+    /* update */
+    for (int ic = lo[0]; ic <= hi[0]; ic++) {
+      for (int jc = lo[1]; jc <= hi[1]; jc++) {
+	for (int kc = lo[2]; kc <= hi[2]; kc++) {
+	  int c[3] = {ic, jc, kc};
+	  long index0, index1 = orc_index(box, ic, jc, kc);
+	  c[id] += dir;
+	  index0 = orc_index(box, c[0], c[1], c[2]);
+	  if (side == 0) {
+	    rho[index0] = rho[index1];
+	    for (int a = 0; a < 3; a++) u[3*index0 + a] = open->u0[a];
+	  }
+	  else {
+	    rho[index0] = open->rho0;
+	    for (int a = 0; a < 3; a++) u[3*index0 + a] = u[3*index1 + a];
+	  }
+	}
+      }
+    }
+    /* impose */
+    for (int ic = lo[0]; ic <= hi[0]; ic++) {
+      for (int jc = lo[1]; jc <= hi[1]; jc++) {
+	for (int kc = lo[2]; kc <= hi[2]; kc++) {
+	  for (int p = 1; p < nvel; p++) {
+	    int c[3] = {ic + model->cv[p][0], jc + model->cv[p][1], kc + model->cv[p][2]};
+	    const int q = nvel - p;                 /* the reverse: into the fluid */
+	    long index;
+	    double udotc = 0.0, sdotq = 0.0;
+	    if (model->cv[p][id] != dir) continue;
+	    if (c[id1] < 1 || c[id1] > box->nlocal[id1]) continue;
+	    if (c[id2] < 1 || c[id2] > box->nlocal[id2]) continue;
+	    index = orc_index(box, c[0], c[1], c[2]);
+	    for (int ia = 0; ia < 3; ia++) {
+	      udotc += u[3*index + ia]*model->cv[q][ia];
+	      for (int ib = 0; ib < 3; ib++) {
+		const double d_ab = (ia == ib);
+		const double s_ab = model->cv[q][ia]*model->cv[q][ib] - cs2*d_ab;
+		sdotq += s_ab*u[3*index + ia]*u[3*index + ib];
+	      }
+	    }
+	    f[(index*ndist + 0)*nvel + q] = rho[index]*model->wv[q]*(1.0 + rcs2*udotc + 0.5*rcs2*rcs2*sdotq);
+	  }
+	}
+      }
+    }
+  }
+  return 0;
+}

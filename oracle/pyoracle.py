@@ -63,6 +63,10 @@ class Wall(ctypes.Structure):
     ]
 
 
+class OpenBC(ctypes.Structure):
+    _fields_ = [("id", ctypes.c_int), ("u0", ctypes.c_double * 3), ("rho0", ctypes.c_double)]
+
+
 class LeesEdwards(ctypes.Structure):
     _fields_ = [
         ("nplanes", ctypes.c_int),
@@ -235,6 +239,23 @@ class Oracle:
         assert self.L.orc_gradient_select(int(npt)) == 0
 
     # -- Lees-Edwards planes (oracle/lb_oracle_le.c) --------------------------------
+    # -- open boundaries (inflow / outflow "rhou") ------------------------------------
+    def open_bc(self, flow_dir, u0=(0.0, 0.0, 0.0), rho0=1.0):
+        o = OpenBC()
+        o.id, o.rho0 = int(flow_dir), float(rho0)
+        o.u0[:] = u0
+        return o
+
+    def open_attach(self, o):
+        self._open = o
+        self.L.orc_open_attach(None if o is None else ctypes.byref(o))
+
+    def open_apply(self, o, rho, u, f):
+        self.L.orc_open_apply.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
+                                          ctypes.c_void_p, c_double_p, c_double_p, c_double_p]
+        assert self.L.orc_open_apply(ctypes.byref(self.model), ctypes.byref(self.box), self.ndist,
+                                     ctypes.byref(o), _p(rho), _p(u), _p(f)) == 0
+
     def le(self, nplanes, uy, oscillatory=0, period=0, nt0=0, t_current=0, t_start=0):
         le = LeesEdwards()
         le.nplanes, le.uy, le.oscillatory = nplanes, uy, oscillatory

@@ -42,7 +42,9 @@ CASES = ["d3q19-short/serial-dist-3du", "d3q19-short/serial-dist-1dp",
          "d3q19/pmpi08-le2d-fd1", "d3q19/pmpi08-le2d-lb1", "d3q19/pmpi08-le3d-fd1",
          "d3q19/pmpi08-le3d-lb1",
          # a drop relaxing for 20 steps (the run the reference's i/o tests restart from)
-         "d3q19-io/iodrop-mpi1-io1"]
+         "d3q19-io/iodrop-mpi1-io1",
+         # open boundaries (inflow / outflow "rhou") along the one direction without walls
+         "d3q19-short/serial-open-ru1", "d3q19-short/serial-open-ru2"]
 NVEL = {"d3q19-short": 19, "d3q19": 19, "d2q9": 9, "d3q19-io": 19}
 
 

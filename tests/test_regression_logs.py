@@ -83,6 +83,18 @@ def initial_state(inp, cv, wv):
     return nt, np.ascontiguousarray(f.reshape(-1, ndist, len(wv)))
 
 
+def open_options(inp):
+    """lb_bc_open yes with inflow / outflow of type rhou (src/lb_bc_open_rt.c:48-170): the
+    flow runs along the one direction without walls. (flow direction, u0, rho0) or None."""
+    if inp.get("lb_bc_open", "no") != "yes":
+        return None
+    assert inp["lb_bc_inflow_type"] == "rhou" and inp["lb_bc_outflow_type"] == "rhou"
+    wall = [int(x) for x in inp["boundary_walls"].split("_")]
+    assert sum(wall) == 2
+    u0 = tuple(float(x) for x in inp.get("lb_bc_inflow_rhou_u0", "0_0_0").split("_"))
+    return wall.index(0), u0, float(inp.get("lb_bc_outflow_rhou_rho0", 1.0))
+
+
 def le_options(inp):
     """N_LE_plane, LE_plane_vel (src/leesedwards_rt.c): steady shear, or None."""
     if int(inp.get("N_LE_plane", 0)) == 0:
@@ -331,7 +343,8 @@ def viscosities(inp):
 # source against the oracle) after the round's GPU allocation was spent: the device run
 # of these cases is opt-in until it has been seen to pass on a B200 once.
 UNVERIFIED_ON_GPU = ({"serial-le2d-lb1", "serial-le2d-fd1", "pmpi08-le2d-fd1", "pmpi08-le2d-lb1",
-                      "pmpi08-le3d-fd1", "pmpi08-le3d-lb1", "iodrop-mpi1-io1"}
+                      "pmpi08-le3d-fd1", "pmpi08-le3d-lb1", "iodrop-mpi1-io1",
+                      "serial-open-ru1", "serial-open-ru2"}
                      | {"serial-le3d-st%d" % k for k in range(1, 9)})
 NOT_ON_DEVICE = set()
 # The reference prints compensated sums (src/util_sum.c, src/stats_distribution.c:201-265);
@@ -375,6 +388,8 @@ def test_oracle_reproduces_reference_log(case):
     orc.wall_attach(wall)
     if le_options(rec["input"]):
         orc.le_attach(orc.le(**le_options(rec["input"])))
+    if open_options(rec["input"]):
+        orc.open_attach(orc.open_bc(*open_options(rec["input"])))
     if fd_route(rec):
         phi.reshape(orc.nall)[1:-1, 1:-1, 1:-1] = initial_phi(rec["input"], nt)
         orc.ch_attach(orc.ch(*fd_options(rec["input"])))
@@ -389,6 +404,7 @@ def test_oracle_reproduces_reference_log(case):
         orc.ch_attach(None)
         orc.visc_attach(None)
         orc.le_attach(None)
+        orc.open_attach(None)
     m = orc.interior_mask()
     sums = orc.stats(f)
     if case in LONG or case in HALFWAY:
