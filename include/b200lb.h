@@ -177,6 +177,17 @@ int  b200lb_wall_commit(b200lb_t * h, const int isboundary[3], const double ubot
 int  b200lb_wall_slip_set(b200lb_t * h, const double sbot[3], const double stop[3],
                           int force_active);                           /* wall_slip src/wall.c:284 */
 int  b200lb_wall_bbl(b200lb_t * h);                                    /* wall_bbl src/wall.c:960 */
+/* Open boundaries for the fluid ("lb_bc_open yes", lb_bc_inflow_type / lb_bc_outflow_type
+ * rhou: lb_bc_inflow_rhou_create / lb_bc_outflow_rhou_create, chosen in
+ * src/lb_bc_open_rt.c:48-170): flow along the one direction without walls (commit the walls
+ * first), inlet at its low end with velocity u0 and the density of the fluid behind it,
+ * outlet at the high end with density rho0 and the velocity of the fluid in front of it.
+ * b200lb_open_bc_apply replaces inflow/outflow->func->update + ->impose between lb_halo
+ * and lb_propagation (src/ludwig.c:820-831; host loops over link lists in the reference):
+ * the populations the propagation will carry in from the two halo layers are set to
+ * equilibrium. flow_dir < 0 switches them off. b200lb_step applies them itself. */
+int  b200lb_open_bc_commit(b200lb_t * h, int flow_dir, const double u0[3], double rho0);
+int  b200lb_open_bc_apply(b200lb_t * h);
 int  b200lb_wall_momentum(b200lb_t * h, double f[3]);                  /* wall_momentum src/wall.c:1299 */
 int  b200lb_wall_momentum_add(b200lb_t * h, const double f[3]);        /* wall_momentum_add src/wall.c:1279 */
 

@@ -17,6 +17,7 @@
 #include "../../include/b200lb.h"
 #include "common_kernels.cuh"
 #include "le_field_kernels.cuh"
+#include "open_bc_kernels.cuh"
 #include "model_ops.cuh"
 #include "ch_kernels.cuh"
 
@@ -125,6 +126,9 @@ struct b200lb_s {
   double le_field_t;         // physics_control_time at which the order parameter is displaced
   double * le_phibuf;        // [2 x local planes][s0] buffer planes of phi (field_leesedwards)
   double * le_chbuf;         // finite-difference order parameter with planes: buffers and scratch (ch_le_run)
+  bool open_on;              // open boundaries for the fluid (b200lb_open_bc_commit)
+  int open_id;               // flow direction
+  double open_u0[3], open_rho0;
   int last_grad_npt;         // stencil of the last field_grad_compute (7 or 27)
   double * le_buf;           // crossing populations of the plane sites
   // the order parameter as a finite-difference field ("free_energy symmetric":
@@ -965,6 +969,63 @@ extern "C" int b200lb_wall_slip_set(b200lb_t * h, const double sbot[3], const do
 // post-collision populations of the sites on the wall faces; the reversed populations
 // themselves are not written into the wall layer: the propagation that follows (fused
 // into the next collision, or on its own) takes them from the site they left.
+// ---------------------------------------------------------------------------
+// open boundaries for the fluid: inflow / outflow "rhou" (open_bc_kernels.cuh)
+// ---------------------------------------------------------------------------
+
+extern "C" int b200lb_open_bc_commit(b200lb_t * h, int flow_dir, const double u0[3], double rho0) {
+  if (!h) return fail("null handle");
+  if (flow_dir < 0) { h->open_on = false; return 0; }
+  if (flow_dir > 2 || !u0) return fail("lb_bc_open: flow direction 0, 1 or 2 and an inflow velocity");
+  if (h->desc.ndim != 3) return fail("lb_bc_open: three-dimensional models on this path");
+  if (h->desc.ndist != 1) return fail("lb_bc_open: the single-fluid distribution (the order parameter has its own open boundaries, src/phi_bc_open.h: not on this path)");
+  if (h->desc.periodic[flow_dir]) return fail("lb_bc_open: the flow direction %d is periodic", flow_dir);
+  for (int a = 0; a < 3; a++) {
+    if (a == flow_dir) continue;
+    // src/lb_bc_open_rt.c:65-67: the flow runs along the one direction without walls
+    if (!h->wall_on || !h->wall_is[a]) return fail("lb_bc_open: walls in the two directions across the flow (boundary_walls) come first");
+    if (h->desc.cartsz[a] > 1) return fail("lb_bc_open: a decomposition across the flow (src/lb_bc_inflow_rhou.c:293, the exchange of the inlet's rho, u) is not on this path");
+  }
+  if (h->wall_on && h->wall_is[flow_dir]) return fail("lb_bc_open: a wall in the flow direction");
+  if (!(rho0 > 0.0)) return fail("lb_bc_outflow_rhou_rho0 must be positive");
+  h->open_on = true;
+  h->open_id = flow_dir;
+  for (int a = 0; a < 3; a++) h->open_u0[a] = u0[a];
+  h->open_rho0 = rho0;
+  return 0;
+}
+
+// inflow->update + impose, outflow->update + impose: src/ludwig.c:820-831
+extern "C" int b200lb_open_bc_apply(b200lb_t * h) {
+  if (!h) return fail("null handle");
+  if (!h->open_on) return 0;
+  if (h->prop_pending) return fail("lb_bc_open: called after lb_propagation (it belongs between lb_halo and lb_propagation)");
+  if (ensure_hydro(h)) return -1;                  // rho, u of the collision just done
+  if (need_hydro(h)) return -1;
+  if (join_comm(h)) return -1;
+  OpenTab T;
+  memset(&T, 0, sizeof(T));
+  T.L = h->L;
+  T.nvel = h->ops->nvel;
+  T.id = h->open_id;
+  T.da = (T.id == 0) ? 1 : 0;
+  T.db = (T.id == 2) ? 1 : 2;
+  T.has_in = (h->desc.cartcoords[T.id] == 0);
+  T.has_out = (h->desc.cartcoords[T.id] == h->desc.cartsz[T.id] - 1);
+  for (int a = 0; a < 3; a++) { T.lo[a] = 0; T.hi[a] = h->L.n[a] - 1; T.u0[a] = h->open_u0[a]; }
+  T.rho0 = h->open_rho0;
+  for (int p = 0; p < T.nvel; p++) {
+    for (int a = 0; a < 3; a++) T.cv[p][a] = (signed char) h->ops->cv[p][a];
+    T.wv[p] = h->ops->wv[p];
+  }
+  dim3 block(128, 1, 1);
+  dim3 grid((h->L.n[T.db] + 127)/128, h->L.n[T.da], 2);
+  open_bc_kernel<<<grid, block, 0, h->s_main>>>(T, h->rho, h->u, h->lat[h->cur]);
+  CU(cudaGetLastError());
+  h->launches++;
+  return 0;
+}
+
 extern "C" int b200lb_wall_bbl(b200lb_t * h) {
   if (!h) return fail("null handle");
   if (!h->wall_on) return 0;                       // wall->nlink == 0: nothing to do
@@ -1934,6 +1995,7 @@ extern "C" int b200lb_step(b200lb_t * h, int nsteps) {
     if (h->prop_pending) return fail("internal: propagation pending after collide");
     if (h->le_nlocal) { if (b200lb_le_apply(h, 1.0*h->le_step)) return -1; }   // src/ludwig.c:810
     if (lattice_halo(h, h->opt_halo)) return -1;
+    if (h->open_on) { if (b200lb_open_bc_apply(h)) return -1; } // src/ludwig.c:820-831
     if (h->wall_on) { if (b200lb_wall_bbl(h)) return -1; }      // src/ludwig.c:837-842
     if (b200lb_propagate(h)) return -1;
   }

@@ -38,7 +38,7 @@ ABI_SYMBOLS = [
     "b200lb_noise_state_download",
     "b200lb_wall_commit", "b200lb_wall_slip_set", "b200lb_wall_bbl", "b200lb_wall_momentum", "b200lb_wall_momentum_add",
     "b200lb_le_commit", "b200lb_le_apply", "b200lb_le_plane_location", "b200lb_le_time_set",
-    "b200lb_le_field_time_set",
+    "b200lb_le_field_time_set", "b200lb_open_bc_commit", "b200lb_open_bc_apply",
     "b200lb_ch_create", "b200lb_ch_grad_mu_set", "b200lb_phi_force", "b200lb_cahn_hilliard",
     "b200lb_hydro_u_halo", "b200lb_visc_arrhenius_commit", "b200lb_visc_update", "b200lb_visc_model_set",
     "b200lb_field_stats", "b200lb_io_record_doubles", "b200lb_io_pack", "b200lb_io_unpack",
@@ -126,6 +126,8 @@ def load():
     L.b200lb_le_plane_location.argtypes = [vp, ctypes.c_int]
     L.b200lb_le_time_set.argtypes = [vp, ctypes.c_int]
     L.b200lb_le_field_time_set.argtypes = [vp, ctypes.c_double]
+    L.b200lb_open_bc_commit.argtypes = [vp, ctypes.c_int, ctypes.POINTER(ctypes.c_double), ctypes.c_double]
+    L.b200lb_open_bc_apply.argtypes = [vp]
     L.b200lb_ch_create.argtypes = [vp, ctypes.c_int, ctypes.c_int]
     L.b200lb_ch_grad_mu_set.argtypes = [vp, vp]
     for name in ("b200lb_phi_force", "b200lb_cahn_hilliard", "b200lb_hydro_u_halo"):
@@ -366,6 +368,14 @@ class Lattice:
     def wall_slip_set(self, sbot, stop, force_active=0):
         self._ck(self.L.b200lb_wall_slip_set(self.h, (ctypes.c_double * 3)(*sbot),
                                              (ctypes.c_double * 3)(*stop), int(force_active)))
+
+    def open_bc_commit(self, flow_dir, u0=(0.0, 0.0, 0.0), rho0=1.0):
+        """lb_bc_open: inflow (rhou, velocity u0) and outflow (rhou, density rho0) along flow_dir."""
+        self._ck(self.L.b200lb_open_bc_commit(self.h, int(flow_dir), (ctypes.c_double * 3)(*u0), float(rho0)))
+
+    def open_bc_apply(self):
+        """inflow/outflow update + impose: between lb_halo() and lb_propagation()."""
+        self._ck(self.L.b200lb_open_bc_apply(self.h))
 
     def wall_bbl(self):
         self._ck(self.L.b200lb_wall_bbl(self.h))

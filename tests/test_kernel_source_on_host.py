@@ -12,6 +12,7 @@ and it is what checked the kernels written after a round's GPU allocation was sp
   le_phi_buffer / le_grad_fix       vs the oracle's field_leesedwards + stencils (bit for bit)
   ch_kernel + buffer kernels + ch_le_pass_a/_b (finite-difference order parameter across
   Lees-Edwards planes)              vs the oracle (phi bit for bit, force 1e-15)
+  open_bc_kernel (inflow/outflow)   vs the oracle (bit for bit)
 """
 
 import os
@@ -62,3 +63,8 @@ def test_finite_difference_order_parameter_across_planes_matches_oracle():
     assert "exact build: order parameter identical to the oracle, force within 1e-15" in out
     assert "fast build: within a few ulp of the oracle" in out
     assert "DIFF" not in out
+
+
+def test_open_boundary_kernel_matches_oracle():
+    out = run_tool("check_open_bc_on_host.py")
+    assert "all identical to the oracle" in out and "DIFF" not in out

@@ -453,6 +453,8 @@ def test_cuda_reproduces_reference_log(case, hydro_write):
         sbot, stop, active = wall_slip(rec["input"])
         if active:
             lat.wall_slip_set(sbot, stop, 1)
+    if open_options(rec["input"]):
+        lat.open_bc_commit(*open_options(rec["input"]))
     if ndist == 2:
         lat.field_grad_set(gradient_points(rec))
     if le_options(rec["input"]):
