@@ -137,6 +137,11 @@ int orc_wall_nlink(const orc_model_t * model, const orc_box_t * box,
 int orc_wall_bbl(const orc_model_t * model, const orc_box_t * box,
 		 const orc_param_t * prm, int ndist, orc_wall_t * wall, double * f);
 
+/* grad_3d_27pt_solid_d2 next to flat walls with neutral wetting (lb_oracle_wall.c);
+ * orc_gradient_select(28) makes orc_step use it (fd_gradient_calculation 3d_27pt_solid) */
+int orc_grad_27pt_solid(const orc_box_t * box, const orc_wall_t * wall, const double * phi,
+			double * grad, double * delsq);
+
 /* Open boundaries for the fluid, inflow/outflow of type "rhou" along the one direction
  * without walls (lb_oracle_wall.c; src/lb_bc_inflow_rhou.c, src/lb_bc_outflow_rhou.c).
  * While attached, orc_step applies them after the halo swap (src/ludwig.c:820-831). */

@@ -265,7 +265,7 @@ int orc_grad_7pt(const orc_box_t * box, const double * phi,
 static int grad_select_npt = 7;
 
 int orc_gradient_select(int npt) {
-  if (npt != 7 && npt != 27) return -1;
+  if (npt != 7 && npt != 27 && npt != 28) return -1;      /* 28: the 27-point stencil next to walls */
   grad_select_npt = npt;
   return 0;
 }
@@ -407,6 +407,7 @@ int orc_step(const orc_model_t * model, const orc_box_t * box,
 	const double t = 1.0*(le->t_start + le->t_current - 1.0);
 	if (orc_le_field_grad(box, le, t, grad_select_npt, phi, grad, delsq)) return -1;
       }
+      else if (grad_select_npt == 28) orc_grad_27pt_solid(box, orc_wall_attached(), phi, grad, delsq);
       else if (grad_select_npt == 27) orc_grad_27pt(box, phi, grad, delsq);
       else orc_grad_7pt(box, phi, grad, delsq);
     }

@@ -257,3 +257,64 @@ int orc_open_apply(const orc_model_t * model, const orc_box_t * box, int ndist,
   }
   return 0;
 }
+
+/* ---------------------------------------------------------------------------
+ * grad_3d_27pt_solid_d2 (src/gradient_3d_27pt_solid.c:131-325) next to flat walls, neutral
+ * wetting (C = H = 0: no "wetting" keys): differences to the 26 neighbours, those inside a
+ * wall contributing the boundary gradient -(C phi_b + H)/kappa = -0; delsq = (1/9) sum,
+ * grad_a = (1/18) sum c_a, both over the links in the order of the reference's table.
+ * A site is solid when a coordinate along a wall direction lies outside 1 .. n.
+ * --------------------------------------------------------------------------- */
+
+int orc_grad_27pt_solid(const orc_box_t * box, const orc_wall_t * wall, const double * phi,
+			double * grad, double * delsq) {
+  const double r9 = (1.0/9.0), r18 = (1.0/18.0);
+  const double c = 0.0, h = 0.0, rkappa = 1.0;     /* neutral: the value of 1/kappa drops out */
+
+  for (int ic = 1; ic <= box->nlocal[0]; ic++) {
+    for (int jc = 1; jc <= box->nlocal[1]; jc++) {
+      for (int kc = 1; kc <= box->nlocal[2]; kc++) {
+	const long index = orc_index(box, ic, jc, kc);
+	double gradt[27], gradn[3] = {0.0, 0.0, 0.0}, count[3] = {0.0, 0.0, 0.0};
+	int solid[27], cv[27][3];
+	double dphi;
+	int p = 1;
+	for (int a = -1; a <= 1; a++) for (int b = -1; b <= 1; b++) for (int cc = -1; cc <= 1; cc++) {
+	  if (a == 0 && b == 0 && cc == 0) continue;
+	  cv[p][0] = a; cv[p][1] = b; cv[p][2] = cc;
+	  p++;
+	}
+	for (p = 1; p < 27; p++) {
+	  const int n[3] = {ic + cv[p][0], jc + cv[p][1], kc + cv[p][2]};
+	  solid[p] = 0;
+	  for (int d = 0; d < 3; d++) {
+	    if (wall && wall->isboundary[d] && (n[d] < 1 || n[d] > box->nlocal[d])) solid[p] = 1;
+	  }
+	  if (solid[p]) continue;
+	  dphi = phi[orc_index(box, n[0], n[1], n[2])] - phi[index];
+	  gradt[p] = dphi;
+	  for (int ia = 0; ia < 3; ia++) {
+	    gradn[ia] += cv[p][ia]*dphi;
+	    count[ia] += cv[p][ia]*cv[p][ia];
+	  }
+	}
+	for (int ia = 0; ia < 3; ia++) if (count[ia] > 0.0) gradn[ia] /= count[ia];
+	for (p = 1; p < 27; p++) {
+	  if (solid[p]) {
+	    const double phi_b = phi[index] + 0.5*(cv[p][0]*gradn[0] + cv[p][1]*gradn[1] + cv[p][2]*gradn[2]);
+	    gradt[p] = -(c*phi_b + h)*rkappa;
+	  }
+	}
+	dphi = 0.0;
+	for (int ia = 0; ia < 3; ia++) gradn[ia] = 0.0;
+	for (p = 1; p < 27; p++) {
+	  dphi += gradt[p];
+	  for (int ia = 0; ia < 3; ia++) gradn[ia] += gradt[p]*cv[p][ia];
+	}
+	delsq[index] = r9*dphi;
+	for (int ia = 0; ia < 3; ia++) grad[3*index + ia] = r18*gradn[ia];
+      }
+    }
+  }
+  return 0;
+}

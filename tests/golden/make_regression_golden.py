@@ -44,7 +44,9 @@ CASES = ["d3q19-short/serial-dist-3du", "d3q19-short/serial-dist-1dp",
          # a drop relaxing for 20 steps (the run the reference's i/o tests restart from)
          "d3q19-io/iodrop-mpi1-io1",
          # open boundaries (inflow / outflow "rhou") along the one direction without walls
-         "d3q19-short/serial-open-ru1", "d3q19-short/serial-open-ru2"]
+         "d3q19-short/serial-open-ru1", "d3q19-short/serial-open-ru2",
+         # the binary fluid in a closed box (walls on all sides, 27-point stencil next to solid)
+         "d3q19-short/serial-spin-lb2"]
 NVEL = {"d3q19-short": 19, "d3q19": 19, "d2q9": 9, "d3q19-io": 19}
 
 
@@ -72,6 +74,8 @@ def main():
                 rec["rho"] = floats(l)                 # total mean variance min max
             if l.startswith("[phi]"):
                 rec["phi"] = floats(l)                 # total mean variance min max
+            if l.startswith("[fe]"):
+                rec["fe"] = floats(l)                  # with walls: f, v, f/v, f_s1, f_s2
             if l.startswith("[fed]"):
                 rec["fed"] = floats(l)                 # total/volume, fluid mean
             if l.startswith("[total   ]"):
