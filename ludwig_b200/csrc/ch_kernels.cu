@@ -587,8 +587,8 @@ static cudaError_t le_launch(const ChParams & P, const ChLeParams & Q, bool do_f
 
 cudaError_t CH_LE_LAUNCH(const ChParams & P, const ChLeParams & Q, bool do_force, bool do_update, cudaStream_t st) {
   if (Q.nplanes < 1 || Q.nplanes > CH_LE_MAXPLANE) return cudaErrorInvalidValue;
-  if (P.accumulate) return cudaErrorInvalidValue;
   if (do_force && P.method == CH_FORCE_NONE) do_force = false;
+  if (do_force && P.accumulate) return cudaErrorInvalidValue;     // pass B writes fconst + f
   switch (do_update ? P.order : 0) {
   case 0: return do_force ? le_launch<0>(P, Q, true, st) : cudaSuccess;
   case 1: return le_launch<1>(P, Q, do_force, st);
