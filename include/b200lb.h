@@ -125,6 +125,11 @@ long b200lb_nsite(const b200lb_t * h);                          /* host nsite = 
  *                      collision that streams in the same pass reads that instead of
  *                      pulling g a second time (same bits, 104 B/site less traffic;
  *                      default 1)
+ *   "binary_walls" 0/1 allow flat walls with the binary fluid (ndist = 2): the bounce-back
+ *                      of both distributions is folded into a propagation of its own,
+ *                      the collision runs on the streamed lattice, the gradient is
+ *                      b200lb_grad27_solid ("gradient" = 28). Default 0 until that path
+ *                      has run on a GPU: b200lb_wall_commit refuses ndist = 2 otherwise
  *   "le_fd"       0/1  allow Lees-Edwards planes together with the finite-difference order
  *                      parameter (buffer-region gradient, flux form of the force with its
  *                      plane correction, phi_ch_le_fix_fluxes: ch_le_pass_a/_b). Default 0
@@ -159,6 +164,7 @@ int  b200lb_phi_from_g(b200lb_t * h);                        /* phi_lb_to_field 
 int  b200lb_phi_halo(b200lb_t * h);                          /* field_halo(phi) src/field.c:434 */
 int  b200lb_grad7(b200lb_t * h);                             /* grad_3d_7pt_fluid_d2 src/gradient_3d_7pt_fluid.c:75 */
 int  b200lb_grad27(b200lb_t * h);                            /* grad_3d_27pt_fluid_d2 src/gradient_3d_27pt_fluid.c:75 */
+int  b200lb_grad27_solid(b200lb_t * h);                                /* grad_3d_27pt_solid_d2 src/gradient_3d_27pt_solid.c:131: next to flat walls, neutral wetting */
 
 /* Flat no-slip walls ("boundary_walls", "boundary_speed_bottom/_top"; src/wall.c,
  * src/wall_rt.c:40-120). A wall in a non-periodic direction occupies the halo layer at

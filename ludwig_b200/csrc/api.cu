@@ -18,6 +18,7 @@
 #include "common_kernels.cuh"
 #include "le_field_kernels.cuh"
 #include "open_bc_kernels.cuh"
+#include "solid_grad_kernels.cuh"
 #include "model_ops.cuh"
 #include "ch_kernels.cuh"
 
@@ -174,7 +175,7 @@ struct b200lb_s {
   bool ghost;
 
   // options
-  int opt_fused, opt_halo, opt_hydro_write, opt_vec, opt_block, opt_halo_lazy, opt_overlap, opt_direct, opt_diag, opt_loopback, opt_grad_lazy, opt_p2p, opt_gradient, opt_ch_fuse, opt_ch_planes, opt_ch_exact, opt_g_moment, opt_le_fd;
+  int opt_fused, opt_halo, opt_hydro_write, opt_vec, opt_block, opt_halo_lazy, opt_overlap, opt_direct, opt_diag, opt_loopback, opt_grad_lazy, opt_p2p, opt_gradient, opt_ch_fuse, opt_ch_planes, opt_ch_exact, opt_g_moment, opt_le_fd, opt_binary_walls;
 
   cudaStream_t s_main, s_x[2];
   cudaStream_t s_comm;       // halo exchange of decomposed directions (overlaps the interior sweep)
@@ -497,6 +498,7 @@ static int create_impl(const b200lb_desc_t * desc, b200lb_s * h, const ModelOps 
   h->opt_ch_exact = 0;
   h->opt_g_moment = 1;
   h->opt_le_fd = 0;
+  h->opt_binary_walls = 0;
 
   b200lb_param_t p0;
   memset(&p0, 0, sizeof(p0));
@@ -574,14 +576,15 @@ extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
   }
   if (!strcmp(name, "g_moment")) { h->opt_g_moment = (v != 0); h->jphi_valid = false; return 0; }
   if (!strcmp(name, "le_fd")) { h->opt_le_fd = (v != 0); return 0; }
+  if (!strcmp(name, "binary_walls")) { h->opt_binary_walls = (v != 0); return 0; }
   if (!strcmp(name, "ch_planes")) {
     if (v < 1 || v > 4096) return fail("ch_planes: x-planes marched by one block of the order-parameter kernel, 1..4096");
     h->opt_ch_planes = (int) v;
     return 0;
   }
   if (!strcmp(name, "gradient")) {
-    if (v != 7 && v != 27) return fail("gradient: 7 or 27 points");
-    if (v == 27 && h->desc.ndim != 3) return fail("the 27-point gradient is three-dimensional");
+    if (v != 7 && v != 27 && v != 28) return fail("gradient: 7 or 27 points (28: the 27-point stencil next to walls, 3d_27pt_solid)");
+    if (v >= 27 && h->desc.ndim != 3) return fail("the 27-point gradient is three-dimensional");
     h->opt_gradient = (int) v;
     return 0;
   }
@@ -628,6 +631,7 @@ extern "C" long b200lb_get_option(const b200lb_t * h, const char * name) {
   if (!strcmp(name, "ch_exact")) return h->opt_ch_exact;
   if (!strcmp(name, "g_moment")) return h->opt_g_moment;
   if (!strcmp(name, "le_fd")) return h->opt_le_fd;
+  if (!strcmp(name, "binary_walls")) return h->opt_binary_walls;
   if (!strcmp(name, "jphi_valid")) return h->jphi_valid;
   if (!strcmp(name, "p2p")) return h->opt_p2p;
   if (!strcmp(name, "p2p_ready")) return h->p2p_ready;
@@ -800,7 +804,7 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
   // of the rank) after this sweep: nothing is pushed to the neighbours ahead of that
   const bool push = collide && h->p2p_ready && h->opt_p2p && h->le_nplanes == 0;
   const bool walls = pull && h->prop_wall && h->wall_on;
-  if (walls && a.binary) return fail("walls with the binary fluid need the solid gradient stencils: not on this path");
+  if (walls && a.binary && collide) return fail("internal: walls with the binary fluid are folded into the propagation, not into the collision");
   const int nbox = walls ? wall_boxes(h, a.P, lo, hi, iswall) : (push ? 1 : split_boxes(h, lo, hi));
   const int vec0 = a.vec;
   h->bnd_valid = false;
@@ -877,6 +881,7 @@ static int materialise(b200lb_s * h) {
 extern "C" int b200lb_collide(b200lb_t * h) {
   if (!h) return fail("null handle");
   if (resolve_ch_force(h)) return -1;     // phi_force_calculation without a Cahn-Hilliard update after it
+  if (h->prop_pending && h->prop_wall && h->desc.ndist == 2) { if (materialise(h)) return -1; }
   if (h->prop_pending) {
     // stream-then-collide in one pass over the lattice
     if (run_sweep(h, true, true, h->lat[h->cur], h->lat[1 - h->cur])) return -1;
@@ -912,7 +917,7 @@ extern "C" int b200lb_propagate(b200lb_t * h) {
 extern "C" int b200lb_wall_commit(b200lb_t * h, const int isboundary[3], const double ubot[3],
 				  const double utop[3]) {
   if (!h || !isboundary) return fail("null argument");
-  if (h->desc.ndist != 1) return fail("walls with the binary fluid need the solid gradient stencils: not on this path");
+  if (h->desc.ndist != 1 && !h->opt_binary_walls) return fail("walls with the binary fluid need the solid gradient stencils: behind option binary_walls until that path has run on a GPU");
   bool any = false;
   for (int a = 0; a < 3; a++) {
     if (!isboundary[a]) continue;
@@ -1590,6 +1595,36 @@ static int run_grad27(b200lb_s * h) {
   return 0;
 }
 
+// grad_3d_27pt_solid_d2 (solid_grad_kernels.cuh): the binary fluid between flat walls
+static int run_grad27_solid(b200lb_s * h) {
+  const Layout & L = h->L;
+  if (h->desc.ndim != 3) return fail("the 27-point gradient is three-dimensional (ndim = %d)", h->desc.ndim);
+  if (h->le_nlocal) return fail("3d_27pt_solid with Lees-Edwards planes is not on this path");
+  if (need_planes(h, &h->grad, 3) || need_planes(h, &h->delsq, 1)) return -1;
+  KParams P;
+  site_kparams(h, P);
+  SolidGradTab T;
+  memset(&T, 0, sizeof(T));
+  T.L = L;
+  for (int d = 0; d < 3; d++) { T.wrap[d] = h->selfper[d]; T.wall_lo[d] = P.wall_lo[d]; T.wall_hi[d] = P.wall_hi[d]; }
+  dim3 block(128, 1, 1);
+  dim3 grid((L.n[2] + 127)/128, L.n[1], L.n[0]);
+  grad27_solid_kernel<<<grid, block, 0, h->s_main>>>(T, h->phi, h->grad, h->delsq);
+  CU(cudaGetLastError());
+  h->launches++;
+  h->grad_state = 0;
+  h->ch_grad_valid = true; h->ch_halo_done = false;
+  h->last_grad_npt = 28;
+  return 0;
+}
+
+extern "C" int b200lb_grad27_solid(b200lb_t * h) {
+  if (!h) return fail("null handle");
+  if (!h->phi) return fail("no order parameter (ndist = 1)");
+  if (h->ch_on) return fail("3d_27pt_solid for the finite-difference order parameter (walls there need the no-flux masks of src/advection_bcs.c) is not on this path");
+  return run_grad27_solid(h);
+}
+
 extern "C" int b200lb_phi_halo(b200lb_t * h) {
   if (!h) return fail("null handle");
   if (!h->phi) return fail("no order parameter (ndist = 1)");
@@ -1615,6 +1650,8 @@ static int flush_phi_halo(b200lb_s * h) {
 extern "C" int b200lb_phi_from_g(b200lb_t * h) {
   if (!h) return fail("null handle");
   if (!h->phi || h->desc.ndist != 2) return fail("no order parameter distribution (ndist = 1)");
+  // the bounce-back of a pending propagation is part of what phi sums: stream first
+  if (h->prop_pending && h->prop_wall) { if (materialise(h)) return -1; }
   if (join_comm(h)) return -1;
   const double * g = h->lat[h->cur] + (i64) h->desc.nvel*h->L.nsd;
   // The collision that follows, if it streams in the same pass, would pull the same g
@@ -1978,7 +2015,8 @@ extern "C" int b200lb_step(b200lb_t * h, int nsteps) {
     if (h->desc.ndist == 2) {
       if (b200lb_phi_from_g(h)) return -1;
       if (b200lb_phi_halo(h)) return -1;
-      if (h->opt_gradient == 27) { if (b200lb_grad27(h)) return -1; }
+      if (h->opt_gradient == 28) { if (b200lb_grad27_solid(h)) return -1; }
+      else if (h->opt_gradient == 27) { if (b200lb_grad27(h)) return -1; }
       else if (b200lb_grad7(h)) return -1;
     }
     if (h->ch_on) {                                 // src/ludwig.c:558-575, 727-768

@@ -15,8 +15,9 @@ typedef B200LB_MODEL MODEL;
 
 template <int VEC, bool PULL, bool COLLIDE, bool BINARY, int GM, bool WALL = false>
 static cudaError_t launch_one(SweepArgs & a) {
-  // walls are folded into the pull of the single-fluid kernels only
-  if constexpr (!WALL && PULL && !BINARY && VEC == 1) {
+  // walls are folded into the pull of the single-fluid kernels, and into the pure
+  // propagation of the binary fluid (whose collision then runs on the streamed lattice)
+  if constexpr (!WALL && PULL && VEC == 1 && (!BINARY || !COLLIDE)) {
     if (a.wall) return launch_one<VEC, PULL, COLLIDE, BINARY, GM, true>(a);
   }
   else if constexpr (!WALL) {

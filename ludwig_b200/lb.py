@@ -33,7 +33,7 @@ ABI_SYMBOLS = [
     "b200lb_f_upload", "b200lb_f_download", "b200lb_field_upload",
     "b200lb_field_download", "b200lb_set_param", "b200lb_hydro_f_zero",
     "b200lb_hydro_u_zero", "b200lb_hydro_rho0", "b200lb_hydro_correct_momentum", "b200lb_collide", "b200lb_halo", "b200lb_halo_swap",
-    "b200lb_propagate", "b200lb_phi_from_g", "b200lb_phi_halo", "b200lb_grad7", "b200lb_grad27",
+    "b200lb_propagate", "b200lb_phi_from_g", "b200lb_phi_halo", "b200lb_grad7", "b200lb_grad27", "b200lb_grad27_solid",
     "b200lb_noise_init", "b200lb_noise_present_set", "b200lb_noise_state_upload",
     "b200lb_noise_state_download",
     "b200lb_wall_commit", "b200lb_wall_slip_set", "b200lb_wall_bbl", "b200lb_wall_momentum", "b200lb_wall_momentum_add",
@@ -112,7 +112,7 @@ def load():
     for name in ("b200lb_field_upload", "b200lb_field_download"):
         getattr(L, name).argtypes = [vp, ctypes.c_int, vp, ctypes.c_int]
     for name in ("b200lb_destroy", "b200lb_collide", "b200lb_halo", "b200lb_propagate",
-                 "b200lb_phi_from_g", "b200lb_phi_halo", "b200lb_grad7", "b200lb_grad27", "b200lb_sync",
+                 "b200lb_phi_from_g", "b200lb_phi_halo", "b200lb_grad7", "b200lb_grad27", "b200lb_grad27_solid", "b200lb_sync",
                  "b200lb_hydro_correct_momentum", "b200lb_timer_start", "b200lb_nsite", "b200lb_launch_count"):
         getattr(L, name).argtypes = [vp]
     L.b200lb_halo_swap.argtypes = [vp, ctypes.c_int]
@@ -324,7 +324,9 @@ class Lattice:
         self.set_option("gradient", int(npt))
 
     def field_grad_compute(self):
-        if self.get_option("gradient") == 27:
+        if self.get_option("gradient") == 28:
+            self._ck(self.L.b200lb_grad27_solid(self.h))
+        elif self.get_option("gradient") == 27:
             self._ck(self.L.b200lb_grad27(self.h))
         else:
             self._ck(self.L.b200lb_grad7(self.h))

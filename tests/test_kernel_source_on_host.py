@@ -13,6 +13,8 @@ and it is what checked the kernels written after a round's GPU allocation was sp
   ch_kernel + buffer kernels + ch_le_pass_a/_b (finite-difference order parameter across
   Lees-Edwards planes)              vs the oracle (phi bit for bit, force 1e-15)
   open_bc_kernel (inflow/outflow)   vs the oracle (bit for bit)
+  lb_sweep_kernel WALL + BINARY     the propagation of both distributions with bounce-back
+  grad27_solid_kernel               vs the oracle's 27-point stencil next to walls (bit for bit)
 """
 
 import os
@@ -50,7 +52,7 @@ def test_binary_sweep_with_handed_over_flux_is_identical():
     r = subprocess.run([exe], capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-3000:]
     assert "all cases identical" in r.stdout and "FAIL" not in r.stdout
-    assert r.stdout.count("ok  ") == 54
+    assert r.stdout.count("ok  ") == 70          # 54 flux hand-over cases + 16 wall propagations
 
 
 def test_lees_edwards_order_parameter_kernels_match_oracle():
@@ -67,4 +69,9 @@ def test_finite_difference_order_parameter_across_planes_matches_oracle():
 
 def test_open_boundary_kernel_matches_oracle():
     out = run_tool("check_open_bc_on_host.py")
+    assert "all identical to the oracle" in out and "DIFF" not in out
+
+
+def test_solid_gradient_kernel_matches_oracle():
+    out = run_tool("check_solid_grad_on_host.py")
     assert "all identical to the oracle" in out and "DIFF" not in out

@@ -352,10 +352,9 @@ def viscosities(inp):
 # of these cases is opt-in until it has been seen to pass on a B200 once.
 UNVERIFIED_ON_GPU = ({"serial-le2d-lb1", "serial-le2d-fd1", "pmpi08-le2d-fd1", "pmpi08-le2d-lb1",
                       "pmpi08-le3d-fd1", "pmpi08-le3d-lb1", "iodrop-mpi1-io1",
-                      "serial-open-ru1", "serial-open-ru2"}
+                      "serial-open-ru1", "serial-open-ru2", "serial-spin-lb2"}
                      | {"serial-le3d-st%d" % k for k in range(1, 9)})
-# walls with the binary fluid (solid gradient stencil, bounce-back of g): oracle only
-NOT_ON_DEVICE = {"serial-spin-lb2"}
+NOT_ON_DEVICE = set()
 # The reference prints compensated sums (src/util_sum.c, src/stats_distribution.c:201-265);
 # over 6e5 populations a plain sum is 1e-12 away. That shows where a printed digit sits on a
 # rounding boundary: the y momentum of this log is 3.41278045e-04 printed as "%14.7e".
@@ -448,6 +447,8 @@ def test_cuda_reproduces_reference_log(case, hydro_write):
     ndist = f.shape[1]
     periodic = tuple(int(x) for x in rec["input"].get("periodicity", "1_1_1").split("_"))
     lat = lb.Lattice(nvel, nt, ndist=ndist, periodic=periodic)
+    if ndist == 2 and walls(rec):
+        lat.set_option("binary_walls", 1)            # behind an option until run on a GPU
     lat.set_option("hydro_write", hydro_write)
     lat.set_option("halo", lb.HALO_REDUCED)          # lb_halo_openmp_reduced in the input
     if fd_route(rec) and le_options(rec["input"]):

@@ -319,3 +319,66 @@ def test_open_boundaries_vs_oracle(nvel, nlocal, walls, u0, fused, hydro_write):
         lat.lb_propagation()
     assert np.array_equal(lat.lb_memcpy_d2h()[m], fd[m])
     lat.close()
+
+
+# ---------------------------------------------------------------------------
+# the binary fluid between flat walls (option binary_walls): bounce-back of both
+# distributions folded into a propagation of its own, grad27_solid_kernel
+# (tools/check_solid_grad_on_host.py, tools/sweep_emulate.cpp)
+# ---------------------------------------------------------------------------
+
+@pytest.mark.parametrize("nvel,nlocal,walls", [
+    (19, (10, 8, 6), (1, 1, 1)), (19, (8, 6, 40), (0, 1, 1)), (27, (6, 7, 9), (1, 0, 0)),
+    (19, (12, 10, 8), (0, 0, 1))])
+@pytest.mark.parametrize("hydro_write", [1, 0])
+def test_binary_fluid_between_walls_vs_oracle(nvel, nlocal, walls, hydro_write):
+    import ctypes
+    import ludwig_b200 as lb
+    from oracle import pyoracle
+    periodic = tuple(0 if w else 1 for w in walls)
+    orc = pyoracle.Oracle(nvel, nlocal, ndist=2)
+    n = orc.nsite
+    m = orc.interior_mask()
+    prm = pyoracle.make_param(**KW)
+    f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal, ndist=2)
+    lat = lb.Lattice(nvel, nlocal, ndist=2, periodic=periodic)
+    lat.set_option("binary_walls", 1)
+    lat.set_option("hydro_write", hydro_write)
+    lat.set_param(**KW)
+    lat.wall_commit(walls)
+    lat.field_grad_set(28)
+    # the stencil next to the walls, bit for bit
+    lat.lb_memcpy_h2d(f0)
+    lat.phi_lb_to_field()
+    lat.field_halo()
+    lat.field_grad_compute()
+    phi, grad, delsq = np.zeros(n), np.zeros((n, 3)), np.zeros(n)
+    orc.phi_from_g(f0, phi)
+    orc.halo(phi, 1)
+    w = orc.wall(walls)
+    dp = ctypes.POINTER(ctypes.c_double)
+    orc.L.orc_grad_27pt_solid.argtypes = [ctypes.c_void_p, ctypes.c_void_p, dp, dp, dp]
+    assert orc.L.orc_grad_27pt_solid(ctypes.byref(orc.box), ctypes.byref(w), phi.ctypes.data_as(dp),
+                                     grad.ctypes.data_as(dp), delsq.ctypes.data_as(dp)) == 0
+    assert np.array_equal(lat.field_d2h(lb.FIELD_GRAD)[m], grad[m])
+    assert np.array_equal(lat.field_d2h(lb.FIELD_DELSQ)[m], delsq[m])
+    # the time loop
+    nsteps = 8
+    f, fp = f0.copy(), np.zeros_like(f0)
+    rho, u, frc = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
+    orc.gradient_select(28)
+    orc.wall_attach(w)
+    try:
+        orc.step(prm, nsteps, f, fp, rho, u, frc, phi, grad, delsq)
+    finally:
+        orc.gradient_select(7)
+        orc.wall_attach(None)
+    lat.lb_memcpy_h2d(f0)
+    lat.step(nsteps)
+    fd = lat.lb_memcpy_d2h()
+    assert relerr(fd[m], f[m]) < TOL
+    assert np.max(np.abs(lat.field_d2h(lb.FIELD_U)[m] - u[m])) < TOL
+    assert abs(fd[m][:, 0].sum() - f0[m][:, 0].sum()) < 1e-9          # closed to mass ...
+    assert abs(fd[m][:, 1].sum() - f0[m][:, 1].sum()) < 1e-9          # ... and to composition
+    assert np.allclose(lat.wall_momentum(), np.array(w.fnet[:]), rtol=1e-9, atol=1e-12)
+    lat.close()
