@@ -125,6 +125,53 @@ int orc_ch_force_divergence(const orc_box_t * box, const double * pth, double * 
   return 0;
 }
 
+/* a site whose coordinate along a wall direction lies outside 1 .. n is solid */
+static int ch_solid(const orc_box_t * box, const orc_wall_t * wall, int ic, int jc, int kc) {
+  const int c[3] = {ic, jc, kc};
+  if (wall == NULL) return 0;
+  for (int d = 0; d < 3; d++) {
+    if (wall->isboundary[d] && (c[d] < 1 || c[d] > box->nlocal[d])) return 1;
+  }
+  return 0;
+}
+
+/* pth_force_fluid_wall_driver (src/phi_force_colloid.c:227-268): pth_force_map_kernel
+ * (:490-676) takes the stress of the site itself at a face shared with solid, and
+ * pth_force_wall_kernel (:677-790) books what crosses those faces to the wall
+ * (wall_momentum_add). Same face order as without walls. */
+static int ch_force_divergence_walls(const orc_box_t * box, orc_wall_t * wall,
+				     const double * pth, double * force) {
+  const long xs = (long) box->nall[1]*box->nall[2], ys = box->nall[2];
+  const long str[3] = {xs, ys, 1};
+  double fwall[3] = {0.0, 0.0, 0.0};
+  for (int ic = 1; ic <= box->nlocal[0]; ic++) {
+    for (int jc = 1; jc <= box->nlocal[1]; jc++) {
+      for (int kc = 1; kc <= box->nlocal[2]; kc++) {
+	const long index = ((long) ic*box->nall[1] + jc)*box->nall[2] + kc;
+	const double * p0 = pth + 9*index;
+	double f[3] = {0.0, 0.0, 0.0};
+	for (int b = 0; b < 3; b++) {
+	  for (int side = +1; side >= -1; side -= 2) {
+	    const int n[3] = {ic + side*(b == 0), jc + side*(b == 1), kc + side*(b == 2)};
+	    const int solid = ch_solid(box, wall, n[0], n[1], n[2]);
+	    const double * p1 = pth + 9*(index + side*str[b]);
+	    for (int ia = 0; ia < 3; ia++) {
+	      const double t = solid ? p0[3*ia + b] : 0.5*(p1[3*ia + b] + p0[3*ia + b]);
+	      if (b == 0 && side == +1) f[ia] = -t;
+	      else if (side == +1) f[ia] -= t;
+	      else f[ia] += t;
+	      if (solid) fwall[ia] += (side == +1) ? -p0[3*ia + b] : p0[3*ia + b];
+	    }
+	  }
+	}
+	for (int ia = 0; ia < 3; ia++) force[3*index + ia] += f[ia];
+      }
+    }
+  }
+  for (int ia = 0; ia < 3; ia++) wall->fnet[ia] += -fwall[ia];
+  return 0;
+}
+
 /* phi_grad_mu_fluid_kernel + phi_grad_mu_external_kernel, src/phi_grad_mu.c:294-380,
  * 528-560: F_a = - phi d_a mu (central difference), then F_a -= phi grad_mu^ext_a. */
 int orc_ch_force_gradmu(const orc_box_t * box, const orc_param_t * prm,
@@ -324,7 +371,8 @@ int orc_phi_force(const orc_box_t * box, const orc_param_t * prm, const orc_ch_t
     double * pth = (double *) malloc(sizeof(double)*9*box->nsite);
     if (pth == NULL) return -1;
     orc_ch_stress(box, prm, phi, grad, delsq, pth);
-    orc_ch_force_divergence(box, pth, force);
+    if (orc_wall_attached()) ch_force_divergence_walls(box, orc_wall_attached(), pth, force);
+    else orc_ch_force_divergence(box, pth, force);
     free(pth);
     return 0;
   }
@@ -346,6 +394,24 @@ int orc_cahn_hilliard(const orc_box_t * box, const orc_param_t * prm, const orc_
   orc_halo_periodic(box, 1, delsq);
   rc = orc_ch_advection(box, ch->order, u, phi, flux);
   if (rc == 0) rc = orc_ch_flux_mu(box, prm, ch->grad_mu, phi, delsq, flux);
+  if (rc == 0 && orc_wall_attached()) {
+    /* advection_bcs_no_normal_flux (src/advection_bcs.c:38-140): no flux through a face
+     * shared with solid */
+    const orc_wall_t * wall = orc_wall_attached();
+    double * fw = flux, * fe = flux + box->nsite, * fy = flux + 2*box->nsite, * fz = flux + 3*box->nsite;
+    for (int ic = 1; ic <= box->nlocal[0]; ic++) {
+      for (int jc = 0; jc <= box->nlocal[1]; jc++) {
+	for (int kc = 0; kc <= box->nlocal[2]; kc++) {
+	  const long i0 = site(box, ic, jc, kc);
+	  const double mask = !ch_solid(box, wall, ic, jc, kc);
+	  fw[i0] *= mask*(!ch_solid(box, wall, ic - 1, jc, kc));
+	  fe[i0] *= mask*(!ch_solid(box, wall, ic + 1, jc, kc));
+	  fy[i0] *= mask*(!ch_solid(box, wall, ic, jc + 1, kc));
+	  fz[i0] *= mask*(!ch_solid(box, wall, ic, jc, kc + 1));
+	}
+      }
+    }
+  }
   if (rc == 0) rc = orc_ch_update(box, flux, phi);
   free(flux);
   return rc;

@@ -421,7 +421,8 @@ int orc_step(const orc_model_t * model, const orc_box_t * box,
       }
       else {
       orc_halo_periodic(box, 1, phi);
-      if (grad_select_npt == 27) orc_grad_27pt(box, phi, grad, delsq);
+      if (grad_select_npt == 28) orc_grad_27pt_solid(box, orc_wall_attached(), phi, grad, delsq);
+      else if (grad_select_npt == 27) orc_grad_27pt(box, phi, grad, delsq);
       else orc_grad_7pt(box, phi, grad, delsq);
       if (orc_phi_force(box, prm, ch, phi, grad, delsq, force)) return -1;
       if (orc_cahn_hilliard(box, prm, ch, phi, delsq, u)) return -1;

@@ -46,7 +46,10 @@ CASES = ["d3q19-short/serial-dist-3du", "d3q19-short/serial-dist-1dp",
          # open boundaries (inflow / outflow "rhou") along the one direction without walls
          "d3q19-short/serial-open-ru1", "d3q19-short/serial-open-ru2",
          # the binary fluid in a closed box (walls on all sides, 27-point stencil next to solid)
-         "d3q19-short/serial-spin-lb2"]
+         "d3q19-short/serial-spin-lb2",
+         # the finite-difference order parameter between two walls (solid stencil, no-flux
+         # faces, one-sided stress at the walls)
+         "d3q19-short/serial-spin-fd2"]
 NVEL = {"d3q19-short": 19, "d3q19": 19, "d2q9": 9, "d3q19-io": 19}
 
 

@@ -337,6 +337,11 @@ def check_fd(rec, nt, phi_interior, grad_interior):
     p = binary_params(rec["input"])
     fed = (0.5*p["a"] + 0.25*p["b"]*phi*phi)*phi*phi \
         + 0.5*p["kappa"]*(grad_interior*grad_interior).sum(-1)
+    if "fe" in rec:                     # with walls: total, volume, ratio, surface terms
+        mine = [printed("%17.10e", x) for x in (fed.sum(), vol, fed.sum()/vol, 0.0, 0.0)]
+        for a, b in zip(mine, rec["fe"]):
+            assert abs(a - b) <= 1e-12, ("fe", mine, rec["fe"])
+        return
     mine = [printed("%17.10e", fed.sum()/vol), printed("%17.10e", fed.sum()/vol)]
     for a, b in zip(mine, rec["fed"]):
         assert abs(a - b) <= 1e-12, ("fed", mine, rec["fed"])
@@ -354,7 +359,8 @@ UNVERIFIED_ON_GPU = ({"serial-le2d-lb1", "serial-le2d-fd1", "pmpi08-le2d-fd1", "
                       "pmpi08-le3d-fd1", "pmpi08-le3d-lb1", "iodrop-mpi1-io1",
                       "serial-open-ru1", "serial-open-ru2", "serial-spin-lb2"}
                      | {"serial-le3d-st%d" % k for k in range(1, 9)})
-NOT_ON_DEVICE = set()
+# walls for the finite-difference order parameter: oracle only (b200lb_ch_create refuses them)
+NOT_ON_DEVICE = {"serial-spin-fd2"}
 # The reference prints compensated sums (src/util_sum.c, src/stats_distribution.c:201-265);
 # over 6e5 populations a plain sum is 1e-12 away. That shows where a printed digit sits on a
 # rounding boundary: the y momentum of this log is 3.41278045e-04 printed as "%14.7e".
@@ -435,8 +441,8 @@ def test_cuda_reproduces_reference_log(case, hydro_write):
     import ludwig_b200 as lb
     from ludwig_b200 import models_host
     if case in NOT_ON_DEVICE:
-        pytest.skip("walls with the binary fluid are not on the device path (b200lb_wall_commit "
-                    "refuses them); the oracle reproduces this log")
+        pytest.skip("walls for the finite-difference order parameter are not on the device path "
+                    "(b200lb_ch_create refuses them); the oracle reproduces this log")
     if case in UNVERIFIED_ON_GPU and not os.environ.get("B200LB_UNVERIFIED"):
         pytest.skip("order parameter across Lees-Edwards planes / fourth-order advection: device path not yet run on a GPU "
                     "(set B200LB_UNVERIFIED=1); the oracle reproduces this log in the CPU suite")
