@@ -235,6 +235,14 @@ class Oracle:
         self.L.orc_grad_27pt(ctypes.byref(self.box), _p(phi), _p(grad),
                              _p(delsq))
 
+    def grad_27pt_solid(self, wall, phi, grad, delsq):
+        """grad_3d_27pt_solid_d2 next to the flat walls of `wall` (None: none), neutral wetting."""
+        self.L.orc_grad_27pt_solid.argtypes = [ctypes.c_void_p, ctypes.c_void_p, c_double_p,
+                                               c_double_p, c_double_p]
+        assert self.L.orc_grad_27pt_solid(ctypes.byref(self.box),
+                                          None if wall is None else ctypes.byref(wall),
+                                          _p(phi), _p(grad), _p(delsq)) == 0
+
     def gradient_select(self, npt):
         assert self.L.orc_gradient_select(int(npt)) == 0
 

@@ -54,6 +54,7 @@
 #include "phi_lb_coupler.h"
 #include "gradient_3d_7pt_fluid.h"
 #include "gradient_3d_27pt_fluid.h"
+#include "gradient_3d_27pt_solid.h"
 #include "timer.h"
 #include "wall.h"
 #include "model_le.h"
@@ -334,6 +335,13 @@ int refdrv_grad_select(int npt) {
   if (rd.phi_grad == NULL) return -1;
   if (npt == 7)  return field_grad_set(rd.phi_grad, grad_3d_7pt_fluid_d2, NULL);
   if (npt == 27) return field_grad_set(rd.phi_grad, grad_3d_27pt_fluid_d2, NULL);
+  if (npt == 28) {
+    /* fd_gradient_calculation 3d_27pt_solid (src/gradient_rt.c): needs the map the walls
+     * have marked (refdrv_wall first) and the free energy for 1/kappa */
+    grad_3d_27pt_solid_map_set(rd.map);
+    if (rd.fe) grad_3d_27pt_solid_fe_set(rd.fe);
+    return field_grad_set(rd.phi_grad, grad_3d_27pt_solid_d2, NULL);
+  }
   return -1;
 }
 

@@ -549,6 +549,53 @@ def test_lees_edwards_order_parameter(nlocal, le, npt):
         assert np.max(np.abs(grad[m] - ref.grad()[m])) < 1e-12
 
 
+@pytest.mark.parametrize("nlocal,walls", [((8, 6, 10), (1, 1, 1)), ((6, 7, 5), (0, 1, 1)),
+                                          ((9, 5, 6), (1, 0, 0)), ((5, 6, 8), (0, 0, 1))])
+def test_gradient_next_to_walls(nlocal, walls):
+    """grad_3d_27pt_solid_d2 (src/gradient_3d_27pt_solid.c:131-325) with neutral wetting
+    next to flat walls, bit for bit, and the binary time loop between them."""
+    nvel = 19
+    need_ref(nvel)
+    periodic = tuple(0 if w else 1 for w in walls)
+    orc = pyoracle.Oracle(nvel, nlocal, ndist=2)
+    m = orc.interior_mask()
+    n = orc.nsite
+    rng = np.random.default_rng(21)
+    phi0 = np.zeros(orc.nall)
+    phi0[1:-1, 1:-1, 1:-1] = 0.4*(rng.random(nlocal) - 0.5)
+    phi0 = phi0.reshape(-1)
+    orc.halo(phi0, 1)
+    kw = dict(eta_shear=0.00625, eta_bulk=0.00625, mobility=3.75)
+    prm = pyoracle.make_param(a=-0.00625, b=0.00625, kappa=0.004, **kw)
+    with pyref.Ref(nvel, nlocal, ndist=2, periodic=periodic) as ref:
+        ref.physics(**kw)
+        ref.fe_symm(-0.00625, 0.00625, 0.004)
+        ref.wall(walls)
+        ref.grad_select(28)
+        ref.phi()[...] = phi0
+        ref.grad_compute()
+        w = orc.wall(walls)
+        grad, delsq = np.zeros((n, 3)), np.zeros(n)
+        orc.grad_27pt_solid(w, phi0, grad, delsq)
+        assert np.array_equal(grad[m], ref.grad()[m])
+        assert np.array_equal(delsq[m], ref.delsq()[m])
+        f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal, ndist=2)
+        ref.f()[...] = f0
+        ref.step(8)
+        f, fp = f0.copy(), np.zeros_like(f0)
+        rho, u, frc = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
+        phi = np.zeros(n)
+        orc.gradient_select(28)
+        orc.wall_attach(w)
+        try:
+            orc.step(prm, 8, f, fp, rho, u, frc, phi, grad, delsq)
+        finally:
+            orc.gradient_select(7)
+            orc.wall_attach(None)
+        assert relerr(f[m], ref.f()[m]) < 1e-12
+        assert np.allclose(np.array(w.fnet[:]), ref.wall_momentum(), rtol=1e-10, atol=1e-14)
+
+
 # ---------------------------------------------------------------------------
 # "free_energy symmetric": the order parameter as a finite-difference field
 # (phi_force_calculation + phi_cahn_hilliard), reference built with nhalo = 2
