@@ -200,6 +200,15 @@ class Ref:
         """The next refdrv_step starts with physics_control_next_step from here."""
         self.L.refdrv_time_set(int(t))
 
+    def open_bc(self, flow_dir, u0=(0.0, 0.0, 0.0), rho0=1.0):
+        """lb_bc_open: inflow and outflow of type rhou along flow_dir (walls across it first)."""
+        self.L.refdrv_open_bc.argtypes = [ctypes.c_int, ctypes.POINTER(ctypes.c_double), ctypes.c_double]
+        assert self.L.refdrv_open_bc(int(flow_dir), (ctypes.c_double * 3)(*u0), float(rho0)) == 0
+
+    def open_apply(self):
+        """inflow/outflow update + impose (src/ludwig.c:820-831)."""
+        assert self.L.refdrv_open_apply() == 0
+
     def time(self):
         """physics_control_time: what the displacement of the order parameter is taken at."""
         self.L.refdrv_time.restype = ctypes.c_double

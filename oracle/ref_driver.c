@@ -55,6 +55,8 @@
 #include "gradient_3d_7pt_fluid.h"
 #include "gradient_3d_27pt_fluid.h"
 #include "gradient_3d_27pt_solid.h"
+#include "lb_bc_inflow_rhou.h"
+#include "lb_bc_outflow_rhou.h"
 #include "timer.h"
 #include "wall.h"
 #include "model_le.h"
@@ -202,6 +204,7 @@ int refdrv_init(const int ntotal[3], int ndist, int halo_scheme) {
 }
 
 int refdrv_finish(void) {
+  refdrv_open_free();
 
   if (rd.visc) rd.visc->func->free(rd.visc);
   if (rd.pch) phi_ch_free(rd.pch);
@@ -331,6 +334,40 @@ int refdrv_grad_compute(void) { return field_grad_compute(rd.phi_grad); }
 
 /* The reference's function-pointer plug point (src/field_grad.c field_grad_set):
  * which d2 stencil field_grad_compute() runs, as gradient_rt.c would select. */
+/* Open boundaries for the fluid: what lb_bc_open_rt (src/lb_bc_open_rt.c:48-170) builds for
+ * "lb_bc_inflow_type rhou" / "lb_bc_outflow_type rhou"; refdrv_open_apply = the four calls
+ * after lb_halo in src/ludwig.c:820-831 */
+static lb_bc_inflow_rhou_t * rd_inflow = NULL;
+static lb_bc_outflow_rhou_t * rd_outflow = NULL;
+
+int refdrv_open_bc(int flow_dir, const double u0[3], double rho0) {
+  lb_bc_inflow_opts_t oi = lb_bc_inflow_opts_default();
+  lb_bc_outflow_opts_t oo = lb_bc_outflow_opts_default();
+  oi.nvel = NVEL; oo.nvel = NVEL;
+  for (int a = 0; a < 3; a++) { oi.flow[a] = (a == flow_dir); oo.flow[a] = (a == flow_dir); oi.u0[a] = u0[a]; }
+  oo.rho0 = rho0;
+  if (rd_inflow) { lb_bc_inflow_rhou_free(rd_inflow); rd_inflow = NULL; }
+  if (rd_outflow) { lb_bc_outflow_rhou_free(rd_outflow); rd_outflow = NULL; }
+  if (lb_bc_inflow_rhou_create(rd.pe, rd.cs, &oi, &rd_inflow)) return -1;
+  if (lb_bc_outflow_rhou_create(rd.pe, rd.cs, &oo, &rd_outflow)) return -1;
+  return 0;
+}
+
+int refdrv_open_apply(void) {
+  if (rd_inflow == NULL || rd_outflow == NULL) return -1;
+  lb_bc_inflow_rhou_update(rd_inflow, rd.hydro);
+  lb_bc_inflow_rhou_impose(rd_inflow, rd.hydro, rd.lb);
+  lb_bc_outflow_rhou_update(rd_outflow, rd.hydro);
+  lb_bc_outflow_rhou_impose(rd_outflow, rd.hydro, rd.lb);
+  return 0;
+}
+
+int refdrv_open_free(void) {
+  if (rd_inflow) { lb_bc_inflow_rhou_free(rd_inflow); rd_inflow = NULL; }
+  if (rd_outflow) { lb_bc_outflow_rhou_free(rd_outflow); rd_outflow = NULL; }
+  return 0;
+}
+
 int refdrv_grad_select(int npt) {
   if (rd.phi_grad == NULL) return -1;
   if (npt == 7)  return field_grad_set(rd.phi_grad, grad_3d_7pt_fluid_d2, NULL);
@@ -461,6 +498,7 @@ double refdrv_step(int nsteps) {
     lb_collide(rd.lb, rd.hydro, rd.map, rd.noise, (fe_t *) rd.fe, rd.visc);
     if (rd.nplanes > 0) lb_le_apply_boundary_conditions(rd.lb, rd.le);   /* src/ludwig.c:810 */
     lb_halo(rd.lb);
+    if (rd_inflow && rd_outflow) refdrv_open_apply();            /* src/ludwig.c:820-831 */
     if (rd.wall && wall_present(rd.wall)) {                      /* src/ludwig.c:837-842 */
       wall_set_wall_distributions(rd.wall);
       wall_bbl(rd.wall);

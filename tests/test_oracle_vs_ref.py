@@ -549,6 +549,54 @@ def test_lees_edwards_order_parameter(nlocal, le, npt):
         assert np.max(np.abs(grad[m] - ref.grad()[m])) < 1e-12
 
 
+@pytest.mark.parametrize("nvel,nlocal,walls,u0", [
+    (19, (12, 6, 6), (0, 1, 1), (0.0, 0.0, 0.0)), (19, (6, 6, 12), (1, 1, 0), (0.0, 0.0, 0.003)),
+    (27, (8, 6, 5), (0, 1, 1), (0.004, 0.0, 0.0)), (19, (5, 9, 7), (1, 0, 1), (0.0, 0.002, 0.0))])
+def test_open_boundaries(nvel, nlocal, walls, u0):
+    """lb_bc_inflow_rhou / lb_bc_outflow_rhou update + impose (src/lb_bc_inflow_rhou.c:235-281,
+    478-531 and the outflow twin): the imposed populations bit for bit, then the time loop
+    with walls across the flow."""
+    need_ref(nvel)
+    flow = walls.index(0)
+    orc = pyoracle.Oracle(nvel, nlocal)
+    n = orc.nsite
+    m = orc.interior_mask()
+    kw = dict(eta_shear=0.1, eta_bulk=0.1)
+    prm = pyoracle.make_param(**kw)
+    f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal)
+    rng = np.random.default_rng(9)
+    rho0 = 1.0 + 0.1*rng.random(n)
+    u_in = 0.05*(rng.random((n, 3)) - 0.5)
+    with pyref.Ref(nvel, nlocal, periodic=(0, 0, 0)) as ref:
+        ref.physics(**kw)
+        ref.wall(walls)
+        ref.open_bc(flow, u0, 1.01)
+        o = orc.open_bc(flow, u0, 1.01)
+        ref.f()[...] = f0
+        ref.rho()[...] = rho0
+        ref.u()[...] = u_in
+        ref.open_apply()
+        f, rho, u = f0.copy(), rho0.copy(), u_in.copy()
+        orc.open_apply(o, rho, u, f)
+        assert np.array_equal(f, ref.f())
+        assert np.array_equal(rho, ref.rho()) and np.array_equal(u, ref.u())
+        assert not np.array_equal(f, f0)
+        ref.f()[...] = f0
+        ref.step(10)
+        f, fp = f0.copy(), np.zeros_like(f0)
+        rho, u, frc = np.zeros(n), np.zeros((n, 3)), np.zeros((n, 3))
+        w = orc.wall(walls)
+        orc.wall_attach(w)
+        orc.open_attach(o)
+        try:
+            orc.step(prm, 10, f, fp, rho, u, frc)
+        finally:
+            orc.wall_attach(None)
+            orc.open_attach(None)
+        assert relerr(f[m], ref.f()[m]) < 1e-12
+        assert np.allclose(np.array(w.fnet[:]), ref.wall_momentum(), rtol=1e-10, atol=1e-14)
+
+
 @pytest.mark.parametrize("nlocal,walls", [((8, 6, 10), (1, 1, 1)), ((6, 7, 5), (0, 1, 1)),
                                           ((9, 5, 6), (1, 0, 0)), ((5, 6, 8), (0, 0, 1))])
 def test_gradient_next_to_walls(nlocal, walls):
