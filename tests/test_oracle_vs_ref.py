@@ -818,6 +818,54 @@ def test_cahn_hilliard_lees_edwards(nlocal, le, order, method, npt, gmu):
         assert np.max(np.abs(phi[m] - ref.inner(ref.phi()).reshape(-1)[m])) < 1e-12
 
 
+@pytest.mark.parametrize("nlocal,walls,order", [((10, 8, 6), (1, 0, 0), 1), ((8, 6, 10), (0, 1, 1), 2),
+                                                ((6, 7, 8), (1, 1, 1), 1)])
+def test_cahn_hilliard_between_walls(nlocal, walls, order):
+    """The finite-difference order parameter between flat walls (serial-spin-fd2): the
+    stress of the site itself at a face shared with solid and what crosses it booked to the
+    walls (pth_force_map_kernel, pth_force_wall_kernel: src/phi_force_colloid.c:490-790), no
+    flux through such faces (src/advection_bcs.c:38-140), the stencil next to solid; stage by
+    stage bit for bit, then the time loop."""
+    nvel = 19
+    need_ref(nvel)
+    A, B, K, M, eta = -0.00625, 0.00625, 0.004, 1.25, 0.00625
+    periodic = tuple(0 if w else 1 for w in walls)
+    orc = pyoracle.Oracle(nvel, nlocal)
+    prm = pyoracle.make_param(eta_shear=eta, eta_bulk=eta, mobility=M, a=A, b=B, kappa=K)
+    ch = orc.ch(order, pyoracle.FORCE_STRESS_DIVERGENCE, (0.0, 0.0, 0.0))
+    phi0, u0 = fd_fields(nlocal)
+    n = orc.nsite
+    m = orc.interior_mask()
+    with pyref.Ref(nvel, nlocal, fd=dict(order=order, method=2), periodic=periodic) as ref:
+        ref.physics(eta_shear=eta, eta_bulk=eta, mobility=M)
+        ref.fe_symm(A, B, K)
+        ref.wall(walls)
+        ref.grad_select(28)
+        ref.inner(ref.phi())[...] = phi0.reshape(orc.nall)
+        ref.inner(ref.u())[...] = u0.reshape(orc.nall + (3,))
+        ref.phi_halo()
+        ref.grad_compute()
+        ref.hydro_f_zero()
+        ref.phi_force()
+        w = orc.wall(walls)
+        phi, u = phi0.copy(), u0.copy()
+        orc.halo(phi, 1)
+        grad, delsq, force = np.zeros((n, 3)), np.zeros(n), np.zeros((n, 3))
+        orc.grad_27pt_solid(w, phi, grad, delsq)
+        assert np.array_equal(grad[m], ref.inner(ref.grad()).reshape(-1, 3)[m])
+        orc.wall_attach(w)
+        try:
+            orc.phi_force(prm, ch, phi, grad, delsq, force)
+            assert np.array_equal(force[m], ref.inner(ref.force()).reshape(-1, 3)[m])
+            assert np.allclose(np.array(w.fnet[:]), ref.wall_momentum(), rtol=1e-12, atol=1e-18)
+            ref.cahn_hilliard()
+            orc.cahn_hilliard(prm, ch, phi, delsq, u)
+        finally:
+            orc.wall_attach(None)
+        assert np.array_equal(phi[m], ref.inner(ref.phi()).reshape(-1)[m])
+        assert abs(phi[m].sum() - phi0[m].sum()) < 1e-13*m.sum()      # nothing leaves through a wall
+
+
 @pytest.mark.parametrize("order,method,npt,gmu", FD_CASES[:4])
 def test_cahn_hilliard_time_loop(order, method, npt, gmu):
     nvel, nlocal, nsteps = 19, (8, 8, 8), 6
