@@ -217,11 +217,18 @@ struct b200lb_s {
 // A direction whose halo planes travel through send/receive buffers: decomposed over
 // ranks, or (option "loopback", for testing and profiling the multi-rank machinery on
 // one GPU) periodic within the rank with this rank as its own neighbour.
+// option "loopback": 1 = every periodic direction, 8 | mask = the physical axes in mask
+static bool loop_axis(const b200lb_s * h, int a) {
+  if (!h->opt_loopback) return false;
+  if (h->opt_loopback & 8) return ((h->opt_loopback >> a) & 1) != 0;
+  return true;
+}
+
 static bool decomposed(const b200lb_s * h, int d) {
   const int a = h->ops->dax[d];
   if (h->L.h[d] == 0) return false;
   if (h->desc.cartsz[a] > 1) return true;
-  return h->opt_loopback && h->desc.periodic[a];
+  return loop_axis(h, a) && h->desc.periodic[a];
 }
 
 static bool have_comm(const b200lb_s * h) { return h->comm != nullptr || h->opt_loopback; }
@@ -230,7 +237,7 @@ static void update_selfper(b200lb_s * h) {
   for (int d = 0; d < 3; d++) {
     const int a = h->ops->dax[d];
     h->selfper[d] = (h->L.h[d] == 1 && h->desc.cartsz[a] == 1 && h->desc.periodic[a]
-		     && !h->opt_loopback) ? 1 : 0;
+		     && !loop_axis(h, a)) ? 1 : 0;
   }
 }
 
@@ -544,6 +551,7 @@ extern "C" long b200lb_nsite(const b200lb_t * h) { return h ? h->nsite_host : 0;
 static int materialise(b200lb_s * h);
 static int join_comm(b200lb_s * h);
 static int flush_halo(b200lb_s * h);
+static int flush_phi_halo(b200lb_s * h);
 static int resolve_ch_force(b200lb_s * h);
 
 extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
@@ -593,7 +601,9 @@ extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
     if (h->desc.nranks > 1 && v) return fail("loopback is for single-rank lattices");
     if (join_comm(h)) return -1;
     if (flush_halo(h)) return -1;
-    h->opt_loopback = (v != 0);
+    if (h->phi) { if (flush_phi_halo(h)) return -1; }
+    if (v < 0 || v > 15) return fail("loopback: 0, 1 (all periodic directions) or 8 | mask of physical axes");
+    h->opt_loopback = (int) v;
     update_selfper(h);
     h->p2p_ready = 0; h->pushed_valid = false; h->push_wait_pending = false;
     // message tables depend on which directions are exchanged

@@ -1,0 +1,78 @@
+"""Seeded synthetic lattice states: the input generator of bench.py, smoke() and the tests.
+
+Counter-based generator (splitmix64 finaliser) keyed on the GLOBAL site id and a
+stream number, so any decomposition of the same global lattice sees the same data
+(SURVEY.md 8(d)). Seed 8361235 is the one used throughout the reference's
+regression inputs.
+"""
+
+import numpy as np
+
+SEED = 8361235
+
+
+def _mix(x):
+    x = (x + np.uint64(0x9E3779B97F4A7C15)) & np.uint64(0xFFFFFFFFFFFFFFFF)
+    x = (x ^ (x >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+    x = (x ^ (x >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+    return x ^ (x >> np.uint64(31))
+
+
+def uniform(ids, stream, seed=SEED):
+    """U(-1,1) doubles, one per entry of the uint64 array ids."""
+    with np.errstate(over="ignore"):
+        key = _mix(np.uint64(seed) + np.uint64(stream) * np.uint64(0xD1342543DE82EF95))
+        x = _mix(ids.astype(np.uint64) ^ key)
+    return (x >> np.uint64(11)).astype(np.float64) * (2.0 / 9007199254740992.0) - 1.0
+
+
+def global_ids(nlocal, ntotal=None, offset=(0, 0, 0)):
+    """Global site id of every site of the halo-inclusive local box (nhalo = 1),
+    periodic images included, shape nall."""
+    ntotal = tuple(ntotal or nlocal)
+    ax = [((np.arange(nlocal[a] + 2) - 1 + offset[a]) % ntotal[a]) for a in range(3)]
+    gx, gy, gz = np.meshgrid(*ax, indexing="ij")
+    return ((gx * ntotal[1] + gy) * ntotal[2] + gz).astype(np.uint64)
+
+
+def equilibrium(cv, wv, rho, u):
+    """lb_1st_moment_equilib_set (src/model.c:916-941), vectorised.
+    rho [n], u [n,3] -> f [n, nvel]."""
+    cu = u @ cv.T.astype(np.float64)                     # [n, nvel]
+    uu = np.einsum("na,na->n", u, u)
+    return rho[:, None] * wv[None, :] * (1.0 + 3.0 * cu + 4.5 * cu * cu
+                                           - 1.5 * uu[:, None])
+
+
+def make_state(cv, wv, nlocal, ndist=1, ntotal=None, offset=(0, 0, 0),
+               amp=0.01, noneq=0.01, ndim=3):
+    """f in the reference host layout [nsite, ndist, nvel]; every site of the
+    halo-inclusive box is filled consistently with periodic images."""
+    nvel = len(wv)
+    ids = global_ids(nlocal, ntotal, offset).reshape(-1)
+    n = ids.size
+    rho = 1.0 + amp * uniform(ids, 1)
+    u = np.zeros((n, 3))
+    for a in range(ndim):
+        u[:, a] = amp * uniform(ids, 2 + a)
+    f = np.zeros((n, ndist, nvel))
+    feq = equilibrium(cv, wv, rho, u)
+    for p in range(nvel):
+        feq[:, p] *= 1.0 + noneq * uniform(ids, 10 + p)
+    f[:, 0, :] = feq
+    if ndist == 2:
+        phi = 0.5 * uniform(ids, 50)
+        g = wv[None, :] * phi[:, None] * 0.0
+        g[:, 0] = phi
+        for p in range(nvel):
+            g[:, p] += 0.01 * wv[p] * uniform(ids, 60 + p)
+        f[:, 1, :] = g
+    return f
+
+
+def make_force(nlocal, ntotal=None, offset=(0, 0, 0), amp=1.0e-3, ndim=3):
+    ids = global_ids(nlocal, ntotal, offset).reshape(-1)
+    force = np.zeros((ids.size, 3))
+    for a in range(ndim):
+        force[:, a] = amp * uniform(ids, 80 + a)
+    return force

@@ -986,6 +986,7 @@ def test_walls_fused_equals_unfused_and_refusals():
         lat.wall_commit((0, 0, 1))
     lat.close()
     lat = lb.Lattice(nvel, (4, 4, 4), ndist=2, periodic=(1, 1, 0))
+    lat.set_option("binary_walls", 0)
     with pytest.raises(lb.B200LBError, match="binary"):
         lat.wall_commit((0, 0, 1))
     lat.close()

@@ -212,6 +212,7 @@ def test_refusals():
     lat.phi_ch_create(1)
     with pytest.raises(lb.B200LBError, match="field_grad_compute"):
         lat.phi_force_calculation()
+    lat.set_option("le_fd", 0)
     with pytest.raises(lb.B200LBError, match="Lees-Edwards"):
         lat.le_commit(2, 0.01)
     lat.close()
