@@ -308,6 +308,26 @@ int  b200lb_step_diag(b200lb_t * h, double out[8]);
  * full-field D2H of src/ludwig.c:955,2335; the caller finishes with its MPI_Reduce. */
 int  b200lb_field_stats(b200lb_t * h, int field, double * out);
 
+/* b200lb_field_stats that allocates nothing. NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid it). Same kernels, same result
+ * (out[4*c + 0..3] = sum, sum of squares, min, max per component over the interior sites);
+ * the per-block partial sums live in a file-scope device array of
+ * 8*(B200LB_NOALLOC_MAXBLOCK + 1) doubles (4 MiB) that every GPU loading the library holds
+ * until exit. Limits and rules:
+ *   - the lattice must need at most B200LB_NOALLOC_MAXBLOCK blocks of 128 x 2 sites,
+ *     ceil(n_z/128)*ceil(n_y/2)*n_x (256^3 fits exactly); larger lattices are refused;
+ *   - the field's device planes must exist and hold current values: a field that was never
+ *     uploaded / written, or is still recorded lazily (rho,u with hydro_write = 0, the
+ *     uniform force of hydro_f_zero, a gradient not yet materialised), is refused -- making
+ *     it current could allocate. b200lb_field_stats or b200lb_field_download does that;
+ *   - all calls on a device share the array, which keeps the last call's contents: calls
+ *     that overlap on the GPU (two handles or threads at once) race. Calls on one handle
+ *     are ordered by its stream.
+ * Calls no cudaMalloc, cudaFree or allocating library routine. */
+#define B200LB_NOALLOC_MAXBLOCK 65536
+int  b200lb_field_stats_noalloc(b200lb_t * h, int field, double * out);
+
 /* lb_io_aggr_pack / lb_io_aggr_unpack with binary records (src/model.c:1498-1560): the
  * interior sites in (ic,jc,kc) order, kc fastest, b200lb_io_record_doubles() =
  * ndist*nvel doubles per site ordered [n][p] (lb_write_buf, src/model.c:1385) -- the

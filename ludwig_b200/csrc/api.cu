@@ -2401,6 +2401,86 @@ extern "C" int b200lb_field_stats(b200lb_t * h, int field, double * out) {
   return 0;
 }
 
+// ---------------------------------------------------------------------------
+// b200lb_field_stats without any allocation (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph
+// capture, tight serving loops, harnesses that forbid it).
+//
+// Same kernels as b200lb_field_stats; the per-block partials and the folded result live
+// in a file-scope device array instead of h->partial / h->stats_dev. Every GPU that
+// loads the library holds the array (B200LB_NOALLOC_BYTES) until exit. ALL calls on a
+// device share it and it keeps the last call's contents: calls that overlap on the GPU
+// (two handles, two streams) race. field_stats_kernel writes every partial slot the fold
+// reads, so only the result slots are cleared per call.
+// ---------------------------------------------------------------------------
+
+// B200LB_NOALLOC_MAXBLOCK (include/b200lb.h): 65536 blocks of 128 x 2 sites, up to 256^3
+#define B200LB_NOALLOC_DOUBLES  (8*B200LB_NOALLOC_MAXBLOCK + 8)
+#define B200LB_NOALLOC_MAXDEV   64
+
+static __device__ __align__(256) double g_noalloc_scratch[B200LB_NOALLOC_DOUBLES];
+
+// In host code g_noalloc_scratch is only a stand-in for the symbol: the device address
+// comes from cudaGetSymbolAddress, once per device, with that device current.
+static double * g_noalloc_ptr[B200LB_NOALLOC_MAXDEV];
+
+static int noalloc_scratch(double ** out) {
+  int dev = -1;
+  CU(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= B200LB_NOALLOC_MAXDEV) return fail("no-alloc scratch: device index %d out of range", dev);
+  if (!g_noalloc_ptr[dev]) {
+    double * ptr = nullptr;
+    CU(cudaGetSymbolAddress((void **) &ptr, g_noalloc_scratch));
+    if (!ptr) return fail("no-alloc scratch: cudaGetSymbolAddress returned a null address");
+    g_noalloc_ptr[dev] = ptr;
+  }
+  *out = g_noalloc_ptr[dev];
+  return 0;
+}
+
+// out[4*c + 0..3] = sum, sum of squares, min, max per component over the interior sites,
+// as b200lb_field_stats. Calls no cudaMalloc / cudaFree: a field whose device planes do
+// not exist yet, or whose values are still recorded lazily (materialising them may
+// allocate), is refused with a message instead.
+extern "C" int b200lb_field_stats_noalloc(b200lb_t * h, int field, double * out) {
+  if (!h || !out) return fail("null argument");
+  double * dev = nullptr; int nf = 0;
+  bool lazy = false;
+  switch (field) {
+  case B200LB_FIELD_RHO:   dev = h->rho;   nf = 1; lazy = h->hydro_stale; break;
+  case B200LB_FIELD_U:     dev = h->u;     nf = 3; lazy = h->hydro_stale || h->u_fill_pending; break;
+  case B200LB_FIELD_FORCE: dev = h->force; nf = 3; lazy = h->force_uniform || h->ch_force_pending; break;
+  case B200LB_FIELD_PHI:   dev = h->phi;   nf = 1; break;      // interior sites only: deferred halo copies do not matter
+  case B200LB_FIELD_GRAD:  dev = h->grad;  nf = 3; lazy = (h->grad_state != 0); break;
+  case B200LB_FIELD_DELSQ: dev = h->delsq; nf = 1; lazy = (h->grad_state != 0); break;
+  case B200LB_FIELD_ETA:   dev = h->eta;   nf = 1; break;
+  default: return fail("unknown field %d", field);
+  }
+  if (!dev) return fail("b200lb_field_stats_noalloc: field %d has no device planes yet and this entry point allocates nothing (upload it, or call b200lb_field_stats once)", field);
+  if (lazy) return fail("b200lb_field_stats_noalloc: field %d is recorded lazily (its values would have to be materialised, which may allocate): call b200lb_field_download or b200lb_field_stats first", field);
+  const Layout & L = h->L;
+  dim3 block(128, 2, 1);
+  dim3 grid((L.n[2] + 127)/128, (L.n[1] + 1)/2, L.n[0]);
+  const i64 nblock = (i64) grid.x*grid.y*grid.z;
+  if (nblock > B200LB_NOALLOC_MAXBLOCK)
+    return fail("b200lb_field_stats_noalloc: %lld blocks of 128 x 2 sites exceed the static scratch (B200LB_NOALLOC_MAXBLOCK = %d, i.e. up to 256^3 interior sites): use b200lb_field_stats", (long long) nblock, B200LB_NOALLOC_MAXBLOCK);
+  double * scratch = nullptr;
+  if (noalloc_scratch(&scratch)) return -1;
+  double * result = scratch + (size_t) 8*B200LB_NOALLOC_MAXBLOCK;
+  if (join_comm(h)) return -1;
+  for (int c = 0; c < nf; c++) {
+    CU(cudaMemsetAsync(result, 0, 8*sizeof(double), h->s_main));
+    field_stats_kernel<<<grid, block, 0, h->s_main>>>(L, dev + (i64) c*L.nsd, scratch);
+    stats_final_kernel<<<1, 256, 0, h->s_main>>>(scratch, nblock, result);
+    CU(cudaGetLastError());
+    h->launches += 2;
+    CU(cudaMemcpyAsync(h->stats_host, result, 8*sizeof(double), cudaMemcpyDeviceToHost, h->s_main));
+    CU(cudaStreamSynchronize(h->s_main));
+    for (int k = 0; k < 4; k++) out[4*c + k] = h->stats_host[k];
+  }
+  return 0;
+}
+
 // lb_io_aggr_pack / lb_io_aggr_unpack with binary records (src/model.c:1498-1560,
 // lb_write_buf :1385): the interior sites in (ic,jc,kc) order, kc fastest, each record
 // [n][p] doubles -- packed straight from the device layout, so the halo shell never

@@ -41,7 +41,7 @@ ABI_SYMBOLS = [
     "b200lb_le_field_time_set", "b200lb_open_bc_commit", "b200lb_open_bc_apply",
     "b200lb_ch_create", "b200lb_ch_grad_mu_set", "b200lb_phi_force", "b200lb_cahn_hilliard",
     "b200lb_hydro_u_halo", "b200lb_visc_arrhenius_commit", "b200lb_visc_update", "b200lb_visc_model_set",
-    "b200lb_field_stats", "b200lb_io_record_doubles", "b200lb_io_pack", "b200lb_io_unpack",
+    "b200lb_field_stats", "b200lb_field_stats_noalloc", "b200lb_io_record_doubles", "b200lb_io_pack", "b200lb_io_unpack",
     "b200lb_step", "b200lb_stats", "b200lb_step_diag", "b200lb_sync", "b200lb_nccl_unique_id",
     "b200lb_comm_init", "b200lb_p2p_export", "b200lb_p2p_import", "b200lb_timer_start", "b200lb_timer_stop",
     "b200lb_launch_count", "b200lb_host_alloc", "b200lb_host_free",
@@ -136,6 +136,7 @@ def load():
     L.b200lb_visc_update.argtypes = [vp]
     L.b200lb_visc_model_set.argtypes = [vp, ctypes.c_int]
     L.b200lb_field_stats.argtypes = [vp, ctypes.c_int, vp]
+    L.b200lb_field_stats_noalloc.argtypes = [vp, ctypes.c_int, vp]
     L.b200lb_io_record_doubles.argtypes = [vp]
     L.b200lb_io_record_doubles.restype = ctypes.c_long
     L.b200lb_io_pack.argtypes = [vp, vp]
@@ -418,6 +419,14 @@ class Lattice:
         nf = _FIELD_NF[field]
         out = np.zeros((nf, 4))
         self._ck(self.L.b200lb_field_stats(self.h, field, _ptr(out)))
+        return out
+
+    def field_stats_noalloc(self, field):
+        """field_stats through the entry point that allocates nothing (static device scratch,
+        at most 65536 blocks of 128 x 2 sites; no counterpart in the reference)."""
+        nf = _FIELD_NF[field]
+        out = np.zeros((nf, 4))
+        self._ck(self.L.b200lb_field_stats_noalloc(self.h, field, _ptr(out)))
         return out
 
     def lb_io_aggr_pack(self, buf=None):
