@@ -102,8 +102,13 @@ long b200lb_nsite(const b200lb_t * h);                          /* host nsite = 
 /* run-time options; recognised names:
  *   "fused"       0/1  collide-and-stream in one pass (lazy propagation)
  *   "halo"        B200LB_HALO_FULL / B200LB_HALO_REDUCED
- *   "hydro_write" 0/1  store rho,u from the collision every step (reference
- *                      behaviour, src/collision.c:570-579); 0 = on demand
+ *   "hydro_write" 0/1/2  1: the collision stores rho,u every step (the reference's
+ *                      behaviour, src/collision.c:570-579); 0: never -- they are recomputed
+ *                      from the post-collision lattice when somebody asks (identical to
+ *                      round-off); 2 (default): the collision stores them when hydro
+ *                      quantities were asked for since the previous collision, so a caller
+ *                      that looks every step gets 1 and a time loop that only looks at
+ *                      statistics steps gets 0 in between
  *   "vec"         1/2  lattice sites per thread
  *   "block"       threads per block along the contiguous direction
  *   "halo_lazy"   0/1  defer the local periodic halo copies until the host looks
@@ -358,6 +363,13 @@ int  b200lb_p2p_import(b200lb_t * h, const char * all, int nranks);
 int  b200lb_timer_start(b200lb_t * h);
 int  b200lb_timer_stop(b200lb_t * h, float * ms);     /* synchronises */
 long b200lb_launch_count(const b200lb_t * h);         /* kernels launched so far */
+/* TIMER_COLLIDE_KERNEL / TIMER_PROP_KERNEL (src/collision.c:198-207, src/propagation.c:84-91):
+ * time of the sweep kernels ALONE. Between _start and _stop every sweep launch (collision,
+ * propagation, the fused pass; each wall or overlap slab is one) is bracketed by CUDA events
+ * on the launching stream; _stop synchronises and returns their summed duration and count.
+ * Other launches of a step (halo kernels, peer synchronisation) are not in it. */
+int  b200lb_kernel_timer_start(b200lb_t * h, int max_launches);
+int  b200lb_kernel_timer_stop(b200lb_t * h, double * ms, long * nlaunch);
 
 /* Pinned host memory for lb->f and friends (optional; speeds up lb_memcpy) */
 int  b200lb_host_alloc(void ** ptr, long nbytes);

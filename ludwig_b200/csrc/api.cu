@@ -158,6 +158,7 @@ struct b200lb_s {
   double fconst[3];
   bool u_fill_pending;       // hydro_u_zero recorded but not yet applied
   double uconst[3];
+  bool hydro_asked;          // somebody wanted rho,u since the last collision (hydro_write = 2: the next one stores them)
   bool hydro_stale;          // collision ran without storing rho,u (recoverable from lat[cur], see ensure_hydro)
   bool last_ffield;          // the last collision read the per-site force field
   double last_fg[3];         // ... and this uniform part
@@ -189,6 +190,8 @@ struct b200lb_s {
   double * diag; i64 diag_cap, diag_count;   // in-sweep diagnostics: per-block partials of the last collision
   double * stats_dev; double * stats_host;
   long launches;
+  // CUDA events around the sweep launches alone (b200lb_kernel_timer_*)
+  cudaEvent_t * tev; int tev_cap, tev_n; bool tev_on;
 
   ncclComm_t comm;
   HaloBuf hb[3];             // per device axis (multi-rank directions only)
@@ -208,9 +211,8 @@ struct b200lb_s {
   int p2p_ready;
   double * peer_lat[2][27];
   P2PSync p2p;
-  void * ipc_open[64]; int n_ipc_open;
+  void * ipc_open[3*26 + 3]; int n_ipc_open;
   unsigned long long push_step;
-  bool push_wait_pending;     // a signal was sent: s_main must pass wait(push_step) before touching halos
   bool pushed_valid;          // the halo data of lat[cur] was pushed by the sweep that wrote it
 };
 
@@ -489,7 +491,7 @@ static int create_impl(const b200lb_desc_t * desc, b200lb_s * h, const ModelOps 
   h->force_uniform = true;
   h->opt_fused = 1;
   h->opt_halo = B200LB_HALO_FULL;
-  h->opt_hydro_write = 1;
+  h->opt_hydro_write = 2;        // auto: see run_sweep
   // two sites per thread (128-bit accesses) for D3Q19; one for D3Q27 (27 live populations
   // per site) and D2Q9 (few streams, occupancy matters more): measured, profiles/r1_bench_*
   h->opt_vec = (desc->nvel == 19) ? 2 : 1;
@@ -522,6 +524,8 @@ extern "C" int b200lb_destroy(b200lb_t * h) {
   cudaDeviceSynchronize();
   if (h->comm) g_nccl.CommDestroy(h->comm);
   for (int i = 0; i < h->n_ipc_open; i++) cudaIpcCloseMemHandle(h->ipc_open[i]);
+  for (int i = 0; i < h->tev_cap; i++) cudaEventDestroy(h->tev[i]);
+  free(h->tev);
   cudaFree(h->p2p.flags);
   cudaFree(h->msg_pack); cudaFree(h->msg_unpack); cudaFree(h->dsend); cudaFree(h->drecv);
   for (int d = 0; d < 3; d++) {
@@ -566,7 +570,10 @@ extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
     if (v != B200LB_HALO_FULL && v != B200LB_HALO_REDUCED) return fail("bad halo scheme %ld", v);
     h->opt_halo = (int) v; return 0;
   }
-  if (!strcmp(name, "hydro_write")) { h->opt_hydro_write = (v != 0); return 0; }
+  if (!strcmp(name, "hydro_write")) {
+    if (v < 0 || v > 2) return fail("hydro_write: 0 (on demand), 1 (every collision, as the reference), 2 (auto)");
+    h->opt_hydro_write = (int) v; return 0;
+  }
   if (!strcmp(name, "halo_lazy")) { h->opt_halo_lazy = (v != 0); return 0; }
   if (!strcmp(name, "overlap")) { h->opt_overlap = (v != 0); return 0; }
   if (!strcmp(name, "direct")) { h->opt_direct = (v != 0); return 0; }
@@ -605,7 +612,7 @@ extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
     if (v < 0 || v > 15) return fail("loopback: 0, 1 (all periodic directions) or 8 | mask of physical axes");
     h->opt_loopback = (int) v;
     update_selfper(h);
-    h->p2p_ready = 0; h->pushed_valid = false; h->push_wait_pending = false;
+    h->p2p_ready = 0; h->pushed_valid = false;
     // message tables depend on which directions are exchanged
     CU(cudaStreamSynchronize(h->s_main));
     CU(cudaStreamSynchronize(h->s_comm));
@@ -671,16 +678,11 @@ extern "C" int b200lb_set_param(b200lb_t * h, const b200lb_param_t * prm) {
 // sweeps
 // ---------------------------------------------------------------------------
 
+// peer-memory halo: how long p2p_sync_kernel waits for a neighbour before it traps
+#define P2P_WATCHDOG_NS 30000000000ULL
+
 // s_main waits for an exchange still running on s_comm
 static int join_comm(b200lb_s * h) {
-  if (h->push_wait_pending) {
-    // neighbours must have finished the sweep that pushed into this rank's halos
-    // (and reading the buffer this rank pushes into next); 10 s watchdog
-    p2p_wait_kernel<<<1, 32, 0, h->s_main>>>(h->p2p, h->push_step, 10000000000ULL);
-    CU(cudaGetLastError());
-    h->launches++;
-    h->push_wait_pending = false;
-  }
   if (h->halo_inflight) {
     CU(cudaStreamWaitEvent(h->s_main, h->ev_halo, 0));
     h->halo_inflight = false;
@@ -778,13 +780,18 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
     if (!h->noise) return fail("isothermal fluctuations are on but noise_init was never called");
     if (h->prm.kt < 0.0) return fail("negative temperature");
   }
+  // rho,u of this collision: stored by it (32 B/site, src/collision.c:570-579), or left to
+  // ensure_hydro. Auto: stored when somebody asked for hydro quantities since the previous
+  // collision -- a caller that looks every step gets the reference's behaviour, a time loop
+  // that only looks at statistics steps does not pay for the store in between.
+  const bool hstore = collide && (h->opt_hydro_write == 1 || (h->opt_hydro_write == 2 && h->hydro_asked));
   a.vec = h->opt_vec;
   a.bx = h->opt_block;
   a.stream = h->s_main;
   if (collide) {
     for (int i = 0; i < 3; i++) a.P.fg[i] = h->prm.force_global[i] + (h->force_uniform ? h->fconst[i] : 0.0);
     if (!h->force_uniform) { if (need_planes(h, &h->force, 3)) return -1; }
-    if (h->opt_hydro_write) { if (need_hydro(h)) return -1; }
+    if (hstore) { if (need_hydro(h)) return -1; }
     if (h->desc.ndist == 2 && h->grad_state == 0) {
       if (need_planes(h, &h->grad, 3) || need_planes(h, &h->delsq, 1)) return -1;
     }
@@ -801,7 +808,7 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
     a.P.force = h->force_uniform ? nullptr : h->force;
     h->last_ffield = !h->force_uniform;
     for (int i = 0; i < 3; i++) h->last_fg[i] = a.P.fg[i];
-    if (h->opt_hydro_write) { a.P.rho = h->rho; a.P.u = h->u; }
+    if (hstore) { a.P.rho = h->rho; a.P.u = h->u; }
     a.P.phi = h->phi;
     if (h->desc.ndist == 2 && h->grad_state == 2) {
       return fail("lb_collide: the order parameter changed after the last field_grad_compute");
@@ -822,6 +829,15 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
   if (push) {
     const int which = (dst == h->lat[0]) ? 0 : 1;
     a.P.push = 1;
+    {
+      // whole-sector stores of the row-end halo sites (site_kernels.cuh): low halo = last
+      // word of an aligned group of four, high halo = first word, everything else in
+      // those groups padding of this row
+      const Layout & L = h->L;
+      const i64 lo = L.z0 + L.h[2] - 1, hi = L.z0 + L.h[2] + L.n[2];
+      a.P.zsec = (L.h[2] == 1 && lo >= 3 && (lo + 1) % 4 == 0 && hi % 4 == 0 && hi + 3 < L.s1
+		  && L.s1 % 4 == 0 && L.s0 % 4 == 0 && L.nsd % 4 == 0) ? 1 : 0;
+    }
     for (int k = 0; k < 27; k++) a.P.peer[k] = h->peer_lat[which][k];
   }
   a.diag = collide && h->opt_diag;
@@ -839,7 +855,10 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
 	h->bnd_valid = true;
       }
     }
+    const bool timed = h->tev_on && h->tev_n + 2 <= h->tev_cap;
+    if (timed) CU(cudaEventRecord(h->tev[h->tev_n], h->s_main));
     CU(h->ops->sweep(a));
+    if (timed) { CU(cudaEventRecord(h->tev[h->tev_n + 1], h->s_main)); h->tev_n += 2; }
     h->launches++;
     if (a.diag) {
       a.P.diag_base += a.nblocks;
@@ -849,17 +868,17 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
   }
   if (push) {
     h->push_step++;
-    p2p_signal_kernel<<<1, 32, 0, h->s_main>>>(h->p2p, h->push_step);
+    p2p_sync_kernel<<<1, 32, 0, h->s_main>>>(h->p2p, h->push_step, P2P_WATCHDOG_NS, 1);
     CU(cudaGetLastError());
     h->launches++;
-    h->push_wait_pending = true;
     h->pushed_valid = true;
   }
   if (pull) h->prop_wall = false;  // the bounce-back belonged to this propagation
   h->halo_deferred = false;        // whatever was written has stale halos until the next lb_halo
   if (collide) {
-    if (h->opt_hydro_write) { h->u_fill_pending = false; h->hydro_stale = false; }
+    if (hstore) { h->u_fill_pending = false; h->hydro_stale = false; }
     else h->hydro_stale = true;
+    h->hydro_asked = false;
   }
   return 0;
 }
@@ -867,6 +886,7 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
 // rho,u that the last collision did not store: recompute them from its
 // post-collision populations, which must still be unstreamed in lat[cur]
 static int ensure_hydro(b200lb_s * h) {
+  h->hydro_asked = true;
   if (!h->hydro_stale) return 0;
   if (join_comm(h)) return -1;
   if (need_hydro(h)) return -1;
@@ -935,6 +955,9 @@ extern "C" int b200lb_wall_commit(b200lb_t * h, const int isboundary[3], const d
     if (h->desc.periodic[a]) return fail("boundary_walls: direction %d is periodic", a);
     if (a >= h->desc.ndim) return fail("boundary_walls: direction %d of a %d-d lattice", a, h->desc.ndim);
   }
+  // src/wall_rt.c:56-60: a wall that moves along x cannot be an x wall
+  if (isboundary[0] && ((ubot && ubot[0] != 0.0) || (utop && utop[0] != 0.0)))
+    return fail("cannot have non-zero u_x wall velocity if the wall is in x");
   if (h->prop_pending) { if (materialise(h)) return -1; }
   for (int a = 0; a < 3; a++) {
     h->wall_is[a] = isboundary[a] ? 1 : 0;
@@ -942,9 +965,6 @@ extern "C" int b200lb_wall_commit(b200lb_t * h, const int isboundary[3], const d
     h->wall_utop[a] = utop ? utop[a] : 0.0;
     h->fnet_host[a] = 0.0;
   }
-  // src/wall_rt.c:56-60: a wall that moves along x cannot be an x wall
-  if (isboundary[0] && (h->wall_ubot[0] != 0.0 || h->wall_utop[0] != 0.0))
-    return fail("cannot have non-zero u_x wall velocity if the wall is in x");
   h->wall_on = any;
   h->wall_slip = 0;
   for (int a = 0; a < 3; a++) { h->wall_sbot[a] = 0.0; h->wall_stop[a] = 0.0; }
@@ -1728,8 +1748,8 @@ extern "C" int b200lb_hydro_u_zero(b200lb_t * h, const double u[3]) {
 extern "C" int b200lb_hydro_rho0(b200lb_t * h, double rho0) {
   if (!h) return fail("null handle");
   if (need_hydro(h)) return -1;
+  if (ensure_hydro(h)) return -1;           // u of the last collision stays current
   const double v[3] = {rho0, 0.0, 0.0};
-  h->hydro_stale = false;
   return fill3(h, h->rho, 1, v);
 }
 
@@ -2090,14 +2110,17 @@ extern "C" int b200lb_step_diag(b200lb_t * h, double out[8]) {
 extern "C" int b200lb_sync(b200lb_t * h) {
   if (!h) return fail("null handle");
   if (join_comm(h)) return -1;
-  CU(cudaStreamSynchronize(h->s_main));
+  {
+    const cudaError_t e = cudaStreamSynchronize(h->s_main);
+    if (e != cudaSuccess) {
+      // the watchdog of p2p_sync_kernel traps: the context is gone and stays gone
+      if (h->p2p_ready) return fail("cudaStreamSynchronize: %s (peer-memory halo: a neighbour that does not reach step %llu within %d s trips the watchdog, which fails closed; every later call fails too)",
+				    cudaGetErrorString(e), h->push_step, (int) (P2P_WATCHDOG_NS/1000000000ULL));
+      return fail("cudaStreamSynchronize: %s", cudaGetErrorString(e));
+    }
+  }
   CU(cudaStreamSynchronize(h->s_x[0]));
   CU(cudaStreamSynchronize(h->s_x[1]));
-  if (h->p2p.flags) {
-    unsigned long long err = 0;
-    CU(cudaMemcpy(&err, h->p2p.flags + 27, sizeof(err), cudaMemcpyDeviceToHost));
-    if (err) return fail("peer-memory halo: a neighbour did not reach step %llu within the watchdog time", err);
-  }
   return 0;
 }
 
@@ -2192,10 +2215,9 @@ extern "C" int b200lb_f_upload(b200lb_t * h, const double * f, int layout) {
     // after that, so the upload takes part in the signal/wait protocol like a sweep:
     // nobody's next sweep starts before every neighbour has finished uploading.
     h->push_step++;
-    p2p_signal_kernel<<<1, 32, 0, h->s_main>>>(h->p2p, h->push_step);
+    p2p_sync_kernel<<<1, 32, 0, h->s_main>>>(h->p2p, h->push_step, P2P_WATCHDOG_NS, 1);
     CU(cudaGetLastError());
     h->launches++;
-    h->push_wait_pending = true;
     h->pushed_valid = false;
   }
   return 0;
@@ -2332,7 +2354,7 @@ extern "C" int b200lb_field_upload(b200lb_t * h, int field, const double * host,
     h->ch_force_pending = false;          // overwritten by this upload
   }
   if (field >= B200LB_FIELD_PHI && field <= B200LB_FIELD_DELSQ) { if (resolve_ch_force(h)) return -1; }
-  if ((field == B200LB_FIELD_U || field == B200LB_FIELD_RHO) && h->hydro_stale) h->hydro_stale = false;
+  if (field == B200LB_FIELD_U || field == B200LB_FIELD_RHO) { if (ensure_hydro(h)) return -1; }   // the other of the two stays current
   if (field == B200LB_FIELD_PHI) {
     h->phi_halo_deferred = false;
     if (h->grad_state == 1) h->grad_state = 2;
@@ -2356,7 +2378,7 @@ static int field_current(b200lb_s * h, int field) {
     if (fill3(h, h->u, 3, h->uconst)) return -1;
     h->u_fill_pending = false;
   }
-  if ((field == B200LB_FIELD_U || field == B200LB_FIELD_RHO) && h->hydro_stale) {
+  if (field == B200LB_FIELD_U || field == B200LB_FIELD_RHO) {
     if (ensure_hydro(h)) return -1;
   }
   if (field == B200LB_FIELD_PHI) { if (flush_phi_halo(h)) return -1; }
@@ -2543,10 +2565,9 @@ extern "C" int b200lb_io_unpack(b200lb_t * h, const double * buf) {
   if (h->p2p_ready && h->opt_p2p) {
     // like lb_memcpy H2D: the restart read takes part in the signal/wait protocol
     h->push_step++;
-    p2p_signal_kernel<<<1, 32, 0, h->s_main>>>(h->p2p, h->push_step);
+    p2p_sync_kernel<<<1, 32, 0, h->s_main>>>(h->p2p, h->push_step, P2P_WATCHDOG_NS, 1);
     CU(cudaGetLastError());
     h->launches++;
-    h->push_wait_pending = true;
     h->pushed_valid = false;
   }
   return 0;
@@ -2631,6 +2652,7 @@ extern "C" int b200lb_p2p_import(b200lb_t * h, const char * all, int nranks) {
     else {
       if (!all) return fail("p2p_import: handles missing");
       if (!opened[r]) {
+        if (h->n_ipc_open + 3 > (int) (sizeof(h->ipc_open)/sizeof(h->ipc_open[0]))) return fail("p2p_import: too many peer mappings");
         cudaIpcMemHandle_t hd[3];
         memcpy(hd, all + (size_t) r*192, 192);
         void * p0 = nullptr, * p1 = nullptr, * p2 = nullptr;
@@ -2647,7 +2669,6 @@ extern "C" int b200lb_p2p_import(b200lb_t * h, const char * all, int nranks) {
   }
   h->p2p_ready = (npeer > 0) ? 1 : 0;
   h->push_step = 0;
-  h->push_wait_pending = false;
   h->pushed_valid = false;
   return 0;
 }
@@ -2670,6 +2691,44 @@ extern "C" int b200lb_timer_stop(b200lb_t * h, float * ms) {
   CU(cudaEventRecord(h->ev1, h->s_main));
   CU(cudaEventSynchronize(h->ev1));
   CU(cudaEventElapsedTime(ms, h->ev0, h->ev1));
+  return 0;
+}
+
+// TIMER_COLLIDE_KERNEL / TIMER_PROP_KERNEL (src/collision.c:198-207, src/propagation.c:84-91):
+// the reference brackets the kernel launch with host timers behind a device synchronise.
+// Here CUDA events are recorded on the launching stream right before and after every sweep
+// launch, so the sum is the time of the sweep kernels alone whatever else a step launches
+// (halo kernels, peer synchronisation, wall slabs count as sweeps of their own).
+extern "C" int b200lb_kernel_timer_start(b200lb_t * h, int max_launches) {
+  if (!h) return fail("null handle");
+  if (max_launches < 1 || max_launches > 65536) return fail("kernel timer: 1..65536 launches");
+  if (2*max_launches > h->tev_cap) {
+    cudaEvent_t * ev = (cudaEvent_t *) realloc(h->tev, sizeof(cudaEvent_t)*2*max_launches);
+    if (!ev) return fail("out of host memory");
+    h->tev = ev;
+    while (h->tev_cap < 2*max_launches) { CU(cudaEventCreate(&h->tev[h->tev_cap])); h->tev_cap++; }
+  }
+  h->tev_n = 0;
+  h->tev_on = true;
+  return 0;
+}
+
+// ms = total time of the sweep launches recorded since b200lb_kernel_timer_start,
+// nlaunch = how many there were; stops the timer
+extern "C" int b200lb_kernel_timer_stop(b200lb_t * h, double * ms, long * nlaunch) {
+  if (!h || !ms || !nlaunch) return fail("null argument");
+  h->tev_on = false;
+  if (join_comm(h)) return -1;
+  CU(cudaStreamSynchronize(h->s_main));
+  double total = 0.0;
+  for (int i = 0; i + 1 < h->tev_n; i += 2) {
+    float t = 0.0f;
+    CU(cudaEventElapsedTime(&t, h->tev[i], h->tev[i + 1]));
+    total += t;
+  }
+  *ms = total;
+  *nlaunch = h->tev_n/2;
+  h->tev_n = 0;
   return 0;
 }
 

@@ -774,7 +774,8 @@ force_correct_kernel(const Layout L, double * __restrict__ force,
 // (peer memory) and wait spins on the local array until every neighbour has
 // reached that step. One rule covers both hazards: a neighbour's pushed values
 // are complete before they are read, and a neighbour has finished reading the
-// buffer this rank is about to push into. The spin has a watchdog (never hangs).
+// buffer this rank is about to push into. The spin has a watchdog (never hangs, and never
+// lets a sweep through: see p2p_sync_kernel).
 // ---------------------------------------------------------------------------
 
 struct P2PSync {
@@ -782,25 +783,33 @@ struct P2PSync {
   unsigned long long * peer_flags[27];   // neighbour's flag array per direction, or null
 };
 
-__global__ void p2p_signal_kernel(const P2PSync S, const unsigned long long step) {
+// signal(step) and wait(step) in ONE launch: between two sweeps of the time loop nothing
+// else sits on the stream, so publishing this rank's step and waiting for the neighbours'
+// back to back is the same protocol with one launch (and one launch gap) less. Every
+// rank signals before it waits: no cycle.
+// The watchdog FAILS CLOSED: a neighbour that does not arrive within timeout_ns leaves the
+// step in flags[27] (read by b200lb_sync for the message) and traps, which poisons the
+// context -- every later CUDA call of this process fails, nothing is ever swept on
+// incomplete halos.
+__global__ void p2p_sync_kernel(const P2PSync S, const unsigned long long step,
+				const unsigned long long timeout_ns, const int do_signal) {
   const int t = threadIdx.x;
   if (t < 27 && S.peer_flags[t] != nullptr) {
-    __threadfence_system();
-    // the neighbour in direction t sees this rank in direction -t = slot 26 - t
-    *((volatile unsigned long long *) (S.peer_flags[t] + (26 - t))) = step;
-  }
-}
-
-__global__ void p2p_wait_kernel(const P2PSync S, const unsigned long long step,
-				const unsigned long long timeout_ns) {
-  const int t = threadIdx.x;
-  if (t < 27 && S.peer_flags[t] != nullptr) {
+    if (do_signal) {
+      __threadfence_system();
+      // the neighbour in direction t sees this rank in direction -t = slot 26 - t
+      *((volatile unsigned long long *) (S.peer_flags[t] + (26 - t))) = step;
+    }
     unsigned long long t0, t1;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
     while (*((volatile unsigned long long *) (S.flags + t)) < step) {
-      __nanosleep(200);
+      __nanosleep(100);
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-      if (t1 - t0 > timeout_ns) { S.flags[27] = step; break; }
+      if (t1 - t0 > timeout_ns) {
+	*((volatile unsigned long long *) (S.flags + 27)) = step;
+	__threadfence_system();
+	__trap();
+      }
     }
   }
   __threadfence_system();

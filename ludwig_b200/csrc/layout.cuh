@@ -40,6 +40,7 @@ struct KParams {
   const double * grad;    // [3][nsd]
   const double * delsq;   // [nsd]
   int push;               // write outgoing populations straight into the neighbours' halo sites
+  int zsec;               // the halo site at either end of a row has a 32-byte sector of its own (rest: padding)
   double * peer[27];      // neighbour's destination lattice per direction (dx+1)*9+(dy+1)*3+(dz+1), or null
   double * diag;          // per-block partial sums of the in-kernel diagnostics, or unused
   i64 diag_base;          // first partial slot of this launch

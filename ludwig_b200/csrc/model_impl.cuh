@@ -37,6 +37,15 @@ static cudaError_t launch_one(SweepArgs & a) {
   dim3 block(bx, by, 1);
   dim3 grid((nt2 + bx - 1)/bx, (n1 + by - 1)/by, n0);
   a.nblocks = (long long) grid.x*grid.y*grid.z;
+  if constexpr (COLLIDE) {
+    if (P.push) {
+      // peer-memory halo: the variants that also store into the neighbours' halo sites
+      if (a.diag) lb_sweep_kernel<MODEL, VEC, PULL, COLLIDE, BINARY, GM, true, WALL, true><<<grid, block, 0, a.stream>>>(P);
+      else lb_sweep_kernel<MODEL, VEC, PULL, COLLIDE, BINARY, GM, false, WALL, true><<<grid, block, 0, a.stream>>>(P);
+      return cudaGetLastError();
+    }
+  }
+  if (P.push) return cudaErrorInvalidValue;
   if (COLLIDE && a.diag) {
     lb_sweep_kernel<MODEL, VEC, PULL, COLLIDE, BINARY, GM, COLLIDE, WALL>
       <<<grid, block, 0, a.stream>>>(P);

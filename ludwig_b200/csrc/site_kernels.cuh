@@ -334,8 +334,10 @@ fluctuations(unsigned int (&w)[4], const KParams & P,
 // the aligned pair), all others and every store are 128-bit.
 // ---------------------------------------------------------------------------
 
-template <class M, int VEC, bool PULL, bool COLLIDE, bool BINARY, int GM, bool DIAG, bool WALL = false>
-__global__ void __launch_bounds__(256)
+// PUSH: the peer-memory halo rides on this sweep (its own instantiations: the kernels of a
+// single-GPU run carry none of that code and keep their register count)
+template <class M, int VEC, bool PULL, bool COLLIDE, bool BINARY, int GM, bool DIAG, bool WALL = false, bool PUSH = false>
+__global__ void __launch_bounds__(256, PUSH ? 2 : 0)
 lb_sweep_kernel(const KParams P) {
 
   constexpr int Q  = M::NVEL;
@@ -615,7 +617,7 @@ lb_sweep_kernel(const KParams P) {
   // the transfer rides on the sweep itself. Same population set as the reduced
   // scheme (src/model.c:1192-1219): p goes to direction s iff s picks components of
   // c_p and the site lies on the boundary in each picked component.
-  if (COLLIDE && P.push) {
+  if constexpr (COLLIDE && PUSH) {
     #pragma unroll
     for (int v = 0; v < VEC; v++) {
       if (v < nv) {
@@ -623,7 +625,73 @@ lb_sweep_kernel(const KParams P) {
 	e[0] = (i0 == 0) ? -1 : ((i0 == L.n[0] - 1) ? 1 : 0);
 	e[1] = (i1 == 0) ? -1 : ((i1 == L.n[1] - 1) ? 1 : 0);
 	e[2] = (i2 + v == 0) ? -1 : ((i2 + v == L.n[2] - 1) ? 1 : 0);
-	if (e[0] | e[1] | e[2]) {
+	const int ne = (e[0] != 0) + (e[1] != 0) + (e[2] != 0);
+	if (ne == 1) {
+	  // A site on one face only (all but the edges of the box): the populations with
+	  // that component go to ONE neighbour, at one offset. Six short branches with
+	  // compile-time population lists instead of the general 7-way loop below --
+	  // along the contiguous axis every row ends in such a site, so half of all warps
+	  // come through here (profiles/r2_push_axes_before.log: 45 us per 256^3 step
+	  // through the general loop).
+	  #pragma unroll
+	  for (int d = 0; d < 3; d++) {
+	    if (e[d] != 0) {
+	      const int sd = e[d];
+	      const int kdir = 13 + sd*((d == 0) ? 9 : ((d == 1) ? 3 : 1));
+	      double * peer = P.peer[kdir];
+	      if (peer != nullptr) {
+		const i64 ext = (d == 0) ? (i64) L.n[0]*L.s0 : ((d == 1) ? (i64) L.n[1]*L.s1 : (i64) L.n[2]);
+		double * base = peer + site + v - sd*ext;
+		if (d == 2 && P.zsec) {
+		  // The contiguous axis: each row ends in ONE halo site, whose 32-byte sector
+		  // holds nothing else but row padding. An 8-byte store leaves a partially
+		  // written sector, which HBM (ECC) turns into a read-modify-write: 2 n_x n_y
+		  // x 5 of them per step cost 39 us at 256^3 (profiles/r2_push_axes_after.log).
+		  // Store the whole sector instead -- the halo value and three padding words
+		  // nobody reads -- as one 256-bit store (also one NVLink packet, not a
+		  // quarter-filled one).
+		  #pragma unroll
+		  for (int n = 0; n < NDIST; n++) {
+		    #pragma unroll
+		    for (int p = 1; p < Q; p++) {
+		      if (dcv<M>(p, 2) == 1 || dcv<M>(p, 2) == -1) {
+			if (dcv<M>(p, 2) == sd) {
+			  double * a = base + (i64)(n*Q + p)*L.nsd;
+			  const double val = f[n][v][p];
+			  if (sd == 1) {   // lands in the low halo: last word of its sector
+			    asm volatile("st.global.v4.f64 [%0], {%1, %1, %1, %2};" :: "l"(a - 3), "d"(0.0), "d"(val) : "memory");
+			  }
+			  else {           // lands in the high halo: first word of its sector
+			    asm volatile("st.global.v4.f64 [%0], {%2, %1, %1, %1};" :: "l"(a), "d"(0.0), "d"(val) : "memory");
+			  }
+			}
+		      }
+		    }
+		  }
+		}
+		else if (sd == 1) {
+		  #pragma unroll
+		  for (int n = 0; n < NDIST; n++) {
+		    #pragma unroll
+		    for (int p = 1; p < Q; p++) {
+		      if (dcv<M>(p, d) == 1) base[(i64)(n*Q + p)*L.nsd] = f[n][v][p];
+		    }
+		  }
+		}
+		else {
+		  #pragma unroll
+		  for (int n = 0; n < NDIST; n++) {
+		    #pragma unroll
+		    for (int p = 1; p < Q; p++) {
+		      if (dcv<M>(p, d) == -1) base[(i64)(n*Q + p)*L.nsd] = f[n][v][p];
+		    }
+		  }
+		}
+	      }
+	    }
+	  }
+	}
+	else if (ne > 1) {
 	  #pragma unroll
 	  for (int n = 0; n < NDIST; n++) {
 	    #pragma unroll

@@ -44,7 +44,7 @@ ABI_SYMBOLS = [
     "b200lb_field_stats", "b200lb_field_stats_noalloc", "b200lb_io_record_doubles", "b200lb_io_pack", "b200lb_io_unpack",
     "b200lb_step", "b200lb_stats", "b200lb_step_diag", "b200lb_sync", "b200lb_nccl_unique_id",
     "b200lb_comm_init", "b200lb_p2p_export", "b200lb_p2p_import", "b200lb_timer_start", "b200lb_timer_stop",
-    "b200lb_launch_count", "b200lb_host_alloc", "b200lb_host_free",
+    "b200lb_launch_count", "b200lb_kernel_timer_start", "b200lb_kernel_timer_stop", "b200lb_host_alloc", "b200lb_host_free",
 ]
 
 
@@ -152,6 +152,8 @@ def load():
     L.b200lb_stats.argtypes = [vp, ctypes.POINTER(ctypes.c_double)]
     L.b200lb_step_diag.argtypes = [vp, ctypes.POINTER(ctypes.c_double)]
     L.b200lb_timer_stop.argtypes = [vp, ctypes.POINTER(ctypes.c_float)]
+    L.b200lb_kernel_timer_start.argtypes = [vp, ctypes.c_int]
+    L.b200lb_kernel_timer_stop.argtypes = [vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_long)]
     L.b200lb_nccl_unique_id.argtypes = [ctypes.c_char_p]
     L.b200lb_comm_init.argtypes = [vp, ctypes.c_char_p]
     L.b200lb_p2p_export.argtypes = [vp, ctypes.c_char_p]
@@ -487,6 +489,16 @@ class Lattice:
 
     def launch_count(self):
         return int(self.L.b200lb_launch_count(self.h))
+
+    def kernel_timer_start(self, max_launches=4096):
+        """TIMER_COLLIDE_KERNEL: CUDA events around every sweep launch from here on."""
+        self._ck(self.L.b200lb_kernel_timer_start(self.h, int(max_launches)))
+
+    def kernel_timer_stop(self):
+        """(ms summed over the sweep launches since kernel_timer_start, how many)."""
+        ms, n = ctypes.c_double(), ctypes.c_long()
+        self._ck(self.L.b200lb_kernel_timer_stop(self.h, ctypes.byref(ms), ctypes.byref(n)))
+        return float(ms.value), int(n.value)
 
     @staticmethod
     def nccl_unique_id():

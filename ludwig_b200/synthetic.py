@@ -76,3 +76,19 @@ def make_force(nlocal, ntotal=None, offset=(0, 0, 0), amp=1.0e-3, ndim=3):
     for a in range(ndim):
         force[:, a] = amp * uniform(ids, 80 + a)
     return force
+
+
+def tiled_state(cv, wv, nlocal, ndist=1, ndim=3, block=(37, 41, 43)):
+    """A large input in seconds: the interior is a seeded block with pairwise coprime edges,
+    repeated and cropped (no two sites a power of two apart see the same data); halo sites
+    stay zero (lb_halo fills them). f [nsite, ndist, nvel] in the reference host layout."""
+    nvel = len(wv)
+    blk = tuple(min(block[a], nlocal[a]) for a in range(3))
+    small = make_state(cv, wv, blk, ndist=ndist, ndim=ndim)
+    ball = tuple(b + 2 for b in blk)
+    small = small.reshape(ball + (ndist, nvel))[1:-1, 1:-1, 1:-1]
+    reps = tuple(-(-nlocal[a]//blk[a]) for a in range(3))
+    nall = tuple(n + 2 for n in nlocal)
+    f0 = np.zeros(nall + (ndist, nvel))
+    f0[1:-1, 1:-1, 1:-1] = np.tile(small, reps + (1, 1))[:nlocal[0], :nlocal[1], :nlocal[2]]
+    return f0.reshape(-1, ndist, nvel)

@@ -57,6 +57,39 @@ def floats(line):
     return [float(x) for x in re.findall(r"[-+]?\d+\.\d+(?:[eE][-+]?\d+)?", line)]
 
 
+def parse_block(lines):
+    """The statistics block printed after the last time step of a Ludwig log."""
+    start = max(i for i, l in enumerate(lines) if l.startswith("Scalars - total"))
+    blk = lines[start:start + 20]
+    rec = {"_start": start}
+    for l in blk:
+        if l.startswith("[rho]"):
+            rec["rho"] = floats(l)                 # total mean variance min max
+        if l.startswith("[phi]"):
+            rec["phi"] = floats(l)                 # total mean variance min max
+        if l.startswith("[fe]"):
+            rec["fe"] = floats(l)                  # with walls: f, v, f/v, f_s1, f_s2
+        if l.startswith("[fed]"):
+            rec["fed"] = floats(l)                 # total/volume, fluid mean
+        if l.startswith("[total   ]"):
+            rec["momentum"] = floats(l)
+        if l.startswith("[fluid   ]"):
+            rec["momentum_fluid"] = floats(l)
+        if l.startswith("[walls   ]"):
+            rec["momentum_walls"] = floats(l)
+        if l.startswith("[vol flux]"):
+            rec["vol_flux"] = floats(l)
+        if l.startswith("[minimum ]"):
+            rec["umin"] = floats(l)
+        if l.startswith("[maximum ]"):
+            rec["umax"] = floats(l)
+        if l.startswith("[eqipart.]"):
+            rec["eqipart"] = floats(l)             # isothermal fluctuations
+        if l.startswith("[measd/kT]"):
+            rec["measd_kt"] = floats(l)
+    return rec
+
+
 def main():
     out = {}
     for case in CASES:
@@ -68,35 +101,11 @@ def main():
             parts = line.split()
             inp[parts[0]] = parts[1] if len(parts) > 1 else ""
         lines = open(os.path.join(REF, case + ".log")).read().splitlines()
-        start = max(i for i, l in enumerate(lines) if l.startswith("Scalars - total"))
-        blk = lines[start:start + 20]
-        rec = {"input": inp, "nvel": NVEL[case.split("/")[0]],
-               "source": "tests/regression/%s.log:%d-%d" % (case, start + 1, start + 10)}
-        for l in blk:
-            if l.startswith("[rho]"):
-                rec["rho"] = floats(l)                 # total mean variance min max
-            if l.startswith("[phi]"):
-                rec["phi"] = floats(l)                 # total mean variance min max
-            if l.startswith("[fe]"):
-                rec["fe"] = floats(l)                  # with walls: f, v, f/v, f_s1, f_s2
-            if l.startswith("[fed]"):
-                rec["fed"] = floats(l)                 # total/volume, fluid mean
-            if l.startswith("[total   ]"):
-                rec["momentum"] = floats(l)
-            if l.startswith("[fluid   ]"):
-                rec["momentum_fluid"] = floats(l)
-            if l.startswith("[walls   ]"):
-                rec["momentum_walls"] = floats(l)
-            if l.startswith("[vol flux]"):
-                rec["vol_flux"] = floats(l)
-            if l.startswith("[minimum ]"):
-                rec["umin"] = floats(l)
-            if l.startswith("[maximum ]"):
-                rec["umax"] = floats(l)
-            if l.startswith("[eqipart.]"):
-                rec["eqipart"] = floats(l)             # isothermal fluctuations
-            if l.startswith("[measd/kT]"):
-                rec["measd_kt"] = floats(l)
+        rec = parse_block(lines)
+        start = rec.pop("_start")
+        rec["input"] = inp
+        rec["nvel"] = NVEL[case.split("/")[0]]
+        rec["source"] = "tests/regression/%s.log:%d-%d" % (case, start + 1, start + 10)
         out[case.split('/')[1]] = rec
     with open(os.path.join(HERE, "regression_logs.json"), "w") as fh:
         json.dump(out, fh, indent=1)

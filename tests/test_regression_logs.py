@@ -28,6 +28,9 @@ import lbinit
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 GOLD = json.load(open(os.path.join(HERE, "golden", "regression_logs.json")))
+# BASELINE configurations the reference ships no log for: made by the unmodified reference
+# executable (tests/golden/make_named_size_golden.py), same record format
+GOLD.update(json.load(open(os.path.join(HERE, "golden", "named_size_logs.json"))))
 FLT_MAX, FLT_MIN = 3.4028234663852886e+38, 1.1754943508222875e-38
 # the finite-difference order-parameter cases (the newest kernels) last
 CASES = sorted(GOLD, key=lambda c: (GOLD[c]["input"].get("free_energy") == "symmetric", c))
@@ -358,8 +361,8 @@ NOT_ON_DEVICE = {"serial-spin-fd2"}
 # over 6e5 populations a plain sum is 1e-12 away. That shows where a printed digit sits on a
 # rounding boundary: the y momentum of this log is 3.41278045e-04 printed as "%14.7e".
 HALFWAY = {"serial-le3d-st4"}
-LONG = {"pmpi08-spin-lb1", "pmpi08-spin-fd1", "pmpi08-le3d-fd1", "pmpi08-le3d-lb1"}      # 400 steps: the momentum line is accumulated round-off
-SLOW = {"pmpi08-spin-lb1", "pmpi08-le3d-fd1", "pmpi08-le3d-lb1"}      # minutes on the CPU oracle: opt in with B200LB_LONG=1 (fd1 takes half a minute)
+LONG = {"pmpi08-spin-lb1", "pmpi08-spin-fd1", "pmpi08-le3d-fd1", "pmpi08-le3d-lb1", "named-spin-lb1-7pt-128"}      # 400 steps: the momentum line is accumulated round-off
+SLOW = {"pmpi08-spin-lb1", "pmpi08-le3d-fd1", "pmpi08-le3d-lb1", "named-spin-lb1-7pt-128"}      # minutes on the CPU oracle: opt in with B200LB_LONG=1 (fd1 takes half a minute)
 
 
 @pytest.mark.parametrize("case", CASES)
