@@ -47,6 +47,8 @@ def main():
     ap.add_argument("--fd", type=int, default=0,
                     help="free_energy symmetric: finite-difference order parameter, advection of this order")
     ap.add_argument("--visc", type=int, default=0, help="with --fd: viscosity_model arrhenius")
+    ap.add_argument("--grid", type=int, nargs=3, default=None,
+                    help="process grid (default: 2x1x1, 2x2x1, 2x2x2 by number of ranks)")
     args = ap.parse_args()
 
     rank = int(os.environ["RANK"])
@@ -65,6 +67,9 @@ def main():
         grid = {1: (1, 1, 1), 2: (2, 1, 1), 4: (2, 1, 2), 8: (4, 1, 2)}[world]
         if ndim == 2:
             grid = (world, 1, 1)
+    if args.grid:
+        grid = tuple(args.grid)
+        assert grid[0]*grid[1]*grid[2] == world, "--grid does not match the number of ranks"
     local = tuple(args.lsize)
     ntotal = tuple(local[a] * grid[a] for a in range(3))
     walls = tuple(args.walls)

@@ -61,3 +61,19 @@ def test_decomposed_equals_single(n, extra):
     if ngpu() < n:
         pytest.skip("needs %d GPUs" % n)
     launch(n, extra, 29600 + n)
+
+
+@pytest.mark.parametrize("extra", [
+    # two ranks along the CONTIGUOUS direction: row-end halo sites written into the
+    # neighbour's memory as whole 32-byte sectors; and along y
+    ["--nvel", "19", "--halo", "reduced", "--grid", "1", "1", "2", "--lsize", "8", "6", "32"],
+    ["--nvel", "19", "--halo", "reduced", "--grid", "1", "1", "2", "--lsize", "6", "5", "16", "--fused", "0"],
+    ["--nvel", "19", "--ndist", "2", "--halo", "full", "--grid", "1", "1", "2", "--lsize", "8", "6", "32"],
+    ["--nvel", "27", "--halo", "reduced", "--grid", "1", "1", "2", "--lsize", "6", "6", "48"],
+    ["--nvel", "9", "--halo", "reduced", "--grid", "1", "2", "1", "--lsize", "16", "32", "1"],
+    ["--nvel", "19", "--halo", "reduced", "--grid", "1", "2", "1", "--lsize", "8", "6", "32", "--kt", "1e-4"],
+])
+def test_two_ranks_along_other_axes(extra):
+    if ngpu() < 2:
+        pytest.skip("needs 2 GPUs")
+    launch(2, extra, 29650)
