@@ -41,7 +41,7 @@ def parse():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--nvel", type=int, default=19)
-    ap.add_argument("--local", type=int, nargs=3, default=None,
+    ap.add_argument("--local", "--lsize", dest="local", type=int, nargs=3, default=None,
                     help="local lattice per GPU (default 256 256 256; D2Q9 4096 4096 1)")
     ap.add_argument("--global-size", type=int, nargs=3, default=None,
                     help="strong scaling: this global lattice divided over the grid")
@@ -561,15 +561,24 @@ def main():
     mode = args.init
     if mode == "auto":
         mode = "seeded" if sites_local <= 2.0**24 else "tiled"
-    f0 = make_input(nvel, ndist, local, ntotal, dec.offset, mode)
-    lat.lb_memcpy_h2d(f0)
+    lattice_bytes = float(np.prod([n + 2 for n in local])) * ndist * nvel * 8
+    if lattice_bytes > 12.0e9:
+        # a host copy of the whole lattice (plus what numpy needs to build it) times the ranks of
+        # the box would not fit: x-slabs of the tiled input, uploaded piece by piece
+        from ludwig_b200 import models_host, synthetic
+        mode, f0 = "tiled, uploaded in x-slabs", None
+        for first, part in synthetic.tiled_slabs(models_host.cv(nvel), models_host.wv(nvel), local,
+                                                 ndist=ndist, ndim=ndim):
+            lat.lb_memcpy_h2d_range(part, first)
+    else:
+        f0 = make_input(nvel, ndist, local, ntotal, dec.offset, mode)
+        lat.lb_memcpy_h2d(f0)
     if args.fd:
         rng = np.random.default_rng(8361235 + rank)      # spinodal start: phi = 0.1 (r - 1/2)
         phi0 = np.zeros(tuple(n + 2 for n in local))
         phi0[1:-1, 1:-1, 1:-1] = 0.1 * (rng.random(local) - 0.5)
         lat.field_h2d(lb.FIELD_PHI, np.ascontiguousarray(phi0.reshape(-1)))
         del phi0
-    lattice_bytes = f0.nbytes
     sums0 = comm.sum(lat.stats()[:7])                    # mass, ., ., ., momentum before
 
     # ---- device-resident throughput: the whole step, and the sweep alone -------------
@@ -625,7 +634,7 @@ def main():
     # AOS layout; lb_memcpy H2D, then every step = the hot path + the conserved sums of that
     # step read back to the host (gathered inside the collision sweep), then lb_memcpy D2H.
     e2e = None
-    if not args.no_e2e:
+    if not args.no_e2e and f0 is not None:
         hbuf = lb.pinned_empty(f0.shape)
         hbuf[...] = f0
         lat.set_option("diag", 1)

@@ -15,6 +15,9 @@
  *   - host arrays use the reference's host layouts (src/memory.h:124-130,187):
  *       B200LB_HOST_AOS  f[(index*ndist + n)*nvel + p]   (default host build)
  *       B200LB_HOST_SOA  f[(n*nvel + p)*nsite + index]   (-DADDR_SOA builds)
+ *       B200LB_HOST_AOSOA(V)  f[((index/V)*ndist*nvel + n*nvel + p)*V + index%V]
+ *                        (-DADDR_AOSOA -DVVL=V builds, src/memory.h:260-284: blocks of V sites;
+ *                        nsite must be a multiple of V)
  *     rank-1 fields (u, force, grad) likewise [index*3 + a] or [a*nsite + index];
  *     index = cs_index(ic,jc,kc) over the halo-inclusive local box with
  *     nhalo = 1 (src/coords.c:617-631). The device layout is private.
@@ -32,7 +35,8 @@ extern "C" {
 
 #define B200LB_NVELMAX 27
 
-enum { B200LB_HOST_AOS = 0, B200LB_HOST_SOA = 1 };
+enum { B200LB_HOST_AOS = 0, B200LB_HOST_SOA = 1, B200LB_HOST_AOSOA_BASE = 256 };
+#define B200LB_HOST_AOSOA(V) (B200LB_HOST_AOSOA_BASE + (V))
 
 /* lb_relaxation_enum_t, src/lb_data_options.h:18-23 */
 enum { B200LB_RELAX_M10 = 0, B200LB_RELAX_BGK = 1, B200LB_RELAX_TRT = 2 };
@@ -147,6 +151,11 @@ long b200lb_get_option(const b200lb_t * h, const char * name);
 /* lb_memcpy (src/model.c:228), hydro_memcpy (src/hydro.c:154), field_memcpy,
  * field_grad_memcpy: layout boundary between host arrays and the device. */
 int  b200lb_f_upload(b200lb_t * h, const double * f_host, int host_layout);
+/* lb_io_read piecewise (src/model.c:1568-1649 goes through an aggregator buffer, never one
+ * array for the whole lattice): host sites [first, first + count) in the AOS layout,
+ * f[(site - first)*ndist*nvel + n*nvel + p]. Pieces follow each other from site 0 to
+ * b200lb_nsite(); a 514^3 lattice (20.6 GB) then needs no 20.6 GB host array. */
+int  b200lb_f_upload_range(b200lb_t * h, const double * f, long first, long count);
 int  b200lb_f_download(b200lb_t * h, double * f_host, int host_layout);
 int  b200lb_field_upload(b200lb_t * h, int field, const double * host, int host_layout);
 int  b200lb_field_download(b200lb_t * h, int field, double * host, int host_layout);

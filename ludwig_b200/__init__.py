@@ -7,7 +7,7 @@ creating a lattice needs a CUDA device and the built library.
 
 from .lb import (Lattice, Param, B200LBError, build, library_path, load,  # noqa: F401
                  pinned_empty, pinned_free,
-                 HOST_AOS, HOST_SOA, RELAX_M10, RELAX_BGK, RELAX_TRT,
+                 HOST_AOS, HOST_SOA, HOST_AOSOA, RELAX_M10, RELAX_BGK, RELAX_TRT,
                  HALO_FULL, HALO_REDUCED, FIELD_RHO, FIELD_U, FIELD_FORCE,
                  FIELD_PHI, FIELD_GRAD, FIELD_DELSQ, FIELD_ETA, ABI_SYMBOLS,
                  FORCE_NONE, FORCE_STRESS_DIVERGENCE, FORCE_PHI_GRADMU)

@@ -7,6 +7,7 @@
 #include <cuda_runtime.h>
 #include <dlfcn.h>
 #include <nccl.h>
+#include <nvtx3/nvToolsExt.h>     // header-only; ranges show up in Nsight Systems / ncu --nvtx
 
 #include <cmath>
 #include <cstdarg>
@@ -84,6 +85,13 @@ static int nccl_load(void) {
 
 #define NC(call) do { ncclResult_t r_ = (call); if (r_ != ncclSuccess) \
   return fail("%s:%d %s: %s", __FILE__, __LINE__, #call, g_nccl.GetErrorString(r_)); } while (0)
+
+// NVTX range over a scope: the stages of the time step by the names Ludwig's timers use
+// (src/timer.h:47-63), so a timeline reads like its timer report
+struct NvtxRange {
+  explicit NvtxRange(const char * name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+};
 
 // ---------------------------------------------------------------------------
 // handle
@@ -760,6 +768,8 @@ static int wall_boxes(const b200lb_s * h, const KParams & P, int lo[7][3], int h
 
 static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
 		     double * dst) {
+  NvtxRange nvtx_(collide ? (pull ? "b200lb: Collision + Propagation (fused sweep)" : "b200lb: Collision (krnl)")
+		  : "b200lb: Propagtn (krnl)");
   if (join_comm(h)) return -1;
   SweepArgs a;
   site_kparams(h, a.P);
@@ -1517,6 +1527,7 @@ static int lattice_exchange(b200lb_s * h, int scheme, cudaStream_t st) {
 // each pass spans the full extent of the other axes and overwrites what an
 // earlier pass could not know yet.
 static int lattice_halo(b200lb_s * h, int scheme) {
+  NvtxRange nvtx_("b200lb: Lattice halos");
   if (!h->opt_halo_lazy) {
     if (join_comm(h)) return -1;
     return halo_exchange(h, h->lat[h->cur], true, h->nplane, scheme, 0, h->s_main);
@@ -1591,6 +1602,7 @@ static int le_grad_fix(b200lb_s * h, int npt) {
 }
 
 static int run_grad7(b200lb_s * h) {
+  NvtxRange nvtx_("b200lb: phi gradients (7 point)");
   const Layout & L = h->L;
   if (need_planes(h, &h->grad, 3) || need_planes(h, &h->delsq, 1)) return -1;
   dim3 block(GRAD_TZ, GRAD_TY, 1);
@@ -1608,6 +1620,7 @@ static int run_grad7(b200lb_s * h) {
 }
 
 static int run_grad27(b200lb_s * h) {
+  NvtxRange nvtx_("b200lb: phi gradients (27 point)");
   const Layout & L = h->L;
   if (h->desc.ndim != 3) return fail("the 27-point gradient is three-dimensional (ndim = %d)", h->desc.ndim);
   if (need_planes(h, &h->grad, 3) || need_planes(h, &h->delsq, 1)) return -1;
@@ -1657,6 +1670,7 @@ extern "C" int b200lb_grad27_solid(b200lb_t * h) {
 
 extern "C" int b200lb_phi_halo(b200lb_t * h) {
   if (!h) return fail("null handle");
+  NvtxRange nvtx_("b200lb: phi halos");
   if (!h->phi) return fail("no order parameter (ndist = 1)");
   if (join_comm(h)) return -1;
   if (!h->opt_halo_lazy) return halo_exchange(h, h->phi, false, 1, B200LB_HALO_FULL, 0, h->s_main);
@@ -1679,6 +1693,7 @@ static int flush_phi_halo(b200lb_s * h) {
 
 extern "C" int b200lb_phi_from_g(b200lb_t * h) {
   if (!h) return fail("null handle");
+  NvtxRange nvtx_("b200lb: phi_lb_to_field");
   if (!h->phi || h->desc.ndist != 2) return fail("no order parameter distribution (ndist = 1)");
   // the bounce-back of a pending propagation is part of what phi sums: stream first
   if (h->prop_pending && h->prop_wall) { if (materialise(h)) return -1; }
@@ -2076,6 +2091,7 @@ extern "C" int b200lb_step(b200lb_t * h, int nsteps) {
 
 extern "C" int b200lb_stats(b200lb_t * h, double out[8]) {
   if (!h || !out) return fail("null argument");
+  NvtxRange nvtx_("b200lb: stats_distribution");
   if (materialise(h)) return -1;
   if (join_comm(h)) return -1;
   const Layout & L = h->L;
@@ -2138,7 +2154,27 @@ static int ensure_stage(b200lb_s * h) {
 
 // nel planes starting at device plane e0 of `dev`; host array `host` holds them
 // in `layout` for all nsite_host sites
+// sites [first, first + count) of the host index space; `host` points at the first of them
+static int transfer_range(b200lb_s * h, double * dev, int nel, double * host, int layout, bool to_device,
+			  i64 first, i64 count);
+
 static int transfer(b200lb_s * h, double * dev, int nel, double * host, int layout, bool to_device) {
+  return transfer_range(h, dev, nel, host, layout, to_device, 0, h->nsite_host);
+}
+
+static int transfer_range(b200lb_s * h, double * dev, int nel, double * host, int layout, bool to_device,
+			  i64 first, i64 count) {
+  NvtxRange nvtx_(to_device ? "b200lb: memcpy host to device (layout conversion)" : "b200lb: memcpy device to host (layout conversion)");
+  if (first < 0 || count < 0 || first + count > h->nsite_host) return fail("site range [%lld, %lld) outside the %ld host sites", (long long) first, (long long) (first + count), h->nsite_host);
+  if (count != h->nsite_host && layout != B200LB_HOST_AOS) return fail("a range of sites is moved in the AOS layout only");
+  int vvl = 0;
+  if (layout > B200LB_HOST_AOSOA_BASE) {
+    // -DADDR_AOSOA -DVVL=V (src/memory.h:260-284): AOS over blocks of V sites
+    vvl = layout - B200LB_HOST_AOSOA_BASE;
+    if (vvl < 2 || vvl > 64) return fail("AoSoA host layout: block length %d (VVL 2..64)", vvl);
+    if (h->nsite_host % vvl) return fail("AoSoA host layout: %ld sites are not a multiple of the block length %d", h->nsite_host, vvl);
+    layout = B200LB_HOST_AOS;
+  }
   if (ensure_stage(h)) return -1;
   if (join_comm(h)) return -1;
   CU(cudaStreamSynchronize(h->s_main));
@@ -2150,21 +2186,23 @@ static int transfer(b200lb_s * h, double * dev, int nel, double * host, int layo
   const i64 ns = h->nsite_host;
   int turn = 0;
   if (layout == B200LB_HOST_AOS) {
-    const i64 chunk = (i64) (STAGE_BYTES/sizeof(double))/nel;
-    X.aos = 1; X.nel = nel; X.e0 = 0;
-    for (i64 s0 = 0; s0 < ns; s0 += chunk, turn ^= 1) {
-      const i64 s1 = (s0 + chunk < ns) ? s0 + chunk : ns;
+    i64 chunk = (i64) (STAGE_BYTES/sizeof(double))/nel;
+    if (vvl > 1) chunk = chunk/vvl*vvl;       // pieces start on a block boundary
+    X.aos = 1; X.nel = nel; X.e0 = 0; X.vvl = vvl;
+    const i64 last = first + count;
+    for (i64 s0 = first; s0 < last; s0 += chunk, turn ^= 1) {
+      const i64 s1 = (s0 + chunk < last) ? s0 + chunk : last;
       cudaStream_t st = h->s_x[turn];
       X.stage = h->stage[turn]; X.hs0 = s0; X.hs1 = s1;
       const size_t nb = (size_t) (s1 - s0)*nel*sizeof(double);
       const unsigned nblk = (unsigned) ((s1 - s0 + 255)/256);
       if (to_device) {
-	CU(cudaMemcpyAsync(X.stage, host + s0*nel, nb, cudaMemcpyHostToDevice, st));
+	CU(cudaMemcpyAsync(X.stage, host + (s0 - first)*nel, nb, cudaMemcpyHostToDevice, st));
 	xfer_kernel<1><<<nblk, 256, 0, st>>>(X);
       }
       else {
 	xfer_kernel<0><<<nblk, 256, 0, st>>>(X);
-	CU(cudaMemcpyAsync(host + s0*nel, X.stage, nb, cudaMemcpyDeviceToHost, st));
+	CU(cudaMemcpyAsync(host + (s0 - first)*nel, X.stage, nb, cudaMemcpyDeviceToHost, st));
       }
       CU(cudaGetLastError());
       h->launches++;
@@ -2214,6 +2252,32 @@ extern "C" int b200lb_f_upload(b200lb_t * h, const double * f, int layout) {
     // The upload wrote this rank's halo sites too. Neighbours may push into them only
     // after that, so the upload takes part in the signal/wait protocol like a sweep:
     // nobody's next sweep starts before every neighbour has finished uploading.
+    h->push_step++;
+    p2p_sync_kernel<<<1, 32, 0, h->s_main>>>(h->p2p, h->push_step, P2P_WATCHDOG_NS, 1);
+    CU(cudaGetLastError());
+    h->launches++;
+    h->pushed_valid = false;
+  }
+  return 0;
+}
+
+// lb_io_read in pieces (src/model.c:1568-1649 reads the lattice through an aggregator buffer,
+// never as one array): host sites [first, first + count) of the AOS layout, f pointing at the
+// first of them. The first piece (first = 0) resets the lattice state like b200lb_f_upload;
+// the caller uploads every site before it steps.
+extern "C" int b200lb_f_upload_range(b200lb_t * h, const double * f, long first, long count) {
+  if (!h || !f) return fail("null argument");
+  if (first == 0) {
+    if (ensure_hydro(h)) return -1;
+    h->prop_pending = false;
+    h->jphi_valid = false;
+    h->bbl_armed = false;
+    h->prop_wall = false;
+    h->halo_deferred = false;
+  }
+  if (transfer_range(h, h->lat[h->cur], h->nplane, const_cast<double *>(f), B200LB_HOST_AOS, true, first, count)) return -1;
+  if (first + count == h->nsite_host && h->p2p_ready && h->opt_p2p) {
+    // the last piece: like b200lb_f_upload, the upload takes part in the peer protocol
     h->push_step++;
     p2p_sync_kernel<<<1, 32, 0, h->s_main>>>(h->p2p, h->push_step, P2P_WATCHDOG_NS, 1);
     CU(cudaGetLastError());

@@ -593,6 +593,8 @@ struct XferParams {
   int aos;
   int hoff[3];        // added to the decoded host coordinates: 0 = the host index space is
                       // the halo-inclusive box, 1 = interior sites only (file records)
+  int vvl;            // AOS piece in blocks of vvl sites (the reference's -DADDR_AOSOA -DVVL=vvl,
+                      // src/memory.h:260-284): element e of site s sits at ((s/vvl)*nel + e)*vvl + s%vvl
   int half;           // SOA piece of 32-bit words: 1 = low, 2 = high half of the 64-bit device
                       // element, stage holds unsigned ints (noise state); 0 = doubles
 };
@@ -619,10 +621,13 @@ xfer_kernel(const XferParams X) {
   const i64 site = (i64) dc[0]*L.s0 + (i64) dc[1]*L.s1 + L.z0 + dc[2];
   if (TO_DEVICE && !primary) return;
   if (X.aos) {
-    double * st = X.stage + (hs - X.hs0)*X.nel;
+    // pieces start on a block boundary, so the block arithmetic is local to the piece
+    const i64 l = hs - X.hs0;
+    const i64 es = (X.vvl > 1) ? X.vvl : 1;
+    double * st = (X.vvl > 1) ? X.stage + (l/X.vvl)*X.nel*X.vvl + l%X.vvl : X.stage + l*X.nel;
     for (int e = 0; e < X.nel; e++) {
-      if (TO_DEVICE) X.dev[(i64)(X.e0 + e)*L.nsd + site] = st[e];
-      else st[e] = X.dev[(i64)(X.e0 + e)*L.nsd + site];
+      if (TO_DEVICE) X.dev[(i64)(X.e0 + e)*L.nsd + site] = st[e*es];
+      else st[e*es] = X.dev[(i64)(X.e0 + e)*L.nsd + site];
     }
   }
   else if (X.half) {

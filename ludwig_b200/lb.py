@@ -19,6 +19,13 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIBPATH = os.path.join(_HERE, "libb200lb.so")
 
 HOST_AOS, HOST_SOA = 0, 1
+
+
+def HOST_AOSOA(vvl):
+    """-DADDR_AOSOA -DVVL=vvl builds of the reference (src/memory.h:260-284)."""
+    return 256 + int(vvl)
+
+
 RELAX_M10, RELAX_BGK, RELAX_TRT = 0, 1, 2
 HALO_FULL, HALO_REDUCED = 0, 2
 FIELD_RHO, FIELD_U, FIELD_FORCE, FIELD_PHI, FIELD_GRAD, FIELD_DELSQ, FIELD_ETA = range(7)
@@ -30,7 +37,7 @@ _FIELD_NF = {FIELD_RHO: 1, FIELD_U: 3, FIELD_FORCE: 3, FIELD_PHI: 1, FIELD_GRAD:
 ABI_SYMBOLS = [
     "b200lb_last_error", "b200lb_device_count", "b200lb_version", "b200lb_create",
     "b200lb_destroy", "b200lb_nsite", "b200lb_set_option", "b200lb_get_option",
-    "b200lb_f_upload", "b200lb_f_download", "b200lb_field_upload",
+    "b200lb_f_upload", "b200lb_f_upload_range", "b200lb_f_download", "b200lb_field_upload",
     "b200lb_field_download", "b200lb_set_param", "b200lb_hydro_f_zero",
     "b200lb_hydro_u_zero", "b200lb_hydro_rho0", "b200lb_hydro_correct_momentum", "b200lb_collide", "b200lb_halo", "b200lb_halo_swap",
     "b200lb_propagate", "b200lb_phi_from_g", "b200lb_phi_halo", "b200lb_grad7", "b200lb_grad27", "b200lb_grad27_solid",
@@ -115,6 +122,7 @@ def load():
                  "b200lb_phi_from_g", "b200lb_phi_halo", "b200lb_grad7", "b200lb_grad27", "b200lb_grad27_solid", "b200lb_sync",
                  "b200lb_hydro_correct_momentum", "b200lb_timer_start", "b200lb_nsite", "b200lb_launch_count"):
         getattr(L, name).argtypes = [vp]
+    L.b200lb_f_upload_range.argtypes = [vp, vp, ctypes.c_long, ctypes.c_long]
     L.b200lb_halo_swap.argtypes = [vp, ctypes.c_int]
     L.b200lb_wall_commit.argtypes = [vp, vp, vp, vp]
     L.b200lb_wall_slip_set.argtypes = [vp, vp, vp, ctypes.c_int]
@@ -271,6 +279,10 @@ class Lattice:
 
     def lb_memcpy_h2d(self, f, layout=HOST_AOS):
         self._ck(self.L.b200lb_f_upload(self.h, _ptr(f), layout))
+
+    def lb_memcpy_h2d_range(self, f_part, first):
+        """lb_io_read piecewise: f_part [count, ndist, nvel] holds host sites first..first+count."""
+        self._ck(self.L.b200lb_f_upload_range(self.h, _ptr(f_part), int(first), int(f_part.shape[0])))
 
     def lb_memcpy_d2h(self, f=None, layout=HOST_AOS):
         if f is None:

@@ -92,3 +92,26 @@ def tiled_state(cv, wv, nlocal, ndist=1, ndim=3, block=(37, 41, 43)):
     f0 = np.zeros(nall + (ndist, nvel))
     f0[1:-1, 1:-1, 1:-1] = np.tile(small, reps + (1, 1))[:nlocal[0], :nlocal[1], :nlocal[2]]
     return f0.reshape(-1, ndist, nvel)
+
+
+def tiled_slabs(cv, wv, nlocal, ndist=1, ndim=3, block=(37, 41, 43), planes=16):
+    """tiled_state in pieces of `planes` x-planes of the halo-inclusive box, for lattices
+    whose host copy would not fit: yields (first host site, f [count, ndist, nvel]). The
+    pieces together are exactly tiled_state(...)."""
+    nvel = len(wv)
+    blk = tuple(min(block[a], nlocal[a]) for a in range(3))
+    small = make_state(cv, wv, blk, ndist=ndist, ndim=ndim)
+    ball = tuple(b + 2 for b in blk)
+    small = small.reshape(ball + (ndist, nvel))[1:-1, 1:-1, 1:-1]
+    reps = tuple(-(-nlocal[a]//blk[a]) for a in range(3))
+    # one x-period of the pattern, already repeated and cropped in y and z
+    yz = np.tile(small, (1, reps[1], reps[2], 1, 1))[:, :nlocal[1], :nlocal[2]]
+    nall = tuple(n + 2 for n in nlocal)
+    per_plane = nall[1]*nall[2]
+    for x0 in range(0, nall[0], planes):
+        x1 = min(x0 + planes, nall[0])
+        part = np.zeros((x1 - x0, nall[1], nall[2], ndist, nvel))
+        for x in range(x0, x1):
+            if 1 <= x <= nlocal[0]:
+                part[x - x0, 1:-1, 1:-1] = yz[(x - 1) % blk[0]]
+        yield x0*per_plane, part.reshape(-1, ndist, nvel)

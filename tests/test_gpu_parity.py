@@ -54,6 +54,34 @@ def test_lb_memcpy_roundtrip(nvel, nlocal, ndist):
     lat.close()
 
 
+@pytest.mark.parametrize("nvel,nlocal,ndist,vvl", [(19, (6, 6, 6), 1, 4), (19, (6, 6, 6), 2, 8),
+                                                   (27, (2, 6, 14), 1, 2), (9, (14, 6, 1), 1, 16)])
+def test_aosoa_host_layout(nvel, nlocal, ndist, vvl):
+    """lb_memcpy against a host built with -DADDR_AOSOA -DVVL=vvl (src/memory.h:260-284):
+    addr_rank2 = (((index/V)*ndist + n)*nvel + p)*V + index%V. Bit-exact both ways."""
+    import ludwig_b200 as lb
+    lat, orc = mk(nvel, nlocal, ndist)
+    assert orc.nsite % vvl == 0
+    rng = np.random.default_rng(2)
+    f0 = rng.standard_normal((orc.nsite, ndist, nvel))
+    if nvel == 9:
+        f3 = f0.reshape(orc.nall + (ndist, nvel))
+        f3[:, :, 0] = f3[:, :, 1]
+        f3[:, :, 2] = f3[:, :, 1]
+    blocked = np.ascontiguousarray(
+        f0.reshape(orc.nsite//vvl, vvl, ndist*nvel).transpose(0, 2, 1)).reshape(-1)
+    lat.lb_memcpy_h2d(blocked, layout=lb.HOST_AOSOA(vvl))
+    assert np.array_equal(lat.lb_memcpy_d2h(), f0)
+    back = np.zeros_like(blocked)
+    lat.lb_memcpy_d2h(back, layout=lb.HOST_AOSOA(vvl))
+    assert np.array_equal(back, blocked)
+    lat.close()
+    lat = lb.Lattice(nvel, (3, 3, 5) if nvel != 9 else (3, 5, 1), ndist=ndist)     # 175 or 105 sites
+    with pytest.raises(lb.B200LBError, match="multiple of the block length"):
+        lat.lb_memcpy_h2d(np.zeros(lat.nsite*ndist*nvel), layout=lb.HOST_AOSOA(4))
+    lat.close()
+
+
 @pytest.mark.parametrize("nvel,nlocal", CASES)
 @pytest.mark.parametrize("nrelax", [0, 1, 2])
 @pytest.mark.parametrize("vec", [1, 2])

@@ -124,3 +124,27 @@ def test_d3q19_512_cubed_equals_repeated_slab():
             blk = gb[1:-1, 1 + per*jy:1 + per*(jy + 1), 1 + per*kz:1 + per*(kz + 1)]
             assert np.array_equal(blk, gsi), (jy, kz)
     assert abs(st[0] - mass0) < 1e-9*float(np.prod(big_n))
+
+
+@pytest.mark.parametrize("nvel,nlocal,ndist", [(19, (21, 10, 12), 2), (9, (40, 33, 1), 1)])
+def test_upload_in_pieces_equals_upload_whole(nvel, nlocal, ndist):
+    """b200lb_f_upload_range (lb_io_read through a buffer): the pieces of
+    synthetic.tiled_slabs give the lattice lb_memcpy H2D of the whole array gives."""
+    import ludwig_b200 as lb
+    from ludwig_b200 import models_host, synthetic
+    cv, wv = models_host.cv(nvel), models_host.wv(nvel)
+    ndim = 2 if nvel == 9 else 3
+    whole = synthetic.tiled_state(cv, wv, nlocal, ndist=ndist, ndim=ndim, block=(7, 5, 3))
+    out = []
+    for pieces in (False, True):
+        lat = lb.Lattice(nvel, nlocal, ndist=ndist)
+        if pieces:
+            for first, part in synthetic.tiled_slabs(cv, wv, nlocal, ndist=ndist, ndim=ndim,
+                                                     block=(7, 5, 3), planes=4):
+                lat.lb_memcpy_h2d_range(part, first)
+        else:
+            lat.lb_memcpy_h2d(whole)
+        lat.step(3)
+        out.append(lat.lb_memcpy_d2h())
+        lat.close()
+    assert np.array_equal(out[0], out[1])
