@@ -76,6 +76,8 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-configs", action="store_true", help="skip the other named shapes (N = 1)")
     ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--no-variants", action="store_true",
+                    help="skip the hydro_every_step variant (profiling: one kernel variant per run)")
     ap.add_argument("--ref-size", type=int, nargs=3, default=None)
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     return ap.parse_args()
@@ -598,7 +600,7 @@ def main():
 
     # ---- the reference's behaviour: rho,u stored by every collision ------------------
     every = None
-    if args.hydro_write != 1 and args.fused:
+    if args.hydro_write != 1 and args.fused and not args.no_variants:
         lat.set_option("hydro_write", 1)
         ems, enl, ekms, enk = timed_steps(lat, comm, args.steps, 3)
         lat.set_option("hydro_write", args.hydro_write)
