@@ -77,3 +77,17 @@ def test_two_ranks_along_other_axes(extra):
     if ngpu() < 2:
         pytest.skip("needs 2 GPUs")
     launch(2, extra, 29650)
+
+
+@pytest.mark.parametrize("grid", [("1", "1", "2"), ("2", "1", "1"), ("1", "2", "1")])
+def test_peer_memory_halo_two_processes_without_nccl(grid):
+    """tools/p2p_two_process.py: two plain processes (no torch, no NCCL), CUDA IPC mappings
+    exchanged over pipes, halo sites written into the neighbour's memory from the sweep;
+    both blocks identical to the whole lattice on one GPU, bit for bit."""
+    if ngpu() < 2:
+        pytest.skip("needs 2 GPUs")
+    tool = os.path.join(os.path.dirname(HERE), "tools", "p2p_two_process.py")
+    r = subprocess.run([sys.executable, tool, "--grid"] + list(grid), capture_output=True, text=True,
+                       timeout=300)
+    sys.stdout.write(r.stdout[-1500:])
+    assert r.returncode == 0 and "PASS" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
