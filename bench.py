@@ -54,6 +54,8 @@ def parse():
     ap.add_argument("--hydro-write", type=int, default=2, choices=[0, 1, 2],
                     help="2 (library default): rho,u stored by the collision only when asked "
                          "for since the previous one; 1: every step, as the reference")
+    ap.add_argument("--lattices", type=int, default=2, choices=[1, 2],
+                    help="1: single-lattice streaming (AA pattern), half the memory")
     ap.add_argument("--overlap", type=int, default=1)
     ap.add_argument("--direct", type=int, default=1)
     ap.add_argument("--p2p", type=int, default=1, help="peer-memory halo (CUDA IPC) instead of NCCL messages")
@@ -581,6 +583,8 @@ def main():
         phi0[1:-1, 1:-1, 1:-1] = 0.1 * (rng.random(local) - 0.5)
         lat.field_h2d(lb.FIELD_PHI, np.ascontiguousarray(phi0.reshape(-1)))
         del phi0
+    if args.lattices == 1:
+        lat.set_option("lattices", 1)
     sums0 = comm.sum(lat.stats()[:7])                    # mass, ., ., ., momentum before
 
     # ---- device-resident throughput: the whole step, and the sweep alone -------------
@@ -610,6 +614,22 @@ def main():
                  "what": "option hydro_write = 1: the collision stores rho,u (32 B/site) every step "
                          "as src/collision.c:570-579 does; `value` is the default, which stores them "
                          "only when they were asked for since the previous collision"}
+
+    # ---- single-lattice streaming (AA pattern): the same steps in half the memory --------
+    single = None
+    if (args.lattices == 2 and args.fused and not args.no_variants and world == 1 and ndist == 1
+            and not (args.walls or args.le or args.fd or args.kt > 0.0 or args.loopback)):
+        lat.set_option("lattices", 1)
+        sms, snl, skms, snk = timed_steps(lat, comm, args.steps + (args.steps % 2), 4)
+        ms1 = lat.stats()[0]
+        lat.set_option("lattices", 2)
+        r2 = roofline(nvel, ndist, local, sites_local, sms, skms, snk, False)
+        single = {"value": sites_total / sms / 1e3, "unit": "MLUPS", "ms_per_step": sms,
+                  "frac": r2["frac"], "step_frac": r2["step_frac"],
+                  "lattice_bytes_on_device": lattice_bytes, "mass_drift_rel": abs(ms1 - sums0[0]) / abs(sums0[0]),
+                  "what": "option lattices = 1: one array instead of f and fprime; an in-place sweep "
+                          "and a pull-collide-push sweep alternate (bit-identical lattices, "
+                          "tests/test_zzz_gpu_single_lattice.py); timed over an even number of steps"}
 
     # ---- finite-difference order parameter: its passes alone --------------------------
     fd = None
@@ -705,7 +725,7 @@ def main():
             "config": {
                 "workload": workload_name(nvel, ndist, local, grid),
                 "global_lattice": list(ntotal), "decomposition": par, "input": mode,
-                "fused": bool(args.fused), "vec": args.vec, "halo": args.halo,
+                "fused": bool(args.fused), "vec": args.vec, "halo": args.halo, "lattices": args.lattices,
                 "hydro_write": args.hydro_write, "overlap": bool(args.overlap),
                 "direct_halo": bool(args.direct),
                 "p2p_halo": bool(args.p2p and (world > 1 or args.loopback)),
@@ -717,6 +737,7 @@ def main():
                 "l2": "lattice %.2f GB per GPU >> 126 MB L2 (no flush needed)" % (2 * lattice_bytes / 1e9),
             },
             "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "hydro_every_step": every,
+            "single_lattice": single,
             "configs": configs, "parity": parity,
             "gpu_launches": launches, "launches_per_step": nl, "clocks": clocks,
         }

@@ -105,6 +105,14 @@ long b200lb_nsite(const b200lb_t * h);                          /* host nsite = 
 
 /* run-time options; recognised names:
  *   "fused"       0/1  collide-and-stream in one pass (lazy propagation)
+ *   "lattices"    1/2  2 (default): two lattices, f and fprime of lb_t. 1: single-lattice
+ *                      streaming (AA pattern): half the memory; lb_collide alternates between
+ *                      an in-place sweep and a sweep that pulls, collides and stores one
+ *                      propagation ahead. For the time loop's cycle lb_collide - lb_halo -
+ *                      lb_propagation on a single-fluid lattice periodic within the rank;
+ *                      the lattice can be looked at (lb_memcpy, statistics) after
+ *                      lb_propagation, other sequences are refused. Same results as 2
+ *                      to round-off of nothing: bit-identical
  *   "halo"        B200LB_HALO_FULL / B200LB_HALO_REDUCED
  *   "hydro_write" 0/1/2  1: the collision stores rho,u every step (the reference's
  *                      behaviour, src/collision.c:570-579); 0: never -- they are recomputed

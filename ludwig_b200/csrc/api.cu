@@ -158,6 +158,12 @@ struct b200lb_s {
   bool noise_on;             // noise_present_set(NOISE_RHO)
   double nv_diag, nv_off, nv_bulk, nv_ghost[B200LB_MAXNOISE];
 
+  // single-lattice streaming (option lattices = 1, AA pattern; site_kernels.cuh)
+  int opt_lattices;          // 2 (default): f and fprime; 1: one array, even and odd sweeps alternate
+  bool aa_swapped;           // lat[0] holds post-collision populations in their opposites' slots (after an even sweep)
+  bool aa_ahead;             // lat[0] is one propagation ahead of the API (after an odd sweep, until lb_propagation)
+  int fstar_mode;            // where ensure_hydro finds the post-collision populations: 0, 1, 2 (aux_kernels.cuh)
+
   // state machine (see b200lb_propagate)
   bool prop_pending;         // lat[cur] holds post-collision values still to be streamed
   double * jphi;             // [3][nsd] first moment of the pulled g (option g_moment), or null
@@ -514,6 +520,7 @@ static int create_impl(const b200lb_desc_t * desc, b200lb_s * h, const ModelOps 
   h->opt_ch_planes = 8;
   h->opt_ch_exact = 0;
   h->opt_g_moment = 1;
+  h->opt_lattices = 2;
   h->opt_le_fd = 1;
   h->opt_binary_walls = 1;
 
@@ -561,6 +568,7 @@ extern "C" int b200lb_destroy(b200lb_t * h) {
 extern "C" long b200lb_nsite(const b200lb_t * h) { return h ? h->nsite_host : 0; }
 
 static int materialise(b200lb_s * h);
+static int aa_supported(const b200lb_s * h);
 static int join_comm(b200lb_s * h);
 static int flush_halo(b200lb_s * h);
 static int flush_phi_halo(b200lb_s * h);
@@ -572,6 +580,29 @@ extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
   if (!strcmp(name, "fused")) {
     if (!v && h->prop_pending) { if (materialise(h)) return -1; }
     h->opt_fused = (v != 0);
+    return 0;
+  }
+  if (!strcmp(name, "lattices")) {
+    if (v != 1 && v != 2) return fail("lattices: 2 (f and fprime, default) or 1 (single-lattice streaming)");
+    if (v == h->opt_lattices) return 0;
+    if (materialise(h)) return -1;                   // the natural, streamed lattice in lat[cur]
+    if (join_comm(h)) return -1;
+    CU(cudaStreamSynchronize(h->s_main));
+    if (v == 1) {
+      if (h->p2p_ready) return fail("lattices = 1: not with the peer-memory halo (the neighbours map both lattices)");
+      h->opt_lattices = 1;
+      if (aa_supported(h)) { h->opt_lattices = 2; return -1; }
+      if (h->cur == 1) { double * t = h->lat[0]; h->lat[0] = h->lat[1]; h->lat[1] = t; h->cur = 0; }
+      CU(cudaFree(h->lat[1]));
+      h->lat[1] = nullptr;
+      h->aa_swapped = false; h->aa_ahead = false; h->fstar_mode = 0;
+    }
+    else {
+      if (h->aa_swapped || h->aa_ahead) return fail("lattices = 2: finish the time step first (lb_propagation)");
+      CU(cudaMalloc(&h->lat[1], plane_bytes(h)*h->nplane));
+      CU(cudaMemsetAsync(h->lat[1], 0, plane_bytes(h)*h->nplane, h->s_main));
+      h->opt_lattices = 2;
+    }
     return 0;
   }
   if (!strcmp(name, "halo")) {
@@ -643,6 +674,7 @@ extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
 extern "C" long b200lb_get_option(const b200lb_t * h, const char * name) {
   if (!h || !name) return -1;
   if (!strcmp(name, "fused")) return h->opt_fused;
+  if (!strcmp(name, "lattices")) return h->opt_lattices;
   if (!strcmp(name, "halo")) return h->opt_halo;
   if (!strcmp(name, "hydro_write")) return h->opt_hydro_write;
   if (!strcmp(name, "halo_lazy")) return h->opt_halo_lazy;
@@ -767,7 +799,7 @@ static int wall_boxes(const b200lb_s * h, const KParams & P, int lo[7][3], int h
 }
 
 static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
-		     double * dst) {
+		     double * dst, int aa = 0) {
   NvtxRange nvtx_(collide ? (pull ? "b200lb: Collision + Propagation (fused sweep)" : "b200lb: Collision (krnl)")
 		  : "b200lb: Propagtn (krnl)");
   if (join_comm(h)) return -1;
@@ -775,6 +807,7 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
   site_kparams(h, a.P);
   a.P.src = src; a.P.dst = dst;
   a.pull = pull; a.collide = collide;
+  a.aa = aa;
   a.binary = (h->desc.ndist == 2);
   a.ghost = h->ghost;
   a.noise = collide && h->noise_on;
@@ -901,7 +934,7 @@ static int ensure_hydro(b200lb_s * h) {
   if (join_comm(h)) return -1;
   if (need_hydro(h)) return -1;
   CU(h->ops->hydro(h->L, h->lat[h->cur], h->desc.ndist, h->last_ffield ? h->force : nullptr,
-		   h->last_fg, h->rho, h->u, h->s_main));
+		   h->last_fg, h->rho, h->u, h->fstar_mode, h->selfper, h->s_main));
   h->launches++;
   h->hydro_stale = false;
   h->u_fill_pending = false;
@@ -909,7 +942,10 @@ static int ensure_hydro(b200lb_s * h) {
 }
 
 // apply a deferred propagation so that lat[cur] is the streamed lattice
+static int aa_materialise(b200lb_s * h);
+
 static int materialise(b200lb_s * h) {
+  if (h->opt_lattices == 1) return aa_materialise(h);
   if (!h->prop_pending) return 0;
   if (ensure_hydro(h)) return -1;       // last chance: streaming scatters f*
   if (run_sweep(h, true, false, h->lat[h->cur], h->lat[1 - h->cur])) return -1;
@@ -918,8 +954,82 @@ static int materialise(b200lb_s * h) {
   return 0;
 }
 
+// ---------------------------------------------------------------------------
+// Single-lattice streaming behind the same API (option lattices = 1). lb_collide
+// alternates between the even sweep (collide in place, slots swapped) and the odd sweep
+// (pull from the swapped slots, collide, store one propagation ahead); lb_propagation is
+// recorded after an even sweep and already done after an odd one. What the reference
+// shows at every API boundary is reproduced for the time loop's sequence
+// collide - halo - propagate; an observer between an even and an odd sweep gets the
+// natural, streamed lattice through a scratch lattice that lives for that call only.
+// ---------------------------------------------------------------------------
+
+static int aa_supported(const b200lb_s * h) {
+  if (h->desc.ndist != 1) return fail("lattices = 1: the single-fluid distribution (ndist = 1)");
+  if (h->wall_on || h->le_nplanes || h->noise_on || h->visc_on || h->open_on || h->ch_on)
+    return fail("lattices = 1: walls, Lees-Edwards planes, fluctuations, viscosity model, open boundaries and the finite-difference order parameter keep two lattices");
+  for (int d = 0; d < 3; d++) {
+    if (decomposed(h, d)) return fail("lattices = 1: a decomposition over ranks is not on this path yet (the odd sweep would store into the neighbours' interior)");
+    if (h->L.h[d] == 1 && !h->selfper[d]) return fail("lattices = 1: every direction periodic");
+  }
+  return 0;
+}
+
+static int aa_materialise(b200lb_s * h) {
+  if (h->aa_ahead) return fail("lattices = 1: the lattice is looked at between lb_collide and lb_propagation of an odd step; finish the step first");
+  if (!h->prop_pending) return 0;
+  if (!h->aa_swapped) return fail("internal: single-lattice state");
+  if (ensure_hydro(h)) return -1;
+  // natural order, streamed: pulled out of the swapped slots into a scratch lattice, which
+  // then IS the lattice (the array it replaces is released): two lattices exist for the
+  // duration of this call only
+  double * scratch = nullptr;
+  const size_t nb = plane_bytes(h)*h->nplane;
+  if (cudaMalloc(&scratch, nb) != cudaSuccess) {
+    cudaGetLastError();
+    return fail("lattices = 1: looking at the lattice between two sweeps needs room for a second lattice for the duration of the call (%zu bytes)", nb);
+  }
+  if (run_sweep(h, true, false, h->lat[0], scratch, 3)) { cudaFree(scratch); return -1; }
+  CU(cudaStreamSynchronize(h->s_main));
+  CU(cudaFree(h->lat[0]));
+  h->lat[0] = scratch;
+  h->prop_pending = false;
+  h->aa_swapped = false;
+  h->fstar_mode = 0;
+  return 0;
+}
+
+// An observer of the lattice proper (lb_memcpy D2H, statistics, file records): the states
+// the time loop passes through between lb_collide and lb_propagation are not presentable
+static int aa_observe(b200lb_s * h) {
+  if (h->opt_lattices != 1) return 0;
+  if (h->aa_ahead || (h->aa_swapped && !h->prop_pending))
+    return fail("lattices = 1: the lattice is looked at between lb_collide and lb_propagation; with a single lattice it is presentable after lb_propagation only");
+  return 0;
+}
+
+static int aa_collide(b200lb_s * h) {
+  if (aa_supported(h)) return -1;
+  if (h->aa_ahead) return fail("lattices = 1: lb_collide twice without lb_propagation");
+  if (h->prop_pending) {
+    // odd sweep: the recorded propagation, the collision, and the next propagation
+    if (run_sweep(h, true, true, h->lat[0], h->lat[0], 2)) return -1;
+    h->prop_pending = false;
+    h->aa_swapped = false;
+    h->aa_ahead = true;
+    h->fstar_mode = 2;
+    return 0;
+  }
+  if (h->aa_swapped) return fail("lattices = 1: lb_collide twice without lb_propagation");
+  if (run_sweep(h, false, true, h->lat[0], h->lat[0], 1)) return -1;
+  h->aa_swapped = true;
+  h->fstar_mode = 1;
+  return 0;
+}
+
 extern "C" int b200lb_collide(b200lb_t * h) {
   if (!h) return fail("null handle");
+  if (h->opt_lattices == 1) return aa_collide(h);
   if (resolve_ch_force(h)) return -1;     // phi_force_calculation without a Cahn-Hilliard update after it
   if (h->prop_pending && h->prop_wall && h->desc.ndist == 2) { if (materialise(h)) return -1; }
   if (h->prop_pending) {
@@ -934,6 +1044,11 @@ extern "C" int b200lb_collide(b200lb_t * h) {
 
 extern "C" int b200lb_propagate(b200lb_t * h) {
   if (!h) return fail("null handle");
+  if (h->opt_lattices == 1) {
+    if (h->aa_ahead) { h->aa_ahead = false; return 0; }          // the odd sweep has done it
+    if (h->aa_swapped && !h->prop_pending) { h->prop_pending = true; return 0; }
+    return fail("lattices = 1: lb_propagation follows lb_collide (a propagation on its own needs the second lattice)");
+  }
   if (h->prop_pending) { if (materialise(h)) return -1; }
   h->prop_wall = h->bbl_armed;      // wall_bbl ran since the collision: this streaming bounces
   h->bbl_armed = false;
@@ -1528,6 +1643,7 @@ static int lattice_exchange(b200lb_s * h, int scheme, cudaStream_t st) {
 // earlier pass could not know yet.
 static int lattice_halo(b200lb_s * h, int scheme) {
   NvtxRange nvtx_("b200lb: Lattice halos");
+  if (h->opt_lattices == 1 && (h->aa_ahead || h->aa_swapped)) return 0;   // see b200lb_halo_swap
   if (!h->opt_halo_lazy) {
     if (join_comm(h)) return -1;
     return halo_exchange(h, h->lat[h->cur], true, h->nplane, scheme, 0, h->s_main);
@@ -1561,6 +1677,12 @@ static int flush_halo(b200lb_s * h) {
 
 extern "C" int b200lb_halo_swap(b200lb_t * h, int scheme) {
   if (!h) return fail("null handle");
+  if (h->opt_lattices == 1 && (h->aa_ahead || h->aa_swapped)) {
+    // single lattice, every direction periodic within the rank: the sweeps wrap, and what
+    // the odd sweep stored is already where the propagation takes it
+    if (aa_supported(h)) return -1;
+    return 0;
+  }
   if (scheme == 1) scheme = B200LB_HALO_FULL;      // LB_HALO_OPENMP_FULL moves the same data
   if (scheme != B200LB_HALO_FULL && scheme != B200LB_HALO_REDUCED) return fail("bad halo scheme %d", scheme);
   if (h->prop_pending) { if (materialise(h)) return -1; }
@@ -2092,6 +2214,7 @@ extern "C" int b200lb_step(b200lb_t * h, int nsteps) {
 extern "C" int b200lb_stats(b200lb_t * h, double out[8]) {
   if (!h || !out) return fail("null argument");
   NvtxRange nvtx_("b200lb: stats_distribution");
+  if (aa_observe(h)) return -1;
   if (materialise(h)) return -1;
   if (join_comm(h)) return -1;
   const Layout & L = h->L;
@@ -2243,6 +2366,7 @@ extern "C" int b200lb_f_upload(b200lb_t * h, const double * f, int layout) {
   if (!h || !f) return fail("null argument");
   if (ensure_hydro(h)) return -1;   // hydro of the state being replaced stays available
   h->prop_pending = false;          // the host copy replaces whatever was in flight
+  h->aa_swapped = false; h->aa_ahead = false; h->fstar_mode = 0;
   h->jphi_valid = false;
   h->bbl_armed = false;
   h->prop_wall = false;
@@ -2269,6 +2393,7 @@ extern "C" int b200lb_f_upload_range(b200lb_t * h, const double * f, long first,
   if (!h || !f) return fail("null argument");
   if (first == 0) {
     if (ensure_hydro(h)) return -1;
+    h->aa_swapped = false; h->aa_ahead = false; h->fstar_mode = 0;
     h->prop_pending = false;
     h->jphi_valid = false;
     h->bbl_armed = false;
@@ -2382,6 +2507,7 @@ extern "C" int b200lb_noise_state_download(b200lb_t * h, unsigned int * state, i
 
 extern "C" int b200lb_f_download(b200lb_t * h, double * f, int layout) {
   if (!h || !f) return fail("null argument");
+  if (aa_observe(h)) return -1;
   if (h->prop_pending) {
     if (materialise(h)) return -1;      // streamed lattice: its halos are stale, as in the reference
   }
@@ -2613,6 +2739,7 @@ extern "C" long b200lb_io_record_doubles(const b200lb_t * h) {
 
 extern "C" int b200lb_io_pack(b200lb_t * h, double * buf) {
   if (!h || !buf) return fail("null argument");
+  if (aa_observe(h)) return -1;
   if (h->prop_pending) { if (materialise(h)) return -1; }
   return io_transfer(h, buf, false);
 }
@@ -2621,6 +2748,7 @@ extern "C" int b200lb_io_unpack(b200lb_t * h, const double * buf) {
   if (!h || !buf) return fail("null argument");
   if (ensure_hydro(h)) return -1;
   h->prop_pending = false;
+  h->aa_swapped = false; h->aa_ahead = false; h->fstar_mode = 0;
   h->jphi_valid = false;
   h->bbl_armed = false;
   h->prop_wall = false;
@@ -2672,6 +2800,7 @@ static int p2p_flags_alloc(b200lb_s * h) {
 
 extern "C" int b200lb_p2p_export(b200lb_t * h, char out[192]) {
   if (!h || !out) return fail("null argument");
+  if (h->opt_lattices == 1) return fail("peer-memory halo: not with lattices = 1");
   if (p2p_flags_alloc(h)) return -1;
   cudaIpcMemHandle_t hd[3];
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle is 64 bytes");

@@ -173,18 +173,41 @@ __global__ void __launch_bounds__(256)
 hydro_from_fstar_kernel(const Layout L, const double * __restrict__ f,
 			const double * __restrict__ force, const double fg0,
 			const double fg1, const double fg2,
-			double * __restrict__ rho, double * __restrict__ u) {
+			double * __restrict__ rho, double * __restrict__ u,
+			const int mode, const int w0, const int w1, const int w2) {
 
+  // mode: where the post-collision population p of a site is kept. 0: its slot at the
+  // site; single-lattice streaming: 1 = the slot of its opposite at the site (after an
+  // even step), 2 = its slot at the site it streams to (after an odd step)
   const int i2 = blockIdx.x*blockDim.x + threadIdx.x;
   const int i1 = blockIdx.y*blockDim.y + threadIdx.y;
   const int i0 = blockIdx.z;
   if (i2 >= L.n[2] || i1 >= L.n[1]) return;
   const i64 site = (i64)(i0 + L.h[0])*L.s0 + (i64)(i1 + L.h[1])*L.s1 + L.z0 + L.h[2] + i2;
+  // offsets that reach coordinate +1 / -1, wrapping around axes periodic within the rank
+  i64 op[3] = {L.s0, L.s1, 1}, om[3] = {-L.s0, -L.s1, -1};
+  if (mode == 2) {
+    if (w0 && i0 == L.n[0] - 1) op[0] = -(i64)(L.n[0] - 1)*L.s0;
+    if (w0 && i0 == 0) om[0] = (i64)(L.n[0] - 1)*L.s0;
+    if (w1 && i1 == L.n[1] - 1) op[1] = -(i64)(L.n[1] - 1)*L.s1;
+    if (w1 && i1 == 0) om[1] = (i64)(L.n[1] - 1)*L.s1;
+    if (w2 && i2 == L.n[2] - 1) op[2] = -(i64)(L.n[2] - 1);
+    if (w2 && i2 == 0) om[2] = (i64)(L.n[2] - 1);
+  }
 
   double r = 0.0, g[3] = {0.0, 0.0, 0.0};
   #pragma unroll
   for (int p = 0; p < M::NVEL; p++) {
-    const double fp = __ldg(f + (i64) p*L.nsd + site);
+    i64 at = (i64) p*L.nsd + site;
+    if (mode == 1 && p > 0) at = (i64)(M::NVEL - p)*L.nsd + site;
+    if (mode == 2) {
+      #pragma unroll
+      for (int d = 0; d < 3; d++) {
+	if (dcv<M>(p, d) ==  1) at += op[d];
+	if (dcv<M>(p, d) == -1) at += om[d];
+      }
+    }
+    const double fp = __ldg(f + at);
     r += fp;
     #pragma unroll
     for (int a = 0; a < M::NDIM; a++) {

@@ -13,7 +13,7 @@ static __constant__ GhostTab c_ghost;
 
 typedef B200LB_MODEL MODEL;
 
-template <int VEC, bool PULL, bool COLLIDE, bool BINARY, int GM, bool WALL = false>
+template <int VEC, bool PULL, bool COLLIDE, bool BINARY, int GM, bool WALL = false, int AA = 0>
 static cudaError_t launch_one(SweepArgs & a) {
   // walls are folded into the pull of the single-fluid kernels, and into the pure
   // propagation of the binary fluid (whose collision then runs on the streamed lattice)
@@ -37,7 +37,7 @@ static cudaError_t launch_one(SweepArgs & a) {
   dim3 block(bx, by, 1);
   dim3 grid((nt2 + bx - 1)/bx, (n1 + by - 1)/by, n0);
   a.nblocks = (long long) grid.x*grid.y*grid.z;
-  if constexpr (COLLIDE) {
+  if constexpr (COLLIDE && AA == 0) {
     if (P.push) {
       // peer-memory halo: the variants that also store into the neighbours' halo sites
       if (a.diag) lb_sweep_kernel<MODEL, VEC, PULL, COLLIDE, BINARY, GM, true, WALL, true><<<grid, block, 0, a.stream>>>(P);
@@ -47,11 +47,11 @@ static cudaError_t launch_one(SweepArgs & a) {
   }
   if (P.push) return cudaErrorInvalidValue;
   if (COLLIDE && a.diag) {
-    lb_sweep_kernel<MODEL, VEC, PULL, COLLIDE, BINARY, GM, COLLIDE, WALL>
+    lb_sweep_kernel<MODEL, VEC, PULL, COLLIDE, BINARY, GM, COLLIDE, WALL, false, AA>
       <<<grid, block, 0, a.stream>>>(P);
   }
   else {
-    lb_sweep_kernel<MODEL, VEC, PULL, COLLIDE, BINARY, GM, false, WALL>
+    lb_sweep_kernel<MODEL, VEC, PULL, COLLIDE, BINARY, GM, false, WALL, false, AA>
       <<<grid, block, 0, a.stream>>>(P);
   }
   return cudaGetLastError();
@@ -119,7 +119,29 @@ static cudaError_t launch_pc(SweepArgs & a) {
   }
 }
 
+// single-lattice streaming (option lattices = 1): plain single-fluid sweeps, M10 or a scheme
+// that keeps ghost modes
+static cudaError_t launch_aa(SweepArgs & a) {
+  if (a.binary || a.noise || a.visc || a.wall || a.gmom || a.P.push) return cudaErrorInvalidValue;
+  if (a.aa == 1 && !a.pull && a.collide) {
+    if (a.ghost) return launch_one<1, false, true, false, 1, false, 1>(a);
+    if (a.vec == 2) return launch_one<2, false, true, false, 0, false, 1>(a);
+    return launch_one<1, false, true, false, 0, false, 1>(a);
+  }
+  if (a.aa == 2 && a.pull && a.collide) {
+    if (a.ghost) return launch_one<1, true, true, false, 1, false, 2>(a);
+    if (a.vec == 2) return launch_one<2, true, true, false, 0, false, 2>(a);
+    return launch_one<1, true, true, false, 0, false, 2>(a);
+  }
+  if (a.aa == 3 && a.pull && !a.collide) {
+    if (a.vec == 2) return launch_one<2, true, false, false, 0, false, 3>(a);
+    return launch_one<1, true, false, false, 0, false, 3>(a);
+  }
+  return cudaErrorInvalidValue;
+}
+
 static cudaError_t sweep_impl(SweepArgs & a) {
+  if (a.aa) return launch_aa(a);
   if (a.pull && a.collide) return launch_pc<true, true>(a);
   if (a.pull) return launch_pc<true, false>(a);
   if (a.collide) return launch_pc<false, true>(a);
@@ -145,11 +167,11 @@ static cudaError_t stats_impl(const Layout & L, const double * f, int ndist,
 
 static cudaError_t hydro_impl(const Layout & L, const double * f, int ndist,
 			      const double * force, const double fg[3], double * rho,
-			      double * u, cudaStream_t s) {
+			      double * u, int mode, const int wrap[3], cudaStream_t s) {
   dim3 block(128, 2, 1);
   dim3 grid((L.n[2] + 127)/128, (L.n[1] + 1)/2, L.n[0]);
-  if (ndist == 2) hydro_from_fstar_kernel<MODEL, true><<<grid, block, 0, s>>>(L, f, force, fg[0], fg[1], fg[2], rho, u);
-  else hydro_from_fstar_kernel<MODEL, false><<<grid, block, 0, s>>>(L, f, force, fg[0], fg[1], fg[2], rho, u);
+  if (ndist == 2) hydro_from_fstar_kernel<MODEL, true><<<grid, block, 0, s>>>(L, f, force, fg[0], fg[1], fg[2], rho, u, mode, wrap[0], wrap[1], wrap[2]);
+  else hydro_from_fstar_kernel<MODEL, false><<<grid, block, 0, s>>>(L, f, force, fg[0], fg[1], fg[2], rho, u, mode, wrap[0], wrap[1], wrap[2]);
   return cudaGetLastError();
 }
 

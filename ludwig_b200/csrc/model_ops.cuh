@@ -15,6 +15,7 @@ struct SweepArgs {
   bool gmom;          // binary fluid, pull + collide: first moment of g from P.jphi, g not read
   bool wall;          // bounce-back on links folded into the pull (pull only)
   bool diag;          // accumulate conserved sums in the sweep (collide only)
+  int aa;             // single-lattice streaming: 0 off, 1 even step, 2 odd step, 3 un-swap and stream
   long long nblocks;  // out: blocks launched (= diagnostic partials written)
   int vec;            // sites per thread (1 or 2)
   int bx;             // threads per block along the contiguous axis
@@ -33,7 +34,8 @@ struct ModelOps {
   cudaError_t (*stats)(const Layout &, const double * f, int ndist,
 		       double * partial, dim3 grid, dim3 block, cudaStream_t);
   cudaError_t (*hydro)(const Layout &, const double * f, int ndist, const double * force,
-		       const double fg[3], double * rho, double * u, cudaStream_t);
+		       const double fg[3], double * rho, double * u, int mode, const int wrap[3],
+		       cudaStream_t);
   cudaError_t (*ghost_upload)(void);
 };
 

@@ -336,14 +336,27 @@ fluctuations(unsigned int (&w)[4], const KParams & P,
 
 // PUSH: the peer-memory halo rides on this sweep (its own instantiations: the kernels of a
 // single-GPU run carry none of that code and keep their register count)
-template <class M, int VEC, bool PULL, bool COLLIDE, bool BINARY, int GM, bool DIAG, bool WALL = false, bool PUSH = false>
+// AA: single-lattice streaming (the "AA pattern", Bailey et al. 2009) -- src == dst, every
+// location is read and written by exactly one site per sweep:
+//   1  even step: collide in place; population p is stored in the slot of its opposite,
+//      Q - p, at the same site (post-collision, unstreamed, "swapped")
+//   2  odd step: population p is pulled from the opposite slot of the site it streams from,
+//      collided, and stored in its own slot at the site it streams TO: the lattice comes
+//      out one propagation ahead, in the natural order
+//   3  no collision: pull from the swapped slots into another lattice in natural order
+//      (what an observer of the state between an even and an odd step needs)
+template <class M, int VEC, bool PULL, bool COLLIDE, bool BINARY, int GM, bool DIAG, bool WALL = false, bool PUSH = false, int AA = 0>
 __global__ void __launch_bounds__(256, PUSH ? 2 : 0)
 lb_sweep_kernel(const KParams P) {
 
   constexpr int Q  = M::NVEL;
   constexpr int ND = M::NDIM;
   constexpr int NDIST = BINARY ? 2 : 1;
-  constexpr bool NC = PULL;          // source is read-only when it is not the destination
+  constexpr bool NC = PULL && AA != 2;   // source is read-only when it is not the destination
+  static_assert(AA == 0 || (!BINARY && !WALL && !PUSH && (GM & ~1) == 0), "single-lattice streaming: plain single-fluid sweeps");
+  static_assert(AA != 1 || (!PULL && COLLIDE), "AA even step is an in-place collision");
+  static_assert(AA != 2 || (PULL && COLLIDE), "AA odd step pulls and collides");
+  static_assert(AA != 3 || (PULL && !COLLIDE), "AA materialisation only streams");
   // GM bit 3: phi_from_g_kernel<PULL, MOM> has left the first moment of the pulled g in
   // P.jphi, which is all the binary collision takes from it: g is written, not read
   constexpr bool GMOM = BINARY && PULL && COLLIDE && ((GM & 8) != 0);
@@ -466,7 +479,9 @@ lb_sweep_kernel(const KParams P) {
   for (int n = 0; n < NLOAD; n++) {
     #pragma unroll
     for (int p = 0; p < Q; p++) {
-      const double * src = P.src + (i64)(n*Q + p)*L.nsd + site;
+      // AA 2, 3: population p waits in the slot of its opposite
+      const int ps = ((AA == 2 || AA == 3) && p > 0) ? Q - p : p;
+      const double * src = P.src + (i64)(n*Q + ps)*L.nsd + site;
       int c2 = 0;
       if (PULL) {
 	if (dcv<M>(p, 0) ==  1) src += om[0];
@@ -596,11 +611,38 @@ lb_sweep_kernel(const KParams P) {
     }
   }
 
+  if constexpr (AA == 2) {
+    // odd step of the single-lattice scheme: every population goes to the site it streams
+    // to (the mirror image of the pull above; same wrap-aware offsets with the roles of
+    // the two directions exchanged)
+    #pragma unroll
+    for (int p = 0; p < Q; p++) {
+      double * dst = P.dst + (i64) p*L.nsd + site;
+      if (dcv<M>(p, 0) ==  1) dst += op[0];
+      if (dcv<M>(p, 0) == -1) dst += om[0];
+      if (dcv<M>(p, 1) ==  1) dst += op[1];
+      if (dcv<M>(p, 1) == -1) dst += om[1];
+      const int c2 = dcv<M>(p, 2);
+      if (c2 == 0) {
+	if (VEC == 2 && nv == 2) *reinterpret_cast<double2 *>(dst) = make_double2(f[0][0][p], f[0][VEC - 1][p]);
+	else if (nv >= 1) *dst = f[0][0][p];
+      }
+      else {
+	#pragma unroll
+	for (int v = 0; v < VEC; v++) {
+	  if (v < nv) dst[v + (c2 == 1 ? zp[v] : zm[v])] = f[0][v][p];
+	}
+      }
+    }
+  }
+  else {
   #pragma unroll
   for (int n = 0; n < NDIST; n++) {
     #pragma unroll
     for (int p = 0; p < Q; p++) {
-      double * dst = P.dst + (i64)(n*Q + p)*L.nsd + site;
+      // AA 1 (even step): post-collision population p into the slot of its opposite
+      const int pd = (AA == 1 && p > 0) ? Q - p : p;
+      double * dst = P.dst + (i64)(n*Q + pd)*L.nsd + site;
       if (VEC == 2 && nv == 2) {
 	*reinterpret_cast<double2 *>(dst) = make_double2(f[n][0][p], f[n][VEC - 1][p]);
       }
@@ -608,6 +650,7 @@ lb_sweep_kernel(const KParams P) {
 	*dst = f[n][0][p];
       }
     }
+  }
   }
 
   // Peer-memory halo: a site on the face of the local box also stores the
