@@ -446,7 +446,7 @@ def small_config(lb, comm, args, nvel, ndist, local, steps, name):
             "mass_drift_rel": abs(m1 - m0) / abs(m0)}
 
 
-def decomposed_equals_single(lb, comm, grid, nvel=19, per_rank=(32, 32, 32), nsteps=10):
+def decomposed_equals_single(lb, comm, grid, nvel=19, per_rank=(32, 32, 32), nsteps=10, lattices=2):
     """Parity inside the bench run: every rank steps its 32^3 block of a small lattice with
     the same options as the timed run, rank 0 also steps the whole lattice on its GPU alone;
     the interiors must be identical bit for bit (what the reference's pmpi08-* logs test
@@ -454,7 +454,7 @@ def decomposed_equals_single(lb, comm, grid, nvel=19, per_rank=(32, 32, 32), nst
     torch, dist = comm.torch, comm.dist
     ntotal = tuple(per_rank[a] * grid[a] for a in range(3))
     dec = lb.Decomposition(ntotal, comm.rank, comm.world, grid=grid)
-    lat = lb.Lattice(nvel, per_rank, decomp=dec, device=torch.cuda.current_device())
+    lat = lb.Lattice(nvel, per_rank, decomp=dec, device=torch.cuda.current_device(), lattices=lattices)
     lat.set_option("halo", lb.HALO_REDUCED)
     lat.set_param(eta_shear=0.1, eta_bulk=0.1)
     comm.connect(lb, lat)
@@ -533,12 +533,13 @@ def main():
     # ---- parity inside the run (N > 1): decomposed == single GPU, bit for bit -------
     parity = {}
     if world > 1 and not args.no_parity:
-        parity["decomposed_equals_single"] = decomposed_equals_single(lb, comm, grid)
-        parity["what"] = ("D3Q19 %s per rank on the %s grid, 10 steps, peer-memory halo: interiors "
-                          "compared bit for bit on rank 0 with the whole lattice on one GPU"
-                          % ("32^3", "x".join(str(g) for g in grid)))
+        parity["decomposed_equals_single"] = decomposed_equals_single(lb, comm, grid, lattices=args.lattices)
+        parity["what"] = ("D3Q19 %s per rank on the %s grid, 10 steps, peer-memory halo, lattices = %d: "
+                          "interiors compared bit for bit on rank 0 with the whole (two-lattice) "
+                          "lattice on one GPU" % ("32^3", "x".join(str(g) for g in grid), args.lattices))
 
-    lat = lb.Lattice(nvel, local, ndist=ndist, decomp=dec, device=local_rank, zalign=args.zalign)
+    lat = lb.Lattice(nvel, local, ndist=ndist, decomp=dec, device=local_rank, zalign=args.zalign,
+                     lattices=args.lattices)
     configure(lb, lat, args, nvel, ndist, args.gradient)
     if args.vec:
         lat.set_option("vec", args.vec)
@@ -583,8 +584,6 @@ def main():
         phi0[1:-1, 1:-1, 1:-1] = 0.1 * (rng.random(local) - 0.5)
         lat.field_h2d(lb.FIELD_PHI, np.ascontiguousarray(phi0.reshape(-1)))
         del phi0
-    if args.lattices == 1:
-        lat.set_option("lattices", 1)
     sums0 = comm.sum(lat.stats()[:7])                    # mass, ., ., ., momentum before
 
     # ---- device-resident throughput: the whole step, and the sweep alone -------------

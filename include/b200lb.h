@@ -76,6 +76,8 @@ typedef struct b200lb_desc_s {
   int nranks;
   int device;            /* CUDA device ordinal, or -1 for the current one */
   int zalign;            /* 0 = default; interior rows start on zalign doubles */
+  int lattices;          /* 0 or 2: f and fprime; 1: single-lattice streaming from the start
+                          * (option "lattices"): the second array is never allocated */
 } b200lb_desc_t;
 
 /* lb_collide_param_t (src/lb_data.h:53-69), collide_param_t

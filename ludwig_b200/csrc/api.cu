@@ -408,6 +408,8 @@ extern "C" int b200lb_create(const b200lb_desc_t * desc, b200lb_t ** out) {
   if (ndev <= 0) return fail("no CUDA device: libb200lb has no CPU path");
   if (desc->nhalo != 1) return fail("nhalo must be 1 (got %d)", desc->nhalo);
   if (desc->ndist != 1 && desc->ndist != 2) return fail("ndist must be 1 or 2");
+  if (desc->lattices < 0 || desc->lattices > 2) return fail("desc.lattices: 0 or 2 (two lattices), 1 (single-lattice streaming)");
+  if (desc->lattices == 1 && desc->ndist != 1) return fail("desc.lattices = 1: the single-fluid distribution (ndist = 1)");
 
   const ModelOps * ops = nullptr;
   if (desc->nvel == 19) ops = model_ops_d3q19();
@@ -481,7 +483,8 @@ static int create_impl(const b200lb_desc_t * desc, b200lb_s * h, const ModelOps 
   CU(cudaEventCreate(&h->ev1));
 
   const size_t pb = plane_bytes(h);
-  for (int i = 0; i < 2; i++) {
+  h->opt_lattices = (desc->lattices == 1) ? 1 : 2;
+  for (int i = 0; i < h->opt_lattices; i++) {
     CU(cudaMalloc(&h->lat[i], pb*h->nplane));
     CU(cudaMemsetAsync(h->lat[i], 0, pb*h->nplane, h->s_main));
   }
@@ -520,7 +523,6 @@ static int create_impl(const b200lb_desc_t * desc, b200lb_s * h, const ModelOps 
   h->opt_ch_planes = 8;
   h->opt_ch_exact = 0;
   h->opt_g_moment = 1;
-  h->opt_lattices = 2;
   h->opt_le_fd = 1;
   h->opt_binary_walls = 1;
 
@@ -589,18 +591,30 @@ extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
     if (join_comm(h)) return -1;
     CU(cudaStreamSynchronize(h->s_main));
     if (v == 1) {
-      if (h->p2p_ready) return fail("lattices = 1: not with the peer-memory halo (the neighbours map both lattices)");
+      if (h->p2p_ready && h->cur == 1) {
+        // the neighbours have lat[0] and lat[1] mapped by name: keep the current state in lat[0]
+        CU(cudaMemcpyAsync(h->lat[0], h->lat[1], plane_bytes(h)*h->nplane, cudaMemcpyDeviceToDevice, h->s_main));
+        CU(cudaStreamSynchronize(h->s_main));
+        h->cur = 0;
+      }
       h->opt_lattices = 1;
       if (aa_supported(h)) { h->opt_lattices = 2; return -1; }
       if (h->cur == 1) { double * t = h->lat[0]; h->lat[0] = h->lat[1]; h->lat[1] = t; h->cur = 0; }
-      CU(cudaFree(h->lat[1]));
-      h->lat[1] = nullptr;
+      if (!h->p2p_ready) {
+        // (with the peer-memory halo the neighbours have the array mapped: it stays, unused;
+        // desc.lattices = 1 never allocates it)
+        CU(cudaFree(h->lat[1]));
+        h->lat[1] = nullptr;
+      }
       h->aa_swapped = false; h->aa_ahead = false; h->fstar_mode = 0;
     }
     else {
       if (h->aa_swapped || h->aa_ahead) return fail("lattices = 2: finish the time step first (lb_propagation)");
-      CU(cudaMalloc(&h->lat[1], plane_bytes(h)*h->nplane));
-      CU(cudaMemsetAsync(h->lat[1], 0, plane_bytes(h)*h->nplane, h->s_main));
+      if (h->p2p_ready && !h->lat[1]) return fail("lattices = 2: the neighbours have mapped a single lattice (desc.lattices = 1)");
+      if (!h->lat[1]) {
+        CU(cudaMalloc(&h->lat[1], plane_bytes(h)*h->nplane));
+        CU(cudaMemsetAsync(h->lat[1], 0, plane_bytes(h)*h->nplane, h->s_main));
+      }
       h->opt_lattices = 2;
     }
     return 0;
@@ -969,8 +983,11 @@ static int aa_supported(const b200lb_s * h) {
   if (h->wall_on || h->le_nplanes || h->noise_on || h->visc_on || h->open_on || h->ch_on)
     return fail("lattices = 1: walls, Lees-Edwards planes, fluctuations, viscosity model, open boundaries and the finite-difference order parameter keep two lattices");
   for (int d = 0; d < 3; d++) {
-    if (decomposed(h, d)) return fail("lattices = 1: a decomposition over ranks is not on this path yet (the odd sweep would store into the neighbours' interior)");
-    if (h->L.h[d] == 1 && !h->selfper[d]) return fail("lattices = 1: every direction periodic");
+    if (h->L.h[d] == 0 || h->selfper[d]) continue;
+    // across ranks the odd sweep stores into the neighbours' interior: peer memory only
+    if (!decomposed(h, d)) return fail("lattices = 1: every direction periodic");
+    if (!(h->p2p_ready && h->opt_p2p)) return fail("lattices = 1 on a decomposed lattice: with the peer-memory halo only (b200lb_p2p_import)");
+    if (h->L.n[d] < 2) return fail("lattices = 1: at least two sites per decomposed direction");
   }
   return 0;
 }
@@ -990,9 +1007,23 @@ static int aa_materialise(b200lb_s * h) {
     return fail("lattices = 1: looking at the lattice between two sweeps needs room for a second lattice for the duration of the call (%zu bytes)", nb);
   }
   if (run_sweep(h, true, false, h->lat[0], scratch, 3)) { cudaFree(scratch); return -1; }
+  // back into the array the neighbours have mapped (halo sites included: they keep what the
+  // even sweeps pushed, stale for the streamed lattice as after any propagation)
+  {
+    const Layout & L = h->L;
+    for (int e = 0; e < h->nplane; e++) {
+      cudaMemcpy3DParms c;
+      memset(&c, 0, sizeof(c));
+      const size_t off = (size_t) e*L.nsd + (size_t) L.h[0]*L.s0 + (size_t) L.h[1]*L.s1 + L.z0 + L.h[2];
+      c.srcPtr = make_cudaPitchedPtr(scratch + off, L.s1*sizeof(double), L.s1, L.s0/L.s1);
+      c.dstPtr = make_cudaPitchedPtr(h->lat[0] + off, L.s1*sizeof(double), L.s1, L.s0/L.s1);
+      c.extent = make_cudaExtent((size_t) L.n[2]*sizeof(double), L.n[1], L.n[0]);
+      c.kind = cudaMemcpyDeviceToDevice;
+      CU(cudaMemcpy3DAsync(&c, h->s_main));
+    }
+  }
   CU(cudaStreamSynchronize(h->s_main));
-  CU(cudaFree(h->lat[0]));
-  h->lat[0] = scratch;
+  CU(cudaFree(scratch));
   h->prop_pending = false;
   h->aa_swapped = false;
   h->fstar_mode = 0;
@@ -2800,7 +2831,16 @@ static int p2p_flags_alloc(b200lb_s * h) {
 
 extern "C" int b200lb_p2p_export(b200lb_t * h, char out[192]) {
   if (!h || !out) return fail("null argument");
-  if (h->opt_lattices == 1) return fail("peer-memory halo: not with lattices = 1");
+  if (h->opt_lattices == 1) {
+    // one array: its handle twice (the importer maps it once)
+    if (p2p_flags_alloc(h)) return -1;
+    cudaIpcMemHandle_t hd1[3];
+    CU(cudaIpcGetMemHandle(&hd1[0], h->lat[0]));
+    hd1[1] = hd1[0];
+    CU(cudaIpcGetMemHandle(&hd1[2], h->p2p.flags));
+    memcpy(out, hd1, 192);
+    return 0;
+  }
   if (p2p_flags_alloc(h)) return -1;
   cudaIpcMemHandle_t hd[3];
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle is 64 bytes");
@@ -2850,10 +2890,11 @@ extern "C" int b200lb_p2p_import(b200lb_t * h, const char * all, int nranks) {
         memcpy(hd, all + (size_t) r*192, 192);
         void * p0 = nullptr, * p1 = nullptr, * p2 = nullptr;
         CU(cudaIpcOpenMemHandle(&p0, hd[0], cudaIpcMemLazyEnablePeerAccess));
-        CU(cudaIpcOpenMemHandle(&p1, hd[1], cudaIpcMemLazyEnablePeerAccess));
+        if (memcmp(&hd[0], &hd[1], sizeof(hd[0])) == 0) p1 = p0;          // a single-lattice neighbour
+        else CU(cudaIpcOpenMemHandle(&p1, hd[1], cudaIpcMemLazyEnablePeerAccess));
         CU(cudaIpcOpenMemHandle(&p2, hd[2], cudaIpcMemLazyEnablePeerAccess));
         rlat[0][r] = (double *) p0; rlat[1][r] = (double *) p1; rflags[r] = (unsigned long long *) p2;
-        h->ipc_open[h->n_ipc_open++] = p0; h->ipc_open[h->n_ipc_open++] = p1; h->ipc_open[h->n_ipc_open++] = p2;
+        h->ipc_open[h->n_ipc_open++] = p0; if (p1 != p0) h->ipc_open[h->n_ipc_open++] = p1; h->ipc_open[h->n_ipc_open++] = p2;
         opened[r] = true;
       }
       h->peer_lat[0][k] = rlat[0][r]; h->peer_lat[1][k] = rlat[1][r]; h->p2p.peer_flags[k] = rflags[r];

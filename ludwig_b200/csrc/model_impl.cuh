@@ -37,11 +37,12 @@ static cudaError_t launch_one(SweepArgs & a) {
   dim3 block(bx, by, 1);
   dim3 grid((nt2 + bx - 1)/bx, (n1 + by - 1)/by, n0);
   a.nblocks = (long long) grid.x*grid.y*grid.z;
-  if constexpr (COLLIDE && AA == 0) {
+  if constexpr (COLLIDE) {
     if (P.push) {
       // peer-memory halo: the variants that also store into the neighbours' halo sites
-      if (a.diag) lb_sweep_kernel<MODEL, VEC, PULL, COLLIDE, BINARY, GM, true, WALL, true><<<grid, block, 0, a.stream>>>(P);
-      else lb_sweep_kernel<MODEL, VEC, PULL, COLLIDE, BINARY, GM, false, WALL, true><<<grid, block, 0, a.stream>>>(P);
+      // (single-lattice odd sweep: into the neighbours' interior)
+      if (a.diag) lb_sweep_kernel<MODEL, VEC, PULL, COLLIDE, BINARY, GM, true, WALL, true, AA><<<grid, block, 0, a.stream>>>(P);
+      else lb_sweep_kernel<MODEL, VEC, PULL, COLLIDE, BINARY, GM, false, WALL, true, AA><<<grid, block, 0, a.stream>>>(P);
       return cudaGetLastError();
     }
   }
@@ -122,7 +123,8 @@ static cudaError_t launch_pc(SweepArgs & a) {
 // single-lattice streaming (option lattices = 1): plain single-fluid sweeps, M10 or a scheme
 // that keeps ghost modes
 static cudaError_t launch_aa(SweepArgs & a) {
-  if (a.binary || a.noise || a.visc || a.wall || a.gmom || a.P.push) return cudaErrorInvalidValue;
+  if (a.binary || a.noise || a.visc || a.wall || a.gmom) return cudaErrorInvalidValue;
+  if (a.aa == 3 && a.P.push) return cudaErrorInvalidValue;
   if (a.aa == 1 && !a.pull && a.collide) {
     if (a.ghost) return launch_one<1, false, true, false, 1, false, 1>(a);
     if (a.vec == 2) return launch_one<2, false, true, false, 0, false, 1>(a);

@@ -353,7 +353,8 @@ lb_sweep_kernel(const KParams P) {
   constexpr int ND = M::NDIM;
   constexpr int NDIST = BINARY ? 2 : 1;
   constexpr bool NC = PULL && AA != 2;   // source is read-only when it is not the destination
-  static_assert(AA == 0 || (!BINARY && !WALL && !PUSH && (GM & ~1) == 0), "single-lattice streaming: plain single-fluid sweeps");
+  static_assert(AA == 0 || (!BINARY && !WALL && (GM & ~1) == 0), "single-lattice streaming: plain single-fluid sweeps");
+  static_assert(AA != 3 || !PUSH, "the materialising sweep stores locally");
   static_assert(AA != 1 || (!PULL && COLLIDE), "AA even step is an in-place collision");
   static_assert(AA != 2 || (PULL && COLLIDE), "AA odd step pulls and collides");
   static_assert(AA != 3 || (PULL && !COLLIDE), "AA materialisation only streams");
@@ -615,6 +616,14 @@ lb_sweep_kernel(const KParams P) {
     // odd step of the single-lattice scheme: every population goes to the site it streams
     // to (the mirror image of the pull above; same wrap-aware offsets with the roles of
     // the two directions exchanged)
+    // decomposed directions (PUSH): a population that leaves the local box belongs to an
+    // interior site of the neighbour -- stored there through the peer mapping -- and is
+    // also left in the local halo site, where rho,u on demand look for it
+    int ex[3] = {0, 0, 0};
+    if constexpr (PUSH) {
+      if (!P.wrap[0]) ex[0] = (i0 == 0) ? -1 : ((i0 == L.n[0] - 1) ? 1 : 0);
+      if (!P.wrap[1]) ex[1] = (i1 == 0) ? -1 : ((i1 == L.n[1] - 1) ? 1 : 0);
+    }
     #pragma unroll
     for (int p = 0; p < Q; p++) {
       double * dst = P.dst + (i64) p*L.nsd + site;
@@ -631,6 +640,32 @@ lb_sweep_kernel(const KParams P) {
 	#pragma unroll
 	for (int v = 0; v < VEC; v++) {
 	  if (v < nv) dst[v + (c2 == 1 ? zp[v] : zm[v])] = f[0][v][p];
+	}
+      }
+      if constexpr (PUSH) {
+	if (p > 0) {
+	  const int s0 = (dcv<M>(p, 0) != 0 && ex[0] == dcv<M>(p, 0)) ? dcv<M>(p, 0) : 0;
+	  const int s1 = (dcv<M>(p, 1) != 0 && ex[1] == dcv<M>(p, 1)) ? dcv<M>(p, 1) : 0;
+	  #pragma unroll
+	  for (int v = 0; v < VEC; v++) {
+	    if (v < nv) {
+	      int s2 = 0;
+	      if (c2 != 0 && !P.wrap[2]) {
+		const int e2 = (i2 + v == 0) ? -1 : ((i2 + v == L.n[2] - 1) ? 1 : 0);
+		if (e2 == c2) s2 = c2;
+	      }
+	      if (s0 | s1 | s2) {
+		double * peer = P.peer[(s0 + 1)*9 + (s1 + 1)*3 + (s2 + 1)];
+		if (peer != nullptr) {
+		  // the same site in the neighbour's frame: one box extent back along each
+		  // crossed direction
+		  const i64 at = (dst - P.dst) + v + (c2 == 0 ? 0 : (c2 == 1 ? zp[v] : zm[v]))
+		    - (i64) s0*L.n[0]*L.s0 - (i64) s1*L.n[1]*L.s1 - (i64) s2*L.n[2];
+		  peer[at] = f[0][v][p];
+		}
+	      }
+	    }
+	  }
 	}
       }
     }
@@ -653,6 +688,9 @@ lb_sweep_kernel(const KParams P) {
   }
   }
 
+  // (single-lattice streaming, even sweep: the same, into the swapped slot Q - p of the
+  // neighbour's halo site, where its odd sweep pulls from; the odd sweep stores into the
+  // neighbours' interior itself, above)
   // Peer-memory halo: a site on the face of the local box also stores the
   // populations that leave through that face directly into the halo site of the
   // neighbouring GPU's lattice (NVLink peer pointers, mapped with CUDA IPC), for
@@ -660,7 +698,7 @@ lb_sweep_kernel(const KParams P) {
   // the transfer rides on the sweep itself. Same population set as the reduced
   // scheme (src/model.c:1192-1219): p goes to direction s iff s picks components of
   // c_p and the site lies on the boundary in each picked component.
-  if constexpr (COLLIDE && PUSH) {
+  if constexpr (COLLIDE && PUSH && AA != 2) {
     #pragma unroll
     for (int v = 0; v < VEC; v++) {
       if (v < nv) {
@@ -699,7 +737,7 @@ lb_sweep_kernel(const KParams P) {
 		    for (int p = 1; p < Q; p++) {
 		      if (dcv<M>(p, 2) == 1 || dcv<M>(p, 2) == -1) {
 			if (dcv<M>(p, 2) == sd) {
-			  double * a = base + (i64)(n*Q + p)*L.nsd;
+			  double * a = base + (i64)(n*Q + ((AA == 1) ? Q - p : p))*L.nsd;
 			  const double val = f[n][v][p];
 			  if (sd == 1) {   // lands in the low halo: last word of its sector
 			    asm volatile("st.global.v4.f64 [%0], {%1, %1, %1, %2};" :: "l"(a - 3), "d"(0.0), "d"(val) : "memory");
@@ -717,7 +755,7 @@ lb_sweep_kernel(const KParams P) {
 		  for (int n = 0; n < NDIST; n++) {
 		    #pragma unroll
 		    for (int p = 1; p < Q; p++) {
-		      if (dcv<M>(p, d) == 1) base[(i64)(n*Q + p)*L.nsd] = f[n][v][p];
+		      if (dcv<M>(p, d) == 1) base[(i64)(n*Q + ((AA == 1) ? Q - p : p))*L.nsd] = f[n][v][p];
 		    }
 		  }
 		}
@@ -726,7 +764,7 @@ lb_sweep_kernel(const KParams P) {
 		  for (int n = 0; n < NDIST; n++) {
 		    #pragma unroll
 		    for (int p = 1; p < Q; p++) {
-		      if (dcv<M>(p, d) == -1) base[(i64)(n*Q + p)*L.nsd] = f[n][v][p];
+		      if (dcv<M>(p, d) == -1) base[(i64)(n*Q + ((AA == 1) ? Q - p : p))*L.nsd] = f[n][v][p];
 		    }
 		  }
 		}
@@ -752,7 +790,7 @@ lb_sweep_kernel(const KParams P) {
 		  double * peer = P.peer[(s0 + 1)*9 + (s1 + 1)*3 + (s2 + 1)];
 		  if (on && peer != nullptr) {
 		    const i64 rs = site + v - (i64) s0*L.n[0]*L.s0 - (i64) s1*L.n[1]*L.s1 - (i64) s2*L.n[2];
-		    peer[(i64)(n*Q + p)*L.nsd + rs] = f[n][v][p];
+		    peer[(i64)(n*Q + ((AA == 1) ? Q - p : p))*L.nsd + rs] = f[n][v][p];
 		  }
 		}
 	      }

@@ -67,6 +67,7 @@ class Desc(ctypes.Structure):
         ("periodic", ctypes.c_int * 3), ("nbr_lo", ctypes.c_int * 3),
         ("nbr_hi", ctypes.c_int * 3), ("rank", ctypes.c_int),
         ("nranks", ctypes.c_int), ("device", ctypes.c_int), ("zalign", ctypes.c_int),
+        ("lattices", ctypes.c_int),
     ]
 
 
@@ -206,7 +207,7 @@ class Lattice:
     reference, device-resident in the library's private layout."""
 
     def __init__(self, nvel, nlocal, ndist=1, decomp=None, device=-1, zalign=0,
-                 periodic=(1, 1, 1)):
+                 periodic=(1, 1, 1), lattices=2):
         self.L = load()
         self.nvel, self.ndist = nvel, ndist
         self.ndim = 2 if nvel == 9 else 3
@@ -229,6 +230,7 @@ class Lattice:
             d.nbr_hi[:] = decomp.nbr_hi
             d.rank, d.nranks = decomp.rank, decomp.nranks
         d.device, d.zalign = device, zalign
+        d.lattices = int(lattices)
         self.h = ctypes.c_void_p()
         self._ck(self.L.b200lb_create(ctypes.byref(d), ctypes.byref(self.h)))
         self.nall = tuple(n + 2 for n in self.nlocal)

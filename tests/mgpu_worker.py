@@ -47,6 +47,8 @@ def main():
     ap.add_argument("--fd", type=int, default=0,
                     help="free_energy symmetric: finite-difference order parameter, advection of this order")
     ap.add_argument("--visc", type=int, default=0, help="with --fd: viscosity_model arrhenius")
+    ap.add_argument("--lattices", type=int, default=2,
+                    help="1: single-lattice streaming from the start (desc.lattices = 1)")
     ap.add_argument("--grid", type=int, nargs=3, default=None,
                     help="process grid (default: 2x1x1, 2x2x1, 2x2x2 by number of ranks)")
     args = ap.parse_args()
@@ -77,7 +79,7 @@ def main():
     dec = lb.Decomposition(ntotal, rank, world, grid=grid, periodic=periodic)
     cv, wv = models_host.cv(nvel), models_host.wv(nvel)
 
-    lat = lb.Lattice(nvel, local, ndist=ndist, decomp=dec, device=local_rank)
+    lat = lb.Lattice(nvel, local, ndist=ndist, decomp=dec, device=local_rank, lattices=args.lattices)
     uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
     if rank == 0:
         uid = torch.tensor(list(lb.Lattice.nccl_unique_id()), dtype=torch.uint8, device="cuda")

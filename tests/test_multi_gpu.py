@@ -56,6 +56,11 @@ def launch(n, extra, port):
     ["--nvel", "19", "--halo", "reduced", "--fd", "1", "--gradient", "27", "--steps", "8"],
     ["--nvel", "19", "--halo", "reduced", "--fd", "2", "--gradient", "7", "--p2p", "0", "--steps", "8"],
     ["--nvel", "27", "--halo", "full", "--lsize", "8", "6", "10", "--fd", "2", "--gradient", "27", "--visc", "1", "--steps", "8"],
+    # single-lattice streaming across ranks: the even sweep pushes into the neighbours' halo,
+    # the odd sweep stores into their interior; looked at after an odd and an even sweep
+    ["--nvel", "19", "--halo", "reduced", "--lattices", "1", "--steps", "6"],
+    ["--nvel", "19", "--halo", "reduced", "--lattices", "1", "--steps", "5"],
+    ["--nvel", "27", "--halo", "reduced", "--lattices", "1", "--steps", "7", "--lsize", "8", "6", "10"],
 ])
 def test_decomposed_equals_single(n, extra):
     if ngpu() < n:
@@ -72,6 +77,10 @@ def test_decomposed_equals_single(n, extra):
     ["--nvel", "27", "--halo", "reduced", "--grid", "1", "1", "2", "--lsize", "6", "6", "48"],
     ["--nvel", "9", "--halo", "reduced", "--grid", "1", "2", "1", "--lsize", "16", "32", "1"],
     ["--nvel", "19", "--halo", "reduced", "--grid", "1", "2", "1", "--lsize", "8", "6", "32", "--kt", "1e-4"],
+    ["--nvel", "19", "--halo", "reduced", "--grid", "1", "1", "2", "--lsize", "8", "6", "32", "--lattices", "1", "--steps", "6"],
+    ["--nvel", "19", "--halo", "reduced", "--grid", "1", "1", "2", "--lsize", "7", "5", "16", "--lattices", "1", "--steps", "5"],
+    ["--nvel", "19", "--halo", "reduced", "--grid", "1", "2", "1", "--lsize", "8", "6", "32", "--lattices", "1", "--steps", "7"],
+    ["--nvel", "9", "--halo", "reduced", "--grid", "1", "2", "1", "--lsize", "16", "32", "1", "--lattices", "1", "--steps", "6"],
 ])
 def test_two_ranks_along_other_axes(extra):
     if ngpu() < 2:
