@@ -153,6 +153,11 @@ long b200lb_nsite(const b200lb_t * h);                          /* host nsite = 
  *                      parameter (buffer-region gradient, flux form of the force with its
  *                      plane correction, phi_ch_le_fix_fluxes: ch_le_pass_a/_b). Default 1;
  *                      with 0 b200lb_le_commit / b200lb_ch_create refuse the combination
+ *   "pdl"         0/1  peer-memory halo: launch the sweep that follows the synchronisation
+ *                      kernel with programmatic stream serialisation, so that its interior
+ *                      starts under that kernel and only threads on a decomposed face wait
+ *                      (griddepcontrol.wait). Correct (tests pass with it) but measured to gain
+ *                      nothing on B200 (0.8066 -> 0.8057 ms): default 0
  *   "loopback"    0/1  single rank: send periodic directions through the exchange
  *                      buffers with this GPU as its own neighbour (tests, profiling) */
 int  b200lb_set_option(b200lb_t * h, const char * name, long value);

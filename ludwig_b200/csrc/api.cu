@@ -227,6 +227,9 @@ struct b200lb_s {
   P2PSync p2p;
   void * ipc_open[3*26 + 3]; int n_ipc_open;
   unsigned long long push_step;
+  long launches_at_sync;      // launch counter right after the last p2p_sync_kernel: if it has not moved,
+                              // that kernel is what the next sweep follows in the stream
+  int opt_pdl;
   bool pushed_valid;          // the halo data of lat[cur] was pushed by the sweep that wrote it
 };
 
@@ -519,6 +522,8 @@ static int create_impl(const b200lb_desc_t * desc, b200lb_s * h, const ModelOps 
   h->opt_grad_lazy = 1;
   h->opt_gradient = 7;
   h->opt_p2p = 1;
+  h->opt_pdl = 0;                // measured: no gain, so the plain launch stays the default
+  h->launches_at_sync = -1;
   h->opt_ch_fuse = 1;
   h->opt_ch_planes = 8;
   h->opt_ch_exact = 0;
@@ -656,6 +661,7 @@ extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
     h->opt_gradient = (int) v;
     return 0;
   }
+  if (!strcmp(name, "pdl")) { h->opt_pdl = (v != 0); return 0; }
   if (!strcmp(name, "p2p")) { if (join_comm(h)) return -1; h->opt_p2p = (v != 0); h->pushed_valid = false; return 0; }
   if (!strcmp(name, "loopback")) {
     if (h->desc.nranks > 1 && v) return fail("loopback is for single-rank lattices");
@@ -705,6 +711,7 @@ extern "C" long b200lb_get_option(const b200lb_t * h, const char * name) {
   if (!strcmp(name, "binary_walls")) return h->opt_binary_walls;
   if (!strcmp(name, "jphi_valid")) return h->jphi_valid;
   if (!strcmp(name, "p2p")) return h->opt_p2p;
+  if (!strcmp(name, "pdl")) return h->opt_pdl;
   if (!strcmp(name, "p2p_ready")) return h->p2p_ready;
   if (!strcmp(name, "loopback")) return h->opt_loopback;
   if (!strcmp(name, "direct_state")) return h->direct_state;
@@ -883,9 +890,13 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
   const int vec0 = a.vec;
   h->bnd_valid = false;
   h->pushed_valid = false;
+  a.pdl = false;
   if (push) {
     const int which = (dst == h->lat[0]) ? 0 : 1;
     a.P.push = 1;
+    // the sweep may start under the synchronisation kernel that precedes it (see
+    // lb_sweep_kernel): only when that kernel really is the previous thing in the stream
+    a.pdl = h->opt_pdl && h->launches == h->launches_at_sync && !h->tev_on;
     {
       // whole-sector stores of the row-end halo sites (site_kernels.cuh): low halo = last
       // word of an aligned group of four, high halo = first word, everything else in
@@ -928,6 +939,7 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
     p2p_sync_kernel<<<1, 32, 0, h->s_main>>>(h->p2p, h->push_step, P2P_WATCHDOG_NS, 1);
     CU(cudaGetLastError());
     h->launches++;
+    h->launches_at_sync = h->launches;
     h->pushed_valid = true;
   }
   if (pull) h->prop_wall = false;  // the bounce-back belonged to this propagation
@@ -2411,6 +2423,7 @@ extern "C" int b200lb_f_upload(b200lb_t * h, const double * f, int layout) {
     p2p_sync_kernel<<<1, 32, 0, h->s_main>>>(h->p2p, h->push_step, P2P_WATCHDOG_NS, 1);
     CU(cudaGetLastError());
     h->launches++;
+    h->launches_at_sync = h->launches;
     h->pushed_valid = false;
   }
   return 0;
@@ -2438,6 +2451,7 @@ extern "C" int b200lb_f_upload_range(b200lb_t * h, const double * f, long first,
     p2p_sync_kernel<<<1, 32, 0, h->s_main>>>(h->p2p, h->push_step, P2P_WATCHDOG_NS, 1);
     CU(cudaGetLastError());
     h->launches++;
+    h->launches_at_sync = h->launches;
     h->pushed_valid = false;
   }
   return 0;
@@ -2791,6 +2805,7 @@ extern "C" int b200lb_io_unpack(b200lb_t * h, const double * buf) {
     p2p_sync_kernel<<<1, 32, 0, h->s_main>>>(h->p2p, h->push_step, P2P_WATCHDOG_NS, 1);
     CU(cudaGetLastError());
     h->launches++;
+    h->launches_at_sync = h->launches;
     h->pushed_valid = false;
   }
   return 0;

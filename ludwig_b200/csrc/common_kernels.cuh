@@ -799,6 +799,9 @@ struct P2PSync {
 __global__ void p2p_sync_kernel(const P2PSync S, const unsigned long long step,
 				const unsigned long long timeout_ns, const int do_signal) {
   const int t = threadIdx.x;
+  // the sweep launched behind this kernel may start now (programmatic dependent launch): its
+  // interior needs nothing from here, its boundary threads wait for this kernel to complete
+  asm volatile("griddepcontrol.launch_dependents;");
   if (t < 27 && S.peer_flags[t] != nullptr) {
     if (do_signal) {
       __threadfence_system();

@@ -3,6 +3,7 @@
 // including. Binary-fluid kernels are built for 3-d models only
 // (src/collision.c:618 asserts NDIM == 3 for lb_collision_binary).
 
+#include <cstring>
 #include "model_ops.cuh"
 #include "model_tables.h"
 
@@ -41,9 +42,16 @@ static cudaError_t launch_one(SweepArgs & a) {
     if (P.push) {
       // peer-memory halo: the variants that also store into the neighbours' halo sites
       // (single-lattice odd sweep: into the neighbours' interior)
-      if (a.diag) lb_sweep_kernel<MODEL, VEC, PULL, COLLIDE, BINARY, GM, true, WALL, true, AA><<<grid, block, 0, a.stream>>>(P);
-      else lb_sweep_kernel<MODEL, VEC, PULL, COLLIDE, BINARY, GM, false, WALL, true, AA><<<grid, block, 0, a.stream>>>(P);
-      return cudaGetLastError();
+      cudaLaunchConfig_t cfg;
+      memset(&cfg, 0, sizeof(cfg));
+      cfg.gridDim = grid; cfg.blockDim = block; cfg.stream = a.stream;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      attr[0].val.programmaticStreamSerializationAllowed = 1;
+      cfg.attrs = attr;
+      cfg.numAttrs = a.pdl ? 1 : 0;
+      if (a.diag) return cudaLaunchKernelEx(&cfg, lb_sweep_kernel<MODEL, VEC, PULL, COLLIDE, BINARY, GM, true, WALL, true, AA>, P);
+      return cudaLaunchKernelEx(&cfg, lb_sweep_kernel<MODEL, VEC, PULL, COLLIDE, BINARY, GM, false, WALL, true, AA>, P);
     }
   }
   if (P.push) return cudaErrorInvalidValue;

@@ -15,6 +15,8 @@ struct SweepArgs {
   bool gmom;          // binary fluid, pull + collide: first moment of g from P.jphi, g not read
   bool wall;          // bounce-back on links folded into the pull (pull only)
   bool diag;          // accumulate conserved sums in the sweep (collide only)
+  bool pdl;           // peer-memory sweeps: launch with programmatic stream serialisation (the kernel
+                      // before it in the stream is p2p_sync_kernel)
   int aa;             // single-lattice streaming: 0 off, 1 even step, 2 odd step, 3 un-swap and stream
   long long nblocks;  // out: blocks launched (= diagnostic partials written)
   int vec;            // sites per thread (1 or 2)

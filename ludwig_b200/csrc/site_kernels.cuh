@@ -381,6 +381,20 @@ lb_sweep_kernel(const KParams P) {
   }
   double dq[8] = {0.0, 0.0, 1.0e300, -1.0e300, 0.0, 0.0, 0.0, 0.0};
 
+  if constexpr (PUSH) {
+    // Programmatic dependent launch: this grid may have started while the kernel before it
+    // in the stream -- p2p_sync_kernel, still waiting for the neighbours' flags -- is
+    // running. Only a thread whose sites touch a decomposed face reads halo sites or stores
+    // into a neighbour, and only such a thread has to wait for that kernel to complete;
+    // everybody else streams and collides meanwhile. (Without the launch attribute the
+    // instruction returns at once.)
+    bool edge = false;
+    if (!P.wrap[0] && L.h[0]) edge = edge || i0 == 0 || i0 == L.n[0] - 1;
+    if (!P.wrap[1] && L.h[1]) edge = edge || i1 == 0 || i1 == L.n[1] - 1;
+    if (!P.wrap[2] && L.h[2]) edge = edge || i2 == 0 || i2 + VEC - 1 >= L.n[2] - 1;
+    if (edge) asm volatile("griddepcontrol.wait;" ::: "memory");
+  }
+
   const i64 site = (i64)(i0 + L.h[0])*L.s0 + (i64)(i1 + L.h[1])*L.s1
                  + L.z0 + L.h[2] + i2;
 
