@@ -137,6 +137,9 @@ def test_single_lattice_state_machine_and_refusals():
     big.close()
 
     ref = run(nvel, nlocal, f0, (4, 9), 2)
+    m = np.zeros(tuple(n + 2 for n in nlocal), dtype=bool)
+    m[1:-1, 1:-1, 1:-1] = True
+    m = m.reshape(-1)             # halo sites of a streamed lattice are stale, as in the reference
     lat = lb.Lattice(nvel, nlocal)
     lat.set_param(eta_shear=0.07, eta_bulk=0.11)
     lat.lb_memcpy_h2d(f0)
@@ -158,13 +161,13 @@ def test_single_lattice_state_machine_and_refusals():
         lat.lb_propagation()
     with pytest.raises(lb.B200LBError, match="follows lb_collide"):
         lat.lb_propagation()
-    assert np.array_equal(lat.lb_memcpy_d2h(), ref[0][0])
+    assert np.array_equal(lat.lb_memcpy_d2h()[m], ref[0][0][m])
     # back to two lattices in mid run, and on: still the same lattice
     lat.set_option("lattices", 2)
     lat.step(2)
     lat.set_option("lattices", 1)
     lat.step(3)
-    assert np.array_equal(lat.lb_memcpy_d2h(), ref[1][0])
+    assert np.array_equal(lat.lb_memcpy_d2h()[m], ref[1][0][m])
     lat.close()
 
     lat = lb.Lattice(nvel, (6, 6, 6), ndist=2)
