@@ -230,6 +230,7 @@ struct b200lb_s {
   long launches_at_sync;      // launch counter right after the last p2p_sync_kernel: if it has not moved,
                               // that kernel is what the next sweep follows in the stream
   int opt_pdl;
+  int opt_grad_direct;        // 27-point gradient: one thread per site through the caches (1) or planes staged in shared memory (0)
   bool pushed_valid;          // the halo data of lat[cur] was pushed by the sweep that wrote it
 };
 
@@ -522,6 +523,7 @@ static int create_impl(const b200lb_desc_t * desc, b200lb_s * h, const ModelOps 
   h->opt_grad_lazy = 1;
   h->opt_gradient = 7;
   h->opt_p2p = 1;
+  h->opt_grad_direct = 1;
   h->opt_pdl = 0;                // measured: no gain, so the plain launch stays the default
   h->launches_at_sync = -1;
   h->opt_ch_fuse = 1;
@@ -662,6 +664,7 @@ extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
     return 0;
   }
   if (!strcmp(name, "pdl")) { h->opt_pdl = (v != 0); return 0; }
+  if (!strcmp(name, "grad_direct")) { h->opt_grad_direct = (v != 0); return 0; }
   if (!strcmp(name, "p2p")) { if (join_comm(h)) return -1; h->opt_p2p = (v != 0); h->pushed_valid = false; return 0; }
   if (!strcmp(name, "loopback")) {
     if (h->desc.nranks > 1 && v) return fail("loopback is for single-rank lattices");
@@ -712,6 +715,7 @@ extern "C" long b200lb_get_option(const b200lb_t * h, const char * name) {
   if (!strcmp(name, "jphi_valid")) return h->jphi_valid;
   if (!strcmp(name, "p2p")) return h->opt_p2p;
   if (!strcmp(name, "pdl")) return h->opt_pdl;
+  if (!strcmp(name, "grad_direct")) return h->opt_grad_direct;
   if (!strcmp(name, "p2p_ready")) return h->p2p_ready;
   if (!strcmp(name, "loopback")) return h->opt_loopback;
   if (!strcmp(name, "direct_state")) return h->direct_state;
@@ -1792,8 +1796,16 @@ static int run_grad27(b200lb_s * h) {
   dim3 block(G27_TZ, G27_TY, 1);
   dim3 grid((L.n[2] + G27_TZ - 1)/G27_TZ, (L.n[1] + G27_TY - 1)/G27_TY,
 	    (L.n[0] + G27_NX - 1)/G27_NX);
-  grad27_kernel<<<grid, block, 0, h->s_main>>>(L, h->selfper[0], h->selfper[1], h->selfper[2],
-					       h->phi, h->grad, h->delsq);
+  if (h->opt_grad_direct) {
+    dim3 b2(128, 2, 1);
+    dim3 g2((L.n[2] + 127)/128, (L.n[1] + 1)/2, (L.n[0] + G27M_NX - 1)/G27M_NX);
+    grad27_direct_kernel<<<g2, b2, 0, h->s_main>>>(L, h->selfper[0], h->selfper[1], h->selfper[2],
+						   h->phi, h->grad, h->delsq);
+  }
+  else {
+    grad27_kernel<<<grid, block, 0, h->s_main>>>(L, h->selfper[0], h->selfper[1], h->selfper[2],
+						 h->phi, h->grad, h->delsq);
+  }
   CU(cudaGetLastError());
   h->launches++;
   if (le_grad_fix(h, 27)) return -1;

@@ -81,76 +81,148 @@ halo_kernel(const HaloParams H) {
 // = 0): grad = (phi(+) - phi(-))/2, delsq summed in the order
 // +x -x +y -y +z -z -6 phi so that results are bit-identical.
 //
-// One block sweeps a (TY x TZ) tile of rows along x, keeping three z-y planes of
-// phi in shared memory as a rolling window: every phi value is fetched from
-// global memory once per tile (plus the tile's one-site apron).
+// One thread per site, seven loads through the read-only path. No shared-memory staging:
+// a z-y plane of phi is ~0.5 MB at 256^2, so the three planes a block's sites touch sit in
+// L2 (126 MB) and the y and z neighbours in L1; DRAM sees each phi once (8 B/site) and the
+// four output planes (32 B/site). Round 1 staged planes in a rolling shared-memory window
+// with two block barriers per plane, which serialised one global-load latency per plane:
+// 48 % of the HBM peak (0.210 ms at 256^3, profiles/r1_aux_kernels_256.log) against 87 %
+// for this form (0.1175 ms, profiles/r2_aux_kernels_256.log).
 // ---------------------------------------------------------------------------
 
-#define GRAD_TZ 64
-#define GRAD_TY 4
-#define GRAD_NX 16     // x-planes marched by one block
+#define GRAD_TZ 128
+#define GRAD_TY 2
+#define GRAD_NX 1      // x-planes per block (grid.z = n_x)
 
 __global__ void __launch_bounds__(GRAD_TZ*GRAD_TY)
 grad7_kernel(const Layout L, const int w0, const int w1, const int w2,
 	     const double * __restrict__ phi,
 	     double * __restrict__ grad, double * __restrict__ delsq) {
 
-  __shared__ double sm[3][GRAD_TY + 2][GRAD_TZ + 2];
+  const int i2 = blockIdx.x*GRAD_TZ + threadIdx.x;          // interior coordinates
+  const int i1 = blockIdx.y*GRAD_TY + threadIdx.y;
+  const int i0 = blockIdx.z;
+  if (i2 >= L.n[2] || i1 >= L.n[1]) return;
+  const i64 site = (i64)(i0 + L.h[0])*L.s0 + (i64)(i1 + L.h[1])*L.s1 + L.z0 + L.h[2] + i2;
 
-  const int tz = threadIdx.x, ty = threadIdx.y;
-  const int i2 = blockIdx.x*GRAD_TZ + tz;          // interior coords
-  const int i1 = blockIdx.y*GRAD_TY + ty;
-  const int x0 = blockIdx.z*GRAD_NX;
-  const int x1 = min(x0 + GRAD_NX, L.n[0]);
+  // Offsets to the -1 / +1 neighbours. A direction that is periodic within this rank
+  // (w = 1) wraps around instead of reading the halo plane.
+  const i64 xmo = (w0 && i0 == 0)           ? (i64) (L.n[0] - 1)*L.s0 : -L.s0;
+  const i64 xpo = (w0 && i0 == L.n[0] - 1)  ? -(i64) (L.n[0] - 1)*L.s0 : L.s0;
+  const i64 ymo = (w1 && i1 == 0)           ? (i64) (L.n[1] - 1)*L.s1 : -L.s1;
+  const i64 ypo = (w1 && i1 == L.n[1] - 1)  ? -(i64) (L.n[1] - 1)*L.s1 : L.s1;
+  const i64 zmo = (w2 && i2 == 0)           ? (i64) (L.n[2] - 1) : -1;
+  const i64 zpo = (w2 && i2 == L.n[2] - 1)  ? -(i64) (L.n[2] - 1) : 1;
 
-  // halo-inclusive coordinates of this thread's column, clamped for loads
-  const int c2 = min(i2, L.n[2] - 1) + L.h[2];
-  const int c1 = min(i1, L.n[1] - 1) + L.h[1];
-  const bool active = (i2 < L.n[2]) && (i1 < L.n[1]);
-  const i64 col = (i64) c1*L.s1 + L.z0 + c2;
+  const double * ph = phi + site;
+  const double c  = __ldg(ph);
+  const double xp = __ldg(ph + xpo), xm = __ldg(ph + xmo);
+  const double yp = __ldg(ph + ypo), ym = __ldg(ph + ymo);
+  const double zp = __ldg(ph + zpo), zm = __ldg(ph + zmo);
+  grad[site]           = 0.5*(xp - xm);
+  grad[L.nsd + site]   = 0.5*(yp - ym);
+  grad[2*L.nsd + site] = 0.5*(zp - zm);
+  // __dmul_rn keeps the product separately rounded (no FMA contraction): bit parity
+  delsq[site] = xp + xm + yp + ym + zp + zm - __dmul_rn(6.0, c);
+}
 
-  // Offsets to the -1 / +1 neighbours along y and z. A direction that is periodic
-  // within this rank (w = 1) wraps around instead of reading the halo plane.
-  const i64 zmo = (w2 && c2 == 1)      ? (i64) (L.n[2] - 1) : -1;
-  const i64 zpo = (w2 && c2 == L.n[2]) ? -(i64) (L.n[2] - 1) : 1;
-  const i64 ymo = (w1 && c1 == 1)      ? (i64) (L.n[1] - 1)*L.s1 : -L.s1;
-  const i64 ypo = (w1 && c1 == L.n[1]) ? -(i64) (L.n[1] - 1)*L.s1 : L.s1;
+// The 27-point arithmetic of one site from its 3 x 3 x 3 neighbourhood, m = plane x - 1,
+// c = plane x, p = plane x + 1, indexed [y][z]: the reference's order of additions.
+__device__ __forceinline__ void
+grad27_site(const Layout & L, const double (&m)[3][3], const double (&c)[3][3], const double (&p)[3][3],
+	    const i64 site, double * __restrict__ grad, double * __restrict__ delsq) {
+  const double r9 = 1.0/9.0;
+  const double hr9 = 0.5*r9;
+  double gx = p[0][0] - m[0][0];
+  double gy = m[2][0] - m[0][0];
+  double gz = m[0][2] - m[0][0];
+  double d2 = m[0][0];
+  #pragma unroll
+  for (int q = 1; q < 9; q++) {
+    const int a = q/3, b = q - 3*a;
+    gx = gx + p[a][b];  gx = gx - m[a][b];
+    d2 = d2 + m[a][b];
+  }
+  // d/dy: planes x-1, x, x+1; z ascending.  d/dz: planes, y ascending.
+  #pragma unroll
+  for (int k = 1; k < 3; k++) { gy = gy + m[2][k]; gy = gy - m[0][k]; }
+  #pragma unroll
+  for (int k = 0; k < 3; k++) { gy = gy + c[2][k]; gy = gy - c[0][k]; }
+  #pragma unroll
+  for (int k = 0; k < 3; k++) { gy = gy + p[2][k]; gy = gy - p[0][k]; }
+  #pragma unroll
+  for (int j = 1; j < 3; j++) { gz = gz + m[j][2]; gz = gz - m[j][0]; }
+  #pragma unroll
+  for (int j = 0; j < 3; j++) { gz = gz + c[j][2]; gz = gz - c[j][0]; }
+  #pragma unroll
+  for (int j = 0; j < 3; j++) { gz = gz + p[j][2]; gz = gz - p[j][0]; }
+  #pragma unroll
+  for (int q = 0; q < 9; q++) { if (q != 4) d2 = d2 + c[q/3][q - 3*(q/3)]; }
+  #pragma unroll
+  for (int q = 0; q < 9; q++) d2 = d2 + p[q/3][q - 3*(q/3)];
+  // separately rounded product (no FMA contraction): bit parity
+  d2 = d2 - __dmul_rn(26.0, c[1][1]);
+  grad[site]           = hr9*gx;
+  grad[L.nsd + site]   = hr9*gy;
+  grad[2*L.nsd + site] = hr9*gz;
+  delsq[site]          = r9*d2;
+}
 
-  // loads one z-y plane (with apron) at halo-inclusive x coordinate xa into sm[slot]
-  auto load_plane = [&](int slot, int xa) {
-    if (w0 && xa == 0) xa = L.n[0];
-    if (w0 && xa == L.n[0] + 1) xa = 1;
-    const double * pl = phi + (i64) xa*L.s0;
-    sm[slot][ty + 1][tz + 1] = __ldg(pl + col);
-    if (tz == 0)             sm[slot][ty + 1][0]           = __ldg(pl + col + zmo);
-    if (tz == GRAD_TZ - 1 || i2 == L.n[2] - 1)
-      sm[slot][ty + 1][tz + 2] = __ldg(pl + col + zpo);
-    if (ty == 0)             sm[slot][0][tz + 1]           = __ldg(pl + col + ymo);
-    if (ty == GRAD_TY - 1 || i1 == L.n[1] - 1)
-      sm[slot][ty + 2][tz + 1] = __ldg(pl + col + ypo);
+// The same stencil without staging: a thread marches G27M_NX sites along x and keeps the
+// 3 x 3 x 3 neighbourhood of its site in registers, shifting it by one plane per step, so a
+// site costs 9 loads through the read-only path (its row and the two next to it, in L1; the
+// plane itself in L2) and no barrier. One thread per site with 27 loads is L1-bound
+// (0.218 ms at 256^3); planes staged in shared memory with a barrier per plane take 0.182 ms;
+// this form 0.180 ms (profiles/r2_aux_kernels_256.log). All three do the same 86 FP64
+// additions per site in the reference's order, four dependent chains, no FMA: that, not
+// data movement, bounds the kernel (8 TFLOP/s of plain adds).
+#define G27M_NX 8
+
+__global__ void __launch_bounds__(256)
+grad27_direct_kernel(const Layout L, const int w0, const int w1, const int w2,
+		     const double * __restrict__ phi,
+		     double * __restrict__ grad, double * __restrict__ delsq) {
+  const int i2 = blockIdx.x*blockDim.x + threadIdx.x;
+  const int i1 = blockIdx.y*blockDim.y + threadIdx.y;
+  const int x0 = blockIdx.z*G27M_NX;
+  const int x1 = min(x0 + G27M_NX, L.n[0]);
+  if (i2 >= L.n[2] || i1 >= L.n[1]) return;
+  i64 oy[3], oz[3];
+  oy[0] = (w1 && i1 == 0)          ? (i64) (L.n[1] - 1)*L.s1 : -L.s1;
+  oy[1] = 0;
+  oy[2] = (w1 && i1 == L.n[1] - 1) ? -(i64) (L.n[1] - 1)*L.s1 : L.s1;
+  oz[0] = (w2 && i2 == 0)          ? (i64) (L.n[2] - 1) : -1;
+  oz[1] = 0;
+  oz[2] = (w2 && i2 == L.n[2] - 1) ? -(i64) (L.n[2] - 1) : 1;
+  const i64 col = (i64)(i1 + L.h[1])*L.s1 + L.z0 + L.h[2] + i2;
+  // halo-inclusive plane index xa (0 .. n_x + 1), wrapped where x is periodic within the rank
+  auto plane = [&](int xa) {
+    if (w0) xa = (xa == 0) ? L.n[0] : ((xa == L.n[0] + 1) ? 1 : xa);
+    return phi + (i64) xa*L.s0 + col;
   };
-
-  // planes x0-1 (halo-inclusive x0) and x0
-  load_plane(0, x0);
-  load_plane(1, x0 + 1);
-
-  for (int x = x0; x < x1; x++) {
-    const int sm1 = (x - x0) % 3, s0_ = (x - x0 + 1) % 3, sp1 = (x - x0 + 2) % 3;
-    load_plane(sp1, x + 2);
-    __syncthreads();
-    if (active) {
-      const double c  = sm[s0_][ty + 1][tz + 1];
-      const double xp = sm[sp1][ty + 1][tz + 1], xm = sm[sm1][ty + 1][tz + 1];
-      const double yp = sm[s0_][ty + 2][tz + 1], ym = sm[s0_][ty][tz + 1];
-      const double zp = sm[s0_][ty + 1][tz + 2], zm = sm[s0_][ty + 1][tz];
-      const i64 site = (i64)(x + L.h[0])*L.s0 + (i64)(i1 + L.h[1])*L.s1 + L.z0 + L.h[2] + i2;
-      grad[site]           = 0.5*(xp - xm);
-      grad[L.nsd + site]   = 0.5*(yp - ym);
-      grad[2*L.nsd + site] = 0.5*(zp - zm);
-      // __dmul_rn keeps the product separately rounded (no FMA contraction): bit parity
-      delsq[site] = xp + xm + yp + ym + zp + zm - __dmul_rn(6.0, c);
+  double m[3][3], c[3][3], p[3][3];
+  {
+    const double * pm = plane(x0), * pc = plane(x0 + 1);
+    #pragma unroll
+    for (int j = 0; j < 3; j++) {
+      #pragma unroll
+      for (int k = 0; k < 3; k++) { m[j][k] = __ldg(pm + oy[j] + oz[k]); c[j][k] = __ldg(pc + oy[j] + oz[k]); }
     }
-    __syncthreads();
+  }
+  for (int x = x0; x < x1; x++) {
+    const double * pp = plane(x + 2);
+    #pragma unroll
+    for (int j = 0; j < 3; j++) {
+      #pragma unroll
+      for (int k = 0; k < 3; k++) p[j][k] = __ldg(pp + oy[j] + oz[k]);
+    }
+    const i64 site = (i64)(x + L.h[0])*L.s0 + col;
+    grad27_site(L, m, c, p, site, grad, delsq);
+    #pragma unroll
+    for (int j = 0; j < 3; j++) {
+      #pragma unroll
+      for (int k = 0; k < 3; k++) { m[j][k] = c[j][k]; c[j][k] = p[j][k]; }
+    }
   }
 }
 
@@ -235,9 +307,6 @@ grad27_kernel(const Layout L, const int w0, const int w1, const int w2,
     for (int k = 0; k < 3; k++) { m[j][k] = sm[0][ty + j][tz + k]; c[j][k] = sm[1][ty + j][tz + k]; }
   __syncthreads();
 
-  const double r9 = 1.0/9.0;
-  const double hr9 = 0.5*r9;
-
   for (int x = x0; x < x1; x++) {
     const int slot = (x - x0) & 1;
     stash(slot, nxt);
@@ -249,41 +318,8 @@ grad27_kernel(const Layout L, const int w0, const int w1, const int w2,
       for (int k = 0; k < 3; k++) p[j][k] = sm[slot][ty + j][tz + k];
 
     if (active) {
-      double gx = p[0][0] - m[0][0];
-      double gy = m[2][0] - m[0][0];
-      double gz = m[0][2] - m[0][0];
-      double d2 = m[0][0];
-      #pragma unroll
-      for (int q = 1; q < 9; q++) {
-	const int a = q/3, b = q - 3*a;
-	gx = gx + p[a][b];  gx = gx - m[a][b];
-	d2 = d2 + m[a][b];
-      }
-      // d/dy: planes x-1, x, x+1; z ascending.  d/dz: planes, y ascending.
-      #pragma unroll
-      for (int k = 1; k < 3; k++) { gy = gy + m[2][k]; gy = gy - m[0][k]; }
-      #pragma unroll
-      for (int k = 0; k < 3; k++) { gy = gy + c[2][k]; gy = gy - c[0][k]; }
-      #pragma unroll
-      for (int k = 0; k < 3; k++) { gy = gy + p[2][k]; gy = gy - p[0][k]; }
-      #pragma unroll
-      for (int j = 1; j < 3; j++) { gz = gz + m[j][2]; gz = gz - m[j][0]; }
-      #pragma unroll
-      for (int j = 0; j < 3; j++) { gz = gz + c[j][2]; gz = gz - c[j][0]; }
-      #pragma unroll
-      for (int j = 0; j < 3; j++) { gz = gz + p[j][2]; gz = gz - p[j][0]; }
-      #pragma unroll
-      for (int q = 0; q < 9; q++) { if (q != 4) d2 = d2 + c[q/3][q - 3*(q/3)]; }
-      #pragma unroll
-      for (int q = 0; q < 9; q++) d2 = d2 + p[q/3][q - 3*(q/3)];
-      // separately rounded product (no FMA contraction): bit parity
-      d2 = d2 - __dmul_rn(26.0, c[1][1]);
-
       const i64 site = (i64)(x + L.h[0])*L.s0 + (i64)(i1 + L.h[1])*L.s1 + L.z0 + L.h[2] + i2;
-      grad[site]           = hr9*gx;
-      grad[L.nsd + site]   = hr9*gy;
-      grad[2*L.nsd + site] = hr9*gz;
-      delsq[site]          = r9*d2;
+      grad27_site(L, m, c, p, site, grad, delsq);
     }
     #pragma unroll
     for (int j = 0; j < 3; j++)

@@ -36,7 +36,9 @@ def main():
             peak = json.load(fh)
     except Exception:
         pass
-    for name, npt, nbytes in (("grad7_kernel", 7, 40), ("grad27_kernel", 27, 40)):
+    for name, npt, nbytes, direct in (("grad7_kernel", 7, 40, 1), ("grad27_direct_kernel", 27, 40, 1),
+                                      ("grad27_kernel (planes staged in shared memory)", 27, 40, 0)):
+        lat.set_option("grad_direct", direct)
         lat.field_grad_set(npt)
         for _ in range(3):
             lat.field_grad_compute()
