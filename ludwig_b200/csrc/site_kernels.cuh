@@ -713,9 +713,46 @@ lb_sweep_kernel(const KParams P) {
   // scheme (src/model.c:1192-1219): p goes to direction s iff s picks components of
   // c_p and the site lies on the boundary in each picked component.
   if constexpr (COLLIDE && PUSH && AA != 2) {
+    // Two sites per thread, both on the same x or y face and neither at a row end: their
+    // populations leave as ONE 128-bit store each, so a warp writes whole contiguous lines
+    // into the neighbour. Site by site (below) the same data are 8-byte stores with a
+    // 16-byte stride across the warp -- half-filled, byte-masked lines over NVLink.
+    bool pair_done = false;
+    if constexpr (VEC == 2) {
+      if (nv == 2 && i2 > 0 && i2 + 1 < L.n[2] - 1) {
+	const int e0 = (i0 == 0) ? -1 : ((i0 == L.n[0] - 1) ? 1 : 0);
+	const int e1 = (i1 == 0) ? -1 : ((i1 == L.n[1] - 1) ? 1 : 0);
+	if ((e0 != 0) != (e1 != 0)) {
+	  pair_done = true;
+	  #pragma unroll
+	  for (int d = 0; d < 2; d++) {
+	    const int sd = (d == 0) ? e0 : e1;
+	    if (sd != 0) {
+	      double * peer = P.peer[13 + sd*((d == 0) ? 9 : 3)];
+	      if (peer != nullptr) {
+		const i64 ext = (d == 0) ? (i64) L.n[0]*L.s0 : (i64) L.n[1]*L.s1;
+		double * base = peer + site - sd*ext;
+		#pragma unroll
+		for (int n = 0; n < NDIST; n++) {
+		  #pragma unroll
+		  for (int p = 1; p < Q; p++) {
+		    if (dcv<M>(p, d) == 1 || dcv<M>(p, d) == -1) {
+		      if (dcv<M>(p, d) == sd) {
+			*reinterpret_cast<double2 *>(base + (i64)(n*Q + ((AA == 1) ? Q - p : p))*L.nsd)
+			  = make_double2(f[n][0][p], f[n][VEC - 1][p]);
+		      }
+		    }
+		  }
+		}
+	      }
+	    }
+	  }
+	}
+      }
+    }
     #pragma unroll
     for (int v = 0; v < VEC; v++) {
-      if (v < nv) {
+      if (v < nv && !pair_done) {
 	int e[3];
 	e[0] = (i0 == 0) ? -1 : ((i0 == L.n[0] - 1) ? 1 : 0);
 	e[1] = (i1 == 0) ? -1 : ((i1 == L.n[1] - 1) ? 1 : 0);
