@@ -17,6 +17,7 @@
 static b200lb_t * b200_ = NULL;
 static pe_t * pe_ = NULL;
 static long nsite_ = 0;
+static int noise_uploaded_ = 0;
 static int sync_ = 0;         /* LUDWIG_B200_SYNC=1: the device is idle when a call returns,
 			       * so that Ludwig's own wall-clock timers (src/timer.c) bracket
 			       * the work of the call and not only its launch */
@@ -145,7 +146,13 @@ int lb_b200_collide(lb_t * lb, hydro_t * hydro, noise_t * noise, fe_t * fe, visc
   if (hydro == NULL) return 0;                     /* as src/collision.c:149 */
   if (visc) pe_fatal(pe_, "lb_halo_b200: viscosity model not wired into this build (b200lb_visc_*)\n");
   if (noise) noise_present(noise, NOISE_RHO, &noise_on);
-  if (noise_on) pe_fatal(pe_, "lb_halo_b200: isothermal fluctuations not wired into this build (b200lb_noise_*)\n");
+  if (noise_on && !noise_uploaded_) {
+    /* the generators Ludwig seeded (noise_init, src/ludwig.c:243) or read from a restart
+     * file move to the device once; from here on they advance there */
+    CK(b200lb_noise_state_upload(b200_, noise->state, HOST_LAYOUT));
+    noise_uploaded_ = 1;
+  }
+  CK(b200lb_noise_present_set(b200_, noise_on));
 
   memset(&p, 0, sizeof(p));
   physics_ref(&phys);
@@ -243,4 +250,30 @@ int lb_b200_field_grad_memcpy(field_grad_t * grad, tdpMemcpyKind flag) {
     CK(b200lb_field_download(b200_, B200LB_FIELD_DELSQ, grad->delsq, HOST_LAYOUT));
   }
   return done();
+}
+
+/* flat walls: the library folds the bounce-back into the propagation that follows wall_bbl
+ * and tallies the walls' momentum on the device */
+int lb_b200_wall_commit(wall_t * wall) {
+  assert(wall);
+  if (wall->param->isporousmedia) pe_fatal(pe_, "lb_halo_b200: porous media are not on the device path\n");
+  if (wall->param->iswall == 0) return 0;
+  if (wall->param->slip.active) pe_fatal(pe_, "lb_halo_b200: wall slip not wired into this build (b200lb_wall_slip_set)\n");
+  CK(b200lb_wall_commit(b200_, wall->param->isboundary, wall->param->ubot, wall->param->utop));
+  return 0;
+}
+
+int lb_b200_wall_bbl(wall_t * wall) {
+  assert(wall);
+  CK(b200lb_wall_bbl(b200_));
+  return done();
+}
+
+int lb_b200_wall_momentum(wall_t * wall, double f[3]) {
+  double fdev[3] = {0.0, 0.0, 0.0};
+  assert(wall);
+  CK(b200lb_wall_momentum(b200_, fdev));
+  /* wall->fnet holds what host code added through wall_momentum_add (src/wall.c:1279) */
+  for (int ia = 0; ia < 3; ia++) f[ia] = wall->fnet[ia] + fdev[ia];
+  return 0;
 }

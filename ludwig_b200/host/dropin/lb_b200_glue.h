@@ -20,6 +20,7 @@
 #include "free_energy.h"
 #include "noise.h"
 #include "visc.h"
+#include "wall.h"
 
 int lb_b200_active(void);                 /* lb_halo_scheme lb_halo_b200 was selected */
 
@@ -30,6 +31,10 @@ int lb_b200_halo(lb_t * lb);                                              /* src
 int lb_b200_collide(lb_t * lb, hydro_t * hydro, noise_t * noise, fe_t * fe, visc_t * visc);
                                                                           /* src/collision.c:144 lb_collide */
 int lb_b200_propagation(lb_t * lb);                                       /* src/propagation.c:43 */
+
+int lb_b200_wall_commit(wall_t * wall);                                   /* src/wall.c:168 wall_commit */
+int lb_b200_wall_bbl(wall_t * wall);                                      /* src/wall.c:960 wall_bbl */
+int lb_b200_wall_momentum(wall_t * wall, double f[3]);                    /* src/wall.c:1299 wall_momentum */
 
 int lb_b200_hydro_f_zero(const double fzero[3]);                          /* src/hydro.c:306 */
 int lb_b200_hydro_u_zero(const double uzero[3]);                          /* src/hydro.c:279 */

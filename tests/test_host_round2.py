@@ -101,7 +101,7 @@ def test_dropin_patch_anchors(tmp_path):
         os.chmod(str(src / n), 0o644)
     touched = mk.patch(str(src))
     assert set(touched) == {"collision.c", "field.c", "field_grad.c", "hydro.c", "model.c",
-                            "phi_lb_coupler.c", "propagation.c"}
+                            "phi_lb_coupler.c", "propagation.c", "wall.c"}
     for n in touched:
         text = open(str(src / n)).read()
         assert '#include "lb_b200_glue.h"' in text and "lb_b200_" in text

@@ -23,7 +23,10 @@ GOLD = json.load(open(os.path.join(HERE, "golden", "regression_logs.json")))
 TOL = 1e-12       # tests/awk-fp-diff.sh:40
 
 CASES = [("serial-dist-3du", "d3q19"), ("serial-dist-2kh", "d3q19"),
-         ("serial-spin-lb1", "d3q19"), ("serial-2khz-bm1", "d2q9")]
+         ("serial-spin-lb1", "d3q19"), ("serial-2khz-bm1", "d2q9"),
+         # the "next" rows of SURVEY 8(f) behind the real driver: isothermal fluctuations
+         # (noise_t handed to the device), flat walls (wall_commit / wall_bbl / wall_momentum)
+         ("serial-flct-t01", "d2q9"), ("serial-rect-ct1", "d3q19"), ("serial-wall-st1", "d3q19")]
 NUM = re.compile(r"[-+]?(?:\d+\.\d*|\.\d+|\d+)(?:[eE][-+]?\d+)?")
 TIMERS = ("Total", "Time step loop", "Propagation", "Propagtn (krnl) ", "Collision",
           "Collision (krnl) ", "Lattice halos", "phi gradients", "phi halos")

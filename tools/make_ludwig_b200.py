@@ -48,6 +48,12 @@ AT_FUNCTION_HEAD = [
      "  if (lb_b200_active()) return lb_b200_hydro_u_zero(uzero);\n"),
     ("hydro.c", r"__host__ int hydro_memcpy\(hydro_t \* obj, tdpMemcpyKind flag\) \{\n",
      "  if (lb_b200_active()) return lb_b200_hydro_memcpy(obj, flag);\n"),
+    ("wall.c", r"__host__ int wall_bbl\(wall_t \* wall\) \{\n",
+     "  if (lb_b200_active()) return lb_b200_wall_bbl(wall);\n"),
+    ("wall.c", r"__host__ int wall_momentum\(wall_t \* wall, double f\[3\]\) \{\n",
+     "  if (lb_b200_active()) return lb_b200_wall_momentum(wall, f);\n"),
+    ("wall.c", r"__host__ int wall_set_wall_distributions\(wall_t \* wall\) \{\n",
+     "  if (lb_b200_active()) return 0;    /* wall_bbl overwrites every population this sets */\n"),
     ("phi_lb_coupler.c", r"__host__ int phi_lb_to_field\(field_t \* phi, lb_t  \* lb\) \{\n",
      "  if (lb_b200_active()) return lb_b200_phi_lb_to_field(phi, lb);\n"),
     ("field.c", r"__host__ int field_halo\(field_t \* obj\) \{\n",
@@ -72,6 +78,9 @@ REPLACE = [
     ("distribution_rt.c", "    else if (havetype) {\n      pe_fatal(pe, \"lb_halo_scheme not recognised",
      "    else if (strcmp(htype, \"lb_halo_b200\") == 0) {\n      options.halo = LB_HALO_B200;\n    }\n"
      "    else if (havetype) {\n      pe_fatal(pe, \"lb_halo_scheme not recognised"),
+    # src/wall.c:168 wall_commit: the walls the host has just laid out
+    ("wall.c", "  wall_memcpy(wall, tdpMemcpyHostToDevice);\n\n  return 0;\n",
+     "  wall_memcpy(wall, tdpMemcpyHostToDevice);\n  if (lb_b200_active()) lb_b200_wall_commit(wall);\n\n  return 0;\n"),
     # src/model.c:132 lb_data_create: the device object next to the host one
     ("model.c", "  lb_halo_create(obj, &obj->h, obj->haloscheme);\n",
      "  if (obj->haloscheme == LB_HALO_B200) {\n"
