@@ -258,8 +258,15 @@ int lb_b200_wall_commit(wall_t * wall) {
   assert(wall);
   if (wall->param->isporousmedia) pe_fatal(pe_, "lb_halo_b200: porous media are not on the device path\n");
   if (wall->param->iswall == 0) return 0;
-  if (wall->param->slip.active) pe_fatal(pe_, "lb_halo_b200: wall slip not wired into this build (b200lb_wall_slip_set)\n");
   CK(b200lb_wall_commit(b200_, wall->param->isboundary, wall->param->ubot, wall->param->utop));
+  if (wall->param->slip.active) {
+    /* the faces of the slip table (src/wall.h:25-28); the library derives edges (the mean
+     * of the two walls) and corners (none) the way wall_init_boundaries_slip lays them out */
+    const double * s = wall->param->slip.s;
+    const double sbot[3] = {s[WALL_SLIP_XBOT], s[WALL_SLIP_YBOT], s[WALL_SLIP_ZBOT]};
+    const double stop[3] = {s[WALL_SLIP_XTOP], s[WALL_SLIP_YTOP], s[WALL_SLIP_ZTOP]};
+    CK(b200lb_wall_slip_set(b200_, sbot, stop, 1));
+  }
   return 0;
 }
 

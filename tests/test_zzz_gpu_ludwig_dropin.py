@@ -26,7 +26,10 @@ CASES = [("serial-dist-3du", "d3q19"), ("serial-dist-2kh", "d3q19"),
          ("serial-spin-lb1", "d3q19"), ("serial-2khz-bm1", "d2q9"),
          # the "next" rows of SURVEY 8(f) behind the real driver: isothermal fluctuations
          # (noise_t handed to the device), flat walls (wall_commit / wall_bbl / wall_momentum)
-         ("serial-flct-t01", "d2q9"), ("serial-rect-ct1", "d3q19"), ("serial-wall-st1", "d3q19")]
+         ("serial-flct-t01", "d2q9"), ("serial-rect-ct1", "d3q19"), ("serial-wall-st1", "d3q19"),
+         # partial slip at the walls (the slip table of wall_rt.c handed over face by face)
+         ("serial-rect-ct2", "d3q19"), ("serial-rect-ct3", "d3q19"), ("serial-rect-ct4", "d3q19"),
+         ("serial-rect-ct5", "d3q19")]
 NUM = re.compile(r"[-+]?(?:\d+\.\d*|\.\d+|\d+)(?:[eE][-+]?\d+)?")
 TIMERS = ("Total", "Time step loop", "Propagation", "Propagtn (krnl) ", "Collision",
           "Collision (krnl) ", "Lattice halos", "phi gradients", "phi halos")
