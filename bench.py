@@ -59,6 +59,9 @@ def parse():
     ap.add_argument("--overlap", type=int, default=1)
     ap.add_argument("--direct", type=int, default=1)
     ap.add_argument("--p2p", type=int, default=1, help="peer-memory halo (CUDA IPC) instead of NCCL messages")
+    ap.add_argument("--threads", type=int, default=0, help="threads per block of the sweep (0 = library default)")
+    ap.add_argument("--zpack", type=int, default=1,
+                    help="peer-memory halo: z faces through packed planes (1, library default) or row-end halo words (0)")
     ap.add_argument("--loopback", type=int, default=0, help="single GPU: run the halo exchange machinery with the GPU as its own neighbour")
     ap.add_argument("--grid", type=int, nargs=3, default=None, help="process grid (default 2x1x1, 2x2x1, 2x2x2)")
     ap.add_argument("--gradient", type=int, default=7, choices=[7, 27],
@@ -422,6 +425,8 @@ def configure(lb, lat, args, nvel, ndist, gradient=7):
     lat.set_option("hydro_write", args.hydro_write)
     lat.set_option("overlap", args.overlap)
     lat.set_option("direct", args.direct)
+    lat.set_option("zpack", args.zpack)
+    lat.set_option("threads", args.threads)
     if ndist == 2:
         lat.set_param(kt=args.kt, **BINARY_KW, **BINARY_FE)
         lat.field_grad_set(gradient)
@@ -592,6 +597,7 @@ def main():
     l0 = lat.launch_count()
     ms, nl, kms, nk = timed_steps(lat, comm, args.steps, args.warmup)
     launches = int(round(nl * args.steps))
+    z_faces_packed = bool(lat.get_option("zpacked"))     # the state the timed sweeps left behind
     clocks = sampler.result()
     mlups = sites_total / ms / 1e3
     stores_hydro = (args.hydro_write == 1) or bool(args.fd) or bool(args.le)
@@ -728,6 +734,7 @@ def main():
                 "hydro_write": args.hydro_write, "overlap": bool(args.overlap),
                 "direct_halo": bool(args.direct),
                 "p2p_halo": bool(args.p2p and (world > 1 or args.loopback)),
+                "z_faces_packed": z_faces_packed,
                 "loopback": args.loopback,
                 "gradient_points": args.gradient if ndist == 2 else None,
                 "walls": args.walls, "lees_edwards_planes": args.le or None,

@@ -17,6 +17,7 @@
 
 #include "../../include/b200lb.h"
 #include "common_kernels.cuh"
+#include "zpack_kernels.cuh"
 #include "le_field_kernels.cuh"
 #include "open_bc_kernels.cuh"
 #include "solid_grad_kernels.cuh"
@@ -190,7 +191,7 @@ struct b200lb_s {
   bool ghost;
 
   // options
-  int opt_fused, opt_halo, opt_hydro_write, opt_vec, opt_block, opt_halo_lazy, opt_overlap, opt_direct, opt_diag, opt_loopback, opt_grad_lazy, opt_p2p, opt_gradient, opt_ch_fuse, opt_ch_planes, opt_ch_exact, opt_g_moment, opt_le_fd, opt_binary_walls;
+  int opt_fused, opt_halo, opt_hydro_write, opt_vec, opt_block, opt_halo_lazy, opt_overlap, opt_direct, opt_diag, opt_loopback, opt_grad_lazy, opt_p2p, opt_gradient, opt_ch_fuse, opt_ch_planes, opt_ch_exact, opt_g_moment, opt_le_fd, opt_binary_walls, opt_threads;
 
   cudaStream_t s_main, s_x[2];
   cudaStream_t s_comm;       // halo exchange of decomposed directions (overlaps the interior sweep)
@@ -232,6 +233,10 @@ struct b200lb_s {
   int opt_pdl;
   int opt_grad_direct;        // 27-point gradient: one thread per site through the caches (1) or planes staged in shared memory (0)
   bool pushed_valid;          // the halo data of lat[cur] was pushed by the sweep that wrote it
+  // packed halo of the contiguous axis (KParams::zoff): every lattice array carries dense
+  // planes behind its population planes for the values peer-memory sweeps push across z faces
+  int opt_zpack;
+  bool zpacked[2];            // the z-face halo of lat[i] is in its packed planes, not in the row-end words
 };
 
 // A direction whose halo planes travel through send/receive buffers: decomposed over
@@ -325,6 +330,16 @@ static int site_kparams(b200lb_s * h, KParams & P) {
 }
 
 static size_t plane_bytes(const b200lb_s * h) { return (size_t) h->L.nsd*sizeof(double); }
+
+// one lattice array: the population planes, then the packed z-face halo planes (two faces,
+// at most nine populations each, over the halo-inclusive x-y extent; 4.8 MB at 256^3)
+static i64 zpack_doubles(const b200lb_s * h) {
+  const i64 n = (i64) 2*9*h->L.na[0]*h->L.na[1];
+  return (n + 15)/16*16;
+}
+static size_t lat_bytes(const b200lb_s * h) {
+  return plane_bytes(h)*h->nplane + (size_t) zpack_doubles(h)*sizeof(double);
+}
 
 // lazily allocated field planes, zero-filled
 static int need_planes(b200lb_s * h, double ** p, int nplanes) {
@@ -489,8 +504,8 @@ static int create_impl(const b200lb_desc_t * desc, b200lb_s * h, const ModelOps 
   const size_t pb = plane_bytes(h);
   h->opt_lattices = (desc->lattices == 1) ? 1 : 2;
   for (int i = 0; i < h->opt_lattices; i++) {
-    CU(cudaMalloc(&h->lat[i], pb*h->nplane));
-    CU(cudaMemsetAsync(h->lat[i], 0, pb*h->nplane, h->s_main));
+    CU(cudaMalloc(&h->lat[i], lat_bytes(h)));
+    CU(cudaMemsetAsync(h->lat[i], 0, lat_bytes(h), h->s_main));
   }
   // rho, u, force, grad and delsq are allocated when first needed (need_planes): a
   // run that keeps hydro on demand and never has a per-site force carries only the two
@@ -517,6 +532,7 @@ static int create_impl(const b200lb_desc_t * desc, b200lb_s * h, const ModelOps 
   // per site) and D2Q9 (few streams, occupancy matters more): measured, profiles/r1_bench_*
   h->opt_vec = (desc->nvel == 19) ? 2 : 1;
   h->opt_block = 128;
+  h->opt_zpack = 1;
   h->opt_halo_lazy = 1;
   h->opt_overlap = 1;
   h->opt_direct = 1;
@@ -619,8 +635,8 @@ extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
       if (h->aa_swapped || h->aa_ahead) return fail("lattices = 2: finish the time step first (lb_propagation)");
       if (h->p2p_ready && !h->lat[1]) return fail("lattices = 2: the neighbours have mapped a single lattice (desc.lattices = 1)");
       if (!h->lat[1]) {
-        CU(cudaMalloc(&h->lat[1], plane_bytes(h)*h->nplane));
-        CU(cudaMemsetAsync(h->lat[1], 0, plane_bytes(h)*h->nplane, h->s_main));
+        CU(cudaMalloc(&h->lat[1], lat_bytes(h)));
+        CU(cudaMemsetAsync(h->lat[1], 0, lat_bytes(h), h->s_main));
       }
       h->opt_lattices = 2;
     }
@@ -664,7 +680,11 @@ extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
     return 0;
   }
   if (!strcmp(name, "pdl")) { h->opt_pdl = (v != 0); return 0; }
-  if (!strcmp(name, "grad_direct")) { h->opt_grad_direct = (v != 0); return 0; }
+  if (!strcmp(name, "zpack")) { h->opt_zpack = (v != 0); return 0; }
+  if (!strcmp(name, "grad_direct")) {
+    if (v < 0 || v > 3) return fail("grad_direct: 0 (planes staged in shared memory), 1 (through the caches), 2 and 3 (the same, next plane prefetched; 80 or 94 registers)");
+    h->opt_grad_direct = (int) v; return 0;
+  }
   if (!strcmp(name, "p2p")) { if (join_comm(h)) return -1; h->opt_p2p = (v != 0); h->pushed_valid = false; return 0; }
   if (!strcmp(name, "loopback")) {
     if (h->desc.nranks > 1 && v) return fail("loopback is for single-rank lattices");
@@ -691,6 +711,10 @@ extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
     if (v != 32 && v != 64 && v != 128 && v != 256) return fail("block must be 32, 64, 128 or 256");
     h->opt_block = (int) v; return 0;
   }
+  if (!strcmp(name, "threads")) {
+    if (v != 0 && v != 64 && v != 128 && v != 256) return fail("threads per block of the sweep: 0 (default), 64, 128 or 256");
+    h->opt_threads = (int) v; return 0;
+  }
   return fail("unknown option '%s'", name);
 }
 
@@ -715,6 +739,8 @@ extern "C" long b200lb_get_option(const b200lb_t * h, const char * name) {
   if (!strcmp(name, "jphi_valid")) return h->jphi_valid;
   if (!strcmp(name, "p2p")) return h->opt_p2p;
   if (!strcmp(name, "pdl")) return h->opt_pdl;
+  if (!strcmp(name, "zpack")) return h->opt_zpack;
+  if (!strcmp(name, "zpacked")) return (h->zpacked[0] ? 1 : 0) | (h->zpacked[1] ? 2 : 0);
   if (!strcmp(name, "grad_direct")) return h->opt_grad_direct;
   if (!strcmp(name, "p2p_ready")) return h->p2p_ready;
   if (!strcmp(name, "loopback")) return h->opt_loopback;
@@ -722,6 +748,7 @@ extern "C" long b200lb_get_option(const b200lb_t * h, const char * name) {
   if (!strcmp(name, "halo_deferred")) return h->halo_deferred;
   if (!strcmp(name, "vec")) return h->opt_vec;
   if (!strcmp(name, "block")) return h->opt_block;
+  if (!strcmp(name, "threads")) return h->opt_threads;
   if (!strcmp(name, "prop_pending")) return h->prop_pending;
   if (!strcmp(name, "nsd")) return (long) h->L.nsd;
   if (!strcmp(name, "row_pitch")) return (long) h->L.s1;
@@ -823,6 +850,49 @@ static int wall_boxes(const b200lb_s * h, const KParams & P, int lo[7][3], int h
   return nb + 1;
 }
 
+// ---------------------------------------------------------------------------
+// Packed halo of the contiguous axis (KParams::zoff, site_kernels.cuh). Peer-memory sweeps
+// of the single fluid on two lattices leave what crosses a z face in the dense planes behind
+// the neighbour's lattice, and read their own z-face halo from theirs; zpacked[i] records
+// that lat[i] is in that state. Everything else that reads halo sites of a lattice goes
+// through zhalo_unpack first (the row-end halo words are then current and the flag clear).
+// ---------------------------------------------------------------------------
+
+static bool zpack_usable(const b200lb_s * h) {
+  return h->opt_zpack && h->desc.ndist == 1 && h->opt_lattices == 2 && !h->wall_on
+    && h->L.h[2] == 1 && decomposed(h, 2);
+}
+
+static int zhalo_unpack(b200lb_s * h, int w, cudaStream_t st) {
+  if (!h->zpacked[w]) return 0;
+  h->zpacked[w] = false;
+  if (!h->lat[w]) return 0;
+  const Layout & L = h->L;
+  ZPackTab T;
+  memset(&T, 0, sizeof(T));
+  int n[2] = {0, 0};
+  for (int p = 0; p < h->ops->nvel; p++) {
+    const int c2 = h->ops->cv[p][h->ops->dax[2]];
+    if (c2 ==  1) T.pidx[0][n[0]++] = p;
+    if (c2 == -1) T.pidx[1][n[1]++] = p;
+  }
+  T.np = n[0];
+  // the apron of a direction holds pushed values only when that direction is decomposed
+  const int x0 = decomposed(h, 0) ? 0 : L.h[0], x1 = L.h[0] + L.n[0] + (decomposed(h, 0) ? L.h[0] : 0);
+  const int y0 = decomposed(h, 1) ? 0 : L.h[1], y1 = L.h[1] + L.n[1] + (decomposed(h, 1) ? L.h[1] : 0);
+  dim3 block(256, 1, 1);
+  dim3 grid((y1 - y0 + 255)/256, x1 - x0, 2*T.np);
+  zhalo_unpack_kernel<<<grid, block, 0, st>>>(L, T, h->lat[w], (i64) h->nplane*L.nsd, x0, x1, y0, y1);
+  CU(cudaGetLastError());
+  h->launches++;
+  return 0;
+}
+
+static int zhalo_flush(b200lb_s * h, cudaStream_t st) {
+  for (int w = 0; w < 2; w++) { if (zhalo_unpack(h, w, st)) return -1; }
+  return 0;
+}
+
 static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
 		     double * dst, int aa = 0) {
   NvtxRange nvtx_(collide ? (pull ? "b200lb: Collision + Propagation (fused sweep)" : "b200lb: Collision (krnl)")
@@ -855,6 +925,7 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
   const bool hstore = collide && (h->opt_hydro_write == 1 || (h->opt_hydro_write == 2 && h->hydro_asked));
   a.vec = h->opt_vec;
   a.bx = h->opt_block;
+  a.bt = h->opt_threads;
   a.stream = h->s_main;
   if (collide) {
     for (int i = 0; i < 3; i++) a.P.fg[i] = h->prm.force_global[i] + (h->force_uniform ? h->fconst[i] : 0.0);
@@ -890,6 +961,15 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
   const bool push = collide && h->p2p_ready && h->opt_p2p && h->le_nplanes == 0;
   const bool walls = pull && h->prop_wall && h->wall_on;
   if (walls && a.binary && collide) return fail("internal: walls with the binary fluid are folded into the propagation, not into the collision");
+  // packed z-face halo: written by this sweep / read by this sweep
+  const int wsrc = (src == h->lat[0]) ? 0 : ((src == h->lat[1]) ? 1 : -1);
+  const int wdst = (dst == h->lat[0]) ? 0 : ((dst == h->lat[1]) ? 1 : -1);
+  const bool zuse = push && aa == 0 && wdst >= 0 && zpack_usable(h);
+  if (pull && wsrc >= 0 && h->zpacked[wsrc]) {
+    if (zuse) a.P.zread = 1;
+    else if (zhalo_unpack(h, wsrc, h->s_main)) return -1;
+  }
+  if (zuse) a.P.zoff = (i64) h->nplane*h->L.nsd;
   const int nbox = walls ? wall_boxes(h, a.P, lo, hi, iswall) : (push ? 1 : split_boxes(h, lo, hi));
   const int vec0 = a.vec;
   h->bnd_valid = false;
@@ -947,6 +1027,7 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
     h->pushed_valid = true;
   }
   if (pull) h->prop_wall = false;  // the bounce-back belonged to this propagation
+  if (wdst >= 0) h->zpacked[wdst] = zuse;
   h->halo_deferred = false;        // whatever was written has stale halos until the next lb_halo
   if (collide) {
     if (hstore) { h->u_fill_pending = false; h->hydro_stale = false; }
@@ -1210,6 +1291,7 @@ extern "C" int b200lb_open_bc_apply(b200lb_t * h) {
   if (ensure_hydro(h)) return -1;                  // rho, u of the collision just done
   if (need_hydro(h)) return -1;
   if (join_comm(h)) return -1;
+  if (zhalo_flush(h, h->s_main)) return -1;
   OpenTab T;
   memset(&T, 0, sizeof(T));
   T.L = h->L;
@@ -1377,6 +1459,7 @@ extern "C" int b200lb_le_apply(b200lb_t * h, double t) {
   if (h->prop_pending) return fail("lb_le_apply_boundary_conditions: called after lb_propagation (it belongs between lb_collide and lb_halo)");
   if (ensure_hydro(h)) return -1;                  // rho, u of the collision, before its populations change
   if (join_comm(h)) return -1;
+  if (zhalo_flush(h, h->s_main)) return -1;
   // velocity jump and displacement now: src/leesedwards.c:572-587, 633-655
   const double tle = ((t < 0.0) ? 0.0 : t) - 1.0*h->le_nt0;
   double uy_now = h->le_uy, dy_now = tle*h->le_uy;
@@ -1674,6 +1757,7 @@ static int direct_exchange(b200lb_s * h, double * data, cudaStream_t st) {
 // the decomposed directions of the current lattice, by the cheapest valid route
 static int lattice_exchange(b200lb_s * h, int scheme, cudaStream_t st) {
   if (scheme == B200LB_HALO_REDUCED && h->pushed_valid) return 0;   // already in the neighbours' halos
+  if (zhalo_flush(h, st)) return -1;
   if (scheme == B200LB_HALO_REDUCED && have_comm(h) && h->opt_direct) {
     if (direct_setup(h)) return -1;
     if (h->direct_state == 1) return direct_exchange(h, h->lat[h->cur], st);
@@ -1693,6 +1777,7 @@ static int lattice_halo(b200lb_s * h, int scheme) {
   if (h->opt_lattices == 1 && (h->aa_ahead || h->aa_swapped)) return 0;   // see b200lb_halo_swap
   if (!h->opt_halo_lazy) {
     if (join_comm(h)) return -1;
+    if (zhalo_flush(h, h->s_main)) return -1;
     return halo_exchange(h, h->lat[h->cur], true, h->nplane, scheme, 0, h->s_main);
   }
   if (have_comm(h) && h->opt_overlap) {
@@ -1717,6 +1802,7 @@ static int lattice_halo(b200lb_s * h, int scheme) {
 
 static int flush_halo(b200lb_s * h) {
   if (join_comm(h)) return -1;
+  if (zhalo_flush(h, h->s_main)) return -1;
   if (!h->halo_deferred) return 0;
   h->halo_deferred = false;
   return halo_exchange(h, h->lat[h->cur], true, h->nplane, h->halo_deferred_scheme, 2, h->s_main);
@@ -1799,8 +1885,15 @@ static int run_grad27(b200lb_s * h) {
   if (h->opt_grad_direct) {
     dim3 b2(128, 2, 1);
     dim3 g2((L.n[2] + 127)/128, (L.n[1] + 1)/2, (L.n[0] + G27M_NX - 1)/G27M_NX);
-    grad27_direct_kernel<<<g2, b2, 0, h->s_main>>>(L, h->selfper[0], h->selfper[1], h->selfper[2],
-						   h->phi, h->grad, h->delsq);
+    if (h->opt_grad_direct == 2)
+      grad27_direct_kernel<1><<<g2, b2, 0, h->s_main>>>(L, h->selfper[0], h->selfper[1], h->selfper[2],
+							h->phi, h->grad, h->delsq);
+    else if (h->opt_grad_direct == 3)
+      grad27_direct_kernel<2><<<g2, b2, 0, h->s_main>>>(L, h->selfper[0], h->selfper[1], h->selfper[2],
+							h->phi, h->grad, h->delsq);
+    else
+      grad27_direct_kernel<0><<<g2, b2, 0, h->s_main>>>(L, h->selfper[0], h->selfper[1], h->selfper[2],
+							h->phi, h->grad, h->delsq);
   }
   else {
     grad27_kernel<<<grid, block, 0, h->s_main>>>(L, h->selfper[0], h->selfper[1], h->selfper[2],
@@ -2426,6 +2519,7 @@ extern "C" int b200lb_f_upload(b200lb_t * h, const double * f, int layout) {
   h->bbl_armed = false;
   h->prop_wall = false;
   h->halo_deferred = false;
+  h->zpacked[h->cur] = false;       // the host copy brings its halo sites along
   if (transfer(h, h->lat[h->cur], h->nplane, const_cast<double *>(f), layout, true)) return -1;
   if (h->p2p_ready && h->opt_p2p) {
     // The upload wrote this rank's halo sites too. Neighbours may push into them only
@@ -2455,6 +2549,7 @@ extern "C" int b200lb_f_upload_range(b200lb_t * h, const double * f, long first,
     h->bbl_armed = false;
     h->prop_wall = false;
     h->halo_deferred = false;
+    h->zpacked[h->cur] = false;
   }
   if (transfer_range(h, h->lat[h->cur], h->nplane, const_cast<double *>(f), B200LB_HOST_AOS, true, first, count)) return -1;
   if (first + count == h->nsite_host && h->p2p_ready && h->opt_p2p) {
@@ -2810,6 +2905,7 @@ extern "C" int b200lb_io_unpack(b200lb_t * h, const double * buf) {
   h->bbl_armed = false;
   h->prop_wall = false;
   h->halo_deferred = false;
+  h->zpacked[h->cur] = false;
   if (io_transfer(h, const_cast<double *>(buf), true)) return -1;
   if (h->p2p_ready && h->opt_p2p) {
     // like lb_memcpy H2D: the restart read takes part in the signal/wait protocol

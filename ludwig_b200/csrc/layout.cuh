@@ -41,6 +41,13 @@ struct KParams {
   const double * delsq;   // [nsd]
   int push;               // write outgoing populations straight into the neighbours' halo sites
   int zsec;               // the halo site at either end of a row has a 32-byte sector of its own (rest: padding)
+  // Packed halo of the contiguous axis (peer-memory sweeps, single fluid, two lattices): the
+  // populations that cross a z face do not go to the row-end halo words -- one isolated
+  // 32-byte sector per row and population on either side -- but to dense planes behind the
+  // lattice's last population plane, [face][k][x][y] over the halo-inclusive x-y extent,
+  // face 0 = low halo (populations with c_z = +1, k-th of them in index order), face 1 = high
+  i64 zoff;               // doubles from a lattice's base to its packed planes; 0 = not in use
+  int zread;              // the source lattice's z-face halo is in its packed planes
   double * peer[27];      // neighbour's destination lattice per direction (dx+1)*9+(dy+1)*3+(dz+1), or null
   double * diag;          // per-block partial sums of the in-kernel diagnostics, or unused
   i64 diag_base;          // first partial slot of this launch

@@ -34,6 +34,7 @@ static cudaError_t launch_one(SweepArgs & a) {
   while (bx > 1 && bx/2 >= nt2) bx /= 2;      // thin slabs: let the warp span rows instead
   int by = 256/bx;
   if (BINARY || GHOST) by = (128/bx > 0) ? 128/bx : 1;
+  if (a.bt > 0) by = (a.bt/bx > 0) ? a.bt/bx : 1;
   while (by > 1 && by/2 >= n1) by /= 2;
   dim3 block(bx, by, 1);
   dim3 grid((nt2 + bx - 1)/bx, (n1 + by - 1)/by, n0);

@@ -21,6 +21,7 @@ struct SweepArgs {
   long long nblocks;  // out: blocks launched (= diagnostic partials written)
   int vec;            // sites per thread (1 or 2)
   int bx;             // threads per block along the contiguous axis
+  int bt;             // threads per block (0: 256, or 128 for the kernels with many live values)
   cudaStream_t stream;
 };
 

@@ -328,6 +328,40 @@ fluctuations(unsigned int (&w)[4], const KParams & P,
 }
 
 // ---------------------------------------------------------------------------
+// Packed halo of the contiguous axis (KParams::zoff). Populations with a component along the
+// contiguous device axis, counted in index order per sign: D3Q19 has 5 per face, D3Q27 9,
+// D2Q9 3.
+// ---------------------------------------------------------------------------
+
+template <class M> HD constexpr int zface_count() {
+  int n = 0;
+  for (int p = 0; p < M::NVEL; p++) if (dcv<M>(p, 2) == 1) n++;
+  return n;
+}
+// plane of population p in the packed block: face 0 (c_z = +1) first, then face 1; a table
+// the front end evaluates, so that unrolled loops fold the entries into immediates
+struct ZPlaneTab { int pl[27]; };
+template <class M> HD constexpr ZPlaneTab make_zplane_tab() {
+  ZPlaneTab t{};
+  int nlo = 0, nhi = 0;
+  for (int p = 0; p < M::NVEL; p++) {
+    t.pl[p] = 0;
+    if (dcv<M>(p, 2) ==  1) t.pl[p] = nlo++;
+    if (dcv<M>(p, 2) == -1) t.pl[p] = zface_count<M>() + nhi++;
+  }
+  return t;
+}
+template <class M> HD constexpr int zplane(int p) {
+  constexpr ZPlaneTab t = make_zplane_tab<M>();
+  return t.pl[p];
+}
+// slot of population p (c_z != 0) of the halo site above/below halo-inclusive column (xa, ya),
+// relative to the start of the packed planes
+template <class M> __device__ __forceinline__ i64 zslot(const Layout & L, const int p, const int xa, const int ya) {
+  return (i64) zplane<M>(p)*((i64) L.na[0]*L.na[1]) + (i64) xa*L.na[1] + ya;
+}
+
+// ---------------------------------------------------------------------------
 // The sweep. Thread (x) covers VEC consecutive sites of the contiguous axis,
 // thread (y) a row; blockIdx.z is the slowest axis. With VEC = 2 populations
 // moving along the contiguous axis are read as two 64-bit loads (they straddle
@@ -392,7 +426,9 @@ lb_sweep_kernel(const KParams P) {
     if (!P.wrap[0] && L.h[0]) edge = edge || i0 == 0 || i0 == L.n[0] - 1;
     if (!P.wrap[1] && L.h[1]) edge = edge || i1 == 0 || i1 == L.n[1] - 1;
     if (!P.wrap[2] && L.h[2]) edge = edge || i2 == 0 || i2 + VEC - 1 >= L.n[2] - 1;
+#ifdef __CUDA_ARCH__
     if (edge) asm volatile("griddepcontrol.wait;" ::: "memory");
+#endif
   }
 
   const i64 site = (i64)(i0 + L.h[0])*L.s0 + (i64)(i1 + L.h[1])*L.s1
@@ -518,6 +554,19 @@ lb_sweep_kernel(const KParams P) {
 	// moving along the contiguous axis: the pair straddles the aligned one
 	#pragma unroll
 	for (int v = 0; v < VEC; v++) {
+	  if constexpr (PUSH && AA == 0 && !BINARY) {
+	    // first / last site of a row, and the neighbours' sweeps left the halo beyond it in
+	    // the packed planes: dense lines shared with the rows next to this one instead of a
+	    // 32-byte sector that holds this one value
+	    const bool atface = !P.wrap[2] && ((c2 == 1) ? (i2 + v == 0) : (i2 + v == L.n[2] - 1));
+	    if (P.zread && atface) {
+	      int xa = i0 + L.h[0] - dcv<M>(p, 0), ya = i1 + L.h[1] - dcv<M>(p, 1);
+	      if (P.wrap[0]) { if (xa < L.h[0]) xa += L.n[0]; else if (xa >= L.h[0] + L.n[0]) xa -= L.n[0]; }
+	      if (P.wrap[1]) { if (ya < L.h[1]) ya += L.n[1]; else if (ya >= L.h[1] + L.n[1]) ya -= L.n[1]; }
+	      f[n][v][p] = ld1<NC>(P.src + P.zoff + zslot<M>(L, p, xa, ya));
+	      continue;
+	    }
+	  }
 	  f[n][v][p] = ld1<NC>(src + v + (c2 == 1 ? zm[v] : zp[v]));
 	}
       }
@@ -774,7 +823,18 @@ lb_sweep_kernel(const KParams P) {
 	      if (peer != nullptr) {
 		const i64 ext = (d == 0) ? (i64) L.n[0]*L.s0 : ((d == 1) ? (i64) L.n[1]*L.s1 : (i64) L.n[2]);
 		double * base = peer + site + v - sd*ext;
-		if (d == 2 && P.zsec) {
+		if (d == 2 && AA == 0 && !BINARY && P.zoff != 0) {
+		  // the neighbour's packed planes: consecutive rows are consecutive words
+		  #pragma unroll
+		  for (int p = 1; p < Q; p++) {
+		    if (dcv<M>(p, 2) == 1 || dcv<M>(p, 2) == -1) {
+		      if (dcv<M>(p, 2) == sd) {
+			peer[P.zoff + zslot<M>(L, p, i0 + L.h[0], i1 + L.h[1])] = f[0][v][p];
+		      }
+		    }
+		  }
+		}
+		else if (d == 2 && P.zsec) {
 		  // The contiguous axis: each row ends in ONE halo site, whose 32-byte sector
 		  // holds nothing else but row padding. An 8-byte store leaves a partially
 		  // written sector, which HBM (ECC) turns into a read-modify-write: 2 n_x n_y
@@ -791,10 +851,18 @@ lb_sweep_kernel(const KParams P) {
 			  double * a = base + (i64)(n*Q + ((AA == 1) ? Q - p : p))*L.nsd;
 			  const double val = f[n][v][p];
 			  if (sd == 1) {   // lands in the low halo: last word of its sector
+#ifdef __CUDA_ARCH__
 			    asm volatile("st.global.v4.f64 [%0], {%1, %1, %1, %2};" :: "l"(a - 3), "d"(0.0), "d"(val) : "memory");
+#else
+			    a[-3] = 0.0; a[-2] = 0.0; a[-1] = 0.0; a[0] = val;      // tools/push_emulate.cpp steps through this on the host
+#endif
 			  }
 			  else {           // lands in the high halo: first word of its sector
+#ifdef __CUDA_ARCH__
 			    asm volatile("st.global.v4.f64 [%0], {%2, %1, %1, %1};" :: "l"(a), "d"(0.0), "d"(val) : "memory");
+#else
+			    a[0] = val; a[1] = 0.0; a[2] = 0.0; a[3] = 0.0;
+#endif
 			  }
 			}
 		      }
@@ -840,8 +908,14 @@ lb_sweep_kernel(const KParams P) {
 		  const bool on = (s0 == 0 || e[0] == s0) && (s1 == 0 || e[1] == s1) && (s2 == 0 || e[2] == s2);
 		  double * peer = P.peer[(s0 + 1)*9 + (s1 + 1)*3 + (s2 + 1)];
 		  if (on && peer != nullptr) {
-		    const i64 rs = site + v - (i64) s0*L.n[0]*L.s0 - (i64) s1*L.n[1]*L.s1 - (i64) s2*L.n[2];
-		    peer[(i64)(n*Q + ((AA == 1) ? Q - p : p))*L.nsd + rs] = f[n][v][p];
+		    if (s2 != 0 && AA == 0 && !BINARY && P.zoff != 0) {
+		      // a halo site beyond a z face of that neighbour (an edge or corner of its box)
+		      peer[P.zoff + zslot<M>(L, p, i0 + L.h[0] - s0*L.n[0], i1 + L.h[1] - s1*L.n[1])] = f[n][v][p];
+		    }
+		    else {
+		      const i64 rs = site + v - (i64) s0*L.n[0]*L.s0 - (i64) s1*L.n[1]*L.s1 - (i64) s2*L.n[2];
+		      peer[(i64)(n*Q + ((AA == 1) ? Q - p : p))*L.nsd + rs] = f[n][v][p];
+		    }
 		  }
 		}
 	      }

@@ -40,6 +40,7 @@ def main():
     ap.add_argument("--overlap", type=int, default=1)
     ap.add_argument("--direct", type=int, default=1)
     ap.add_argument("--p2p", type=int, default=1)
+    ap.add_argument("--zpack", type=int, default=1)
     ap.add_argument("--kt", type=float, default=0.0, help="> 0: isothermal fluctuations")
     ap.add_argument("--gradient", type=int, default=7)
     ap.add_argument("--walls", type=int, nargs=3, default=[0, 0, 0])
@@ -93,6 +94,7 @@ def main():
     lat.set_option("fused", args.fused)
     lat.set_option("overlap", args.overlap)
     lat.set_option("direct", args.direct)
+    lat.set_option("zpack", args.zpack)
     lat.set_option("halo", lb.HALO_REDUCED if args.halo == "reduced" else lb.HALO_FULL)
     kw = dict(eta_shear=0.1, eta_bulk=0.1)
     if ndist == 2:

@@ -643,11 +643,13 @@ def test_peer_memory_halo_loopback(nvel, nlocal, ndist, fused):
 @pytest.mark.parametrize("nvel,nlocal", [(19, (10, 8, 6)), (27, (5, 7, 6)), (19, (3, 70, 130)),
                                          (19, (40, 5, 64)), (19, (2, 1, 3))])
 @pytest.mark.parametrize("mode", ["wrap", "halo", "loopback"])
-def test_gradient_27pt_bit_exact(nvel, nlocal, mode):
+@pytest.mark.parametrize("kernel", [None, 0, 1, 2, 3])
+def test_gradient_27pt_bit_exact(nvel, nlocal, mode, kernel):
     """grad_3d_27pt_fluid_d2: bit-exact against the oracle on random phi, with the
     periodic directions wrapped inside the kernel (halo_lazy), read from the halo
     planes after the eager local copies, and after a loopback exchange (corners must
-    arrive through the x, y, z sequence). Tile-edge and ragged extents included."""
+    arrive through the x, y, z sequence). Tile-edge and ragged extents included.
+    kernel: option grad_direct -- every form of the kernel (None: the library's default)."""
     import ludwig_b200 as lb
     lat, orc = mk(nvel, nlocal, 2)
     n = orc.nsite
@@ -662,6 +664,8 @@ def test_gradient_27pt_bit_exact(nvel, nlocal, mode):
     if mode == "loopback":
         lat.set_option("loopback", 1)
     lat.field_grad_set(27)
+    if kernel is not None:
+        lat.set_option("grad_direct", kernel)
     # upload interior values only (halo zeroed): field_halo has to provide the rest
     phi_in = np.where(m, phi, 0.0)
     lat.field_h2d(lb.FIELD_PHI, phi_in)

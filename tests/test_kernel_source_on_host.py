@@ -55,6 +55,19 @@ def test_binary_sweep_with_handed_over_flux_is_identical():
     assert r.stdout.count("ok  ") == 70          # 54 flux hand-over cases + 16 wall propagations
 
 
+def test_peer_memory_sweeps_identical_to_wrap_sweeps():
+    """tools/push_emulate.cpp: the PUSH variants of the sweep with the lattice as its own
+    neighbour, halo words / whole sectors / packed z-face planes, and zhalo_unpack_kernel."""
+    exe = os.path.join(TOOLS, "_push_emulate")
+    subprocess.check_call(["g++", "-O1", "-ffp-contract=off", "-w", "-std=c++17", "-I" + CUDA_INC,
+                           "-o", exe, os.path.join(TOOLS, "push_emulate.cpp")])
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:]
+    assert "all cases identical" in r.stdout and "FAIL" not in r.stdout
+    assert r.stdout.count("ok  ") == 231         # 198 three-step cases + 33 unpack cases
+    assert r.stdout.count("packed planes") == 66
+
+
 def test_lees_edwards_order_parameter_kernels_match_oracle():
     out = run_tool("check_le_field_on_host.py")
     assert "all identical to the oracle" in out and "FAIL" not in out

@@ -18,10 +18,11 @@ from ludwig_b200 import synthetic             # noqa: E402
 from ludwig_b200 import models_host           # noqa: E402
 
 
-def run(nvel, local, mask, p2p, steps, hydro_write, f0):
+def run(nvel, local, mask, p2p, steps, hydro_write, f0, zpack=1):
     lat = lb.Lattice(nvel, local)
     lat.set_option("halo", lb.HALO_REDUCED)
     lat.set_option("hydro_write", hydro_write)
+    lat.set_option("zpack", zpack)
     lat.set_param(eta_shear=0.1, eta_bulk=0.1)
     if mask:
         lat.set_option("loopback", 8 | mask)
@@ -40,7 +41,7 @@ def run(nvel, local, mask, p2p, steps, hydro_write, f0):
     sites = float(local[0]) * local[1] * local[2]
     st = lat.stats()
     lat.close()
-    return {"mask": mask, "p2p": p2p, "ms_per_step": ms, "mlups": sites / ms / 1e3,
+    return {"mask": mask, "p2p": p2p, "zpack": zpack if (p2p and mask & 4) else None, "ms_per_step": ms, "mlups": sites / ms / 1e3,
             "launches_per_step": nl, "mass": st[0]}
 
 
@@ -54,8 +55,10 @@ def main():
     local = (args.size,) * 3
     cv, wv = models_host.cv(args.nvel), models_host.wv(args.nvel)
     f0 = synthetic.make_state(cv, wv, local)
-    for mask, p2p in [(0, 0), (1, 1), (2, 1), (4, 1), (7, 1), (1, 0), (4, 0), (7, 0)]:
-        print(json.dumps(run(args.nvel, local, mask, p2p, args.steps, args.hydro_write, f0)),
+    # z faces and all three axes: row-end halo words (zpack 0) against the packed planes (1)
+    for mask, p2p, zpack in [(0, 0, 1), (1, 1, 1), (2, 1, 1), (4, 1, 0), (4, 1, 1), (7, 1, 0), (7, 1, 1),
+                             (0, 0, 1), (4, 1, 0), (4, 1, 1), (7, 1, 0), (7, 1, 1)]:
+        print(json.dumps(run(args.nvel, local, mask, p2p, args.steps, args.hydro_write, f0, zpack)),
               flush=True)
 
 
