@@ -235,8 +235,8 @@ struct b200lb_s {
   bool pushed_valid;          // the halo data of lat[cur] was pushed by the sweep that wrote it
   // packed halo of the contiguous axis (KParams::zoff): every lattice array carries dense
   // planes behind its population planes for the values peer-memory sweeps push across z faces
-  int opt_zpack;
-  bool zpacked[2];            // the z-face halo of lat[i] is in its packed planes, not in the row-end words
+  int opt_zpack;              // 0 off; arrangement of the packed planes, see zpack_geom
+  int zpacked[2];             // != 0: the z-face halo of lat[i] is in its packed planes (in this arrangement), not in the row-end words
 };
 
 // A direction whose halo planes travel through send/receive buffers: decomposed over
@@ -334,8 +334,20 @@ static size_t plane_bytes(const b200lb_s * h) { return (size_t) h->L.nsd*sizeof(
 // one lattice array: the population planes, then the packed z-face halo planes (two faces,
 // at most nine populations each, over the halo-inclusive x-y extent; 4.8 MB at 256^3)
 static i64 zpack_doubles(const b200lb_s * h) {
-  const i64 n = (i64) 2*9*h->L.na[0]*h->L.na[1];
+  const i64 n = (i64) 2*9*h->L.na[0]*h->L.na[1]*4;      // room for a 32-byte sector per column
   return (n + 15)/16*16;
+}
+
+// arrangement of the packed planes (option zpack), y fastest: 1 = one word per column
+// (default); 2 = a whole 32-byte sector per column, written as one 256-bit store. Measured
+// (profiles/r2b_push_axes_zpack2.log, r2b_bench_2gpu_112_zpack*.json): 1 is the faster one,
+// on one GPU and across NVLink; x fastest makes no difference.
+static void zpack_geom(const b200lb_s * h, int mode, i64 * zsx, i64 * zsy, i64 * zsp, int * zvec) {
+  const i64 na0 = h->L.na[0], na1 = h->L.na[1];
+  const i64 w = (mode == 2) ? 4 : 1;
+  *zvec = (mode == 2) ? 1 : 0;
+  *zsy = w; *zsx = w*na1;
+  *zsp = w*na0*na1;
 }
 static size_t lat_bytes(const b200lb_s * h) {
   return plane_bytes(h)*h->nplane + (size_t) zpack_doubles(h)*sizeof(double);
@@ -680,11 +692,11 @@ extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
     return 0;
   }
   if (!strcmp(name, "pdl")) { h->opt_pdl = (v != 0); return 0; }
-  if (!strcmp(name, "zpack")) { h->opt_zpack = (v != 0); return 0; }
-  if (!strcmp(name, "grad_direct")) {
-    if (v < 0 || v > 3) return fail("grad_direct: 0 (planes staged in shared memory), 1 (through the caches), 2 and 3 (the same, next plane prefetched; 80 or 94 registers)");
-    h->opt_grad_direct = (int) v; return 0;
+  if (!strcmp(name, "zpack")) {
+    if (v < 0 || v > 2) return fail("zpack: 0 (row-end halo words), 1 (packed planes, one word per column), 2 (packed planes, a 32-byte sector per column)");
+    h->opt_zpack = (int) v; return 0;
   }
+  if (!strcmp(name, "grad_direct")) { h->opt_grad_direct = (v != 0); return 0; }
   if (!strcmp(name, "p2p")) { if (join_comm(h)) return -1; h->opt_p2p = (v != 0); h->pushed_valid = false; return 0; }
   if (!strcmp(name, "loopback")) {
     if (h->desc.nranks > 1 && v) return fail("loopback is for single-rank lattices");
@@ -865,8 +877,11 @@ static bool zpack_usable(const b200lb_s * h) {
 
 static int zhalo_unpack(b200lb_s * h, int w, cudaStream_t st) {
   if (!h->zpacked[w]) return 0;
-  h->zpacked[w] = false;
+  const int mode = h->zpacked[w];
+  h->zpacked[w] = 0;
   if (!h->lat[w]) return 0;
+  i64 zsx, zsy, zsp; int zvec;
+  zpack_geom(h, mode, &zsx, &zsy, &zsp, &zvec);
   const Layout & L = h->L;
   ZPackTab T;
   memset(&T, 0, sizeof(T));
@@ -882,7 +897,7 @@ static int zhalo_unpack(b200lb_s * h, int w, cudaStream_t st) {
   const int y0 = decomposed(h, 1) ? 0 : L.h[1], y1 = L.h[1] + L.n[1] + (decomposed(h, 1) ? L.h[1] : 0);
   dim3 block(256, 1, 1);
   dim3 grid((y1 - y0 + 255)/256, x1 - x0, 2*T.np);
-  zhalo_unpack_kernel<<<grid, block, 0, st>>>(L, T, h->lat[w], (i64) h->nplane*L.nsd, x0, x1, y0, y1);
+  zhalo_unpack_kernel<<<grid, block, 0, st>>>(L, T, h->lat[w], (i64) h->nplane*L.nsd, zsx, zsy, zsp, x0, x1, y0, y1);
   CU(cudaGetLastError());
   h->launches++;
   return 0;
@@ -966,10 +981,14 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
   const int wdst = (dst == h->lat[0]) ? 0 : ((dst == h->lat[1]) ? 1 : -1);
   const bool zuse = push && aa == 0 && wdst >= 0 && zpack_usable(h);
   if (pull && wsrc >= 0 && h->zpacked[wsrc]) {
-    if (zuse) a.P.zread = 1;
+    if (zuse && h->zpacked[wsrc] == h->opt_zpack) a.P.zread = 1;
     else if (zhalo_unpack(h, wsrc, h->s_main)) return -1;
   }
-  if (zuse) a.P.zoff = (i64) h->nplane*h->L.nsd;
+  if (zuse) {
+    a.P.zoff = (i64) h->nplane*h->L.nsd;
+    a.P.zwrite = 1;
+    zpack_geom(h, h->opt_zpack, &a.P.zsx, &a.P.zsy, &a.P.zsp, &a.P.zvec);
+  }
   const int nbox = walls ? wall_boxes(h, a.P, lo, hi, iswall) : (push ? 1 : split_boxes(h, lo, hi));
   const int vec0 = a.vec;
   h->bnd_valid = false;
@@ -1027,7 +1046,7 @@ static int run_sweep(b200lb_s * h, bool pull, bool collide, const double * src,
     h->pushed_valid = true;
   }
   if (pull) h->prop_wall = false;  // the bounce-back belonged to this propagation
-  if (wdst >= 0) h->zpacked[wdst] = zuse;
+  if (wdst >= 0) h->zpacked[wdst] = zuse ? h->opt_zpack : 0;
   h->halo_deferred = false;        // whatever was written has stale halos until the next lb_halo
   if (collide) {
     if (hstore) { h->u_fill_pending = false; h->hydro_stale = false; }
@@ -1885,15 +1904,8 @@ static int run_grad27(b200lb_s * h) {
   if (h->opt_grad_direct) {
     dim3 b2(128, 2, 1);
     dim3 g2((L.n[2] + 127)/128, (L.n[1] + 1)/2, (L.n[0] + G27M_NX - 1)/G27M_NX);
-    if (h->opt_grad_direct == 2)
-      grad27_direct_kernel<1><<<g2, b2, 0, h->s_main>>>(L, h->selfper[0], h->selfper[1], h->selfper[2],
-							h->phi, h->grad, h->delsq);
-    else if (h->opt_grad_direct == 3)
-      grad27_direct_kernel<2><<<g2, b2, 0, h->s_main>>>(L, h->selfper[0], h->selfper[1], h->selfper[2],
-							h->phi, h->grad, h->delsq);
-    else
-      grad27_direct_kernel<0><<<g2, b2, 0, h->s_main>>>(L, h->selfper[0], h->selfper[1], h->selfper[2],
-							h->phi, h->grad, h->delsq);
+    grad27_direct_kernel<<<g2, b2, 0, h->s_main>>>(L, h->selfper[0], h->selfper[1], h->selfper[2],
+						   h->phi, h->grad, h->delsq);
   }
   else {
     grad27_kernel<<<grid, block, 0, h->s_main>>>(L, h->selfper[0], h->selfper[1], h->selfper[2],
@@ -2519,7 +2531,7 @@ extern "C" int b200lb_f_upload(b200lb_t * h, const double * f, int layout) {
   h->bbl_armed = false;
   h->prop_wall = false;
   h->halo_deferred = false;
-  h->zpacked[h->cur] = false;       // the host copy brings its halo sites along
+  h->zpacked[h->cur] = 0;           // the host copy brings its halo sites along
   if (transfer(h, h->lat[h->cur], h->nplane, const_cast<double *>(f), layout, true)) return -1;
   if (h->p2p_ready && h->opt_p2p) {
     // The upload wrote this rank's halo sites too. Neighbours may push into them only
@@ -2549,7 +2561,7 @@ extern "C" int b200lb_f_upload_range(b200lb_t * h, const double * f, long first,
     h->bbl_armed = false;
     h->prop_wall = false;
     h->halo_deferred = false;
-    h->zpacked[h->cur] = false;
+    h->zpacked[h->cur] = 0;
   }
   if (transfer_range(h, h->lat[h->cur], h->nplane, const_cast<double *>(f), B200LB_HOST_AOS, true, first, count)) return -1;
   if (first + count == h->nsite_host && h->p2p_ready && h->opt_p2p) {
@@ -2905,7 +2917,7 @@ extern "C" int b200lb_io_unpack(b200lb_t * h, const double * buf) {
   h->bbl_armed = false;
   h->prop_wall = false;
   h->halo_deferred = false;
-  h->zpacked[h->cur] = false;
+  h->zpacked[h->cur] = 0;
   if (io_transfer(h, const_cast<double *>(buf), true)) return -1;
   if (h->p2p_ready && h->opt_p2p) {
     // like lb_memcpy H2D: the restart read takes part in the signal/wait protocol

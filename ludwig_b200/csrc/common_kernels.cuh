@@ -178,12 +178,11 @@ grad27_site(const Layout & L, const double (&m)[3][3], const double (&c)[3][3], 
 // data movement, bounds the kernel (8 TFLOP/s of plain adds).
 #define G27M_NX 8
 
-// PF: the nine values of the plane after next are requested before the site's 86 additions
-// start, so that a warp's loads (DRAM latency: each plane is new) and its arithmetic overlap
-// instead of alternating -- with 24 warps per SM the other warps alone do not cover both.
-// PF = 1: held to 80 registers (three blocks per SM, a few spilled words); PF = 2: 94 registers
-template <int PF>
-__global__ void __launch_bounds__(256, PF == 1 ? 3 : 1)
+// Tried and dropped (profiles/r2b_aux_kernels_256.log): requesting the nine values of the plane
+// after next before the additions start, so that a warp's own loads and arithmetic overlap.
+// The nine extra live values cost registers (94, or 80 with a few spills): 0.249 and 0.201 ms
+// against 0.180 ms -- the kernel lives on occupancy, not on per-warp overlap.
+__global__ void __launch_bounds__(256)
 grad27_direct_kernel(const Layout L, const int w0, const int w1, const int w2,
 		     const double * __restrict__ phi,
 		     double * __restrict__ grad, double * __restrict__ delsq) {
@@ -214,35 +213,6 @@ grad27_direct_kernel(const Layout L, const int w0, const int w1, const int w2,
       for (int k = 0; k < 3; k++) { m[j][k] = __ldg(pm + oy[j] + oz[k]); c[j][k] = __ldg(pc + oy[j] + oz[k]); }
     }
   }
-  if constexpr (PF != 0) {
-    double q[3][3];
-    {
-      const double * pp = plane(x0 + 2);
-      #pragma unroll
-      for (int j = 0; j < 3; j++) {
-	#pragma unroll
-	for (int k = 0; k < 3; k++) p[j][k] = __ldg(pp + oy[j] + oz[k]);
-      }
-    }
-    for (int x = x0; x < x1; x++) {
-      if (x + 1 < x1) {
-	const double * pq = plane(x + 3);
-	#pragma unroll
-	for (int j = 0; j < 3; j++) {
-	  #pragma unroll
-	  for (int k = 0; k < 3; k++) q[j][k] = __ldg(pq + oy[j] + oz[k]);
-	}
-      }
-      const i64 site = (i64)(x + L.h[0])*L.s0 + col;
-      grad27_site(L, m, c, p, site, grad, delsq);
-      #pragma unroll
-      for (int j = 0; j < 3; j++) {
-	#pragma unroll
-	for (int k = 0; k < 3; k++) { m[j][k] = c[j][k]; c[j][k] = p[j][k]; p[j][k] = q[j][k]; }
-      }
-    }
-  }
-  else {
   for (int x = x0; x < x1; x++) {
     const double * pp = plane(x + 2);
     #pragma unroll
@@ -257,7 +227,6 @@ grad27_direct_kernel(const Layout L, const int w0, const int w1, const int w2,
       #pragma unroll
       for (int k = 0; k < 3; k++) { m[j][k] = c[j][k]; c[j][k] = p[j][k]; }
     }
-  }
   }
 }
 

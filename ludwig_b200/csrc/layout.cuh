@@ -48,6 +48,9 @@ struct KParams {
   // face 0 = low halo (populations with c_z = +1, k-th of them in index order), face 1 = high
   i64 zoff;               // doubles from a lattice's base to its packed planes; 0 = not in use
   int zread;              // the source lattice's z-face halo is in its packed planes
+  int zwrite;             // this sweep pushes across z faces into the neighbours' packed planes
+  i64 zsx, zsy, zsp;      // strides (doubles) of the halo-inclusive x and y column index and of a plane
+  int zvec;               // a column owns a whole 32-byte sector (its value + three padding words), stored as one
   double * peer[27];      // neighbour's destination lattice per direction (dx+1)*9+(dy+1)*3+(dz+1), or null
   double * diag;          // per-block partial sums of the in-kernel diagnostics, or unused
   i64 diag_base;          // first partial slot of this launch

@@ -357,8 +357,20 @@ template <class M> HD constexpr int zplane(int p) {
 }
 // slot of population p (c_z != 0) of the halo site above/below halo-inclusive column (xa, ya),
 // relative to the start of the packed planes
-template <class M> __device__ __forceinline__ i64 zslot(const Layout & L, const int p, const int xa, const int ya) {
-  return (i64) zplane<M>(p)*((i64) L.na[0]*L.na[1]) + (i64) xa*L.na[1] + ya;
+template <class M> __device__ __forceinline__ i64 zslot(const KParams & P, const int p, const int xa, const int ya) {
+  return (i64) zplane<M>(p)*P.zsp + (i64) xa*P.zsx + (i64) ya*P.zsy;
+}
+__device__ __forceinline__ void zstore(double * a, const double val, const int zvec) {
+  if (zvec) {
+#ifdef __CUDA_ARCH__
+    asm volatile("st.global.v4.f64 [%0], {%2, %1, %1, %1};" :: "l"(a), "d"(0.0), "d"(val) : "memory");
+#else
+    a[0] = val; a[1] = 0.0; a[2] = 0.0; a[3] = 0.0;
+#endif
+  }
+  else {
+    *a = val;
+  }
 }
 
 // ---------------------------------------------------------------------------
@@ -458,6 +470,32 @@ lb_sweep_kernel(const KParams P) {
 
   double f[NDIST][VEC][Q];
 
+  // Packed z-face planes (KParams::zoff) of the source lattice: which of this thread's sites
+  // pull from beyond a z face, and the column part of the slot for c = -1, 0, +1 along x and
+  // y (32-bit: the planes of one lattice hold fewer than 2^31 words)
+  bool zlo[VEC], zhi[VEC];
+  int zcx[3], zcy[3], zpl = 0;
+  if constexpr (PUSH && AA == 0 && !BINARY && PULL) {
+    const bool zr = P.zread && !P.wrap[2];
+    #pragma unroll
+    for (int v = 0; v < VEC; v++) { zlo[v] = zr && (i2 + v == 0); zhi[v] = zr && (i2 + v == L.n[2] - 1); }
+    zpl = (int) P.zsp;
+    #pragma unroll
+    for (int c = -1; c <= 1; c++) {
+      int xa = i0 + L.h[0] - c, ya = i1 + L.h[1] - c;
+      if (P.wrap[0]) { if (xa < L.h[0]) xa += L.n[0]; else if (xa >= L.h[0] + L.n[0]) xa -= L.n[0]; }
+      if (P.wrap[1]) { if (ya < L.h[1]) ya += L.n[1]; else if (ya >= L.h[1] + L.n[1]) ya -= L.n[1]; }
+      zcx[c + 1] = xa*(int) P.zsx;
+      zcy[c + 1] = ya*(int) P.zsy;
+    }
+  }
+  else {
+    #pragma unroll
+    for (int v = 0; v < VEC; v++) { zlo[v] = false; zhi[v] = false; }
+    #pragma unroll
+    for (int c = 0; c < 3; c++) { zcx[c] = 0; zcy[c] = 0; }
+  }
+
   // Walls: is this site next to a wall layer, per device axis and side? (axes 0 and 1
   // are uniform over a row of threads; the contiguous axis differs per site)
   bool w0lo = false, w0hi = false, w1lo = false, w1hi = false;
@@ -554,20 +592,19 @@ lb_sweep_kernel(const KParams P) {
 	// moving along the contiguous axis: the pair straddles the aligned one
 	#pragma unroll
 	for (int v = 0; v < VEC; v++) {
+	  const double * at = src + v + (c2 == 1 ? zm[v] : zp[v]);
 	  if constexpr (PUSH && AA == 0 && !BINARY) {
-	    // first / last site of a row, and the neighbours' sweeps left the halo beyond it in
-	    // the packed planes: dense lines shared with the rows next to this one instead of a
-	    // 32-byte sector that holds this one value
-	    const bool atface = !P.wrap[2] && ((c2 == 1) ? (i2 + v == 0) : (i2 + v == L.n[2] - 1));
-	    if (P.zread && atface) {
-	      int xa = i0 + L.h[0] - dcv<M>(p, 0), ya = i1 + L.h[1] - dcv<M>(p, 1);
-	      if (P.wrap[0]) { if (xa < L.h[0]) xa += L.n[0]; else if (xa >= L.h[0] + L.n[0]) xa -= L.n[0]; }
-	      if (P.wrap[1]) { if (ya < L.h[1]) ya += L.n[1]; else if (ya >= L.h[1] + L.n[1]) ya -= L.n[1]; }
-	      f[n][v][p] = ld1<NC>(P.src + P.zoff + zslot<M>(L, p, xa, ya));
-	      continue;
-	    }
+	    // first / last site of a row whose halo site the neighbours' sweeps left in the packed
+	    // planes: another address for the same load. A select, not a branch -- a branch
+	    // per population keeps the loads of a thread from being issued back to back, and
+	    // the sweep then waits for memory one population at a time (0.81 -> 1.00 ms at
+	    // 256^3, profiles/r2b_zpack.md)
+	    const bool pk = (c2 == 1) ? zlo[v] : zhi[v];
+	    const double * zat = P.src + P.zoff
+	      + (i64) (zplane<M>(p)*zpl + zcx[dcv<M>(p, 0) + 1] + zcy[dcv<M>(p, 1) + 1]);
+	    at = pk ? zat : at;
 	  }
-	  f[n][v][p] = ld1<NC>(src + v + (c2 == 1 ? zm[v] : zp[v]));
+	  f[n][v][p] = ld1<NC>(at);
 	}
       }
     }
@@ -823,13 +860,13 @@ lb_sweep_kernel(const KParams P) {
 	      if (peer != nullptr) {
 		const i64 ext = (d == 0) ? (i64) L.n[0]*L.s0 : ((d == 1) ? (i64) L.n[1]*L.s1 : (i64) L.n[2]);
 		double * base = peer + site + v - sd*ext;
-		if (d == 2 && AA == 0 && !BINARY && P.zoff != 0) {
+		if (d == 2 && AA == 0 && !BINARY && P.zwrite) {
 		  // the neighbour's packed planes: consecutive rows are consecutive words
 		  #pragma unroll
 		  for (int p = 1; p < Q; p++) {
 		    if (dcv<M>(p, 2) == 1 || dcv<M>(p, 2) == -1) {
 		      if (dcv<M>(p, 2) == sd) {
-			peer[P.zoff + zslot<M>(L, p, i0 + L.h[0], i1 + L.h[1])] = f[0][v][p];
+			zstore(peer + P.zoff + zslot<M>(P, p, i0 + L.h[0], i1 + L.h[1]), f[0][v][p], P.zvec);
 		      }
 		    }
 		  }
@@ -908,9 +945,9 @@ lb_sweep_kernel(const KParams P) {
 		  const bool on = (s0 == 0 || e[0] == s0) && (s1 == 0 || e[1] == s1) && (s2 == 0 || e[2] == s2);
 		  double * peer = P.peer[(s0 + 1)*9 + (s1 + 1)*3 + (s2 + 1)];
 		  if (on && peer != nullptr) {
-		    if (s2 != 0 && AA == 0 && !BINARY && P.zoff != 0) {
+		    if (s2 != 0 && AA == 0 && !BINARY && P.zwrite) {
 		      // a halo site beyond a z face of that neighbour (an edge or corner of its box)
-		      peer[P.zoff + zslot<M>(L, p, i0 + L.h[0] - s0*L.n[0], i1 + L.h[1] - s1*L.n[1])] = f[n][v][p];
+		      zstore(peer + P.zoff + zslot<M>(P, p, i0 + L.h[0] - s0*L.n[0], i1 + L.h[1] - s1*L.n[1]), f[n][v][p], P.zvec);
 		    }
 		    else {
 		      const i64 rs = site + v - (i64) s0*L.n[0]*L.s0 - (i64) s1*L.n[1]*L.s1 - (i64) s2*L.n[2];

@@ -22,6 +22,7 @@ struct ZPackTab {
 
 __global__ void __launch_bounds__(256)
 zhalo_unpack_kernel(const Layout L, const ZPackTab T, double * __restrict__ lat, const i64 zoff,
+		    const i64 zsx, const i64 zsy, const i64 zsp,
 		    const int x0, const int x1, const int y0, const int y1) {
   const int ya = y0 + blockIdx.x*blockDim.x + threadIdx.x;
   const int xa = x0 + blockIdx.y;
@@ -29,7 +30,7 @@ zhalo_unpack_kernel(const Layout L, const ZPackTab T, double * __restrict__ lat,
   if (ya >= y1 || xa >= x1) return;
   const int face = pl/T.np, k = pl - face*T.np;
   const int p = T.pidx[face][k];
-  const double val = lat[zoff + (i64) pl*((i64) L.na[0]*L.na[1]) + (i64) xa*L.na[1] + ya];
+  const double val = lat[zoff + (i64) pl*zsp + (i64) xa*zsx + (i64) ya*zsy];
   const i64 zw = (face == 0) ? (L.h[2] - 1) : (L.h[2] + L.n[2]);
   lat[(i64) p*L.nsd + (i64) xa*L.s0 + (i64) ya*L.s1 + L.z0 + zw] = val;
 }

@@ -643,7 +643,7 @@ def test_peer_memory_halo_loopback(nvel, nlocal, ndist, fused):
 @pytest.mark.parametrize("nvel,nlocal", [(19, (10, 8, 6)), (27, (5, 7, 6)), (19, (3, 70, 130)),
                                          (19, (40, 5, 64)), (19, (2, 1, 3))])
 @pytest.mark.parametrize("mode", ["wrap", "halo", "loopback"])
-@pytest.mark.parametrize("kernel", [None, 0, 1, 2, 3])
+@pytest.mark.parametrize("kernel", [None, 0, 1])
 def test_gradient_27pt_bit_exact(nvel, nlocal, mode, kernel):
     """grad_3d_27pt_fluid_d2: bit-exact against the oracle on random phi, with the
     periodic directions wrapped inside the kernel (halo_lazy), read from the halo

@@ -64,8 +64,8 @@ def test_peer_memory_sweeps_identical_to_wrap_sweeps():
     r = subprocess.run([exe], capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-3000:]
     assert "all cases identical" in r.stdout and "FAIL" not in r.stdout
-    assert r.stdout.count("ok  ") == 231         # 198 three-step cases + 33 unpack cases
-    assert r.stdout.count("packed planes") == 66
+    assert r.stdout.count("ok  ") == 330         # 264 three-step cases + 66 unpack cases
+    assert r.stdout.count("packed planes") == 132  # both arrangements (option zpack = 1, 2)
 
 
 def test_lees_edwards_order_parameter_kernels_match_oracle():

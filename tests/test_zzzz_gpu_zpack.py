@@ -49,15 +49,19 @@ def state(nvel, nlocal):
 @pytest.mark.parametrize("fused", [1, 0])
 @pytest.mark.parametrize("nrelax", [0, 2])
 def test_packed_planes_equal_wrap(nvel, nlocal, mask, fused, nrelax):
+    if nrelax == 2 and nvel != 19:
+        nrelax = 1            # TRT is D3Q19's (as in the reference); BGK keeps ghost modes too
     f0 = state(nvel, nlocal)
     m = interior(nvel, nlocal)
     ref = lattice(nvel, nlocal, 0, 0, fused, nrelax)
     ref.lb_memcpy_h2d(f0)
     ref.step(7)
     want = ref.lb_memcpy_d2h()
+    ref.step(7)
+    want14 = ref.lb_memcpy_d2h()
     ref.close()
     got = {}
-    for zpack in (0, 1):
+    for zpack in (0, 1, 2):
         lat = lattice(nvel, nlocal, mask, zpack, fused, nrelax)
         lat.lb_memcpy_h2d(f0)
         lat.step(7)
@@ -67,9 +71,19 @@ def test_packed_planes_equal_wrap(nvel, nlocal, mask, fused, nrelax):
             assert (lat.get_option("zpacked") != 0) == bool(zpack and zdec)
         got[zpack] = lat.lb_memcpy_d2h()
         assert lat.get_option("zpacked") == 0
+        if zpack:
+            # switching the arrangement between two sweeps goes through the halo words
+            lat.step(2)
+            lat.set_option("zpack", 3 - zpack)
+            lat.step(2)
+            lat.set_option("zpack", 0)
+            lat.step(3)
+            more = lat.lb_memcpy_d2h()
         lat.sync()
         lat.close()
         assert np.array_equal(got[zpack][m], want[m]), "zpack %d" % zpack
+        if zpack:
+            assert np.array_equal(more[m], want14[m]), "zpack %d and on" % zpack
 
 
 def test_every_way_out_of_the_packed_state():
@@ -114,8 +128,9 @@ def test_every_way_out_of_the_packed_state():
         lat.close()
         return out
 
-    for how in ("collide_then_download", "full_halo", "option_off", "p2p_off", "stats_then_on"):
-        a, b = run(0, how), run(1, how)
+    for how, zpack in [(h, z) for h in ("collide_then_download", "full_halo", "option_off", "p2p_off",
+                                         "stats_then_on") for z in (1, 2)]:
+        a, b = run(0, how), run(zpack, how)
         if how == "collide_then_download":
             assert np.array_equal(a, b), how          # halo sites too
         else:

@@ -41,7 +41,8 @@ def run(nvel, local, mask, p2p, steps, hydro_write, f0, zpack=1):
     sites = float(local[0]) * local[1] * local[2]
     st = lat.stats()
     lat.close()
-    return {"mask": mask, "p2p": p2p, "zpack": zpack if (p2p and mask & 4) else None, "ms_per_step": ms, "mlups": sites / ms / 1e3,
+    return {"mask": mask, "p2p": p2p, "zpack": zpack if (p2p and mask & 4) else None,
+            "ms_per_step": ms, "mlups": sites / ms / 1e3,
             "launches_per_step": nl, "mass": st[0]}
 
 
@@ -55,12 +56,14 @@ def main():
     local = (args.size,) * 3
     cv, wv = models_host.cv(args.nvel), models_host.wv(args.nvel)
     f0 = synthetic.make_state(cv, wv, local)
-    # z faces and all three axes: row-end halo words (zpack 0) against the packed planes (1)
-    for mask, p2p, zpack in [(0, 0, 1), (1, 1, 1), (2, 1, 1), (4, 1, 0), (4, 1, 1), (7, 1, 0), (7, 1, 1),
-                             (0, 0, 1), (4, 1, 0), (4, 1, 1), (7, 1, 0), (7, 1, 1)]:
+    # z faces and all three axes: row-end halo words (zpack 0) against the packed planes, one
+    # word (1) or one sector (2) per column
+    cases = [(0, 0, 0), (1, 1, 0), (2, 1, 0)]
+    cases += [(4, 1, z) for z in (0, 1, 2)]
+    cases += [(7, 1, z) for z in (0, 1, 2)]
+    for mask, p2p, zpack in cases:
         print(json.dumps(run(args.nvel, local, mask, p2p, args.steps, args.hydro_write, f0, zpack)),
               flush=True)
-
 
 if __name__ == "__main__":
     main()

@@ -96,15 +96,24 @@ template <int VEC> static void geometry(const Layout & L, dim3 & grid, dim3 & bl
   grid = dim3((nt2 + bx - 1)/bx, (L.n[1] + by - 1)/by, L.n[0]);
 }
 
+// zpack_geom (api.cu)
+static void zgeom(const Layout & L, int arr, KParams & P) {
+  const i64 na0 = L.na[0], na1 = L.na[1];
+  const i64 w = (arr == 2) ? 4 : 1;
+  P.zvec = (arr == 2) ? 1 : 0;
+  P.zsy = w; P.zsx = w*na1;
+  P.zsp = w*na0*na1;
+}
+
 // mode 0: 8-byte stores into the row-end halo words; 1: whole-sector stores where the layout
-// allows; 2: packed planes
+// allows; 2, 3: packed planes in arrangement mode - 1 (option zpack)
 template <class M, int VEC, int GM>
 static int run_case(const int nlocal[3], const int dec[3], int mode, int zalign) {
   constexpr int Q = M::NVEL;
   const bool twod = (M::NDIM == 2);
   const Layout L = make_layout(nlocal, zalign, twod);
   const size_t nsd = (size_t) L.nsd;
-  const size_t zpack = (size_t) 2*9*L.na[0]*L.na[1] + 16;
+  const size_t zpack = (size_t) 2*9*L.na[0]*L.na[1]*4 + 16;
   const size_t nlat = Q*nsd + zpack;
 
   std::vector<double> init(nlat, 0.0), force(3*nsd);
@@ -151,8 +160,8 @@ static int run_case(const int nlocal[3], const int dec[3], int mode, int zalign)
       P.zsec = (L.h[2] == 1 && lo >= 3 && (lo + 1) % 4 == 0 && hi % 4 == 0 && hi + 3 < L.s1
 		&& L.s1 % 4 == 0 && L.s0 % 4 == 0 && L.nsd % 4 == 0) ? 1 : 0;
     }
-    const bool zuse = (mode == 2) && dec[2];
-    if (zuse) P.zoff = (i64) Q*L.nsd;
+    const bool zuse = (mode >= 2) && dec[2];
+    if (zuse) { P.zoff = (i64) Q*L.nsd; P.zwrite = 1; zgeom(L, mode - 1, P); }
     auto peers = [&](double * lat) {
       for (int k = 0; k < 27; k++) {
 	const int dir[3] = {k/9 - 1, (k/3)%3 - 1, k%3 - 1};
@@ -179,7 +188,7 @@ static int run_case(const int nlocal[3], const int dec[3], int mode, int zalign)
   const bool ok = (ndiff == 0);
   printf("%s Q=%d VEC=%d GM=%d local %dx%dx%d zalign %d decomposed %d%d%d %s: %zu of %zu values differ\n",
 	 ok ? "ok  " : "FAIL", Q, VEC, GM, nlocal[0], nlocal[1], nlocal[2], zalign, dec[0], dec[1], dec[2],
-	 mode == 0 ? "halo words" : (mode == 1 ? "halo sectors" : "packed planes"), ndiff, nint);
+	 mode == 0 ? "halo words" : (mode == 1 ? "halo sectors" : (mode == 2 ? "packed planes 1" : "packed planes 2")), ndiff, nint);
   return ok ? 0 : 1;
 }
 
@@ -187,11 +196,11 @@ static int run_case(const int nlocal[3], const int dec[3], int mode, int zalign)
 // propagation on its own, which reads the row-end halo words: against the same with the
 // halo words pushed directly.
 template <class M, int VEC>
-static int run_unpack_case(const int nlocal[3], const int dec[3]) {
+static int run_unpack_case(const int nlocal[3], const int dec[3], int arr) {
   constexpr int Q = M::NVEL;
   const Layout L = make_layout(nlocal, 16, M::NDIM == 2);
   const size_t nsd = (size_t) L.nsd;
-  const size_t nlat = Q*nsd + (size_t) 2*9*L.na[0]*L.na[1] + 16;
+  const size_t nlat = Q*nsd + (size_t) 2*9*L.na[0]*L.na[1]*4 + 16;
   std::vector<double> init(nlat, 0.0), force(3*nsd, 0.0);
   for (size_t k = 0; k < Q*nsd; k++) init[k] = M::wv((int) (k/nsd))*(1.0 + 0.2*(rnd() - 0.5));
   build_ghost_tab<M>(c_ghost);
@@ -207,7 +216,7 @@ static int run_unpack_case(const int nlocal[3], const int dec[3]) {
     std::vector<double> a(init), b(nlat, -1.0);
     KParams P = P0;
     P.push = 1;
-    if (packed) P.zoff = (i64) Q*L.nsd;
+    if (packed) { P.zoff = (i64) Q*L.nsd; P.zwrite = 1; zgeom(L, arr, P); }
     for (int k = 0; k < 27; k++) {
       const int dir[3] = {k/9 - 1, (k/3)%3 - 1, k%3 - 1};
       bool ok = (k != 13);
@@ -228,7 +237,7 @@ static int run_unpack_case(const int nlocal[3], const int dec[3]) {
       const int x0 = (dec[0] && L.h[0]) ? 0 : L.h[0], x1 = L.h[0] + L.n[0] + ((dec[0] && L.h[0]) ? L.h[0] : 0);
       const int y0 = dec[1] ? 0 : L.h[1], y1 = L.h[1] + L.n[1] + (dec[1] ? L.h[1] : 0);
       dim3 ub(256, 1, 1), ug((y1 - y0 + 255)/256, x1 - x0, 2*T.np);
-      for_grid(ug, ub, [&]() { zhalo_unpack_kernel(L, T, a.data(), (i64) Q*L.nsd, x0, x1, y0, y1); });
+      for_grid(ug, ub, [&]() { zhalo_unpack_kernel(L, T, a.data(), (i64) Q*L.nsd, P.zsx, P.zsy, P.zsp, x0, x1, y0, y1); });
     }
     KParams R = P0;
     R.src = a.data(); R.dst = b.data();
@@ -237,8 +246,8 @@ static int run_unpack_case(const int nlocal[3], const int dec[3]) {
   }
   size_t ndiff = 0;
   for (size_t k = 0; k < out[0].size(); k++) if (memcmp(&out[0][k], &out[1][k], 8) != 0) ndiff++;
-  printf("%s Q=%d VEC=%d local %dx%dx%d decomposed %d%d%d unpack + propagation: %zu values differ\n",
-	 ndiff == 0 ? "ok  " : "FAIL", Q, VEC, nlocal[0], nlocal[1], nlocal[2], dec[0], dec[1], dec[2], ndiff);
+  printf("%s Q=%d VEC=%d local %dx%dx%d decomposed %d%d%d arrangement %d unpack + propagation: %zu values differ\n",
+	 ndiff == 0 ? "ok  " : "FAIL", Q, VEC, nlocal[0], nlocal[1], nlocal[2], dec[0], dec[1], dec[2], arr, ndiff);
   return ndiff == 0 ? 0 : 1;
 }
 
@@ -246,7 +255,7 @@ int main(void) {
   int bad = 0;
   const int sizes[4][3] = {{6, 5, 8}, {4, 4, 70}, {3, 9, 16}, {2, 2, 2}};
   const int decs[5][3] = {{1, 1, 1}, {0, 0, 1}, {1, 0, 1}, {0, 1, 1}, {1, 1, 0}};
-  for (int s = 0; s < 4; s++) for (int w = 0; w < 5; w++) for (int mode = 0; mode < 3; mode++) {
+  for (int s = 0; s < 4; s++) for (int w = 0; w < 5; w++) for (int mode = 0; mode < 4; mode++) {
     bad += run_case<D3Q19, 2, 0>(sizes[s], decs[w], mode, 16);
     bad += run_case<D3Q19, 1, 1>(sizes[s], decs[w], mode, 16);
     bad += run_case<D3Q27, 1, 0>(sizes[s], decs[w], mode, 16);
@@ -255,16 +264,16 @@ int main(void) {
     // two-dimensional: device axes (z, x, y), the unit axis first and without halo
     const int s2[2][3] = {{1, 6, 8}, {1, 5, 33}};
     const int d2[3][3] = {{0, 1, 1}, {0, 0, 1}, {0, 1, 0}};
-    for (int s = 0; s < 2; s++) for (int w = 0; w < 3; w++) for (int mode = 0; mode < 3; mode++)
+    for (int s = 0; s < 2; s++) for (int w = 0; w < 3; w++) for (int mode = 0; mode < 4; mode++)
       bad += run_case<D2Q9, 1, 0>(s2[s], d2[w], mode, 16);
   }
-  for (int s = 0; s < 4; s++) for (int w = 0; w < 4; w++) {
-    bad += run_unpack_case<D3Q19, 2>(sizes[s], decs[w]);
-    bad += run_unpack_case<D3Q27, 1>(sizes[s], decs[w]);
+  for (int s = 0; s < 4; s++) for (int w = 0; w < 4; w++) for (int arr = 1; arr <= 2; arr++) {
+    bad += run_unpack_case<D3Q19, 2>(sizes[s], decs[w], arr);
+    bad += run_unpack_case<D3Q27, 1>(sizes[s], decs[w], arr);
   }
-  {
+  for (int arr = 1; arr <= 2; arr++) {
     const int s2[3] = {1, 6, 8}, d2[3] = {0, 1, 1};
-    bad += run_unpack_case<D2Q9, 1>(s2, d2);
+    bad += run_unpack_case<D2Q9, 1>(s2, d2, arr);
   }
   printf(bad ? "%d case(s) FAILED\n" : "all cases identical (%d failures)\n", bad);
   return bad ? 1 : 0;

@@ -36,9 +36,7 @@ def main():
             peak = json.load(fh)
     except Exception:
         pass
-    for name, npt, nbytes, direct in (("grad7_kernel", 7, 40, 1), ("grad27_direct_kernel<0>", 27, 40, 1),
-                                      ("grad27_direct_kernel<1> (next plane prefetched, 80 registers)", 27, 40, 2),
-                                      ("grad27_direct_kernel<2> (next plane prefetched, 94 registers)", 27, 40, 3),
+    for name, npt, nbytes, direct in (("grad7_kernel", 7, 40, 1), ("grad27_direct_kernel", 27, 40, 1),
                                       ("grad27_kernel (planes staged in shared memory)", 27, 40, 0)):
         lat.set_option("grad_direct", direct)
         lat.field_grad_set(npt)
