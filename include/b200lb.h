@@ -125,6 +125,8 @@ long b200lb_nsite(const b200lb_t * h);                          /* host nsite = 
  *                      statistics steps gets 0 in between
  *   "vec"         1/2  lattice sites per thread
  *   "block"       threads per block along the contiguous direction
+ *   "threads"     threads per block of the sweep in all: 0 (default: 256, or 128 for the
+ *                      binary fluid and the schemes that keep ghost modes), 64, 128, 256
  *   "halo_lazy"   0/1  defer the local periodic halo copies until the host looks
  *   "overlap"     0/1  exchange halos on a second stream next to the interior sweep
  *   "direct"      0/1  reduced halo as one message per neighbour direction
@@ -158,6 +160,12 @@ long b200lb_nsite(const b200lb_t * h);                          /* host nsite = 
  *                      starts under that kernel and only threads on a decomposed face wait
  *                      (griddepcontrol.wait). Correct (tests pass with it) but measured to gain
  *                      nothing on B200 (0.8066 -> 0.8057 ms): default 0
+ *   "zpack"       0/1/2 peer-memory halo, single fluid on two lattices: what crosses a face of
+ *                      the contiguous direction goes to dense planes behind the neighbour's
+ *                      lattice array and is pulled from one's own (1, default: one word
+ *                      per column; 2: a 32-byte sector per column) instead of the row-end
+ *                      halo words (0). Same results; anything that looks at halo sites
+ *                      gets them unpacked first
  *   "loopback"    0/1  single rank: send periodic directions through the exchange
  *                      buffers with this GPU as its own neighbour (tests, profiling) */
 int  b200lb_set_option(b200lb_t * h, const char * name, long value);

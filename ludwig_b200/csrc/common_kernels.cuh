@@ -595,10 +595,38 @@ field_stats_kernel(const Layout L, const double * __restrict__ data, double * __
   block_reduce8(q, partial + 8*b);
 }
 
+// One block folds the per-block partials: thread t takes partials t, t + 256, ... in that
+// order (the order fixes the bits of the sums). The loads of eight of its turns are issued
+// before the first addition: with one load latency per turn the 32768 partials of a 256^3
+// sweep took 119 us (profiles/r2_ncu_traffic.md, launch list), which was most of what
+// b200lb_step_diag or a statistics step cost.
+#define STATS_FINAL_AHEAD 8
+
 __global__ void __launch_bounds__(256)
 stats_final_kernel(const double * __restrict__ partial, i64 nblock, double * __restrict__ out) {
   double q[8] = {0.0, 0.0, 1.0e300, -1.0e300, 0.0, 0.0, 0.0, 0.0};
-  for (i64 b = threadIdx.x; b < nblock; b += blockDim.x) {
+  i64 b = threadIdx.x;
+  for (; b + (i64) (STATS_FINAL_AHEAD - 1)*blockDim.x < nblock; b += (i64) STATS_FINAL_AHEAD*blockDim.x) {
+    double v[STATS_FINAL_AHEAD][8];
+    #pragma unroll
+    for (int u = 0; u < STATS_FINAL_AHEAD; u++) {
+      // a partial is 64 bytes on a 64-byte boundary
+      const double2 * src = reinterpret_cast<const double2 *>(partial + 8*(b + (i64) u*blockDim.x));
+      #pragma unroll
+      for (int k = 0; k < 4; k++) {
+	const double2 t = __ldg(src + k);
+	v[u][2*k] = t.x; v[u][2*k + 1] = t.y;
+      }
+    }
+    #pragma unroll
+    for (int u = 0; u < STATS_FINAL_AHEAD; u++) {
+      #pragma unroll
+      for (int k = 0; k < 8; k++) {
+	q[k] = (k == 2) ? fmin(q[k], v[u][k]) : ((k == 3) ? fmax(q[k], v[u][k]) : q[k] + v[u][k]);
+      }
+    }
+  }
+  for (; b < nblock; b += blockDim.x) {
     #pragma unroll
     for (int k = 0; k < 8; k++) {
       const double v = partial[8*b + k];
