@@ -204,6 +204,7 @@ struct b200lb_s {
   double * partial; i64 npartial;
   double * diag; i64 diag_cap, diag_count;   // in-sweep diagnostics: per-block partials of the last collision
   double * stats_dev; double * stats_host;
+  double * stats_chain;      // [2048] scratch of stats_final
   long launches;
   // CUDA events around the sweep launches alone (b200lb_kernel_timer_*)
   cudaEvent_t * tev; int tev_cap, tev_n; bool tev_on;
@@ -532,6 +533,7 @@ static int create_impl(const b200lb_desc_t * desc, b200lb_s * h, const ModelOps 
   h->diag_cap = 4*h->npartial + 4096;
   CU(cudaMalloc(&h->diag, 8*sizeof(double)*h->diag_cap));
   CU(cudaMalloc(&h->stats_dev, 8*sizeof(double)));
+  CU(cudaMalloc(&h->stats_chain, 2048*sizeof(double)));
   CU(cudaMallocHost(&h->stats_host, 8*sizeof(double)));
 
   CU(ops->ghost_upload());
@@ -593,7 +595,7 @@ extern "C" int b200lb_destroy(b200lb_t * h) {
   cudaFree(h->rho); cudaFree(h->u); cudaFree(h->force);
   cudaFree(h->phi2); cudaFree(h->eta); cudaFree(h->jphi); cudaFree(h->le_phibuf); cudaFree(h->le_chbuf);
   cudaFree(h->phi); cudaFree(h->grad); cudaFree(h->delsq); cudaFree(h->noise); cudaFree(h->fnet_dev); cudaFree(h->le_buf);
-  cudaFree(h->partial); cudaFree(h->diag); cudaFree(h->stats_dev); cudaFreeHost(h->stats_host);
+  cudaFree(h->partial); cudaFree(h->diag); cudaFree(h->stats_dev); cudaFree(h->stats_chain); cudaFreeHost(h->stats_host);
   cudaEventDestroy(h->ev0); cudaEventDestroy(h->ev1);
   cudaStreamDestroy(h->s_main);
   cudaStreamDestroy(h->s_comm);
@@ -2063,8 +2065,7 @@ extern "C" int b200lb_hydro_correct_momentum(b200lb_t * h) {
   dim3 block(128, 2, 1);
   dim3 grid((L.n[2] + 127)/128, (L.n[1] + 1)/2, L.n[0]);
   force_sum_kernel<<<grid, block, 0, h->s_main>>>(L, h->force, h->partial);
-  stats_final_kernel<<<1, 256, 0, h->s_main>>>(h->partial, h->npartial, h->stats_dev);
-  CU(cudaGetLastError());
+  CU(stats_final(h->partial, h->npartial, h->stats_dev, h->stats_chain, h->s_main));
   if (h->comm) {
     // MPI_Allreduce(3 doubles, SUM) of src/hydro.c:873, on the device
     NC(g_nccl.AllReduce(h->stats_dev + 4, h->stats_dev + 4, 3, ncclDouble, ncclSum, h->comm, h->s_main));
@@ -2381,9 +2382,8 @@ extern "C" int b200lb_stats(b200lb_t * h, double out[8]) {
   dim3 block(128, 2, 1);
   dim3 grid((L.n[2] + 127)/128, (L.n[1] + 1)/2, L.n[0]);
   CU(h->ops->stats(L, h->lat[h->cur], h->desc.ndist, h->partial, grid, block, h->s_main));
-  stats_final_kernel<<<1, 256, 0, h->s_main>>>(h->partial, h->npartial, h->stats_dev);
-  CU(cudaGetLastError());
-  h->launches += 2;
+  CU(stats_final(h->partial, h->npartial, h->stats_dev, h->stats_chain, h->s_main));
+  h->launches += 3;
   CU(cudaMemcpyAsync(h->stats_host, h->stats_dev, 8*sizeof(double), cudaMemcpyDeviceToHost, h->s_main));
   CU(cudaStreamSynchronize(h->s_main));
   for (int k = 0; k < 8; k++) out[k] = h->stats_host[k];
@@ -2397,9 +2397,8 @@ extern "C" int b200lb_step_diag(b200lb_t * h, double out[8]) {
   if (!h || !out) return fail("null argument");
   if (!h->opt_diag || h->diag_count == 0) return fail("no in-sweep diagnostics: set option diag = 1 before lb_collide");
   if (join_comm(h)) return -1;
-  stats_final_kernel<<<1, 256, 0, h->s_main>>>(h->diag, h->diag_count, h->stats_dev);
-  CU(cudaGetLastError());
-  h->launches++;
+  CU(stats_final(h->diag, h->diag_count, h->stats_dev, h->stats_chain, h->s_main));
+  h->launches += 2;
   CU(cudaMemcpyAsync(h->stats_host, h->stats_dev, 8*sizeof(double), cudaMemcpyDeviceToHost, h->s_main));
   CU(cudaStreamSynchronize(h->s_main));
   for (int k = 0; k < 8; k++) out[k] = h->stats_host[k];
@@ -2767,9 +2766,8 @@ extern "C" int b200lb_field_stats(b200lb_t * h, int field, double * out) {
   dim3 grid((L.n[2] + 127)/128, (L.n[1] + 1)/2, L.n[0]);
   for (int c = 0; c < nf; c++) {
     field_stats_kernel<<<grid, block, 0, h->s_main>>>(L, dev + (i64) c*L.nsd, h->partial);
-    stats_final_kernel<<<1, 256, 0, h->s_main>>>(h->partial, h->npartial, h->stats_dev);
-    CU(cudaGetLastError());
-    h->launches += 2;
+    CU(stats_final(h->partial, h->npartial, h->stats_dev, h->stats_chain, h->s_main));
+    h->launches += 3;
     CU(cudaMemcpyAsync(h->stats_host, h->stats_dev, 8*sizeof(double), cudaMemcpyDeviceToHost, h->s_main));
     CU(cudaStreamSynchronize(h->s_main));
     for (int k = 0; k < 4; k++) out[4*c + k] = h->stats_host[k];
@@ -2791,7 +2789,7 @@ extern "C" int b200lb_field_stats(b200lb_t * h, int field, double * out) {
 // ---------------------------------------------------------------------------
 
 // B200LB_NOALLOC_MAXBLOCK (include/b200lb.h): 65536 blocks of 128 x 2 sites, up to 256^3
-#define B200LB_NOALLOC_DOUBLES  (8*B200LB_NOALLOC_MAXBLOCK + 8)
+#define B200LB_NOALLOC_DOUBLES  (8*B200LB_NOALLOC_MAXBLOCK + 8 + 2048)   // partials, result, the 256 x 8 chain sums of stats_final
 #define B200LB_NOALLOC_MAXDEV   64
 
 static __device__ __align__(256) double g_noalloc_scratch[B200LB_NOALLOC_DOUBLES];
@@ -2847,9 +2845,8 @@ extern "C" int b200lb_field_stats_noalloc(b200lb_t * h, int field, double * out)
   for (int c = 0; c < nf; c++) {
     CU(cudaMemsetAsync(result, 0, 8*sizeof(double), h->s_main));
     field_stats_kernel<<<grid, block, 0, h->s_main>>>(L, dev + (i64) c*L.nsd, scratch);
-    stats_final_kernel<<<1, 256, 0, h->s_main>>>(scratch, nblock, result);
-    CU(cudaGetLastError());
-    h->launches += 2;
+    CU(stats_final(scratch, nblock, result, result + 8, h->s_main));
+    h->launches += 3;
     CU(cudaMemcpyAsync(h->stats_host, result, 8*sizeof(double), cudaMemcpyDeviceToHost, h->s_main));
     CU(cudaStreamSynchronize(h->s_main));
     for (int k = 0; k < 4; k++) out[4*c + k] = h->stats_host[k];

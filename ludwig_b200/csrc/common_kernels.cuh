@@ -595,45 +595,67 @@ field_stats_kernel(const Layout L, const double * __restrict__ data, double * __
   block_reduce8(q, partial + 8*b);
 }
 
-// One block folds the per-block partials: thread t takes partials t, t + 256, ... in that
-// order (the order fixes the bits of the sums). The loads of eight of its turns are issued
-// before the first addition: with one load latency per turn the 32768 partials of a 256^3
-// sweep took 119 us (profiles/r2_ncu_traffic.md, launch list), which was most of what
-// b200lb_step_diag or a statistics step cost.
-#define STATS_FINAL_AHEAD 8
+// Folding the per-block partials of a sweep (8 values per block: two sums, min, max, four
+// sums). The arithmetic is that of ONE block of 256 threads in which thread t takes partials
+// t, t + 256, ... in that order and block_reduce8 folds the 256 results -- that order fixes
+// the bits of the sums. Done literally, every turn of a thread waits for one memory latency:
+// 119 us for the 32768 partials of a 256^3 sweep (profiles/r2_ncu_traffic.md), which was
+// most of what b200lb_step_diag or a statistics step cost, and no more threads or blocks
+// help a dependent chain. The 256 x 8 chains are independent of each other, though:
+// stats_chain_kernel gives 64 of them to each of 32 blocks, which bring the partials in
+// through shared memory 64 turns at a time (every thread loads, nothing waits on an
+// addition) and then add them up in the same order as before; stats_fold_kernel is the old
+// tail. Same bits, two short launches.
+#define STATS_CHAIN_BLOCKS 32     // x 8 threads of the one-block form each
+#define STATS_CHAIN_TURNS  64     // turns staged at a time: 64 x 64 values = 32 KB
+
+__device__ __forceinline__ double stats_combine(const int k, const double q, const double v) {
+  return (k == 2) ? fmin(q, v) : ((k == 3) ? fmax(q, v) : q + v);
+}
+
+// chain[8 t + k], t < 256: what thread t of the one-block form holds for value k
+__global__ void __launch_bounds__(256)
+stats_chain_kernel(const double * __restrict__ partial, const i64 nblock, double * __restrict__ chain) {
+  __shared__ double tile[STATS_CHAIN_TURNS][64];
+  const int tid = threadIdx.x;
+  const int t0 = 8*blockIdx.x;                       // first of this block's eight threads
+  const int l = (tid & 63) >> 3, k = tid & 7;         // the chain thread tid < 64 adds up
+  double q = (k == 2) ? 1.0e300 : ((k == 3) ? -1.0e300 : 0.0);
+  // turns of thread t0 + l: partials t0 + l + 256 i < nblock
+  const i64 mine = (nblock > t0 + l) ? (nblock - (t0 + l) + 255)/256 : 0;
+  const i64 nturn = (nblock + 255)/256;
+  for (i64 i0 = 0; i0 < nturn; i0 += STATS_CHAIN_TURNS) {
+    #pragma unroll
+    for (int e = tid; e < STATS_CHAIN_TURNS*64; e += 256) {
+      const int turn = e >> 6, lk = e & 63;
+      const i64 b = t0 + (lk >> 3) + 256*(i0 + turn);
+      tile[turn][lk] = (b < nblock) ? __ldg(partial + 8*b + (lk & 7)) : 0.0;
+    }
+    __syncthreads();
+    if (tid < 64) {
+      const i64 left = mine - i0;
+      const int n = (left < STATS_CHAIN_TURNS) ? (int) ((left > 0) ? left : 0) : STATS_CHAIN_TURNS;
+      for (int turn = 0; turn < n; turn++) q = stats_combine(k, q, tile[turn][tid]);
+    }
+    __syncthreads();
+  }
+  if (tid < 64) chain[8*(t0 + l) + k] = q;
+}
 
 __global__ void __launch_bounds__(256)
-stats_final_kernel(const double * __restrict__ partial, i64 nblock, double * __restrict__ out) {
-  double q[8] = {0.0, 0.0, 1.0e300, -1.0e300, 0.0, 0.0, 0.0, 0.0};
-  i64 b = threadIdx.x;
-  for (; b + (i64) (STATS_FINAL_AHEAD - 1)*blockDim.x < nblock; b += (i64) STATS_FINAL_AHEAD*blockDim.x) {
-    double v[STATS_FINAL_AHEAD][8];
-    #pragma unroll
-    for (int u = 0; u < STATS_FINAL_AHEAD; u++) {
-      // a partial is 64 bytes on a 64-byte boundary
-      const double2 * src = reinterpret_cast<const double2 *>(partial + 8*(b + (i64) u*blockDim.x));
-      #pragma unroll
-      for (int k = 0; k < 4; k++) {
-	const double2 t = __ldg(src + k);
-	v[u][2*k] = t.x; v[u][2*k + 1] = t.y;
-      }
-    }
-    #pragma unroll
-    for (int u = 0; u < STATS_FINAL_AHEAD; u++) {
-      #pragma unroll
-      for (int k = 0; k < 8; k++) {
-	q[k] = (k == 2) ? fmin(q[k], v[u][k]) : ((k == 3) ? fmax(q[k], v[u][k]) : q[k] + v[u][k]);
-      }
-    }
-  }
-  for (; b < nblock; b += blockDim.x) {
-    #pragma unroll
-    for (int k = 0; k < 8; k++) {
-      const double v = partial[8*b + k];
-      q[k] = (k == 2) ? fmin(q[k], v) : ((k == 3) ? fmax(q[k], v) : q[k] + v);
-    }
-  }
+stats_fold_kernel(const double * __restrict__ chain, double * __restrict__ out) {
+  double q[8];
+  #pragma unroll
+  for (int k = 0; k < 8; k++) q[k] = chain[8*threadIdx.x + k];
   block_reduce8(q, out);
+}
+
+// chain: 2048 doubles of scratch
+static inline cudaError_t stats_final(const double * partial, i64 nblock, double * out, double * chain,
+				      cudaStream_t st) {
+  stats_chain_kernel<<<STATS_CHAIN_BLOCKS, 256, 0, st>>>(partial, nblock, chain);
+  stats_fold_kernel<<<1, 256, 0, st>>>(chain, out);
+  return cudaGetLastError();
 }
 
 // ---------------------------------------------------------------------------
