@@ -349,9 +349,9 @@ int  b200lb_field_stats(b200lb_t * h, int field, double * out);
  * request of this run's operators, for callers that cannot call cudaMalloc (code under CUDA
  * graph capture, tight serving loops, harnesses that forbid it). Same kernels, same result
  * (out[4*c + 0..3] = sum, sum of squares, min, max per component over the interior sites);
- * the per-block partial sums live in a file-scope device array of
- * 8*(B200LB_NOALLOC_MAXBLOCK + 1) doubles (4 MiB) that every GPU loading the library holds
- * until exit. Limits and rules:
+ * the per-block partial sums, the 256 x 8 intermediate sums of their fold and the result live
+ * in a file-scope device array of 8*(B200LB_NOALLOC_MAXBLOCK + 1) + 2048 doubles (4 MiB +
+ * 16 KiB) that every GPU loading the library holds until exit. Limits and rules:
  *   - the lattice must need at most B200LB_NOALLOC_MAXBLOCK blocks of 128 x 2 sites,
  *     ceil(n_z/128)*ceil(n_y/2)*n_x (256^3 fits exactly); larger lattices are refused;
  *   - the field's device planes must exist and hold current values: a field that was never
