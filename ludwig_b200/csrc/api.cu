@@ -610,6 +610,7 @@ static int materialise(b200lb_s * h);
 static int aa_supported(const b200lb_s * h);
 static int join_comm(b200lb_s * h);
 static int flush_halo(b200lb_s * h);
+static int zhalo_flush(b200lb_s * h, cudaStream_t st);
 static int flush_phi_halo(b200lb_s * h);
 static int resolve_ch_force(b200lb_s * h);
 
@@ -626,6 +627,7 @@ extern "C" int b200lb_set_option(b200lb_t * h, const char * name, long v) {
     if (v == h->opt_lattices) return 0;
     if (materialise(h)) return -1;                   // the natural, streamed lattice in lat[cur]
     if (join_comm(h)) return -1;
+    if (zhalo_flush(h, h->s_main)) return -1;        // the arrays may change places below
     CU(cudaStreamSynchronize(h->s_main));
     if (v == 1) {
       if (h->p2p_ready && h->cur == 1) {
